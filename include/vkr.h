@@ -1,0 +1,218 @@
+/*
+ * vkr.h — C-ABI of the B200-native raster + shading path ("libvkr").
+ *
+ * This is the drop-in boundary for the per-frame path of mzwang34/vk_renderer:
+ * everything VulkanEngine::draw() records into a VkCommandBuffer (shadow pass,
+ * background, geometry, skybox, postprocess, present blit) is replaced by the
+ * calls below.  Plain C types only: no CUDA, torch or C++ types cross the ABI.
+ *
+ * Each export cites the reference interface it replaces as
+ * (path:line, relative to the reference checkout).
+ *
+ * Threading: one host thread per VkrDevice (the reference is single-threaded,
+ * src/vk_engine_run.cpp:62-64); different devices may be driven concurrently.
+ * Errors: every call returns VKR_SUCCESS (0) or a negative VkrResult; nothing
+ * aborts (the reference aborts in VK_CHECK, src/vk_types.h:171-178).
+ * There is no CPU fallback: vkr_create fails with VKR_ERROR_NO_DEVICE when no
+ * sm_100 class CUDA device is usable.
+ */
+#ifndef VKR_H
+#define VKR_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VKR_NUM_CASCADES 4          /* src/vk_types.h:16, shaders/common.glsl:4 */
+#define VKR_MAX_BINDLESS 4096       /* src/vk_engine_init.cpp:226,252 */
+#define VKR_FRAME_OVERLAP 2         /* src/vk_engine.h:10 */
+
+typedef enum VkrResult {
+    VKR_SUCCESS = 0,
+    VKR_ERROR_INVALID_ARGUMENT = -1,
+    VKR_ERROR_OUT_OF_MEMORY = -2,
+    VKR_ERROR_CUDA = -3,
+    VKR_ERROR_NO_DEVICE = -4,
+    VKR_ERROR_CAPACITY = -5
+} VkrResult;
+
+typedef struct VkrDevice VkrDevice;   /* opaque */
+typedef uint32_t VkrMesh;             /* handle: MeshAsset::meshBuffer      */
+typedef uint32_t VkrImage;            /* handle: AllocatedImage             */
+typedef uint32_t VkrMaterial;         /* handle: MaterialInstance           */
+
+/* struct Vertex — src/vk_types.h:85-91, shaders/common.glsl:6-16 (48 B AoS). */
+typedef struct VkrVertex {
+    float position[3];
+    float uv_x;
+    float normal[3];
+    float uv_y;
+    float color[4];
+} VkrVertex;
+
+/* struct GPUSceneData — src/vk_types.h:93-102, shaders/common.glsl:18-28
+ * (scalar layout, 512 B, column-major matrices).
+ * sunlightDirection.w = shadowMode and sunlightColor.w = enableShadows are
+ * written by the engine exactly as src/vk_engine_run.cpp:124-125 does. */
+typedef struct VkrGPUSceneData {
+    float view[16];
+    float proj[16];
+    float viewproj[16];
+    float lightViewproj[VKR_NUM_CASCADES][16];
+    float cascadeDistances[VKR_NUM_CASCADES];
+    float ambientColor[4];
+    float sunlightDirection[4];
+    float sunlightColor[4];
+} VkrGPUSceneData;
+
+/* struct MaterialConstants — src/vk_materials.h:14-21 (48 B UBO). */
+typedef struct VkrMaterialConstants {
+    float colorFactors[4];
+    float metal_rough_factors[4];
+    int32_t albedoID;
+    int32_t normalID;
+    int32_t metalRoughID;
+    int32_t padding;
+} VkrMaterialConstants;
+
+/* enum class MaterialPass — src/vk_materials.h:8-12. */
+typedef enum VkrMaterialPass {
+    VKR_PASS_MAIN_COLOR = 0,   /* "Opaque": depth write, no blend (src/vk_engine_init.cpp:536-543) */
+    VKR_PASS_TRANSPARENT = 1,  /* additive blend, depth test, no depth write (:545-547) */
+    VKR_PASS_OTHER = 2
+} VkrMaterialPass;
+
+/* struct RenderObject — src/vk_types.h:130-137 with the two raw pointers
+ * replaced by handles.  Array order = submission order = depth tie-break
+ * order (later object wins equal depth under LESS_OR_EQUAL). */
+typedef struct VkrRenderObject {
+    VkrMesh mesh;
+    VkrMaterial material;
+    float transform[16];       /* column-major world matrix */
+    uint32_t indexCount;
+    uint32_t firstIndex;
+} VkrRenderObject;
+
+/* struct ComputePushConstants — src/vk_types.h:50-55, gradient_color.comp:8-14. */
+typedef struct VkrComputePushConstants {
+    float data1[4];
+    float data2[4];
+    float data3[4];
+    float data4[4];
+} VkrComputePushConstants;
+
+typedef enum VkrFormat {
+    VKR_FORMAT_R8G8B8A8_UNORM = 0,
+    VKR_FORMAT_R8G8B8A8_SRGB = 1
+} VkrFormat;
+
+typedef enum VkrSampler {
+    VKR_SAMPLER_NEAREST = 0,   /* _defaultSamplerNearest, src/vk_engine_init.cpp:346-348 */
+    VKR_SAMPLER_LINEAR = 1     /* _defaultSamplerLinear,  src/vk_engine_init.cpp:343-344 */
+} VkrSampler;
+
+typedef enum VkrFragShader {
+    VKR_FRAG_MESH_PBR = 0,     /* shaders/mesh_pbr.frag (what the engine loads, src/vk_engine_init.cpp:530) */
+    VKR_FRAG_MESH_LAMBERT = 1  /* shaders/mesh.frag (BASELINE config 1) */
+} VkrFragShader;
+
+/* The ImGui toggles of src/vk_engine.h:112-126 plus the dynamic state that
+ * draw_geometry sets (scissor, src/vk_engine_run.cpp:266-269). */
+typedef struct VkrFrameParams {
+    int32_t enableShadows;       /* _enableShadows */
+    int32_t shadowMode;          /* _shadowMode: 0 hard, 1 PCF, 2 PCSS, 3 CSM */
+    int32_t enableBackground;    /* _enableBackground */
+    int32_t enablePostprocess;   /* _enablePostprocess */
+    int32_t enableSkybox;        /* _skyboxMesh != nullptr && cubemap set */
+    int32_t fragShader;          /* VkrFragShader */
+    int32_t scissor[4];          /* x, y, w, h; w==0||h==0 -> full extent.  Used for sort-first sharding. */
+    VkrComputePushConstants background; /* backgroundEffects[0].data */
+} VkrFrameParams;
+
+typedef struct VkrConfig {
+    int32_t device;            /* CUDA device ordinal */
+    uint32_t width, height;    /* _drawExtent (src/vk_engine_init.cpp:93-101) */
+    uint32_t shadowExtent;     /* _shadowExtent, 2048 (src/vk_engine.h:107); 0 -> 2048 */
+    void* stream;              /* optional cudaStream_t to submit on; NULL -> own stream */
+    uint32_t flags;            /* VKR_CONFIG_* */
+} VkrConfig;
+
+#define VKR_CONFIG_TIMINGS 1u  /* record CUDA events around every pass */
+
+/* struct EngineStats — src/vk_types.h:78-83. */
+typedef struct VkrEngineStats {
+    float frametime;           /* ms, device time of the last completed frame (needs VKR_CONFIG_TIMINGS) */
+    int32_t triangle_count;
+    int32_t drawcall_count;
+    float mesh_draw_time;      /* ms, geometry+raster passes only */
+} VkrEngineStats;
+
+typedef enum VkrTarget {
+    VKR_TARGET_RGBA8 = 0,      /* presented image, R,G,B,A bytes, W*H*4 (the swapchain blit, src/vk_engine_run.cpp:159-161) */
+    VKR_TARGET_HDR16F = 1,     /* _drawImage, RGBA16F, W*H*8 */
+    VKR_TARGET_DEPTH = 2,      /* _depthImage, D32, W*H*4 */
+    VKR_TARGET_SHADOW = 3,     /* _shadowImage, D32, S*S*4*NUM_CASCADES */
+    VKR_TARGET_PRIMID = 4      /* uint32 per pixel: submission-order primitive id, 0xFFFFFFFF = none */
+} VkrTarget;
+
+/* Pass indices for vkr_get_timings. */
+enum { VKR_T_UPLOAD = 0, VKR_T_SHADOW, VKR_T_GEOMETRY, VKR_T_SHADE, VKR_T_TRANSPARENT, VKR_T_POST, VKR_T_TOTAL, VKR_T_COUNT };
+
+/* init_vulkan + init_swapchain + init_shadow_resources + init_default_data
+ * (src/vk_engine_init.cpp:42-138,318-402). Seeds bindless slot 0 with the
+ * default normal texture, NEAREST (the reference's double write, :351-355). */
+int vkr_create(const VkrConfig* cfg, VkrDevice** out);
+void vkr_destroy(VkrDevice* dev);
+
+/* upload_mesh(std::span<uint32_t>, std::span<Vertex>) — src/vk_loader.cpp:186-225.
+ * Host arrays stay owned by the caller; the device repacks AoS -> SoA. */
+int vkr_upload_mesh(VkrDevice* dev, const uint32_t* indices, size_t indexCount,
+                    const VkrVertex* vertices, size_t vertexCount, VkrMesh* out);
+
+/* create_image(void*, VkExtent3D, VkFormat, usage, mipmapped) — src/vk_loader.cpp:109-165;
+ * mip chain as generate_mipmaps builds it (src/vk_images.cpp:64-157). */
+int vkr_create_image(VkrDevice* dev, const void* rgba8, uint32_t width, uint32_t height,
+                     VkrFormat format, int mipmapped, VkrImage* out);
+
+/* update_bindless_texture(int, VkImageView, VkSampler) — src/vk_loader.cpp:167-184. */
+int vkr_update_bindless_texture(VkrDevice* dev, int index, VkrImage image, VkrSampler sampler);
+
+/* load_cubemap's upload half — src/vk_loader.cpp:521-558 (KTX decode is out of scope).
+ * faces in Vulkan layer order +X,-X,+Y,-Y,+Z,-Z, each width*height*4 bytes. */
+int vkr_set_cubemap(VkrDevice* dev, const void* const faces[6], uint32_t width, uint32_t height,
+                    VkrFormat format, int mipmapped);
+
+/* MaterialSystem::build_instance — src/vk_materials.cpp:60-85. */
+int vkr_build_material(VkrDevice* dev, const VkrMaterialConstants* params, VkrMaterialPass pass,
+                       VkrMaterial* out);
+
+/* draw_shadow + draw_background + draw_geometry + draw_skybox + draw_postprocess
+ * + present blit — src/vk_engine_run.cpp:140-161,234-408.  Asynchronous. */
+int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject* objects,
+             size_t objectCount, const VkrFrameParams* params);
+
+/* Headless replacement of present (src/vk_engine_run.cpp:159-190). */
+int vkr_readback(VkrDevice* dev, VkrTarget what, void* dst, size_t dstBytes);          /* synchronous */
+int vkr_readback_async(VkrDevice* dev, VkrTarget what, void* pinnedDst, size_t dstBytes); /* last drawn frame */
+int vkr_sync(VkrDevice* dev);
+
+/* stats.triangle_count / drawcall_count — src/vk_engine_run.cpp:70-71,309-310. */
+int vkr_stats(VkrDevice* dev, VkrEngineStats* out);
+int vkr_get_timings(VkrDevice* dev, float* msOut, int count);      /* last synced frame */
+
+/* Raw device pointer of a target of the last drawn frame (for NCCL gathers). */
+int vkr_device_ptr(VkrDevice* dev, VkrTarget what, void** ptr, size_t* bytes);
+
+/* Number of kernel launches issued by the last vkr_draw. */
+int vkr_launch_count(VkrDevice* dev);
+
+const char* vkr_last_error(VkrDevice* dev);
+const char* vkr_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VKR_H */

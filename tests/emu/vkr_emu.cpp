@@ -1,0 +1,245 @@
+// vkr_emu.cpp — TEST-ONLY host emulation of the CUDA kernels' per-thread bodies.
+//
+// There is no GPU in the development container, so this harness compiles the very same
+// __host__ __device__ functions the kernels call (vkr_raster.cuh, vkr_shade.cuh,
+// vkr_frameprep.h) with g++ and runs "one thread per triangle / per pixel" as plain loops.
+// It lets the CPU test-suite check the kernels' logic against the oracle before a GPU run.
+// It is NOT part of the product: libvkr.so does not contain it and nothing in
+// vk_renderer_b200/ references it.  Warp-cooperative code paths (lane-strided loops) run
+// with nlanes = 32 lanes executed sequentially.
+//
+// Build: g++ -O2 -std=c++17 -ffp-contract=off -fPIC -shared (tests/conftest.py does it).
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../vk_renderer_b200/csrc/vkr_internal.h"
+#include "../../vk_renderer_b200/csrc/vkr_raster.cuh"
+#include "../../vk_renderer_b200/csrc/vkr_shade.cuh"
+#include "../../vk_renderer_b200/csrc/vkr_frameprep.h"
+
+using namespace vkr;
+
+struct EmuImage {
+    std::vector<uchar4> data; uint32_t w, h, levels; uint32_t mipOffset[16]; int format; bool cutout;
+};
+struct EmuMesh { std::vector<float4> pos, a, b; std::vector<uint32_t> idx; };
+
+struct EmuDevice {
+    uint32_t W, H, S;
+    std::vector<EmuMesh*> meshStore;
+    std::vector<DMesh> meshes;
+    std::vector<EmuImage*> images;
+    std::vector<DTexture> tex;
+    DTexture cube[6]; bool haveCube = false;
+    std::vector<DMaterial> materials;
+    std::vector<uint64_t> vis;
+    std::vector<uint32_t> shadowBits;
+    std::vector<uint16_t> hdr;
+    std::vector<uint32_t> rgba8;
+    std::vector<LargeTri> ltris; std::vector<LargeItem> litems; uint32_t counters[4];
+    float lut[256];
+    FramePlan plan;
+    VkrEngineStats stats{};
+    std::string err;
+};
+
+static uint32_t srgb8(float l) {
+    if (!(l > 0.0f)) return 0u;
+    if (l >= 1.0f) return 255u;
+    float s = l <= 0.0031308f ? l * 12.92f : 1.055f * powf(l, 1.0f / 2.4f) - 0.055f;
+    return unorm8(s);
+}
+
+static EmuImage* build_image(EmuDevice* d, const void* rgba8, uint32_t w, uint32_t h, int fmt, int mipmapped) {
+    EmuImage* im = new EmuImage();
+    im->w = w; im->h = h; im->format = fmt;
+    im->levels = mipmapped ? (uint32_t)std::floor(std::log2((double)std::max(w, h))) + 1 : 1;
+    size_t total = 0;
+    for (uint32_t l = 0; l < im->levels; ++l) { im->mipOffset[l] = (uint32_t)total; total += (size_t)std::max(1u, w >> l) * std::max(1u, h >> l); }
+    im->data.resize(total);
+    std::memcpy(im->data.data(), rgba8, (size_t)w * h * 4);
+    im->cutout = false;
+    for (size_t i = 0; i < (size_t)w * h; ++i) if (im->data[i].w < 128) { im->cutout = true; break; }
+    for (uint32_t l = 0; l + 1 < im->levels; ++l) {   // same arithmetic as mip_blit_kernel
+        int sw = std::max(1u, w >> l), sh = std::max(1u, h >> l), dw = std::max(1u, w >> (l + 1)), dh = std::max(1u, h >> (l + 1));
+        const uchar4* src = im->data.data() + im->mipOffset[l];
+        uchar4* dst = im->data.data() + im->mipOffset[l + 1];
+        float scx = (float)sw / (float)dw, scy = (float)sh / (float)dh;
+        for (int y = 0; y < dh; ++y) for (int x = 0; x < dw; ++x) {
+            float u = ((float)x + 0.5f) * scx - 0.5f, v = ((float)y + 0.5f) * scy - 0.5f;
+            float fu = floorf(u), fv = floorf(v), a = u - fu, b = v - fv;
+            int x0 = std::min(std::max((int)fu, 0), sw - 1), x1 = std::min(std::max((int)fu + 1, 0), sw - 1);
+            int y0 = std::min(std::max((int)fv, 0), sh - 1), y1 = std::min(std::max((int)fv + 1, 0), sh - 1);
+            uchar4 q[4] = {src[(size_t)y0 * sw + x0], src[(size_t)y0 * sw + x1], src[(size_t)y1 * sw + x0], src[(size_t)y1 * sw + x1]};
+            float wgt[4] = {(1.0f - a) * (1.0f - b), a * (1.0f - b), (1.0f - a) * b, a * b};
+            float c[4] = {0, 0, 0, 0};
+            for (int k = 0; k < 4; ++k) {
+                float r, g, bl;
+                if (fmt == 1) { r = d->lut[q[k].x]; g = d->lut[q[k].y]; bl = d->lut[q[k].z]; }
+                else { r = q[k].x / 255.0f; g = q[k].y / 255.0f; bl = q[k].z / 255.0f; }
+                float al = q[k].w / 255.0f;
+                c[0] = c[0] + r * wgt[k]; c[1] = c[1] + g * wgt[k]; c[2] = c[2] + bl * wgt[k]; c[3] = c[3] + al * wgt[k];
+            }
+            uchar4 o;
+            if (fmt == 1) { o.x = srgb8(c[0]); o.y = srgb8(c[1]); o.z = srgb8(c[2]); }
+            else { o.x = unorm8(c[0]); o.y = unorm8(c[1]); o.z = unorm8(c[2]); }
+            o.w = unorm8(c[3]);
+            dst[(size_t)y * dw + x] = o;
+        }
+    }
+    return im;
+}
+static DTexture make_tex(const EmuImage* im, int sampler) {
+    DTexture t{};
+    t.data = im->data.data(); t.w = im->w; t.h = im->h; t.levels = im->levels;
+    t.flags = (im->format == 1 ? 1u : 0u) | (sampler == 1 ? 2u : 0u) | (im->cutout ? 4u : 0u);
+    std::memcpy(t.mipOffset, im->mipOffset, sizeof(t.mipOffset));
+    return t;
+}
+
+extern "C" {
+
+int emu_create_image(EmuDevice* d, const void* rgba8, uint32_t w, uint32_t h, int fmt, int mipmapped, uint32_t* out);
+int emu_update_bindless_texture(EmuDevice* d, int index, uint32_t image, int sampler);
+
+int emu_create(const VkrConfig* cfg, EmuDevice** out) {
+    EmuDevice* d = new EmuDevice();
+    d->W = cfg->width; d->H = cfg->height; d->S = cfg->shadowExtent ? cfg->shadowExtent : 2048;
+    size_t px = (size_t)d->W * d->H;
+    d->vis.assign(px, VIS_CLEAR);
+    d->hdr.assign(px * 4, 0); d->rgba8.assign(px, 0);
+    d->shadowBits.assign((size_t)d->S * d->S * VKR_NUM_CASCADES, DEPTH_ONE_BITS);
+    d->tex.assign(VKR_MAX_BINDLESS, DTexture{});
+    d->ltris.resize(1 << 16); d->litems.resize(1 << 20);
+    for (int i = 0; i < 256; ++i) { double c = i / 255.0; d->lut[i] = (float)(c <= 0.04045 ? c / 12.92 : std::pow((c + 0.055) / 1.055, 2.4)); }
+    uint32_t nd = 0xFFFF8080u, img;
+    emu_create_image(d, &nd, 1, 1, 0, 0, &img);
+    emu_update_bindless_texture(d, 0, img, 0);
+    *out = d;
+    return 0;
+}
+void emu_destroy(EmuDevice* d) {
+    if (!d) return;
+    for (auto* m : d->meshStore) delete m;
+    for (auto* i : d->images) delete i;
+    delete d;
+}
+int emu_upload_mesh(EmuDevice* d, const uint32_t* idx, size_t ni, const VkrVertex* v, size_t nv, uint32_t* out) {
+    EmuMesh* m = new EmuMesh();
+    m->idx.assign(idx, idx + ni);
+    m->pos.resize(nv); m->a.resize(nv); m->b.resize(nv);
+    for (size_t i = 0; i < nv; ++i) {   // repack_vertices_kernel
+        m->pos[i] = make_float4(v[i].position[0], v[i].position[1], v[i].position[2], 1.0f);
+        m->a[i] = make_float4(v[i].normal[0], v[i].normal[1], v[i].normal[2], v[i].uv_x);
+        m->b[i] = make_float4(v[i].color[0], v[i].color[1], v[i].color[2], v[i].uv_y);
+    }
+    d->meshStore.push_back(m);
+    DMesh dm{m->pos.data(), m->a.data(), m->b.data(), m->idx.data(), (uint32_t)nv, (uint32_t)ni};
+    d->meshes.push_back(dm);
+    *out = (uint32_t)d->meshes.size() - 1;
+    return 0;
+}
+int emu_create_image(EmuDevice* d, const void* rgba8, uint32_t w, uint32_t h, int fmt, int mipmapped, uint32_t* out) {
+    d->images.push_back(build_image(d, rgba8, w, h, fmt, mipmapped));
+    *out = (uint32_t)d->images.size() - 1;
+    return 0;
+}
+int emu_update_bindless_texture(EmuDevice* d, int index, uint32_t image, int sampler) {
+    d->tex[index] = make_tex(d->images[image], sampler);
+    return 0;
+}
+int emu_set_cubemap(EmuDevice* d, const void* const faces[6], uint32_t w, uint32_t h, int fmt, int mipmapped) {
+    for (int f = 0; f < 6; ++f) {
+        EmuImage* im = build_image(d, faces[f], w, h, fmt, mipmapped);
+        d->images.push_back(im);
+        d->cube[f] = make_tex(im, 1);
+    }
+    d->haveCube = true;
+    return 0;
+}
+int emu_build_material(EmuDevice* d, const VkrMaterialConstants* p, int pass, uint32_t* out) {
+    DMaterial m;
+    std::memcpy(m.colorFactors, p->colorFactors, 16);
+    std::memcpy(m.metalRough, p->metal_rough_factors, 16);
+    m.albedoID = p->albedoID; m.normalID = p->normalID; m.metalRoughID = p->metalRoughID; m.pass = pass;
+    d->materials.push_back(m);
+    *out = (uint32_t)d->materials.size() - 1;
+    return 0;
+}
+
+}  // extern "C"
+
+template <bool SHADOW>
+static void run_pass(EmuDevice* d, const FramePlan& plan, RasterTarget rt, const float* mvps, uint32_t stride, unsigned nChunks) {
+    Queues q{d->ltris.data(), d->litems.data(), d->counters, (uint32_t)d->ltris.size(), (uint32_t)d->litems.size()};
+    d->counters[0] = d->counters[1] = d->counters[2] = 0;
+    for (unsigned c = 0; c < nChunks; ++c) {                 // geometry_kernel
+        const DChunk ch = plan.chunks[c];
+        const DObject& o = plan.objects[ch.obj];
+        for (uint32_t t = 0; t < GEOM_BLOCK; ++t) {
+            uint32_t tri = ch.firstTri + t;
+            if (tri >= o.triCount) break;
+            if (SHADOW) { DepthSink s{rt.depthBits, rt.width}; geometry_triangle(mvps + (size_t)ch.obj * stride, o.pos, o.idx, tri, 0u, rt, q, s); }
+            else { uint32_t seq = o.primBase + tri; VisSink s{rt.vis, rt.width, 0xFFFFFFFEu - seq}; geometry_triangle(mvps + (size_t)ch.obj * stride, o.pos, o.idx, tri, seq, rt, q, s); }
+        }
+    }
+    for (uint32_t i = 0; i < d->counters[1]; ++i) {          // large_raster_kernel
+        const LargeItem it = q.items[i];
+        const LargeTri lt = q.tris[it.tri];
+        for (int lane = 0; lane < 32; ++lane) {
+            if (SHADOW) { DepthSink s{rt.depthBits, rt.width}; raster_item(lt, it, s, lane, 32); }
+            else { VisSink s{rt.vis, rt.width, 0xFFFFFFFEu - lt.seq}; raster_item(lt, it, s, lane, 32); }
+        }
+    }
+}
+
+extern "C" {
+
+int emu_draw(EmuDevice* d, const VkrGPUSceneData* scene, const VkrRenderObject* objs, size_t n, const VkrFrameParams* fp) {
+    FramePlan& plan = d->plan;
+    std::string why = plan_frame(scene, objs, n, fp, d->meshes, d->materials, d->W, d->H, d->S, plan);
+    if (!why.empty()) { d->err = why; return VKR_ERROR_INVALID_ARGUMENT; }
+    const unsigned nChunks = (unsigned)plan.chunks.size();
+    for (int layer = 0; layer < plan.shadowLayers; ++layer) {
+        RasterTarget rt = plan.shadowTarget;
+        rt.depthBits = d->shadowBits.data() + (size_t)layer * d->S * d->S;
+        std::fill(rt.depthBits, rt.depthBits + (size_t)d->S * d->S, DEPTH_ONE_BITS);
+        run_pass<true>(d, plan, rt, plan.shadowMvp.data() + (size_t)layer * n * 16, 16, nChunks);
+    }
+    RasterTarget rt = plan.mainTarget;
+    rt.vis = d->vis.data();
+    std::fill(d->vis.begin(), d->vis.end(), VIS_CLEAR);
+    unsigned opaqueChunks = 0;
+    while (opaqueChunks < nChunks && plan.chunks[opaqueChunks].obj < plan.opaqueCount) ++opaqueChunks;
+    run_pass<false>(d, plan, rt, (const float*)plan.objects.data(), sizeof(DObject) / 4, opaqueChunks);
+    if (d->counters[2]) { d->err = "queue overflow"; return VKR_ERROR_CAPACITY; }
+    ShadeBuffers sb{};
+    sb.vis = d->vis.data(); sb.objects = plan.objects.data(); sb.primBase = plan.primBase.data();
+    sb.materials = d->materials.data(); sb.textures = d->tex.data(); sb.cube = d->haveCube ? d->cube : nullptr;
+    sb.shadow = reinterpret_cast<const float*>(d->shadowBits.data());
+    sb.hdr = d->hdr.data(); sb.rgba8 = d->rgba8.data(); sb.srgbLut = d->lut;
+    for (int py = plan.sc.sy0; py < plan.sc.sy1; ++py)
+        for (int px = plan.sc.sx0; px < plan.sc.sx1; ++px) shade_pixel(plan.sc, sb, px, py);
+    d->stats.drawcall_count = (int)n; d->stats.triangle_count = (int)plan.totalTris;
+    return 0;
+}
+int emu_readback(EmuDevice* d, int what, void* dst, size_t bytes) {
+    size_t px = (size_t)d->W * d->H;
+    switch (what) {
+        case VKR_TARGET_RGBA8: if (bytes < px * 4) return -1; std::memcpy(dst, d->rgba8.data(), px * 4); return 0;
+        case VKR_TARGET_HDR16F: if (bytes < px * 8) return -1; std::memcpy(dst, d->hdr.data(), px * 8); return 0;
+        case VKR_TARGET_SHADOW: std::memcpy(dst, d->shadowBits.data(), d->shadowBits.size() * 4); return 0;
+        case VKR_TARGET_DEPTH: for (size_t i = 0; i < px; ++i) ((uint32_t*)dst)[i] = (uint32_t)(d->vis[i] >> 32); return 0;
+        case VKR_TARGET_PRIMID:
+            for (size_t i = 0; i < px; ++i) { uint32_t lo = (uint32_t)d->vis[i]; ((uint32_t*)dst)[i] = lo == VIS_EMPTY_LO ? 0xFFFFFFFFu : 0xFFFFFFFEu - lo; }
+            return 0;
+    }
+    return -1;
+}
+int emu_stats(EmuDevice* d, VkrEngineStats* out) { *out = d->stats; return 0; }
+const char* emu_last_error(EmuDevice* d) { return d->err.c_str(); }
+
+}  // extern "C"

@@ -1,0 +1,300 @@
+"""ctypes view of include/vkr.h.
+
+`Renderer` binds one shared library exporting the vkr C-ABI.  The product binds
+`libvkr.so` (prefix ``vkr_``); the test-suite binds the CPU oracle, which exports
+the same entry points with prefix ``ork_`` (oracle/ork.h), through the same class so
+that parity tests issue literally the same calls to both.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import numpy as np
+
+NUM_CASCADES = 4
+MAX_BINDLESS = 4096
+
+SUCCESS = 0
+FORMAT_UNORM, FORMAT_SRGB = 0, 1
+SAMPLER_NEAREST, SAMPLER_LINEAR = 0, 1
+PASS_MAIN_COLOR, PASS_TRANSPARENT, PASS_OTHER = 0, 1, 2
+FRAG_PBR, FRAG_LAMBERT = 0, 1
+TARGET_RGBA8, TARGET_HDR16F, TARGET_DEPTH, TARGET_SHADOW, TARGET_PRIMID = range(5)
+CONFIG_TIMINGS = 1
+T_NAMES = ["upload", "shadow", "geometry", "shade", "transparent", "post", "total"]
+
+# struct Vertex (src/vk_types.h:85-91), 48 bytes
+VERTEX_DTYPE = np.dtype(
+    [("position", "<f4", 3), ("uv_x", "<f4"), ("normal", "<f4", 3), ("uv_y", "<f4"), ("color", "<f4", 4)]
+)
+assert VERTEX_DTYPE.itemsize == 48
+
+# struct RenderObject with handles (include/vkr.h), 80 bytes
+RENDER_OBJECT_DTYPE = np.dtype(
+    [("mesh", "<u4"), ("material", "<u4"), ("transform", "<f4", 16), ("indexCount", "<u4"), ("firstIndex", "<u4")]
+)
+assert RENDER_OBJECT_DTYPE.itemsize == 80
+
+
+class GPUSceneData(C.Structure):
+    """struct GPUSceneData (src/vk_types.h:93-102) — 512 bytes, column-major matrices."""
+
+    _fields_ = [
+        ("view", C.c_float * 16),
+        ("proj", C.c_float * 16),
+        ("viewproj", C.c_float * 16),
+        ("lightViewproj", (C.c_float * 16) * NUM_CASCADES),
+        ("cascadeDistances", C.c_float * NUM_CASCADES),
+        ("ambientColor", C.c_float * 4),
+        ("sunlightDirection", C.c_float * 4),
+        ("sunlightColor", C.c_float * 4),
+    ]
+
+
+assert C.sizeof(GPUSceneData) == 512
+
+
+class MaterialConstants(C.Structure):
+    """struct MaterialConstants (src/vk_materials.h:14-21) — 48 bytes."""
+
+    _fields_ = [
+        ("colorFactors", C.c_float * 4),
+        ("metal_rough_factors", C.c_float * 4),
+        ("albedoID", C.c_int32),
+        ("normalID", C.c_int32),
+        ("metalRoughID", C.c_int32),
+        ("padding", C.c_int32),
+    ]
+
+
+assert C.sizeof(MaterialConstants) == 48
+
+
+class ComputePushConstants(C.Structure):
+    _fields_ = [("data1", C.c_float * 4), ("data2", C.c_float * 4), ("data3", C.c_float * 4), ("data4", C.c_float * 4)]
+
+
+class FrameParams(C.Structure):
+    _fields_ = [
+        ("enableShadows", C.c_int32),
+        ("shadowMode", C.c_int32),
+        ("enableBackground", C.c_int32),
+        ("enablePostprocess", C.c_int32),
+        ("enableSkybox", C.c_int32),
+        ("fragShader", C.c_int32),
+        ("scissor", C.c_int32 * 4),
+        ("background", ComputePushConstants),
+    ]
+
+
+class Config(C.Structure):
+    _fields_ = [
+        ("device", C.c_int32),
+        ("width", C.c_uint32),
+        ("height", C.c_uint32),
+        ("shadowExtent", C.c_uint32),
+        ("stream", C.c_void_p),
+        ("flags", C.c_uint32),
+    ]
+
+
+class EngineStats(C.Structure):
+    _fields_ = [
+        ("frametime", C.c_float),
+        ("triangle_count", C.c_int32),
+        ("drawcall_count", C.c_int32),
+        ("mesh_draw_time", C.c_float),
+    ]
+
+
+# every symbol include/vkr.h declares (tests check the library exports them all)
+VKR_SYMBOLS = [
+    "create", "destroy", "upload_mesh", "create_image", "update_bindless_texture", "set_cubemap",
+    "build_material", "draw", "readback", "readback_async", "sync", "stats", "get_timings",
+    "device_ptr", "launch_count", "last_error", "version",
+]
+
+
+class VkrError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"vkr error {code}: {msg}")
+        self.code = code
+
+
+def default_frame_params(**kw) -> FrameParams:
+    fp = FrameParams()
+    fp.background.data1[:] = (1.0, 0.0, 0.0, 1.0)  # src/vk_engine_init.cpp:504-505
+    fp.background.data2[:] = (0.0, 0.0, 1.0, 1.0)
+    for k, v in kw.items():
+        if k == "scissor":
+            fp.scissor[:] = v
+        else:
+            setattr(fp, k, v)
+    return fp
+
+
+def make_scene_data(view, proj, light_viewproj=None, cascade_distances=None, ambient=(0.1, 0.1, 0.1, 1.0),
+                    sun_dir=(0.5, -1.0, -0.5, 0.0), sun_color=(1.0, 1.0, 1.0, 1.0), shadow_mode=0,
+                    enable_shadows=False, viewproj=None) -> GPUSceneData:
+    """Fill GPUSceneData the way VulkanEngine::draw does (src/vk_engine_run.cpp:107-125).
+    Matrices are numpy (4,4) arrays in math (row, col) convention; stored column-major."""
+    sd = GPUSceneData()
+    view = np.asarray(view, np.float32)
+    proj = np.asarray(proj, np.float32)
+    vp = (proj @ view).astype(np.float32) if viewproj is None else np.asarray(viewproj, np.float32)
+    sd.view[:] = view.T.reshape(-1)
+    sd.proj[:] = proj.T.reshape(-1)
+    sd.viewproj[:] = vp.T.reshape(-1)
+    for i in range(NUM_CASCADES):
+        m = np.eye(4, dtype=np.float32) if light_viewproj is None else np.asarray(light_viewproj[i], np.float32)
+        sd.lightViewproj[i][:] = m.T.reshape(-1)
+    cd = cascade_distances if cascade_distances is not None else (12.8186712, 26.6061382, 46.4039001, 100.0)
+    sd.cascadeDistances[:] = cd
+    sd.ambientColor[:] = ambient
+    sd.sunlightDirection[:] = (*sun_dir[:3], float(shadow_mode))
+    sd.sunlightColor[:] = (*sun_color[:3], 1.0 if enable_shadows else 0.0)
+    return sd
+
+
+class Renderer:
+    """One VkrDevice behind the C-ABI of `lib` (prefix 'vkr' = product, 'ork' = oracle)."""
+
+    def __init__(self, lib: C.CDLL, prefix: str, width: int, height: int, shadow_extent: int = 2048,
+                 device: int = 0, stream: int | None = None, flags: int = 0):
+        self.lib, self.prefix = lib, prefix
+        self.width, self.height, self.shadow_extent = width, height, shadow_extent
+        self._bind()
+        cfg = Config(device, width, height, shadow_extent, stream, flags)
+        self.dev = C.c_void_p()
+        rc = self._f("create")(C.byref(cfg), C.byref(self.dev))
+        if rc != SUCCESS:
+            raise VkrError(rc, f"{prefix}_create failed (no CUDA device / bad config?)")
+        self._keep = []
+
+    # ---- plumbing
+    def _f(self, name):
+        return getattr(self.lib, f"{self.prefix}_{name}")
+
+    def _bind(self):
+        p = C.c_void_p
+        sigs = {
+            "create": ([C.POINTER(Config), C.POINTER(p)], C.c_int),
+            "destroy": ([p], None),
+            "upload_mesh": ([p, p, C.c_size_t, p, C.c_size_t, C.POINTER(C.c_uint32)], C.c_int),
+            "create_image": ([p, p, C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.POINTER(C.c_uint32)], C.c_int),
+            "update_bindless_texture": ([p, C.c_int, C.c_uint32, C.c_int], C.c_int),
+            "set_cubemap": ([p, C.POINTER(p), C.c_uint32, C.c_uint32, C.c_int, C.c_int], C.c_int),
+            "build_material": ([p, C.POINTER(MaterialConstants), C.c_int, C.POINTER(C.c_uint32)], C.c_int),
+            "draw": ([p, C.POINTER(GPUSceneData), p, C.c_size_t, C.POINTER(FrameParams)], C.c_int),
+            "readback": ([p, C.c_int, p, C.c_size_t], C.c_int),
+            "stats": ([p, C.POINTER(EngineStats)], C.c_int),
+            "last_error": ([p], C.c_char_p),
+        }
+        if self.prefix == "vkr":
+            sigs.update({
+                "readback_async": ([p, C.c_int, p, C.c_size_t], C.c_int),
+                "sync": ([p], C.c_int),
+                "get_timings": ([p, C.POINTER(C.c_float), C.c_int], C.c_int),
+                "device_ptr": ([p, C.c_int, C.POINTER(p), C.POINTER(C.c_size_t)], C.c_int),
+                "launch_count": ([p], C.c_int),
+                "version": ([], C.c_char_p),
+            })
+        for name, (args, res) in sigs.items():
+            fn = self._f(name)
+            fn.argtypes, fn.restype = args, res
+
+    def _check(self, rc):
+        if rc != SUCCESS:
+            msg = self._f("last_error")(self.dev)
+            raise VkrError(rc, msg.decode() if msg else "")
+
+    def close(self):
+        if self.dev:
+            self._f("destroy")(self.dev)
+            self.dev = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- resources
+    def upload_mesh(self, indices: np.ndarray, vertices: np.ndarray) -> int:
+        idx = np.ascontiguousarray(indices, dtype=np.uint32)
+        v = np.ascontiguousarray(vertices, dtype=VERTEX_DTYPE)
+        out = C.c_uint32()
+        self._check(self._f("upload_mesh")(self.dev, idx.ctypes.data, idx.size, v.ctypes.data, v.size, C.byref(out)))
+        return out.value
+
+    def create_image(self, rgba8: np.ndarray, fmt: int = FORMAT_SRGB, mipmapped: bool = True) -> int:
+        px = np.ascontiguousarray(rgba8, dtype=np.uint8)
+        h, w = px.shape[:2]
+        out = C.c_uint32()
+        self._check(self._f("create_image")(self.dev, px.ctypes.data, w, h, fmt, int(mipmapped), C.byref(out)))
+        return out.value
+
+    def update_bindless_texture(self, index: int, image: int, sampler: int = SAMPLER_LINEAR):
+        self._check(self._f("update_bindless_texture")(self.dev, index, image, sampler))
+
+    def set_cubemap(self, faces, fmt: int = FORMAT_SRGB, mipmapped: bool = True):
+        fs = [np.ascontiguousarray(f, dtype=np.uint8) for f in faces]
+        h, w = fs[0].shape[:2]
+        arr = (C.c_void_p * 6)(*[f.ctypes.data for f in fs])
+        self._check(self._f("set_cubemap")(self.dev, arr, w, h, fmt, int(mipmapped)))
+
+    def build_material(self, color=(1, 1, 1, 1), metallic=1.0, roughness=1.0, albedo_id=0, normal_id=1,
+                       metal_rough_id=0, pass_type=PASS_MAIN_COLOR) -> int:
+        mc = MaterialConstants()
+        mc.colorFactors[:] = color
+        mc.metal_rough_factors[:] = (metallic, roughness, 0.0, 0.0)
+        mc.albedoID, mc.normalID, mc.metalRoughID = albedo_id, normal_id, metal_rough_id
+        out = C.c_uint32()
+        self._check(self._f("build_material")(self.dev, C.byref(mc), pass_type, C.byref(out)))
+        return out.value
+
+    # ---- per frame
+    def draw(self, scene: GPUSceneData, objects: np.ndarray, params: FrameParams):
+        objs = np.ascontiguousarray(objects, dtype=RENDER_OBJECT_DTYPE)
+        self._check(self._f("draw")(self.dev, C.byref(scene), objs.ctypes.data, objs.size, C.byref(params)))
+
+    def readback(self, what: int) -> np.ndarray:
+        W, H, S = self.width, self.height, self.shadow_extent
+        if what == TARGET_RGBA8:
+            out = np.empty((H, W, 4), np.uint8)
+        elif what == TARGET_HDR16F:
+            out = np.empty((H, W, 4), np.float16)
+        elif what == TARGET_DEPTH:
+            out = np.empty((H, W), np.float32)
+        elif what == TARGET_SHADOW:
+            out = np.empty((NUM_CASCADES, S, S), np.float32)
+        elif what == TARGET_PRIMID:
+            out = np.empty((H, W), np.uint32)
+        else:
+            raise ValueError(what)
+        self._check(self._f("readback")(self.dev, what, out.ctypes.data, out.nbytes))
+        return out
+
+    def stats(self) -> EngineStats:
+        st = EngineStats()
+        self._check(self._f("stats")(self.dev, C.byref(st)))
+        return st
+
+    # ---- product-only
+    def sync(self):
+        self._check(self._f("sync")(self.dev))
+
+    def readback_async(self, what: int, pinned_ptr: int, nbytes: int):
+        self._check(self._f("readback_async")(self.dev, what, pinned_ptr, nbytes))
+
+    def timings(self) -> dict:
+        arr = (C.c_float * len(T_NAMES))()
+        self._check(self._f("get_timings")(self.dev, arr, len(T_NAMES)))
+        return dict(zip(T_NAMES, list(arr)))
+
+    def device_ptr(self, what: int):
+        p, n = C.c_void_p(), C.c_size_t()
+        self._check(self._f("device_ptr")(self.dev, what, C.byref(p), C.byref(n)))
+        return p.value, n.value
+
+    def launch_count(self) -> int:
+        return self._f("launch_count")(self.dev)

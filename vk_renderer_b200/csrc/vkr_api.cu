@@ -1,0 +1,654 @@
+// vkr_api.cu — the C-ABI (include/vkr.h) and the kernels behind it.  sm_100a only.
+//
+// Frame = [upload draw list] -> [shadow: clear, geometry, large-triangle raster] x layers
+//       -> [main: clear visibility buffer, geometry, large-triangle raster] -> [shade+resolve].
+// All work is enqueued on one stream; vkr_draw never blocks on the device.
+#include <cuda_runtime.h>
+#include <cuda_fp16.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "vkr_internal.h"
+#include "vkr_raster.cuh"
+#include "vkr_shade.cuh"
+#include "vkr_frameprep.h"
+
+using namespace vkr;
+
+// ======================================================================= kernels
+
+// ---- fills / format helpers
+__global__ void fill_u64_kernel(uint64_t* __restrict__ dst, size_t n, uint64_t v) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    ulonglong2* d2 = reinterpret_cast<ulonglong2*>(dst);
+    const size_t n2 = n >> 1;
+    for (size_t k = i; k < n2; k += stride) d2[k] = make_ulonglong2(v, v);
+    if (i == 0 && (n & 1)) dst[n - 1] = v;
+}
+__global__ void fill_u32_kernel(uint32_t* __restrict__ dst, size_t n, uint32_t v) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    uint4* d4 = reinterpret_cast<uint4*>(dst);
+    const size_t n4 = n >> 2;
+    for (size_t k = i; k < n4; k += stride) d4[k] = make_uint4(v, v, v, v);
+    if (i == 0) for (size_t k = n4 << 2; k < n; ++k) dst[k] = v;
+}
+__global__ void extract_vis_kernel(const uint64_t* __restrict__ vis, uint32_t* __restrict__ out, size_t n, int what) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint64_t k = vis[i];
+    if (what == 0) out[i] = (uint32_t)(k >> 32);                                  // depth bits
+    else { uint32_t lo = (uint32_t)k; out[i] = lo == VIS_EMPTY_LO ? 0xFFFFFFFFu : 0xFFFFFFFEu - lo; }
+}
+
+// ---- upload_mesh: AoS Vertex (48 B) -> three float4 streams
+__global__ void repack_vertices_kernel(const VkrVertex* __restrict__ v, size_t n, float4* __restrict__ pos,
+                                       float4* __restrict__ attrA, float4* __restrict__ attrB) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4* src = reinterpret_cast<const float4*>(v + i);   // 48 B = 3 x 16 B, 16-aligned
+    float4 a = src[0], b = src[1], c = src[2];
+    // a = (px,py,pz,uv_x)  b = (nx,ny,nz,uv_y)  c = color
+    pos[i] = make_float4(a.x, a.y, a.z, 1.0f);
+    attrA[i] = make_float4(b.x, b.y, b.z, a.w);
+    attrB[i] = make_float4(c.x, c.y, c.z, b.w);
+}
+
+// ---- generate_mipmaps (src/vk_images.cpp:64-157): LINEAR blit level i -> i+1
+__device__ __forceinline__ uint32_t linear_to_srgb8_dev(float l) {
+    if (!(l > 0.0f)) return 0u;
+    if (l >= 1.0f) return 255u;
+    float s = l <= 0.0031308f ? l * 12.92f : 1.055f * powf(l, 1.0f / 2.4f) - 0.055f;
+    return unorm8(s);
+}
+__global__ void mip_blit_kernel(const uchar4* __restrict__ src, int sw, int sh, uchar4* __restrict__ dst, int dw, int dh,
+                                int srgb, const float* __restrict__ lut) {
+    int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y * blockDim.y + threadIdx.y;
+    if (x >= dw || y >= dh) return;
+    float scx = (float)sw / (float)dw, scy = (float)sh / (float)dh;
+    float u = __fsub_rn(__fmul_rn((float)x + 0.5f, scx), 0.5f), v = __fsub_rn(__fmul_rn((float)y + 0.5f, scy), 0.5f);
+    float fu = floorf(u), fv = floorf(v);
+    float a = u - fu, b = v - fv;
+    int x0 = min(max((int)fu, 0), sw - 1), x1 = min(max((int)fu + 1, 0), sw - 1);
+    int y0 = min(max((int)fv, 0), sh - 1), y1 = min(max((int)fv + 1, 0), sh - 1);
+    uchar4 q[4] = {src[(size_t)y0 * sw + x0], src[(size_t)y0 * sw + x1], src[(size_t)y1 * sw + x0], src[(size_t)y1 * sw + x1]};
+    float wgt[4] = {__fmul_rn(1.0f - a, 1.0f - b), __fmul_rn(a, 1.0f - b), __fmul_rn(1.0f - a, b), __fmul_rn(a, b)};
+    float c[4] = {0, 0, 0, 0};
+    for (int k = 0; k < 4; ++k) {
+        float r, g, bl;
+        if (srgb) { r = lut[q[k].x]; g = lut[q[k].y]; bl = lut[q[k].z]; }
+        else { r = __fdiv_rn((float)q[k].x, 255.0f); g = __fdiv_rn((float)q[k].y, 255.0f); bl = __fdiv_rn((float)q[k].z, 255.0f); }
+        float al = __fdiv_rn((float)q[k].w, 255.0f);
+        c[0] = __fadd_rn(c[0], __fmul_rn(r, wgt[k])); c[1] = __fadd_rn(c[1], __fmul_rn(g, wgt[k]));
+        c[2] = __fadd_rn(c[2], __fmul_rn(bl, wgt[k])); c[3] = __fadd_rn(c[3], __fmul_rn(al, wgt[k]));
+    }
+    uchar4 o;
+    if (srgb) { o.x = linear_to_srgb8_dev(c[0]); o.y = linear_to_srgb8_dev(c[1]); o.z = linear_to_srgb8_dev(c[2]); }
+    else { o.x = unorm8(c[0]); o.y = unorm8(c[1]); o.z = unorm8(c[2]); }
+    o.w = unorm8(c[3]);
+    dst[(size_t)y * dw + x] = o;
+}
+
+// ---- geometry: one thread per triangle of a GEOM_BLOCK chunk of one draw
+template <bool SHADOW>
+__global__ void __launch_bounds__(GEOM_BLOCK) geometry_kernel(const DObject* __restrict__ objects, const DChunk* __restrict__ chunks,
+                                                              const float* __restrict__ mvps, uint32_t mvpStride,
+                                                              const __grid_constant__ RasterTarget rt, const __grid_constant__ Queues q) {
+    __shared__ float s_mvp[16];
+    const DChunk ch = chunks[blockIdx.x];
+    const DObject& o = objects[ch.obj];
+    if (threadIdx.x < 16) s_mvp[threadIdx.x] = mvps[(size_t)ch.obj * mvpStride + threadIdx.x];
+    __syncthreads();
+    const uint32_t tri = ch.firstTri + threadIdx.x;
+    if (tri >= o.triCount) return;
+    if (SHADOW) {
+        DepthSink sink{rt.depthBits, rt.width};
+        geometry_triangle(s_mvp, o.pos, o.idx, tri, 0u, rt, q, sink);
+    } else {
+        const uint32_t seq = o.primBase + tri;
+        VisSink sink{rt.vis, rt.width, 0xFFFFFFFEu - seq};
+        geometry_triangle(s_mvp, o.pos, o.idx, tri, seq, rt, q, sink);
+    }
+}
+
+// ---- large triangles: one warp per (triangle, 64x64 tile) item, grid-stride over the queue
+template <bool SHADOW>
+__global__ void __launch_bounds__(256) large_raster_kernel(const __grid_constant__ RasterTarget rt, const __grid_constant__ Queues q) {
+    const uint32_t nItems = min(q.counters[1], q.itemCap);
+    const uint32_t warpsPerGrid = (gridDim.x * blockDim.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    for (uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < nItems; i += warpsPerGrid) {
+        const LargeItem it = q.items[i];
+        const LargeTri lt = q.tris[it.tri];
+        if (SHADOW) {
+            DepthSink sink{rt.depthBits, rt.width};
+            raster_item(lt, it, sink, lane, 32);
+        } else {
+            VisSink sink{rt.vis, rt.width, 0xFFFFFFFEu - lt.seq};
+            raster_item(lt, it, sink, lane, 32);
+        }
+    }
+}
+
+// ---- shade + resolve: one thread per pixel of the scissor rectangle, 8x8 pixel blocks per 2 warps
+__global__ void __launch_bounds__(128) shade_kernel(const __grid_constant__ ShadeConst sc, const __grid_constant__ ShadeBuffers sb) {
+    // 16x8 pixel block; each warp covers an 8x4... lanes map to a 8x4 footprint for locality
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int lx = (lane & 7) + ((warp & 1) << 3), ly = (lane >> 3) + ((warp >> 1) << 2);
+    const int px = sc.sx0 + blockIdx.x * 16 + lx, py = sc.sy0 + blockIdx.y * 8 + ly;
+    if (px >= sc.sx1 || py >= sc.sy1) return;
+    shade_pixel(sc, sb, px, py);
+}
+
+// ======================================================================= host side
+
+#define CK(call)                                                                      \
+    do {                                                                              \
+        cudaError_t e_ = (call);                                                      \
+        if (e_ != cudaSuccess) { return dev->fail(VKR_ERROR_CUDA, #call, e_); }       \
+    } while (0)
+
+struct ImageRec {
+    uchar4* data = nullptr;
+    uint32_t w = 0, h = 0, levels = 1;
+    uint32_t mipOffset[16] = {0};
+    size_t texels = 0;
+    int format = 0;
+    bool hasCutout = false;
+};
+
+struct FrameSlot {
+    void* pinned = nullptr; size_t pinnedCap = 0;
+    void* devbuf = nullptr; size_t devCap = 0;
+    cudaEvent_t uploaded = nullptr;
+    cudaEvent_t rendered = nullptr;
+};
+
+struct VkrDevice {
+    int device = 0;
+    cudaStream_t stream = nullptr, copyStream = nullptr;
+    bool ownStream = false;
+    uint32_t W = 0, H = 0, S = 2048, flags = 0;
+    int smCount = 148;
+
+    uint64_t* vis = nullptr;
+    uint32_t* shadowBits = nullptr;
+    uint16_t* hdr = nullptr;
+    uint32_t* rgba8[VKR_FRAME_OVERLAP] = {nullptr, nullptr};
+    uint32_t* scratch = nullptr;        // W*H*4, lazily allocated for depth / primid readback
+    float* lut = nullptr;
+
+    std::vector<DMesh> meshes;
+    std::vector<void*> allocations;     // freed LIFO at destroy (DeletionQueue, src/vk_types.h:34-48)
+    std::vector<ImageRec> images;
+    std::vector<DTexture> texHost;
+    DTexture* texDev = nullptr;
+    bool texDirty = true;
+    DTexture* cubeDev = nullptr;
+    bool haveCube = false;
+    std::vector<DMaterial> materials;
+    DMaterial* matDev = nullptr; size_t matCap = 0; bool matDirty = true;
+
+    Queues q{};
+    uint32_t* countersHost = nullptr;   // pinned mirror of q.counters after the last frame
+
+    FrameSlot slots[VKR_FRAME_OVERLAP];
+    uint64_t frameIndex = 0;
+    int lastSlot = 0;
+    FramePlan plan;
+
+    cudaEvent_t tev[VKR_T_COUNT + 1] = {nullptr};
+    bool tevValid = false;
+    float timings[VKR_T_COUNT] = {0};
+
+    VkrEngineStats stats{};
+    int launches = 0;
+    std::string err;
+
+    int fail(int code, const char* what, cudaError_t e = cudaSuccess) {
+        err = what;
+        if (e != cudaSuccess) { err += ": "; err += cudaGetErrorString(e); }
+        return code;
+    }
+};
+
+static float g_srgb_lut[256];
+static void init_lut() {
+    for (int i = 0; i < 256; ++i) {
+        double c = i / 255.0;
+        g_srgb_lut[i] = (float)(c <= 0.04045 ? c / 12.92 : std::pow((c + 0.055) / 1.055, 2.4));
+    }
+}
+
+static int dev_alloc(VkrDevice* dev, void** p, size_t bytes) {
+    cudaError_t e = cudaMalloc(p, bytes ? bytes : 16);
+    if (e != cudaSuccess) return dev->fail(e == cudaErrorMemoryAllocation ? VKR_ERROR_OUT_OF_MEMORY : VKR_ERROR_CUDA, "cudaMalloc", e);
+    dev->allocations.push_back(*p);
+    return VKR_SUCCESS;
+}
+#define ALLOC(ptr, bytes)                                                    \
+    do { int rc_ = dev_alloc(dev, (void**)&(ptr), (bytes)); if (rc_) return rc_; } while (0)
+
+static inline unsigned grid_for(size_t n, unsigned block, unsigned maxBlocks) {
+    size_t g = (n + block - 1) / block;
+    return (unsigned)std::max<size_t>(1, std::min<size_t>(g, maxBlocks));
+}
+
+extern "C" {
+
+const char* vkr_version(void) { return "vkr 0.1 (sm_100a)"; }
+
+const char* vkr_last_error(VkrDevice* dev) { return dev ? dev->err.c_str() : "null device"; }
+
+int vkr_create(const VkrConfig* cfg, VkrDevice** out) {
+    if (!cfg || !out || cfg->width == 0 || cfg->height == 0 || cfg->width > 16384 || cfg->height > 16384)
+        return VKR_ERROR_INVALID_ARGUMENT;
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0 || cfg->device < 0 || cfg->device >= count) {
+        cudaGetLastError();
+        return VKR_ERROR_NO_DEVICE;
+    }
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, cfg->device) != cudaSuccess || prop.major < 10) return VKR_ERROR_NO_DEVICE;
+    VkrDevice* dev = new VkrDevice();
+    dev->device = cfg->device;
+    dev->W = cfg->width; dev->H = cfg->height;
+    dev->S = cfg->shadowExtent ? cfg->shadowExtent : 2048;
+    dev->flags = cfg->flags;
+    dev->smCount = prop.multiProcessorCount;
+    *out = dev;
+    auto body = [&]() -> int {
+        CK(cudaSetDevice(dev->device));
+        if (cfg->stream) dev->stream = (cudaStream_t)cfg->stream;
+        else { CK(cudaStreamCreateWithFlags(&dev->stream, cudaStreamNonBlocking)); dev->ownStream = true; }
+        CK(cudaStreamCreateWithFlags(&dev->copyStream, cudaStreamNonBlocking));
+        const size_t px = (size_t)dev->W * dev->H;
+        ALLOC(dev->vis, px * 8);
+        ALLOC(dev->hdr, px * 8);
+        for (int i = 0; i < VKR_FRAME_OVERLAP; ++i) ALLOC(dev->rgba8[i], px * 4);
+        ALLOC(dev->shadowBits, (size_t)dev->S * dev->S * 4 * VKR_NUM_CASCADES);
+        ALLOC(dev->lut, 256 * 4);
+        init_lut();
+        CK(cudaMemcpyAsync(dev->lut, g_srgb_lut, sizeof(g_srgb_lut), cudaMemcpyHostToDevice, dev->stream));
+        ALLOC(dev->texDev, sizeof(DTexture) * VKR_MAX_BINDLESS);
+        ALLOC(dev->cubeDev, sizeof(DTexture) * 6);
+        dev->texHost.assign(VKR_MAX_BINDLESS, DTexture{});
+        dev->q.triCap = 1u << 20; dev->q.itemCap = 1u << 22;
+        ALLOC(dev->q.tris, sizeof(LargeTri) * dev->q.triCap);
+        ALLOC(dev->q.items, sizeof(LargeItem) * dev->q.itemCap);
+        ALLOC(dev->q.counters, 16);
+        CK(cudaMallocHost(&dev->countersHost, 16));
+        std::memset(dev->countersHost, 0, 16);
+        for (auto& s : dev->slots) {
+            CK(cudaEventCreateWithFlags(&s.uploaded, cudaEventDisableTiming));
+            CK(cudaEventCreateWithFlags(&s.rendered, cudaEventDisableTiming));
+        }
+        for (auto& e : dev->tev) CK(cudaEventCreate(&e));
+        // shadow image starts cleared to 1.0 so an un-rendered map reads "unshadowed"
+        fill_u32_kernel<<<grid_for((size_t)dev->S * dev->S * VKR_NUM_CASCADES / 4, 256, 4096), 256, 0, dev->stream>>>(
+            dev->shadowBits, (size_t)dev->S * dev->S * VKR_NUM_CASCADES, DEPTH_ONE_BITS);
+        fill_u64_kernel<<<grid_for(px / 2, 256, 4096), 256, 0, dev->stream>>>(dev->vis, px, VIS_CLEAR);
+        CK(cudaGetLastError());
+        // init_default_data: bindless slot 0 = default normal texture, NEAREST (src/vk_engine_init.cpp:351-355)
+        uint32_t normalDefault = 0xFFFF8080u;
+        VkrImage img;
+        int rc = vkr_create_image(dev, &normalDefault, 1, 1, VKR_FORMAT_R8G8B8A8_UNORM, 0, &img);
+        if (rc) return rc;
+        rc = vkr_update_bindless_texture(dev, 0, img, VKR_SAMPLER_NEAREST);
+        if (rc) return rc;
+        CK(cudaStreamSynchronize(dev->stream));
+        return VKR_SUCCESS;
+    };
+    int rc = body();
+    if (rc != VKR_SUCCESS) {
+        std::fprintf(stderr, "vkr_create: %s\n", dev->err.c_str());
+        vkr_destroy(dev);
+        *out = nullptr;
+    }
+    return rc;
+}
+
+void vkr_destroy(VkrDevice* dev) {
+    if (!dev) return;
+    cudaSetDevice(dev->device);
+    cudaDeviceSynchronize();
+    for (auto it = dev->allocations.rbegin(); it != dev->allocations.rend(); ++it) cudaFree(*it);
+    for (auto& s : dev->slots) {
+        if (s.pinned) cudaFreeHost(s.pinned);
+        if (s.devbuf) cudaFree(s.devbuf);
+        if (s.uploaded) cudaEventDestroy(s.uploaded);
+        if (s.rendered) cudaEventDestroy(s.rendered);
+    }
+    for (auto& e : dev->tev) if (e) cudaEventDestroy(e);
+    if (dev->countersHost) cudaFreeHost(dev->countersHost);
+    if (dev->copyStream) cudaStreamDestroy(dev->copyStream);
+    if (dev->ownStream && dev->stream) cudaStreamDestroy(dev->stream);
+    delete dev;
+}
+
+int vkr_upload_mesh(VkrDevice* dev, const uint32_t* indices, size_t ni, const VkrVertex* vertices, size_t nv, VkrMesh* out) {
+    if (!dev) return VKR_ERROR_INVALID_ARGUMENT;
+    if (!out || (ni && !indices) || (nv && !vertices) || nv >= 0xFFFFFFFFull || ni >= 0xFFFFFFFFull)
+        return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_upload_mesh: bad arguments");
+    for (size_t i = 0; i < ni; ++i)
+        if (indices[i] >= nv) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_upload_mesh: index out of range");
+    CK(cudaSetDevice(dev->device));
+    DMesh m{};
+    m.nv = (uint32_t)nv; m.ni = (uint32_t)ni;
+    float4 *pos, *aA, *aB; uint32_t* idx; VkrVertex* staging = nullptr;
+    ALLOC(pos, nv * 16); ALLOC(aA, nv * 16); ALLOC(aB, nv * 16); ALLOC(idx, ni * 4);
+    if (nv) {
+        cudaError_t e = cudaMalloc(&staging, nv * sizeof(VkrVertex));
+        if (e != cudaSuccess) return dev->fail(VKR_ERROR_OUT_OF_MEMORY, "cudaMalloc(staging)", e);
+        CK(cudaMemcpyAsync(staging, vertices, nv * sizeof(VkrVertex), cudaMemcpyHostToDevice, dev->stream));
+        repack_vertices_kernel<<<(unsigned)((nv + 255) / 256), 256, 0, dev->stream>>>(staging, nv, pos, aA, aB);
+        CK(cudaGetLastError());
+    }
+    if (ni) CK(cudaMemcpyAsync(idx, indices, ni * 4, cudaMemcpyHostToDevice, dev->stream));
+    CK(cudaStreamSynchronize(dev->stream));     // caller keeps ownership of the host arrays (immediate_submit semantics)
+    if (staging) cudaFree(staging);
+    m.pos = pos; m.attrA = aA; m.attrB = aB; m.idx = idx;
+    dev->meshes.push_back(m);
+    *out = (VkrMesh)(dev->meshes.size() - 1);
+    return VKR_SUCCESS;
+}
+
+static int build_image(VkrDevice* dev, const void* rgba8, uint32_t w, uint32_t h, VkrFormat fmt, int mipmapped, ImageRec& im) {
+    im.w = w; im.h = h; im.format = fmt;
+    im.levels = mipmapped ? (uint32_t)std::floor(std::log2((double)std::max(w, h))) + 1 : 1;
+    if (im.levels > 16) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "image too large");
+    size_t total = 0;
+    for (uint32_t l = 0; l < im.levels; ++l) {
+        im.mipOffset[l] = (uint32_t)total;
+        total += (size_t)std::max(1u, w >> l) * std::max(1u, h >> l);
+    }
+    im.texels = total;
+    ALLOC(im.data, total * 4);
+    CK(cudaMemcpyAsync(im.data, rgba8, (size_t)w * h * 4, cudaMemcpyHostToDevice, dev->stream));
+    for (uint32_t l = 0; l + 1 < im.levels; ++l) {
+        int sw = std::max(1u, w >> l), sh = std::max(1u, h >> l), dw = std::max(1u, w >> (l + 1)), dh = std::max(1u, h >> (l + 1));
+        dim3 b(16, 16), g((dw + 15) / 16, (dh + 15) / 16);
+        mip_blit_kernel<<<g, b, 0, dev->stream>>>(im.data + im.mipOffset[l], sw, sh, im.data + im.mipOffset[l + 1], dw, dh,
+                                                  fmt == VKR_FORMAT_R8G8B8A8_SRGB, dev->lut);
+    }
+    CK(cudaGetLastError());
+    const uint8_t* p = (const uint8_t*)rgba8;
+    im.hasCutout = false;
+    for (size_t i = 0; i < (size_t)w * h; ++i) if (p[i * 4 + 3] < 128) { im.hasCutout = true; break; }
+    CK(cudaStreamSynchronize(dev->stream));
+    return VKR_SUCCESS;
+}
+
+static DTexture make_dtexture(const ImageRec& im, int sampler) {
+    DTexture t{};
+    t.data = im.data; t.w = im.w; t.h = im.h; t.levels = im.levels;
+    t.flags = (im.format == VKR_FORMAT_R8G8B8A8_SRGB ? 1u : 0u) | (sampler == VKR_SAMPLER_LINEAR ? 2u : 0u) | (im.hasCutout ? 4u : 0u);
+    std::memcpy(t.mipOffset, im.mipOffset, sizeof(t.mipOffset));
+    return t;
+}
+
+int vkr_create_image(VkrDevice* dev, const void* rgba8, uint32_t w, uint32_t h, VkrFormat fmt, int mipmapped, VkrImage* out) {
+    if (!dev) return VKR_ERROR_INVALID_ARGUMENT;
+    if (!rgba8 || !out || w == 0 || h == 0 || (fmt != VKR_FORMAT_R8G8B8A8_UNORM && fmt != VKR_FORMAT_R8G8B8A8_SRGB))
+        return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_create_image: bad arguments");
+    CK(cudaSetDevice(dev->device));
+    ImageRec im;
+    int rc = build_image(dev, rgba8, w, h, fmt, mipmapped, im);
+    if (rc) return rc;
+    dev->images.push_back(im);
+    *out = (VkrImage)(dev->images.size() - 1);
+    return VKR_SUCCESS;
+}
+
+int vkr_update_bindless_texture(VkrDevice* dev, int index, VkrImage image, VkrSampler sampler) {
+    if (!dev) return VKR_ERROR_INVALID_ARGUMENT;
+    if (index < 0 || index >= VKR_MAX_BINDLESS || image >= dev->images.size())
+        return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_update_bindless_texture: bad index or image");
+    dev->texHost[index] = make_dtexture(dev->images[image], sampler);
+    dev->texDirty = true;
+    return VKR_SUCCESS;
+}
+
+int vkr_set_cubemap(VkrDevice* dev, const void* const faces[6], uint32_t w, uint32_t h, VkrFormat fmt, int mipmapped) {
+    if (!dev) return VKR_ERROR_INVALID_ARGUMENT;
+    if (!faces || w == 0 || h == 0) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_set_cubemap: bad arguments");
+    CK(cudaSetDevice(dev->device));
+    DTexture t[6];
+    for (int f = 0; f < 6; ++f) {
+        if (!faces[f]) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_set_cubemap: null face");
+        ImageRec im;
+        int rc = build_image(dev, faces[f], w, h, fmt, mipmapped, im);
+        if (rc) return rc;
+        t[f] = make_dtexture(im, VKR_SAMPLER_LINEAR);
+    }
+    CK(cudaMemcpyAsync(dev->cubeDev, t, sizeof(t), cudaMemcpyHostToDevice, dev->stream));
+    CK(cudaStreamSynchronize(dev->stream));
+    dev->haveCube = true;
+    return VKR_SUCCESS;
+}
+
+int vkr_build_material(VkrDevice* dev, const VkrMaterialConstants* p, VkrMaterialPass pass, VkrMaterial* out) {
+    if (!dev) return VKR_ERROR_INVALID_ARGUMENT;
+    if (!p || !out) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_build_material: bad arguments");
+    DMaterial m;
+    std::memcpy(m.colorFactors, p->colorFactors, 16);
+    std::memcpy(m.metalRough, p->metal_rough_factors, 16);
+    m.albedoID = p->albedoID; m.normalID = p->normalID; m.metalRoughID = p->metalRoughID; m.pass = (int32_t)pass;
+    dev->materials.push_back(m);
+    dev->matDirty = true;
+    *out = (VkrMaterial)(dev->materials.size() - 1);
+    return VKR_SUCCESS;
+}
+
+static int ensure_slot(VkrDevice* dev, FrameSlot& s, size_t bytes) {
+    if (s.pinnedCap < bytes) {
+        if (s.pinned) cudaFreeHost(s.pinned);
+        if (s.devbuf) cudaFree(s.devbuf);
+        size_t cap = std::max<size_t>(bytes * 3 / 2, 1 << 16);
+        CK(cudaMallocHost(&s.pinned, cap));
+        CK(cudaMalloc(&s.devbuf, cap));
+        s.pinnedCap = s.devCap = cap;
+    }
+    return VKR_SUCCESS;
+}
+
+int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject* objs, size_t n, const VkrFrameParams* fp) {
+    if (!dev) return VKR_ERROR_INVALID_ARGUMENT;
+    if (!scene || !fp || (n && !objs)) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_draw: null argument");
+    CK(cudaSetDevice(dev->device));
+    FramePlan& plan = dev->plan;
+    std::string why = plan_frame(scene, objs, n, fp, dev->meshes, dev->materials, dev->W, dev->H, dev->S, plan);
+    if (!why.empty()) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, why.c_str());
+    cudaStream_t st = dev->stream;
+    dev->launches = 0;
+    const bool timing = dev->flags & VKR_CONFIG_TIMINGS;
+    if (timing) CK(cudaEventRecord(dev->tev[0], st));
+
+    // ---- descriptor-ish state
+    if (dev->texDirty) {
+        CK(cudaMemcpyAsync(dev->texDev, dev->texHost.data(), sizeof(DTexture) * VKR_MAX_BINDLESS, cudaMemcpyHostToDevice, st));
+        CK(cudaStreamSynchronize(st));   // texHost may change right after return
+        dev->texDirty = false;
+    }
+    if (dev->matDirty) {
+        if (dev->matCap < dev->materials.size()) {
+            dev->matCap = std::max<size_t>(dev->materials.size() * 2, 64);
+            ALLOC(dev->matDev, dev->matCap * sizeof(DMaterial));
+        }
+        CK(cudaMemcpyAsync(dev->matDev, dev->materials.data(), dev->materials.size() * sizeof(DMaterial), cudaMemcpyHostToDevice, st));
+        CK(cudaStreamSynchronize(st));
+        dev->matDirty = false;
+    }
+
+    // ---- upload the draw list (replaces per-object push constants + the scene UBO)
+    const int slotIdx = (int)(dev->frameIndex % VKR_FRAME_OVERLAP);
+    FrameSlot& slot = dev->slots[slotIdx];
+    const size_t szObj = sizeof(DObject) * n, szPrim = 4 * (n + 1), szChunk = sizeof(DChunk) * plan.chunks.size();
+    const size_t szShadow = plan.shadowMvp.size() * 4;
+    auto align16 = [](size_t v) { return (v + 15) & ~(size_t)15; };
+    const size_t offObj = 0, offPrim = align16(offObj + szObj), offChunk = align16(offPrim + szPrim), offShadow = align16(offChunk + szChunk);
+    const size_t total = align16(offShadow + szShadow) + 16;
+    if (dev->frameIndex >= VKR_FRAME_OVERLAP) CK(cudaEventSynchronize(slot.uploaded));   // pinned buffer reuse
+    int rc = ensure_slot(dev, slot, total);
+    if (rc) return rc;
+    char* hp = (char*)slot.pinned;
+    if (n) std::memcpy(hp + offObj, plan.objects.data(), szObj);
+    std::memcpy(hp + offPrim, plan.primBase.data(), szPrim);
+    if (szChunk) std::memcpy(hp + offChunk, plan.chunks.data(), szChunk);
+    if (szShadow) std::memcpy(hp + offShadow, plan.shadowMvp.data(), szShadow);
+    CK(cudaMemcpyAsync(slot.devbuf, slot.pinned, total, cudaMemcpyHostToDevice, st));
+    CK(cudaEventRecord(slot.uploaded, st));
+    char* dp = (char*)slot.devbuf;
+    const DObject* dObjects = (const DObject*)(dp + offObj);
+    const uint32_t* dPrimBase = (const uint32_t*)(dp + offPrim);
+    const DChunk* dChunks = (const DChunk*)(dp + offChunk);
+    const float* dShadowMvp = (const float*)(dp + offShadow);
+    if (timing) CK(cudaEventRecord(dev->tev[1], st));
+
+    const unsigned nChunks = (unsigned)plan.chunks.size();
+    const unsigned largeGrid = (unsigned)dev->smCount * 4;
+
+    // ---- draw_shadow (src/vk_engine_run.cpp:334-382)
+    for (int layer = 0; layer < plan.shadowLayers; ++layer) {
+        RasterTarget rt = plan.shadowTarget;
+        rt.depthBits = dev->shadowBits + (size_t)layer * dev->S * dev->S;
+        const size_t sn = (size_t)dev->S * dev->S;
+        fill_u32_kernel<<<grid_for(sn / 4, 256, 2048), 256, 0, st>>>(rt.depthBits, sn, DEPTH_ONE_BITS);
+        CK(cudaMemsetAsync(dev->q.counters, 0, 16, st));
+        dev->launches += 1;
+        if (nChunks) {
+            geometry_kernel<true><<<nChunks, GEOM_BLOCK, 0, st>>>(dObjects, dChunks, dShadowMvp + (size_t)layer * n * 16, 16u, rt, dev->q);
+            large_raster_kernel<true><<<largeGrid, 256, 0, st>>>(rt, dev->q);
+            dev->launches += 2;
+        }
+    }
+    if (timing) CK(cudaEventRecord(dev->tev[2], st));
+
+    // ---- draw_geometry, raster half (src/vk_engine_run.cpp:244-311)
+    {
+        RasterTarget rt = plan.mainTarget;
+        rt.vis = dev->vis;
+        const size_t px = (size_t)dev->W * dev->H;
+        fill_u64_kernel<<<grid_for(px / 2, 256, 4096), 256, 0, st>>>(dev->vis, px, VIS_CLEAR);
+        CK(cudaMemsetAsync(dev->q.counters, 0, 16, st));
+        dev->launches += 1;
+        // only the opaque prefix writes depth; transparent draws are blended in a later pass
+        unsigned opaqueChunks = 0;
+        while (opaqueChunks < nChunks && plan.chunks[opaqueChunks].obj < plan.opaqueCount) ++opaqueChunks;
+        if (opaqueChunks) {
+            geometry_kernel<false><<<opaqueChunks, GEOM_BLOCK, 0, st>>>(dObjects, dChunks, (const float*)dObjects, (uint32_t)(sizeof(DObject) / 4), rt, dev->q);
+            large_raster_kernel<false><<<largeGrid, 256, 0, st>>>(rt, dev->q);
+            dev->launches += 2;
+        }
+        CK(cudaMemcpyAsync(dev->countersHost, dev->q.counters, 16, cudaMemcpyDeviceToHost, st));
+    }
+    if (timing) CK(cudaEventRecord(dev->tev[3], st));
+
+    // ---- shading half of draw_geometry + draw_skybox + draw_background + draw_postprocess + present blit
+    {
+        ShadeBuffers sb{};
+        sb.vis = dev->vis; sb.objects = dObjects; sb.primBase = dPrimBase; sb.materials = dev->matDev;
+        sb.textures = dev->texDev; sb.cube = dev->haveCube ? dev->cubeDev : nullptr;
+        sb.shadow = reinterpret_cast<const float*>(dev->shadowBits);
+        sb.hdr = dev->hdr; sb.rgba8 = dev->rgba8[slotIdx]; sb.srgbLut = dev->lut;
+        const ShadeConst& sc = plan.sc;
+        dim3 grid((sc.sx1 - sc.sx0 + 15) / 16, (sc.sy1 - sc.sy0 + 7) / 8);
+        if (grid.x && grid.y) { shade_kernel<<<grid, 128, 0, st>>>(sc, sb); dev->launches += 1; }
+    }
+    if (timing) { CK(cudaEventRecord(dev->tev[4], st)); CK(cudaEventRecord(dev->tev[5], st)); CK(cudaEventRecord(dev->tev[6], st)); dev->tevValid = true; }
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(slot.rendered, st));
+    dev->lastSlot = slotIdx;
+    dev->frameIndex++;
+    dev->stats.drawcall_count = (int32_t)n;
+    dev->stats.triangle_count = (int32_t)plan.totalTris;
+    return VKR_SUCCESS;
+}
+
+int vkr_sync(VkrDevice* dev) {
+    if (!dev) return VKR_ERROR_INVALID_ARGUMENT;
+    CK(cudaSetDevice(dev->device));
+    CK(cudaStreamSynchronize(dev->stream));
+    CK(cudaStreamSynchronize(dev->copyStream));
+    if (dev->countersHost[2]) return dev->fail(VKR_ERROR_CAPACITY, "large-triangle queue overflow");
+    if (dev->tevValid) {
+        // tev: 0 start, 1 upload done, 2 shadow done, 3 geometry done, 4 shade done
+        float ms;
+        cudaEventElapsedTime(&ms, dev->tev[0], dev->tev[1]); dev->timings[VKR_T_UPLOAD] = ms;
+        cudaEventElapsedTime(&ms, dev->tev[1], dev->tev[2]); dev->timings[VKR_T_SHADOW] = ms;
+        cudaEventElapsedTime(&ms, dev->tev[2], dev->tev[3]); dev->timings[VKR_T_GEOMETRY] = ms;
+        cudaEventElapsedTime(&ms, dev->tev[3], dev->tev[4]); dev->timings[VKR_T_SHADE] = ms;
+        dev->timings[VKR_T_TRANSPARENT] = 0; dev->timings[VKR_T_POST] = 0;
+        cudaEventElapsedTime(&ms, dev->tev[0], dev->tev[4]); dev->timings[VKR_T_TOTAL] = ms;
+        dev->stats.frametime = dev->timings[VKR_T_TOTAL];
+        dev->stats.mesh_draw_time = dev->timings[VKR_T_SHADOW] + dev->timings[VKR_T_GEOMETRY];
+    }
+    return VKR_SUCCESS;
+}
+
+static int target_info(VkrDevice* dev, VkrTarget what, const void** src, size_t* bytes) {
+    const size_t px = (size_t)dev->W * dev->H;
+    switch (what) {
+        case VKR_TARGET_RGBA8: *src = dev->rgba8[dev->lastSlot]; *bytes = px * 4; return 0;
+        case VKR_TARGET_HDR16F: *src = dev->hdr; *bytes = px * 8; return 0;
+        case VKR_TARGET_SHADOW: *src = dev->shadowBits; *bytes = (size_t)dev->S * dev->S * 4 * VKR_NUM_CASCADES; return 0;
+        case VKR_TARGET_DEPTH: case VKR_TARGET_PRIMID: *src = nullptr; *bytes = px * 4; return 0;
+        default: return -1;
+    }
+}
+
+static int do_readback(VkrDevice* dev, VkrTarget what, void* dst, size_t dstBytes, bool sync) {
+    if (!dev) return VKR_ERROR_INVALID_ARGUMENT;
+    const void* src; size_t bytes;
+    if (!dst || target_info(dev, what, &src, &bytes)) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_readback: bad target");
+    if (dstBytes < bytes) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_readback: destination too small");
+    CK(cudaSetDevice(dev->device));
+    if (what == VKR_TARGET_DEPTH || what == VKR_TARGET_PRIMID) {
+        const size_t px = (size_t)dev->W * dev->H;
+        if (!dev->scratch) ALLOC(dev->scratch, px * 4);
+        extract_vis_kernel<<<(unsigned)((px + 255) / 256), 256, 0, dev->stream>>>(dev->vis, dev->scratch, px, what == VKR_TARGET_DEPTH ? 0 : 1);
+        CK(cudaGetLastError());
+        CK(cudaMemcpyAsync(dst, dev->scratch, bytes, cudaMemcpyDeviceToHost, dev->stream));
+        if (sync) return vkr_sync(dev);
+        return VKR_SUCCESS;
+    }
+    // copy engine work goes to the copy stream so the next frame's kernels overlap it
+    CK(cudaStreamWaitEvent(dev->copyStream, dev->slots[dev->lastSlot].rendered, 0));
+    CK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, dev->copyStream));
+    if (sync) return vkr_sync(dev);
+    return VKR_SUCCESS;
+}
+
+int vkr_readback(VkrDevice* dev, VkrTarget what, void* dst, size_t dstBytes) { return do_readback(dev, what, dst, dstBytes, true); }
+int vkr_readback_async(VkrDevice* dev, VkrTarget what, void* dst, size_t dstBytes) { return do_readback(dev, what, dst, dstBytes, false); }
+
+int vkr_stats(VkrDevice* dev, VkrEngineStats* out) {
+    if (!dev || !out) return VKR_ERROR_INVALID_ARGUMENT;
+    *out = dev->stats;
+    return VKR_SUCCESS;
+}
+
+int vkr_get_timings(VkrDevice* dev, float* msOut, int count) {
+    if (!dev || !msOut || count < 0) return VKR_ERROR_INVALID_ARGUMENT;
+    for (int i = 0; i < count && i < VKR_T_COUNT; ++i) msOut[i] = dev->timings[i];
+    return VKR_SUCCESS;
+}
+
+int vkr_device_ptr(VkrDevice* dev, VkrTarget what, void** ptr, size_t* bytes) {
+    if (!dev || !ptr || !bytes) return VKR_ERROR_INVALID_ARGUMENT;
+    const void* src; size_t n;
+    if (target_info(dev, what, &src, &n) || !src) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_device_ptr: target has no linear buffer");
+    *ptr = const_cast<void*>(src); *bytes = n;
+    return VKR_SUCCESS;
+}
+
+int vkr_launch_count(VkrDevice* dev) { return dev ? dev->launches : 0; }
+
+}  // extern "C"

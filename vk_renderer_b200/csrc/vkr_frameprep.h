@@ -1,0 +1,151 @@
+// vkr_frameprep.h — host-side per-frame preparation (pure C++, no CUDA calls).
+//
+// Turns the reference's per-object command recording (src/vk_engine_run.cpp:284-311 for the
+// geometry pass, :367-378 for the shadow pass: bind index buffer, push 80 bytes of constants,
+// vkCmdDrawIndexed) into flat arrays the kernels consume: one DObject per draw, a prefix sum
+// of triangle counts (submission-order primitive ids), GEOM_BLOCK-triangle work chunks and
+// the per-cascade light MVPs.
+//
+// Must be compiled without FMA contraction (-ffp-contract=off): the matrices computed here
+// feed the bit-exact position path.
+#pragma once
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <string>
+#include <vector>
+#include "vkr_internal.h"
+
+namespace vkr {
+
+// glm mat4*mat4 association: ((A0*b0 + A1*b1) + A2*b2) + A3*b3
+inline void mat_mul(const float* a, const float* b, float* r) {
+    for (int j = 0; j < 4; ++j)
+        for (int i = 0; i < 4; ++i)
+            r[j * 4 + i] = ((a[0 * 4 + i] * b[j * 4 + 0] + a[1 * 4 + i] * b[j * 4 + 1]) + a[2 * 4 + i] * b[j * 4 + 2]) +
+                           a[3 * 4 + i] * b[j * 4 + 3];
+}
+
+// inverse(view)[3].xyz by cofactors (shaders/mesh_pbr.frag:187 evaluates this per fragment).
+inline void camera_position(const float* m, float out[3]) {
+    double inv12 = -(double)m[4] * m[9] * m[14] + (double)m[4] * m[10] * m[13] + (double)m[8] * m[5] * m[14] -
+                   (double)m[8] * m[6] * m[13] - (double)m[12] * m[5] * m[10] + (double)m[12] * m[6] * m[9];
+    double inv13 = (double)m[0] * m[9] * m[14] - (double)m[0] * m[10] * m[13] - (double)m[8] * m[1] * m[14] +
+                   (double)m[8] * m[2] * m[13] + (double)m[12] * m[1] * m[10] - (double)m[12] * m[2] * m[9];
+    double inv14 = -(double)m[0] * m[5] * m[14] + (double)m[0] * m[6] * m[13] + (double)m[4] * m[1] * m[14] -
+                   (double)m[4] * m[2] * m[13] - (double)m[12] * m[1] * m[6] + (double)m[12] * m[2] * m[5];
+    double inv15 = (double)m[0] * m[5] * m[10] - (double)m[0] * m[6] * m[9] - (double)m[4] * m[1] * m[10] +
+                   (double)m[4] * m[2] * m[9] + (double)m[8] * m[1] * m[6] - (double)m[8] * m[2] * m[5];
+    // column 3 of the inverse = (inv[12], inv[13], inv[14], inv[15]) / det; det*inv[15]... use w-normalised form
+    double inv0 = (double)m[5] * m[10] * m[15] - (double)m[5] * m[11] * m[14] - (double)m[9] * m[6] * m[15] +
+                  (double)m[9] * m[7] * m[14] + (double)m[13] * m[6] * m[11] - (double)m[13] * m[7] * m[10];
+    double inv4 = -(double)m[4] * m[10] * m[15] + (double)m[4] * m[11] * m[14] + (double)m[8] * m[6] * m[15] -
+                  (double)m[8] * m[7] * m[14] - (double)m[12] * m[6] * m[11] + (double)m[12] * m[7] * m[10];
+    double inv8 = (double)m[4] * m[9] * m[15] - (double)m[4] * m[11] * m[13] - (double)m[8] * m[5] * m[15] +
+                  (double)m[8] * m[7] * m[13] + (double)m[12] * m[5] * m[11] - (double)m[12] * m[7] * m[9];
+    double det = (double)m[0] * inv0 + (double)m[1] * inv4 + (double)m[2] * inv8 + (double)m[3] * inv12;
+    (void)inv15;
+    out[0] = (float)(inv12 / det);
+    out[1] = (float)(inv13 / det);
+    out[2] = (float)(inv14 / det);
+}
+
+struct MeshInfo { DMesh d; };
+
+struct FramePlan {
+    std::vector<DObject> objects;
+    std::vector<uint32_t> primBase;     // nobj + 1
+    std::vector<DChunk> chunks;
+    std::vector<float> shadowMvp;       // layers * nobj * 16
+    int shadowLayers = 0;
+    uint32_t totalTris = 0;
+    uint32_t opaqueCount = 0;           // objects [0, opaqueCount) are MainColor, the rest Transparent
+    ShadeConst sc;
+    RasterTarget mainTarget;
+    RasterTarget shadowTarget;
+};
+
+// Returns an empty string on success, else the reason the draw list is invalid.
+inline std::string plan_frame(const VkrGPUSceneData* scene, const VkrRenderObject* objs, size_t n, const VkrFrameParams* fp,
+                              const std::vector<DMesh>& meshes, const std::vector<DMaterial>& materials,
+                              uint32_t W, uint32_t H, uint32_t S, FramePlan& plan) {
+    plan.objects.resize(n);
+    plan.primBase.resize(n + 1);
+    plan.chunks.clear();
+    plan.shadowLayers = fp->enableShadows ? (fp->shadowMode < 3 ? 1 : VKR_NUM_CASCADES) : 0;
+    plan.shadowMvp.resize((size_t)plan.shadowLayers * n * 16);
+    uint64_t prim = 0;
+    bool seenTransparent = false;
+    plan.opaqueCount = (uint32_t)n;
+    for (size_t i = 0; i < n; ++i) {
+        const VkrRenderObject& ro = objs[i];
+        if (ro.mesh >= meshes.size()) return "render object references an unknown mesh";
+        if (ro.material >= materials.size()) return "render object references an unknown material";
+        const DMesh& m = meshes[ro.mesh];
+        if ((uint64_t)ro.firstIndex + ro.indexCount > m.ni) return "render object index range exceeds the mesh";
+        const bool transparent = materials[ro.material].pass == VKR_PASS_TRANSPARENT;
+        if (transparent && !seenTransparent) { seenTransparent = true; plan.opaqueCount = (uint32_t)i; }
+        if (!transparent && seenTransparent)
+            return "draw list must be sorted opaque-first as update_scene does (src/vk_engine_run.cpp:454-458)";
+        DObject& o = plan.objects[i];
+        mat_mul(scene->viewproj, ro.transform, o.mvp);
+        std::memcpy(o.world, ro.transform, 64);
+        o.pos = m.pos; o.attrA = m.attrA; o.attrB = m.attrB;
+        o.idx = m.idx + ro.firstIndex;
+        o.triCount = ro.indexCount / 3;
+        o.primBase = (uint32_t)prim;
+        o.material = ro.material;
+        o.flags = transparent ? 1u : 0u;
+        plan.primBase[i] = (uint32_t)prim;
+        for (uint32_t t = 0; t < o.triCount; t += GEOM_BLOCK) plan.chunks.push_back(DChunk{(uint32_t)i, t});
+        prim += o.triCount;
+        if (prim >= 0xFFFFFFF0ull) return "too many primitives in one frame";
+        for (int l = 0; l < plan.shadowLayers; ++l)
+            mat_mul(scene->lightViewproj[l], ro.transform, &plan.shadowMvp[((size_t)l * n + i) * 16]);
+    }
+    plan.primBase[n] = (uint32_t)prim;
+    plan.totalTris = (uint32_t)prim;
+
+    ShadeConst& sc = plan.sc;
+    sc.scene = *scene;
+    camera_position(scene->view, sc.camPos);
+    {   // outLightVec = normalize(-sunlightDirection.xyz) (shaders/mesh.vert:21)
+        float x = -scene->sunlightDirection[0], y = -scene->sunlightDirection[1], z = -scene->sunlightDirection[2];
+        float inv = 1.0f / std::sqrt(x * x + y * y + z * z);
+        sc.lightVec[0] = x * inv; sc.lightVec[1] = y * inv; sc.lightVec[2] = z * inv;
+    }
+    const float bias[16] = {0.5f, 0, 0, 0, 0, 0.5f, 0, 0, 0, 0, 1.0f, 0, 0.5f, 0.5f, 0, 1.0f};   // mesh_pbr.frag:31-35
+    for (int l = 0; l < VKR_NUM_CASCADES; ++l) mat_mul(bias, scene->lightViewproj[l], sc.shadowMat[l]);
+    std::memcpy(sc.bgTop, fp->background.data1, 16);
+    std::memcpy(sc.bgBottom, fp->background.data2, 16);
+    sc.width = (int32_t)W; sc.height = (int32_t)H; sc.shadowExtent = (int32_t)S;
+    sc.sx0 = 0; sc.sy0 = 0; sc.sx1 = (int32_t)W; sc.sy1 = (int32_t)H;
+    if (fp->scissor[2] > 0 && fp->scissor[3] > 0) {
+        sc.sx0 = std::max(0, fp->scissor[0]); sc.sy0 = std::max(0, fp->scissor[1]);
+        sc.sx1 = std::min((int32_t)W, fp->scissor[0] + fp->scissor[2]);
+        sc.sy1 = std::min((int32_t)H, fp->scissor[1] + fp->scissor[3]);
+    }
+    sc.enableBackground = fp->enableBackground; sc.enablePostprocess = fp->enablePostprocess;
+    sc.enableSkybox = fp->enableSkybox; sc.fragShader = fp->fragShader;
+    // the shaders read the flags from the UBO .w components (src/vk_engine_run.cpp:124-125)
+    sc.shadowMode = (int32_t)scene->sunlightDirection[3];
+    sc.enableShadows = scene->sunlightColor[3] > 0.5f ? 1 : 0;
+    sc.nobj = (uint32_t)n;
+    sc.halfW = (float)W * 0.5f; sc.halfH = (float)H * 0.5f;
+
+    RasterTarget& mt = plan.mainTarget;
+    mt.vis = nullptr; mt.depthBits = nullptr;
+    mt.width = (int32_t)W; mt.height = (int32_t)H;
+    mt.sx0 = sc.sx0; mt.sy0 = sc.sy0; mt.sx1 = sc.sx1; mt.sy1 = sc.sy1;
+    mt.halfW = sc.halfW; mt.halfH = sc.halfH;
+    mt.cullFront = 0;                                   // VK_CULL_MODE_BACK_BIT (src/vk_engine_init.cpp:536)
+    RasterTarget& st = plan.shadowTarget;
+    st = mt;
+    st.width = st.height = (int32_t)S;
+    st.sx0 = st.sy0 = 0; st.sx1 = st.sy1 = (int32_t)S;
+    st.halfW = st.halfH = (float)S * 0.5f;
+    st.cullFront = 1;                                   // VK_CULL_MODE_FRONT_BIT (src/vk_engine_init.cpp:441)
+    return std::string();
+}
+
+}  // namespace vkr

@@ -1,0 +1,131 @@
+// vkr_internal.h — device-side data layout shared by the kernels and the C-ABI host code.
+// Everything here is POD; matrices are column-major (m[col*4+row]) like glm/GLSL.
+#pragma once
+#include <stdint.h>
+#include "../../include/vkr.h"
+
+#if defined(__CUDACC__)
+#define VKR_HD __host__ __device__ __forceinline__
+#define VKR_HDN __host__ __device__ __noinline__
+#else
+#define VKR_HD inline
+#define VKR_HDN inline
+struct alignas(16) float4 { float x, y, z, w; };
+struct alignas(8) float2 { float x, y; };
+struct alignas(4) uchar4 { unsigned char x, y, z, w; };
+static inline float4 make_float4(float x, float y, float z, float w) { return float4{x, y, z, w}; }
+#endif
+
+namespace vkr {
+
+// ---- visibility-buffer encoding -------------------------------------------------
+// key = (depth bits << 32) | (0xFFFFFFFE - primSeq).  64-bit atomicMin keeps the nearest
+// fragment; among equal depths the LARGER primSeq wins, which is LESS_OR_EQUAL with
+// depth writes in submission order (src/vk_engine_init.cpp:539).  Depth is clamped to
+// [0,1] so the IEEE bit pattern orders like the value.
+static const uint64_t VIS_CLEAR = 0x3F800000FFFFFFFFull;   // depth 1.0, no primitive
+static const uint32_t VIS_EMPTY_LO = 0xFFFFFFFFu;
+static const uint32_t DEPTH_ONE_BITS = 0x3F800000u;
+
+static const int TILE = 64;                // large-triangle tile edge in pixels
+static const int SMALL_MAX = 16;           // in-thread raster when bbox is <= SMALL_MAX x SMALL_MAX
+static const int GEOM_BLOCK = 256;         // triangles per geometry CTA (one per thread)
+static const float GUARD_BAND = 64.0f;     // clip x,y only beyond +-GUARD_BAND*w
+
+// One mesh in HBM: SoA, 3 x 16-byte streams + u32 indices.
+//   pos   = (x, y, z, 1)               read by every geometry pass (128-bit loads)
+//   attrA = (nx, ny, nz, uv_x)         read only by the shading pass
+//   attrB = (r, g, b, uv_y)            read only by the shading pass (Vertex.color.w is never used)
+struct DMesh {
+    const float4* pos;
+    const float4* attrA;
+    const float4* attrB;
+    const uint32_t* idx;
+    uint32_t nv, ni;
+};
+
+// Per-draw record, rebuilt every frame from VkrRenderObject (replaces GPUDrawPushConstants,
+// src/vk_types.h:72-76, plus the index-buffer binding).
+struct DObject {
+    float mvp[16];            // viewproj * world, glm association, computed on the host
+    float world[16];
+    const float4* pos;
+    const float4* attrA;
+    const float4* attrB;
+    const uint32_t* idx;      // already offset by firstIndex
+    uint32_t triCount;
+    uint32_t primBase;        // submission-order id of this draw's first triangle
+    uint32_t material;
+    uint32_t flags;           // bit0: transparent pass
+};
+
+struct DChunk { uint32_t obj, firstTri; };   // GEOM_BLOCK triangles of one draw
+
+struct DMaterial {
+    float colorFactors[4];
+    float metalRough[4];
+    int32_t albedoID, normalID, metalRoughID, pass;
+};
+
+struct DTexture {             // one bindless slot (combined image sampler)
+    const uchar4* data;       // mip chain, level l at data + mipOffset[l]
+    uint32_t w, h, levels;
+    uint32_t flags;           // bit0: sRGB, bit1: LINEAR sampler (else NEAREST), bit2: has alpha < 0.5 somewhere
+    uint32_t mipOffset[16];
+};
+
+// A projected, snapped, oriented triangle too large for the in-thread path (48 B).
+struct LargeTri {
+    int32_t X[3], Y[3];       // 24.8 fixed point, doubled area > 0
+    float z0, dzdx, dzdy;
+    int16_t bx0, by0, bx1, by1;
+    uint32_t seq;
+};
+struct LargeItem { uint32_t tri; uint16_t tx, ty; };   // (triangle, 64x64 tile)
+
+struct Queues {
+    LargeTri* tris;
+    LargeItem* items;
+    uint32_t* counters;       // [0] tri count, [1] item count, [2] overflow flag
+    uint32_t triCap, itemCap;
+};
+
+// Raster target of one geometry pass.
+struct RasterTarget {
+    uint64_t* vis;            // main pass: W*H keys
+    uint32_t* depthBits;      // shadow pass: S*S float bits
+    int32_t width, height;
+    int32_t sx0, sy0, sx1, sy1;   // scissor [sx0,sx1) x [sy0,sy1)
+    float halfW, halfH;
+    int32_t cullFront;        // 1: cull front faces (shadow), 0: cull back faces (main)
+};
+
+// Per-frame constants for the shading pass.
+struct ShadeConst {
+    VkrGPUSceneData scene;
+    float camPos[3];
+    float lightVec[3];                 // normalize(-sunlightDirection.xyz)
+    float shadowMat[VKR_NUM_CASCADES][16];   // biasMat * lightViewproj[i]
+    float bgTop[4], bgBottom[4];
+    int32_t width, height, shadowExtent;
+    int32_t sx0, sy0, sx1, sy1;
+    int32_t enableBackground, enablePostprocess, enableSkybox, fragShader;
+    int32_t shadowMode, enableShadows;
+    uint32_t nobj;
+    float halfW, halfH;
+};
+
+struct ShadeBuffers {
+    const uint64_t* vis;
+    const DObject* objects;
+    const uint32_t* primBase;          // nobj+1 prefix of triangle counts
+    const DMaterial* materials;
+    const DTexture* textures;          // VKR_MAX_BINDLESS slots
+    const DTexture* cube;              // 6 faces (nullptr when no cubemap)
+    const float* shadow;               // S*S*NUM_CASCADES
+    uint16_t* hdr;                     // RGBA16F
+    uint32_t* rgba8;
+    const float* srgbLut;              // 256 floats
+};
+
+}  // namespace vkr
