@@ -20,7 +20,7 @@ PASS_MAIN_COLOR, PASS_TRANSPARENT, PASS_OTHER = 0, 1, 2
 FRAG_PBR, FRAG_LAMBERT = 0, 1
 TARGET_RGBA8, TARGET_HDR16F, TARGET_DEPTH, TARGET_SHADOW, TARGET_PRIMID = range(5)
 CONFIG_TIMINGS = 1
-T_NAMES = ["upload", "shadow", "geometry", "shade", "transparent", "post", "total"]
+T_NAMES = ["upload", "shadow", "geometry", "shade", "transparent", "post", "total", "geom_kernel", "large_kernel", "clear"]
 
 # struct Vertex (src/vk_types.h:85-91), 48 bytes
 VERTEX_DTYPE = np.dtype(

@@ -204,7 +204,7 @@ struct VkrDevice {
     int lastSlot = 0;
     FramePlan plan;
 
-    cudaEvent_t tev[VKR_T_COUNT + 1] = {nullptr};
+    cudaEvent_t tev[8] = {nullptr};   // 0 start, 1 uploaded, 2 shadow, 3 cleared, 4 geometry kernel, 5 large kernel, 6 shaded
     bool tevValid = false;
     float timings[VKR_T_COUNT] = {0};
 
@@ -539,17 +539,19 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
         fill_u64_kernel<<<grid_for(px / 2, 256, 4096), 256, 0, st>>>(dev->vis, px, VIS_CLEAR);
         CK(cudaMemsetAsync(dev->q.counters, 0, 16, st));
         dev->launches += 1;
+        if (timing) CK(cudaEventRecord(dev->tev[3], st));
         // only the opaque prefix writes depth; transparent draws are blended in a later pass
         unsigned opaqueChunks = 0;
         while (opaqueChunks < nChunks && plan.chunks[opaqueChunks].obj < plan.opaqueCount) ++opaqueChunks;
         if (opaqueChunks) {
             geometry_kernel<false><<<opaqueChunks, GEOM_BLOCK, 0, st>>>(dObjects, dChunks, (const float*)dObjects, (uint32_t)(sizeof(DObject) / 4), rt, dev->q);
+            if (timing) CK(cudaEventRecord(dev->tev[4], st));
             large_raster_kernel<false><<<largeGrid, 256, 0, st>>>(rt, dev->q);
             dev->launches += 2;
-        }
+        } else if (timing) CK(cudaEventRecord(dev->tev[4], st));
         CK(cudaMemcpyAsync(dev->countersHost, dev->q.counters, 16, cudaMemcpyDeviceToHost, st));
     }
-    if (timing) CK(cudaEventRecord(dev->tev[3], st));
+    if (timing) CK(cudaEventRecord(dev->tev[5], st));
 
     // ---- shading half of draw_geometry + draw_skybox + draw_background + draw_postprocess + present blit
     {
@@ -562,7 +564,7 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
         dim3 grid((sc.sx1 - sc.sx0 + 15) / 16, (sc.sy1 - sc.sy0 + 7) / 8);
         if (grid.x && grid.y) { shade_kernel<<<grid, 128, 0, st>>>(sc, sb); dev->launches += 1; }
     }
-    if (timing) { CK(cudaEventRecord(dev->tev[4], st)); CK(cudaEventRecord(dev->tev[5], st)); CK(cudaEventRecord(dev->tev[6], st)); dev->tevValid = true; }
+    if (timing) { CK(cudaEventRecord(dev->tev[6], st)); dev->tevValid = true; }
     CK(cudaGetLastError());
     CK(cudaEventRecord(slot.rendered, st));
     dev->lastSlot = slotIdx;
@@ -579,14 +581,16 @@ int vkr_sync(VkrDevice* dev) {
     CK(cudaStreamSynchronize(dev->copyStream));
     if (dev->countersHost[2]) return dev->fail(VKR_ERROR_CAPACITY, "large-triangle queue overflow");
     if (dev->tevValid) {
-        // tev: 0 start, 1 upload done, 2 shadow done, 3 geometry done, 4 shade done
-        float ms;
-        cudaEventElapsedTime(&ms, dev->tev[0], dev->tev[1]); dev->timings[VKR_T_UPLOAD] = ms;
-        cudaEventElapsedTime(&ms, dev->tev[1], dev->tev[2]); dev->timings[VKR_T_SHADOW] = ms;
-        cudaEventElapsedTime(&ms, dev->tev[2], dev->tev[3]); dev->timings[VKR_T_GEOMETRY] = ms;
-        cudaEventElapsedTime(&ms, dev->tev[3], dev->tev[4]); dev->timings[VKR_T_SHADE] = ms;
+        auto el = [&](int a, int b) { float ms = 0; cudaEventElapsedTime(&ms, dev->tev[a], dev->tev[b]); return ms; };
+        dev->timings[VKR_T_UPLOAD] = el(0, 1);
+        dev->timings[VKR_T_SHADOW] = el(1, 2);
+        dev->timings[VKR_T_GEOMETRY] = el(2, 5);
+        dev->timings[VKR_T_CLEAR] = el(2, 3);
+        dev->timings[VKR_T_GEOM_KERNEL] = el(3, 4);
+        dev->timings[VKR_T_LARGE_KERNEL] = el(4, 5);
+        dev->timings[VKR_T_SHADE] = el(5, 6);
         dev->timings[VKR_T_TRANSPARENT] = 0; dev->timings[VKR_T_POST] = 0;
-        cudaEventElapsedTime(&ms, dev->tev[0], dev->tev[4]); dev->timings[VKR_T_TOTAL] = ms;
+        dev->timings[VKR_T_TOTAL] = el(0, 6);
         dev->stats.frametime = dev->timings[VKR_T_TOTAL];
         dev->stats.mesh_draw_time = dev->timings[VKR_T_SHADOW] + dev->timings[VKR_T_GEOMETRY];
     }
