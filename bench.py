@@ -55,7 +55,7 @@ def build_scene(r, width=W, height=H):
                 objs.append(mg.render_object(mesh, mats[k % 16], t, len(si)))
                 k += 1
     objs = np.array(objs)
-    view = mg.camera_view((0.0, 10.0, 48.0), pitch=-0.2)
+    view = mg.camera_view((0.0, 7.0, 40.0), pitch=-0.17)
     proj = mg.camera_projection(width / height)
     L = mg.light_matrix()
     sd = capi.make_scene_data(view, proj, [L] * 4, shadow_mode=1, enable_shadows=True)

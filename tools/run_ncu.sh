@@ -1,0 +1,11 @@
+# usage: bash tools/run_ncu.sh <tag>   (one gpurun call: plain run && launch list && full capture of the hot kernels)
+TAG=${1:-r01}
+mkdir -p gpurun_out
+CMD="python bench.py --steps 2 --warmup 3 --no-cpu-baseline"
+$CMD > gpurun_out/plain_$TAG.log 2>&1 &&
+ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches_$TAG.csv $CMD > gpurun_out/ncu_launch_$TAG.log 2>&1
+echo "launch list rc=$?"
+$CMD > gpurun_out/plain2_$TAG.log 2>&1 &&
+ncu --set full --clock-control none --import-source on -k regex:"geometry_kernel|shade_kernel" -s 9 -c 3 -f -o gpurun_out/prof_$TAG $CMD > gpurun_out/ncu_full_$TAG.log 2>&1
+echo "full capture rc=$?"
+ls -la gpurun_out | tail -12
