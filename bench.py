@@ -209,7 +209,11 @@ def run_b200(args):
         dist = dist_mod
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     lib = vk_renderer_b200.load()
+    # one explicit stream for everything (kernels, NCCL, events): the legacy default stream has
+    # handle 0, which VkrConfig.stream reads as "create your own"
+    torch.cuda.set_stream(torch.cuda.Stream())
     stream = torch.cuda.current_stream().cuda_stream
+    assert stream != 0
     r = capi.Renderer(lib, "vkr", W, H, shadow_extent=S, device=local, stream=stream, flags=capi.CONFIG_TIMINGS)
     sd, objs, fp, info = build_scene(r)
 

@@ -207,8 +207,10 @@ int vkr_get_timings(VkrDevice* dev, float* msOut, int count);      /* last synce
 /* Raw device pointer of a target of the last drawn frame (for NCCL gathers). */
 int vkr_device_ptr(VkrDevice* dev, VkrTarget what, void** ptr, size_t* bytes);
 
-/* Number of kernel launches issued by the last vkr_draw. */
+/* Number of kernel launches issued by the last vkr_draw, and the bytes it copied host->device
+ * (draw list + cluster table + light matrices: what replaces the push constants and the scene UBO). */
 int vkr_launch_count(VkrDevice* dev);
+size_t vkr_upload_bytes(VkrDevice* dev);
 
 const char* vkr_last_error(VkrDevice* dev);
 const char* vkr_version(void);

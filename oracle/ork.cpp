@@ -63,6 +63,13 @@ inline vec4 mul(const mat4& m, vec4 v) {
         o[i] = (m.m[0][i] * v.x + m.m[1][i] * v.y) + (m.m[2][i] * v.z + m.m[3][i] * v.w);
     return r;
 }
+// Position path (spec): clip = M*(p,1) as three nested FMAs per component.
+inline vec4 mul_point_fma(const mat4& m, float x, float y, float z) {
+    vec4 r;
+    float* o = &r.x;
+    for (int i = 0; i < 4; ++i) o[i] = std::fmaf(m.m[0][i], x, std::fmaf(m.m[1][i], y, std::fmaf(m.m[2][i], z, m.m[3][i])));
+    return r;
+}
 // glm mat4*mat4: column j = ((A0*b0 + A1*b1) + A2*b2) + A3*b3 (type_mat4x4.inl:606-625).
 inline mat4 mul(const mat4& a, const mat4& b) {
     mat4 r;
@@ -633,12 +640,13 @@ bool setup_tri(const vec4 c[3], const Viewport& vp, CullMode cull, RTri& t) {
     int32_t X[3], Y[3];
     float z[3];
     for (int i = 0; i < 3; ++i) {
-        float xn = c[i].x / c[i].w, yn = c[i].y / c[i].w;
-        z[i] = c[i].z / c[i].w;
-        float xf = xn * vp.halfW + vp.halfW;   // viewport transform, x=0,y=0,minDepth=0,maxDepth=1
-        float yf = yn * vp.halfH + vp.halfH;
-        X[i] = (int32_t)std::floor(xf * 256.0f + 0.5f);   // subPixelPrecisionBits = 8
-        Y[i] = (int32_t)std::floor(yf * 256.0f + 0.5f);
+        float rw = 1.0f / c[i].w;
+        float xn = c[i].x * rw, yn = c[i].y * rw;
+        z[i] = c[i].z * rw;
+        // viewport transform (x=0,y=0,minDepth=0,maxDepth=1) fused with the snap to 8 sub-pixel bits
+        // (subPixelPrecisionBits = 8): X = rint(xn * 128W + 128W), round-half-even
+        X[i] = (int32_t)std::nearbyint(std::fmaf(xn, vp.halfW * 256.0f, vp.halfW * 256.0f));
+        Y[i] = (int32_t)std::nearbyint(std::fmaf(yn, vp.halfH * 256.0f, vp.halfH * 256.0f));
     }
     int64_t A2 = (int64_t)(X[1] - X[0]) * (Y[2] - Y[0]) - (int64_t)(X[2] - X[0]) * (Y[1] - Y[0]);
     // Vulkan: a = -1/2 * sum(x_i*y_j - x_j*y_i) in y-down framebuffer coords; frontFace CCW => a>0 front.
@@ -664,8 +672,9 @@ bool setup_tri(const vec4 c[3], const Viewport& vp, CullMode cull, RTri& t) {
     float d1z = z[1] - z[0], d2z = z[2] - z[0];
     float fA = (float)A2;
     t.z0 = z[0];
-    t.dzdx = ((d1z * d2y - d2z * d1y) / fA) * 256.0f;
-    t.dzdy = ((d2z * d1x - d1z * d2x) / fA) * 256.0f;
+    float rA = 1.0f / fA;
+    t.dzdx = ((d1z * d2y - d2z * d1y) * rA) * 256.0f;
+    t.dzdy = ((d2z * d1x - d1z * d2x) * rA) * 256.0f;
     return true;
 }
 
@@ -805,7 +814,7 @@ void build_rtris(const DrawCtx& dc, const mat4& vpMat, const Viewport& vp, CullM
             for (int k = 0; k < 3; ++k) {
                 uint32_t vi = mesh.idx[ro.firstIndex + 3 * t + k];
                 const VkrVertex& v = mesh.v[vi];
-                c[k] = mul(M, vec4{v.position[0], v.position[1], v.position[2], 1.0f});
+                c[k] = mul_point_fma(M, v.position[0], v.position[1], v.position[2]);
             }
             process_triangle(c, vp, cull, ch.seq0 + (t - ch.t0), ch.obj, t, [&](const RTri& rt) { outp.push_back(rt); });
         }
@@ -852,7 +861,7 @@ void pass_shadow(const DrawCtx& dc) {
 VSOut vertex_main(const VkrVertex& v, const mat4& world, const mat4& M, const VkrGPUSceneData& sd) {
     VSOut o;
     vec4 p = {v.position[0], v.position[1], v.position[2], 1.0f};
-    o.clip = mul(M, p);
+    o.clip = mul_point_fma(M, v.position[0], v.position[1], v.position[2]);
     o.normal = mul3(world, vec3{v.normal[0], v.normal[1], v.normal[2]});
     o.color = {v.color[0], v.color[1], v.color[2]};
     o.uv = {v.uv_x, v.uv_y};

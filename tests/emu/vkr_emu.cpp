@@ -27,8 +27,18 @@ struct EmuImage {
 };
 struct EmuMesh { std::vector<float4> pos, a, b; std::vector<uint32_t> idx; };
 
+struct EmuDevice;
+struct EmuClusters : ClusterProvider {
+    EmuDevice* d;
+    std::vector<ClusterData*> store;
+    std::vector<std::pair<std::vector<uint32_t>, ClusterRange>> cache;   // key (mesh, first, count)
+    bool get(uint32_t mesh, uint32_t firstIndex, uint32_t indexCount, ClusterRange& out) override;
+    ~EmuClusters() { for (auto* c : store) delete c; }
+};
+
 struct EmuDevice {
     uint32_t W, H, S;
+    EmuClusters clusters;
     std::vector<EmuMesh*> meshStore;
     std::vector<DMesh> meshes;
     std::vector<EmuImage*> images;
@@ -45,6 +55,16 @@ struct EmuDevice {
     VkrEngineStats stats{};
     std::string err;
 };
+
+bool EmuClusters::get(uint32_t mesh, uint32_t firstIndex, uint32_t indexCount, ClusterRange& out) {
+    for (auto& e : cache) if (e.first[0] == mesh && e.first[1] == firstIndex && e.first[2] == indexCount) { out = e.second; return true; }
+    ClusterData* cd = new ClusterData();
+    build_clusters(d->meshes[mesh].idx + firstIndex, indexCount / 3, d->meshes[mesh].nv, *cd);
+    store.push_back(cd);
+    out = ClusterRange{cd->verts.data(), cd->tris.data(), cd->info.data()};
+    cache.push_back({{mesh, firstIndex, indexCount}, out});
+    return true;
+}
 
 static uint32_t srgb8(float l) {
     if (!(l > 0.0f)) return 0u;
@@ -107,6 +127,7 @@ int emu_update_bindless_texture(EmuDevice* d, int index, uint32_t image, int sam
 
 int emu_create(const VkrConfig* cfg, EmuDevice** out) {
     EmuDevice* d = new EmuDevice();
+    d->clusters.d = d;
     d->W = cfg->width; d->H = cfg->height; d->S = cfg->shadowExtent ? cfg->shadowExtent : 2048;
     size_t px = (size_t)d->W * d->H;
     d->vis.assign(px, VIS_CLEAR);
@@ -176,14 +197,22 @@ template <bool SHADOW>
 static void run_pass(EmuDevice* d, const FramePlan& plan, RasterTarget rt, const float* mvps, uint32_t stride, unsigned nChunks) {
     Queues q{d->ltris.data(), d->litems.data(), d->counters, (uint32_t)d->ltris.size(), (uint32_t)d->litems.size()};
     d->counters[0] = d->counters[1] = d->counters[2] = 0;
-    for (unsigned c = 0; c < nChunks; ++c) {                 // geometry_kernel
+    std::vector<CachedVtx> svtx(3 * GEOM_BLOCK);
+    for (unsigned c = 0; c < nChunks; ++c) {                 // geometry_kernel: one CTA per cluster
         const DChunk ch = plan.chunks[c];
         const DObject& o = plan.objects[ch.obj];
-        for (uint32_t t = 0; t < GEOM_BLOCK; ++t) {
-            uint32_t tri = ch.firstTri + t;
-            if (tri >= o.triCount) break;
-            if (SHADOW) { DepthSink s{rt.depthBits, rt.width}; geometry_triangle(mvps + (size_t)ch.obj * stride, o.pos, o.idx, tri, 0u, rt, q, s); }
-            else { uint32_t seq = o.primBase + tri; VisSink s{rt.vis, rt.width, 0xFFFFFFFEu - seq}; geometry_triangle(mvps + (size_t)ch.obj * stride, o.pos, o.idx, tri, seq, rt, q, s); }
+        const float* mvp = mvps + (size_t)ch.obj * stride;
+        const uint32_t cluster = ch.firstTri / GEOM_BLOCK;
+        const uint2 info = o.clInfo[cluster];
+        const uint32_t nVerts = info.y & 0xFFFFu, nTris = info.y >> 16;
+        const uint32_t* clVerts = o.clVerts + info.x;
+        for (uint32_t v = 0; v < nVerts; ++v) svtx[v] = cluster_vertex(mvp, o.pos[clVerts[v]], rt);      // phase 1
+        for (uint32_t t = 0; t < nTris; ++t) {                                                           // phase 2
+            const uint32_t packed = o.clTris[(size_t)cluster * GEOM_BLOCK + t];
+            const uint32_t l0 = packed & 1023u, l1 = (packed >> 10) & 1023u, l2 = packed >> 20;
+            const uint32_t seq = c * GEOM_BLOCK + t;
+            if (SHADOW) { DepthSink s{rt.depthBits, rt.width}; cluster_triangle(svtx[l0], svtx[l1], svtx[l2], mvp, o.pos, clVerts[l0], clVerts[l1], clVerts[l2], 0u, rt, q, s); }
+            else { VisSink s{rt.vis, rt.width, 0xFFFFFFFEu - seq}; cluster_triangle(svtx[l0], svtx[l1], svtx[l2], mvp, o.pos, clVerts[l0], clVerts[l1], clVerts[l2], seq, rt, q, s); }
         }
     }
     for (uint32_t i = 0; i < d->counters[1]; ++i) {          // large_raster_kernel
@@ -200,7 +229,7 @@ extern "C" {
 
 int emu_draw(EmuDevice* d, const VkrGPUSceneData* scene, const VkrRenderObject* objs, size_t n, const VkrFrameParams* fp) {
     FramePlan& plan = d->plan;
-    std::string why = plan_frame(scene, objs, n, fp, d->meshes, d->materials, d->W, d->H, d->S, plan);
+    std::string why = plan_frame(scene, objs, n, fp, d->meshes, d->materials, d->clusters, d->W, d->H, d->S, plan);
     if (!why.empty()) { d->err = why; return VKR_ERROR_INVALID_ARGUMENT; }
     const unsigned nChunks = (unsigned)plan.chunks.size();
     for (int layer = 0; layer < plan.shadowLayers; ++layer) {
@@ -217,7 +246,7 @@ int emu_draw(EmuDevice* d, const VkrGPUSceneData* scene, const VkrRenderObject* 
     run_pass<false>(d, plan, rt, (const float*)plan.objects.data(), sizeof(DObject) / 4, opaqueChunks);
     if (d->counters[2]) { d->err = "queue overflow"; return VKR_ERROR_CAPACITY; }
     ShadeBuffers sb{};
-    sb.vis = d->vis.data(); sb.objects = plan.objects.data(); sb.primBase = plan.primBase.data();
+    sb.vis = d->vis.data(); sb.objects = plan.objects.data(); sb.chunks = plan.chunks.data();
     sb.materials = d->materials.data(); sb.textures = d->tex.data(); sb.cube = d->haveCube ? d->cube : nullptr;
     sb.shadow = reinterpret_cast<const float*>(d->shadowBits.data());
     sb.hdr = d->hdr.data(); sb.rgba8 = d->rgba8.data(); sb.srgbLut = d->lut;
@@ -234,7 +263,13 @@ int emu_readback(EmuDevice* d, int what, void* dst, size_t bytes) {
         case VKR_TARGET_SHADOW: std::memcpy(dst, d->shadowBits.data(), d->shadowBits.size() * 4); return 0;
         case VKR_TARGET_DEPTH: for (size_t i = 0; i < px; ++i) ((uint32_t*)dst)[i] = (uint32_t)(d->vis[i] >> 32); return 0;
         case VKR_TARGET_PRIMID:
-            for (size_t i = 0; i < px; ++i) { uint32_t lo = (uint32_t)d->vis[i]; ((uint32_t*)dst)[i] = lo == VIS_EMPTY_LO ? 0xFFFFFFFFu : 0xFFFFFFFEu - lo; }
+            for (size_t i = 0; i < px; ++i) {
+                uint32_t lo = (uint32_t)d->vis[i];
+                if (lo == VIS_EMPTY_LO) { ((uint32_t*)dst)[i] = 0xFFFFFFFFu; continue; }
+                uint32_t seq = 0xFFFFFFFEu - lo;
+                const DChunk ch = d->plan.chunks[seq >> 8];
+                ((uint32_t*)dst)[i] = d->plan.objects[ch.obj].primBase + ch.firstTri + (seq & 255u);
+            }
             return 0;
     }
     return -1;

@@ -110,7 +110,7 @@ class EngineStats(C.Structure):
 VKR_SYMBOLS = [
     "create", "destroy", "upload_mesh", "create_image", "update_bindless_texture", "set_cubemap",
     "build_material", "draw", "readback", "readback_async", "sync", "stats", "get_timings",
-    "device_ptr", "launch_count", "last_error", "version",
+    "device_ptr", "launch_count", "upload_bytes", "last_error", "version",
 ]
 
 
@@ -196,6 +196,7 @@ class Renderer:
                 "get_timings": ([p, C.POINTER(C.c_float), C.c_int], C.c_int),
                 "device_ptr": ([p, C.c_int, C.POINTER(p), C.POINTER(C.c_size_t)], C.c_int),
                 "launch_count": ([p], C.c_int),
+                "upload_bytes": ([p], C.c_size_t),
                 "version": ([], C.c_char_p),
             })
         for name, (args, res) in sigs.items():
@@ -298,3 +299,6 @@ class Renderer:
 
     def launch_count(self) -> int:
         return self._f("launch_count")(self.dev)
+
+    def upload_bytes(self) -> int:
+        return self._f("upload_bytes")(self.dev)

@@ -11,6 +11,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <map>
 #include <string>
 #include <vector>
 
@@ -40,12 +41,17 @@ __global__ void fill_u32_kernel(uint32_t* __restrict__ dst, size_t n, uint32_t v
     for (size_t k = i; k < n4; k += stride) d4[k] = make_uint4(v, v, v, v);
     if (i == 0) for (size_t k = n4 << 2; k < n; ++k) dst[k] = v;
 }
-__global__ void extract_vis_kernel(const uint64_t* __restrict__ vis, uint32_t* __restrict__ out, size_t n, int what) {
+__global__ void extract_vis_kernel(const uint64_t* __restrict__ vis, uint32_t* __restrict__ out, size_t n, int what,
+                                   const DChunk* __restrict__ chunks, const DObject* __restrict__ objects) {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     uint64_t k = vis[i];
-    if (what == 0) out[i] = (uint32_t)(k >> 32);                                  // depth bits
-    else { uint32_t lo = (uint32_t)k; out[i] = lo == VIS_EMPTY_LO ? 0xFFFFFFFFu : 0xFFFFFFFEu - lo; }
+    if (what == 0) { out[i] = (uint32_t)(k >> 32); return; }                     // depth bits
+    uint32_t lo = (uint32_t)k;
+    if (lo == VIS_EMPTY_LO) { out[i] = 0xFFFFFFFFu; return; }
+    const uint32_t seq = 0xFFFFFFFEu - lo;                                        // cluster*256 + local triangle
+    const DChunk ch = chunks[seq >> 8];
+    out[i] = objects[ch.obj].primBase + ch.firstTri + (seq & 255u);               // dense submission-order id
 }
 
 // ---- upload_mesh: AoS Vertex (48 B) -> three float4 streams
@@ -96,25 +102,43 @@ __global__ void mip_blit_kernel(const uchar4* __restrict__ src, int sw, int sh, 
     dst[(size_t)y * dw + x] = o;
 }
 
-// ---- geometry: one thread per triangle of a GEOM_BLOCK chunk of one draw
+// ---- geometry: one CTA per cluster (<= 256 triangles of one draw).
+// Phase 1 transforms each DISTINCT vertex of the cluster once (128-bit position loads) into shared
+// memory as snapped window coordinates; phase 2 runs one thread per triangle on those.
 template <bool SHADOW>
 __global__ void __launch_bounds__(GEOM_BLOCK) geometry_kernel(const DObject* __restrict__ objects, const DChunk* __restrict__ chunks,
                                                               const float* __restrict__ mvps, uint32_t mvpStride,
                                                               const __grid_constant__ RasterTarget rt, const __grid_constant__ Queues q) {
     __shared__ float s_mvp[16];
+    __shared__ uint4 s_vtx[3 * GEOM_BLOCK];
     const DChunk ch = chunks[blockIdx.x];
     const DObject& o = objects[ch.obj];
     if (threadIdx.x < 16) s_mvp[threadIdx.x] = mvps[(size_t)ch.obj * mvpStride + threadIdx.x];
+    const uint32_t cluster = ch.firstTri / GEOM_BLOCK;
+    const uint2 info = __ldg(o.clInfo + cluster);
+    const uint32_t nVerts = info.y & 0xFFFFu, nTris = info.y >> 16;
+    const uint32_t* __restrict__ clVerts = o.clVerts + info.x;
+    const float4* __restrict__ pos = o.pos;
     __syncthreads();
-    const uint32_t tri = ch.firstTri + threadIdx.x;
-    if (tri >= o.triCount) return;
+    for (uint32_t v = threadIdx.x; v < nVerts; v += GEOM_BLOCK) {
+        const CachedVtx cv = cluster_vertex(s_mvp, __ldg(pos + __ldg(clVerts + v)), rt);
+        s_vtx[v] = make_uint4((uint32_t)cv.X, (uint32_t)cv.Y, cv.zbits, cv.flag);
+    }
+    __syncthreads();
+    if (threadIdx.x >= nTris) return;
+    const uint32_t packed = __ldg(o.clTris + (size_t)cluster * GEOM_BLOCK + threadIdx.x);
+    const uint32_t l0 = packed & 1023u, l1 = (packed >> 10) & 1023u, l2 = packed >> 20;
+    const uint4 a = s_vtx[l0], b = s_vtx[l1], c = s_vtx[l2];
+    const CachedVtx va{(int32_t)a.x, (int32_t)a.y, a.z, a.w}, vb{(int32_t)b.x, (int32_t)b.y, b.z, b.w}, vc{(int32_t)c.x, (int32_t)c.y, c.z, c.w};
+    uint32_t g0 = 0, g1 = 0, g2 = 0;
+    if (a.w | b.w | c.w) { g0 = __ldg(clVerts + l0); g1 = __ldg(clVerts + l1); g2 = __ldg(clVerts + l2); }
+    const uint32_t seq = blockIdx.x * GEOM_BLOCK + threadIdx.x;
     if (SHADOW) {
         DepthSink sink{rt.depthBits, rt.width};
-        geometry_triangle(s_mvp, o.pos, o.idx, tri, 0u, rt, q, sink);
+        cluster_triangle(va, vb, vc, s_mvp, pos, g0, g1, g2, 0u, rt, q, sink);
     } else {
-        const uint32_t seq = o.primBase + tri;
         VisSink sink{rt.vis, rt.width, 0xFFFFFFFEu - seq};
-        geometry_triangle(s_mvp, o.pos, o.idx, tri, seq, rt, q, sink);
+        cluster_triangle(va, vb, vc, s_mvp, pos, g0, g1, g2, seq, rt, q, sink);
     }
 }
 
@@ -137,9 +161,16 @@ __global__ void __launch_bounds__(256) large_raster_kernel(const __grid_constant
     }
 }
 
-// ---- shade + resolve: one thread per pixel of the scissor rectangle, 8x8 pixel blocks per 2 warps
-__global__ void __launch_bounds__(128) shade_kernel(const __grid_constant__ ShadeConst sc, const __grid_constant__ ShadeBuffers sb) {
-    // 16x8 pixel block; each warp covers an 8x4... lanes map to a 8x4 footprint for locality
+// ---- shade + resolve: one thread per pixel of the scissor rectangle; a CTA is a 16x8 pixel block,
+// each warp an 8x4 footprint (triangle / texel / shadow-map locality).  The sRGB decode table
+// lives in shared memory.
+__global__ void __launch_bounds__(128) shade_kernel(const __grid_constant__ ShadeConst sc, const __grid_constant__ ShadeBuffers sbIn) {
+    __shared__ float s_lut[256];
+    s_lut[threadIdx.x] = sbIn.srgbLut[threadIdx.x];
+    s_lut[threadIdx.x + 128] = sbIn.srgbLut[threadIdx.x + 128];
+    __syncthreads();
+    ShadeBuffers sb = sbIn;
+    sb.srgbLut = s_lut;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int lx = (lane & 7) + ((warp & 1) << 3), ly = (lane >> 3) + ((warp >> 1) << 2);
     const int px = sc.sx0 + blockIdx.x * 16 + lx, py = sc.sy0 + blockIdx.y * 8 + ly;
@@ -196,12 +227,19 @@ struct VkrDevice {
     std::vector<DMaterial> materials;
     DMaterial* matDev = nullptr; size_t matCap = 0; bool matDirty = true;
 
+    struct RangeKey { uint32_t mesh, first, count; bool operator<(const RangeKey& o) const {
+        return mesh != o.mesh ? mesh < o.mesh : (first != o.first ? first < o.first : count < o.count); } };
+    std::map<RangeKey, ClusterRange> ranges;   // cluster data per (mesh, firstIndex, indexCount), built at first use
+    std::vector<std::vector<uint32_t>> meshIndexHost;   // host copy of each mesh's indices (cluster building)
+    size_t uploadBytes = 0;
+
     Queues q{};
     uint32_t* countersHost = nullptr;   // pinned mirror of q.counters after the last frame
 
     FrameSlot slots[VKR_FRAME_OVERLAP];
     uint64_t frameIndex = 0;
     int lastSlot = 0;
+    const DChunk* lastChunks = nullptr; const DObject* lastObjects = nullptr;
     FramePlan plan;
 
     cudaEvent_t tev[8] = {nullptr};   // 0 start, 1 uploaded, 2 shadow, 3 cleared, 4 geometry kernel, 5 large kernel, 6 shaded
@@ -226,6 +264,32 @@ static void init_lut() {
         g_srgb_lut[i] = (float)(c <= 0.04045 ? c / 12.92 : std::pow((c + 0.055) / 1.055, 2.4));
     }
 }
+
+static int dev_alloc(VkrDevice* dev, void** p, size_t bytes);
+
+struct DeviceClusterProvider : ClusterProvider {
+    VkrDevice* dev;
+    explicit DeviceClusterProvider(VkrDevice* d) : dev(d) {}
+    bool get(uint32_t mesh, uint32_t firstIndex, uint32_t indexCount, ClusterRange& out) override {
+        VkrDevice::RangeKey key{mesh, firstIndex, indexCount};
+        auto it = dev->ranges.find(key);
+        if (it != dev->ranges.end()) { out = it->second; return true; }
+        ClusterData cd;
+        build_clusters(dev->meshIndexHost[mesh].data() + firstIndex, indexCount / 3, dev->meshes[mesh].nv, cd);
+        uint32_t *dv = nullptr, *dt = nullptr; uint2* di = nullptr;
+        if (dev_alloc(dev, (void**)&dv, cd.verts.size() * 4) || dev_alloc(dev, (void**)&dt, cd.tris.size() * 4) ||
+            dev_alloc(dev, (void**)&di, cd.info.size() * sizeof(uint2)))
+            return false;
+        bool ok = cudaMemcpyAsync(dv, cd.verts.data(), cd.verts.size() * 4, cudaMemcpyHostToDevice, dev->stream) == cudaSuccess &&
+                  cudaMemcpyAsync(dt, cd.tris.data(), cd.tris.size() * 4, cudaMemcpyHostToDevice, dev->stream) == cudaSuccess &&
+                  cudaMemcpyAsync(di, cd.info.data(), cd.info.size() * sizeof(uint2), cudaMemcpyHostToDevice, dev->stream) == cudaSuccess &&
+                  cudaStreamSynchronize(dev->stream) == cudaSuccess;   // cd is a local
+        if (!ok) return false;
+        out = ClusterRange{dv, dt, di};
+        dev->ranges[key] = out;
+        return true;
+    }
+};
 
 static int dev_alloc(VkrDevice* dev, void** p, size_t bytes) {
     cudaError_t e = cudaMalloc(p, bytes ? bytes : 16);
@@ -356,6 +420,7 @@ int vkr_upload_mesh(VkrDevice* dev, const uint32_t* indices, size_t ni, const Vk
     if (staging) cudaFree(staging);
     m.pos = pos; m.attrA = aA; m.attrB = aB; m.idx = idx;
     dev->meshes.push_back(m);
+    dev->meshIndexHost.emplace_back(indices, indices + ni);
     *out = (VkrMesh)(dev->meshes.size() - 1);
     return VKR_SUCCESS;
 }
@@ -464,7 +529,8 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
     if (!scene || !fp || (n && !objs)) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_draw: null argument");
     CK(cudaSetDevice(dev->device));
     FramePlan& plan = dev->plan;
-    std::string why = plan_frame(scene, objs, n, fp, dev->meshes, dev->materials, dev->W, dev->H, dev->S, plan);
+    DeviceClusterProvider provider(dev);
+    std::string why = plan_frame(scene, objs, n, fp, dev->meshes, dev->materials, provider, dev->W, dev->H, dev->S, plan);
     if (!why.empty()) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, why.c_str());
     cudaStream_t st = dev->stream;
     dev->launches = 0;
@@ -490,6 +556,7 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
     // ---- upload the draw list (replaces per-object push constants + the scene UBO)
     const int slotIdx = (int)(dev->frameIndex % VKR_FRAME_OVERLAP);
     FrameSlot& slot = dev->slots[slotIdx];
+    dev->uploadBytes = 0;
     const size_t szObj = sizeof(DObject) * n, szPrim = 4 * (n + 1), szChunk = sizeof(DChunk) * plan.chunks.size();
     const size_t szShadow = plan.shadowMvp.size() * 4;
     auto align16 = [](size_t v) { return (v + 15) & ~(size_t)15; };
@@ -504,10 +571,10 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
     if (szChunk) std::memcpy(hp + offChunk, plan.chunks.data(), szChunk);
     if (szShadow) std::memcpy(hp + offShadow, plan.shadowMvp.data(), szShadow);
     CK(cudaMemcpyAsync(slot.devbuf, slot.pinned, total, cudaMemcpyHostToDevice, st));
+    dev->uploadBytes = total;
     CK(cudaEventRecord(slot.uploaded, st));
     char* dp = (char*)slot.devbuf;
     const DObject* dObjects = (const DObject*)(dp + offObj);
-    const uint32_t* dPrimBase = (const uint32_t*)(dp + offPrim);
     const DChunk* dChunks = (const DChunk*)(dp + offChunk);
     const float* dShadowMvp = (const float*)(dp + offShadow);
     if (timing) CK(cudaEventRecord(dev->tev[1], st));
@@ -556,7 +623,7 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
     // ---- shading half of draw_geometry + draw_skybox + draw_background + draw_postprocess + present blit
     {
         ShadeBuffers sb{};
-        sb.vis = dev->vis; sb.objects = dObjects; sb.primBase = dPrimBase; sb.materials = dev->matDev;
+        sb.vis = dev->vis; sb.objects = dObjects; sb.chunks = dChunks; sb.materials = dev->matDev;
         sb.textures = dev->texDev; sb.cube = dev->haveCube ? dev->cubeDev : nullptr;
         sb.shadow = reinterpret_cast<const float*>(dev->shadowBits);
         sb.hdr = dev->hdr; sb.rgba8 = dev->rgba8[slotIdx]; sb.srgbLut = dev->lut;
@@ -568,6 +635,7 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
     CK(cudaGetLastError());
     CK(cudaEventRecord(slot.rendered, st));
     dev->lastSlot = slotIdx;
+    dev->lastChunks = dChunks; dev->lastObjects = dObjects;
     dev->frameIndex++;
     dev->stats.drawcall_count = (int32_t)n;
     dev->stats.triangle_count = (int32_t)plan.totalTris;
@@ -617,7 +685,8 @@ static int do_readback(VkrDevice* dev, VkrTarget what, void* dst, size_t dstByte
     if (what == VKR_TARGET_DEPTH || what == VKR_TARGET_PRIMID) {
         const size_t px = (size_t)dev->W * dev->H;
         if (!dev->scratch) ALLOC(dev->scratch, px * 4);
-        extract_vis_kernel<<<(unsigned)((px + 255) / 256), 256, 0, dev->stream>>>(dev->vis, dev->scratch, px, what == VKR_TARGET_DEPTH ? 0 : 1);
+        extract_vis_kernel<<<(unsigned)((px + 255) / 256), 256, 0, dev->stream>>>(dev->vis, dev->scratch, px, what == VKR_TARGET_DEPTH ? 0 : 1,
+                                                                                    dev->lastChunks, dev->lastObjects);
         CK(cudaGetLastError());
         CK(cudaMemcpyAsync(dst, dev->scratch, bytes, cudaMemcpyDeviceToHost, dev->stream));
         if (sync) return vkr_sync(dev);
@@ -654,5 +723,6 @@ int vkr_device_ptr(VkrDevice* dev, VkrTarget what, void** ptr, size_t* bytes) {
 }
 
 int vkr_launch_count(VkrDevice* dev) { return dev ? dev->launches : 0; }
+size_t vkr_upload_bytes(VkrDevice* dev) { return dev ? dev->uploadBytes : 0; }
 
 }  // extern "C"

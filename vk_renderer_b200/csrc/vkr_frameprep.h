@@ -50,11 +50,43 @@ inline void camera_position(const float* m, float out[3]) {
     out[2] = (float)(inv14 / det);
 }
 
-struct MeshInfo { DMesh d; };
+// Host-side builder of the per-range cluster data (DObject::clVerts / clTris / clInfo).
+struct ClusterData {
+    std::vector<uint32_t> verts;     // concatenated distinct-vertex lists
+    std::vector<uint32_t> tris;      // nClusters * GEOM_BLOCK packed local ids
+    std::vector<uint2> info;         // per cluster
+};
+inline void build_clusters(const uint32_t* idx, uint32_t triCount, uint32_t nv, ClusterData& out) {
+    const uint32_t nCl = (triCount + GEOM_BLOCK - 1) / GEOM_BLOCK;
+    out.verts.clear(); out.tris.assign((size_t)nCl * GEOM_BLOCK, 0u); out.info.resize(nCl);
+    std::vector<uint32_t> stamp(nv, 0xFFFFFFFFu), local(nv, 0u);
+    for (uint32_t c = 0; c < nCl; ++c) {
+        const uint32_t t0 = c * GEOM_BLOCK, t1 = std::min(triCount, t0 + GEOM_BLOCK);
+        const uint32_t off = (uint32_t)out.verts.size();
+        uint32_t count = 0;
+        for (uint32_t t = t0; t < t1; ++t) {
+            uint32_t l[3];
+            for (int k = 0; k < 3; ++k) {
+                const uint32_t v = idx[3 * (size_t)t + k];
+                if (stamp[v] != c) { stamp[v] = c; local[v] = count++; out.verts.push_back(v); }
+                l[k] = local[v];
+            }
+            out.tris[(size_t)c * GEOM_BLOCK + (t - t0)] = l[0] | (l[1] << 10) | (l[2] << 20);
+        }
+        out.info[c] = uint2{off, count | ((t1 - t0) << 16)};
+    }
+}
+
+struct ClusterRange { const uint32_t* verts; const uint32_t* tris; const uint2* info; };
+// Implemented by the owner of the device (or emulated) memory: returns the cached range, building it on first use.
+struct ClusterProvider {
+    virtual ~ClusterProvider() {}
+    virtual bool get(uint32_t mesh, uint32_t firstIndex, uint32_t indexCount, ClusterRange& out) = 0;
+};
 
 struct FramePlan {
     std::vector<DObject> objects;
-    std::vector<uint32_t> primBase;     // nobj + 1
+    std::vector<uint32_t> primBase;     // nobj + 1 (dense ids, for stats / readback)
     std::vector<DChunk> chunks;
     std::vector<float> shadowMvp;       // layers * nobj * 16
     int shadowLayers = 0;
@@ -68,7 +100,7 @@ struct FramePlan {
 // Returns an empty string on success, else the reason the draw list is invalid.
 inline std::string plan_frame(const VkrGPUSceneData* scene, const VkrRenderObject* objs, size_t n, const VkrFrameParams* fp,
                               const std::vector<DMesh>& meshes, const std::vector<DMaterial>& materials,
-                              uint32_t W, uint32_t H, uint32_t S, FramePlan& plan) {
+                              ClusterProvider& clusters, uint32_t W, uint32_t H, uint32_t S, FramePlan& plan) {
     plan.objects.resize(n);
     plan.primBase.resize(n + 1);
     plan.chunks.clear();
@@ -93,13 +125,17 @@ inline std::string plan_frame(const VkrGPUSceneData* scene, const VkrRenderObjec
         o.pos = m.pos; o.attrA = m.attrA; o.attrB = m.attrB;
         o.idx = m.idx + ro.firstIndex;
         o.triCount = ro.indexCount / 3;
+        ClusterRange cr{nullptr, nullptr, nullptr};
+        if (o.triCount && !clusters.get(ro.mesh, ro.firstIndex, ro.indexCount, cr)) return "out of memory building clusters";
+        o.clVerts = cr.verts; o.clTris = cr.tris; o.clInfo = cr.info;
+        o.pad[0] = o.pad[1] = 0;
         o.primBase = (uint32_t)prim;
         o.material = ro.material;
         o.flags = transparent ? 1u : 0u;
         plan.primBase[i] = (uint32_t)prim;
         for (uint32_t t = 0; t < o.triCount; t += GEOM_BLOCK) plan.chunks.push_back(DChunk{(uint32_t)i, t});
         prim += o.triCount;
-        if (prim >= 0xFFFFFFF0ull) return "too many primitives in one frame";
+        if (prim >= 0xFFFFFFF0ull || plan.chunks.size() >= 0xFFFFFFull) return "too many primitives in one frame";
         for (int l = 0; l < plan.shadowLayers; ++l)
             mat_mul(scene->lightViewproj[l], ro.transform, &plan.shadowMvp[((size_t)l * n + i) * 16]);
     }
@@ -132,18 +168,30 @@ inline std::string plan_frame(const VkrGPUSceneData* scene, const VkrRenderObjec
     sc.enableShadows = scene->sunlightColor[3] > 0.5f ? 1 : 0;
     sc.nobj = (uint32_t)n;
     sc.halfW = (float)W * 0.5f; sc.halfH = (float)H * 0.5f;
+    sc.invHalfW = 1.0f / sc.halfW; sc.invHalfH = 1.0f / sc.halfH;
+    {
+        const float* P = scene->proj; const float* V = scene->view;
+        for (int j = 0; j < 3; ++j) {
+            double sx = (double)V[4 * j] / ((double)sc.halfW * P[0]), sy = (double)V[4 * j + 1] / ((double)sc.halfH * P[5]);
+            double so = (double)V[4 * j] * ((double)P[8] - 1.0) / P[0] + (double)V[4 * j + 1] * ((double)P[9] - 1.0) / P[5] - (double)V[4 * j + 2];
+            const double sgn = j == 1 ? -1.0 : 1.0;
+            sc.skyX[j] = (float)(sgn * sx); sc.skyY[j] = (float)(sgn * sy); sc.skyO[j] = (float)(sgn * so);
+        }
+    }
 
     RasterTarget& mt = plan.mainTarget;
     mt.vis = nullptr; mt.depthBits = nullptr;
     mt.width = (int32_t)W; mt.height = (int32_t)H;
     mt.sx0 = sc.sx0; mt.sy0 = sc.sy0; mt.sx1 = sc.sx1; mt.sy1 = sc.sy1;
     mt.halfW = sc.halfW; mt.halfH = sc.halfH;
+    mt.halfW256 = sc.halfW * 256.0f; mt.halfH256 = sc.halfH * 256.0f;
     mt.cullFront = 0;                                   // VK_CULL_MODE_BACK_BIT (src/vk_engine_init.cpp:536)
     RasterTarget& st = plan.shadowTarget;
     st = mt;
     st.width = st.height = (int32_t)S;
     st.sx0 = st.sy0 = 0; st.sx1 = st.sy1 = (int32_t)S;
     st.halfW = st.halfH = (float)S * 0.5f;
+    st.halfW256 = st.halfH256 = (float)S * 128.0f;
     st.cullFront = 1;                                   // VK_CULL_MODE_FRONT_BIT (src/vk_engine_init.cpp:441)
     return std::string();
 }

@@ -5,6 +5,7 @@
 #include "../../include/vkr.h"
 
 #if defined(__CUDACC__)
+#include <vector_types.h>
 #define VKR_HD __host__ __device__ __forceinline__
 #define VKR_HDN __host__ __device__ __noinline__
 #else
@@ -13,6 +14,7 @@
 struct alignas(16) float4 { float x, y, z, w; };
 struct alignas(8) float2 { float x, y; };
 struct alignas(4) uchar4 { unsigned char x, y, z, w; };
+struct alignas(8) uint2 { unsigned int x, y; };
 static inline float4 make_float4(float x, float y, float z, float w) { return float4{x, y, z, w}; }
 #endif
 
@@ -53,13 +55,24 @@ struct DObject {
     const float4* attrA;
     const float4* attrB;
     const uint32_t* idx;      // already offset by firstIndex
+    const uint32_t* clVerts;  // cluster data of this draw's index range (see ClusterRange)
+    const uint32_t* clTris;
+    const uint2* clInfo;
     uint32_t triCount;
-    uint32_t primBase;        // submission-order id of this draw's first triangle
+    uint32_t primBase;        // dense submission-order id of this draw's first triangle (readback only)
     uint32_t material;
     uint32_t flags;           // bit0: transparent pass
+    uint32_t pad[2];
 };
 
-struct DChunk { uint32_t obj, firstTri; };   // GEOM_BLOCK triangles of one draw
+// One cluster = GEOM_BLOCK consecutive triangles of one draw.  Cluster k of the frame owns the
+// primitive sequence numbers [k*256, k*256+255]: seq order == submission order.
+struct DChunk { uint32_t obj, firstTri; };
+
+// Built once per (mesh, firstIndex, indexCount) at first use: for every cluster the list of
+// distinct mesh vertices it references and, per triangle, three 10-bit local ids.
+//   clInfo[c] = (offset of the cluster's first entry in clVerts, vertexCount | triCount << 16)
+//   clTris[c*256 + t] = l0 | l1 << 10 | l2 << 20
 
 struct DMaterial {
     float colorFactors[4];
@@ -97,6 +110,7 @@ struct RasterTarget {
     int32_t width, height;
     int32_t sx0, sy0, sx1, sy1;   // scissor [sx0,sx1) x [sy0,sy1)
     float halfW, halfH;
+    float halfW256, halfH256; // 128*W, 128*H: viewport scale fused with the 8-bit sub-pixel snap
     int32_t cullFront;        // 1: cull front faces (shadow), 0: cull back faces (main)
 };
 
@@ -113,12 +127,16 @@ struct ShadeConst {
     int32_t shadowMode, enableShadows;
     uint32_t nobj;
     float halfW, halfH;
+    float invHalfW, invHalfH;
+    // skybox ray through window position (x,y): dir = skyO + x*skyX + y*skyY
+    // (= transpose(mat3(view)) * unproject, y negated: shaders/skybox.vert:10-15)
+    float skyO[3], skyX[3], skyY[3];
 };
 
 struct ShadeBuffers {
     const uint64_t* vis;
     const DObject* objects;
-    const uint32_t* primBase;          // nobj+1 prefix of triangle counts
+    const DChunk* chunks;              // frame cluster table: seq >> 8 -> (draw, first triangle)
     const DMaterial* materials;
     const DTexture* textures;          // VKR_MAX_BINDLESS slots
     const DTexture* cube;              // 6 faces (nullptr when no cubemap)

@@ -21,13 +21,23 @@ VKR_HD f3 operator*(f3 a, f3 b) { return {a.x * b.x, a.y * b.y, a.z * b.z}; }
 VKR_HD f3 operator*(f3 a, float s) { return {a.x * s, a.y * s, a.z * s}; }
 VKR_HD f3 operator*(float s, f3 a) { return {a.x * s, a.y * s, a.z * s}; }
 VKR_HD float dot3(f3 a, f3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
-VKR_HD f3 norm3(f3 a) { float inv = 1.0f / sqrtf(dot3(a, a)); return a * inv; }
+VKR_HD f3 norm3(f3 a);
 VKR_HD float clamp01(float x) { return fminf(fmaxf(x, 0.0f), 1.0f); }
 
 #if defined(__CUDA_ARCH__)
 #define VKR_LDG(p) __ldg(p)
+VKR_HD float fdiv(float a, float b) { return __fdividef(a, b); }
+VKR_HD float frcp(float a) { return __frcp_rn(a); }
+VKR_HD float frsqrt(float a) { return rsqrtf(a); }
+VKR_HD float fpow(float x, float e) { return __powf(x, e); }
+VKR_HD float flog2(float x) { return __log2f(x); }
 #else
 #define VKR_LDG(p) (*(p))
+VKR_HD float fdiv(float a, float b) { return a / b; }
+VKR_HD float frcp(float a) { return 1.0f / a; }
+VKR_HD float frsqrt(float a) { return 1.0f / sqrtf(a); }
+VKR_HD float fpow(float x, float e) { return powf(x, e); }
+VKR_HD float flog2(float x) { return log2f(x); }
 #endif
 
 VKR_HD uint16_t f2h_bits(float f) {
@@ -70,10 +80,12 @@ VKR_HD uint32_t unorm8(float x) {
     return (uint32_t)floorf(x * 255.0f + 0.5f);
 }
 
+VKR_HD f3 norm3(f3 a) { return a * frsqrt(dot3(a, a)); }
+
 // ---- texture units in software ------------------------------------------------------
 VKR_HD float4 fetch_texel(const DTexture& t, const float* __restrict__ lut, int level, int x, int y, int w) {
     uchar4 p = VKR_LDG(t.data + t.mipOffset[level] + (size_t)y * w + x);
-    if (t.flags & 1u) return make_float4(VKR_LDG(lut + p.x), VKR_LDG(lut + p.y), VKR_LDG(lut + p.z), p.w * (1.0f / 255.0f));
+    if (t.flags & 1u) return make_float4(lut[p.x], lut[p.y], lut[p.z], p.w * (1.0f / 255.0f));   // lut: shared memory on the device
     return make_float4(p.x * (1.0f / 255.0f), p.y * (1.0f / 255.0f), p.z * (1.0f / 255.0f), p.w * (1.0f / 255.0f));
 }
 VKR_HD int wrap_repeat(int i, int n) { int r = i % n; return r < 0 ? r + n : r; }
@@ -100,7 +112,7 @@ VKR_HD float4 sample_level(const DTexture& t, const float* lut, int level, float
 }
 
 VKR_HD float lod_from_rho(float rho, int levels) {
-    float lambda = rho > 0.0f ? log2f(rho) : -126.0f;
+    float lambda = rho > 0.0f ? flog2(rho) : -126.0f;
     return fminf(fmaxf(lambda, 0.0f), (float)(levels - 1));
 }
 
@@ -177,6 +189,41 @@ VKR_HD float shadow_pcss(const float* sm, int S, float su, float sv, float sz) {
     return sum / 16.0f;
 }
 
+// PCF (shaders/mesh_pbr.frag:48-59): nine bilinear taps one texel apart share a 4x4 texel block and
+// the same fractional weights, so fetch 16 texels once and filter separably (12 + 9 lerps).
+VKR_HD float pcf3x3(const float* __restrict__ sm, int S, float su, float sv, float sz) {
+    const float fu = su * (float)S - 0.5f, fv = sv * (float)S - 0.5f;
+    float iu = floorf(fu), iv = floorf(fv);
+    const float a = fu - iu, b = fv - iv;
+    iu = fminf(fmaxf(iu, -4.0f), (float)S + 3.0f);
+    iv = fminf(fmaxf(iv, -4.0f), (float)S + 3.0f);
+    const int x0 = (int)iu - 1, y0 = (int)iv - 1;
+    float h[4][3];
+    const bool interior = x0 >= 0 && y0 >= 0 && x0 + 3 < S && y0 + 3 < S;
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+        float t0, t1, t2, t3;
+        if (interior) {
+            const float* row = sm + (size_t)(y0 + r) * S + x0;
+            t0 = VKR_LDG(row); t1 = VKR_LDG(row + 1); t2 = VKR_LDG(row + 2); t3 = VKR_LDG(row + 3);
+        } else {
+            t0 = shadow_fetch(sm, S, x0, y0 + r); t1 = shadow_fetch(sm, S, x0 + 1, y0 + r);
+            t2 = shadow_fetch(sm, S, x0 + 2, y0 + r); t3 = shadow_fetch(sm, S, x0 + 3, y0 + r);
+        }
+        h[r][0] = t0 + a * (t1 - t0); h[r][1] = t1 + a * (t2 - t1); h[r][2] = t2 + a * (t3 - t2);
+    }
+    const float ref = sz - VKR_SHADOW_BIAS;
+    float shadow = 0.0f;
+#pragma unroll
+    for (int r = 0; r < 3; ++r)
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            const float d = h[r][c] + b * (h[r + 1][c] - h[r][c]);
+            shadow += (ref > d) ? 1.0f : 0.0f;
+        }
+    return shadow * (1.0f / 9.0f);
+}
+
 VKR_HD float calc_shadow(const ShadeConst& sc, const ShadeBuffers& sb, f3 pw, float viewZ) {
     if (!sc.enableShadows) return 0.0f;
     int layer = 0;
@@ -197,15 +244,7 @@ VKR_HD float calc_shadow(const ShadeConst& sc, const ShadeBuffers& sb, f3 pw, fl
         float d = texture_shadow(sm, S, su, sv);
         return (d + VKR_SHADOW_BIAS < sz) ? 1.0f : 0.0f;
     }
-    if (sc.shadowMode == 1) {
-        float texSize = 1.0f / (float)S, shadow = 0.0f;
-        for (int i = -1; i <= 1; ++i)
-            for (int j = -1; j <= 1; ++j) {
-                float pd = texture_shadow(sm, S, su + (float)i * texSize, sv + (float)j * texSize);
-                shadow += (sz - VKR_SHADOW_BIAS > pd) ? 1.0f : 0.0f;
-            }
-        return shadow / 9.0f;
-    }
+    if (sc.shadowMode == 1) return pcf3x3(sm, S, su, sv, sz);
     return shadow_pcss(sm, S, su, sv, sz);
 }
 
@@ -215,11 +254,11 @@ VKR_HD float distribution_ggx(f3 N, f3 H, float roughness) {
     float a = roughness * roughness, a2 = a * a;
     float NdotH = fmaxf(dot3(N, H), 0.0f);
     float denom = NdotH * NdotH * (a2 - 1.0f) + 1.0f;
-    return a2 / (VKR_PI * denom * denom);
+    return fdiv(a2, VKR_PI * denom * denom);
 }
 VKR_HD float geometry_schlick_ggx(float NdotV, float roughness) {
     float r = roughness + 1.0f, k = r * r / 8.0f;
-    return NdotV / (NdotV * (1.0f - k) + k);
+    return fdiv(NdotV, NdotV * (1.0f - k) + k);
 }
 VKR_HD float pow5(float x) { float x2 = x * x; return x2 * x2 * x; }
 
@@ -257,7 +296,7 @@ VKR_HD bool shade_fragment(const ShadeConst& sc, const ShadeBuffers& sb, const D
     f3 F = F0 + (f3{1.0f, 1.0f, 1.0f} - F0) * p5;
     f3 kD = (f3{1.0f, 1.0f, 1.0f} - F) * (1.0f - metallic);
     float denominator = 4.0f * NdotV * NdotL + 0.0001f;
-    f3 specular = (NDF * G * F) * (1.0f / denominator);
+    f3 specular = (NDF * G * F) * frcp(denominator);
     f3 Lo = (kD * base * (1.0f / VKR_PI) + specular) * NdotL * sun;
     out = amb * base + Lo * (1.0f - shadow);
     return true;
@@ -274,8 +313,9 @@ VKR_HD void cube_project(f3 r, int face, float& s, float& t) {
         case 4: sc = r.x; tc = -r.y; ma = fabsf(r.z); break;
         default: sc = -r.x; tc = -r.y; ma = fabsf(r.z); break;
     }
-    s = 0.5f * (sc / ma + 1.0f);
-    t = 0.5f * (tc / ma + 1.0f);
+    const float rma = frcp(ma);
+    s = 0.5f * (sc * rma + 1.0f);
+    t = 0.5f * (tc * rma + 1.0f);
 }
 VKR_HD int cube_select(f3 r) {
     float ax = fabsf(r.x), ay = fabsf(r.y), az = fabsf(r.z);
@@ -322,14 +362,8 @@ VKR_HD float4 texture_cube(const ShadeBuffers& sb, f3 r, f3 rdx, f3 rdy) {
                        c0.w * (1.0f - f) + c1.w * f);
 }
 VKR_HD f3 sky_dir(const ShadeConst& sc, float sx, float sy) {
-    const float* P = sc.scene.proj;
-    const float* Vw = sc.scene.view;
-    float nx = (sx - sc.halfW) / sc.halfW, ny = (sy - sc.halfH) / sc.halfH;
-    f3 dv = {(nx + P[8]) / P[0], (ny + P[9]) / P[5], -1.0f};
-    f3 p = {Vw[0] * dv.x + Vw[1] * dv.y + Vw[2] * dv.z, Vw[4] * dv.x + Vw[5] * dv.y + Vw[6] * dv.z,
-            Vw[8] * dv.x + Vw[9] * dv.y + Vw[10] * dv.z};
-    p.y = -p.y;
-    return p;
+    return {sc.skyO[0] + sx * sc.skyX[0] + sy * sc.skyY[0], sc.skyO[1] + sx * sc.skyX[1] + sy * sc.skyY[1],
+            sc.skyO[2] + sx * sc.skyX[2] + sy * sc.skyY[2]};
 }
 
 // ---- perspective-correct barycentrics of the original triangle (2-D homogeneous) --------
@@ -342,7 +376,7 @@ VKR_HD void bary_at(const float4 c[3], float nx, float ny, float b[3]) {
     float e2 = q0x * q1y - q1x * q0y;
     float s = e0 + e1 + e2;
     if (s == 0.0f) { b[0] = 1.0f; b[1] = 0.0f; b[2] = 0.0f; return; }
-    float inv = 1.0f / s;
+    float inv = frcp(s);
     b[0] = e0 * inv; b[1] = e1 * inv; b[2] = e2 * inv;
 }
 
@@ -354,21 +388,17 @@ VKR_HD float4 xform(const float* m, float4 p) {
 // Rebuild the fragment of primitive `seq` at pixel (px,py) from the SoA vertex streams.
 VKR_HD void fetch_fragment(const ShadeConst& sc, const ShadeBuffers& sb, uint32_t seq, int px, int py,
                            Fragment& fr, uint32_t& material) {
-    // draw lookup: last primBase <= seq
-    uint32_t lo = 0, hi = sc.nobj;
-    while (hi - lo > 1) {
-        uint32_t mid = (lo + hi) >> 1;
-        if (VKR_LDG(sb.primBase + mid) <= seq) lo = mid; else hi = mid;
-    }
-    const DObject& o = sb.objects[lo];
-    const uint32_t tri = seq - o.primBase;
+    // cluster table: seq >> 8 -> (draw, first triangle of the cluster)
+    const uint2 ch = VKR_LDG(reinterpret_cast<const uint2*>(sb.chunks) + (seq >> 8));   // (obj, firstTri)
+    const DObject& o = sb.objects[ch.x];
+    const uint32_t tri = ch.y + (seq & 255u);
     material = o.material;
     const uint32_t i0 = VKR_LDG(o.idx + 3 * tri), i1 = VKR_LDG(o.idx + 3 * tri + 1), i2 = VKR_LDG(o.idx + 3 * tri + 2);
     const float4 p0 = VKR_LDG(o.pos + i0), p1 = VKR_LDG(o.pos + i1), p2 = VKR_LDG(o.pos + i2);
     float4 c[3] = {xform(o.mvp, p0), xform(o.mvp, p1), xform(o.mvp, p2)};
     const float cx = (float)px + 0.5f, cy = (float)py + 0.5f;
     const float ox = (px & 1) ? -1.0f : 1.0f, oy = (py & 1) ? -1.0f : 1.0f;
-    const float ihw = 1.0f / sc.halfW, ihh = 1.0f / sc.halfH;
+    const float ihw = sc.invHalfW, ihh = sc.invHalfH;
     float b[3], bx[3], by[3];
     bary_at(c, (cx - sc.halfW) * ihw, (cy - sc.halfH) * ihh, b);
     bary_at(c, (cx + ox - sc.halfW) * ihw, (cy - sc.halfH) * ihh, bx);
@@ -395,9 +425,9 @@ VKR_HD void fetch_fragment(const ShadeConst& sc, const ShadeBuffers& sb, uint32_
 }
 
 VKR_HD f3 tonemap_reinhard(f3 c) {      // shaders/tonemap.comp:13-19
-    f3 m = {c.x / (c.x + 1.0f), c.y / (c.y + 1.0f), c.z / (c.z + 1.0f)};
+    f3 m = {fdiv(c.x, c.x + 1.0f), fdiv(c.y, c.y + 1.0f), fdiv(c.z, c.z + 1.0f)};
     const float e = 1.0f / 2.2f;
-    return {powf(m.x, e), powf(m.y, e), powf(m.z, e)};
+    return {fpow(m.x, e), fpow(m.y, e), fpow(m.z, e)};
 }
 
 // Resolve one pixel: visibility key -> draw-image texel (RGBA16F) -> presented texel (RGBA8).
@@ -421,7 +451,10 @@ VKR_HD void shade_pixel(const ShadeConst& sc, const ShadeBuffers& sb, int px, in
         if (sc.enableSkybox && sb.cube != nullptr && inScissor && (uint32_t)(key >> 32) >= DEPTH_ONE_BITS) {
             const float cx = (float)px + 0.5f, cy = (float)py + 0.5f;
             const float ox = (px & 1) ? -1.0f : 1.0f, oy = (py & 1) ? -1.0f : 1.0f;
-            float4 c = texture_cube(sb, sky_dir(sc, cx, cy), sky_dir(sc, cx + ox, cy), sky_dir(sc, cx, cy + oy));
+            const f3 d0 = sky_dir(sc, cx, cy);
+            const f3 dx = {d0.x + ox * sc.skyX[0], d0.y + ox * sc.skyX[1], d0.z + ox * sc.skyX[2]};
+            const f3 dy = {d0.x + oy * sc.skyY[0], d0.y + oy * sc.skyY[1], d0.z + oy * sc.skyY[2]};
+            float4 c = texture_cube(sb, d0, dx, dy);
             r = c.x; g = c.y; b = c.z; a = c.w;
         } else if (sc.enableBackground) {                   // gradient_color.comp:27-29
             float blend = (float)py / (float)sc.height;
