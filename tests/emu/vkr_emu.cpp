@@ -52,6 +52,7 @@ struct EmuDevice {
     std::vector<LargeTri> ltris; std::vector<LargeItem> litems; uint32_t counters[4];
     float lut[256];
     FramePlan plan;
+    std::vector<DChunk> chunks;
     VkrEngineStats stats{};
     std::string err;
 };
@@ -199,16 +200,14 @@ static void run_pass(EmuDevice* d, const FramePlan& plan, RasterTarget rt, const
     d->counters[0] = d->counters[1] = d->counters[2] = 0;
     std::vector<CachedVtx> svtx(3 * GEOM_BLOCK);
     for (unsigned c = 0; c < nChunks; ++c) {                 // geometry_kernel: one CTA per cluster
-        const DChunk ch = plan.chunks[c];
-        const DObject& o = plan.objects[ch.obj];
+        const DChunk ch = d->chunks[c];
         const float* mvp = mvps + (size_t)ch.obj * stride;
-        const uint32_t cluster = ch.firstTri / GEOM_BLOCK;
-        const uint2 info = o.clInfo[cluster];
-        const uint32_t nVerts = info.y & 0xFFFFu, nTris = info.y >> 16;
-        const uint32_t* clVerts = o.clVerts + info.x;
+        const uint32_t nVerts = ch.counts & 0xFFFFu, nTris = ch.counts >> 16;
+        const uint32_t* clVerts = ch.clVerts;
+        struct { const float4* pos; } o{ch.pos};
         for (uint32_t v = 0; v < nVerts; ++v) svtx[v] = cluster_vertex(mvp, o.pos[clVerts[v]], rt);      // phase 1
         for (uint32_t t = 0; t < nTris; ++t) {                                                           // phase 2
-            const uint32_t packed = o.clTris[(size_t)cluster * GEOM_BLOCK + t];
+            const uint32_t packed = ch.clTris[t];
             const uint32_t l0 = packed & 1023u, l1 = (packed >> 10) & 1023u, l2 = packed >> 20;
             const uint32_t seq = c * GEOM_BLOCK + t;
             if (SHADOW) { DepthSink s{rt.depthBits, rt.width}; cluster_triangle(svtx[l0], svtx[l1], svtx[l2], mvp, o.pos, clVerts[l0], clVerts[l1], clVerts[l2], 0u, rt, q, s); }
@@ -231,7 +230,11 @@ int emu_draw(EmuDevice* d, const VkrGPUSceneData* scene, const VkrRenderObject* 
     FramePlan& plan = d->plan;
     std::string why = plan_frame(scene, objs, n, fp, d->meshes, d->materials, d->clusters, d->W, d->H, d->S, plan);
     if (!why.empty()) { d->err = why; return VKR_ERROR_INVALID_ARGUMENT; }
-    const unsigned nChunks = (unsigned)plan.chunks.size();
+    const unsigned nChunks = plan.clusterBase[n];
+    d->chunks.resize(nChunks);
+    for (size_t o = 0; o < n; ++o)                            // expand_chunks_kernel
+        for (uint32_t c = plan.clusterBase[o]; c < plan.clusterBase[o + 1]; ++c)
+            d->chunks[c] = make_chunk(plan.objects[o], (uint32_t)o, c - plan.clusterBase[o]);
     for (int layer = 0; layer < plan.shadowLayers; ++layer) {
         RasterTarget rt = plan.shadowTarget;
         rt.depthBits = d->shadowBits.data() + (size_t)layer * d->S * d->S;
@@ -241,12 +244,11 @@ int emu_draw(EmuDevice* d, const VkrGPUSceneData* scene, const VkrRenderObject* 
     RasterTarget rt = plan.mainTarget;
     rt.vis = d->vis.data();
     std::fill(d->vis.begin(), d->vis.end(), VIS_CLEAR);
-    unsigned opaqueChunks = 0;
-    while (opaqueChunks < nChunks && plan.chunks[opaqueChunks].obj < plan.opaqueCount) ++opaqueChunks;
+    const unsigned opaqueChunks = plan.opaqueClusters;
     run_pass<false>(d, plan, rt, (const float*)plan.objects.data(), sizeof(DObject) / 4, opaqueChunks);
     if (d->counters[2]) { d->err = "queue overflow"; return VKR_ERROR_CAPACITY; }
     ShadeBuffers sb{};
-    sb.vis = d->vis.data(); sb.objects = plan.objects.data(); sb.chunks = plan.chunks.data();
+    sb.vis = d->vis.data(); sb.objects = plan.objects.data(); sb.chunks = d->chunks.data();
     sb.materials = d->materials.data(); sb.textures = d->tex.data(); sb.cube = d->haveCube ? d->cube : nullptr;
     sb.shadow = reinterpret_cast<const float*>(d->shadowBits.data());
     sb.hdr = d->hdr.data(); sb.rgba8 = d->rgba8.data(); sb.srgbLut = d->lut;
@@ -267,7 +269,7 @@ int emu_readback(EmuDevice* d, int what, void* dst, size_t bytes) {
                 uint32_t lo = (uint32_t)d->vis[i];
                 if (lo == VIS_EMPTY_LO) { ((uint32_t*)dst)[i] = 0xFFFFFFFFu; continue; }
                 uint32_t seq = 0xFFFFFFFEu - lo;
-                const DChunk ch = d->plan.chunks[seq >> 8];
+                const DChunk ch = d->chunks[seq >> 8];
                 ((uint32_t*)dst)[i] = d->plan.objects[ch.obj].primBase + ch.firstTri + (seq & 255u);
             }
             return 0;

@@ -102,6 +102,15 @@ __global__ void mip_blit_kernel(const uchar4* __restrict__ src, int sw, int sh, 
     dst[(size_t)y * dw + x] = o;
 }
 
+// ---- per-frame cluster table, written on the device from the per-draw prefix (one CTA per draw)
+__global__ void expand_chunks_kernel(const DObject* __restrict__ objects, const uint32_t* __restrict__ clusterBase,
+                                     DChunk* __restrict__ chunks) {
+    const uint32_t obj = blockIdx.x;
+    const uint32_t base = clusterBase[obj], n = clusterBase[obj + 1] - base;
+    const DObject& o = objects[obj];
+    for (uint32_t c = threadIdx.x; c < n; c += blockDim.x) chunks[base + c] = make_chunk(o, obj, c);
+}
+
 // ---- geometry: one CTA per cluster (<= 256 triangles of one draw).
 // Phase 1 transforms each DISTINCT vertex of the cluster once (128-bit position loads) into shared
 // memory as snapped window coordinates; phase 2 runs one thread per triangle on those.
@@ -111,14 +120,16 @@ __global__ void __launch_bounds__(GEOM_BLOCK) geometry_kernel(const DObject* __r
                                                               const __grid_constant__ RasterTarget rt, const __grid_constant__ Queues q) {
     __shared__ float s_mvp[16];
     __shared__ uint4 s_vtx[3 * GEOM_BLOCK];
-    const DChunk ch = chunks[blockIdx.x];
-    const DObject& o = objects[ch.obj];
-    if (threadIdx.x < 16) s_mvp[threadIdx.x] = mvps[(size_t)ch.obj * mvpStride + threadIdx.x];
-    const uint32_t cluster = ch.firstTri / GEOM_BLOCK;
-    const uint2 info = __ldg(o.clInfo + cluster);
-    const uint32_t nVerts = info.y & 0xFFFFu, nTris = info.y >> 16;
-    const uint32_t* __restrict__ clVerts = o.clVerts + info.x;
-    const float4* __restrict__ pos = o.pos;
+    // the 48-byte cluster record is everything this CTA needs: one level of indirection
+    const uint4* chp = reinterpret_cast<const uint4*>(chunks + blockIdx.x);
+    const uint4 c0 = __ldg(chp), c1 = __ldg(chp + 1), c2 = __ldg(chp + 2);
+    const float4* __restrict__ pos = reinterpret_cast<const float4*>(((uint64_t)c0.y << 32) | c0.x);
+    const uint32_t* __restrict__ clVerts = reinterpret_cast<const uint32_t*>(((uint64_t)c0.w << 32) | c0.z);
+    const uint32_t* __restrict__ clTris = reinterpret_cast<const uint32_t*>(((uint64_t)c1.y << 32) | c1.x);
+    const uint32_t obj = c1.z, counts = c2.x;
+    (void)objects;
+    if (threadIdx.x < 16) s_mvp[threadIdx.x] = __ldg(mvps + (size_t)obj * mvpStride + threadIdx.x);
+    const uint32_t nVerts = counts & 0xFFFFu, nTris = counts >> 16;
     __syncthreads();
     for (uint32_t v = threadIdx.x; v < nVerts; v += GEOM_BLOCK) {
         const CachedVtx cv = cluster_vertex(s_mvp, __ldg(pos + __ldg(clVerts + v)), rt);
@@ -126,7 +137,7 @@ __global__ void __launch_bounds__(GEOM_BLOCK) geometry_kernel(const DObject* __r
     }
     __syncthreads();
     if (threadIdx.x >= nTris) return;
-    const uint32_t packed = __ldg(o.clTris + (size_t)cluster * GEOM_BLOCK + threadIdx.x);
+    const uint32_t packed = __ldg(clTris + threadIdx.x);
     const uint32_t l0 = packed & 1023u, l1 = (packed >> 10) & 1023u, l2 = packed >> 20;
     const uint4 a = s_vtx[l0], b = s_vtx[l1], c = s_vtx[l2];
     const CachedVtx va{(int32_t)a.x, (int32_t)a.y, a.z, a.w}, vb{(int32_t)b.x, (int32_t)b.y, b.z, b.w}, vc{(int32_t)c.x, (int32_t)c.y, c.z, c.w};
@@ -232,6 +243,8 @@ struct VkrDevice {
     std::map<RangeKey, ClusterRange> ranges;   // cluster data per (mesh, firstIndex, indexCount), built at first use
     std::vector<std::vector<uint32_t>> meshIndexHost;   // host copy of each mesh's indices (cluster building)
     size_t uploadBytes = 0;
+
+    DChunk* chunkBuf = nullptr; size_t chunkCap = 0;   // per-frame cluster table (device-written)
 
     Queues q{};
     uint32_t* countersHost = nullptr;   // pinned mirror of q.counters after the last frame
@@ -557,29 +570,33 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
     const int slotIdx = (int)(dev->frameIndex % VKR_FRAME_OVERLAP);
     FrameSlot& slot = dev->slots[slotIdx];
     dev->uploadBytes = 0;
-    const size_t szObj = sizeof(DObject) * n, szPrim = 4 * (n + 1), szChunk = sizeof(DChunk) * plan.chunks.size();
+    const size_t szObj = sizeof(DObject) * n, szBase = 4 * (n + 1);
+    const unsigned nChunks = plan.clusterBase[n];
     const size_t szShadow = plan.shadowMvp.size() * 4;
     auto align16 = [](size_t v) { return (v + 15) & ~(size_t)15; };
-    const size_t offObj = 0, offPrim = align16(offObj + szObj), offChunk = align16(offPrim + szPrim), offShadow = align16(offChunk + szChunk);
+    const size_t offObj = 0, offBase = align16(offObj + szObj), offShadow = align16(offBase + szBase);
     const size_t total = align16(offShadow + szShadow) + 16;
+    if (dev->chunkCap < nChunks) {
+        dev->chunkCap = std::max<size_t>((size_t)nChunks * 3 / 2, 1024);
+        ALLOC(dev->chunkBuf, dev->chunkCap * sizeof(DChunk));     // the previous table is freed at destroy
+    }
     if (dev->frameIndex >= VKR_FRAME_OVERLAP) CK(cudaEventSynchronize(slot.uploaded));   // pinned buffer reuse
     int rc = ensure_slot(dev, slot, total);
     if (rc) return rc;
     char* hp = (char*)slot.pinned;
     if (n) std::memcpy(hp + offObj, plan.objects.data(), szObj);
-    std::memcpy(hp + offPrim, plan.primBase.data(), szPrim);
-    if (szChunk) std::memcpy(hp + offChunk, plan.chunks.data(), szChunk);
+    std::memcpy(hp + offBase, plan.clusterBase.data(), szBase);
     if (szShadow) std::memcpy(hp + offShadow, plan.shadowMvp.data(), szShadow);
     CK(cudaMemcpyAsync(slot.devbuf, slot.pinned, total, cudaMemcpyHostToDevice, st));
     dev->uploadBytes = total;
     CK(cudaEventRecord(slot.uploaded, st));
     char* dp = (char*)slot.devbuf;
     const DObject* dObjects = (const DObject*)(dp + offObj);
-    const DChunk* dChunks = (const DChunk*)(dp + offChunk);
+    const DChunk* dChunks = dev->chunkBuf;
     const float* dShadowMvp = (const float*)(dp + offShadow);
+    if (n) { expand_chunks_kernel<<<(unsigned)n, 64, 0, st>>>(dObjects, (const uint32_t*)(dp + offBase), dev->chunkBuf); dev->launches += 1; }
     if (timing) CK(cudaEventRecord(dev->tev[1], st));
 
-    const unsigned nChunks = (unsigned)plan.chunks.size();
     const unsigned largeGrid = (unsigned)dev->smCount * 4;
 
     // ---- draw_shadow (src/vk_engine_run.cpp:334-382)
@@ -608,8 +625,7 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
         dev->launches += 1;
         if (timing) CK(cudaEventRecord(dev->tev[3], st));
         // only the opaque prefix writes depth; transparent draws are blended in a later pass
-        unsigned opaqueChunks = 0;
-        while (opaqueChunks < nChunks && plan.chunks[opaqueChunks].obj < plan.opaqueCount) ++opaqueChunks;
+        const unsigned opaqueChunks = plan.opaqueClusters;
         if (opaqueChunks) {
             geometry_kernel<false><<<opaqueChunks, GEOM_BLOCK, 0, st>>>(dObjects, dChunks, (const float*)dObjects, (uint32_t)(sizeof(DObject) / 4), rt, dev->q);
             if (timing) CK(cudaEventRecord(dev->tev[4], st));

@@ -87,7 +87,8 @@ struct ClusterProvider {
 struct FramePlan {
     std::vector<DObject> objects;
     std::vector<uint32_t> primBase;     // nobj + 1 (dense ids, for stats / readback)
-    std::vector<DChunk> chunks;
+    std::vector<uint32_t> clusterBase;  // nobj + 1: first frame-cluster index of every draw
+    uint32_t opaqueClusters = 0;        // clusters of the opaque prefix
     std::vector<float> shadowMvp;       // layers * nobj * 16
     int shadowLayers = 0;
     uint32_t totalTris = 0;
@@ -103,7 +104,8 @@ inline std::string plan_frame(const VkrGPUSceneData* scene, const VkrRenderObjec
                               ClusterProvider& clusters, uint32_t W, uint32_t H, uint32_t S, FramePlan& plan) {
     plan.objects.resize(n);
     plan.primBase.resize(n + 1);
-    plan.chunks.clear();
+    plan.clusterBase.resize(n + 1);
+    uint64_t ncl = 0;
     plan.shadowLayers = fp->enableShadows ? (fp->shadowMode < 3 ? 1 : VKR_NUM_CASCADES) : 0;
     plan.shadowMvp.resize((size_t)plan.shadowLayers * n * 16);
     uint64_t prim = 0;
@@ -133,13 +135,16 @@ inline std::string plan_frame(const VkrGPUSceneData* scene, const VkrRenderObjec
         o.material = ro.material;
         o.flags = transparent ? 1u : 0u;
         plan.primBase[i] = (uint32_t)prim;
-        for (uint32_t t = 0; t < o.triCount; t += GEOM_BLOCK) plan.chunks.push_back(DChunk{(uint32_t)i, t});
+        plan.clusterBase[i] = (uint32_t)ncl;
+        ncl += (o.triCount + GEOM_BLOCK - 1) / GEOM_BLOCK;
+        if (!transparent) plan.opaqueClusters = (uint32_t)ncl;
         prim += o.triCount;
-        if (prim >= 0xFFFFFFF0ull || plan.chunks.size() >= 0xFFFFFFull) return "too many primitives in one frame";
+        if (prim >= 0xFFFFFFF0ull || ncl >= 0xFFFFFFull) return "too many primitives in one frame";
         for (int l = 0; l < plan.shadowLayers; ++l)
             mat_mul(scene->lightViewproj[l], ro.transform, &plan.shadowMvp[((size_t)l * n + i) * 16]);
     }
     plan.primBase[n] = (uint32_t)prim;
+    plan.clusterBase[n] = (uint32_t)ncl;
     plan.totalTris = (uint32_t)prim;
 
     ShadeConst& sc = plan.sc;

@@ -67,7 +67,26 @@ struct DObject {
 
 // One cluster = GEOM_BLOCK consecutive triangles of one draw.  Cluster k of the frame owns the
 // primitive sequence numbers [k*256, k*256+255]: seq order == submission order.
-struct DChunk { uint32_t obj, firstTri; };
+// The host uploads only the per-draw cluster prefix; expand_chunks_kernel writes this table on the
+// device with everything the geometry CTA needs in one 48-byte record (no dependent loads).
+struct DChunk {
+    const float4* pos;        // mesh positions
+    const uint32_t* clVerts;  // this cluster's distinct-vertex list
+    const uint32_t* clTris;   // this cluster's packed triangles
+    uint32_t obj, firstTri;
+    uint32_t counts;          // vertexCount | triCount << 16
+    uint32_t pad[3];
+};
+static_assert(sizeof(DChunk) == 48, "DChunk is read as three 16-byte words");
+// Cluster c of draw `obj` (what expand_chunks_kernel writes).
+VKR_HD DChunk make_chunk(const DObject& o, uint32_t obj, uint32_t c) {
+    const uint2 info = o.clInfo[c];
+    DChunk ch;
+    ch.pos = o.pos; ch.clVerts = o.clVerts + info.x; ch.clTris = o.clTris + (size_t)c * GEOM_BLOCK;
+    ch.obj = obj; ch.firstTri = c * GEOM_BLOCK; ch.counts = info.y;
+    ch.pad[0] = ch.pad[1] = ch.pad[2] = 0;
+    return ch;
+}
 
 // Built once per (mesh, firstIndex, indexCount) at first use: for every cluster the list of
 // distinct mesh vertices it references and, per triangle, three 10-bit local ids.
@@ -136,7 +155,7 @@ struct ShadeConst {
 struct ShadeBuffers {
     const uint64_t* vis;
     const DObject* objects;
-    const DChunk* chunks;              // frame cluster table: seq >> 8 -> (draw, first triangle)
+    const DChunk* chunks;              // frame cluster table: seq >> 8 -> cluster record
     const DMaterial* materials;
     const DTexture* textures;          // VKR_MAX_BINDLESS slots
     const DTexture* cube;              // 6 faces (nullptr when no cubemap)

@@ -131,7 +131,7 @@ struct VisSink {           // main pass: 64-bit key into the visibility buffer
         const uint64_t key = ((uint64_t)f2bits(z) << 32) | lo;
         uint64_t* p = vis + (size_t)py * width + px;
 #if defined(__CUDA_ARCH__)
-        if (key < __ldcg((const unsigned long long*)p)) atomicMin((unsigned long long*)p, (unsigned long long)key);
+        atomicMin((unsigned long long*)p, (unsigned long long)key);   // result unused -> RED.MIN.64: fire and forget, no L2 round trip
 #else
         if (key < *p) *p = key;
 #endif
@@ -143,7 +143,7 @@ struct DepthSink {         // shadow pass: float bits, LESS_OR_EQUAL + write == 
         const uint32_t v = f2bits(z);
         uint32_t* p = bits + (size_t)py * width + px;
 #if defined(__CUDA_ARCH__)
-        if (v < __ldcg(p)) atomicMin(p, v);
+        atomicMin(p, v);                                                // RED.MIN.32
 #else
         if (v < *p) *p = v;
 #endif

@@ -389,7 +389,7 @@ VKR_HD float4 xform(const float* m, float4 p) {
 VKR_HD void fetch_fragment(const ShadeConst& sc, const ShadeBuffers& sb, uint32_t seq, int px, int py,
                            Fragment& fr, uint32_t& material) {
     // cluster table: seq >> 8 -> (draw, first triangle of the cluster)
-    const uint2 ch = VKR_LDG(reinterpret_cast<const uint2*>(sb.chunks) + (seq >> 8));   // (obj, firstTri)
+    const uint2 ch = VKR_LDG(reinterpret_cast<const uint2*>(&sb.chunks[seq >> 8].obj));   // (obj, firstTri)
     const DObject& o = sb.objects[ch.x];
     const uint32_t tri = ch.y + (seq & 255u);
     material = o.material;
