@@ -215,7 +215,9 @@ struct FrameSlot {
 
 struct VkrDevice {
     int device = 0;
-    cudaStream_t stream = nullptr, copyStream = nullptr;
+    cudaStream_t stream = nullptr, copyStream = nullptr;   // frame stream; device->host copies
+    cudaStream_t shadowStream = nullptr, upStream = nullptr; // shadow pass runs beside the main pass; host->device uploads
+    cudaEvent_t evFork = nullptr, evShadow = nullptr;
     bool ownStream = false;
     uint32_t W = 0, H = 0, S = 2048, flags = 0;
     int smCount = 148;
@@ -246,7 +248,8 @@ struct VkrDevice {
 
     DChunk* chunkBuf = nullptr; size_t chunkCap = 0;   // per-frame cluster table (device-written)
 
-    Queues q{};
+    Queues q{};                         // large-triangle queue of the main pass
+    Queues qShadow{};                   // ... of the shadow pass (the two passes overlap)
     uint32_t* countersHost = nullptr;   // pinned mirror of q.counters after the last frame
 
     FrameSlot slots[VKR_FRAME_OVERLAP];
@@ -255,8 +258,8 @@ struct VkrDevice {
     const DChunk* lastChunks = nullptr; const DObject* lastObjects = nullptr;
     FramePlan plan;
 
-    cudaEvent_t tev[8] = {nullptr};   // 0 start, 1 uploaded, 2 shadow, 3 cleared, 4 geometry kernel, 5 large kernel, 6 shaded
-    bool tevValid = false;
+    cudaEvent_t tev[9] = {nullptr};   // 0 start, 1 uploaded, 3 cleared, 4 geometry kernel, 5 large kernel, 6 shaded; 7,8 shadow pass (shadow stream)
+    bool tevValid = false, shadowTimed = false;
     float timings[VKR_T_COUNT] = {0};
 
     VkrEngineStats stats{};
@@ -346,6 +349,10 @@ int vkr_create(const VkrConfig* cfg, VkrDevice** out) {
         if (cfg->stream) dev->stream = (cudaStream_t)cfg->stream;
         else { CK(cudaStreamCreateWithFlags(&dev->stream, cudaStreamNonBlocking)); dev->ownStream = true; }
         CK(cudaStreamCreateWithFlags(&dev->copyStream, cudaStreamNonBlocking));
+        CK(cudaStreamCreateWithFlags(&dev->shadowStream, cudaStreamNonBlocking));
+        CK(cudaStreamCreateWithFlags(&dev->upStream, cudaStreamNonBlocking));
+        CK(cudaEventCreateWithFlags(&dev->evFork, cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&dev->evShadow, cudaEventDisableTiming));
         const size_t px = (size_t)dev->W * dev->H;
         ALLOC(dev->vis, px * 8);
         ALLOC(dev->hdr, px * 8);
@@ -361,8 +368,12 @@ int vkr_create(const VkrConfig* cfg, VkrDevice** out) {
         ALLOC(dev->q.tris, sizeof(LargeTri) * dev->q.triCap);
         ALLOC(dev->q.items, sizeof(LargeItem) * dev->q.itemCap);
         ALLOC(dev->q.counters, 16);
-        CK(cudaMallocHost(&dev->countersHost, 16));
-        std::memset(dev->countersHost, 0, 16);
+        dev->qShadow.triCap = 1u << 18; dev->qShadow.itemCap = 1u << 20;
+        ALLOC(dev->qShadow.tris, sizeof(LargeTri) * dev->qShadow.triCap);
+        ALLOC(dev->qShadow.items, sizeof(LargeItem) * dev->qShadow.itemCap);
+        ALLOC(dev->qShadow.counters, 16);
+        CK(cudaMallocHost(&dev->countersHost, 32));
+        std::memset(dev->countersHost, 0, 32);
         for (auto& s : dev->slots) {
             CK(cudaEventCreateWithFlags(&s.uploaded, cudaEventDisableTiming));
             CK(cudaEventCreateWithFlags(&s.rendered, cudaEventDisableTiming));
@@ -406,6 +417,10 @@ void vkr_destroy(VkrDevice* dev) {
     for (auto& e : dev->tev) if (e) cudaEventDestroy(e);
     if (dev->countersHost) cudaFreeHost(dev->countersHost);
     if (dev->copyStream) cudaStreamDestroy(dev->copyStream);
+    if (dev->shadowStream) cudaStreamDestroy(dev->shadowStream);
+    if (dev->upStream) cudaStreamDestroy(dev->upStream);
+    if (dev->evFork) cudaEventDestroy(dev->evFork);
+    if (dev->evShadow) cudaEventDestroy(dev->evShadow);
     if (dev->ownStream && dev->stream) cudaStreamDestroy(dev->stream);
     delete dev;
 }
@@ -587,9 +602,13 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
     if (n) std::memcpy(hp + offObj, plan.objects.data(), szObj);
     std::memcpy(hp + offBase, plan.clusterBase.data(), szBase);
     if (szShadow) std::memcpy(hp + offShadow, plan.shadowMvp.data(), szShadow);
-    CK(cudaMemcpyAsync(slot.devbuf, slot.pinned, total, cudaMemcpyHostToDevice, st));
+    // the upload rides its own stream so it overlaps the previous frame's kernels; the slot's device
+    // buffer is free once the frame that last used it (FRAME_OVERLAP frames ago) has rendered
+    CK(cudaStreamWaitEvent(dev->upStream, slot.rendered, 0));
+    CK(cudaMemcpyAsync(slot.devbuf, slot.pinned, total, cudaMemcpyHostToDevice, dev->upStream));
     dev->uploadBytes = total;
-    CK(cudaEventRecord(slot.uploaded, st));
+    CK(cudaEventRecord(slot.uploaded, dev->upStream));
+    CK(cudaStreamWaitEvent(st, slot.uploaded, 0));
     char* dp = (char*)slot.devbuf;
     const DObject* dObjects = (const DObject*)(dp + offObj);
     const DChunk* dChunks = dev->chunkBuf;
@@ -599,21 +618,30 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
 
     const unsigned largeGrid = (unsigned)dev->smCount * 4;
 
-    // ---- draw_shadow (src/vk_engine_run.cpp:334-382)
-    for (int layer = 0; layer < plan.shadowLayers; ++layer) {
-        RasterTarget rt = plan.shadowTarget;
-        rt.depthBits = dev->shadowBits + (size_t)layer * dev->S * dev->S;
-        const size_t sn = (size_t)dev->S * dev->S;
-        fill_u32_kernel<<<grid_for(sn / 4, 256, 2048), 256, 0, st>>>(rt.depthBits, sn, DEPTH_ONE_BITS);
-        CK(cudaMemsetAsync(dev->q.counters, 0, 16, st));
-        dev->launches += 1;
-        if (nChunks) {
-            geometry_kernel<true><<<nChunks, GEOM_BLOCK, 0, st>>>(dObjects, dChunks, dShadowMvp + (size_t)layer * n * 16, 16u, rt, dev->q);
-            large_raster_kernel<true><<<largeGrid, 256, 0, st>>>(rt, dev->q);
-            dev->launches += 2;
+    // ---- draw_shadow (src/vk_engine_run.cpp:334-382) on the shadow stream, concurrently with the main
+    // pass's rasterisation: both are latency-bound, together they fill the SMs' issue slots
+    cudaStream_t ss = dev->shadowStream;
+    if (plan.shadowLayers) {
+        CK(cudaEventRecord(dev->evFork, st));
+        CK(cudaStreamWaitEvent(ss, dev->evFork, 0));
+        if (timing) CK(cudaEventRecord(dev->tev[7], ss));
+        for (int layer = 0; layer < plan.shadowLayers; ++layer) {
+            RasterTarget rt = plan.shadowTarget;
+            rt.depthBits = dev->shadowBits + (size_t)layer * dev->S * dev->S;
+            const size_t sn = (size_t)dev->S * dev->S;
+            fill_u32_kernel<<<grid_for(sn / 4, 256, 2048), 256, 0, ss>>>(rt.depthBits, sn, DEPTH_ONE_BITS);
+            CK(cudaMemsetAsync(dev->qShadow.counters, 0, 16, ss));
+            dev->launches += 1;
+            if (nChunks) {
+                geometry_kernel<true><<<nChunks, GEOM_BLOCK, 0, ss>>>(dObjects, dChunks, dShadowMvp + (size_t)layer * n * 16, 16u, rt, dev->qShadow);
+                large_raster_kernel<true><<<largeGrid, 256, 0, ss>>>(rt, dev->qShadow);
+                dev->launches += 2;
+            }
+            CK(cudaMemcpyAsync(dev->countersHost + 4, dev->qShadow.counters, 16, cudaMemcpyDeviceToHost, ss));
         }
+        if (timing) CK(cudaEventRecord(dev->tev[8], ss));
+        CK(cudaEventRecord(dev->evShadow, ss));
     }
-    if (timing) CK(cudaEventRecord(dev->tev[2], st));
 
     // ---- draw_geometry, raster half (src/vk_engine_run.cpp:244-311)
     {
@@ -637,6 +665,7 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
     if (timing) CK(cudaEventRecord(dev->tev[5], st));
 
     // ---- shading half of draw_geometry + draw_skybox + draw_background + draw_postprocess + present blit
+    if (plan.shadowLayers) CK(cudaStreamWaitEvent(st, dev->evShadow, 0));   // join: the shader samples the shadow map
     {
         ShadeBuffers sb{};
         sb.vis = dev->vis; sb.objects = dObjects; sb.chunks = dChunks; sb.materials = dev->matDev;
@@ -647,7 +676,7 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
         dim3 grid((sc.sx1 - sc.sx0 + 15) / 16, (sc.sy1 - sc.sy0 + 7) / 8);
         if (grid.x && grid.y) { shade_kernel<<<grid, 128, 0, st>>>(sc, sb); dev->launches += 1; }
     }
-    if (timing) { CK(cudaEventRecord(dev->tev[6], st)); dev->tevValid = true; }
+    if (timing) { CK(cudaEventRecord(dev->tev[6], st)); dev->tevValid = true; dev->shadowTimed = plan.shadowLayers > 0; }
     CK(cudaGetLastError());
     CK(cudaEventRecord(slot.rendered, st));
     dev->lastSlot = slotIdx;
@@ -663,13 +692,14 @@ int vkr_sync(VkrDevice* dev) {
     CK(cudaSetDevice(dev->device));
     CK(cudaStreamSynchronize(dev->stream));
     CK(cudaStreamSynchronize(dev->copyStream));
-    if (dev->countersHost[2]) return dev->fail(VKR_ERROR_CAPACITY, "large-triangle queue overflow");
+    CK(cudaStreamSynchronize(dev->shadowStream));
+    if (dev->countersHost[2] || dev->countersHost[6]) return dev->fail(VKR_ERROR_CAPACITY, "large-triangle queue overflow");
     if (dev->tevValid) {
         auto el = [&](int a, int b) { float ms = 0; cudaEventElapsedTime(&ms, dev->tev[a], dev->tev[b]); return ms; };
         dev->timings[VKR_T_UPLOAD] = el(0, 1);
-        dev->timings[VKR_T_SHADOW] = el(1, 2);
-        dev->timings[VKR_T_GEOMETRY] = el(2, 5);
-        dev->timings[VKR_T_CLEAR] = el(2, 3);
+        dev->timings[VKR_T_SHADOW] = dev->shadowTimed ? el(7, 8) : 0.0f;   // overlaps the geometry pass
+        dev->timings[VKR_T_GEOMETRY] = el(1, 5);
+        dev->timings[VKR_T_CLEAR] = el(1, 3);
         dev->timings[VKR_T_GEOM_KERNEL] = el(3, 4);
         dev->timings[VKR_T_LARGE_KERNEL] = el(4, 5);
         dev->timings[VKR_T_SHADE] = el(5, 6);
