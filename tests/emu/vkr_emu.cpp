@@ -205,6 +205,17 @@ static void run_pass(EmuDevice* d, const FramePlan& plan, RasterTarget rt, const
         const uint32_t nVerts = ch.counts & 0xFFFFu, nTris = ch.counts >> 16;
         const uint32_t* clVerts = ch.clVerts;
         struct { const float4* pos; } o{ch.pos};
+        const AlphaCtx ax{plan.objects.data(), d->chunks.data(), d->materials.data(), d->tex.data()};
+        if (!SHADOW && (ch.pad[0] & 2u)) {                    // geometry_cutout_kernel
+            const DObject& ob = plan.objects[ch.obj];
+            for (uint32_t t = 0; t < nTris; ++t) {
+                const uint32_t packed = ch.clTris[t];
+                VisSink s{rt.vis, rt.width, 0xFFFFFFFEu - (c * GEOM_BLOCK + t)};
+                cutout_triangle(ob, ob.mvp, clVerts[packed & 1023u], clVerts[(packed >> 10) & 1023u], clVerts[packed >> 20],
+                                c * GEOM_BLOCK + t, rt, q, ax, s);
+            }
+            continue;
+        }
         for (uint32_t v = 0; v < nVerts; ++v) svtx[v] = cluster_vertex(mvp, o.pos[clVerts[v]], rt);      // phase 1
         for (uint32_t t = 0; t < nTris; ++t) {                                                           // phase 2
             const uint32_t packed = ch.clTris[t];
@@ -219,7 +230,19 @@ static void run_pass(EmuDevice* d, const FramePlan& plan, RasterTarget rt, const
         const LargeTri lt = q.tris[it.tri];
         for (int lane = 0; lane < 32; ++lane) {
             if (SHADOW) { DepthSink s{rt.depthBits, rt.width}; raster_item(lt, it, s, lane, 32); }
-            else { VisSink s{rt.vis, rt.width, 0xFFFFFFFEu - lt.seq}; raster_item(lt, it, s, lane, 32); }
+            else {
+                VisSink s{rt.vis, rt.width, 0xFFFFFFFEu - lt.seq};
+                const DChunk& ch = d->chunks[lt.seq >> 8];
+                if (ch.pad[0] & 2u) {
+                    const AlphaCtx ax{plan.objects.data(), d->chunks.data(), d->materials.data(), d->tex.data()};
+                    const DObject& ob = plan.objects[ch.obj];
+                    const uint32_t tri = ch.firstTri + (lt.seq & 255u);
+                    AlphaTri at;
+                    make_alpha_tri(ob, ob.mvp, ob.idx[3 * tri], ob.idx[3 * tri + 1], ob.idx[3 * tri + 2], ax, rt, at);
+                    CutoutSink<VisSink> cs{s, &at};
+                    raster_item(lt, it, cs, lane, 32);
+                } else raster_item(lt, it, s, lane, 32);
+            }
         }
     }
 }
@@ -228,7 +251,7 @@ extern "C" {
 
 int emu_draw(EmuDevice* d, const VkrGPUSceneData* scene, const VkrRenderObject* objs, size_t n, const VkrFrameParams* fp) {
     FramePlan& plan = d->plan;
-    std::string why = plan_frame(scene, objs, n, fp, d->meshes, d->materials, d->clusters, d->W, d->H, d->S, plan);
+    std::string why = plan_frame(scene, objs, n, fp, d->meshes, d->materials, d->tex, d->clusters, d->W, d->H, d->S, plan);
     if (!why.empty()) { d->err = why; return VKR_ERROR_INVALID_ARGUMENT; }
     const unsigned nChunks = plan.clusterBase[n];
     d->chunks.resize(nChunks);

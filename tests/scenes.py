@@ -198,7 +198,45 @@ def big_triangles(r):
     return sd0, objs, fp
 
 
+def cutout(r):
+    """Alpha-tested geometry (`discard` when albedo alpha < 0.5): small triangles (tessellated drape), a
+    screen-sized quad (large-triangle path), a drape crossing the near plane, all in front of opaque
+    geometry that must show through the holes and receive the correct depth."""
+    W, H = r.width, r.height
+    tex = r.create_image(mg.cutout_texture(128, 4, seed=2), capi.FORMAT_SRGB, True)
+    r.update_bindless_texture(3, tex, capi.SAMPLER_LINEAR)
+    tex2 = r.create_image(mg.cutout_texture(32, 2, seed=5), capi.FORMAT_UNORM, False)     # single level, NEAREST
+    r.update_bindless_texture(4, tex2, capi.SAMPLER_NEAREST)
+    back = r.create_image(mg.checker_texture(64, 8, seed=1), capi.FORMAT_SRGB, True)
+    r.update_bindless_texture(2, back, capi.SAMPLER_LINEAR)
+    m_cut = r.build_material((1, 1, 1, 1), 0.0, 0.9, albedo_id=3)
+    m_cut2 = r.build_material((1, 0.8, 0.8, 1), 0.2, 0.7, albedo_id=4)
+    m_back = r.build_material((1, 1, 1, 1), 0.0, 1.0, albedo_id=2)
+    m_sph = r.build_material((0.9, 0.5, 0.2, 1), 0.0, 0.5)
+    pv, pi = mg.plane(24, 24, 6.0, 0.0, uv_scale=3)          # tessellated: small triangles
+    qv, qi = mg.plane(1, 1, 14.0, 0.0, uv_scale=4)           # two big triangles
+    gv, gi = mg.plane(4, 4, 40.0, -2.0, uv_scale=10)
+    sv, si = mg.uv_sphere(16, 16, 1.0)
+    mp, mq, mgr, ms = r.upload_mesh(pi, pv), r.upload_mesh(qi, qv), r.upload_mesh(gi, gv), r.upload_mesh(si, sv)
+    rot = np.array([[1, 0, 0, 0], [0, 0, -1, 0], [0, 1, 0, 0], [0, 0, 0, 1]], np.float32)     # +Y normal -> +Z (faces the camera)
+    objs = [
+        mg.render_object(mgr, m_back, np.eye(4), len(gi)),
+        mg.render_object(ms, m_sph, mg.translate(-1.5, 0.0, -1.0), len(si)),
+        mg.render_object(ms, m_sph, mg.translate(2.0, 0.5, -3.0), len(si)),
+        mg.render_object(mq, m_cut, mg.translate(0, 1.0, -6.0) @ rot, len(qi)),            # big, far
+        mg.render_object(mp, m_cut, mg.translate(-1.0, 0.5, 1.5) @ rot, len(pi)),          # tessellated, near
+        mg.render_object(mp, m_cut2, mg.translate(2.5, 0.0, 2.0) @ rot, len(pi)),
+        mg.render_object(mq, m_cut2, mg.translate(0.0, 0.0, 7.95) @ rot, len(qi)),         # crosses the near plane
+    ]
+    view = mg.camera_view((0, 1.0, 8.0), pitch=-0.05)
+    proj = mg.camera_projection(W / H)
+    sd = capi.make_scene_data(view, proj, _lights(1), shadow_mode=1, enable_shadows=True)
+    fp = capi.default_frame_params(enableShadows=1, shadowMode=1, enablePostprocess=1)
+    return sd, np.array(objs), fp
+
+
 SCENES = {
+    "cutout": cutout,
     "basic_hard": lambda r: basic(r, 0),
     "basic_pcf": lambda r: basic(r, 1),
     "basic_pcss": lambda r: basic(r, 2),

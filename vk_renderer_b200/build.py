@@ -58,7 +58,7 @@ def build_engine(force=False):
     if not force and _newer(target, deps):
         return target
     srcs = [s for s in deps if s.endswith(".cpp")]
-    cmd = ["g++", "-O2", "-std=c++17", "-ffp-contract=off", "-fPIC", "-shared", "-Wall", "-I", os.path.join(ROOT, "include"),
+    cmd = ["g++", "-O2", "-std=c++20", "-ffp-contract=off", "-fPIC", "-shared", "-Wall", "-I", os.path.join(ROOT, "include"),
            "-o", target, *srcs, "-L", PKG, "-lvkr", "-Wl,-rpath,$ORIGIN", "-lpthread"]
     subprocess.run(cmd, check=True)
     return target

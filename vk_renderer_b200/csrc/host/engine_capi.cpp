@@ -1,0 +1,77 @@
+// engine_capi.cpp — extern "C" surface of the C++ host engine (libvkr_engine.so), the call a user of
+// this repo makes: create an engine, build a scene, then update_scene() + draw() per frame.
+// Python (tests, bench.py) drives it through ctypes; see vk_renderer_b200/engine.py.
+#include <cstring>
+
+#include "vk_engine.h"
+#include "vk_loader.h"
+
+const VkrApi& libvkr_api() {
+    static const VkrApi api = {vkr_create, vkr_destroy, vkr_upload_mesh, vkr_create_image, vkr_update_bindless_texture,
+                               vkr_set_cubemap, vkr_build_material, vkr_draw, vkr_readback, vkr_readback_async, vkr_sync};
+    return api;
+}
+
+extern "C" {
+
+// api == nullptr -> libvkr (the product).  A non-null table is how tests put the oracle behind the engine.
+VulkanEngine* vke_create(uint32_t width, uint32_t height, int device, void* stream, uint32_t flags, const VkrApi* api,
+                         uint32_t shadowExtent) {
+    VulkanEngine* e = new VulkanEngine();
+    if (api) e->_api = *api;
+    if (shadowExtent) e->_shadowExtent = {shadowExtent, shadowExtent};   // default 2048 (src/vk_engine.h:107)
+    if (e->init(width, height, device, stream, flags) != VKR_SUCCESS) { delete e; return nullptr; }
+    return e;
+}
+void vke_destroy(VulkanEngine* e) { delete e; }
+VkrDevice* vke_device(VulkanEngine* e) { return e->_vkr; }
+
+uint64_t vke_load_procedural(VulkanEngine* e, int config, uint32_t seed) { return load_procedural(e, config, seed); }
+void vke_orbit_camera(VulkanEngine* e, uint32_t seed, int view) { orbit_camera(e, seed, view); }
+
+void vke_set_camera(VulkanEngine* e, float x, float y, float z, float pitch, float yaw) {
+    e->_mainCamera.position = vkm::vec3{x, y, z};
+    e->_mainCamera.pitch = pitch; e->_mainCamera.yaw = yaw;
+}
+void vke_set_light(VulkanEngine* e, const float dir[3], const float color[3], const float ambient[3]) {
+    if (dir) e->_sunlightDirection = vkm::vec4{dir[0], dir[1], dir[2], 0.0f};
+    if (color) e->_sunlightColor = vkm::vec4{color[0], color[1], color[2], 1.0f};
+    if (ambient) e->_ambientColor = vkm::vec4{ambient[0], ambient[1], ambient[2], 1.0f};
+}
+// the ImGui "Settings" toggles (src/vk_engine_run.cpp:200-232); a negative value leaves a field unchanged
+void vke_set_toggles(VulkanEngine* e, int enableShadows, int shadowMode, int enableBackground, int enablePostprocess, int fragShader) {
+    if (enableShadows >= 0) e->_enableShadows = enableShadows != 0;
+    if (shadowMode >= 0) e->_shadowMode = shadowMode;
+    if (enableBackground >= 0) e->_enableBackground = enableBackground != 0;
+    if (enablePostprocess >= 0) e->_enablePostprocess = enablePostprocess != 0;
+    if (fragShader >= 0) e->_fragShader = fragShader;
+}
+void vke_set_scissor(VulkanEngine* e, int x, int y, int w, int h, int cullToScissor) {
+    e->_scissor[0] = x; e->_scissor[1] = y; e->_scissor[2] = w; e->_scissor[3] = h;
+    e->_cullToScissor = cullToScissor != 0;
+}
+
+void vke_update_scene(VulkanEngine* e, float dt) { e->update_scene(dt); }
+int vke_draw(VulkanEngine* e) { return e->draw(); }
+int vke_present(VulkanEngine* e, void* pinnedDst, size_t bytes) { return e->present(pinnedDst, bytes); }
+int vke_sync(VulkanEngine* e) { return e->_api.sync ? e->_api.sync(e->_vkr) : VKR_SUCCESS; }
+int vke_readback(VulkanEngine* e, int what, void* dst, size_t bytes) { return e->_api.readback(e->_vkr, (VkrTarget)what, dst, bytes); }
+
+void vke_stats(VulkanEngine* e, EngineStats* out) { *out = e->stats; }
+size_t vke_visible_objects(VulkanEngine* e) { return e->_renderObjects.size(); }
+void vke_scene_data(VulkanEngine* e, GPUSceneData* out) { *out = e->_sceneData; }
+
+// host-math probes (checked against glm golden vectors and the oracle's restatement)
+void vke_camera_matrices(VulkanEngine* e, float view[16], float proj[16]) {
+    vkm::mat4 v = e->_mainCamera.getViewMatrix();
+    vkm::mat4 p = e->_mainCamera.getProjectionMatrix((float)e->_windowExtent.width / (float)e->_windowExtent.height);
+    std::memcpy(view, v.data(), 64); std::memcpy(proj, p.data(), 64);
+}
+void vke_light_matrix(VulkanEngine* e, float out[16]) { vkm::mat4 m = e->compute_light_matrix(); std::memcpy(out, m.data(), 64); }
+void vke_csm(VulkanEngine* e, float matrices[64], float distances[4]) {
+    CSMData c = e->compute_csmdata();
+    for (int i = 0; i < NUM_CASCADES; ++i) { std::memcpy(matrices + 16 * i, c.lightMatrices[i].data(), 64); distances[i] = c.planeDistances[i]; }
+}
+float vke_compute_split(float n, float f, int i) { return compute_split(n, f, i); }
+
+}  // extern "C"

@@ -128,6 +128,7 @@ __global__ void __launch_bounds__(GEOM_BLOCK) geometry_kernel(const DObject* __r
     const uint32_t* __restrict__ clTris = reinterpret_cast<const uint32_t*>(((uint64_t)c1.y << 32) | c1.x);
     const uint32_t obj = c1.z, counts = c2.x;
     (void)objects;
+    if (!SHADOW && (c2.y & 2u)) return;     // alpha-tested draw: geometry_cutout_kernel owns this cluster
     if (threadIdx.x < 16) s_mvp[threadIdx.x] = __ldg(mvps + (size_t)obj * mvpStride + threadIdx.x);
     const uint32_t nVerts = counts & 0xFFFFu, nTris = counts >> 16;
     __syncthreads();
@@ -153,9 +154,27 @@ __global__ void __launch_bounds__(GEOM_BLOCK) geometry_kernel(const DObject* __r
     }
 }
 
+// ---- main pass, alpha-tested draws only (launched when the frame has any): one thread per triangle,
+// straight from the original vertices, coverage gated by the albedo alpha (vkr_raster.cuh alpha_passes)
+__global__ void __launch_bounds__(GEOM_BLOCK) geometry_cutout_kernel(const DObject* __restrict__ objects, const DChunk* __restrict__ chunks,
+                                                                     const __grid_constant__ RasterTarget rt, const __grid_constant__ Queues q,
+                                                                     const __grid_constant__ AlphaCtx ax) {
+    const DChunk& ch = chunks[blockIdx.x];
+    if (!(ch.pad[0] & 2u)) return;
+    const uint32_t nTris = ch.counts >> 16;
+    if (threadIdx.x >= nTris) return;
+    const DObject& o = objects[ch.obj];
+    const uint32_t packed = ch.clTris[threadIdx.x];
+    const uint32_t g0 = ch.clVerts[packed & 1023u], g1 = ch.clVerts[(packed >> 10) & 1023u], g2 = ch.clVerts[packed >> 20];
+    const uint32_t seq = blockIdx.x * GEOM_BLOCK + threadIdx.x;
+    VisSink sink{rt.vis, rt.width, 0xFFFFFFFEu - seq};
+    cutout_triangle(o, o.mvp, g0, g1, g2, seq, rt, q, ax, sink);
+}
+
 // ---- large triangles: one warp per (triangle, 64x64 tile) item, grid-stride over the queue
 template <bool SHADOW>
-__global__ void __launch_bounds__(256) large_raster_kernel(const __grid_constant__ RasterTarget rt, const __grid_constant__ Queues q) {
+__global__ void __launch_bounds__(256) large_raster_kernel(const __grid_constant__ RasterTarget rt, const __grid_constant__ Queues q,
+                                                           const __grid_constant__ AlphaCtx ax, int anyCutout) {
     const uint32_t nItems = min(q.counters[1], q.itemCap);
     const uint32_t warpsPerGrid = (gridDim.x * blockDim.x) >> 5;
     const int lane = threadIdx.x & 31;
@@ -167,7 +186,15 @@ __global__ void __launch_bounds__(256) large_raster_kernel(const __grid_constant
             raster_item(lt, it, sink, lane, 32);
         } else {
             VisSink sink{rt.vis, rt.width, 0xFFFFFFFEu - lt.seq};
-            raster_item(lt, it, sink, lane, 32);
+            if (anyCutout && (ax.chunks[lt.seq >> 8].pad[0] & 2u)) {
+                const DChunk& ch = ax.chunks[lt.seq >> 8];
+                const DObject& o = ax.objects[ch.obj];
+                const uint32_t tri = ch.firstTri + (lt.seq & 255u);
+                AlphaTri at;
+                make_alpha_tri(o, o.mvp, o.idx[3 * tri], o.idx[3 * tri + 1], o.idx[3 * tri + 2], ax, rt, at);
+                CutoutSink<VisSink> cs{sink, &at};
+                raster_item(lt, it, cs, lane, 32);
+            } else raster_item(lt, it, sink, lane, 32);
         }
     }
 }
@@ -558,7 +585,7 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
     CK(cudaSetDevice(dev->device));
     FramePlan& plan = dev->plan;
     DeviceClusterProvider provider(dev);
-    std::string why = plan_frame(scene, objs, n, fp, dev->meshes, dev->materials, provider, dev->W, dev->H, dev->S, plan);
+    std::string why = plan_frame(scene, objs, n, fp, dev->meshes, dev->materials, dev->texHost, provider, dev->W, dev->H, dev->S, plan);
     if (!why.empty()) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, why.c_str());
     cudaStream_t st = dev->stream;
     dev->launches = 0;
@@ -634,7 +661,7 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
             dev->launches += 1;
             if (nChunks) {
                 geometry_kernel<true><<<nChunks, GEOM_BLOCK, 0, ss>>>(dObjects, dChunks, dShadowMvp + (size_t)layer * n * 16, 16u, rt, dev->qShadow);
-                large_raster_kernel<true><<<largeGrid, 256, 0, ss>>>(rt, dev->qShadow);
+                large_raster_kernel<true><<<largeGrid, 256, 0, ss>>>(rt, dev->qShadow, AlphaCtx{}, 0);
                 dev->launches += 2;
             }
             CK(cudaMemcpyAsync(dev->countersHost + 4, dev->qShadow.counters, 16, cudaMemcpyDeviceToHost, ss));
@@ -657,7 +684,12 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
         if (opaqueChunks) {
             geometry_kernel<false><<<opaqueChunks, GEOM_BLOCK, 0, st>>>(dObjects, dChunks, (const float*)dObjects, (uint32_t)(sizeof(DObject) / 4), rt, dev->q);
             if (timing) CK(cudaEventRecord(dev->tev[4], st));
-            large_raster_kernel<false><<<largeGrid, 256, 0, st>>>(rt, dev->q);
+            const AlphaCtx ax{dObjects, dChunks, dev->matDev, dev->texDev};
+            if (plan.anyCutout) {
+                geometry_cutout_kernel<<<opaqueChunks, GEOM_BLOCK, 0, st>>>(dObjects, dChunks, rt, dev->q, ax);
+                dev->launches += 1;
+            }
+            large_raster_kernel<false><<<largeGrid, 256, 0, st>>>(rt, dev->q, ax, plan.anyCutout ? 1 : 0);
             dev->launches += 2;
         } else if (timing) CK(cudaEventRecord(dev->tev[4], st));
         CK(cudaMemcpyAsync(dev->countersHost, dev->q.counters, 16, cudaMemcpyDeviceToHost, st));

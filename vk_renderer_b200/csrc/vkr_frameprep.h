@@ -89,6 +89,7 @@ struct FramePlan {
     std::vector<uint32_t> primBase;     // nobj + 1 (dense ids, for stats / readback)
     std::vector<uint32_t> clusterBase;  // nobj + 1: first frame-cluster index of every draw
     uint32_t opaqueClusters = 0;        // clusters of the opaque prefix
+    bool anyCutout = false;             // some draw needs the raster-stage alpha test
     std::vector<float> shadowMvp;       // layers * nobj * 16
     int shadowLayers = 0;
     uint32_t totalTris = 0;
@@ -101,7 +102,7 @@ struct FramePlan {
 // Returns an empty string on success, else the reason the draw list is invalid.
 inline std::string plan_frame(const VkrGPUSceneData* scene, const VkrRenderObject* objs, size_t n, const VkrFrameParams* fp,
                               const std::vector<DMesh>& meshes, const std::vector<DMaterial>& materials,
-                              ClusterProvider& clusters, uint32_t W, uint32_t H, uint32_t S, FramePlan& plan) {
+                              const std::vector<DTexture>& textures, ClusterProvider& clusters, uint32_t W, uint32_t H, uint32_t S, FramePlan& plan) {
     plan.objects.resize(n);
     plan.primBase.resize(n + 1);
     plan.clusterBase.resize(n + 1);
@@ -111,6 +112,7 @@ inline std::string plan_frame(const VkrGPUSceneData* scene, const VkrRenderObjec
     uint64_t prim = 0;
     bool seenTransparent = false;
     plan.opaqueCount = (uint32_t)n;
+    plan.anyCutout = false;
     for (size_t i = 0; i < n; ++i) {
         const VkrRenderObject& ro = objs[i];
         if (ro.mesh >= meshes.size()) return "render object references an unknown mesh";
@@ -134,6 +136,10 @@ inline std::string plan_frame(const VkrGPUSceneData* scene, const VkrRenderObjec
         o.primBase = (uint32_t)prim;
         o.material = ro.material;
         o.flags = transparent ? 1u : 0u;
+        {   // alpha-tested draw: its albedo texture has texels with alpha < 0.5 (DTexture flag bit2)
+            const int aid = materials[ro.material].albedoID;
+            if (aid >= 0 && aid < (int)textures.size() && textures[aid].data != nullptr && (textures[aid].flags & 4u)) { o.flags |= 2u; plan.anyCutout = true; }
+        }
         plan.primBase[i] = (uint32_t)prim;
         plan.clusterBase[i] = (uint32_t)ncl;
         ncl += (o.triCount + GEOM_BLOCK - 1) / GEOM_BLOCK;

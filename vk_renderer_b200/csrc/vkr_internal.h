@@ -61,7 +61,7 @@ struct DObject {
     uint32_t triCount;
     uint32_t primBase;        // dense submission-order id of this draw's first triangle (readback only)
     uint32_t material;
-    uint32_t flags;           // bit0: transparent pass
+    uint32_t flags;           // bit0: transparent pass, bit1: alpha-tested (albedo texture has alpha < 0.5)
     uint32_t pad[2];
 };
 
@@ -84,7 +84,8 @@ VKR_HD DChunk make_chunk(const DObject& o, uint32_t obj, uint32_t c) {
     DChunk ch;
     ch.pos = o.pos; ch.clVerts = o.clVerts + info.x; ch.clTris = o.clTris + (size_t)c * GEOM_BLOCK;
     ch.obj = obj; ch.firstTri = c * GEOM_BLOCK; ch.counts = info.y;
-    ch.pad[0] = ch.pad[1] = ch.pad[2] = 0;
+    ch.pad[0] = o.flags;      // draw flags (bit0 transparent, bit1 alpha-tested) ride along for the geometry CTA
+    ch.pad[1] = ch.pad[2] = 0;
     return ch;
 }
 

@@ -368,4 +368,129 @@ VKR_HD void cluster_triangle(const CachedVtx& a, const CachedVtx& b, const Cache
     if (setup_snapped(v0, v1, v2, rt, t)) emit_setup(t, seq, q, sink);
 }
 
+// ---- alpha test in the raster stage ---------------------------------------------------------
+// mesh_pbr.frag / mesh.frag `discard` fragments whose albedo alpha < 0.5 (shaders/mesh_pbr.frag:193):
+// such fragments must not write depth, so for draws whose albedo texture has any texel alpha < 0.5 the
+// test runs here, before the visibility-buffer atomic.  It decides coverage, so it is evaluated with
+// explicitly rounded operations in the oracle's order (texture2D + bary_at in oracle/ork.cpp).
+struct AlphaCtx {              // what the alpha test needs to find a primitive's texture and vertices
+    const DObject* objects;
+    const DChunk* chunks;
+    const DMaterial* materials;
+    const DTexture* textures;
+};
+struct AlphaTri {
+    float cx[3], cy[3], cw[3];   // clip x, y, w of the ORIGINAL triangle's vertices
+    float u[3], v[3];
+    const DTexture* tex;
+    float halfW, halfH;
+};
+
+VKR_HD float alpha_texel(const DTexture& t, int level, int x, int y, int w) {
+    return xdiv((float)t.data[t.mipOffset[level] + (size_t)y * w + x].w, 255.0f);
+}
+VKR_HD int alpha_wrap(int i, int n) { int r = i % n; return r < 0 ? r + n : r; }
+VKR_HD float alpha_sample_level(const DTexture& t, int level, float u, float v) {
+    int w = (int)(t.w >> level), h = (int)(t.h >> level);
+    if (w < 1) w = 1;
+    if (h < 1) h = 1;
+    if (!(t.flags & 2u)) {
+        const int x = alpha_wrap((int)floorf(xmul(u, (float)w)), w), y = alpha_wrap((int)floorf(xmul(v, (float)h)), h);
+        return alpha_texel(t, level, x, y, w);
+    }
+    const float fu = xsub(xmul(u, (float)w), 0.5f), fv = xsub(xmul(v, (float)h), 0.5f);
+    const float iu = floorf(fu), iv = floorf(fv);
+    const float a = xsub(fu, iu), b = xsub(fv, iv);
+    const int x0 = alpha_wrap((int)iu, w), x1 = alpha_wrap((int)iu + 1, w);
+    const int y0 = alpha_wrap((int)iv, h), y1 = alpha_wrap((int)iv + 1, h);
+    const float t00 = alpha_texel(t, level, x0, y0, w), t10 = alpha_texel(t, level, x1, y0, w);
+    const float t01 = alpha_texel(t, level, x0, y1, w), t11 = alpha_texel(t, level, x1, y1, w);
+    const float w00 = xmul(xsub(1.0f, a), xsub(1.0f, b)), w10 = xmul(a, xsub(1.0f, b)), w01 = xmul(xsub(1.0f, a), b), w11 = xmul(a, b);
+    return xadd(xadd(xadd(xmul(t00, w00), xmul(t10, w10)), xmul(t01, w01)), xmul(t11, w11));
+}
+VKR_HD void alpha_bary(const AlphaTri& a, float sx, float sy, float b[3]) {
+    const float nx = xdiv(xsub(sx, a.halfW), a.halfW), ny = xdiv(xsub(sy, a.halfH), a.halfH);
+    float qx[3], qy[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) { qx[i] = xsub(a.cx[i], xmul(nx, a.cw[i])); qy[i] = xsub(a.cy[i], xmul(ny, a.cw[i])); }
+    const float e0 = xsub(xmul(qx[1], qy[2]), xmul(qx[2], qy[1]));
+    const float e1 = xsub(xmul(qx[2], qy[0]), xmul(qx[0], qy[2]));
+    const float e2 = xsub(xmul(qx[0], qy[1]), xmul(qx[1], qy[0]));
+    const float s = xadd(xadd(e0, e1), e2);
+    if (s == 0.0f) { b[0] = 1.0f; b[1] = 0.0f; b[2] = 0.0f; return; }
+    b[0] = xdiv(e0, s); b[1] = xdiv(e1, s); b[2] = xdiv(e2, s);
+}
+VKR_HD float alpha_lerp(const float a[3], const float b[3]) { return xadd(xadd(xmul(b[0], a[0]), xmul(b[1], a[1])), xmul(b[2], a[2])); }
+
+VKR_HDN bool alpha_passes(const AlphaTri& a, int px, int py) {
+    const DTexture& t = *a.tex;
+    if (t.data == nullptr) return true;                       // unbound slot samples (0,0,0,1)
+    const float cx = xadd((float)px, 0.5f), cy = xadd((float)py, 0.5f);
+    float bc[3];
+    alpha_bary(a, cx, cy, bc);
+    const float u = alpha_lerp(a.u, bc), v = alpha_lerp(a.v, bc);
+    const int levels = (int)t.levels;
+    float alpha;
+    if (levels == 1) alpha = alpha_sample_level(t, 0, u, v);
+    else {
+        const float ox = (px & 1) ? -1.0f : 1.0f, oy = (py & 1) ? -1.0f : 1.0f;
+        float bx[3], by[3];
+        alpha_bary(a, xadd(cx, ox), cy, bx);
+        alpha_bary(a, cx, xadd(cy, oy), by);
+        const float dudx = xmul(xsub(alpha_lerp(a.u, bx), u), ox), dvdx = xmul(xsub(alpha_lerp(a.v, bx), v), ox);
+        const float dudy = xmul(xsub(alpha_lerp(a.u, by), u), oy), dvdy = xmul(xsub(alpha_lerp(a.v, by), v), oy);
+        const float w = (float)t.w, h = (float)t.h;
+        const float ax = xmul(dudx, w), bxv = xmul(dvdx, h), ay = xmul(dudy, w), byv = xmul(dvdy, h);
+        const float rx = sqrtf(xadd(xmul(ax, ax), xmul(bxv, bxv))), ry = sqrtf(xadd(xmul(ay, ay), xmul(byv, byv)));
+        const float rho = fmaxf(rx, ry);
+        const float lambda = rho > 0.0f ? log2f(rho) : -126.0f;
+        const float lod = fminf(fmaxf(lambda, 0.0f), (float)(levels - 1));
+        const int l0 = (int)floorf(lod), l1 = l0 + 1 < levels ? l0 + 1 : levels - 1;
+        const float f = xsub(lod, (float)l0);
+        const float c0 = alpha_sample_level(t, l0, u, v);
+        if (f == 0.0f) alpha = c0;
+        else alpha = xadd(xmul(c0, xsub(1.0f, f)), xmul(alpha_sample_level(t, l1, u, v), f));
+    }
+    return !(alpha < 0.5f);
+}
+
+// Gather the alpha-test inputs of primitive `tri` of draw `o` (positions re-transformed exactly as the
+// geometry pass does, uv from the attribute streams).
+VKR_HD void make_alpha_tri(const DObject& o, const float* __restrict__ mvp, uint32_t g0, uint32_t g1, uint32_t g2,
+                           const AlphaCtx& ax, const RasterTarget& rt, AlphaTri& a) {
+    const uint32_t g[3] = {g0, g1, g2};
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const float4 p = o.pos[g[k]];
+        const float4 c = transform_point(mvp, p.x, p.y, p.z);
+        a.cx[k] = c.x; a.cy[k] = c.y; a.cw[k] = c.w;
+        a.u[k] = o.attrA[g[k]].w; a.v[k] = o.attrB[g[k]].w;
+    }
+    const int id = ax.materials[o.material].albedoID;
+    a.tex = ax.textures + ((id >= 0 && id < VKR_MAX_BINDLESS) ? id : 0);
+    a.halfW = rt.halfW; a.halfH = rt.halfH;
+}
+
+template <class Base>
+struct CutoutSink {
+    Base base;
+    const AlphaTri* a;
+    VKR_HD void put(int32_t px, int32_t py, float z) const { if (alpha_passes(*a, px, py)) base.put(px, py, z); }
+};
+
+// Phase 2 for a triangle of an alpha-tested draw (always from the original vertices).
+template <class Sink>
+VKR_HDN void cutout_triangle(const DObject& o, const float* __restrict__ mvp, uint32_t g0, uint32_t g1, uint32_t g2, uint32_t seq,
+                             const RasterTarget& rt, const Queues& q, const AlphaCtx& ax, const Sink& base) {
+    AlphaTri a;
+    make_alpha_tri(o, mvp, g0, g1, g2, ax, rt, a);
+    CutoutSink<Sink> sink{base, &a};
+    const float4 p0 = o.pos[g0], p1 = o.pos[g1], p2 = o.pos[g2];
+    const float4 c0 = transform_point(mvp, p0.x, p0.y, p0.z), c1 = transform_point(mvp, p1.x, p1.y, p1.z), c2 = transform_point(mvp, p2.x, p2.y, p2.z);
+    if (inside_clip_volume(c0) && inside_clip_volume(c1) && inside_clip_volume(c2)) {
+        SetupTri t;
+        if (setup_snapped(project_vertex(c0, rt), project_vertex(c1, rt), project_vertex(c2, rt), rt, t)) emit_setup(t, seq, q, sink);
+    } else clip_and_emit(c0, c1, c2, seq, rt, q, sink);
+}
+
 }  // namespace vkr

@@ -268,10 +268,10 @@ struct Fragment {
     float dudx, dvdx, dudy, dvdy;
 };
 
-// Returns false on discard (alpha test).
+// The shaders' `discard` (albedo alpha < 0.5) was already applied in the raster stage (vkr_raster.cuh
+// alpha_passes), which owns that decision: a fragment that reached the visibility buffer is shaded.
 VKR_HD bool shade_fragment(const ShadeConst& sc, const ShadeBuffers& sb, const DMaterial& m, const Fragment& fr, f3& out) {
     float4 albedoTex = texture2d(sb, m.albedoID, fr.u, fr.v, fr.dudx, fr.dvdx, fr.dudy, fr.dvdy);
-    if (albedoTex.w < 0.5f) return false;
     f3 base = f3{m.colorFactors[0], m.colorFactors[1], m.colorFactors[2]} * f3{albedoTex.x, albedoTex.y, albedoTex.z} * fr.color;
     f3 N = norm3(fr.normal);
     f3 L = norm3(f3{sc.lightVec[0], sc.lightVec[1], sc.lightVec[2]});
