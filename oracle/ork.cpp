@@ -880,15 +880,34 @@ vec4 read_hdr(const OrkDevice* d, size_t pix) {
     return {f16_to_f32(p[0]), f16_to_f32(p[1]), f16_to_f32(p[2]), f16_to_f32(p[3])};
 }
 
+// gradient_color.comp main() — shaders/gradient_color.comp:16-31: mix(top, bottom, y / height)
+vec4 gradient_color(const float* top, const float* bot, int y, int height) {
+    float blend = (float)y / (float)height;
+    return {top[0] * (1.0f - blend) + bot[0] * blend, top[1] * (1.0f - blend) + bot[1] * blend,
+            top[2] * (1.0f - blend) + bot[2] * blend, top[3] * (1.0f - blend) + bot[3] * blend};
+}
+
+// Per-pixel form of skybox.vert (shaders/skybox.vert:8-17): the cube position whose projection
+// proj * mat4(mat3(view)) * pos lands on window position (sx, sy), with outUVW.y negated.
+vec3 skybox_dir(const mat4& view, const mat4& proj, float halfW, float halfH, float sx, float sy) {
+    float nx = (sx - halfW) / halfW, ny = (sy - halfH) / halfH;
+    // view-space ray: proj * (xv, yv, -1, 1) = (nx, ny, ., 1) * w  for a perspective proj
+    vec3 dv = {(nx + proj.m[2][0]) / proj.m[0][0], (ny + proj.m[2][1]) / proj.m[1][1], -1.0f};
+    // pos = transpose(mat3(view)) * dv   (inverse of the rotation skybox.vert applies, skybox.vert:14-15)
+    vec3 p = {view.m[0][0] * dv.x + view.m[0][1] * dv.y + view.m[0][2] * dv.z,
+              view.m[1][0] * dv.x + view.m[1][1] * dv.y + view.m[1][2] * dv.z,
+              view.m[2][0] * dv.x + view.m[2][1] * dv.y + view.m[2][2] * dv.z};
+    p.y *= -1.0f;   // outUVW.y *= -1.0 (skybox.vert:11)
+    return p;
+}
+
 // draw_background — src/vk_engine_run.cpp:234-242 + gradient_color.comp:16-31
 void pass_background(const DrawCtx& dc) {
     OrkDevice* d = dc.d;
     const float* top = dc.fp->background.data1;
     const float* bot = dc.fp->background.data2;
     parallel_for(d->nthreads, d->H, [&](int y) {
-        float blend = (float)y / (float)d->H;
-        vec4 c = {top[0] * (1.0f - blend) + bot[0] * blend, top[1] * (1.0f - blend) + bot[1] * blend,
-                  top[2] * (1.0f - blend) + bot[2] * blend, top[3] * (1.0f - blend) + bot[3] * blend};
+        vec4 c = gradient_color(top, bot, y, d->H);
         for (int x = 0; x < d->W; ++x) write_hdr(d, (size_t)y * d->W + x, c);
     });
 }
@@ -985,17 +1004,7 @@ void pass_geometry(const DrawCtx& dc) {
     // draw_skybox: cull FRONT cube at depth 1.0, LEQUAL, no depth write -> every pixel whose depth is still 1.0
     if (dc.fp->enableSkybox && d->haveCube) {
         mat4 view = load_mat(sd.view), proj = load_mat(sd.proj);
-        auto dir_at = [&](float sx, float sy) {
-            float nx = (sx - vp.halfW) / vp.halfW, ny = (sy - vp.halfH) / vp.halfH;
-            // view-space ray: proj * (xv, yv, -1, 1) = (nx, ny, ., 1) * w  for a perspective proj
-            vec3 dv = {(nx + proj.m[2][0]) / proj.m[0][0], (ny + proj.m[2][1]) / proj.m[1][1], -1.0f};
-            // pos = transpose(mat3(view)) * dv   (inverse of the rotation skybox.vert applies, skybox.vert:14-15)
-            vec3 p = {view.m[0][0] * dv.x + view.m[0][1] * dv.y + view.m[0][2] * dv.z,
-                      view.m[1][0] * dv.x + view.m[1][1] * dv.y + view.m[1][2] * dv.z,
-                      view.m[2][0] * dv.x + view.m[2][1] * dv.y + view.m[2][2] * dv.z};
-            p.y *= -1.0f;   // outUVW.y *= -1.0 (skybox.vert:11)
-            return p;
-        };
+        auto dir_at = [&](float sx, float sy) { return skybox_dir(view, proj, vp.halfW, vp.halfH, sx, sy); };
         parallel_for(d->nthreads, vp.sy1 - vp.sy0, [&](int yy) {
             int py = vp.sy0 + yy;
             for (int px = vp.sx0; px < vp.sx1; ++px) {
@@ -1205,6 +1214,40 @@ void ork_brdf(const float N[3], const float V[3], const float L[3], float roughn
 void ork_tonemap(const float in[3], float out[3]) {
     vec3 m = tonemap({in[0], in[1], in[2]});
     out[0] = m.x; out[1] = m.y; out[2] = m.z;
+}
+void ork_gradient(const VkrComputePushConstants* push, int y, int height, float out[4]) {
+    vec4 c = gradient_color(push->data1, push->data2, y, height);
+    out[0] = c.x; out[1] = c.y; out[2] = c.z; out[3] = c.w;
+}
+void ork_vertex(const VkrGPUSceneData* scene, const float world[16], const VkrVertex* v, float out[23]) {
+    mat4 w = load_mat(world);
+    VSOut o = vertex_main(*v, w, mul(load_mat(scene->viewproj), w), *scene);
+    float r[23] = {o.clip.x, o.clip.y, o.clip.z, o.clip.w, o.normal.x, o.normal.y, o.normal.z, o.color.x, o.color.y, o.color.z,
+                   o.uv.x, o.uv.y, o.lightVec.x, o.lightVec.y, o.lightVec.z, o.posWorld.x, o.posWorld.y, o.posWorld.z, o.posWorld.w,
+                   o.posView.x, o.posView.y, o.posView.z, o.posView.w};
+    std::memcpy(out, r, sizeof r);
+}
+void ork_shadow_vertex(const VkrGPUSceneData* scene, const float world[16], int cascade, const VkrVertex* v, float out[4]) {
+    mat4 M = mul(load_mat(scene->lightViewproj[cascade]), load_mat(world));
+    vec4 c = mul_point_fma(M, v->position[0], v->position[1], v->position[2]);
+    out[0] = c.x; out[1] = c.y; out[2] = c.z; out[3] = c.w;
+}
+void ork_skybox_dir(const VkrGPUSceneData* scene, int width, int height, float sx, float sy, float out[3]) {
+    vec3 p = skybox_dir(load_mat(scene->view), load_mat(scene->proj), (float)width * 0.5f, (float)height * 0.5f, sx, sy);
+    out[0] = p.x; out[1] = p.y; out[2] = p.z;
+}
+void ork_cb_tex2d(void* ctx, int id, float u, float v, float out[4]) {
+    const OrkTexCtx* c = (const OrkTexCtx*)ctx;
+    vec4 t = texture2D(c->dev, id, {u, v}, {c->duvdx[0], c->duvdx[1]}, {c->duvdy[0], c->duvdy[1]});
+    out[0] = t.x; out[1] = t.y; out[2] = t.z; out[3] = t.w;
+}
+float ork_cb_shadow(void* ctx, float u, float v, int layer) {
+    return texture_shadow(((const OrkTexCtx*)ctx)->dev, u, v, layer);
+}
+void ork_cb_cube(void* ctx, const float dir[3], float out[4]) {
+    vec3 r = {dir[0], dir[1], dir[2]};
+    vec4 t = texture_cube(((const OrkTexCtx*)ctx)->dev, r, r, r);
+    out[0] = t.x; out[1] = t.y; out[2] = t.z; out[3] = t.w;
 }
 
 }  // extern "C"

@@ -61,6 +61,21 @@ int ork_load_shadow(OrkDevice* dev, const float* depth, size_t count);  /* overw
 void ork_brdf(const float N[3], const float V[3], const float L[3], float roughness, const float F0[3],
               float* D, float* G, float F[3]);
 void ork_tonemap(const float in[3], float out[3]);
+/* gradient_color.comp for pixel row y of a height-row image. */
+void ork_gradient(const VkrComputePushConstants* push, int y, int height, float out[4]);
+/* mesh.vert main(): out = gl_Position[4], normal[3], color[3], uv[2], lightVec[3], posWorld[4], posView[4]. */
+void ork_vertex(const VkrGPUSceneData* scene, const float world[16], const VkrVertex* v, float out[23]);
+/* shadow.vert main(): gl_Position for cascade `cascade`. */
+void ork_shadow_vertex(const VkrGPUSceneData* scene, const float world[16], int cascade, const VkrVertex* v, float out[4]);
+/* The per-pixel form of skybox.vert's outUVW at window position (sx, sy). */
+void ork_skybox_dir(const VkrGPUSceneData* scene, int width, int height, float sx, float sy, float out[3]);
+
+/* The oracle's texture unit as callbacks, so oracle/_ref/librefshader.so (the reference's shader text)
+ * can be run against the same fixed-function sampling when golden vectors are generated. */
+typedef struct OrkTexCtx { OrkDevice* dev; float duvdx[2], duvdy[2]; } OrkTexCtx;
+void ork_cb_tex2d(void* ctx, int id, float u, float v, float out[4]);
+float ork_cb_shadow(void* ctx, float u, float v, int layer);
+void ork_cb_cube(void* ctx, const float dir[3], float out[4]);
 
 #ifdef __cplusplus
 }
