@@ -58,6 +58,39 @@ def rewrite_body(s: str) -> str:
     return s
 
 
+HOST_FUNCS = [  # (file, function name as it appears before the parameter list)
+    ("src/vk_camera.cpp", "Camera::getViewMatrix"), ("src/vk_camera.cpp", "Camera::getRotationMatrix"),
+    ("src/vk_camera.cpp", "Camera::getProjectionMatrix"),
+    ("src/vk_engine_run.cpp", "extract_frustum_planes"), ("src/vk_engine_run.cpp", "VulkanEngine::is_visible"),
+    ("src/vk_engine_run.cpp", "VulkanEngine::compute_light_matrix"), ("src/vk_engine_run.cpp", "getFrustumCornerWorld"),
+    ("src/vk_engine_run.cpp", "VulkanEngine::getLightMatrix"), ("src/vk_engine_run.cpp", "compute_split"),
+    ("src/vk_engine_run.cpp", "VulkanEngine::compute_csmdata"),
+]
+
+
+def extract_function(text: str, name: str) -> str:
+    """The verbatim definition `<ret> name(...) {...}` (brace matched) from a C++ source text."""
+    m = re.search(r"^[^\n;{}()]*\b" + re.escape(name) + r"\s*\([^)]*\)\s*\{", text, flags=re.M)
+    if not m:
+        raise SystemExit(f"gen.py: {name} not found")
+    depth, i = 0, m.end() - 1
+    while True:
+        depth += {"{": 1, "}": -1}.get(text[i], 0)
+        i += 1
+        if depth == 0:
+            return text[m.start():i]
+
+
+def host_math(ref: str, out: str):
+    """Host functions of the path (camera, light/CSM matrices, frustum cull), verbatim, for refhost.cpp.
+    Their translation units include <vulkan/vulkan.h>, SDL and VMA, so they cannot be compiled whole."""
+    parts = []
+    for rel, name in HOST_FUNCS:
+        parts.append(f"// ---- {rel}: {name}\n" + extract_function(open(os.path.join(ref, rel)).read(), name))
+    with open(os.path.join(out, "host_math.inc"), "w") as f:
+        f.write("// generated from the reference's src/*.cpp by oracle/refshader/gen.py — do not commit\n" + "\n\n".join(parts) + "\n")
+
+
 def main():
     ref, out = sys.argv[1], sys.argv[2]
     sd = os.path.join(ref, "shaders")
@@ -66,6 +99,7 @@ def main():
         text = rewrite(open(os.path.join(sd, name)).read(), sd)
         with open(os.path.join(out, name.replace(".", "_") + ".inc"), "w") as f:
             f.write(f"// generated from {sd}/{name} by oracle/refshader/gen.py — do not commit\n" + text + "\n")
+    host_math(ref, out)
 
 
 if __name__ == "__main__":

@@ -56,12 +56,15 @@ def test_known_answer_vectors(ork_lib):
 
 
 def test_golden_host_math(ork_lib):
-    """tests/golden/host_math.json: outputs of the reference's own host functions' formulas evaluated with
-    the vendored glm (generated by oracle/refshader/gen_golden; see tests/golden/README.md)."""
+    """tests/golden/host_math.json: outputs of the reference's own host functions (src/vk_camera.cpp,
+    src/vk_engine_run.cpp:420-566) compiled from their source text against the vendored glm
+    (oracle/refshader/refhost.cpp; generator tools/gen_golden.py)."""
     path = os.path.join(HERE, "golden", "host_math.json")
-    if not os.path.exists(path):
-        pytest.skip("golden vectors not generated")
     G = json.load(open(path))
+    e = Engine(64, 64, api_lib=ork_lib, api_prefix="ork", shadow_extent=64)
+    np.testing.assert_allclose([e.lib.vke_compute_split(0.1, 100.0, i) for i in (1, 2, 3, 4)], G["compute_split_0.1_100"], rtol=2e-7)
+    e.close()
+    n_vis = 0
     for case in G["cases"]:
         e = Engine(case["width"], case["height"], api_lib=ork_lib, api_prefix="ork", shadow_extent=64)
         e.set_camera(case["position"], case["pitch"], case["yaw"])
@@ -73,7 +76,20 @@ def test_golden_host_math(ork_lib):
         m, d = e.csm()
         np.testing.assert_allclose(d, case["csm_distances"], rtol=1e-6)
         np.testing.assert_allclose(m.transpose(0, 2, 1).reshape(-1), case["csm_matrices"], rtol=2e-4, atol=2e-4)
+        np.testing.assert_allclose(e.frustum_planes().reshape(-1), case["planes"], rtol=1e-5, atol=2e-5)
+        planes = np.array(case["planes"], np.float64).reshape(6, 4)
+        for v in case["is_visible"]:
+            # skip spheres within rounding distance of a plane (the engine's own math differs from glm by ulps)
+            T = np.array(v["transform"], np.float64).reshape(4, 4).T
+            c = (T @ np.append(v["origin"], 1.0))[:3]
+            rad = v["radius"] * np.sqrt((T[:3, :3] ** 2).sum(axis=0)).max()
+            margin = np.abs(planes[:, :3] @ c + planes[:, 3] + rad).min()
+            if margin < 1e-3:
+                continue
+            assert e.is_visible(v["transform"], v["origin"], v["radius"]) == bool(v["visible"])
+            n_vis += 1
         e.close()
+    assert n_vis > 200
 
 
 def test_update_scene_culls_and_sorts(ork_lib):

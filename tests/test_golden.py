@@ -120,14 +120,22 @@ def test_golden_is_current(tmp_path, golden):
     import subprocess
     import sys
     import shutil
-    bak = tmp_path / "golden.json"
+    HOST = os.path.join(ROOT, "tests", "golden", "host_math.json")
+    bak, bak2 = tmp_path / "golden.json", tmp_path / "host.json"
     shutil.copy(GOLDEN, bak)
+    shutil.copy(HOST, bak2)
+    with open(HOST) as f:
+        host_old = json.load(f)
     try:
         subprocess.run([sys.executable, os.path.join(ROOT, "tools", "gen_golden.py")], check=True, capture_output=True)
         with open(GOLDEN) as f:
             fresh = json.load(f)
+        with open(HOST) as f:
+            host_new = json.load(f)
     finally:
         shutil.copy(bak, GOLDEN)
+        shutil.copy(bak2, HOST)
+    assert host_new == host_old
     for key in ("frag", "vert", "shadow_vert", "skybox", "tonemap", "gradient", "brdf"):
         assert len(fresh[key]) == len(golden[key])
         for a, b in zip(fresh[key], golden[key]):

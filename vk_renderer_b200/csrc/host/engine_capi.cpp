@@ -73,5 +73,27 @@ void vke_csm(VulkanEngine* e, float matrices[64], float distances[4]) {
     for (int i = 0; i < NUM_CASCADES; ++i) { std::memcpy(matrices + 16 * i, c.lightMatrices[i].data(), 64); distances[i] = c.planeDistances[i]; }
 }
 float vke_compute_split(float n, float f, int i) { return compute_split(n, f, i); }
+// extract_frustum_planes(proj * view) of the current camera, 6 planes x 4 floats
+void vke_frustum_planes(VulkanEngine* e, float out[24]) {
+    vkm::mat4 v = e->_mainCamera.getViewMatrix();
+    vkm::mat4 p = e->_mainCamera.getProjectionMatrix((float)e->_windowExtent.width / (float)e->_windowExtent.height);
+    Frustum f;
+    extract_frustum_planes(p * v, f);
+    std::memcpy(out, f.planes.data(), 96);
+}
+// is_visible for an object with a sphere bound (origin, radius) under `transform` (column-major), current camera
+int vke_is_visible(VulkanEngine* e, const float transform[16], const float origin[3], float sphereRadius) {
+    vkm::mat4 v = e->_mainCamera.getViewMatrix();
+    vkm::mat4 p = e->_mainCamera.getProjectionMatrix((float)e->_windowExtent.width / (float)e->_windowExtent.height);
+    Frustum f;
+    extract_frustum_planes(p * v, f);
+    MeshAsset mesh;
+    mesh.bounds.origin = {origin[0], origin[1], origin[2]};
+    mesh.bounds.sphereRadius = sphereRadius;
+    RenderObject ro{};
+    ro.mesh = &mesh;
+    std::memcpy(ro.transform.data(), transform, 64);
+    return e->is_visible(ro, f) ? 1 : 0;
+}
 
 }  // extern "C"

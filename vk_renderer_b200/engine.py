@@ -58,6 +58,8 @@ def load_engine() -> C.CDLL:
         lib.vke_light_matrix.argtypes = [p, C.POINTER(C.c_float)]
         lib.vke_csm.argtypes = [p, C.POINTER(C.c_float), C.POINTER(C.c_float)]
         lib.vke_compute_split.argtypes = [C.c_float, C.c_float, C.c_int]; lib.vke_compute_split.restype = C.c_float
+        lib.vke_frustum_planes.argtypes = [p, C.POINTER(C.c_float)]
+        lib.vke_is_visible.argtypes = [p, C.POINTER(C.c_float), C.POINTER(C.c_float), C.c_float]; lib.vke_is_visible.restype = C.c_int
         _engine_lib = lib
     return _engine_lib
 
@@ -165,6 +167,16 @@ class Engine:
         m = (C.c_float * 16)()
         self.lib.vke_light_matrix(self.e, m)
         return np.array(m, np.float32).reshape(4, 4).T
+
+    def frustum_planes(self):
+        out = (C.c_float * 24)()
+        self.lib.vke_frustum_planes(self.e, out)
+        return np.array(out, np.float32).reshape(6, 4)
+
+    def is_visible(self, transform_colmajor, origin, radius) -> bool:
+        t = (C.c_float * 16)(*transform_colmajor)
+        o = (C.c_float * 3)(*origin)
+        return bool(self.lib.vke_is_visible(self.e, t, o, float(radius)))
 
     def csm(self):
         m, d = (C.c_float * 64)(), (C.c_float * 4)()
