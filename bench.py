@@ -285,6 +285,7 @@ def run_b200(args):
         r.sync()
         gk.append(r.timings())
     avg = {k: float(np.mean([g[k] for g in gk])) for k in gk[0]}
+    cull = r.cull_stats()
 
     # ---- e2e: host draw list in, RGBA8 frame out to pinned host memory, every step (FRAME_OVERLAP=2 pipelining)
     pinned = [torch.empty((H, W, 4), dtype=torch.uint8).pin_memory() for _ in range(2)]
@@ -332,6 +333,7 @@ def run_b200(args):
                          "frac": achieved / peak, "traffic": None, "algorithmic_bytes": gk_bytes, "kernel_ms": gk_ms,
                          "peak_source": peak_src},
             "pass_ms": avg,
+            "cluster_culling": cull,
             "e2e": {"value": args.steps / e2e_s, "unit": "frames/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                     "checksum": checksum},
             "gpu_launches": int(launches),

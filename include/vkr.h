@@ -212,6 +212,12 @@ int vkr_device_ptr(VkrDevice* dev, VkrTarget what, void** ptr, size_t* bytes);
 int vkr_launch_count(VkrDevice* dev);
 size_t vkr_upload_bytes(VkrDevice* dev);
 
+/* Cluster culling of the last synced frame: out = {main-pass clusters, of which dropped before any vertex
+ * work (outside the frustum, no pixel centre, or hidden by nearer geometry already drawn), shadow-pass
+ * clusters (last layer), of which dropped}.  The reference's counterpart is the per-object is_visible
+ * test (src/vk_engine_run.cpp:461-480); this one is per 256-triangle cluster and never changes the image. */
+int vkr_cull_stats(VkrDevice* dev, uint32_t out[4]);
+
 const char* vkr_last_error(VkrDevice* dev);
 const char* vkr_version(void);
 

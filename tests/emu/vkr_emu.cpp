@@ -53,6 +53,9 @@ struct EmuDevice {
     float lut[256];
     FramePlan plan;
     std::vector<DChunk> chunks;
+    std::vector<uint2> chunkObj;
+    std::vector<uint32_t> perm;          // passes x clusters
+    uint32_t culled[2] = {0, 0};         // clusters dropped by the cluster test: [0] main, [1] shadow
     VkrEngineStats stats{};
     std::string err;
 };
@@ -60,9 +63,10 @@ struct EmuDevice {
 bool EmuClusters::get(uint32_t mesh, uint32_t firstIndex, uint32_t indexCount, ClusterRange& out) {
     for (auto& e : cache) if (e.first[0] == mesh && e.first[1] == firstIndex && e.first[2] == indexCount) { out = e.second; return true; }
     ClusterData* cd = new ClusterData();
-    build_clusters(d->meshes[mesh].idx + firstIndex, indexCount / 3, d->meshes[mesh].nv, *cd);
+    build_clusters(d->meshes[mesh].idx + firstIndex, indexCount / 3, d->meshes[mesh].nv, d->meshes[mesh].pos, *cd);
     store.push_back(cd);
-    out = ClusterRange{cd->verts.data(), cd->tris.data(), cd->info.data()};
+    out = ClusterRange{cd->verts.data(), cd->tris.data(), cd->orig.data(), cd->info.data(), cd->bounds.data(), {0, 0, 0}, 0};
+    range_sphere(*cd, out);
     cache.push_back({{mesh, firstIndex, indexCount}, out});
     return true;
 }
@@ -194,35 +198,55 @@ int emu_build_material(EmuDevice* d, const VkrMaterialConstants* p, int pass, ui
 
 }  // extern "C"
 
+// geometry_kernel phase 0 (cluster culling), the 8 corner lanes run as a loop
 template <bool SHADOW>
-static void run_pass(EmuDevice* d, const FramePlan& plan, RasterTarget rt, const float* mvps, uint32_t stride, unsigned nChunks) {
+static bool cluster_survives(const DChunk& ch, const float* mvp, const RasterTarget& rt) {
+    CornerAcc a = corner_eval(mvp, ch.bmin, ch.bmax, 0);
+    for (int k = 1; k < 8; ++k) a = corner_merge(a, corner_eval(mvp, ch.bmin, ch.bmax, k));
+    const ClusterRect r = cluster_finalize(a, rt);
+    if (r.verdict == CLUSTER_CULLED) return false;
+    if (r.verdict == CLUSTER_DRAW) return true;
+    for (int32_t py = r.y0; py <= r.y1; ++py)
+        for (int32_t px = r.x0; px <= r.x1; ++px) {
+            const uint32_t stored = SHADOW ? rt.depthBits[(size_t)py * rt.width + px] : (uint32_t)(rt.vis[(size_t)py * rt.width + px] >> 32);
+            if (!depth_hides(stored, r.zminBits)) return true;
+        }
+    return false;
+}
+
+template <bool SHADOW>
+static void run_pass(EmuDevice* d, const FramePlan& plan, RasterTarget rt, const float* mvps, uint32_t stride, unsigned nChunks,
+                     const uint32_t* perm) {
     Queues q{d->ltris.data(), d->litems.data(), d->counters, (uint32_t)d->ltris.size(), (uint32_t)d->litems.size()};
     d->counters[0] = d->counters[1] = d->counters[2] = 0;
     std::vector<CachedVtx> svtx(3 * GEOM_BLOCK);
-    for (unsigned c = 0; c < nChunks; ++c) {                 // geometry_kernel: one CTA per cluster
-        const DChunk ch = d->chunks[c];
+    const AlphaCtx ax{plan.objects.data(), d->chunks.data(), d->materials.data(), d->tex.data()};
+    if (!SHADOW)
+        for (unsigned c = 0; c < nChunks; ++c) {             // geometry_cutout_kernel: natural order, no culling
+            const DChunk ch = d->chunks[c];
+            if (!(ch.flags & 2u)) continue;
+            const DObject& ob = plan.objects[ch.obj];
+            for (uint32_t t = 0; t < (ch.counts >> 16); ++t) {
+                const uint32_t packed = ch.clTris[t];
+                const uint32_t seq = ch.seqBase + ch.clOrig[t];
+                VisSink s{rt.vis, rt.width, 0xFFFFFFFEu - seq};
+                cutout_triangle(ob, ob.mvp, ch.clVerts[packed & 1023u], ch.clVerts[(packed >> 10) & 1023u], ch.clVerts[packed >> 20], seq, rt, q, ax, s);
+            }
+        }
+    for (unsigned slot = 0; slot < nChunks; ++slot) {        // geometry_kernel: one CTA per cluster, in processing order
+        const DChunk ch = d->chunks[perm[slot]];
+        if (!SHADOW && (ch.flags & 2u)) continue;
         const float* mvp = mvps + (size_t)ch.obj * stride;
+        if (!cluster_survives<SHADOW>(ch, mvp, rt)) { d->culled[SHADOW ? 1 : 0]++; continue; }
         const uint32_t nVerts = ch.counts & 0xFFFFu, nTris = ch.counts >> 16;
         const uint32_t* clVerts = ch.clVerts;
-        struct { const float4* pos; } o{ch.pos};
-        const AlphaCtx ax{plan.objects.data(), d->chunks.data(), d->materials.data(), d->tex.data()};
-        if (!SHADOW && (ch.pad[0] & 2u)) {                    // geometry_cutout_kernel
-            const DObject& ob = plan.objects[ch.obj];
-            for (uint32_t t = 0; t < nTris; ++t) {
-                const uint32_t packed = ch.clTris[t];
-                VisSink s{rt.vis, rt.width, 0xFFFFFFFEu - (c * GEOM_BLOCK + t)};
-                cutout_triangle(ob, ob.mvp, clVerts[packed & 1023u], clVerts[(packed >> 10) & 1023u], clVerts[packed >> 20],
-                                c * GEOM_BLOCK + t, rt, q, ax, s);
-            }
-            continue;
-        }
-        for (uint32_t v = 0; v < nVerts; ++v) svtx[v] = cluster_vertex(mvp, o.pos[clVerts[v]], rt);      // phase 1
+        for (uint32_t v = 0; v < nVerts; ++v) svtx[v] = cluster_vertex(mvp, ch.pos[clVerts[v]], rt);     // phase 1
         for (uint32_t t = 0; t < nTris; ++t) {                                                           // phase 2
             const uint32_t packed = ch.clTris[t];
             const uint32_t l0 = packed & 1023u, l1 = (packed >> 10) & 1023u, l2 = packed >> 20;
-            const uint32_t seq = c * GEOM_BLOCK + t;
-            if (SHADOW) { DepthSink s{rt.depthBits, rt.width}; cluster_triangle(svtx[l0], svtx[l1], svtx[l2], mvp, o.pos, clVerts[l0], clVerts[l1], clVerts[l2], 0u, rt, q, s); }
-            else { VisSink s{rt.vis, rt.width, 0xFFFFFFFEu - seq}; cluster_triangle(svtx[l0], svtx[l1], svtx[l2], mvp, o.pos, clVerts[l0], clVerts[l1], clVerts[l2], seq, rt, q, s); }
+            const uint32_t seq = ch.seqBase + ch.clOrig[t];
+            if (SHADOW) { DepthSink s{rt.depthBits, rt.width}; cluster_triangle(svtx[l0], svtx[l1], svtx[l2], mvp, ch.pos, clVerts[l0], clVerts[l1], clVerts[l2], 0u, rt, q, s); }
+            else { VisSink s{rt.vis, rt.width, 0xFFFFFFFEu - seq}; cluster_triangle(svtx[l0], svtx[l1], svtx[l2], mvp, ch.pos, clVerts[l0], clVerts[l1], clVerts[l2], seq, rt, q, s); }
         }
     }
     for (uint32_t i = 0; i < d->counters[1]; ++i) {          // large_raster_kernel
@@ -233,8 +257,7 @@ static void run_pass(EmuDevice* d, const FramePlan& plan, RasterTarget rt, const
             else {
                 VisSink s{rt.vis, rt.width, 0xFFFFFFFEu - lt.seq};
                 const DChunk& ch = d->chunks[lt.seq >> 8];
-                if (ch.pad[0] & 2u) {
-                    const AlphaCtx ax{plan.objects.data(), d->chunks.data(), d->materials.data(), d->tex.data()};
+                if (ch.flags & 2u) {
                     const DObject& ob = plan.objects[ch.obj];
                     const uint32_t tri = ch.firstTri + (lt.seq & 255u);
                     AlphaTri at;
@@ -255,23 +278,34 @@ int emu_draw(EmuDevice* d, const VkrGPUSceneData* scene, const VkrRenderObject* 
     if (!why.empty()) { d->err = why; return VKR_ERROR_INVALID_ARGUMENT; }
     const unsigned nChunks = plan.clusterBase[n];
     d->chunks.resize(nChunks);
+    d->chunkObj.resize(nChunks);
+    const uint32_t passes = 1u + (uint32_t)plan.shadowLayers;
+    d->perm.assign((size_t)passes * nChunks, 0u);
     for (size_t o = 0; o < n; ++o)                            // expand_chunks_kernel
-        for (uint32_t c = plan.clusterBase[o]; c < plan.clusterBase[o + 1]; ++c)
-            d->chunks[c] = make_chunk(plan.objects[o], (uint32_t)o, c - plan.clusterBase[o]);
+        for (uint32_t c = plan.clusterBase[o]; c < plan.clusterBase[o + 1]; ++c) {
+            const uint32_t lc = c - plan.clusterBase[o];
+            d->chunks[c] = make_chunk(plan.objects[o], (uint32_t)o, lc, plan.clusterBase[o]);
+            d->chunkObj[c] = uint2{(uint32_t)o, lc * GEOM_BLOCK};
+            for (uint32_t p = 0; p < passes; ++p) {
+                const uint32_t sb = plan.slotBase[(size_t)p * n + o];
+                if (sb != 0xFFFFFFFFu) d->perm[(size_t)p * nChunks + sb + lc] = c;
+            }
+        }
+    d->culled[0] = d->culled[1] = 0;
     for (int layer = 0; layer < plan.shadowLayers; ++layer) {
         RasterTarget rt = plan.shadowTarget;
         rt.depthBits = d->shadowBits.data() + (size_t)layer * d->S * d->S;
         std::fill(rt.depthBits, rt.depthBits + (size_t)d->S * d->S, DEPTH_ONE_BITS);
-        run_pass<true>(d, plan, rt, plan.shadowMvp.data() + (size_t)layer * n * 16, 16, nChunks);
+        run_pass<true>(d, plan, rt, plan.shadowMvp.data() + (size_t)layer * n * 16, 16, nChunks, d->perm.data() + (size_t)(1 + layer) * nChunks);
     }
     RasterTarget rt = plan.mainTarget;
     rt.vis = d->vis.data();
     std::fill(d->vis.begin(), d->vis.end(), VIS_CLEAR);
     const unsigned opaqueChunks = plan.opaqueClusters;
-    run_pass<false>(d, plan, rt, (const float*)plan.objects.data(), sizeof(DObject) / 4, opaqueChunks);
+    run_pass<false>(d, plan, rt, (const float*)plan.objects.data(), sizeof(DObject) / 4, opaqueChunks, d->perm.data());
     if (d->counters[2]) { d->err = "queue overflow"; return VKR_ERROR_CAPACITY; }
     ShadeBuffers sb{};
-    sb.vis = d->vis.data(); sb.objects = plan.objects.data(); sb.chunks = d->chunks.data();
+    sb.vis = d->vis.data(); sb.objects = plan.objects.data(); sb.chunkObj = d->chunkObj.data();
     sb.materials = d->materials.data(); sb.textures = d->tex.data(); sb.cube = d->haveCube ? d->cube : nullptr;
     sb.shadow = reinterpret_cast<const float*>(d->shadowBits.data());
     sb.hdr = d->hdr.data(); sb.rgba8 = d->rgba8.data(); sb.srgbLut = d->lut;
@@ -292,14 +326,15 @@ int emu_readback(EmuDevice* d, int what, void* dst, size_t bytes) {
                 uint32_t lo = (uint32_t)d->vis[i];
                 if (lo == VIS_EMPTY_LO) { ((uint32_t*)dst)[i] = 0xFFFFFFFFu; continue; }
                 uint32_t seq = 0xFFFFFFFEu - lo;
-                const DChunk ch = d->chunks[seq >> 8];
-                ((uint32_t*)dst)[i] = d->plan.objects[ch.obj].primBase + ch.firstTri + (seq & 255u);
+                const uint2 ch = d->chunkObj[seq >> 8];
+                ((uint32_t*)dst)[i] = d->plan.objects[ch.x].primBase + ch.y + (seq & 255u);
             }
             return 0;
     }
     return -1;
 }
 int emu_stats(EmuDevice* d, VkrEngineStats* out) { *out = d->stats; return 0; }
+void emu_culled(EmuDevice* d, uint32_t out[2]) { out[0] = d->culled[0]; out[1] = d->culled[1]; }
 const char* emu_last_error(EmuDevice* d) { return d->err.c_str(); }
 
 }  // extern "C"

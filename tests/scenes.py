@@ -235,8 +235,34 @@ def cutout(r):
     return sd, np.array(objs), fp
 
 
+def lattice(r, n=4, rings=24, shadow_mode=1):
+    """n^3 instanced spheres seen head-on, submitted back to front (the worst order for the depth test):
+    most of them hidden, partly off-screen — exercises instancing, the front-to-back processing order
+    and the cluster frustum / occlusion culling, which must not change a single pixel."""
+    W, H = r.width, r.height
+    sv, si = mg.uv_sphere(rings, 2 * rings, 1.0)
+    mesh = r.upload_mesh(si, sv)
+    rng = np.random.default_rng(11)
+    mats = [r.build_material(tuple(rng.uniform(0.2, 1.0, 3)) + (1.0,), float(rng.random() < 0.3), float(rng.uniform(0.2, 0.9))) for _ in range(5)]
+    objs = []
+    k = 0
+    for iz in range(n):                      # far layers first
+        for iy in range(n):
+            for ix in range(n):
+                t = mg.translate((ix - (n - 1) / 2) * 2.6, (iy - (n - 1) / 2) * 2.6, (iz - (n - 1) / 2) * 2.6)
+                objs.append(mg.render_object(mesh, mats[k % 5], t, len(si)))
+                k += 1
+    view = mg.camera_view((0.4, 0.8, 3.0 + 1.3 * n), pitch=-0.08)      # close: the outer columns leave the frustum
+    proj = mg.camera_projection(W / H)
+    sd = capi.make_scene_data(view, proj, _lights(4 if shadow_mode == 3 else 1), shadow_mode=shadow_mode, enable_shadows=True,
+                              cascade_distances=(6.0, 12.0, 20.0, 100.0))
+    fp = capi.default_frame_params(enableShadows=1, shadowMode=shadow_mode, enablePostprocess=1)
+    return sd, np.array(objs), fp
+
+
 SCENES = {
     "cutout": cutout,
+    "lattice": lattice,
     "basic_hard": lambda r: basic(r, 0),
     "basic_pcf": lambda r: basic(r, 1),
     "basic_pcss": lambda r: basic(r, 2),

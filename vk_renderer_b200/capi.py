@@ -110,7 +110,7 @@ class EngineStats(C.Structure):
 VKR_SYMBOLS = [
     "create", "destroy", "upload_mesh", "create_image", "update_bindless_texture", "set_cubemap",
     "build_material", "draw", "readback", "readback_async", "sync", "stats", "get_timings",
-    "device_ptr", "launch_count", "upload_bytes", "last_error", "version",
+    "device_ptr", "launch_count", "upload_bytes", "cull_stats", "last_error", "version",
 ]
 
 
@@ -197,6 +197,7 @@ class Renderer:
                 "device_ptr": ([p, C.c_int, C.POINTER(p), C.POINTER(C.c_size_t)], C.c_int),
                 "launch_count": ([p], C.c_int),
                 "upload_bytes": ([p], C.c_size_t),
+                "cull_stats": ([p, C.POINTER(C.c_uint32)], C.c_int),
                 "version": ([], C.c_char_p),
             })
         for name, (args, res) in sigs.items():
@@ -299,6 +300,11 @@ class Renderer:
 
     def launch_count(self) -> int:
         return self._f("launch_count")(self.dev)
+
+    def cull_stats(self) -> dict:
+        out = (C.c_uint32 * 4)()
+        self._check(self._f("cull_stats")(self.dev, out))
+        return {"main_clusters": out[0], "main_culled": out[1], "shadow_clusters": out[2], "shadow_culled": out[3]}
 
     def upload_bytes(self) -> int:
         return self._f("upload_bytes")(self.dev)

@@ -42,16 +42,16 @@ __global__ void fill_u32_kernel(uint32_t* __restrict__ dst, size_t n, uint32_t v
     if (i == 0) for (size_t k = n4 << 2; k < n; ++k) dst[k] = v;
 }
 __global__ void extract_vis_kernel(const uint64_t* __restrict__ vis, uint32_t* __restrict__ out, size_t n, int what,
-                                   const DChunk* __restrict__ chunks, const DObject* __restrict__ objects) {
+                                   const uint2* __restrict__ chunkObj, const DObject* __restrict__ objects) {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     uint64_t k = vis[i];
     if (what == 0) { out[i] = (uint32_t)(k >> 32); return; }                     // depth bits
     uint32_t lo = (uint32_t)k;
     if (lo == VIS_EMPTY_LO) { out[i] = 0xFFFFFFFFu; return; }
-    const uint32_t seq = 0xFFFFFFFEu - lo;                                        // cluster*256 + local triangle
-    const DChunk ch = chunks[seq >> 8];
-    out[i] = objects[ch.obj].primBase + ch.firstTri + (seq & 255u);               // dense submission-order id
+    const uint32_t seq = 0xFFFFFFFEu - lo;                                        // slot*256 + triangle within the slot
+    const uint2 ch = chunkObj[seq >> 8];
+    out[i] = objects[ch.x].primBase + ch.y + (seq & 255u);                        // dense submission-order id
 }
 
 // ---- upload_mesh: AoS Vertex (48 B) -> three float4 streams
@@ -102,36 +102,84 @@ __global__ void mip_blit_kernel(const uchar4* __restrict__ src, int sw, int sh, 
     dst[(size_t)y * dw + x] = o;
 }
 
-// ---- per-frame cluster table, written on the device from the per-draw prefix (one CTA per draw)
+__device__ __forceinline__ uint32_t c3_seq(const uint4* chp) { return __ldg(reinterpret_cast<const uint32_t*>(chp + 3)); }   // DChunk::seqBase
+
+// ---- per-frame cluster table, written on the device from the per-draw prefixes (one CTA per draw):
+// the 96-byte records, the (draw, first triangle) pairs the shading pass looks up through seq >> 8, and for
+// every pass the processing order (geometry CTA slot -> cluster), front to back by draw.
 __global__ void expand_chunks_kernel(const DObject* __restrict__ objects, const uint32_t* __restrict__ clusterBase,
-                                     DChunk* __restrict__ chunks) {
+                                     const uint32_t* __restrict__ slotBase, uint32_t nobj, uint32_t passes, uint32_t permStride,
+                                     DChunk* __restrict__ chunks, uint2* __restrict__ chunkObj, uint32_t* __restrict__ perm) {
     const uint32_t obj = blockIdx.x;
     const uint32_t base = clusterBase[obj], n = clusterBase[obj + 1] - base;
     const DObject& o = objects[obj];
-    for (uint32_t c = threadIdx.x; c < n; c += blockDim.x) chunks[base + c] = make_chunk(o, obj, c);
+    for (uint32_t c = threadIdx.x; c < n; c += blockDim.x) {
+        chunks[base + c] = make_chunk(o, obj, c, base);
+        chunkObj[base + c] = make_uint2(obj, c * GEOM_BLOCK);
+        for (uint32_t p = 0; p < passes; ++p) {
+            const uint32_t sb = slotBase[(size_t)p * nobj + obj];
+            if (sb != 0xFFFFFFFFu) perm[(size_t)p * permStride + sb + c] = base + c;
+        }
+    }
 }
 
 // ---- geometry: one CTA per cluster (<= 256 triangles of one draw).
+// Phase 0 (8 lanes) projects the cluster's bounding box and drops the cluster when it is outside the
+// frustum, holds no pixel centre, or is hidden by what is already in the depth / visibility buffer.
 // Phase 1 transforms each DISTINCT vertex of the cluster once (128-bit position loads) into shared
 // memory as snapped window coordinates; phase 2 runs one thread per triangle on those.
 template <bool SHADOW>
-__global__ void __launch_bounds__(GEOM_BLOCK) geometry_kernel(const DObject* __restrict__ objects, const DChunk* __restrict__ chunks,
+__global__ void __launch_bounds__(GEOM_BLOCK) geometry_kernel(const DChunk* __restrict__ chunks, const uint32_t* __restrict__ perm,
                                                               const float* __restrict__ mvps, uint32_t mvpStride,
                                                               const __grid_constant__ RasterTarget rt, const __grid_constant__ Queues q) {
     __shared__ float s_mvp[16];
     __shared__ uint4 s_vtx[3 * GEOM_BLOCK];
-    // the 48-byte cluster record is everything this CTA needs: one level of indirection
-    const uint4* chp = reinterpret_cast<const uint4*>(chunks + blockIdx.x);
+    __shared__ ClusterRect s_rect;
+    // the 96-byte cluster record is everything this CTA needs: one level of indirection
+    const uint4* chp = reinterpret_cast<const uint4*>(chunks + __ldg(perm + blockIdx.x));
     const uint4 c0 = __ldg(chp), c1 = __ldg(chp + 1), c2 = __ldg(chp + 2);
     const float4* __restrict__ pos = reinterpret_cast<const float4*>(((uint64_t)c0.y << 32) | c0.x);
     const uint32_t* __restrict__ clVerts = reinterpret_cast<const uint32_t*>(((uint64_t)c0.w << 32) | c0.z);
     const uint32_t* __restrict__ clTris = reinterpret_cast<const uint32_t*>(((uint64_t)c1.y << 32) | c1.x);
-    const uint32_t obj = c1.z, counts = c2.x;
-    (void)objects;
-    if (!SHADOW && (c2.y & 2u)) return;     // alpha-tested draw: geometry_cutout_kernel owns this cluster
+    const uint32_t* __restrict__ clOrig = reinterpret_cast<const uint32_t*>(((uint64_t)c1.w << 32) | c1.z);
+    const uint32_t obj = c2.x, counts = c2.z, flags = c2.w;
+    if (!SHADOW && (flags & 2u)) return;     // alpha-tested draw: geometry_cutout_kernel owns this cluster
     if (threadIdx.x < 16) s_mvp[threadIdx.x] = __ldg(mvps + (size_t)obj * mvpStride + threadIdx.x);
-    const uint32_t nVerts = counts & 0xFFFFu, nTris = counts >> 16;
     __syncthreads();
+
+    // ---- phase 0: cluster culling
+    if (threadIdx.x < 32) {
+        const float4 bmin = __ldg(reinterpret_cast<const float4*>(chp + 4)), bmax = __ldg(reinterpret_cast<const float4*>(chp + 5));
+        CornerAcc a = corner_eval(s_mvp, bmin, bmax, threadIdx.x & 7);
+#pragma unroll
+        for (int d = 1; d < 8; d <<= 1) {
+            CornerAcc b;
+            b.xmin = __shfl_xor_sync(0xFFFFFFFFu, a.xmin, d); b.xmax = __shfl_xor_sync(0xFFFFFFFFu, a.xmax, d);
+            b.ymin = __shfl_xor_sync(0xFFFFFFFFu, a.ymin, d); b.ymax = __shfl_xor_sync(0xFFFFFFFFu, a.ymax, d);
+            b.zmin = __shfl_xor_sync(0xFFFFFFFFu, a.zmin, d); b.zmax = __shfl_xor_sync(0xFFFFFFFFu, a.zmax, d);
+            b.outAll = __shfl_xor_sync(0xFFFFFFFFu, a.outAll, d); b.allFront = __shfl_xor_sync(0xFFFFFFFFu, a.allFront, d);
+            a = corner_merge(a, b);
+        }
+        if (threadIdx.x == 0) s_rect = cluster_finalize(a, rt);
+    }
+    __syncthreads();
+    const ClusterRect rect = s_rect;
+    if (rect.verdict == CLUSTER_CULLED) { if (threadIdx.x == 0) atomicAdd(q.counters + 3, 1u); return; }
+    if (rect.verdict == CLUSTER_TEST) {
+        const int32_t w = rect.x1 - rect.x0 + 1, n = w * (rect.y1 - rect.y0 + 1);
+        int hidden = 1;
+        for (int32_t i = threadIdx.x; i < n; i += GEOM_BLOCK) {
+            const int32_t row = i / w, px = rect.x0 + (i - row * w), py = rect.y0 + row;
+            // .cg: read at L2, where the RED.MIN of the other CTAs land (stale L1 lines would only lose culls)
+            uint32_t stored;
+            if (SHADOW) stored = __ldcg(rt.depthBits + (size_t)py * rt.width + px);
+            else stored = __ldcg(reinterpret_cast<const uint32_t*>(rt.vis + (size_t)py * rt.width + px) + 1);
+            hidden &= depth_hides(stored, rect.zminBits) ? 1 : 0;
+        }
+        if (__syncthreads_and(hidden)) { if (threadIdx.x == 0) atomicAdd(q.counters + 3, 1u); return; }
+    }
+
+    const uint32_t nVerts = counts & 0xFFFFu, nTris = counts >> 16;
     for (uint32_t v = threadIdx.x; v < nVerts; v += GEOM_BLOCK) {
         const CachedVtx cv = cluster_vertex(s_mvp, __ldg(pos + __ldg(clVerts + v)), rt);
         s_vtx[v] = make_uint4((uint32_t)cv.X, (uint32_t)cv.Y, cv.zbits, cv.flag);
@@ -144,11 +192,11 @@ __global__ void __launch_bounds__(GEOM_BLOCK) geometry_kernel(const DObject* __r
     const CachedVtx va{(int32_t)a.x, (int32_t)a.y, a.z, a.w}, vb{(int32_t)b.x, (int32_t)b.y, b.z, b.w}, vc{(int32_t)c.x, (int32_t)c.y, c.z, c.w};
     uint32_t g0 = 0, g1 = 0, g2 = 0;
     if (a.w | b.w | c.w) { g0 = __ldg(clVerts + l0); g1 = __ldg(clVerts + l1); g2 = __ldg(clVerts + l2); }
-    const uint32_t seq = blockIdx.x * GEOM_BLOCK + threadIdx.x;
     if (SHADOW) {
         DepthSink sink{rt.depthBits, rt.width};
         cluster_triangle(va, vb, vc, s_mvp, pos, g0, g1, g2, 0u, rt, q, sink);
     } else {
+        const uint32_t seq = c3_seq(chp) + __ldg(clOrig + threadIdx.x);   // submission order, whatever the processing order
         VisSink sink{rt.vis, rt.width, 0xFFFFFFFEu - seq};
         cluster_triangle(va, vb, vc, s_mvp, pos, g0, g1, g2, seq, rt, q, sink);
     }
@@ -160,13 +208,13 @@ __global__ void __launch_bounds__(GEOM_BLOCK) geometry_cutout_kernel(const DObje
                                                                      const __grid_constant__ RasterTarget rt, const __grid_constant__ Queues q,
                                                                      const __grid_constant__ AlphaCtx ax) {
     const DChunk& ch = chunks[blockIdx.x];
-    if (!(ch.pad[0] & 2u)) return;
+    if (!(ch.flags & 2u)) return;
     const uint32_t nTris = ch.counts >> 16;
     if (threadIdx.x >= nTris) return;
     const DObject& o = objects[ch.obj];
     const uint32_t packed = ch.clTris[threadIdx.x];
     const uint32_t g0 = ch.clVerts[packed & 1023u], g1 = ch.clVerts[(packed >> 10) & 1023u], g2 = ch.clVerts[packed >> 20];
-    const uint32_t seq = blockIdx.x * GEOM_BLOCK + threadIdx.x;
+    const uint32_t seq = ch.seqBase + ch.clOrig[threadIdx.x];
     VisSink sink{rt.vis, rt.width, 0xFFFFFFFEu - seq};
     cutout_triangle(o, o.mvp, g0, g1, g2, seq, rt, q, ax, sink);
 }
@@ -186,7 +234,7 @@ __global__ void __launch_bounds__(256) large_raster_kernel(const __grid_constant
             raster_item(lt, it, sink, lane, 32);
         } else {
             VisSink sink{rt.vis, rt.width, 0xFFFFFFFEu - lt.seq};
-            if (anyCutout && (ax.chunks[lt.seq >> 8].pad[0] & 2u)) {
+            if (anyCutout && (ax.chunks[lt.seq >> 8].flags & 2u)) {
                 const DChunk& ch = ax.chunks[lt.seq >> 8];
                 const DObject& o = ax.objects[ch.obj];
                 const uint32_t tri = ch.firstTri + (lt.seq & 255u);
@@ -271,9 +319,12 @@ struct VkrDevice {
         return mesh != o.mesh ? mesh < o.mesh : (first != o.first ? first < o.first : count < o.count); } };
     std::map<RangeKey, ClusterRange> ranges;   // cluster data per (mesh, firstIndex, indexCount), built at first use
     std::vector<std::vector<uint32_t>> meshIndexHost;   // host copy of each mesh's indices (cluster building)
+    std::vector<std::vector<float4>> meshPosHost;       // ... and positions (cluster bounds, Morton order)
     size_t uploadBytes = 0;
 
     DChunk* chunkBuf = nullptr; size_t chunkCap = 0;   // per-frame cluster table (device-written)
+    uint2* chunkObjBuf = nullptr;                      // seq >> 8 -> (draw, first triangle)
+    uint32_t* permBuf = nullptr; size_t permCap = 0;   // (1 + shadow layers) x clusters: processing order per pass
 
     Queues q{};                         // large-triangle queue of the main pass
     Queues qShadow{};                   // ... of the shadow pass (the two passes overlap)
@@ -282,7 +333,7 @@ struct VkrDevice {
     FrameSlot slots[VKR_FRAME_OVERLAP];
     uint64_t frameIndex = 0;
     int lastSlot = 0;
-    const DChunk* lastChunks = nullptr; const DObject* lastObjects = nullptr;
+    const uint2* lastChunkObj = nullptr; const DObject* lastObjects = nullptr;
     FramePlan plan;
 
     cudaEvent_t tev[9] = {nullptr};   // 0 start, 1 uploaded, 3 cleared, 4 geometry kernel, 5 large kernel, 6 shaded; 7,8 shadow pass (shadow stream)
@@ -290,6 +341,7 @@ struct VkrDevice {
     float timings[VKR_T_COUNT] = {0};
 
     VkrEngineStats stats{};
+    uint32_t lastOpaqueClusters = 0, lastShadowClusters = 0;
     int launches = 0;
     std::string err;
 
@@ -318,17 +370,21 @@ struct DeviceClusterProvider : ClusterProvider {
         auto it = dev->ranges.find(key);
         if (it != dev->ranges.end()) { out = it->second; return true; }
         ClusterData cd;
-        build_clusters(dev->meshIndexHost[mesh].data() + firstIndex, indexCount / 3, dev->meshes[mesh].nv, cd);
-        uint32_t *dv = nullptr, *dt = nullptr; uint2* di = nullptr;
+        build_clusters(dev->meshIndexHost[mesh].data() + firstIndex, indexCount / 3, dev->meshes[mesh].nv, dev->meshPosHost[mesh].data(), cd);
+        uint32_t *dv = nullptr, *dt = nullptr, *dorig = nullptr; uint2* di = nullptr; float4* db = nullptr;
         if (dev_alloc(dev, (void**)&dv, cd.verts.size() * 4) || dev_alloc(dev, (void**)&dt, cd.tris.size() * 4) ||
-            dev_alloc(dev, (void**)&di, cd.info.size() * sizeof(uint2)))
+            dev_alloc(dev, (void**)&dorig, cd.orig.size() * 4) || dev_alloc(dev, (void**)&di, cd.info.size() * sizeof(uint2)) ||
+            dev_alloc(dev, (void**)&db, cd.bounds.size() * sizeof(float4)))
             return false;
         bool ok = cudaMemcpyAsync(dv, cd.verts.data(), cd.verts.size() * 4, cudaMemcpyHostToDevice, dev->stream) == cudaSuccess &&
                   cudaMemcpyAsync(dt, cd.tris.data(), cd.tris.size() * 4, cudaMemcpyHostToDevice, dev->stream) == cudaSuccess &&
+                  cudaMemcpyAsync(dorig, cd.orig.data(), cd.orig.size() * 4, cudaMemcpyHostToDevice, dev->stream) == cudaSuccess &&
                   cudaMemcpyAsync(di, cd.info.data(), cd.info.size() * sizeof(uint2), cudaMemcpyHostToDevice, dev->stream) == cudaSuccess &&
+                  cudaMemcpyAsync(db, cd.bounds.data(), cd.bounds.size() * sizeof(float4), cudaMemcpyHostToDevice, dev->stream) == cudaSuccess &&
                   cudaStreamSynchronize(dev->stream) == cudaSuccess;   // cd is a local
         if (!ok) return false;
-        out = ClusterRange{dv, dt, di};
+        out = ClusterRange{dv, dt, dorig, di, db, {0, 0, 0}, 0};
+        range_sphere(cd, out);
         dev->ranges[key] = out;
         return true;
     }
@@ -476,6 +532,11 @@ int vkr_upload_mesh(VkrDevice* dev, const uint32_t* indices, size_t ni, const Vk
     m.pos = pos; m.attrA = aA; m.attrB = aB; m.idx = idx;
     dev->meshes.push_back(m);
     dev->meshIndexHost.emplace_back(indices, indices + ni);
+    {
+        std::vector<float4> hp(nv);
+        for (size_t i = 0; i < nv; ++i) hp[i] = make_float4(vertices[i].position[0], vertices[i].position[1], vertices[i].position[2], 1.0f);
+        dev->meshPosHost.push_back(std::move(hp));
+    }
     *out = (VkrMesh)(dev->meshes.size() - 1);
     return VKR_SUCCESS;
 }
@@ -614,13 +675,19 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
     dev->uploadBytes = 0;
     const size_t szObj = sizeof(DObject) * n, szBase = 4 * (n + 1);
     const unsigned nChunks = plan.clusterBase[n];
-    const size_t szShadow = plan.shadowMvp.size() * 4;
+    const size_t szShadow = plan.shadowMvp.size() * 4, szSlot = plan.slotBase.size() * 4;
+    const uint32_t passes = 1u + (uint32_t)plan.shadowLayers;
     auto align16 = [](size_t v) { return (v + 15) & ~(size_t)15; };
-    const size_t offObj = 0, offBase = align16(offObj + szObj), offShadow = align16(offBase + szBase);
-    const size_t total = align16(offShadow + szShadow) + 16;
+    const size_t offObj = 0, offBase = align16(offObj + szObj), offShadow = align16(offBase + szBase), offSlot = align16(offShadow + szShadow);
+    const size_t total = align16(offSlot + szSlot) + 16;
     if (dev->chunkCap < nChunks) {
         dev->chunkCap = std::max<size_t>((size_t)nChunks * 3 / 2, 1024);
-        ALLOC(dev->chunkBuf, dev->chunkCap * sizeof(DChunk));     // the previous table is freed at destroy
+        ALLOC(dev->chunkBuf, dev->chunkCap * sizeof(DChunk));     // the previous tables are freed at destroy
+        ALLOC(dev->chunkObjBuf, dev->chunkCap * sizeof(uint2));
+    }
+    if (dev->permCap < (size_t)passes * nChunks) {
+        dev->permCap = std::max<size_t>((size_t)passes * nChunks * 3 / 2, 1024);
+        ALLOC(dev->permBuf, dev->permCap * 4);
     }
     if (dev->frameIndex >= VKR_FRAME_OVERLAP) CK(cudaEventSynchronize(slot.uploaded));   // pinned buffer reuse
     int rc = ensure_slot(dev, slot, total);
@@ -629,6 +696,7 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
     if (n) std::memcpy(hp + offObj, plan.objects.data(), szObj);
     std::memcpy(hp + offBase, plan.clusterBase.data(), szBase);
     if (szShadow) std::memcpy(hp + offShadow, plan.shadowMvp.data(), szShadow);
+    if (szSlot) std::memcpy(hp + offSlot, plan.slotBase.data(), szSlot);
     // the upload rides its own stream so it overlaps the previous frame's kernels; the slot's device
     // buffer is free once the frame that last used it (FRAME_OVERLAP frames ago) has rendered
     CK(cudaStreamWaitEvent(dev->upStream, slot.rendered, 0));
@@ -640,7 +708,12 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
     const DObject* dObjects = (const DObject*)(dp + offObj);
     const DChunk* dChunks = dev->chunkBuf;
     const float* dShadowMvp = (const float*)(dp + offShadow);
-    if (n) { expand_chunks_kernel<<<(unsigned)n, 64, 0, st>>>(dObjects, (const uint32_t*)(dp + offBase), dev->chunkBuf); dev->launches += 1; }
+    const uint32_t* dPerm = dev->permBuf;
+    if (n) {
+        expand_chunks_kernel<<<(unsigned)n, 64, 0, st>>>(dObjects, (const uint32_t*)(dp + offBase), (const uint32_t*)(dp + offSlot), (uint32_t)n, passes,
+                                                         nChunks, dev->chunkBuf, dev->chunkObjBuf, dev->permBuf);
+        dev->launches += 1;
+    }
     if (timing) CK(cudaEventRecord(dev->tev[1], st));
 
     const unsigned largeGrid = (unsigned)dev->smCount * 4;
@@ -660,7 +733,7 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
             CK(cudaMemsetAsync(dev->qShadow.counters, 0, 16, ss));
             dev->launches += 1;
             if (nChunks) {
-                geometry_kernel<true><<<nChunks, GEOM_BLOCK, 0, ss>>>(dObjects, dChunks, dShadowMvp + (size_t)layer * n * 16, 16u, rt, dev->qShadow);
+                geometry_kernel<true><<<nChunks, GEOM_BLOCK, 0, ss>>>(dChunks, dPerm + (size_t)(1 + layer) * nChunks, dShadowMvp + (size_t)layer * n * 16, 16u, rt, dev->qShadow);
                 large_raster_kernel<true><<<largeGrid, 256, 0, ss>>>(rt, dev->qShadow, AlphaCtx{}, 0);
                 dev->launches += 2;
             }
@@ -682,7 +755,7 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
         // only the opaque prefix writes depth; transparent draws are blended in a later pass
         const unsigned opaqueChunks = plan.opaqueClusters;
         if (opaqueChunks) {
-            geometry_kernel<false><<<opaqueChunks, GEOM_BLOCK, 0, st>>>(dObjects, dChunks, (const float*)dObjects, (uint32_t)(sizeof(DObject) / 4), rt, dev->q);
+            geometry_kernel<false><<<opaqueChunks, GEOM_BLOCK, 0, st>>>(dChunks, dPerm, (const float*)dObjects, (uint32_t)(sizeof(DObject) / 4), rt, dev->q);
             if (timing) CK(cudaEventRecord(dev->tev[4], st));
             const AlphaCtx ax{dObjects, dChunks, dev->matDev, dev->texDev};
             if (plan.anyCutout) {
@@ -700,7 +773,7 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
     if (plan.shadowLayers) CK(cudaStreamWaitEvent(st, dev->evShadow, 0));   // join: the shader samples the shadow map
     {
         ShadeBuffers sb{};
-        sb.vis = dev->vis; sb.objects = dObjects; sb.chunks = dChunks; sb.materials = dev->matDev;
+        sb.vis = dev->vis; sb.objects = dObjects; sb.chunkObj = dev->chunkObjBuf; sb.materials = dev->matDev;
         sb.textures = dev->texDev; sb.cube = dev->haveCube ? dev->cubeDev : nullptr;
         sb.shadow = reinterpret_cast<const float*>(dev->shadowBits);
         sb.hdr = dev->hdr; sb.rgba8 = dev->rgba8[slotIdx]; sb.srgbLut = dev->lut;
@@ -712,10 +785,12 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
     CK(cudaGetLastError());
     CK(cudaEventRecord(slot.rendered, st));
     dev->lastSlot = slotIdx;
-    dev->lastChunks = dChunks; dev->lastObjects = dObjects;
+    dev->lastChunkObj = dev->chunkObjBuf; dev->lastObjects = dObjects;
     dev->frameIndex++;
     dev->stats.drawcall_count = (int32_t)n;
     dev->stats.triangle_count = (int32_t)plan.totalTris;
+    dev->lastOpaqueClusters = plan.opaqueClusters;
+    dev->lastShadowClusters = plan.shadowLayers ? nChunks : 0;
     return VKR_SUCCESS;
 }
 
@@ -764,7 +839,7 @@ static int do_readback(VkrDevice* dev, VkrTarget what, void* dst, size_t dstByte
         const size_t px = (size_t)dev->W * dev->H;
         if (!dev->scratch) ALLOC(dev->scratch, px * 4);
         extract_vis_kernel<<<(unsigned)((px + 255) / 256), 256, 0, dev->stream>>>(dev->vis, dev->scratch, px, what == VKR_TARGET_DEPTH ? 0 : 1,
-                                                                                    dev->lastChunks, dev->lastObjects);
+                                                                                    dev->lastChunkObj, dev->lastObjects);
         CK(cudaGetLastError());
         CK(cudaMemcpyAsync(dst, dev->scratch, bytes, cudaMemcpyDeviceToHost, dev->stream));
         if (sync) return vkr_sync(dev);
@@ -797,6 +872,13 @@ int vkr_device_ptr(VkrDevice* dev, VkrTarget what, void** ptr, size_t* bytes) {
     const void* src; size_t n;
     if (target_info(dev, what, &src, &n) || !src) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_device_ptr: target has no linear buffer");
     *ptr = const_cast<void*>(src); *bytes = n;
+    return VKR_SUCCESS;
+}
+
+int vkr_cull_stats(VkrDevice* dev, uint32_t out[4]) {
+    if (!dev || !out) return VKR_ERROR_INVALID_ARGUMENT;
+    out[0] = dev->lastOpaqueClusters; out[1] = dev->countersHost[3];
+    out[2] = dev->lastShadowClusters; out[3] = dev->countersHost[7];
     return VKR_SUCCESS;
 }
 

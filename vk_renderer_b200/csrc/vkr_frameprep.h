@@ -50,39 +50,106 @@ inline void camera_position(const float* m, float out[3]) {
     out[2] = (float)(inv14 / det);
 }
 
-// Host-side builder of the per-range cluster data (DObject::clVerts / clTris / clInfo).
+// Host-side builder of the per-range cluster data (DObject::clVerts / clTris / clOrig / clInfo / clBounds).
 struct ClusterData {
     std::vector<uint32_t> verts;     // concatenated distinct-vertex lists
     std::vector<uint32_t> tris;      // nClusters * GEOM_BLOCK packed local ids
+    std::vector<uint32_t> orig;      // nClusters * GEOM_BLOCK submission-order triangle numbers
     std::vector<uint2> info;         // per cluster
+    std::vector<float4> bounds;      // per cluster: min, max
 };
-inline void build_clusters(const uint32_t* idx, uint32_t triCount, uint32_t nv, ClusterData& out) {
+// Spread the low 10 bits of v so that there are two zero bits between each.
+inline uint32_t morton_part(uint32_t v) {
+    v &= 1023u;
+    v = (v | (v << 16)) & 0x030000FFu;
+    v = (v | (v << 8)) & 0x0300F00Fu;
+    v = (v | (v << 4)) & 0x030C30C3u;
+    v = (v | (v << 2)) & 0x09249249u;
+    return v;
+}
+// `pos` are the mesh's positions (x,y,z,1).  Triangles are ordered along a 30-bit Morton curve of their
+// centroids inside the range's bounding box (ties keep submission order), then cut every GEOM_BLOCK.
+inline void build_clusters(const uint32_t* idx, uint32_t triCount, uint32_t nv, const float4* pos, ClusterData& out) {
     const uint32_t nCl = (triCount + GEOM_BLOCK - 1) / GEOM_BLOCK;
-    out.verts.clear(); out.tris.assign((size_t)nCl * GEOM_BLOCK, 0u); out.info.resize(nCl);
+    out.verts.clear(); out.tris.assign((size_t)nCl * GEOM_BLOCK, 0u); out.orig.assign((size_t)nCl * GEOM_BLOCK, 0u);
+    out.info.resize(nCl); out.bounds.resize((size_t)nCl * 2);
+    std::vector<uint32_t> order(triCount);
+    for (uint32_t t = 0; t < triCount; ++t) order[t] = t;
+    if (triCount > (uint32_t)GEOM_BLOCK) {
+        float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+        for (size_t i = 0; i < (size_t)triCount * 3; ++i) {
+            const float4 p = pos[idx[i]];
+            const float c[3] = {p.x, p.y, p.z};
+            for (int k = 0; k < 3; ++k) { lo[k] = std::min(lo[k], c[k]); hi[k] = std::max(hi[k], c[k]); }
+        }
+        float inv[3];
+        for (int k = 0; k < 3; ++k) inv[k] = hi[k] > lo[k] ? 1023.0f / (hi[k] - lo[k]) : 0.0f;
+        std::vector<uint32_t> code(triCount);
+        for (uint32_t t = 0; t < triCount; ++t) {
+            const float4 a = pos[idx[3 * (size_t)t]], b = pos[idx[3 * (size_t)t + 1]], c = pos[idx[3 * (size_t)t + 2]];
+            const float cen[3] = {(a.x + b.x + c.x) * (1.0f / 3.0f), (a.y + b.y + c.y) * (1.0f / 3.0f), (a.z + b.z + c.z) * (1.0f / 3.0f)};
+            uint32_t q[3];
+            for (int k = 0; k < 3; ++k) {
+                float f = (cen[k] - lo[k]) * inv[k];
+                q[k] = !(f > 0.0f) ? 0u : (f >= 1023.0f ? 1023u : (uint32_t)f);      // NaN-safe
+            }
+            code[t] = morton_part(q[0]) | (morton_part(q[1]) << 1) | (morton_part(q[2]) << 2);
+        }
+        std::stable_sort(order.begin(), order.end(), [&](uint32_t x, uint32_t y) { return code[x] < code[y]; });
+    }
     std::vector<uint32_t> stamp(nv, 0xFFFFFFFFu), local(nv, 0u);
     for (uint32_t c = 0; c < nCl; ++c) {
         const uint32_t t0 = c * GEOM_BLOCK, t1 = std::min(triCount, t0 + GEOM_BLOCK);
         const uint32_t off = (uint32_t)out.verts.size();
         uint32_t count = 0;
-        for (uint32_t t = t0; t < t1; ++t) {
+        float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+        for (uint32_t s = t0; s < t1; ++s) {
+            const uint32_t t = order[s];
             uint32_t l[3];
             for (int k = 0; k < 3; ++k) {
                 const uint32_t v = idx[3 * (size_t)t + k];
-                if (stamp[v] != c) { stamp[v] = c; local[v] = count++; out.verts.push_back(v); }
+                if (stamp[v] != c) {
+                    stamp[v] = c; local[v] = count++; out.verts.push_back(v);
+                    const float4 p = pos[v];
+                    const float pc[3] = {p.x, p.y, p.z};
+                    for (int a = 0; a < 3; ++a) { lo[a] = std::min(lo[a], pc[a]); hi[a] = std::max(hi[a], pc[a]); }
+                }
                 l[k] = local[v];
             }
-            out.tris[(size_t)c * GEOM_BLOCK + (t - t0)] = l[0] | (l[1] << 10) | (l[2] << 20);
+            out.tris[(size_t)c * GEOM_BLOCK + (s - t0)] = l[0] | (l[1] << 10) | (l[2] << 20);
+            out.orig[(size_t)c * GEOM_BLOCK + (s - t0)] = t;
         }
         out.info[c] = uint2{off, count | ((t1 - t0) << 16)};
+        // (positions are required to be finite; min/max skip NaNs)
+        out.bounds[2 * (size_t)c] = make_float4(lo[0], lo[1], lo[2], 0.0f);
+        out.bounds[2 * (size_t)c + 1] = make_float4(hi[0], hi[1], hi[2], 0.0f);
     }
 }
 
-struct ClusterRange { const uint32_t* verts; const uint32_t* tris; const uint2* info; };
+struct ClusterRange {
+    const uint32_t* verts; const uint32_t* tris; const uint32_t* orig; const uint2* info; const float4* bounds;
+    float center[3], radius;          // bounding sphere of the whole range (object space), for the processing order
+};
 // Implemented by the owner of the device (or emulated) memory: returns the cached range, building it on first use.
 struct ClusterProvider {
     virtual ~ClusterProvider() {}
     virtual bool get(uint32_t mesh, uint32_t firstIndex, uint32_t indexCount, ClusterRange& out) = 0;
 };
+inline void range_sphere(const ClusterData& cd, ClusterRange& r) {
+    float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    for (size_t c = 0; c + 1 < cd.bounds.size(); c += 2) {
+        const float4 a = cd.bounds[c], b = cd.bounds[c + 1];
+        lo[0] = std::min(lo[0], a.x); lo[1] = std::min(lo[1], a.y); lo[2] = std::min(lo[2], a.z);
+        hi[0] = std::max(hi[0], b.x); hi[1] = std::max(hi[1], b.y); hi[2] = std::max(hi[2], b.z);
+    }
+    float r2 = 0.0f;
+    for (int k = 0; k < 3; ++k) {
+        r.center[k] = std::isfinite(lo[k]) && std::isfinite(hi[k]) ? 0.5f * (lo[k] + hi[k]) : 0.0f;
+        const float e = std::isfinite(lo[k]) && std::isfinite(hi[k]) ? 0.5f * (hi[k] - lo[k]) : 0.0f;
+        r2 += e * e;
+    }
+    r.radius = std::sqrt(r2);
+}
 
 struct FramePlan {
     std::vector<DObject> objects;
@@ -91,6 +158,12 @@ struct FramePlan {
     uint32_t opaqueClusters = 0;        // clusters of the opaque prefix
     bool anyCutout = false;             // some draw needs the raster-stage alpha test
     std::vector<float> shadowMvp;       // layers * nobj * 16
+    // Processing order (front to back, so the cluster occlusion test finds the occluders already drawn):
+    // slotBase[p*nobj + i] = first geometry-CTA slot of draw i in pass p (0 = main, 1.. = shadow layers),
+    // 0xFFFFFFFF when the draw is not part of the pass.  Primitive ids do not depend on it.
+    std::vector<uint32_t> slotBase;
+    std::vector<std::pair<float, uint32_t>> sortScratch;
+    std::vector<float> sphereScratch;
     int shadowLayers = 0;
     uint32_t totalTris = 0;
     uint32_t opaqueCount = 0;           // objects [0, opaqueCount) are MainColor, the rest Transparent
@@ -111,6 +184,8 @@ inline std::string plan_frame(const VkrGPUSceneData* scene, const VkrRenderObjec
     plan.shadowMvp.resize((size_t)plan.shadowLayers * n * 16);
     uint64_t prim = 0;
     bool seenTransparent = false;
+    std::vector<float>& sphere = plan.sphereScratch;
+    sphere.resize(4 * n + 4);
     plan.opaqueCount = (uint32_t)n;
     plan.anyCutout = false;
     for (size_t i = 0; i < n; ++i) {
@@ -129,10 +204,12 @@ inline std::string plan_frame(const VkrGPUSceneData* scene, const VkrRenderObjec
         o.pos = m.pos; o.attrA = m.attrA; o.attrB = m.attrB;
         o.idx = m.idx + ro.firstIndex;
         o.triCount = ro.indexCount / 3;
-        ClusterRange cr{nullptr, nullptr, nullptr};
+        ClusterRange cr{};
         if (o.triCount && !clusters.get(ro.mesh, ro.firstIndex, ro.indexCount, cr)) return "out of memory building clusters";
-        o.clVerts = cr.verts; o.clTris = cr.tris; o.clInfo = cr.info;
+        o.clVerts = cr.verts; o.clTris = cr.tris; o.clOrig = cr.orig; o.clInfo = cr.info; o.clBounds = cr.bounds;
         o.pad[0] = o.pad[1] = 0;
+        // bounding sphere of the draw's range (object space): sort key of the processing order below
+        sphere[4 * i] = cr.center[0]; sphere[4 * i + 1] = cr.center[1]; sphere[4 * i + 2] = cr.center[2]; sphere[4 * i + 3] = cr.radius;
         o.primBase = (uint32_t)prim;
         o.material = ro.material;
         o.flags = transparent ? 1u : 0u;
@@ -152,6 +229,32 @@ inline std::string plan_frame(const VkrGPUSceneData* scene, const VkrRenderObjec
     plan.primBase[n] = (uint32_t)prim;
     plan.clusterBase[n] = (uint32_t)ncl;
     plan.totalTris = (uint32_t)prim;
+
+    // ---- processing order per pass
+    plan.slotBase.assign((size_t)(1 + plan.shadowLayers) * n, 0xFFFFFFFFu);
+    for (int p = 0; p <= plan.shadowLayers; ++p) {
+        auto& keys = plan.sortScratch;
+        keys.clear();
+        const size_t cnt = p == 0 ? plan.opaqueCount : n;
+        for (size_t i = 0; i < cnt; ++i) {
+            const DObject& o = plan.objects[i];
+            const float cx = sphere[4 * i], cy = sphere[4 * i + 1], cz = sphere[4 * i + 2], rad = sphere[4 * i + 3];
+            const float* m = p == 0 ? o.mvp : &plan.shadowMvp[((size_t)(p - 1) * n + i) * 16];
+            // main pass: clip w (view depth); shadow pass (orthographic light): clip z
+            const int r = p == 0 ? 3 : 2;
+            const float d = m[r] * cx + m[4 + r] * cy + m[8 + r] * cz + m[12 + r];
+            const float ext = rad * std::sqrt(m[r] * m[r] + m[4 + r] * m[4 + r] + m[8 + r] * m[8 + r]);
+            float key = d - ext;
+            if (!(key == key)) key = 0.0f;
+            keys.emplace_back(key, (uint32_t)i);
+        }
+        std::stable_sort(keys.begin(), keys.end(), [](const std::pair<float, uint32_t>& a, const std::pair<float, uint32_t>& b) { return a.first < b.first; });
+        uint32_t slot = 0;
+        for (const auto& k : keys) {
+            plan.slotBase[(size_t)p * n + k.second] = slot;
+            slot += plan.clusterBase[k.second + 1] - plan.clusterBase[k.second];
+        }
+    }
 
     ShadeConst& sc = plan.sc;
     sc.scene = *scene;

@@ -57,42 +57,55 @@ struct DObject {
     const uint32_t* idx;      // already offset by firstIndex
     const uint32_t* clVerts;  // cluster data of this draw's index range (see ClusterRange)
     const uint32_t* clTris;
+    const uint32_t* clOrig;
     const uint2* clInfo;
+    const float4* clBounds;
     uint32_t triCount;
     uint32_t primBase;        // dense submission-order id of this draw's first triangle (readback only)
     uint32_t material;
     uint32_t flags;           // bit0: transparent pass, bit1: alpha-tested (albedo texture has alpha < 0.5)
     uint32_t pad[2];
 };
+static_assert(sizeof(DObject) % 16 == 0, "DObject array is read with 16-byte loads");
 
-// One cluster = GEOM_BLOCK consecutive triangles of one draw.  Cluster k of the frame owns the
-// primitive sequence numbers [k*256, k*256+255]: seq order == submission order.
-// The host uploads only the per-draw cluster prefix; expand_chunks_kernel writes this table on the
-// device with everything the geometry CTA needs in one 48-byte record (no dependent loads).
-struct DChunk {
+// Cluster data, built once per (mesh, firstIndex, indexCount) at first use (build_clusters):
+// the draw's triangles are sorted along a Morton curve of their centroids and cut into clusters of
+// <= GEOM_BLOCK triangles, so a cluster is a compact surface patch with a tight bounding box.
+//   clInfo[c]          = (offset of the cluster's first entry in clVerts, vertexCount | triCount << 16)
+//   clVerts[...]       = the cluster's distinct mesh vertices
+//   clTris[c*256 + t]  = l0 | l1 << 10 | l2 << 20   (local vertex ids)
+//   clOrig[c*256 + t]  = the triangle's index in the draw's index range (submission order)
+//   clBounds[2c, 2c+1] = object-space AABB (min.xyz, max.xyz) of the cluster's vertices
+//
+// Primitive sequence numbers stay in SUBMISSION order whatever the processing order: a draw owns
+// the numbers [clusterBase*256, ...) and triangle t of the draw is clusterBase*256 + t, so
+// seq >> 8 indexes the frame's chunk table and later primitives win equal-depth ties.
+struct DChunk {               // what one geometry CTA needs, written on the device by expand_chunks_kernel
     const float4* pos;        // mesh positions
     const uint32_t* clVerts;  // this cluster's distinct-vertex list
     const uint32_t* clTris;   // this cluster's packed triangles
-    uint32_t obj, firstTri;
+    const uint32_t* clOrig;   // ... and their submission-order triangle numbers
+    uint32_t obj, firstTri;   // firstTri: cluster slot * 256 (used through seq >> 8 by the shading pass)
     uint32_t counts;          // vertexCount | triCount << 16
+    uint32_t flags;           // draw flags (bit0 transparent, bit1 alpha-tested)
+    uint32_t seqBase;         // first sequence number of the draw
     uint32_t pad[3];
+    float4 bmin, bmax;        // object-space bounding box of the cluster
 };
-static_assert(sizeof(DChunk) == 48, "DChunk is read as three 16-byte words");
-// Cluster c of draw `obj` (what expand_chunks_kernel writes).
-VKR_HD DChunk make_chunk(const DObject& o, uint32_t obj, uint32_t c) {
+static_assert(sizeof(DChunk) == 96, "DChunk is read as six 16-byte words");
+// Cluster c of draw `obj` whose first frame cluster slot is `base`.
+VKR_HD DChunk make_chunk(const DObject& o, uint32_t obj, uint32_t c, uint32_t base) {
     const uint2 info = o.clInfo[c];
     DChunk ch;
     ch.pos = o.pos; ch.clVerts = o.clVerts + info.x; ch.clTris = o.clTris + (size_t)c * GEOM_BLOCK;
+    ch.clOrig = o.clOrig + (size_t)c * GEOM_BLOCK;
     ch.obj = obj; ch.firstTri = c * GEOM_BLOCK; ch.counts = info.y;
-    ch.pad[0] = o.flags;      // draw flags (bit0 transparent, bit1 alpha-tested) ride along for the geometry CTA
-    ch.pad[1] = ch.pad[2] = 0;
+    ch.flags = o.flags;
+    ch.seqBase = base * GEOM_BLOCK;
+    ch.pad[0] = ch.pad[1] = ch.pad[2] = 0;
+    ch.bmin = o.clBounds[2 * c]; ch.bmax = o.clBounds[2 * c + 1];
     return ch;
 }
-
-// Built once per (mesh, firstIndex, indexCount) at first use: for every cluster the list of
-// distinct mesh vertices it references and, per triangle, three 10-bit local ids.
-//   clInfo[c] = (offset of the cluster's first entry in clVerts, vertexCount | triCount << 16)
-//   clTris[c*256 + t] = l0 | l1 << 10 | l2 << 20
 
 struct DMaterial {
     float colorFactors[4];
@@ -119,7 +132,7 @@ struct LargeItem { uint32_t tri; uint16_t tx, ty; };   // (triangle, 64x64 tile)
 struct Queues {
     LargeTri* tris;
     LargeItem* items;
-    uint32_t* counters;       // [0] tri count, [1] item count, [2] overflow flag
+    uint32_t* counters;       // [0] tri count, [1] item count, [2] overflow flag, [3] clusters culled
     uint32_t triCap, itemCap;
 };
 
@@ -156,7 +169,7 @@ struct ShadeConst {
 struct ShadeBuffers {
     const uint64_t* vis;
     const DObject* objects;
-    const DChunk* chunks;              // frame cluster table: seq >> 8 -> cluster record
+    const uint2* chunkObj;             // frame cluster slots: seq >> 8 -> (draw, first triangle of the slot)
     const DMaterial* materials;
     const DTexture* textures;          // VKR_MAX_BINDLESS slots
     const DTexture* cube;              // 6 faces (nullptr when no cubemap)

@@ -368,6 +368,97 @@ VKR_HD void cluster_triangle(const CachedVtx& a, const CachedVtx& b, const Cache
     if (setup_snapped(v0, v1, v2, rt, t)) emit_setup(t, seq, q, sink);
 }
 
+// ---- cluster culling --------------------------------------------------------------------------
+// Before a geometry CTA transforms anything it projects the 8 corners of its cluster's object-space
+// bounding box and drops the cluster when no fragment of it can survive:
+//   (1) every corner outside one frustum plane  -> all triangles are clipped away or scissored;
+//   (2) the projected rectangle holds no pixel centre inside the scissor;
+//   (3) every pixel of that rectangle already stores a depth nearer than the nearest the cluster can
+//       produce (occlusion against the live depth / visibility buffer; draws are processed front to back).
+// All three are conservative, so the image is identical with and without them.  Rigour: x, y, z and w
+// are affine in the object-space position, so over the box they are bounded by their corner values,
+// and x/w, y/w, z/w (linear-fractional, w > 0) too.  The corners are evaluated in floating point like
+// the vertices; both are within 3 roundings of the exact affine value, |err| <= 3*2^-24*mag with
+// mag = sum |m_i * p_i|; the margins below use 2^-20*mag (>5x that bound, both sides) plus the
+// 1/512 px vertex snap.  Depth written by the rasteriser is the triangle's plane evaluated at a covered
+// sample (inside the triangle), so it lies in the vertex depth range up to the rounding of the plane
+// evaluation; a quarter of the cluster's own depth range plus 2^-19 is subtracted for that.
+struct CornerAcc {
+    float xmin, xmax, ymin, ymax;   // NDC bounds, already widened by the margins (valid when allFront)
+    float zmin, zmax;               // depth bounds (valid when allFront)
+    uint32_t outAll;                // bit p set: every corner is outside frustum plane p by more than the margin
+    uint32_t allFront;              // every corner has w safely > 0
+};
+static const float CULL_EPS = 9.5367431640625e-07f;   // 2^-20
+
+VKR_HD CornerAcc corner_eval(const float* __restrict__ m, float4 bmin, float4 bmax, int corner) {
+    const float px = (corner & 1) ? bmax.x : bmin.x, py = (corner & 2) ? bmax.y : bmin.y, pz = (corner & 4) ? bmax.z : bmin.z;
+    const float4 c = transform_point(m, px, py, pz);
+    const float ax = fabsf(px), ay = fabsf(py), az = fabsf(pz);
+    const float ex = CULL_EPS * (fabsf(m[0]) * ax + fabsf(m[4]) * ay + fabsf(m[8]) * az + fabsf(m[12]));
+    const float ey = CULL_EPS * (fabsf(m[1]) * ax + fabsf(m[5]) * ay + fabsf(m[9]) * az + fabsf(m[13]));
+    const float ez = CULL_EPS * (fabsf(m[2]) * ax + fabsf(m[6]) * ay + fabsf(m[10]) * az + fabsf(m[14]));
+    const float ew = CULL_EPS * (fabsf(m[3]) * ax + fabsf(m[7]) * ay + fabsf(m[11]) * az + fabsf(m[15]));
+    CornerAcc a;
+    uint32_t out = 0;
+    if (c.x + c.w < -(ex + ew)) out |= 1u;
+    if (c.x - c.w > (ex + ew)) out |= 2u;
+    if (c.y + c.w < -(ey + ew)) out |= 4u;
+    if (c.y - c.w > (ey + ew)) out |= 8u;
+    if (c.z < -ez) out |= 16u;
+    if (c.z - c.w > (ez + ew)) out |= 32u;
+    a.outAll = out;
+    const bool front = c.w > 2.0f * ew && c.w > 1e-30f;
+    a.allFront = front ? 1u : 0u;
+    if (front) {
+        const float rw = 1.0f / (c.w - ew);           // >= 1/w_exact
+        const float xn = c.x / c.w, yn = c.y / c.w, zn = c.z / c.w;
+        const float mx = (ex + fabsf(xn) * ew) * rw * 2.0f, my = (ey + fabsf(yn) * ew) * rw * 2.0f, mz = (ez + fabsf(zn) * ew) * rw * 2.0f;
+        a.xmin = xn - mx; a.xmax = xn + mx; a.ymin = yn - my; a.ymax = yn + my; a.zmin = zn - mz; a.zmax = zn + mz;
+    } else {
+        a.xmin = a.ymin = a.zmin = 0.0f; a.xmax = a.ymax = a.zmax = 0.0f;
+    }
+    return a;
+}
+VKR_HD CornerAcc corner_merge(const CornerAcc& a, const CornerAcc& b) {
+    CornerAcc r;
+    r.xmin = fminf(a.xmin, b.xmin); r.xmax = fmaxf(a.xmax, b.xmax);
+    r.ymin = fminf(a.ymin, b.ymin); r.ymax = fmaxf(a.ymax, b.ymax);
+    r.zmin = fminf(a.zmin, b.zmin); r.zmax = fmaxf(a.zmax, b.zmax);
+    r.outAll = a.outAll & b.outAll;
+    r.allFront = a.allFront & b.allFront;
+    return r;
+}
+
+static const int CLUSTER_DRAW = 1, CLUSTER_CULLED = 0, CLUSTER_TEST = 2;
+static const int OCC_MAX_PIXELS = 2048;      // occlusion test only when the rectangle is at most this many pixels
+struct ClusterRect { int32_t x0, y0, x1, y1; uint32_t zminBits; int32_t verdict; };
+
+VKR_HD ClusterRect cluster_finalize(const CornerAcc& a, const RasterTarget& rt) {
+    ClusterRect r;
+    r.x0 = rt.sx0; r.y0 = rt.sy0; r.x1 = rt.sx1 - 1; r.y1 = rt.sy1 - 1; r.zminBits = 0u;
+    if (a.outAll) { r.verdict = CLUSTER_CULLED; return r; }
+    if (!a.allFront) { r.verdict = CLUSTER_DRAW; return r; }
+    // pixel i is sampled at i + 0.5; a covered sample lies within the widened bounds (+ the snap of 1/512 px)
+    const float snap = 0.004f;
+    const float fx0 = fmaf(a.xmin, rt.halfW, rt.halfW) - snap - 0.5f, fx1 = fmaf(a.xmax, rt.halfW, rt.halfW) + snap - 0.5f;
+    const float fy0 = fmaf(a.ymin, rt.halfH, rt.halfH) - snap - 0.5f, fy1 = fmaf(a.ymax, rt.halfH, rt.halfH) + snap - 0.5f;
+    // NaN-safe clamps: fmaxf/fminf return the non-NaN operand, which is the scissor bound (= widest rectangle)
+    const float cx0 = fminf(fmaxf(ceilf(fx0), (float)rt.sx0), (float)rt.sx1), cx1 = fmaxf(fminf(floorf(fx1), (float)(rt.sx1 - 1)), (float)rt.sx0 - 1.0f);
+    const float cy0 = fminf(fmaxf(ceilf(fy0), (float)rt.sy0), (float)rt.sy1), cy1 = fmaxf(fminf(floorf(fy1), (float)(rt.sy1 - 1)), (float)rt.sy0 - 1.0f);
+    r.x0 = (int32_t)cx0; r.x1 = (int32_t)cx1; r.y0 = (int32_t)cy0; r.y1 = (int32_t)cy1;
+    if (r.x0 > r.x1 || r.y0 > r.y1) { r.verdict = CLUSTER_CULLED; return r; }
+    if ((int64_t)(r.x1 - r.x0 + 1) * (r.y1 - r.y0 + 1) > OCC_MAX_PIXELS) { r.verdict = CLUSTER_DRAW; return r; }
+    float z = a.zmin - (0.25f * (a.zmax - a.zmin) + 1.9073486328125e-06f);
+    if (!(z > 0.0f)) { r.verdict = CLUSTER_DRAW; return r; }        // reaches depth 0 (or NaN): nothing can hide it
+    if (z > 1.0f) z = 1.0f;
+    r.zminBits = f2bits(z);
+    r.verdict = CLUSTER_TEST;
+    return r;
+}
+// A stored depth hides the cluster at that pixel iff it is strictly nearer than anything the cluster can write.
+VKR_HD bool depth_hides(uint32_t storedBits, uint32_t zminBits) { return storedBits < zminBits; }
+
 // ---- alpha test in the raster stage ---------------------------------------------------------
 // mesh_pbr.frag / mesh.frag `discard` fragments whose albedo alpha < 0.5 (shaders/mesh_pbr.frag:193):
 // such fragments must not write depth, so for draws whose albedo texture has any texel alpha < 0.5 the

@@ -388,8 +388,8 @@ VKR_HD float4 xform(const float* m, float4 p) {
 // Rebuild the fragment of primitive `seq` at pixel (px,py) from the SoA vertex streams.
 VKR_HD void fetch_fragment(const ShadeConst& sc, const ShadeBuffers& sb, uint32_t seq, int px, int py,
                            Fragment& fr, uint32_t& material) {
-    // cluster table: seq >> 8 -> (draw, first triangle of the cluster)
-    const uint2 ch = VKR_LDG(reinterpret_cast<const uint2*>(&sb.chunks[seq >> 8].obj));   // (obj, firstTri)
+    // cluster slots: seq >> 8 -> (draw, first triangle of the slot); seq is in submission order
+    const uint2 ch = VKR_LDG(sb.chunkObj + (seq >> 8));
     const DObject& o = sb.objects[ch.x];
     const uint32_t tri = ch.y + (seq & 255u);
     material = o.material;
