@@ -49,6 +49,7 @@ struct EmuDevice {
     std::vector<uint32_t> shadowBits;
     std::vector<uint16_t> hdr;
     std::vector<uint32_t> rgba8;
+    std::vector<float> accum;
     std::vector<LargeTri> ltris; std::vector<LargeItem> litems; uint32_t counters[4];
     float lut[256];
     FramePlan plan;
@@ -65,7 +66,7 @@ bool EmuClusters::get(uint32_t mesh, uint32_t firstIndex, uint32_t indexCount, C
     ClusterData* cd = new ClusterData();
     build_clusters(d->meshes[mesh].idx + firstIndex, indexCount / 3, d->meshes[mesh].nv, d->meshes[mesh].pos, *cd);
     store.push_back(cd);
-    out = ClusterRange{cd->verts.data(), cd->tris.data(), cd->orig.data(), cd->info.data(), cd->bounds.data(), {0, 0, 0}, 0};
+    out = ClusterRange{cd->verts.data(), cd->tris.data(), cd->orig.data(), cd->info.data(), cd->bounds.data(), 0u, {0, 0, 0}, 0};
     range_sphere(*cd, out);
     cache.push_back({{mesh, firstIndex, indexCount}, out});
     return true;
@@ -214,14 +215,16 @@ static bool cluster_survives(const DChunk& ch, const float* mvp, const RasterTar
     return false;
 }
 
-template <bool SHADOW>
+// PASS: 0 main, 1 shadow, 2 transparent (clusters [first, first + nChunks) in natural order, BlendSink)
+template <int PASS>
 static void run_pass(EmuDevice* d, const FramePlan& plan, RasterTarget rt, const float* mvps, uint32_t stride, unsigned nChunks,
-                     const uint32_t* perm) {
+                     const uint32_t* perm, unsigned first = 0, const ShadeBuffers* sbT = nullptr) {
+    const bool SHADOW = PASS == 1;
     Queues q{d->ltris.data(), d->litems.data(), d->counters, (uint32_t)d->ltris.size(), (uint32_t)d->litems.size()};
     d->counters[0] = d->counters[1] = d->counters[2] = 0;
-    std::vector<CachedVtx> svtx(3 * GEOM_BLOCK);
-    const AlphaCtx ax{plan.objects.data(), d->chunks.data(), d->materials.data(), d->tex.data()};
-    if (!SHADOW)
+    std::vector<CachedVtx> svtx(CL_VERTS);
+    const AlphaCtx ax{plan.objects.data(), d->chunkObj.data(), d->materials.data(), d->tex.data()};
+    if (PASS == 0)
         for (unsigned c = 0; c < nChunks; ++c) {             // geometry_cutout_kernel: natural order, no culling
             const DChunk ch = d->chunks[c];
             if (!(ch.flags & 2u)) continue;
@@ -230,22 +233,23 @@ static void run_pass(EmuDevice* d, const FramePlan& plan, RasterTarget rt, const
                 const uint32_t packed = ch.clTris[t];
                 const uint32_t seq = ch.seqBase + ch.clOrig[t];
                 VisSink s{rt.vis, rt.width, 0xFFFFFFFEu - seq};
-                cutout_triangle(ob, ob.mvp, ch.clVerts[packed & 1023u], ch.clVerts[(packed >> 10) & 1023u], ch.clVerts[packed >> 20], seq, rt, q, ax, s);
+                cutout_triangle(ob, ob.mvp, ch.clVerts[packed & 127u], ch.clVerts[(packed >> 7) & 127u], ch.clVerts[(packed >> 14) & 127u], seq, rt, q, ax, s);
             }
         }
     for (unsigned slot = 0; slot < nChunks; ++slot) {        // geometry_kernel: one CTA per cluster, in processing order
-        const DChunk ch = d->chunks[perm[slot]];
-        if (!SHADOW && (ch.flags & 2u)) continue;
+        const DChunk ch = d->chunks[perm ? perm[slot] : first + slot];
+        if (PASS == 0 && (ch.flags & 2u)) continue;
         const float* mvp = mvps + (size_t)ch.obj * stride;
-        if (!cluster_survives<SHADOW>(ch, mvp, rt)) { d->culled[SHADOW ? 1 : 0]++; continue; }
+        if (!cluster_survives<PASS == 1>(ch, mvp, rt)) { d->culled[SHADOW ? 1 : 0]++; continue; }
         const uint32_t nVerts = ch.counts & 0xFFFFu, nTris = ch.counts >> 16;
         const uint32_t* clVerts = ch.clVerts;
         for (uint32_t v = 0; v < nVerts; ++v) svtx[v] = cluster_vertex(mvp, ch.pos[clVerts[v]], rt);     // phase 1
         for (uint32_t t = 0; t < nTris; ++t) {                                                           // phase 2
             const uint32_t packed = ch.clTris[t];
-            const uint32_t l0 = packed & 1023u, l1 = (packed >> 10) & 1023u, l2 = packed >> 20;
+            const uint32_t l0 = packed & 127u, l1 = (packed >> 7) & 127u, l2 = (packed >> 14) & 127u;
             const uint32_t seq = ch.seqBase + ch.clOrig[t];
-            if (SHADOW) { DepthSink s{rt.depthBits, rt.width}; cluster_triangle(svtx[l0], svtx[l1], svtx[l2], mvp, ch.pos, clVerts[l0], clVerts[l1], clVerts[l2], 0u, rt, q, s); }
+            if (PASS == 1) { DepthSink s{rt.depthBits, rt.width}; cluster_triangle(svtx[l0], svtx[l1], svtx[l2], mvp, ch.pos, clVerts[l0], clVerts[l1], clVerts[l2], 0u, rt, q, s); }
+            else if (PASS == 2) { BlendSink s{&plan.sc, sbT, seq}; cluster_triangle(svtx[l0], svtx[l1], svtx[l2], mvp, ch.pos, clVerts[l0], clVerts[l1], clVerts[l2], seq, rt, q, s); }
             else { VisSink s{rt.vis, rt.width, 0xFFFFFFFEu - seq}; cluster_triangle(svtx[l0], svtx[l1], svtx[l2], mvp, ch.pos, clVerts[l0], clVerts[l1], clVerts[l2], seq, rt, q, s); }
         }
     }
@@ -253,13 +257,14 @@ static void run_pass(EmuDevice* d, const FramePlan& plan, RasterTarget rt, const
         const LargeItem it = q.items[i];
         const LargeTri lt = q.tris[it.tri];
         for (int lane = 0; lane < 32; ++lane) {
-            if (SHADOW) { DepthSink s{rt.depthBits, rt.width}; raster_item(lt, it, s, lane, 32); }
+            if (PASS == 1) { DepthSink s{rt.depthBits, rt.width}; raster_item(lt, it, s, lane, 32); }
+            else if (PASS == 2) { BlendSink s{&plan.sc, sbT, lt.seq}; raster_item(lt, it, s, lane, 32); }
             else {
                 VisSink s{rt.vis, rt.width, 0xFFFFFFFEu - lt.seq};
-                const DChunk& ch = d->chunks[lt.seq >> 8];
-                if (ch.flags & 2u) {
-                    const DObject& ob = plan.objects[ch.obj];
-                    const uint32_t tri = ch.firstTri + (lt.seq & 255u);
+                const uint2 co = d->chunkObj[lt.seq >> 8];
+                if (plan.objects[co.x].flags & 2u) {
+                    const DObject& ob = plan.objects[co.x];
+                    const uint32_t tri = co.y + (lt.seq & 255u);
                     AlphaTri at;
                     make_alpha_tri(ob, ob.mvp, ob.idx[3 * tri], ob.idx[3 * tri + 1], ob.idx[3 * tri + 2], ax, rt, at);
                     CutoutSink<VisSink> cs{s, &at};
@@ -278,37 +283,45 @@ int emu_draw(EmuDevice* d, const VkrGPUSceneData* scene, const VkrRenderObject* 
     if (!why.empty()) { d->err = why; return VKR_ERROR_INVALID_ARGUMENT; }
     const unsigned nChunks = plan.clusterBase[n];
     d->chunks.resize(nChunks);
-    d->chunkObj.resize(nChunks);
+    d->chunkObj.resize(plan.seqSlotBase[n]);
     const uint32_t passes = 1u + (uint32_t)plan.shadowLayers;
     d->perm.assign((size_t)passes * nChunks, 0u);
     for (size_t o = 0; o < n; ++o)                            // expand_chunks_kernel
         for (uint32_t c = plan.clusterBase[o]; c < plan.clusterBase[o + 1]; ++c) {
             const uint32_t lc = c - plan.clusterBase[o];
-            d->chunks[c] = make_chunk(plan.objects[o], (uint32_t)o, lc, plan.clusterBase[o]);
-            d->chunkObj[c] = uint2{(uint32_t)o, lc * GEOM_BLOCK};
+            d->chunks[c] = make_chunk(plan.objects[o], (uint32_t)o, lc, plan.seqSlotBase[o]);
             for (uint32_t p = 0; p < passes; ++p) {
                 const uint32_t sb = plan.slotBase[(size_t)p * n + o];
                 if (sb != 0xFFFFFFFFu) d->perm[(size_t)p * nChunks + sb + lc] = c;
             }
         }
+    for (size_t o = 0; o < n; ++o)
+        for (uint32_t k = plan.seqSlotBase[o]; k < plan.seqSlotBase[o + 1]; ++k) d->chunkObj[k] = uint2{(uint32_t)o, (k - plan.seqSlotBase[o]) * SEQ_SLOT};
     d->culled[0] = d->culled[1] = 0;
     for (int layer = 0; layer < plan.shadowLayers; ++layer) {
         RasterTarget rt = plan.shadowTarget;
         rt.depthBits = d->shadowBits.data() + (size_t)layer * d->S * d->S;
         std::fill(rt.depthBits, rt.depthBits + (size_t)d->S * d->S, DEPTH_ONE_BITS);
-        run_pass<true>(d, plan, rt, plan.shadowMvp.data() + (size_t)layer * n * 16, 16, nChunks, d->perm.data() + (size_t)(1 + layer) * nChunks);
+        run_pass<1>(d, plan, rt, plan.shadowMvp.data() + (size_t)layer * n * 16, 16, nChunks, d->perm.data() + (size_t)(1 + layer) * nChunks);
     }
     RasterTarget rt = plan.mainTarget;
     rt.vis = d->vis.data();
     std::fill(d->vis.begin(), d->vis.end(), VIS_CLEAR);
     const unsigned opaqueChunks = plan.opaqueClusters;
-    run_pass<false>(d, plan, rt, (const float*)plan.objects.data(), sizeof(DObject) / 4, opaqueChunks, d->perm.data());
+    run_pass<0>(d, plan, rt, (const float*)plan.objects.data(), sizeof(DObject) / 4, opaqueChunks, d->perm.data());
     if (d->counters[2]) { d->err = "queue overflow"; return VKR_ERROR_CAPACITY; }
     ShadeBuffers sb{};
+    sb.accum = nullptr;
     sb.vis = d->vis.data(); sb.objects = plan.objects.data(); sb.chunkObj = d->chunkObj.data();
     sb.materials = d->materials.data(); sb.textures = d->tex.data(); sb.cube = d->haveCube ? d->cube : nullptr;
     sb.shadow = reinterpret_cast<const float*>(d->shadowBits.data());
     sb.hdr = d->hdr.data(); sb.rgba8 = d->rgba8.data(); sb.srgbLut = d->lut;
+    if (nChunks > opaqueChunks) {                             // geometry_transparent_kernel + large_transparent_kernel
+        d->accum.assign((size_t)d->W * d->H * 4, 0.0f);
+        sb.accum = d->accum.data();
+        run_pass<2>(d, plan, rt, (const float*)plan.objects.data(), sizeof(DObject) / 4, nChunks - opaqueChunks, nullptr, opaqueChunks, &sb);
+        if (d->counters[2]) { d->err = "queue overflow"; return VKR_ERROR_CAPACITY; }
+    }
     for (int py = plan.sc.sy0; py < plan.sc.sy1; ++py)
         for (int px = plan.sc.sx0; px < plan.sc.sx1; ++px) shade_pixel(plan.sc, sb, px, py);
     d->stats.drawcall_count = (int)n; d->stats.triangle_count = (int)plan.totalTris;

@@ -260,8 +260,37 @@ def lattice(r, n=4, rings=24, shadow_mode=1):
     return sd, np.array(objs), fp
 
 
+def transparent(r, skybox=True):
+    """"Transparent" materials (additive blend, depth test, no depth write — src/vk_engine_init.cpp:545-547):
+    overlapping tessellated spheres, a screen-sized quad (large-triangle path), one behind opaque geometry
+    (must be hidden), one textured with cut-outs (discard inside the transparent pass), over opaque geometry
+    and over the background / skybox (where the skybox, drawn last at depth 1.0, wins)."""
+    sd, objs, fp = basic(r, 1, skybox=skybox, background=not skybox)
+    W, H = r.width, r.height
+    sv, si = mg.uv_sphere(20, 20, 1.0)
+    qv, qi = mg.plane(1, 1, 9.0, 0.0, uv_scale=3)
+    ms, mq = r.upload_mesh(si, sv), r.upload_mesh(qi, qv)
+    cut = r.create_image(mg.cutout_texture(64, 3, seed=7), capi.FORMAT_SRGB, True)
+    r.update_bindless_texture(7, cut, capi.SAMPLER_LINEAR)
+    t_blue = r.build_material((0.1, 0.2, 0.6, 1), 0.0, 0.4, pass_type=capi.PASS_TRANSPARENT)
+    t_warm = r.build_material((0.5, 0.3, 0.1, 1), 0.8, 0.3, pass_type=capi.PASS_TRANSPARENT)
+    t_cut = r.build_material((0.3, 0.6, 0.3, 1), 0.0, 0.7, albedo_id=7, pass_type=capi.PASS_TRANSPARENT)
+    rot = np.array([[1, 0, 0, 0], [0, 0, -1, 0], [0, 1, 0, 0], [0, 0, 0, 1]], np.float32)
+    extra = [
+        mg.render_object(ms, t_blue, mg.translate(-1.5, 1.0, 3.0) @ mg.scale(1.4), len(si)),
+        mg.render_object(ms, t_warm, mg.translate(-0.5, 1.2, 4.0) @ mg.scale(1.2), len(si)),      # overlaps the first
+        mg.render_object(ms, t_blue, mg.translate(3.0, 0.0, -4.0), len(si)),                      # behind an opaque sphere row
+        mg.render_object(mq, t_warm, mg.translate(0.0, 2.0, 1.0) @ rot, len(qi)),                 # big quad: large-triangle path
+        mg.render_object(mq, t_cut, mg.translate(2.0, 1.0, 6.0) @ rot @ mg.scale(0.4), len(qi)),
+        mg.render_object(ms, t_cut, mg.translate(5.0, 3.5, 2.0), len(si)),                        # against the sky / background
+    ]
+    return sd, np.concatenate([objs, np.array(extra)]), fp
+
+
 SCENES = {
     "cutout": cutout,
+    "transparent": transparent,
+    "transparent_background": lambda r: transparent(r, skybox=False),
     "lattice": lattice,
     "basic_hard": lambda r: basic(r, 0),
     "basic_pcf": lambda r: basic(r, 1),

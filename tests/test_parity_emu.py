@@ -35,7 +35,7 @@ def test_emu_cluster_culling_is_exercised(ork_lib, emu_lib):
     r.draw(sd, objs, fp)
     out = (ctypes.c_uint32 * 2)()
     emu_lib.emu_culled(r.dev, out)
-    total = sum((int(o["indexCount"]) // 3 + 255) // 256 for o in objs)
+    total = sum((int(o["indexCount"]) // 3 + 127) // 128 for o in objs)
     assert out[0] > total // 4, f"main pass culled only {out[0]} of {total} clusters"
     assert out[1] > 0, "shadow pass culled nothing"
     r.close()

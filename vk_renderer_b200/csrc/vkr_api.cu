@@ -102,55 +102,56 @@ __global__ void mip_blit_kernel(const uchar4* __restrict__ src, int sw, int sh, 
     dst[(size_t)y * dw + x] = o;
 }
 
-__device__ __forceinline__ uint32_t c3_seq(const uint4* chp) { return __ldg(reinterpret_cast<const uint32_t*>(chp + 3)); }   // DChunk::seqBase
-
-// ---- per-frame cluster table, written on the device from the per-draw prefixes (one CTA per draw):
-// the 96-byte records, the (draw, first triangle) pairs the shading pass looks up through seq >> 8, and for
-// every pass the processing order (geometry CTA slot -> cluster), front to back by draw.
+// ---- per-frame tables, written on the device from the per-draw prefixes (one CTA per draw):
+// the 80-byte cluster records, for every pass the processing order (geometry warp slot -> cluster, front to
+// back by draw), and the (draw, first triangle) pairs the shading pass looks up through seq >> 8.
 __global__ void expand_chunks_kernel(const DObject* __restrict__ objects, const uint32_t* __restrict__ clusterBase,
-                                     const uint32_t* __restrict__ slotBase, uint32_t nobj, uint32_t passes, uint32_t permStride,
+                                     const uint32_t* __restrict__ seqSlotBase, const uint32_t* __restrict__ slotBase,
+                                     uint32_t nobj, uint32_t passes, uint32_t permStride,
                                      DChunk* __restrict__ chunks, uint2* __restrict__ chunkObj, uint32_t* __restrict__ perm) {
     const uint32_t obj = blockIdx.x;
     const uint32_t base = clusterBase[obj], n = clusterBase[obj + 1] - base;
+    const uint32_t sbase = seqSlotBase[obj], ns = seqSlotBase[obj + 1] - sbase;
     const DObject& o = objects[obj];
     for (uint32_t c = threadIdx.x; c < n; c += blockDim.x) {
-        chunks[base + c] = make_chunk(o, obj, c, base);
-        chunkObj[base + c] = make_uint2(obj, c * GEOM_BLOCK);
+        chunks[base + c] = make_chunk(o, obj, c, sbase);
         for (uint32_t p = 0; p < passes; ++p) {
             const uint32_t sb = slotBase[(size_t)p * nobj + obj];
             if (sb != 0xFFFFFFFFu) perm[(size_t)p * permStride + sb + c] = base + c;
         }
     }
+    for (uint32_t k = threadIdx.x; k < ns; k += blockDim.x) chunkObj[sbase + k] = make_uint2(obj, k * SEQ_SLOT);
 }
 
-// ---- geometry: one CTA per cluster (<= 256 triangles of one draw).
+// ---- geometry: one WARP per cluster (<= 128 triangles, <= 128 distinct vertices of one draw); the warps of a
+// CTA never synchronise with each other, so every warp of the SM is an independent latency-hiding stream.
 // Phase 0 (8 lanes) projects the cluster's bounding box and drops the cluster when it is outside the
 // frustum, holds no pixel centre, or is hidden by what is already in the depth / visibility buffer.
-// Phase 1 transforms each DISTINCT vertex of the cluster once (128-bit position loads) into shared
-// memory as snapped window coordinates; phase 2 runs one thread per triangle on those.
-template <bool SHADOW>
-__global__ void __launch_bounds__(GEOM_BLOCK) geometry_kernel(const DChunk* __restrict__ chunks, const uint32_t* __restrict__ perm,
-                                                              const float* __restrict__ mvps, uint32_t mvpStride,
-                                                              const __grid_constant__ RasterTarget rt, const __grid_constant__ Queues q) {
-    __shared__ float s_mvp[16];
-    __shared__ uint4 s_vtx[3 * GEOM_BLOCK];
-    __shared__ ClusterRect s_rect;
-    // the 96-byte cluster record is everything this CTA needs: one level of indirection
-    const uint4* chp = reinterpret_cast<const uint4*>(chunks + __ldg(perm + blockIdx.x));
+// Phase 1 transforms each DISTINCT vertex of the cluster once (128-bit position loads) into the warp's
+// 2 KB of shared memory as snapped window coordinates; phase 2 runs the triangles, 32 at a time, on those.
+// PASS: 0 main (visibility buffer), 1 shadow (depth only), 2 transparent (shade + additive blend, no depth write).
+enum { PASS_MAIN = 0, PASS_SHADOW = 1, PASS_TRANSPARENT = 2 };
+
+template <int PASS, class MakeSink>
+__device__ __forceinline__ void geometry_warp(const DChunk* __restrict__ chunk, const float* __restrict__ mvps, uint32_t mvpStride,
+                                              const RasterTarget& rt, const Queues& q, uint4* s_vtx, float* mvp, const MakeSink& makeSink) {
+    const int lane = threadIdx.x & 31;
+    // the 80-byte cluster record is everything this warp needs: one level of indirection (uniform loads)
+    const uint4* chp = reinterpret_cast<const uint4*>(chunk);
     const uint4 c0 = __ldg(chp), c1 = __ldg(chp + 1), c2 = __ldg(chp + 2);
     const float4* __restrict__ pos = reinterpret_cast<const float4*>(((uint64_t)c0.y << 32) | c0.x);
     const uint32_t* __restrict__ clVerts = reinterpret_cast<const uint32_t*>(((uint64_t)c0.w << 32) | c0.z);
     const uint32_t* __restrict__ clTris = reinterpret_cast<const uint32_t*>(((uint64_t)c1.y << 32) | c1.x);
     const uint32_t* __restrict__ clOrig = reinterpret_cast<const uint32_t*>(((uint64_t)c1.w << 32) | c1.z);
-    const uint32_t obj = c2.x, counts = c2.z, flags = c2.w;
-    if (!SHADOW && (flags & 2u)) return;     // alpha-tested draw: geometry_cutout_kernel owns this cluster
-    if (threadIdx.x < 16) s_mvp[threadIdx.x] = __ldg(mvps + (size_t)obj * mvpStride + threadIdx.x);
-    __syncthreads();
+    const uint32_t obj = c2.x, seqBase = c2.y, counts = c2.z, flags = c2.w;
+    if (PASS == PASS_MAIN && (flags & 2u)) return;     // alpha-tested draw: geometry_cutout_kernel owns this cluster
+    if (lane < 16) mvp[lane] = __ldg(mvps + (size_t)obj * mvpStride + lane);
+    __syncwarp();
 
-    // ---- phase 0: cluster culling
-    if (threadIdx.x < 32) {
-        const float4 bmin = __ldg(reinterpret_cast<const float4*>(chp + 4)), bmax = __ldg(reinterpret_cast<const float4*>(chp + 5));
-        CornerAcc a = corner_eval(s_mvp, bmin, bmax, threadIdx.x & 7);
+    // ---- phase 0: cluster culling (every group of 8 lanes evaluates the 8 corners; all lanes end up with the result)
+    {
+        const float4 bmin = __ldg(reinterpret_cast<const float4*>(chp + 3)), bmax = __ldg(reinterpret_cast<const float4*>(chp + 4));
+        CornerAcc a = corner_eval(mvp, bmin, bmax, lane & 7);
 #pragma unroll
         for (int d = 1; d < 8; d <<= 1) {
             CornerAcc b;
@@ -160,60 +161,96 @@ __global__ void __launch_bounds__(GEOM_BLOCK) geometry_kernel(const DChunk* __re
             b.outAll = __shfl_xor_sync(0xFFFFFFFFu, a.outAll, d); b.allFront = __shfl_xor_sync(0xFFFFFFFFu, a.allFront, d);
             a = corner_merge(a, b);
         }
-        if (threadIdx.x == 0) s_rect = cluster_finalize(a, rt);
-    }
-    __syncthreads();
-    const ClusterRect rect = s_rect;
-    if (rect.verdict == CLUSTER_CULLED) { if (threadIdx.x == 0) atomicAdd(q.counters + 3, 1u); return; }
-    if (rect.verdict == CLUSTER_TEST) {
-        const int32_t w = rect.x1 - rect.x0 + 1, n = w * (rect.y1 - rect.y0 + 1);
-        int hidden = 1;
-        for (int32_t i = threadIdx.x; i < n; i += GEOM_BLOCK) {
-            const int32_t row = i / w, px = rect.x0 + (i - row * w), py = rect.y0 + row;
-            // .cg: read at L2, where the RED.MIN of the other CTAs land (stale L1 lines would only lose culls)
-            uint32_t stored;
-            if (SHADOW) stored = __ldcg(rt.depthBits + (size_t)py * rt.width + px);
-            else stored = __ldcg(reinterpret_cast<const uint32_t*>(rt.vis + (size_t)py * rt.width + px) + 1);
-            hidden &= depth_hides(stored, rect.zminBits) ? 1 : 0;
+        const ClusterRect rect = cluster_finalize(a, rt);
+        bool culled = rect.verdict == CLUSTER_CULLED;
+        if (rect.verdict == CLUSTER_TEST) {
+            // the warp walks the rectangle as 8x4 pixel footprints and stops at the first visible pixel
+            bool hidden = true;
+            for (int32_t py = rect.y0 + (lane >> 3); __any_sync(0xFFFFFFFFu, py <= rect.y1) && hidden; py += 4) {
+                for (int32_t px = rect.x0 + (lane & 7); px <= rect.x1 && py <= rect.y1; px += 8) {
+                    // .cg: read at L2, where the RED.MIN of the other warps land (stale L1 lines would only lose culls)
+                    uint32_t stored;
+                    if (PASS == PASS_SHADOW) stored = __ldcg(rt.depthBits + (size_t)py * rt.width + px);
+                    else stored = __ldcg(reinterpret_cast<const uint32_t*>(rt.vis + (size_t)py * rt.width + px) + 1);
+                    hidden = hidden && depth_hides(stored, rect.zminBits);
+                }
+                hidden = __all_sync(0xFFFFFFFFu, hidden);
+            }
+            culled = hidden;
         }
-        if (__syncthreads_and(hidden)) { if (threadIdx.x == 0) atomicAdd(q.counters + 3, 1u); return; }
+        if (culled) { if (lane == 0) atomicAdd(q.counters + 3, 1u); return; }
     }
 
+    // ---- phase 1: distinct vertices
     const uint32_t nVerts = counts & 0xFFFFu, nTris = counts >> 16;
-    for (uint32_t v = threadIdx.x; v < nVerts; v += GEOM_BLOCK) {
-        const CachedVtx cv = cluster_vertex(s_mvp, __ldg(pos + __ldg(clVerts + v)), rt);
+    for (uint32_t v = lane; v < nVerts; v += 32) {
+        const CachedVtx cv = cluster_vertex(mvp, __ldg(pos + __ldg(clVerts + v)), rt);
         s_vtx[v] = make_uint4((uint32_t)cv.X, (uint32_t)cv.Y, cv.zbits, cv.flag);
     }
-    __syncthreads();
-    if (threadIdx.x >= nTris) return;
-    const uint32_t packed = __ldg(clTris + threadIdx.x);
-    const uint32_t l0 = packed & 1023u, l1 = (packed >> 10) & 1023u, l2 = packed >> 20;
-    const uint4 a = s_vtx[l0], b = s_vtx[l1], c = s_vtx[l2];
-    const CachedVtx va{(int32_t)a.x, (int32_t)a.y, a.z, a.w}, vb{(int32_t)b.x, (int32_t)b.y, b.z, b.w}, vc{(int32_t)c.x, (int32_t)c.y, c.z, c.w};
-    uint32_t g0 = 0, g1 = 0, g2 = 0;
-    if (a.w | b.w | c.w) { g0 = __ldg(clVerts + l0); g1 = __ldg(clVerts + l1); g2 = __ldg(clVerts + l2); }
-    if (SHADOW) {
-        DepthSink sink{rt.depthBits, rt.width};
-        cluster_triangle(va, vb, vc, s_mvp, pos, g0, g1, g2, 0u, rt, q, sink);
-    } else {
-        const uint32_t seq = c3_seq(chp) + __ldg(clOrig + threadIdx.x);   // submission order, whatever the processing order
-        VisSink sink{rt.vis, rt.width, 0xFFFFFFFEu - seq};
-        cluster_triangle(va, vb, vc, s_mvp, pos, g0, g1, g2, seq, rt, q, sink);
+    __syncwarp();
+
+    // ---- phase 2: triangles
+    for (uint32_t t = lane; t < nTris; t += 32) {
+        const uint32_t packed = __ldg(clTris + t);
+        const uint32_t l0 = packed & 127u, l1 = (packed >> 7) & 127u, l2 = (packed >> 14) & 127u;
+        const uint4 a = s_vtx[l0], b = s_vtx[l1], c = s_vtx[l2];
+        const CachedVtx va{(int32_t)a.x, (int32_t)a.y, a.z, a.w}, vb{(int32_t)b.x, (int32_t)b.y, b.z, b.w}, vc{(int32_t)c.x, (int32_t)c.y, c.z, c.w};
+        uint32_t g0 = 0, g1 = 0, g2 = 0;
+        if (a.w | b.w | c.w) { g0 = __ldg(clVerts + l0); g1 = __ldg(clVerts + l1); g2 = __ldg(clVerts + l2); }
+        // submission-order sequence number, whatever the processing order (the shadow pass has no use for it)
+        const uint32_t seq = PASS == PASS_SHADOW ? 0u : seqBase + __ldg(clOrig + t);
+        cluster_triangle(va, vb, vc, mvp, pos, g0, g1, g2, seq, rt, q, makeSink(seq));
     }
+}
+
+struct MakeVisSink { uint64_t* vis; int32_t width; __device__ VisSink operator()(uint32_t seq) const { return VisSink{vis, width, 0xFFFFFFFEu - seq}; } };
+struct MakeDepthSink { uint32_t* bits; int32_t width; __device__ DepthSink operator()(uint32_t) const { return DepthSink{bits, width}; } };
+struct MakeBlendSink { const ShadeConst* sc; const ShadeBuffers* sb; __device__ BlendSink operator()(uint32_t seq) const { return BlendSink{sc, sb, seq}; } };
+
+template <bool SHADOW>
+__global__ void __launch_bounds__(GEOM_WARPS * 32, 4) geometry_kernel(const DChunk* __restrict__ chunks, const uint32_t* __restrict__ perm,
+                                                                     uint32_t nClusters, const float* __restrict__ mvps, uint32_t mvpStride,
+                                                                     const __grid_constant__ RasterTarget rt, const __grid_constant__ Queues q) {
+    __shared__ uint4 s_vtxAll[GEOM_WARPS][CL_VERTS];
+    __shared__ float s_mvpAll[GEOM_WARPS][16];
+    const uint32_t slot = blockIdx.x * GEOM_WARPS + (threadIdx.x >> 5);
+    if (slot >= nClusters) return;
+    const DChunk* chunk = chunks + __ldg(perm + slot);
+    if (SHADOW) geometry_warp<PASS_SHADOW>(chunk, mvps, mvpStride, rt, q, s_vtxAll[threadIdx.x >> 5], s_mvpAll[threadIdx.x >> 5], MakeDepthSink{rt.depthBits, rt.width});
+    else geometry_warp<PASS_MAIN>(chunk, mvps, mvpStride, rt, q, s_vtxAll[threadIdx.x >> 5], s_mvpAll[threadIdx.x >> 5], MakeVisSink{rt.vis, rt.width});
+}
+
+// ---- "Transparent" draws (the tail of the draw list), after every opaque fragment is in the visibility buffer
+__global__ void __launch_bounds__(GEOM_WARPS * 32) geometry_transparent_kernel(const DChunk* __restrict__ chunks, uint32_t firstCluster, uint32_t nClusters,
+                                                                              const float* __restrict__ mvps, uint32_t mvpStride,
+                                                                              const __grid_constant__ RasterTarget rt, const __grid_constant__ Queues q,
+                                                                              const __grid_constant__ ShadeConst sc, const __grid_constant__ ShadeBuffers sbIn) {
+    __shared__ uint4 s_vtxAll[GEOM_WARPS][CL_VERTS];
+    __shared__ float s_mvpAll[GEOM_WARPS][16];
+    __shared__ float s_lut[256];
+    s_lut[threadIdx.x] = sbIn.srgbLut[threadIdx.x];
+    __syncthreads();
+    __shared__ ShadeBuffers s_sb;
+    if (threadIdx.x == 0) { s_sb = sbIn; s_sb.srgbLut = s_lut; }
+    __syncthreads();
+    const uint32_t slot = blockIdx.x * GEOM_WARPS + (threadIdx.x >> 5);
+    if (slot >= nClusters) return;
+    geometry_warp<PASS_TRANSPARENT>(chunks + firstCluster + slot, mvps, mvpStride, rt, q, s_vtxAll[threadIdx.x >> 5], s_mvpAll[threadIdx.x >> 5],
+                                    MakeBlendSink{&sc, &s_sb});
 }
 
 // ---- main pass, alpha-tested draws only (launched when the frame has any): one thread per triangle,
 // straight from the original vertices, coverage gated by the albedo alpha (vkr_raster.cuh alpha_passes)
-__global__ void __launch_bounds__(GEOM_BLOCK) geometry_cutout_kernel(const DObject* __restrict__ objects, const DChunk* __restrict__ chunks,
-                                                                     const __grid_constant__ RasterTarget rt, const __grid_constant__ Queues q,
-                                                                     const __grid_constant__ AlphaCtx ax) {
+__global__ void __launch_bounds__(CL_TRIS) geometry_cutout_kernel(const DObject* __restrict__ objects, const DChunk* __restrict__ chunks,
+                                                                  const __grid_constant__ RasterTarget rt, const __grid_constant__ Queues q,
+                                                                  const __grid_constant__ AlphaCtx ax) {
     const DChunk& ch = chunks[blockIdx.x];
     if (!(ch.flags & 2u)) return;
     const uint32_t nTris = ch.counts >> 16;
     if (threadIdx.x >= nTris) return;
     const DObject& o = objects[ch.obj];
     const uint32_t packed = ch.clTris[threadIdx.x];
-    const uint32_t g0 = ch.clVerts[packed & 1023u], g1 = ch.clVerts[(packed >> 10) & 1023u], g2 = ch.clVerts[packed >> 20];
+    const uint32_t g0 = ch.clVerts[packed & 127u], g1 = ch.clVerts[(packed >> 7) & 127u], g2 = ch.clVerts[(packed >> 14) & 127u];
     const uint32_t seq = ch.seqBase + ch.clOrig[threadIdx.x];
     VisSink sink{rt.vis, rt.width, 0xFFFFFFFEu - seq};
     cutout_triangle(o, o.mvp, g0, g1, g2, seq, rt, q, ax, sink);
@@ -234,16 +271,33 @@ __global__ void __launch_bounds__(256) large_raster_kernel(const __grid_constant
             raster_item(lt, it, sink, lane, 32);
         } else {
             VisSink sink{rt.vis, rt.width, 0xFFFFFFFEu - lt.seq};
-            if (anyCutout && (ax.chunks[lt.seq >> 8].flags & 2u)) {
-                const DChunk& ch = ax.chunks[lt.seq >> 8];
-                const DObject& o = ax.objects[ch.obj];
-                const uint32_t tri = ch.firstTri + (lt.seq & 255u);
+            if (anyCutout && (ax.objects[ax.chunkObj[lt.seq >> 8].x].flags & 2u)) {
+                const uint2 co = ax.chunkObj[lt.seq >> 8];
+                const DObject& o = ax.objects[co.x];
+                const uint32_t tri = co.y + (lt.seq & 255u);
                 AlphaTri at;
                 make_alpha_tri(o, o.mvp, o.idx[3 * tri], o.idx[3 * tri + 1], o.idx[3 * tri + 2], ax, rt, at);
                 CutoutSink<VisSink> cs{sink, &at};
                 raster_item(lt, it, cs, lane, 32);
             } else raster_item(lt, it, sink, lane, 32);
         }
+    }
+}
+__global__ void __launch_bounds__(256) large_transparent_kernel(const __grid_constant__ RasterTarget rt, const __grid_constant__ Queues q,
+                                                                const __grid_constant__ ShadeConst sc, const __grid_constant__ ShadeBuffers sbIn) {
+    __shared__ float s_lut[256];
+    s_lut[threadIdx.x] = sbIn.srgbLut[threadIdx.x];
+    __syncthreads();
+    ShadeBuffers sb = sbIn;
+    sb.srgbLut = s_lut;
+    const uint32_t nItems = min(q.counters[1], q.itemCap);
+    const uint32_t warpsPerGrid = (gridDim.x * blockDim.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    for (uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < nItems; i += warpsPerGrid) {
+        const LargeItem it = q.items[i];
+        const LargeTri lt = q.tris[it.tri];
+        BlendSink sink{&sc, &sb, lt.seq};
+        raster_item(lt, it, sink, lane, 32);
     }
 }
 
@@ -302,6 +356,7 @@ struct VkrDevice {
     uint16_t* hdr = nullptr;
     uint32_t* rgba8[VKR_FRAME_OVERLAP] = {nullptr, nullptr};
     uint32_t* scratch = nullptr;        // W*H*4, lazily allocated for depth / primid readback
+    float* accum = nullptr;             // W*H*16, lazily allocated: additive sums of the transparent pass
     float* lut = nullptr;
 
     std::vector<DMesh> meshes;
@@ -323,7 +378,7 @@ struct VkrDevice {
     size_t uploadBytes = 0;
 
     DChunk* chunkBuf = nullptr; size_t chunkCap = 0;   // per-frame cluster table (device-written)
-    uint2* chunkObjBuf = nullptr;                      // seq >> 8 -> (draw, first triangle)
+    uint2* chunkObjBuf = nullptr; size_t seqSlotCap = 0;   // seq >> 8 -> (draw, first triangle)
     uint32_t* permBuf = nullptr; size_t permCap = 0;   // (1 + shadow layers) x clusters: processing order per pass
 
     Queues q{};                         // large-triangle queue of the main pass
@@ -336,7 +391,7 @@ struct VkrDevice {
     const uint2* lastChunkObj = nullptr; const DObject* lastObjects = nullptr;
     FramePlan plan;
 
-    cudaEvent_t tev[9] = {nullptr};   // 0 start, 1 uploaded, 3 cleared, 4 geometry kernel, 5 large kernel, 6 shaded; 7,8 shadow pass (shadow stream)
+    cudaEvent_t tev[10] = {nullptr};   // 0 start, 1 uploaded, 3 cleared, 4 geometry kernel, 5 large kernel, 6 shaded; 7,8 shadow pass (shadow stream)
     bool tevValid = false, shadowTimed = false;
     float timings[VKR_T_COUNT] = {0};
 
@@ -383,7 +438,7 @@ struct DeviceClusterProvider : ClusterProvider {
                   cudaMemcpyAsync(db, cd.bounds.data(), cd.bounds.size() * sizeof(float4), cudaMemcpyHostToDevice, dev->stream) == cudaSuccess &&
                   cudaStreamSynchronize(dev->stream) == cudaSuccess;   // cd is a local
         if (!ok) return false;
-        out = ClusterRange{dv, dt, dorig, di, db, {0, 0, 0}, 0};
+        out = ClusterRange{dv, dt, dorig, di, db, 0u, {0, 0, 0}, 0};
         range_sphere(cd, out);
         dev->ranges[key] = out;
         return true;
@@ -455,8 +510,8 @@ int vkr_create(const VkrConfig* cfg, VkrDevice** out) {
         ALLOC(dev->qShadow.tris, sizeof(LargeTri) * dev->qShadow.triCap);
         ALLOC(dev->qShadow.items, sizeof(LargeItem) * dev->qShadow.itemCap);
         ALLOC(dev->qShadow.counters, 16);
-        CK(cudaMallocHost(&dev->countersHost, 32));
-        std::memset(dev->countersHost, 0, 32);
+        CK(cudaMallocHost(&dev->countersHost, 48));
+        std::memset(dev->countersHost, 0, 48);
         for (auto& s : dev->slots) {
             CK(cudaEventCreateWithFlags(&s.uploaded, cudaEventDisableTiming));
             CK(cudaEventCreateWithFlags(&s.rendered, cudaEventDisableTiming));
@@ -674,16 +729,20 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
     FrameSlot& slot = dev->slots[slotIdx];
     dev->uploadBytes = 0;
     const size_t szObj = sizeof(DObject) * n, szBase = 4 * (n + 1);
-    const unsigned nChunks = plan.clusterBase[n];
+    const unsigned nChunks = plan.clusterBase[n], nSeqSlots = plan.seqSlotBase[n];
     const size_t szShadow = plan.shadowMvp.size() * 4, szSlot = plan.slotBase.size() * 4;
     const uint32_t passes = 1u + (uint32_t)plan.shadowLayers;
     auto align16 = [](size_t v) { return (v + 15) & ~(size_t)15; };
-    const size_t offObj = 0, offBase = align16(offObj + szObj), offShadow = align16(offBase + szBase), offSlot = align16(offShadow + szShadow);
+    const size_t offObj = 0, offBase = align16(offObj + szObj), offSeq = align16(offBase + szBase), offShadow = align16(offSeq + szBase),
+                 offSlot = align16(offShadow + szShadow);
     const size_t total = align16(offSlot + szSlot) + 16;
     if (dev->chunkCap < nChunks) {
         dev->chunkCap = std::max<size_t>((size_t)nChunks * 3 / 2, 1024);
         ALLOC(dev->chunkBuf, dev->chunkCap * sizeof(DChunk));     // the previous tables are freed at destroy
-        ALLOC(dev->chunkObjBuf, dev->chunkCap * sizeof(uint2));
+    }
+    if (dev->seqSlotCap < nSeqSlots) {
+        dev->seqSlotCap = std::max<size_t>((size_t)nSeqSlots * 3 / 2, 1024);
+        ALLOC(dev->chunkObjBuf, dev->seqSlotCap * sizeof(uint2));
     }
     if (dev->permCap < (size_t)passes * nChunks) {
         dev->permCap = std::max<size_t>((size_t)passes * nChunks * 3 / 2, 1024);
@@ -695,6 +754,7 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
     char* hp = (char*)slot.pinned;
     if (n) std::memcpy(hp + offObj, plan.objects.data(), szObj);
     std::memcpy(hp + offBase, plan.clusterBase.data(), szBase);
+    std::memcpy(hp + offSeq, plan.seqSlotBase.data(), szBase);
     if (szShadow) std::memcpy(hp + offShadow, plan.shadowMvp.data(), szShadow);
     if (szSlot) std::memcpy(hp + offSlot, plan.slotBase.data(), szSlot);
     // the upload rides its own stream so it overlaps the previous frame's kernels; the slot's device
@@ -710,7 +770,7 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
     const float* dShadowMvp = (const float*)(dp + offShadow);
     const uint32_t* dPerm = dev->permBuf;
     if (n) {
-        expand_chunks_kernel<<<(unsigned)n, 64, 0, st>>>(dObjects, (const uint32_t*)(dp + offBase), (const uint32_t*)(dp + offSlot), (uint32_t)n, passes,
+        expand_chunks_kernel<<<(unsigned)n, 64, 0, st>>>(dObjects, (const uint32_t*)(dp + offBase), (const uint32_t*)(dp + offSeq), (const uint32_t*)(dp + offSlot), (uint32_t)n, passes,
                                                          nChunks, dev->chunkBuf, dev->chunkObjBuf, dev->permBuf);
         dev->launches += 1;
     }
@@ -733,7 +793,8 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
             CK(cudaMemsetAsync(dev->qShadow.counters, 0, 16, ss));
             dev->launches += 1;
             if (nChunks) {
-                geometry_kernel<true><<<nChunks, GEOM_BLOCK, 0, ss>>>(dChunks, dPerm + (size_t)(1 + layer) * nChunks, dShadowMvp + (size_t)layer * n * 16, 16u, rt, dev->qShadow);
+                geometry_kernel<true><<<(nChunks + GEOM_WARPS - 1) / GEOM_WARPS, GEOM_WARPS * 32, 0, ss>>>(dChunks, dPerm + (size_t)(1 + layer) * nChunks, nChunks,
+                                                                                                      dShadowMvp + (size_t)layer * n * 16, 16u, rt, dev->qShadow);
                 large_raster_kernel<true><<<largeGrid, 256, 0, ss>>>(rt, dev->qShadow, AlphaCtx{}, 0);
                 dev->launches += 2;
             }
@@ -755,11 +816,12 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
         // only the opaque prefix writes depth; transparent draws are blended in a later pass
         const unsigned opaqueChunks = plan.opaqueClusters;
         if (opaqueChunks) {
-            geometry_kernel<false><<<opaqueChunks, GEOM_BLOCK, 0, st>>>(dChunks, dPerm, (const float*)dObjects, (uint32_t)(sizeof(DObject) / 4), rt, dev->q);
+            geometry_kernel<false><<<(opaqueChunks + GEOM_WARPS - 1) / GEOM_WARPS, GEOM_WARPS * 32, 0, st>>>(dChunks, dPerm, opaqueChunks, (const float*)dObjects,
+                                                                                                            (uint32_t)(sizeof(DObject) / 4), rt, dev->q);
             if (timing) CK(cudaEventRecord(dev->tev[4], st));
-            const AlphaCtx ax{dObjects, dChunks, dev->matDev, dev->texDev};
+            const AlphaCtx ax{dObjects, dev->chunkObjBuf, dev->matDev, dev->texDev};
             if (plan.anyCutout) {
-                geometry_cutout_kernel<<<opaqueChunks, GEOM_BLOCK, 0, st>>>(dObjects, dChunks, rt, dev->q, ax);
+                geometry_cutout_kernel<<<opaqueChunks, CL_TRIS, 0, st>>>(dObjects, dChunks, rt, dev->q, ax);
                 dev->launches += 1;
             }
             large_raster_kernel<false><<<largeGrid, 256, 0, st>>>(rt, dev->q, ax, plan.anyCutout ? 1 : 0);
@@ -769,15 +831,35 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
     }
     if (timing) CK(cudaEventRecord(dev->tev[5], st));
 
+    if (plan.shadowLayers) CK(cudaStreamWaitEvent(st, dev->evShadow, 0));   // join: the shaders sample the shadow map
+    ShadeBuffers sb{};
+    sb.vis = dev->vis; sb.objects = dObjects; sb.chunkObj = dev->chunkObjBuf; sb.materials = dev->matDev;
+    sb.textures = dev->texDev; sb.cube = dev->haveCube ? dev->cubeDev : nullptr;
+    sb.shadow = reinterpret_cast<const float*>(dev->shadowBits);
+    sb.hdr = dev->hdr; sb.rgba8 = dev->rgba8[slotIdx]; sb.srgbLut = dev->lut;
+    sb.accum = nullptr;
+    const ShadeConst& sc = plan.sc;
+
+    // ---- "Transparent" draws: depth-tested against the finished opaque depth, shaded and summed (BlendSink)
+    const unsigned transChunks = nChunks - plan.opaqueClusters;
+    if (transChunks) {
+        const size_t px = (size_t)dev->W * dev->H;
+        if (!dev->accum) ALLOC(dev->accum, px * 16);
+        sb.accum = dev->accum;
+        CK(cudaMemsetAsync(dev->accum, 0, px * 16, st));
+        CK(cudaMemsetAsync(dev->q.counters, 0, 16, st));
+        RasterTarget rt = plan.mainTarget;
+        rt.vis = dev->vis;
+        geometry_transparent_kernel<<<(transChunks + GEOM_WARPS - 1) / GEOM_WARPS, GEOM_WARPS * 32, 0, st>>>(
+            dChunks, plan.opaqueClusters, transChunks, (const float*)dObjects, (uint32_t)(sizeof(DObject) / 4), rt, dev->q, sc, sb);
+        large_transparent_kernel<<<largeGrid, 256, 0, st>>>(rt, dev->q, sc, sb);
+        dev->launches += 2;
+        CK(cudaMemcpyAsync(dev->countersHost + 8, dev->q.counters, 16, cudaMemcpyDeviceToHost, st));
+    } else dev->countersHost[10] = 0;
+    if (timing) CK(cudaEventRecord(dev->tev[9], st));
+
     // ---- shading half of draw_geometry + draw_skybox + draw_background + draw_postprocess + present blit
-    if (plan.shadowLayers) CK(cudaStreamWaitEvent(st, dev->evShadow, 0));   // join: the shader samples the shadow map
     {
-        ShadeBuffers sb{};
-        sb.vis = dev->vis; sb.objects = dObjects; sb.chunkObj = dev->chunkObjBuf; sb.materials = dev->matDev;
-        sb.textures = dev->texDev; sb.cube = dev->haveCube ? dev->cubeDev : nullptr;
-        sb.shadow = reinterpret_cast<const float*>(dev->shadowBits);
-        sb.hdr = dev->hdr; sb.rgba8 = dev->rgba8[slotIdx]; sb.srgbLut = dev->lut;
-        const ShadeConst& sc = plan.sc;
         dim3 grid((sc.sx1 - sc.sx0 + 15) / 16, (sc.sy1 - sc.sy0 + 7) / 8);
         if (grid.x && grid.y) { shade_kernel<<<grid, 128, 0, st>>>(sc, sb); dev->launches += 1; }
     }
@@ -800,7 +882,7 @@ int vkr_sync(VkrDevice* dev) {
     CK(cudaStreamSynchronize(dev->stream));
     CK(cudaStreamSynchronize(dev->copyStream));
     CK(cudaStreamSynchronize(dev->shadowStream));
-    if (dev->countersHost[2] || dev->countersHost[6]) return dev->fail(VKR_ERROR_CAPACITY, "large-triangle queue overflow");
+    if (dev->countersHost[2] || dev->countersHost[6] || dev->countersHost[10]) return dev->fail(VKR_ERROR_CAPACITY, "large-triangle queue overflow");
     if (dev->tevValid) {
         auto el = [&](int a, int b) { float ms = 0; cudaEventElapsedTime(&ms, dev->tev[a], dev->tev[b]); return ms; };
         dev->timings[VKR_T_UPLOAD] = el(0, 1);
@@ -809,8 +891,8 @@ int vkr_sync(VkrDevice* dev) {
         dev->timings[VKR_T_CLEAR] = el(1, 3);
         dev->timings[VKR_T_GEOM_KERNEL] = el(3, 4);
         dev->timings[VKR_T_LARGE_KERNEL] = el(4, 5);
-        dev->timings[VKR_T_SHADE] = el(5, 6);
-        dev->timings[VKR_T_TRANSPARENT] = 0; dev->timings[VKR_T_POST] = 0;
+        dev->timings[VKR_T_SHADE] = el(9, 6);
+        dev->timings[VKR_T_TRANSPARENT] = el(5, 9); dev->timings[VKR_T_POST] = 0;   // tonemap + present are fused into the shade kernel
         dev->timings[VKR_T_TOTAL] = el(0, 6);
         dev->stats.frametime = dev->timings[VKR_T_TOTAL];
         dev->stats.mesh_draw_time = dev->timings[VKR_T_SHADOW] + dev->timings[VKR_T_GEOMETRY];

@@ -53,8 +53,8 @@ inline void camera_position(const float* m, float out[3]) {
 // Host-side builder of the per-range cluster data (DObject::clVerts / clTris / clOrig / clInfo / clBounds).
 struct ClusterData {
     std::vector<uint32_t> verts;     // concatenated distinct-vertex lists
-    std::vector<uint32_t> tris;      // nClusters * GEOM_BLOCK packed local ids
-    std::vector<uint32_t> orig;      // nClusters * GEOM_BLOCK submission-order triangle numbers
+    std::vector<uint32_t> tris;      // nClusters * CL_TRIS packed local ids
+    std::vector<uint32_t> orig;      // nClusters * CL_TRIS submission-order triangle numbers
     std::vector<uint2> info;         // per cluster
     std::vector<float4> bounds;      // per cluster: min, max
 };
@@ -68,14 +68,13 @@ inline uint32_t morton_part(uint32_t v) {
     return v;
 }
 // `pos` are the mesh's positions (x,y,z,1).  Triangles are ordered along a 30-bit Morton curve of their
-// centroids inside the range's bounding box (ties keep submission order), then cut every GEOM_BLOCK.
+// centroids inside the range's bounding box (ties keep submission order), then cut greedily: a cluster
+// closes when it holds CL_TRIS triangles or the next triangle would take it past CL_VERTS vertices.
 inline void build_clusters(const uint32_t* idx, uint32_t triCount, uint32_t nv, const float4* pos, ClusterData& out) {
-    const uint32_t nCl = (triCount + GEOM_BLOCK - 1) / GEOM_BLOCK;
-    out.verts.clear(); out.tris.assign((size_t)nCl * GEOM_BLOCK, 0u); out.orig.assign((size_t)nCl * GEOM_BLOCK, 0u);
-    out.info.resize(nCl); out.bounds.resize((size_t)nCl * 2);
+    out.verts.clear(); out.tris.clear(); out.orig.clear(); out.info.clear(); out.bounds.clear();
     std::vector<uint32_t> order(triCount);
     for (uint32_t t = 0; t < triCount; ++t) order[t] = t;
-    if (triCount > (uint32_t)GEOM_BLOCK) {
+    if (triCount > (uint32_t)CL_TRIS) {
         float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
         for (size_t i = 0; i < (size_t)triCount * 3; ++i) {
             const float4 p = pos[idx[i]];
@@ -98,13 +97,23 @@ inline void build_clusters(const uint32_t* idx, uint32_t triCount, uint32_t nv, 
         std::stable_sort(order.begin(), order.end(), [&](uint32_t x, uint32_t y) { return code[x] < code[y]; });
     }
     std::vector<uint32_t> stamp(nv, 0xFFFFFFFFu), local(nv, 0u);
-    for (uint32_t c = 0; c < nCl; ++c) {
-        const uint32_t t0 = c * GEOM_BLOCK, t1 = std::min(triCount, t0 + GEOM_BLOCK);
+    uint32_t s = 0, c = 0;
+    while (s < triCount) {
         const uint32_t off = (uint32_t)out.verts.size();
-        uint32_t count = 0;
+        uint32_t count = 0, nt = 0;
         float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
-        for (uint32_t s = t0; s < t1; ++s) {
+        out.tris.resize((size_t)(c + 1) * CL_TRIS, 0u);
+        out.orig.resize((size_t)(c + 1) * CL_TRIS, 0u);
+        while (s < triCount && nt < (uint32_t)CL_TRIS) {
             const uint32_t t = order[s];
+            uint32_t fresh = 0;
+            for (int k = 0; k < 3; ++k) {
+                const uint32_t v = idx[3 * (size_t)t + k];
+                bool seen = stamp[v] == c;
+                for (int j = 0; j < k && !seen; ++j) seen = idx[3 * (size_t)t + j] == v;
+                if (!seen) ++fresh;
+            }
+            if (count + fresh > (uint32_t)CL_VERTS) break;
             uint32_t l[3];
             for (int k = 0; k < 3; ++k) {
                 const uint32_t v = idx[3 * (size_t)t + k];
@@ -116,18 +125,21 @@ inline void build_clusters(const uint32_t* idx, uint32_t triCount, uint32_t nv, 
                 }
                 l[k] = local[v];
             }
-            out.tris[(size_t)c * GEOM_BLOCK + (s - t0)] = l[0] | (l[1] << 10) | (l[2] << 20);
-            out.orig[(size_t)c * GEOM_BLOCK + (s - t0)] = t;
+            out.tris[(size_t)c * CL_TRIS + nt] = l[0] | (l[1] << 7) | (l[2] << 14);
+            out.orig[(size_t)c * CL_TRIS + nt] = t;
+            ++nt; ++s;
         }
-        out.info[c] = uint2{off, count | ((t1 - t0) << 16)};
+        out.info.push_back(uint2{off, count | (nt << 16)});
         // (positions are required to be finite; min/max skip NaNs)
-        out.bounds[2 * (size_t)c] = make_float4(lo[0], lo[1], lo[2], 0.0f);
-        out.bounds[2 * (size_t)c + 1] = make_float4(hi[0], hi[1], hi[2], 0.0f);
+        out.bounds.push_back(make_float4(lo[0], lo[1], lo[2], 0.0f));
+        out.bounds.push_back(make_float4(hi[0], hi[1], hi[2], 0.0f));
+        ++c;
     }
 }
 
 struct ClusterRange {
     const uint32_t* verts; const uint32_t* tris; const uint32_t* orig; const uint2* info; const float4* bounds;
+    uint32_t nClusters;
     float center[3], radius;          // bounding sphere of the whole range (object space), for the processing order
 };
 // Implemented by the owner of the device (or emulated) memory: returns the cached range, building it on first use.
@@ -136,6 +148,7 @@ struct ClusterProvider {
     virtual bool get(uint32_t mesh, uint32_t firstIndex, uint32_t indexCount, ClusterRange& out) = 0;
 };
 inline void range_sphere(const ClusterData& cd, ClusterRange& r) {
+    r.nClusters = (uint32_t)cd.info.size();
     float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
     for (size_t c = 0; c + 1 < cd.bounds.size(); c += 2) {
         const float4 a = cd.bounds[c], b = cd.bounds[c + 1];
@@ -155,6 +168,7 @@ struct FramePlan {
     std::vector<DObject> objects;
     std::vector<uint32_t> primBase;     // nobj + 1 (dense ids, for stats / readback)
     std::vector<uint32_t> clusterBase;  // nobj + 1: first frame-cluster index of every draw
+    std::vector<uint32_t> seqSlotBase;  // nobj + 1: first 256-number sequence slot of every draw
     uint32_t opaqueClusters = 0;        // clusters of the opaque prefix
     bool anyCutout = false;             // some draw needs the raster-stage alpha test
     std::vector<float> shadowMvp;       // layers * nobj * 16
@@ -179,7 +193,8 @@ inline std::string plan_frame(const VkrGPUSceneData* scene, const VkrRenderObjec
     plan.objects.resize(n);
     plan.primBase.resize(n + 1);
     plan.clusterBase.resize(n + 1);
-    uint64_t ncl = 0;
+    plan.seqSlotBase.resize(n + 1);
+    uint64_t ncl = 0, nslot = 0;
     plan.shadowLayers = fp->enableShadows ? (fp->shadowMode < 3 ? 1 : VKR_NUM_CASCADES) : 0;
     plan.shadowMvp.resize((size_t)plan.shadowLayers * n * 16);
     uint64_t prim = 0;
@@ -187,6 +202,7 @@ inline std::string plan_frame(const VkrGPUSceneData* scene, const VkrRenderObjec
     std::vector<float>& sphere = plan.sphereScratch;
     sphere.resize(4 * n + 4);
     plan.opaqueCount = (uint32_t)n;
+    plan.opaqueClusters = 0;
     plan.anyCutout = false;
     for (size_t i = 0; i < n; ++i) {
         const VkrRenderObject& ro = objs[i];
@@ -219,15 +235,18 @@ inline std::string plan_frame(const VkrGPUSceneData* scene, const VkrRenderObjec
         }
         plan.primBase[i] = (uint32_t)prim;
         plan.clusterBase[i] = (uint32_t)ncl;
-        ncl += (o.triCount + GEOM_BLOCK - 1) / GEOM_BLOCK;
+        plan.seqSlotBase[i] = (uint32_t)nslot;
+        ncl += o.triCount ? cr.nClusters : 0u;
+        nslot += (o.triCount + SEQ_SLOT - 1) / SEQ_SLOT;
         if (!transparent) plan.opaqueClusters = (uint32_t)ncl;
         prim += o.triCount;
-        if (prim >= 0xFFFFFFF0ull || ncl >= 0xFFFFFFull) return "too many primitives in one frame";
+        if (prim >= 0xFFFFFFF0ull || nslot >= 0xFFFFFFull || ncl >= 0x7FFFFFFFull) return "too many primitives in one frame";
         for (int l = 0; l < plan.shadowLayers; ++l)
             mat_mul(scene->lightViewproj[l], ro.transform, &plan.shadowMvp[((size_t)l * n + i) * 16]);
     }
     plan.primBase[n] = (uint32_t)prim;
     plan.clusterBase[n] = (uint32_t)ncl;
+    plan.seqSlotBase[n] = (uint32_t)nslot;
     plan.totalTris = (uint32_t)prim;
 
     // ---- processing order per pass

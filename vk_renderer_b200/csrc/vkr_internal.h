@@ -31,7 +31,10 @@ static const uint32_t DEPTH_ONE_BITS = 0x3F800000u;
 
 static const int TILE = 64;                // large-triangle tile edge in pixels
 static const int SMALL_MAX = 16;           // in-thread raster when bbox is <= SMALL_MAX x SMALL_MAX
-static const int GEOM_BLOCK = 256;         // triangles per geometry CTA (one per thread)
+static const int CL_TRIS = 128;            // a cluster (one warp's unit of work) holds at most this many triangles ...
+static const int CL_VERTS = 128;           // ... and this many distinct vertices (7-bit local ids, 2 KB of shared memory)
+static const int SEQ_SLOT = 256;           // primitive sequence numbers are handed out to draws in slots of 256
+static const int GEOM_WARPS = 8;           // warps (clusters) per geometry CTA
 static const float GUARD_BAND = 64.0f;     // clip x,y only beyond +-GUARD_BAND*w
 
 // One mesh in HBM: SoA, 3 x 16-byte streams + u32 indices.
@@ -70,39 +73,36 @@ static_assert(sizeof(DObject) % 16 == 0, "DObject array is read with 16-byte loa
 
 // Cluster data, built once per (mesh, firstIndex, indexCount) at first use (build_clusters):
 // the draw's triangles are sorted along a Morton curve of their centroids and cut into clusters of
-// <= GEOM_BLOCK triangles, so a cluster is a compact surface patch with a tight bounding box.
-//   clInfo[c]          = (offset of the cluster's first entry in clVerts, vertexCount | triCount << 16)
-//   clVerts[...]       = the cluster's distinct mesh vertices
-//   clTris[c*256 + t]  = l0 | l1 << 10 | l2 << 20   (local vertex ids)
-//   clOrig[c*256 + t]  = the triangle's index in the draw's index range (submission order)
-//   clBounds[2c, 2c+1] = object-space AABB (min.xyz, max.xyz) of the cluster's vertices
+// <= CL_TRIS triangles and <= CL_VERTS distinct vertices, so a cluster is a compact surface patch
+// with a tight bounding box.
+//   clInfo[c]              = (offset of the cluster's first entry in clVerts, vertexCount | triCount << 16)
+//   clVerts[...]           = the cluster's distinct mesh vertices
+//   clTris[c*CL_TRIS + t]  = l0 | l1 << 7 | l2 << 14   (local vertex ids)
+//   clOrig[c*CL_TRIS + t]  = the triangle's index in the draw's index range (submission order)
+//   clBounds[2c, 2c+1]     = object-space AABB (min.xyz, max.xyz) of the cluster's vertices
 //
 // Primitive sequence numbers stay in SUBMISSION order whatever the processing order: a draw owns
-// the numbers [clusterBase*256, ...) and triangle t of the draw is clusterBase*256 + t, so
-// seq >> 8 indexes the frame's chunk table and later primitives win equal-depth ties.
-struct DChunk {               // what one geometry CTA needs, written on the device by expand_chunks_kernel
+// ceil(triCount / 256) slots of 256 numbers starting at seqBase, triangle t of the draw is seqBase + t,
+// so seq >> 8 indexes the frame's (draw, first triangle) table and later primitives win equal-depth ties.
+struct DChunk {               // what one geometry warp needs, written on the device by expand_chunks_kernel
     const float4* pos;        // mesh positions
     const uint32_t* clVerts;  // this cluster's distinct-vertex list
     const uint32_t* clTris;   // this cluster's packed triangles
     const uint32_t* clOrig;   // ... and their submission-order triangle numbers
-    uint32_t obj, firstTri;   // firstTri: cluster slot * 256 (used through seq >> 8 by the shading pass)
+    uint32_t obj, seqBase;    // draw; first sequence number of the draw
     uint32_t counts;          // vertexCount | triCount << 16
     uint32_t flags;           // draw flags (bit0 transparent, bit1 alpha-tested)
-    uint32_t seqBase;         // first sequence number of the draw
-    uint32_t pad[3];
     float4 bmin, bmax;        // object-space bounding box of the cluster
 };
-static_assert(sizeof(DChunk) == 96, "DChunk is read as six 16-byte words");
-// Cluster c of draw `obj` whose first frame cluster slot is `base`.
-VKR_HD DChunk make_chunk(const DObject& o, uint32_t obj, uint32_t c, uint32_t base) {
+static_assert(sizeof(DChunk) == 80, "DChunk is read as five 16-byte words");
+// Cluster c of draw `obj` whose first sequence slot is `seqSlot`.
+VKR_HD DChunk make_chunk(const DObject& o, uint32_t obj, uint32_t c, uint32_t seqSlot) {
     const uint2 info = o.clInfo[c];
     DChunk ch;
-    ch.pos = o.pos; ch.clVerts = o.clVerts + info.x; ch.clTris = o.clTris + (size_t)c * GEOM_BLOCK;
-    ch.clOrig = o.clOrig + (size_t)c * GEOM_BLOCK;
-    ch.obj = obj; ch.firstTri = c * GEOM_BLOCK; ch.counts = info.y;
+    ch.pos = o.pos; ch.clVerts = o.clVerts + info.x; ch.clTris = o.clTris + (size_t)c * CL_TRIS;
+    ch.clOrig = o.clOrig + (size_t)c * CL_TRIS;
+    ch.obj = obj; ch.seqBase = seqSlot * SEQ_SLOT; ch.counts = info.y;
     ch.flags = o.flags;
-    ch.seqBase = base * GEOM_BLOCK;
-    ch.pad[0] = ch.pad[1] = ch.pad[2] = 0;
     ch.bmin = o.clBounds[2 * c]; ch.bmax = o.clBounds[2 * c + 1];
     return ch;
 }
@@ -169,11 +169,12 @@ struct ShadeConst {
 struct ShadeBuffers {
     const uint64_t* vis;
     const DObject* objects;
-    const uint2* chunkObj;             // frame cluster slots: seq >> 8 -> (draw, first triangle of the slot)
+    const uint2* chunkObj;             // sequence slots: seq >> 8 -> (draw, first triangle of the slot)
     const DMaterial* materials;
     const DTexture* textures;          // VKR_MAX_BINDLESS slots
     const DTexture* cube;              // 6 faces (nullptr when no cubemap)
     const float* shadow;               // S*S*NUM_CASCADES
+    float* accum;                      // RGBA32F sums of the transparent pass (nullptr: the frame has none)
     uint16_t* hdr;                     // RGBA16F
     uint32_t* rgba8;
     const float* srgbLut;              // 256 floats

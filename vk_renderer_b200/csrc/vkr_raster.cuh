@@ -431,7 +431,7 @@ VKR_HD CornerAcc corner_merge(const CornerAcc& a, const CornerAcc& b) {
 }
 
 static const int CLUSTER_DRAW = 1, CLUSTER_CULLED = 0, CLUSTER_TEST = 2;
-static const int OCC_MAX_PIXELS = 2048;      // occlusion test only when the rectangle is at most this many pixels
+static const int OCC_MAX_PIXELS = 1024;      // occlusion test only when the rectangle is at most this many pixels
 struct ClusterRect { int32_t x0, y0, x1, y1; uint32_t zminBits; int32_t verdict; };
 
 VKR_HD ClusterRect cluster_finalize(const CornerAcc& a, const RasterTarget& rt) {
@@ -466,7 +466,7 @@ VKR_HD bool depth_hides(uint32_t storedBits, uint32_t zminBits) { return storedB
 // explicitly rounded operations in the oracle's order (texture2D + bary_at in oracle/ork.cpp).
 struct AlphaCtx {              // what the alpha test needs to find a primitive's texture and vertices
     const DObject* objects;
-    const DChunk* chunks;
+    const uint2* chunkObj;       // seq >> 8 -> (draw, first triangle of the slot)
     const DMaterial* materials;
     const DTexture* textures;
 };

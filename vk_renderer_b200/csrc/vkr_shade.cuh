@@ -270,8 +270,9 @@ struct Fragment {
 
 // The shaders' `discard` (albedo alpha < 0.5) was already applied in the raster stage (vkr_raster.cuh
 // alpha_passes), which owns that decision: a fragment that reached the visibility buffer is shaded.
-VKR_HD bool shade_fragment(const ShadeConst& sc, const ShadeBuffers& sb, const DMaterial& m, const Fragment& fr, f3& out) {
+VKR_HD bool shade_fragment(const ShadeConst& sc, const ShadeBuffers& sb, const DMaterial& m, const Fragment& fr, f3& out, bool alphaTest = false) {
     float4 albedoTex = texture2d(sb, m.albedoID, fr.u, fr.v, fr.dudx, fr.dvdx, fr.dudy, fr.dvdy);
+    if (alphaTest && albedoTex.w < 0.5f) return false;      // `discard` of a fragment that writes no depth (transparent pass)
     f3 base = f3{m.colorFactors[0], m.colorFactors[1], m.colorFactors[2]} * f3{albedoTex.x, albedoTex.y, albedoTex.z} * fr.color;
     f3 N = norm3(fr.normal);
     f3 L = norm3(f3{sc.lightVec[0], sc.lightVec[1], sc.lightVec[2]});
@@ -424,6 +425,33 @@ VKR_HD void fetch_fragment(const ShadeConst& sc, const ShadeBuffers& sb, uint32_
     fr.viewZ = (vm[2] * pw.x + vm[6] * pw.y) + (vm[10] * pw.z + vm[14] * pw.w);
 }
 
+// ---- "Transparent" material pass (src/vk_engine_init.cpp:545-547): depth test LESS_OR_EQUAL against the opaque
+// depth, no depth write, blend rgb = src.rgb * src.a + dst.rgb, a = src.a (src/vk_pipelines.cpp:108-118).
+// The blend is a sum, so fragments are shaded where they are rasterised and added (f32 atomics) into an
+// accumulation image that shade_pixel folds into the draw image before tone mapping; the reference rounds the
+// destination to f16 after every fragment, this path once — far inside the 1/255 tolerance.
+struct BlendSink {
+    const ShadeConst* sc; const ShadeBuffers* sb; uint32_t seq;
+    VKR_HD void put(int32_t px, int32_t py, float z) const {
+        const size_t pix = (size_t)py * sc->width + px;
+        const uint32_t stored = (uint32_t)(sb->vis[pix] >> 32);
+        if (!(f2bits(z) <= stored)) return;
+        // draw_skybox runs after the geometry (src/vk_engine_run.cpp:313) and overwrites every texel still at depth 1.0
+        if (sc->enableSkybox && sb->cube != nullptr && stored >= DEPTH_ONE_BITS) return;
+        Fragment fr;
+        uint32_t material;
+        fetch_fragment(*sc, *sb, seq, px, py, fr, material);
+        f3 col;
+        if (!shade_fragment(*sc, *sb, sb->materials[material], fr, col, true)) return;
+        float* acc = sb->accum + pix * 4;     // src alpha is 1.0 (outFragColor.a, shaders/mesh_pbr.frag:225)
+#if defined(__CUDA_ARCH__)
+        atomicAdd(acc, col.x); atomicAdd(acc + 1, col.y); atomicAdd(acc + 2, col.z); atomicAdd(acc + 3, 1.0f);
+#else
+        acc[0] += col.x; acc[1] += col.y; acc[2] += col.z; acc[3] += 1.0f;
+#endif
+    }
+};
+
 VKR_HD f3 tonemap_reinhard(f3 c) {      // shaders/tonemap.comp:13-19
     f3 m = {fdiv(c.x, c.x + 1.0f), fdiv(c.y, c.y + 1.0f), fdiv(c.z, c.z + 1.0f)};
     const float e = 1.0f / 2.2f;
@@ -463,6 +491,10 @@ VKR_HD void shade_pixel(const ShadeConst& sc, const ShadeBuffers& sb, int px, in
             b = sc.bgTop[2] * (1.0f - blend) + sc.bgBottom[2] * blend;
             a = sc.bgTop[3] * (1.0f - blend) + sc.bgBottom[3] * blend;
         } else { r = 0.0f; g = 0.0f; b = 0.0f; a = 1.0f; }   // clear (0,0,0,1), src/vk_engine_run.cpp:247
+    }
+    if (sb.accum != nullptr) {      // "Transparent" draws: additive blend accumulated by BlendSink
+        const float4 t = reinterpret_cast<const float4*>(sb.accum)[pix];
+        if (t.w > 0.0f) { r += t.x; g += t.y; b += t.z; a = 1.0f; }
     }
     // colour attachment store (RGBA16F), then tonemap.comp reads that image
     r = round_f16(r); g = round_f16(g); b = round_f16(b); a = round_f16(a);
