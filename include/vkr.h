@@ -130,6 +130,8 @@ typedef struct VkrFrameParams {
     int32_t fragShader;          /* VkrFragShader */
     int32_t scissor[4];          /* x, y, w, h; w==0||h==0 -> full extent.  Used for sort-first sharding. */
     VkrComputePushConstants background; /* backgroundEffects[0].data */
+    int32_t shadowScissor[4];    /* x, y, w, h in shadow texels; w==0||h==0 -> full map.  A sharded shadow pass renders
+                                    only this part of every layer; the rest is expected from the shadow-exchange hook. */
 } VkrFrameParams;
 
 typedef struct VkrConfig {
@@ -194,6 +196,14 @@ int vkr_build_material(VkrDevice* dev, const VkrMaterialConstants* params, VkrMa
  * + present blit — src/vk_engine_run.cpp:140-161,234-408.  Asynchronous. */
 int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject* objects,
              size_t objectCount, const VkrFrameParams* params);
+
+/* Sort-first sharding of the shadow pass: when set, vkr_draw calls `fn(user, shadow, layerBytes, layers, stream)`
+ * right after enqueueing the shadow pass, on the thread that called vkr_draw.  `shadow` is the device
+ * pointer of the D32 shadow image (layers * layerBytes), `stream` the cudaStream_t the pass was enqueued on:
+ * the hook enqueues on that stream whatever completes the map (e.g. an NCCL all-gather of row bands) and
+ * returns 0; the shading pass is ordered after it.  fn == NULL removes the hook. */
+typedef int (*VkrShadowExchangeFn)(void* user, void* shadow, size_t layerBytes, int layers, void* stream);
+int vkr_set_shadow_exchange(VkrDevice* dev, VkrShadowExchangeFn fn, void* user);
 
 /* Headless replacement of present (src/vk_engine_run.cpp:159-190). */
 int vkr_readback(VkrDevice* dev, VkrTarget what, void* dst, size_t dstBytes);          /* synchronous */

@@ -58,6 +58,7 @@ struct EmuDevice {
     std::vector<uint32_t> perm;          // passes x clusters
     uint32_t culled[2] = {0, 0};         // clusters dropped by the cluster test: [0] main, [1] shadow
     VkrEngineStats stats{};
+    VkrShadowExchangeFn shadowExchange = nullptr; void* shadowExchangeUser = nullptr;
     std::string err;
 };
 
@@ -304,6 +305,10 @@ int emu_draw(EmuDevice* d, const VkrGPUSceneData* scene, const VkrRenderObject* 
         std::fill(rt.depthBits, rt.depthBits + (size_t)d->S * d->S, DEPTH_ONE_BITS);
         run_pass<1>(d, plan, rt, plan.shadowMvp.data() + (size_t)layer * n * 16, 16, nChunks, d->perm.data() + (size_t)(1 + layer) * nChunks);
     }
+    if (plan.shadowLayers && d->shadowExchange &&
+        d->shadowExchange(d->shadowExchangeUser, d->shadowBits.data(), (size_t)d->S * d->S * 4, plan.shadowLayers, nullptr) != 0) {
+        d->err = "shadow exchange hook failed"; return VKR_ERROR_CUDA;
+    }
     RasterTarget rt = plan.mainTarget;
     rt.vis = d->vis.data();
     std::fill(d->vis.begin(), d->vis.end(), VIS_CLEAR);
@@ -347,6 +352,8 @@ int emu_readback(EmuDevice* d, int what, void* dst, size_t bytes) {
     return -1;
 }
 int emu_stats(EmuDevice* d, VkrEngineStats* out) { *out = d->stats; return 0; }
+int emu_set_shadow_exchange(EmuDevice* d, VkrShadowExchangeFn fn, void* user) { d->shadowExchange = fn; d->shadowExchangeUser = user; return 0; }
+void* emu_host_ptr(EmuDevice* d, int what) { return what == VKR_TARGET_RGBA8 ? (void*)d->rgba8.data() : nullptr; }
 void emu_culled(EmuDevice* d, uint32_t out[2]) { out[0] = d->culled[0]; out[1] = d->culled[1]; }
 const char* emu_last_error(EmuDevice* d) { return d->err.c_str(); }
 

@@ -83,6 +83,7 @@ class FrameParams(C.Structure):
         ("fragShader", C.c_int32),
         ("scissor", C.c_int32 * 4),
         ("background", ComputePushConstants),
+        ("shadowScissor", C.c_int32 * 4),
     ]
 
 
@@ -110,8 +111,12 @@ class EngineStats(C.Structure):
 VKR_SYMBOLS = [
     "create", "destroy", "upload_mesh", "create_image", "update_bindless_texture", "set_cubemap",
     "build_material", "draw", "readback", "readback_async", "sync", "stats", "get_timings",
-    "device_ptr", "launch_count", "upload_bytes", "cull_stats", "last_error", "version",
+    "device_ptr", "launch_count", "upload_bytes", "cull_stats", "set_shadow_exchange", "last_error", "version",
 ]
+
+
+# VkrShadowExchangeFn(user, shadow device pointer, bytes per layer, layers, cudaStream_t) -> 0 on success
+SHADOW_EXCHANGE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p)
 
 
 class VkrError(RuntimeError):
@@ -127,6 +132,8 @@ def default_frame_params(**kw) -> FrameParams:
     for k, v in kw.items():
         if k == "scissor":
             fp.scissor[:] = v
+        elif k == "shadowScissor":
+            fp.shadowScissor[:] = v
         else:
             setattr(fp, k, v)
     return fp
@@ -198,8 +205,11 @@ class Renderer:
                 "launch_count": ([p], C.c_int),
                 "upload_bytes": ([p], C.c_size_t),
                 "cull_stats": ([p, C.POINTER(C.c_uint32)], C.c_int),
+                "set_shadow_exchange": ([p, SHADOW_EXCHANGE_FN, p], C.c_int),
                 "version": ([], C.c_char_p),
             })
+        if self.prefix == "emu":     # the test-only host emulation (tests/emu) exposes the sharding hooks too
+            sigs.update({"set_shadow_exchange": ([p, SHADOW_EXCHANGE_FN, p], C.c_int), "host_ptr": ([p, C.c_int], C.c_void_p)})
         for name, (args, res) in sigs.items():
             fn = self._f(name)
             fn.argtypes, fn.restype = args, res
@@ -300,6 +310,28 @@ class Renderer:
 
     def launch_count(self) -> int:
         return self._f("launch_count")(self.dev)
+
+    def set_shadow_exchange(self, fn):
+        """fn(shadow_ptr, layer_bytes, layers, stream) -> None, called inside draw() after the shadow pass is enqueued."""
+        if fn is None:
+            self._shadow_cb = None
+            self._check(self._f("set_shadow_exchange")(self.dev, C.cast(None, SHADOW_EXCHANGE_FN), None))
+            return
+
+        def tramp(user, shadow, layer_bytes, layers, stream):
+            try:
+                fn(shadow, layer_bytes, layers, stream)
+                return 0
+            except Exception as e:      # never let an exception cross the C boundary
+                import sys
+                print(f"shadow exchange hook failed: {e!r}", file=sys.stderr)
+                return 1
+        self._shadow_cb = SHADOW_EXCHANGE_FN(tramp)     # keep the trampoline alive
+        self._check(self._f("set_shadow_exchange")(self.dev, self._shadow_cb, None))
+
+    def host_ptr(self, what: int):
+        """(emulation backend only) host address and size of a target."""
+        return self._f("host_ptr")(self.dev, what), self.width * self.height * 4
 
     def cull_stats(self) -> dict:
         out = (C.c_uint32 * 4)()

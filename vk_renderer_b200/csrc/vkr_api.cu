@@ -395,6 +395,7 @@ struct VkrDevice {
     bool tevValid = false, shadowTimed = false;
     float timings[VKR_T_COUNT] = {0};
 
+    VkrShadowExchangeFn shadowExchange = nullptr; void* shadowExchangeUser = nullptr;
     VkrEngineStats stats{};
     uint32_t lastOpaqueClusters = 0, lastShadowClusters = 0;
     int launches = 0;
@@ -801,6 +802,10 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
             CK(cudaMemcpyAsync(dev->countersHost + 4, dev->qShadow.counters, 16, cudaMemcpyDeviceToHost, ss));
         }
         if (timing) CK(cudaEventRecord(dev->tev[8], ss));
+        if (dev->shadowExchange) {
+            if (dev->shadowExchange(dev->shadowExchangeUser, dev->shadowBits, (size_t)dev->S * dev->S * 4, plan.shadowLayers, (void*)ss) != 0)
+                return dev->fail(VKR_ERROR_CUDA, "shadow exchange hook failed");
+        }
         CK(cudaEventRecord(dev->evShadow, ss));
     }
 
@@ -954,6 +959,12 @@ int vkr_device_ptr(VkrDevice* dev, VkrTarget what, void** ptr, size_t* bytes) {
     const void* src; size_t n;
     if (target_info(dev, what, &src, &n) || !src) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_device_ptr: target has no linear buffer");
     *ptr = const_cast<void*>(src); *bytes = n;
+    return VKR_SUCCESS;
+}
+
+int vkr_set_shadow_exchange(VkrDevice* dev, VkrShadowExchangeFn fn, void* user) {
+    if (!dev) return VKR_ERROR_INVALID_ARGUMENT;
+    dev->shadowExchange = fn; dev->shadowExchangeUser = user;
     return VKR_SUCCESS;
 }
 

@@ -325,6 +325,11 @@ inline std::string plan_frame(const VkrGPUSceneData* scene, const VkrRenderObjec
     st.sx0 = st.sy0 = 0; st.sx1 = st.sy1 = (int32_t)S;
     st.halfW = st.halfH = (float)S * 0.5f;
     st.halfW256 = st.halfH256 = (float)S * 128.0f;
+    if (fp->shadowScissor[2] > 0 && fp->shadowScissor[3] > 0) {
+        st.sx0 = std::max(0, fp->shadowScissor[0]); st.sy0 = std::max(0, fp->shadowScissor[1]);
+        st.sx1 = std::min((int32_t)S, fp->shadowScissor[0] + fp->shadowScissor[2]);
+        st.sy1 = std::min((int32_t)S, fp->shadowScissor[1] + fp->shadowScissor[3]);
+    }
     st.cullFront = 1;                                   // VK_CULL_MODE_FRONT_BIT (src/vk_engine_init.cpp:441)
     return std::string();
 }
