@@ -189,7 +189,8 @@ def workload_config(info, n_gpus):
     return {"workload": "BASELINE config 4: 10M-triangle instanced scene (10k-tri sphere x 1000), 3840x2160, PBR mesh_pbr.frag, "
                         "2048^2 PCF shadow, skybox, tonemap",
             "triangles": info["tris"], "objects": info["nobj"], "resolution": [W, H], "shadow_extent": S,
-            "parallelism": "single GPU" if n_gpus == 1 else f"sort-first {n_gpus} row bands + NCCL all-gather of RGBA8 bands",
+            "parallelism": "single GPU" if n_gpus == 1 else f"sort-first: {n_gpus} row bands of the frame and of the shadow map, geometry replicated, "
+                                                                 "NCCL all-gather of the shadow bands (inside the frame) and of the RGBA8 bands",
             "l2": "per-frame working set (visibility 66 MB + HDR 66 MB + RGBA8 33 MB + shadow 17 MB) exceeds the 126 MB L2; no explicit flush"}
 
 
@@ -217,38 +218,19 @@ def run_b200(args):
     r = capi.Renderer(lib, "vkr", W, H, shadow_extent=S, device=local, stream=stream, flags=capi.CONFIG_TIMINGS)
     sd, objs, fp, info = build_scene(r)
 
-    # ---- sort-first: this rank's row band, and the draws that can touch it
-    band_h = H // world
-    y0 = rank * band_h
-    if world > 1:
-        fp.scissor[:] = (0, y0, W, band_h)
-        vp = np.array(sd.viewproj[:], np.float32).reshape(4, 4).T
-        keep = band_frustum_visible(objs, vp, np.zeros(3, np.float32), np.float32(np.sqrt(3.0)),
-                                    2.0 * y0 / H - 1.0, 2.0 * (y0 + band_h) / H - 1.0)
-        my_objs = np.ascontiguousarray(objs[keep])
-    else:
-        my_objs = objs
-    # shadow casters are the whole camera-visible list on every rank (replicated shadow map):
-    # draw the shadow pass with all objects, the main pass with this band's objects
-    # (v1: one draw list for both passes -> keep all objects when shadows are on)
-    if world > 1 and fp.enableShadows:
-        my_objs = objs
-
-    gathered = None
-    band = None
-    if world > 1:
-        gathered = torch.empty((H, W, 4), dtype=torch.uint8, device="cuda")
-
-    class _Ptr:
-        def __init__(self, ptr, nbytes):
-            self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 3}
+    # ---- sort-first: this rank's row band of the frame and of the shadow map (vk_renderer_b200/sharding.py).
+    # Every rank keeps the whole draw list: the geometry pass's cluster test drops what falls outside the band.
+    from vk_renderer_b200.sharding import TileSharder, row_band
+    sharder = TileSharder(r, rank, world, cuda=True, shadow_group=dist.new_group()) if world > 1 else None
+    y0, band_h = row_band(rank, world, H)
+    if sharder:
+        fp = sharder.frame_params(fp)
+    my_objs = objs
 
     def step():
         r.draw(sd, my_objs, fp)
-        if world > 1:
-            ptr, nbytes = r.device_ptr(capi.TARGET_RGBA8)
-            full = torch.as_tensor(_Ptr(ptr, nbytes), device="cuda").view(H, W, 4)
-            dist.all_gather_into_tensor(gathered.view(-1), full[y0:y0 + band_h].reshape(-1))
+        if sharder:
+            sharder.gather(async_op=True)       # frame i's gather overlaps frame i+1's rendering (FRAME_OVERLAP = 2)
 
     def barrier():
         torch.cuda.synchronize()
@@ -264,9 +246,13 @@ def run_b200(args):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     kern_ms, launches = [], 0
+    t_issue = time.perf_counter()
     for _ in range(args.steps):
         step()
         launches += r.launch_count()
+    host_issue_ms = (time.perf_counter() - t_issue) * 1000.0 / args.steps     # host time to ISSUE a step (no device wait)
+    if sharder:
+        sharder.wait()                           # the last gathers are part of the timed region
     e1.record()
     barrier()
     r.sync()
@@ -279,9 +265,11 @@ def run_b200(args):
     clocks = sampler.stop() if sampler else None
 
     # ---- dominant-kernel duration, averaged over a few extra frames (events around the kernel itself)
-    gk = []
+    gk, host_call = [], []
     for _ in range(5):
+        t0 = time.perf_counter()
         r.draw(sd, my_objs, fp)
+        host_call.append((time.perf_counter() - t0) * 1000.0)      # vkr_draw on an idle device: pure host cost of one call
         r.sync()
         gk.append(r.timings())
     avg = {k: float(np.mean([g[k] for g in gk])) for k in gk[0]}
@@ -291,18 +279,16 @@ def run_b200(args):
     pinned = [torch.empty((H, W, 4), dtype=torch.uint8).pin_memory() for _ in range(2)]
     n = len(my_objs)
     h2d = n * 176 + (n + 1) * 4 + ((info["idx_per_mesh"] // 3 + 255) // 256) * n * 8 + n * 64 + 512
-    d2h = W * band_h * 4 if world > 1 else W * H * 4
+    d2h = W * H * 4                                         # rank 0 reads the assembled frame back
     barrier()
     t0 = time.perf_counter()
     for i in range(args.steps):
         objs_frame = np.array(my_objs, copy=True)            # the host rebuilds its draw list every frame (update_scene)
         r.draw(sd, objs_frame, fp)
-        if world > 1:
-            ptr, nbytes = r.device_ptr(capi.TARGET_RGBA8)
-            full = torch.as_tensor(_Ptr(ptr, nbytes), device="cuda").view(H, W, 4)
-            dist.all_gather_into_tensor(gathered.view(-1), full[y0:y0 + band_h].reshape(-1))
+        if sharder:
+            buf = sharder.gather(async_op=False)
             if rank == 0:
-                pinned[i % 2].copy_(gathered, non_blocking=True)
+                pinned[i % 2].copy_(sharder.image(buf), non_blocking=True)
         else:
             r.readback_async(capi.TARGET_RGBA8, pinned[i % 2].data_ptr(), W * H * 4)
     r.sync()
@@ -333,6 +319,7 @@ def run_b200(args):
                          "frac": achieved / peak, "traffic": None, "algorithmic_bytes": gk_bytes, "kernel_ms": gk_ms,
                          "peak_source": peak_src},
             "pass_ms": avg,
+            "host_issue_ms_per_step": host_issue_ms, "host_vkr_draw_call_ms": float(np.median(host_call)),
             "cluster_culling": cull,
             "e2e": {"value": args.steps / e2e_s, "unit": "frames/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                     "checksum": checksum},

@@ -42,8 +42,11 @@ def host_tensor_from_ptr(ptr: int, nbytes: int) -> torch.Tensor:
 
 
 class TileSharder:
-    def __init__(self, renderer, rank: int, world: int, cuda: bool, group=None, shard_shadow: bool = True):
+    def __init__(self, renderer, rank: int, world: int, cuda: bool, group=None, shard_shadow: bool = True, shadow_group=None):
+        """`shadow_group`: a second process group (its own communicator, hence its own NCCL stream) for the shadow
+        exchange, so that frame i+1's shadow bands do not queue behind frame i's image gather."""
         self.r, self.rank, self.world, self.cuda, self.group = renderer, rank, world, cuda, group
+        self.shadow_group = shadow_group if shadow_group is not None else group
         self.W, self.H, self.S = renderer.width, renderer.height, renderer.shadow_extent
         self.y0, self.h = row_band(rank, world, self.H)
         self.rows_per = (self.H + world - 1) // world
@@ -77,7 +80,7 @@ class TileSharder:
         with ctx:
             for layer in range(layers):
                 out = full[layer]
-                dist.all_gather_into_tensor(out.view(-1), out[self.s0:self.s0 + self.sh].reshape(-1), group=self.group)
+                dist.all_gather_into_tensor(out.view(-1), out[self.s0:self.s0 + self.sh].reshape(-1), group=self.shadow_group)
 
     def gather(self, async_op: bool = False) -> torch.Tensor:
         """All-gather the presented image of the frame just drawn.  Returns the buffer it lands in (valid once
@@ -89,9 +92,10 @@ class TileSharder:
             ptr, nbytes = self._rgba_ptr()
             out.view(-1).copy_(self._from_ptr(ptr, nbytes))
             return out
-        if self._pending[k] is not None:
-            self._pending[k].wait()
-            self._pending[k] = None
+        # The renderer double-buffers the presented image: the NEXT draw writes the buffer the PREVIOUS frame's
+        # gather reads, so that gather must be complete (stream-ordered) before this call returns; the gather issued
+        # here then overlaps the next draw.  (Its own landing buffer was released by the same rule one frame ago.)
+        self.wait()
         ptr, nbytes = self._rgba_ptr()
         img = self._from_ptr(ptr, nbytes).view(self.H, self.W, 4)
         if self.even:
