@@ -78,22 +78,6 @@ def algorithmic_bytes(info, width=W, height=H, shadow=S, layers=1):
     return frame, geom_kernel
 
 
-def band_frustum_visible(objs, viewproj, center, radius, y0_ndc, y1_ndc):
-    """update_scene's sphere-vs-plane test (src/vk_engine_run.cpp:461-480) against the sub-frustum of a
-    row band: the top/bottom planes are replaced by y_ndc >= y0 and y_ndc <= y1."""
-    M = viewproj  # math convention rows
-    planes = [M[3] + M[0], M[3] - M[0], M[1] - y0_ndc * M[3], y1_ndc * M[3] - M[1], M[2], M[3] - M[2]]
-    keep = np.ones(len(objs), bool)
-    T = objs["transform"].reshape(-1, 4, 4).transpose(0, 2, 1)  # (n, row, col)
-    c = (T @ np.append(center, 1.0).astype(np.float32))[:, :3]
-    scale = np.sqrt((T[:, :3, :3] ** 2).sum(axis=1)).max(axis=1)
-    rad = radius * scale
-    for p in planes:
-        p = p / np.linalg.norm(p[:3])
-        keep &= (c @ p[:3] + p[3]) >= -rad
-    return keep
-
-
 # ------------------------------------------------------------------------------- helpers
 class ClockSampler:
     def __init__(self, device_index):
@@ -218,19 +202,20 @@ def run_b200(args):
     r = capi.Renderer(lib, "vkr", W, H, shadow_extent=S, device=local, stream=stream, flags=capi.CONFIG_TIMINGS)
     sd, objs, fp, info = build_scene(r)
 
-    # ---- sort-first: this rank's row band of the frame and of the shadow map (vk_renderer_b200/sharding.py).
+    # ---- sort-first (native, include/vkr.h vkr_shard_init): this rank renders its rows of the frame and of the shadow
+    # map; libvkr all-gathers the shadow bands inside the frame and the RGBA8 bands after it over NCCL, the latter
+    # overlapped with the next frame.  torch.distributed is the plumbing: it carries the communicator ids.
     # Every rank keeps the whole draw list: the geometry pass's cluster test drops what falls outside the band.
-    from vk_renderer_b200.sharding import TileSharder, row_band
-    sharder = TileSharder(r, rank, world, cuda=True, shadow_group=dist.new_group()) if world > 1 else None
-    y0, band_h = row_band(rank, world, H)
-    if sharder:
-        fp = sharder.frame_params(fp)
+    if world > 1:
+        ids = torch.zeros(2 * capi.COMM_ID_BYTES, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            ids.copy_(torch.frombuffer(bytearray(r.comm_unique_ids()), dtype=torch.uint8))
+        dist.broadcast(ids, 0)
+        r.shard_init(rank, world, ids.cpu().numpy().tobytes())
     my_objs = objs
 
     def step():
         r.draw(sd, my_objs, fp)
-        if sharder:
-            sharder.gather(async_op=True)       # frame i's gather overlaps frame i+1's rendering (FRAME_OVERLAP = 2)
 
     def barrier():
         torch.cuda.synchronize()
@@ -251,8 +236,8 @@ def run_b200(args):
         step()
         launches += r.launch_count()
     host_issue_ms = (time.perf_counter() - t_issue) * 1000.0 / args.steps     # host time to ISSUE a step (no device wait)
-    if sharder:
-        sharder.wait()                           # the last gathers are part of the timed region
+    if world > 1:
+        r.sync()                                 # the last gather (on libvkr's gather stream) is part of the timed region
     e1.record()
     barrier()
     r.sync()
@@ -285,10 +270,9 @@ def run_b200(args):
     for i in range(args.steps):
         objs_frame = np.array(my_objs, copy=True)            # the host rebuilds its draw list every frame (update_scene)
         r.draw(sd, objs_frame, fp)
-        if sharder:
-            buf = sharder.gather(async_op=False)
+        if world > 1:
             if rank == 0:
-                pinned[i % 2].copy_(sharder.image(buf), non_blocking=True)
+                r.readback_async(capi.TARGET_RGBA8_GATHERED, pinned[i % 2].data_ptr(), W * H * 4)
         else:
             r.readback_async(capi.TARGET_RGBA8, pinned[i % 2].data_ptr(), W * H * 4)
     r.sync()

@@ -157,7 +157,8 @@ typedef enum VkrTarget {
     VKR_TARGET_HDR16F = 1,     /* _drawImage, RGBA16F, W*H*8 */
     VKR_TARGET_DEPTH = 2,      /* _depthImage, D32, W*H*4 */
     VKR_TARGET_SHADOW = 3,     /* _shadowImage, D32, S*S*4*NUM_CASCADES */
-    VKR_TARGET_PRIMID = 4      /* uint32 per pixel: submission-order primitive id, 0xFFFFFFFF = none */
+    VKR_TARGET_PRIMID = 4,     /* uint32 per pixel: submission-order primitive id, 0xFFFFFFFF = none */
+    VKR_TARGET_RGBA8_GATHERED = 5 /* sharded devices: the presented image assembled from every rank's rows (vkr_shard_init) */
 } VkrTarget;
 
 /* Pass indices for vkr_get_timings. */
@@ -204,6 +205,20 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
  * returns 0; the shading pass is ordered after it.  fn == NULL removes the hook. */
 typedef int (*VkrShadowExchangeFn)(void* user, void* shadow, size_t layerBytes, int layers, void* stream);
 int vkr_set_shadow_exchange(VkrDevice* dev, VkrShadowExchangeFn fn, void* user);
+
+/* Native sort-first sharding over NCCL (one VkrDevice per rank, one rank per GPU of an NVLink/NVSwitch box).
+ * The reference has no counterpart (single queue, src/vk_engine_init.cpp:80).  vkr_comm_unique_id fills
+ * VKR_COMM_ID_BYTES bytes (an ncclUniqueId); rank 0 makes TWO of them and hands them to every rank through the
+ * host's own plumbing (torch.distributed broadcast, MPI, a file...).  After vkr_shard_init, vkr_draw on this device
+ *   - renders rows [rank*H/n, (rank+1)*H/n) of the frame and rows [rank*S/n, ...) of every shadow layer
+ *     (the cluster test drops everything else before any vertex work),
+ *   - all-gathers the shadow bands on the shadow stream (communicator 0) before shading,
+ *   - all-gathers the presented RGBA8 bands (communicator 1) on its own stream, overlapped with the next frame,
+ *     into VKR_TARGET_RGBA8_GATHERED (double-buffered like the presented image).
+ * H and the shadow extent must be multiples of nranks.  Draw lists must be identical on every rank. */
+#define VKR_COMM_ID_BYTES 128
+int vkr_comm_unique_id(void* out, size_t bytes);
+int vkr_shard_init(VkrDevice* dev, int rank, int nranks, const void* twoIds, size_t bytes);
 
 /* Headless replacement of present (src/vk_engine_run.cpp:159-190). */
 int vkr_readback(VkrDevice* dev, VkrTarget what, void* dst, size_t dstBytes);          /* synchronous */

@@ -219,14 +219,14 @@ static bool cluster_survives(const DChunk& ch, const float* mvp, const RasterTar
 // PASS: 0 main, 1 shadow, 2 transparent (clusters [first, first + nChunks) in natural order, BlendSink)
 template <int PASS>
 static void run_pass(EmuDevice* d, const FramePlan& plan, RasterTarget rt, const float* mvps, uint32_t stride, unsigned nChunks,
-                     const uint32_t* perm, unsigned first = 0, const ShadeBuffers* sbT = nullptr) {
+                     const uint32_t* perm, unsigned first = 0, const ShadeBuffers* sbT = nullptr, unsigned cutoutChunks = 0) {
     const bool SHADOW = PASS == 1;
     Queues q{d->ltris.data(), d->litems.data(), d->counters, (uint32_t)d->ltris.size(), (uint32_t)d->litems.size()};
     d->counters[0] = d->counters[1] = d->counters[2] = 0;
     std::vector<CachedVtx> svtx(CL_VERTS);
     const AlphaCtx ax{plan.objects.data(), d->chunkObj.data(), d->materials.data(), d->tex.data()};
     if (PASS == 0)
-        for (unsigned c = 0; c < nChunks; ++c) {             // geometry_cutout_kernel: natural order, no culling
+        for (unsigned c = 0; c < cutoutChunks; ++c) {        // geometry_cutout_kernel: natural order, no culling
             const DChunk ch = d->chunks[c];
             if (!(ch.flags & 2u)) continue;
             const DObject& ob = plan.objects[ch.obj];
@@ -303,7 +303,7 @@ int emu_draw(EmuDevice* d, const VkrGPUSceneData* scene, const VkrRenderObject* 
         RasterTarget rt = plan.shadowTarget;
         rt.depthBits = d->shadowBits.data() + (size_t)layer * d->S * d->S;
         std::fill(rt.depthBits, rt.depthBits + (size_t)d->S * d->S, DEPTH_ONE_BITS);
-        run_pass<1>(d, plan, rt, plan.shadowMvp.data() + (size_t)layer * n * 16, 16, nChunks, d->perm.data() + (size_t)(1 + layer) * nChunks);
+        run_pass<1>(d, plan, rt, plan.shadowMvp.data() + (size_t)layer * n * 16, 16, plan.passSlots[1 + layer], d->perm.data() + (size_t)(1 + layer) * nChunks);
     }
     if (plan.shadowLayers && d->shadowExchange &&
         d->shadowExchange(d->shadowExchangeUser, d->shadowBits.data(), (size_t)d->S * d->S * 4, plan.shadowLayers, nullptr) != 0) {
@@ -313,7 +313,7 @@ int emu_draw(EmuDevice* d, const VkrGPUSceneData* scene, const VkrRenderObject* 
     rt.vis = d->vis.data();
     std::fill(d->vis.begin(), d->vis.end(), VIS_CLEAR);
     const unsigned opaqueChunks = plan.opaqueClusters;
-    run_pass<0>(d, plan, rt, (const float*)plan.objects.data(), sizeof(DObject) / 4, opaqueChunks, d->perm.data());
+    run_pass<0>(d, plan, rt, (const float*)plan.objects.data(), sizeof(DObject) / 4, plan.passSlots[0], d->perm.data(), 0, nullptr, opaqueChunks);
     if (d->counters[2]) { d->err = "queue overflow"; return VKR_ERROR_CAPACITY; }
     ShadeBuffers sb{};
     sb.accum = nullptr;

@@ -12,7 +12,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 
 
-def _worker(rank, world, port, scene, W, H, S, out_dir):
+def _worker(rank, world, port, scene, W, H, S, out_dir, native):
     sys.path.insert(0, ROOT)
     sys.path.insert(0, HERE)
     import torch
@@ -29,21 +29,32 @@ def _worker(rank, world, port, scene, W, H, S, out_dir):
     lib = vk_renderer_b200.load()
     r = capi.Renderer(lib, "vkr", W, H, shadow_extent=S, device=rank, stream=torch.cuda.current_stream().cuda_stream)
     sd, objs, fp = scenes.SCENES[scene](r)
-    sh = TileSharder(r, rank, world, cuda=True, shadow_group=dist.new_group())
-    fp = sh.frame_params(fp)
-    for _ in range(3):
-        r.draw(sd, objs, fp)
-        buf = sh.gather(async_op=True)
-    sh.wait()
-    torch.cuda.synchronize()
-    np.save(os.path.join(out_dir, f"img{rank}.npy"), sh.image(buf).cpu().numpy())
+    if native:      # libvkr's own NCCL sharding (vkr_shard_init); torch.distributed only carries the communicator ids
+        ids = torch.zeros(2 * capi.COMM_ID_BYTES, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            ids.copy_(torch.frombuffer(bytearray(r.comm_unique_ids()), dtype=torch.uint8))
+        dist.broadcast(ids, 0)
+        r.shard_init(rank, world, ids.cpu().numpy().tobytes())
+        for _ in range(3):
+            r.draw(sd, objs, fp)
+        img = r.readback(capi.TARGET_RGBA8_GATHERED)
+    else:           # the same sharding driven from Python over torch.distributed (vk_renderer_b200/sharding.py)
+        sh = TileSharder(r, rank, world, cuda=True, shadow_group=dist.new_group())
+        fp = sh.frame_params(fp)
+        for _ in range(3):
+            r.draw(sd, objs, fp)
+            buf = sh.gather(async_op=True)
+        sh.wait()
+        torch.cuda.synchronize()
+        img = sh.image(buf).cpu().numpy()
+    np.save(os.path.join(out_dir, f"img{rank}.npy"), img)
     np.save(os.path.join(out_dir, f"shadow{rank}.npy"), r.readback(capi.TARGET_SHADOW))
     r.close()
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("scene", ["lattice", "basic_csm"])
-def test_nccl_sharded_frame_equals_single_gpu(vkr_lib, tmp_path, scene):
+@pytest.mark.parametrize("scene,native", [("lattice", True), ("basic_csm", True), ("lattice", False)])
+def test_nccl_sharded_frame_equals_single_gpu(vkr_lib, tmp_path, scene, native):
     import torch
     import torch.multiprocessing as mp
     import scenes
@@ -51,7 +62,7 @@ def test_nccl_sharded_frame_equals_single_gpu(vkr_lib, tmp_path, scene):
     world = min(torch.cuda.device_count(), 4)
     if world < 2:
         pytest.skip("needs >= 2 GPUs")
-    W, H, S = 640, 360 if world != 3 else 363, 1024 if world != 3 else 1023
+    W, H, S = 640, 360, 1024 if world != 3 else 1023
     r = capi.Renderer(vkr_lib, "vkr", W, H, shadow_extent=S)
     sd, objs, fp = scenes.SCENES[scene](r)
     r.draw(sd, objs, fp)
@@ -60,7 +71,7 @@ def test_nccl_sharded_frame_equals_single_gpu(vkr_lib, tmp_path, scene):
     layers = 4 if fp.shadowMode == 3 else 1
     r.close()
     port = 29700 + (os.getpid() % 2000)
-    mp.spawn(_worker, args=(world, port, scene, W, H, S, str(tmp_path)), nprocs=world, join=True)
+    mp.spawn(_worker, args=(world, port, scene, W, H, S, str(tmp_path), native), nprocs=world, join=True)
     for rank in range(world):
         got = np.load(tmp_path / f"img{rank}.npy")
         assert np.array_equal(got, want), f"rank {rank}: {(got != want).any(-1).sum()} pixels differ"

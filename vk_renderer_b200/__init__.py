@@ -30,6 +30,12 @@ def load() -> ctypes.CDLL:
                 f"{LIBVKR_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
                 "(nvcc, sm_100a). There is no CPU fallback."
             )
+        # libvkr links libnccl.so.2 (native sort-first sharding).  PyTorch ships its own copy of that soname and refuses
+        # to start on an older one, so when torch is installed let it map its NCCL first; a C++ host gets the system's.
+        try:
+            import torch  # noqa: F401
+        except ImportError:
+            pass
         _lib = ctypes.CDLL(LIBVKR_PATH, mode=ctypes.RTLD_GLOBAL)
     return _lib
 

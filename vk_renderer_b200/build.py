@@ -42,7 +42,9 @@ def build_libvkr(force=False, verbose=False):
     deps = _sources([CSRC, os.path.join(ROOT, "include")], (".cu", ".cuh", ".h"))
     if not force and _newer(target, deps):
         return target
-    cmd = ["nvcc", *NVCC_FLAGS, "-o", target, os.path.join(CSRC, "vkr_api.cu")]
+    # -lnccl: the native sort-first sharding (vkr_shard_init).  In a process that has imported torch the loader
+    # resolves libnccl.so.2 to the copy torch already mapped; a plain C++ host gets the system library.
+    cmd = ["nvcc", *NVCC_FLAGS, "-o", target, os.path.join(CSRC, "vkr_api.cu"), "-lnccl"]
     if verbose:
         cmd.insert(1, "-Xptxas=-v")
     subprocess.run(cmd, check=True)

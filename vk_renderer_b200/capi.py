@@ -18,7 +18,8 @@ FORMAT_UNORM, FORMAT_SRGB = 0, 1
 SAMPLER_NEAREST, SAMPLER_LINEAR = 0, 1
 PASS_MAIN_COLOR, PASS_TRANSPARENT, PASS_OTHER = 0, 1, 2
 FRAG_PBR, FRAG_LAMBERT = 0, 1
-TARGET_RGBA8, TARGET_HDR16F, TARGET_DEPTH, TARGET_SHADOW, TARGET_PRIMID = range(5)
+TARGET_RGBA8, TARGET_HDR16F, TARGET_DEPTH, TARGET_SHADOW, TARGET_PRIMID, TARGET_RGBA8_GATHERED = range(6)
+COMM_ID_BYTES = 128
 CONFIG_TIMINGS = 1
 T_NAMES = ["upload", "shadow", "geometry", "shade", "transparent", "post", "total", "geom_kernel", "large_kernel", "clear"]
 
@@ -111,7 +112,7 @@ class EngineStats(C.Structure):
 VKR_SYMBOLS = [
     "create", "destroy", "upload_mesh", "create_image", "update_bindless_texture", "set_cubemap",
     "build_material", "draw", "readback", "readback_async", "sync", "stats", "get_timings",
-    "device_ptr", "launch_count", "upload_bytes", "cull_stats", "set_shadow_exchange", "last_error", "version",
+    "device_ptr", "launch_count", "upload_bytes", "cull_stats", "set_shadow_exchange", "comm_unique_id", "shard_init", "last_error", "version",
 ]
 
 
@@ -206,6 +207,8 @@ class Renderer:
                 "upload_bytes": ([p], C.c_size_t),
                 "cull_stats": ([p, C.POINTER(C.c_uint32)], C.c_int),
                 "set_shadow_exchange": ([p, SHADOW_EXCHANGE_FN, p], C.c_int),
+                "comm_unique_id": ([p, C.c_size_t], C.c_int),
+                "shard_init": ([p, C.c_int, C.c_int, p, C.c_size_t], C.c_int),
                 "version": ([], C.c_char_p),
             })
         if self.prefix == "emu":     # the test-only host emulation (tests/emu) exposes the sharding hooks too
@@ -271,7 +274,7 @@ class Renderer:
 
     def readback(self, what: int) -> np.ndarray:
         W, H, S = self.width, self.height, self.shadow_extent
-        if what == TARGET_RGBA8:
+        if what in (TARGET_RGBA8, TARGET_RGBA8_GATHERED):
             out = np.empty((H, W, 4), np.uint8)
         elif what == TARGET_HDR16F:
             out = np.empty((H, W, 4), np.float16)
@@ -328,6 +331,18 @@ class Renderer:
                 return 1
         self._shadow_cb = SHADOW_EXCHANGE_FN(tramp)     # keep the trampoline alive
         self._check(self._f("set_shadow_exchange")(self.dev, self._shadow_cb, None))
+
+    def comm_unique_ids(self) -> bytes:
+        """Two communicator ids (rank 0 calls this and broadcasts the result)."""
+        buf = C.create_string_buffer(2 * COMM_ID_BYTES)
+        for i in range(2):
+            rc = self._f("comm_unique_id")(C.byref(buf, i * COMM_ID_BYTES), COMM_ID_BYTES)
+            if rc != SUCCESS:
+                raise VkrError(rc, "vkr_comm_unique_id")
+        return buf.raw
+
+    def shard_init(self, rank: int, nranks: int, ids: bytes):
+        self._check(self._f("shard_init")(self.dev, rank, nranks, ids, len(ids)))
 
     def host_ptr(self, what: int):
         """(emulation backend only) host address and size of a target."""

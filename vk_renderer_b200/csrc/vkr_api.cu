@@ -5,6 +5,7 @@
 // All work is enqueued on one stream; vkr_draw never blocks on the device.
 #include <cuda_runtime.h>
 #include <cuda_fp16.h>
+#include <nccl.h>
 
 #include <algorithm>
 #include <cmath>
@@ -396,6 +397,13 @@ struct VkrDevice {
     float timings[VKR_T_COUNT] = {0};
 
     VkrShadowExchangeFn shadowExchange = nullptr; void* shadowExchangeUser = nullptr;
+    // native sort-first sharding (vkr_shard_init)
+    int shardRank = 0, shardRanks = 1;
+    ncclComm_t commShadow = nullptr, commFrame = nullptr;
+    cudaStream_t gatherStream = nullptr;
+    uint32_t* gathered[VKR_FRAME_OVERLAP] = {nullptr, nullptr};
+    cudaEvent_t gatheredEv[VKR_FRAME_OVERLAP] = {nullptr, nullptr};
+    bool gatheredValid[VKR_FRAME_OVERLAP] = {false, false};
     VkrEngineStats stats{};
     uint32_t lastOpaqueClusters = 0, lastShadowClusters = 0;
     int launches = 0;
@@ -488,7 +496,11 @@ int vkr_create(const VkrConfig* cfg, VkrDevice** out) {
         if (cfg->stream) dev->stream = (cudaStream_t)cfg->stream;
         else { CK(cudaStreamCreateWithFlags(&dev->stream, cudaStreamNonBlocking)); dev->ownStream = true; }
         CK(cudaStreamCreateWithFlags(&dev->copyStream, cudaStreamNonBlocking));
-        CK(cudaStreamCreateWithFlags(&dev->shadowStream, cudaStreamNonBlocking));
+        // the shadow stream carries the shadow exchange of a sharded frame: highest priority, so that the collective's
+        // CTAs are dispatched ahead of the main pass's thousands of queued geometry CTAs
+        int prLo = 0, prHi = 0;
+        CK(cudaDeviceGetStreamPriorityRange(&prLo, &prHi));
+        CK(cudaStreamCreateWithPriority(&dev->shadowStream, cudaStreamNonBlocking, prHi));
         CK(cudaStreamCreateWithFlags(&dev->upStream, cudaStreamNonBlocking));
         CK(cudaEventCreateWithFlags(&dev->evFork, cudaEventDisableTiming));
         CK(cudaEventCreateWithFlags(&dev->evShadow, cudaEventDisableTiming));
@@ -555,6 +567,10 @@ void vkr_destroy(VkrDevice* dev) {
     }
     for (auto& e : dev->tev) if (e) cudaEventDestroy(e);
     if (dev->countersHost) cudaFreeHost(dev->countersHost);
+    if (dev->commShadow) ncclCommDestroy(dev->commShadow);
+    if (dev->commFrame) ncclCommDestroy(dev->commFrame);
+    if (dev->gatherStream) cudaStreamDestroy(dev->gatherStream);
+    for (auto& e : dev->gatheredEv) if (e) cudaEventDestroy(e);
     if (dev->copyStream) cudaStreamDestroy(dev->copyStream);
     if (dev->shadowStream) cudaStreamDestroy(dev->shadowStream);
     if (dev->upStream) cudaStreamDestroy(dev->upStream);
@@ -702,6 +718,14 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
     CK(cudaSetDevice(dev->device));
     FramePlan& plan = dev->plan;
     DeviceClusterProvider provider(dev);
+    VkrFrameParams shardFp;
+    if (dev->shardRanks > 1) {      // sort-first: this rank's rows of the frame and of the shadow layers
+        shardFp = *fp;
+        const int32_t bh = (int32_t)dev->H / dev->shardRanks, sh = (int32_t)dev->S / dev->shardRanks;
+        shardFp.scissor[0] = 0; shardFp.scissor[1] = dev->shardRank * bh; shardFp.scissor[2] = (int32_t)dev->W; shardFp.scissor[3] = bh;
+        shardFp.shadowScissor[0] = 0; shardFp.shadowScissor[1] = dev->shardRank * sh; shardFp.shadowScissor[2] = (int32_t)dev->S; shardFp.shadowScissor[3] = sh;
+        fp = &shardFp;
+    }
     std::string why = plan_frame(scene, objs, n, fp, dev->meshes, dev->materials, dev->texHost, provider, dev->W, dev->H, dev->S, plan);
     if (!why.empty()) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, why.c_str());
     cudaStream_t st = dev->stream;
@@ -793,8 +817,9 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
             fill_u32_kernel<<<grid_for(sn / 4, 256, 2048), 256, 0, ss>>>(rt.depthBits, sn, DEPTH_ONE_BITS);
             CK(cudaMemsetAsync(dev->qShadow.counters, 0, 16, ss));
             dev->launches += 1;
-            if (nChunks) {
-                geometry_kernel<true><<<(nChunks + GEOM_WARPS - 1) / GEOM_WARPS, GEOM_WARPS * 32, 0, ss>>>(dChunks, dPerm + (size_t)(1 + layer) * nChunks, nChunks,
+            const unsigned shadowSlots = plan.passSlots[1 + layer];
+            if (shadowSlots) {
+                geometry_kernel<true><<<(shadowSlots + GEOM_WARPS - 1) / GEOM_WARPS, GEOM_WARPS * 32, 0, ss>>>(dChunks, dPerm + (size_t)(1 + layer) * nChunks, shadowSlots,
                                                                                                       dShadowMvp + (size_t)layer * n * 16, 16u, rt, dev->qShadow);
                 large_raster_kernel<true><<<largeGrid, 256, 0, ss>>>(rt, dev->qShadow, AlphaCtx{}, 0);
                 dev->launches += 2;
@@ -802,6 +827,14 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
             CK(cudaMemcpyAsync(dev->countersHost + 4, dev->qShadow.counters, 16, cudaMemcpyDeviceToHost, ss));
         }
         if (timing) CK(cudaEventRecord(dev->tev[8], ss));
+        if (dev->shardRanks > 1) {      // complete every layer from the other ranks' rows (in place)
+            const size_t layerTexels = (size_t)dev->S * dev->S, band = layerTexels / dev->shardRanks;
+            for (int layer = 0; layer < plan.shadowLayers; ++layer) {
+                uint32_t* base = dev->shadowBits + (size_t)layer * layerTexels;
+                if (ncclAllGather(base + (size_t)dev->shardRank * band, base, band, ncclUint32, dev->commShadow, ss) != ncclSuccess)
+                    return dev->fail(VKR_ERROR_CUDA, "ncclAllGather(shadow bands)");
+            }
+        }
         if (dev->shadowExchange) {
             if (dev->shadowExchange(dev->shadowExchangeUser, dev->shadowBits, (size_t)dev->S * dev->S * 4, plan.shadowLayers, (void*)ss) != 0)
                 return dev->fail(VKR_ERROR_CUDA, "shadow exchange hook failed");
@@ -819,9 +852,10 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
         dev->launches += 1;
         if (timing) CK(cudaEventRecord(dev->tev[3], st));
         // only the opaque prefix writes depth; transparent draws are blended in a later pass
-        const unsigned opaqueChunks = plan.opaqueClusters;
+        const unsigned opaqueChunks = plan.opaqueClusters, mainSlots = plan.passSlots[0];
         if (opaqueChunks) {
-            geometry_kernel<false><<<(opaqueChunks + GEOM_WARPS - 1) / GEOM_WARPS, GEOM_WARPS * 32, 0, st>>>(dChunks, dPerm, opaqueChunks, (const float*)dObjects,
+            if (mainSlots)
+                geometry_kernel<false><<<(mainSlots + GEOM_WARPS - 1) / GEOM_WARPS, GEOM_WARPS * 32, 0, st>>>(dChunks, dPerm, mainSlots, (const float*)dObjects,
                                                                                                             (uint32_t)(sizeof(DObject) / 4), rt, dev->q);
             if (timing) CK(cudaEventRecord(dev->tev[4], st));
             const AlphaCtx ax{dObjects, dev->chunkObjBuf, dev->matDev, dev->texDev};
@@ -864,6 +898,7 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
     if (timing) CK(cudaEventRecord(dev->tev[9], st));
 
     // ---- shading half of draw_geometry + draw_skybox + draw_background + draw_postprocess + present blit
+    if (dev->shardRanks > 1 && dev->gatheredValid[slotIdx]) CK(cudaStreamWaitEvent(st, dev->gatheredEv[slotIdx], 0));   // rgba8[slot] still being gathered
     {
         dim3 grid((sc.sx1 - sc.sx0 + 15) / 16, (sc.sy1 - sc.sy0 + 7) / 8);
         if (grid.x && grid.y) { shade_kernel<<<grid, 128, 0, st>>>(sc, sb); dev->launches += 1; }
@@ -871,13 +906,22 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
     if (timing) { CK(cudaEventRecord(dev->tev[6], st)); dev->tevValid = true; dev->shadowTimed = plan.shadowLayers > 0; }
     CK(cudaGetLastError());
     CK(cudaEventRecord(slot.rendered, st));
+    if (dev->shardRanks > 1) {          // assemble the presented image; overlaps the next frame's rendering
+        CK(cudaStreamWaitEvent(dev->gatherStream, slot.rendered, 0));
+        const size_t band = (size_t)dev->W * dev->H / dev->shardRanks;
+        if (ncclAllGather(dev->rgba8[slotIdx] + (size_t)dev->shardRank * band, dev->gathered[slotIdx], band, ncclUint32, dev->commFrame,
+                          dev->gatherStream) != ncclSuccess)
+            return dev->fail(VKR_ERROR_CUDA, "ncclAllGather(frame bands)");
+        CK(cudaEventRecord(dev->gatheredEv[slotIdx], dev->gatherStream));
+        dev->gatheredValid[slotIdx] = true;
+    }
     dev->lastSlot = slotIdx;
     dev->lastChunkObj = dev->chunkObjBuf; dev->lastObjects = dObjects;
     dev->frameIndex++;
     dev->stats.drawcall_count = (int32_t)n;
     dev->stats.triangle_count = (int32_t)plan.totalTris;
-    dev->lastOpaqueClusters = plan.opaqueClusters;
-    dev->lastShadowClusters = plan.shadowLayers ? nChunks : 0;
+    dev->lastOpaqueClusters = plan.passSlots[0];
+    dev->lastShadowClusters = plan.shadowLayers ? plan.passSlots[plan.shadowLayers] : 0;
     return VKR_SUCCESS;
 }
 
@@ -887,6 +931,7 @@ int vkr_sync(VkrDevice* dev) {
     CK(cudaStreamSynchronize(dev->stream));
     CK(cudaStreamSynchronize(dev->copyStream));
     CK(cudaStreamSynchronize(dev->shadowStream));
+    if (dev->gatherStream) CK(cudaStreamSynchronize(dev->gatherStream));
     if (dev->countersHost[2] || dev->countersHost[6] || dev->countersHost[10]) return dev->fail(VKR_ERROR_CAPACITY, "large-triangle queue overflow");
     if (dev->tevValid) {
         auto el = [&](int a, int b) { float ms = 0; cudaEventElapsedTime(&ms, dev->tev[a], dev->tev[b]); return ms; };
@@ -909,6 +954,9 @@ static int target_info(VkrDevice* dev, VkrTarget what, const void** src, size_t*
     const size_t px = (size_t)dev->W * dev->H;
     switch (what) {
         case VKR_TARGET_RGBA8: *src = dev->rgba8[dev->lastSlot]; *bytes = px * 4; return 0;
+        case VKR_TARGET_RGBA8_GATHERED:
+            if (dev->shardRanks <= 1) { *src = dev->rgba8[dev->lastSlot]; *bytes = px * 4; return 0; }
+            *src = dev->gathered[dev->lastSlot]; *bytes = px * 4; return 0;
         case VKR_TARGET_HDR16F: *src = dev->hdr; *bytes = px * 8; return 0;
         case VKR_TARGET_SHADOW: *src = dev->shadowBits; *bytes = (size_t)dev->S * dev->S * 4 * VKR_NUM_CASCADES; return 0;
         case VKR_TARGET_DEPTH: case VKR_TARGET_PRIMID: *src = nullptr; *bytes = px * 4; return 0;
@@ -934,6 +982,7 @@ static int do_readback(VkrDevice* dev, VkrTarget what, void* dst, size_t dstByte
     }
     // copy engine work goes to the copy stream so the next frame's kernels overlap it
     CK(cudaStreamWaitEvent(dev->copyStream, dev->slots[dev->lastSlot].rendered, 0));
+    if (what == VKR_TARGET_RGBA8_GATHERED && dev->shardRanks > 1) CK(cudaStreamWaitEvent(dev->copyStream, dev->gatheredEv[dev->lastSlot], 0));
     CK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, dev->copyStream));
     if (sync) return vkr_sync(dev);
     return VKR_SUCCESS;
@@ -959,6 +1008,40 @@ int vkr_device_ptr(VkrDevice* dev, VkrTarget what, void** ptr, size_t* bytes) {
     const void* src; size_t n;
     if (target_info(dev, what, &src, &n) || !src) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_device_ptr: target has no linear buffer");
     *ptr = const_cast<void*>(src); *bytes = n;
+    return VKR_SUCCESS;
+}
+
+int vkr_comm_unique_id(void* out, size_t bytes) {
+    static_assert(sizeof(ncclUniqueId) == VKR_COMM_ID_BYTES, "ncclUniqueId size");
+    if (!out || bytes < VKR_COMM_ID_BYTES) return VKR_ERROR_INVALID_ARGUMENT;
+    ncclUniqueId id;
+    if (ncclGetUniqueId(&id) != ncclSuccess) return VKR_ERROR_CUDA;
+    std::memcpy(out, &id, VKR_COMM_ID_BYTES);
+    return VKR_SUCCESS;
+}
+
+int vkr_shard_init(VkrDevice* dev, int rank, int nranks, const void* twoIds, size_t bytes) {
+    if (!dev) return VKR_ERROR_INVALID_ARGUMENT;
+    if (!twoIds || bytes < 2 * VKR_COMM_ID_BYTES || nranks < 1 || rank < 0 || rank >= nranks)
+        return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_shard_init: bad arguments");
+    if (dev->H % nranks || dev->S % nranks) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_shard_init: frame height and shadow extent must be multiples of nranks");
+    if (dev->commShadow || dev->commFrame) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_shard_init: already initialised");
+    CK(cudaSetDevice(dev->device));
+    if (nranks == 1) return VKR_SUCCESS;
+    ncclUniqueId ids[2];
+    std::memcpy(ids, twoIds, sizeof(ids));
+    ncclResult_t rc = ncclCommInitRank(&dev->commShadow, nranks, ids[0], rank);
+    if (rc == ncclSuccess) rc = ncclCommInitRank(&dev->commFrame, nranks, ids[1], rank);
+    if (rc != ncclSuccess) { dev->err = std::string("ncclCommInitRank: ") + ncclGetErrorString(rc); return VKR_ERROR_CUDA; }
+    int prLo = 0, prHi = 0;
+    CK(cudaDeviceGetStreamPriorityRange(&prLo, &prHi));
+    CK(cudaStreamCreateWithPriority(&dev->gatherStream, cudaStreamNonBlocking, prHi));
+    const size_t px = (size_t)dev->W * dev->H;
+    for (int i = 0; i < VKR_FRAME_OVERLAP; ++i) {
+        ALLOC(dev->gathered[i], px * 4);
+        CK(cudaEventCreateWithFlags(&dev->gatheredEv[i], cudaEventDisableTiming));
+    }
+    dev->shardRank = rank; dev->shardRanks = nranks;
     return VKR_SUCCESS;
 }
 

@@ -176,6 +176,7 @@ struct FramePlan {
     // slotBase[p*nobj + i] = first geometry-CTA slot of draw i in pass p (0 = main, 1.. = shadow layers),
     // 0xFFFFFFFF when the draw is not part of the pass.  Primitive ids do not depend on it.
     std::vector<uint32_t> slotBase;
+    std::vector<uint32_t> passSlots;    // per pass: geometry warp slots in use (= clusters of the draws taking part)
     std::vector<std::pair<float, uint32_t>> sortScratch;
     std::vector<float> sphereScratch;
     int shadowLayers = 0;
@@ -249,16 +250,37 @@ inline std::string plan_frame(const VkrGPUSceneData* scene, const VkrRenderObjec
     plan.seqSlotBase[n] = (uint32_t)nslot;
     plan.totalTris = (uint32_t)prim;
 
-    // ---- processing order per pass
+    // ---- processing order per pass; draws whose bounding sphere misses the pass's scissor rows are left out
+    // (sort-first sharding: a rank only touches the draws that reach its band)
     plan.slotBase.assign((size_t)(1 + plan.shadowLayers) * n, 0xFFFFFFFFu);
+    plan.passSlots.assign((size_t)(1 + plan.shadowLayers), 0u);
     for (int p = 0; p <= plan.shadowLayers; ++p) {
         auto& keys = plan.sortScratch;
         keys.clear();
         const size_t cnt = p == 0 ? plan.opaqueCount : n;
+        // scissor rows of the pass as an NDC interval, widened by a pixel (vertex snapping, rounding)
+        const int32_t* sci = p == 0 ? fp->scissor : fp->shadowScissor;
+        const float extent = p == 0 ? (float)H : (float)S;
+        const bool banded = sci[2] > 0 && sci[3] > 0;
+        const float b0 = banded ? 2.0f * ((float)sci[1] - 1.0f) / extent - 1.0f : -2.0f;
+        const float b1 = banded ? 2.0f * ((float)(sci[1] + sci[3]) + 1.0f) / extent - 1.0f : 2.0f;
         for (size_t i = 0; i < cnt; ++i) {
             const DObject& o = plan.objects[i];
             const float cx = sphere[4 * i], cy = sphere[4 * i + 1], cz = sphere[4 * i + 2], rad = sphere[4 * i + 3];
             const float* m = p == 0 ? o.mvp : &plan.shadowMvp[((size_t)(p - 1) * n + i) * 16];
+            if (banded) {
+                // every point of the sphere satisfies y - b*w > 0 (resp. < 0): nothing of it can land on a row <= b1 (>= b0);
+                // y - b*w is linear in the object-space position, its range over the sphere is centre value +- r*|gradient|
+                const float yc = m[1] * cx + m[5] * cy + m[9] * cz + m[13], wc = m[3] * cx + m[7] * cy + m[11] * cz + m[15];
+                const float r1 = rad * 1.001f + 1e-6f;
+                auto gradLen = [&](float b) {
+                    const float gx = m[1] - b * m[3], gy = m[5] - b * m[7], gz = m[9] - b * m[11];
+                    return std::sqrt(gx * gx + gy * gy + gz * gz);
+                };
+                const float slack = 1e-5f * (std::fabs(yc) + std::fabs(wc));
+                if ((yc - b1 * wc) - r1 * gradLen(b1) > slack) continue;      // entirely past the last row
+                if ((yc - b0 * wc) + r1 * gradLen(b0) < -slack) continue;     // entirely before the first row
+            }
             // main pass: clip w (view depth); shadow pass (orthographic light): clip z
             const int r = p == 0 ? 3 : 2;
             const float d = m[r] * cx + m[4 + r] * cy + m[8 + r] * cz + m[12 + r];
@@ -273,6 +295,7 @@ inline std::string plan_frame(const VkrGPUSceneData* scene, const VkrRenderObjec
             plan.slotBase[(size_t)p * n + k.second] = slot;
             slot += plan.clusterBase[k.second + 1] - plan.clusterBase[k.second];
         }
+        plan.passSlots[p] = slot;
     }
 
     ShadeConst& sc = plan.sc;
