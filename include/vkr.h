@@ -210,12 +210,13 @@ int vkr_set_shadow_exchange(VkrDevice* dev, VkrShadowExchangeFn fn, void* user);
  * The reference has no counterpart (single queue, src/vk_engine_init.cpp:80).  vkr_comm_unique_id fills
  * VKR_COMM_ID_BYTES bytes (an ncclUniqueId); rank 0 makes TWO of them and hands them to every rank through the
  * host's own plumbing (torch.distributed broadcast, MPI, a file...).  After vkr_shard_init, vkr_draw on this device
- *   - renders rows [rank*H/n, (rank+1)*H/n) of the frame and rows [rank*S/n, ...) of every shadow layer
- *     (the cluster test drops everything else before any vertex work),
- *   - all-gathers the shadow bands on the shadow stream (communicator 0) before shading,
- *   - all-gathers the presented RGBA8 bands (communicator 1) on its own stream, overlapped with the next frame,
+ *   - renders one contiguous band of rows of the frame and one of every shadow layer; the bands are re-split every
+ *     frame so that each holds the same estimated cost (triangles of the draws reaching a row + pixels to shade),
+ *     identically on every rank from the draw list; draws and clusters outside the band cost (almost) nothing,
+ *   - exchanges the shadow bands on the shadow stream (communicator 0, one grouped broadcast per band) before shading,
+ *   - assembles the presented RGBA8 image (communicator 1) on its own stream, overlapped with the next frame,
  *     into VKR_TARGET_RGBA8_GATHERED (double-buffered like the presented image).
- * H and the shadow extent must be multiples of nranks.  Draw lists must be identical on every rank. */
+ * Draw lists, scene data and frame parameters must be identical on every rank. */
 #define VKR_COMM_ID_BYTES 128
 int vkr_comm_unique_id(void* out, size_t bytes);
 int vkr_shard_init(VkrDevice* dev, int rank, int nranks, const void* twoIds, size_t bytes);

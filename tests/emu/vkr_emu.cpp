@@ -59,6 +59,7 @@ struct EmuDevice {
     uint32_t culled[2] = {0, 0};         // clusters dropped by the cluster test: [0] main, [1] shadow
     VkrEngineStats stats{};
     VkrShadowExchangeFn shadowExchange = nullptr; void* shadowExchangeUser = nullptr;
+    int shardRank = 0, shardRanks = 1;      // vkr_shard_init's band split, without the exchange (the test supplies it)
     std::string err;
 };
 
@@ -280,7 +281,7 @@ extern "C" {
 
 int emu_draw(EmuDevice* d, const VkrGPUSceneData* scene, const VkrRenderObject* objs, size_t n, const VkrFrameParams* fp) {
     FramePlan& plan = d->plan;
-    std::string why = plan_frame(scene, objs, n, fp, d->meshes, d->materials, d->tex, d->clusters, d->W, d->H, d->S, plan);
+    std::string why = plan_frame(scene, objs, n, fp, d->meshes, d->materials, d->tex, d->clusters, d->W, d->H, d->S, plan, d->shardRank, d->shardRanks);
     if (!why.empty()) { d->err = why; return VKR_ERROR_INVALID_ARGUMENT; }
     const unsigned nChunks = plan.clusterBase[n];
     d->chunks.resize(nChunks);
@@ -353,6 +354,13 @@ int emu_readback(EmuDevice* d, int what, void* dst, size_t bytes) {
 }
 int emu_stats(EmuDevice* d, VkrEngineStats* out) { *out = d->stats; return 0; }
 int emu_set_shadow_exchange(EmuDevice* d, VkrShadowExchangeFn fn, void* user) { d->shadowExchange = fn; d->shadowExchangeUser = user; return 0; }
+int emu_set_shard(EmuDevice* d, int rank, int nranks) { d->shardRank = rank; d->shardRanks = nranks; return 0; }
+// row split points of the last frame: out[0..nranks] frame rows, out[nranks+1 .. 2*nranks+1] shadow rows
+int emu_bands(EmuDevice* d, int32_t* out) {
+    for (size_t i = 0; i < d->plan.bandMain.size(); ++i) out[i] = d->plan.bandMain[i];
+    for (size_t i = 0; i < d->plan.bandShadow.size(); ++i) out[d->plan.bandMain.size() + i] = d->plan.bandShadow[i];
+    return (int)d->plan.bandMain.size();
+}
 void* emu_host_ptr(EmuDevice* d, int what) { return what == VKR_TARGET_RGBA8 ? (void*)d->rgba8.data() : nullptr; }
 void emu_culled(EmuDevice* d, uint32_t out[2]) { out[0] = d->culled[0]; out[1] = d->culled[1]; }
 const char* emu_last_error(EmuDevice* d) { return d->err.c_str(); }

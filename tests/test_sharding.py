@@ -74,3 +74,56 @@ def test_row_bands_cover_the_frame():
             for y0, h in bands:
                 assert y0 == y or h == 0
                 y += h
+
+
+@pytest.mark.parametrize("scene,nranks", [("lattice", 4), ("basic_pcf", 3), ("basic_csm", 2), ("transparent", 5)])
+def test_cost_balanced_bands_reassemble_the_frame(emu_lib, scene, nranks):
+    """vkr_shard_init's split (plan_frame: one contiguous, cost-balanced band of frame rows and of shadow rows per
+    rank, recomputed from the draw list): rendering every rank's band with the host emulation and stacking them must
+    reproduce the unsharded frame and shadow map exactly; the bands must tile the rows; the split must be the same on
+    every rank."""
+    import ctypes
+    import scenes
+    from vk_renderer_b200 import capi
+    W, H, S = 160, 100, 192
+    r = capi.Renderer(emu_lib, "emu", W, H, shadow_extent=S)
+    sd, objs, fp = scenes.SCENES[scene](r)
+    r.draw(sd, objs, fp)
+    want = r.readback(capi.TARGET_RGBA8)
+    want_shadow = r.readback(capi.TARGET_SHADOW)
+    layers = 4 if fp.shadowMode == 3 else 1
+    r.close()
+    full_shadow = np.ascontiguousarray(want_shadow)
+    got = np.zeros_like(want)
+    got_shadow = np.ones_like(want_shadow)
+    splits = None
+    for rank in range(nranks):
+        r = capi.Renderer(emu_lib, "emu", W, H, shadow_extent=S)
+        sd, objs, fp = scenes.SCENES[scene](r)
+        emu_lib.emu_set_shard(r.dev, rank, nranks)
+        own = {}
+
+        def exchange(shadow_ptr, layer_bytes, nlayers, stream):
+            buf = np.frombuffer((ctypes.c_ubyte * (layer_bytes * nlayers)).from_address(shadow_ptr), dtype=np.float32).reshape(nlayers, S, S)
+            own["shadow"] = buf.copy()                # what this rank rasterised (its band; the rest is still cleared)
+            buf[:] = full_shadow[:nlayers]            # the exchange: everybody's bands
+        r.set_shadow_exchange(exchange)
+        r.draw(sd, objs, fp)
+        bands = (ctypes.c_int32 * (2 * nranks + 2))()
+        assert emu_lib.emu_bands(r.dev, bands) == nranks + 1
+        b = list(bands)
+        if splits is None:
+            splits = b
+        assert b == splits
+        fb, sb = b[:nranks + 1], b[nranks + 1:]
+        assert fb[0] == 0 and fb[-1] == H and all(y1 > y0 for y0, y1 in zip(fb, fb[1:]))
+        assert sb[0] == 0 and sb[-1] == S and all(y1 > y0 for y0, y1 in zip(sb, sb[1:]))
+        img = r.readback(capi.TARGET_RGBA8)
+        got[fb[rank]:fb[rank + 1]] = img[fb[rank]:fb[rank + 1]]
+        got_shadow[:layers, sb[rank]:sb[rank + 1]] = own["shadow"][:layers, sb[rank]:sb[rank + 1]]
+        # nothing may be rasterised outside the rank's shadow band
+        mask = np.ones(S, bool); mask[sb[rank]:sb[rank + 1]] = False
+        assert (own["shadow"][:layers, mask] == 1.0).all()
+        r.close()
+    assert np.array_equal(got, want), f"{(got != want).any(-1).sum()} pixels differ"
+    assert np.array_equal(got_shadow[:layers].view(np.uint32), want_shadow[:layers].view(np.uint32))

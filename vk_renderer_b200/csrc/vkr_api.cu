@@ -718,15 +718,8 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
     CK(cudaSetDevice(dev->device));
     FramePlan& plan = dev->plan;
     DeviceClusterProvider provider(dev);
-    VkrFrameParams shardFp;
-    if (dev->shardRanks > 1) {      // sort-first: this rank's rows of the frame and of the shadow layers
-        shardFp = *fp;
-        const int32_t bh = (int32_t)dev->H / dev->shardRanks, sh = (int32_t)dev->S / dev->shardRanks;
-        shardFp.scissor[0] = 0; shardFp.scissor[1] = dev->shardRank * bh; shardFp.scissor[2] = (int32_t)dev->W; shardFp.scissor[3] = bh;
-        shardFp.shadowScissor[0] = 0; shardFp.shadowScissor[1] = dev->shardRank * sh; shardFp.shadowScissor[2] = (int32_t)dev->S; shardFp.shadowScissor[3] = sh;
-        fp = &shardFp;
-    }
-    std::string why = plan_frame(scene, objs, n, fp, dev->meshes, dev->materials, dev->texHost, provider, dev->W, dev->H, dev->S, plan);
+    std::string why = plan_frame(scene, objs, n, fp, dev->meshes, dev->materials, dev->texHost, provider, dev->W, dev->H, dev->S, plan,
+                                 dev->shardRank, dev->shardRanks);     // sharded: also splits the rows into cost-balanced bands
     if (!why.empty()) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, why.c_str());
     cudaStream_t st = dev->stream;
     dev->launches = 0;
@@ -827,13 +820,17 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
             CK(cudaMemcpyAsync(dev->countersHost + 4, dev->qShadow.counters, 16, cudaMemcpyDeviceToHost, ss));
         }
         if (timing) CK(cudaEventRecord(dev->tev[8], ss));
-        if (dev->shardRanks > 1) {      // complete every layer from the other ranks' rows (in place)
-            const size_t layerTexels = (size_t)dev->S * dev->S, band = layerTexels / dev->shardRanks;
-            for (int layer = 0; layer < plan.shadowLayers; ++layer) {
-                uint32_t* base = dev->shadowBits + (size_t)layer * layerTexels;
-                if (ncclAllGather(base + (size_t)dev->shardRank * band, base, band, ncclUint32, dev->commShadow, ss) != ncclSuccess)
-                    return dev->fail(VKR_ERROR_CUDA, "ncclAllGather(shadow bands)");
+        if (dev->shardRanks > 1) {      // complete every layer from the other ranks' row bands, in place
+            ncclResult_t rc = ncclGroupStart();
+            for (int layer = 0; layer < plan.shadowLayers && rc == ncclSuccess; ++layer) {
+                uint32_t* base = dev->shadowBits + (size_t)layer * dev->S * dev->S;
+                for (int r = 0; r < dev->shardRanks && rc == ncclSuccess; ++r) {
+                    uint32_t* rows = base + (size_t)plan.bandShadow[r] * dev->S;
+                    rc = ncclBroadcast(rows, rows, (size_t)(plan.bandShadow[r + 1] - plan.bandShadow[r]) * dev->S, ncclUint32, r, dev->commShadow, ss);
+                }
             }
+            if (rc == ncclSuccess) rc = ncclGroupEnd();
+            if (rc != ncclSuccess) return dev->fail(VKR_ERROR_CUDA, "NCCL shadow band exchange");
         }
         if (dev->shadowExchange) {
             if (dev->shadowExchange(dev->shadowExchangeUser, dev->shadowBits, (size_t)dev->S * dev->S * 4, plan.shadowLayers, (void*)ss) != 0)
@@ -908,10 +905,13 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
     CK(cudaEventRecord(slot.rendered, st));
     if (dev->shardRanks > 1) {          // assemble the presented image; overlaps the next frame's rendering
         CK(cudaStreamWaitEvent(dev->gatherStream, slot.rendered, 0));
-        const size_t band = (size_t)dev->W * dev->H / dev->shardRanks;
-        if (ncclAllGather(dev->rgba8[slotIdx] + (size_t)dev->shardRank * band, dev->gathered[slotIdx], band, ncclUint32, dev->commFrame,
-                          dev->gatherStream) != ncclSuccess)
-            return dev->fail(VKR_ERROR_CUDA, "ncclAllGather(frame bands)");
+        ncclResult_t rc = ncclGroupStart();
+        for (int r = 0; r < dev->shardRanks && rc == ncclSuccess; ++r) {
+            const size_t off = (size_t)plan.bandMain[r] * dev->W, cnt = (size_t)(plan.bandMain[r + 1] - plan.bandMain[r]) * dev->W;
+            rc = ncclBroadcast(dev->rgba8[slotIdx] + off, dev->gathered[slotIdx] + off, cnt, ncclUint32, r, dev->commFrame, dev->gatherStream);
+        }
+        if (rc == ncclSuccess) rc = ncclGroupEnd();
+        if (rc != ncclSuccess) return dev->fail(VKR_ERROR_CUDA, "NCCL frame band gather");
         CK(cudaEventRecord(dev->gatheredEv[slotIdx], dev->gatherStream));
         dev->gatheredValid[slotIdx] = true;
     }
@@ -1024,7 +1024,7 @@ int vkr_shard_init(VkrDevice* dev, int rank, int nranks, const void* twoIds, siz
     if (!dev) return VKR_ERROR_INVALID_ARGUMENT;
     if (!twoIds || bytes < 2 * VKR_COMM_ID_BYTES || nranks < 1 || rank < 0 || rank >= nranks)
         return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_shard_init: bad arguments");
-    if (dev->H % nranks || dev->S % nranks) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_shard_init: frame height and shadow extent must be multiples of nranks");
+    if ((int)dev->H < nranks || (int)dev->S < nranks) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_shard_init: more ranks than rows");
     if (dev->commShadow || dev->commFrame) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_shard_init: already initialised");
     CK(cudaSetDevice(dev->device));
     if (nranks == 1) return VKR_SUCCESS;

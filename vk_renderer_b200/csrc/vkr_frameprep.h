@@ -176,6 +176,8 @@ struct FramePlan {
     // slotBase[p*nobj + i] = first geometry-CTA slot of draw i in pass p (0 = main, 1.. = shadow layers),
     // 0xFFFFFFFF when the draw is not part of the pass.  Primitive ids do not depend on it.
     std::vector<uint32_t> slotBase;
+    std::vector<int32_t> bandMain, bandShadow;   // sort-first: row split points (nranks + 1) of the frame / the shadow layers
+    std::vector<double> rowCost;
     std::vector<uint32_t> passSlots;    // per pass: geometry warp slots in use (= clusters of the draws taking part)
     std::vector<std::pair<float, uint32_t>> sortScratch;
     std::vector<float> sphereScratch;
@@ -190,7 +192,10 @@ struct FramePlan {
 // Returns an empty string on success, else the reason the draw list is invalid.
 inline std::string plan_frame(const VkrGPUSceneData* scene, const VkrRenderObject* objs, size_t n, const VkrFrameParams* fp,
                               const std::vector<DMesh>& meshes, const std::vector<DMaterial>& materials,
-                              const std::vector<DTexture>& textures, ClusterProvider& clusters, uint32_t W, uint32_t H, uint32_t S, FramePlan& plan) {
+                              const std::vector<DTexture>& textures, ClusterProvider& clusters, uint32_t W, uint32_t H, uint32_t S, FramePlan& plan,
+                              int shardRank = 0, int shardRanks = 1) {
+    VkrFrameParams fpLocal = *fp;       // sort-first sharding rewrites the two scissors below
+    fp = &fpLocal;
     plan.objects.resize(n);
     plan.primBase.resize(n + 1);
     plan.clusterBase.resize(n + 1);
@@ -249,6 +254,52 @@ inline std::string plan_frame(const VkrGPUSceneData* scene, const VkrRenderObjec
     plan.clusterBase[n] = (uint32_t)ncl;
     plan.seqSlotBase[n] = (uint32_t)nslot;
     plan.totalTris = (uint32_t)prim;
+
+    // ---- sort-first sharding: split the rows of the frame and of the shadow map into one contiguous band per rank
+    // with equal estimated cost (triangles whose draw reaches the row + pixels to shade), from the draws' bounding
+    // spheres.  Every rank computes the same split from the same draw list.
+    plan.bandMain.assign(1, 0); plan.bandShadow.assign(1, 0);
+    if (shardRanks > 1) {
+        for (int p = 0; p <= (plan.shadowLayers ? 1 : 0); ++p) {
+            const uint32_t rows = p == 0 ? H : S;
+            std::vector<double>& cost = plan.rowCost;
+            cost.assign(rows + 1, 0.0);
+            const size_t cnt = p == 0 ? plan.opaqueCount : n;
+            for (size_t i = 0; i < cnt; ++i) {
+                const float* m = p == 0 ? plan.objects[i].mvp : &plan.shadowMvp[i * 16];      // shadow: layer 0 decides for all layers
+                const float cx = sphere[4 * i], cy = sphere[4 * i + 1], cz = sphere[4 * i + 2], rad = sphere[4 * i + 3];
+                const float yc = m[1] * cx + m[5] * cy + m[9] * cz + m[13], wc = m[3] * cx + m[7] * cy + m[11] * cz + m[15];
+                const float ry = rad * std::sqrt(m[1] * m[1] + m[5] * m[5] + m[9] * m[9]), rw = rad * std::sqrt(m[3] * m[3] + m[7] * m[7] + m[11] * m[11]);
+                float r0 = 0.0f, r1 = (float)rows;
+                if (wc - rw > 1e-6f) {       // wholly in front: interval bound of y/w
+                    const float ylo = yc - ry, yhi = yc + ry, wlo = wc - rw, whi = wc + rw;
+                    const float nlo = std::min(ylo / wlo, ylo / whi), nhi = std::max(yhi / wlo, yhi / whi);
+                    r0 = (nlo + 1.0f) * 0.5f * (float)rows; r1 = (nhi + 1.0f) * 0.5f * (float)rows;
+                }
+                if (!(r0 == r0) || !(r1 == r1)) { r0 = 0.0f; r1 = (float)rows; }
+                if (r1 < 0.0f || r0 > (float)rows) continue;
+                const uint32_t a = (uint32_t)std::max(0.0f, std::floor(r0)), b = (uint32_t)std::min((float)rows - 1.0f, std::max(0.0f, std::floor(r1)));
+                const double per = (double)plan.objects[i].triCount / (double)(b - a + 1);
+                cost[a] += per; cost[b + 1] -= per;            // difference array
+            }
+            const double perRow = p == 0 ? (double)W : 0.25 * (double)S;     // a shaded pixel costs about what a triangle costs; clearing a texel less
+            std::vector<int32_t>& band = p == 0 ? plan.bandMain : plan.bandShadow;
+            band.assign((size_t)shardRanks + 1, 0);
+            double run = 0.0, total = 0.0;
+            for (uint32_t y = 0; y < rows; ++y) { run += cost[y]; total += run + perRow; cost[y] = total; }   // cost[y] := cumulative cost through row y
+            uint32_t y = 0;
+            for (int k = 1; k < shardRanks; ++k) {
+                const double target = total * (double)k / (double)shardRanks;
+                while (y + 1 < rows && cost[y] < target) ++y;
+                // split after row y; keep every band non-empty
+                const int32_t lo = band[k - 1] + 1, hi = (int32_t)rows - (shardRanks - k);
+                band[k] = std::min(hi, std::max(lo, (int32_t)y + 1));
+            }
+            band[shardRanks] = (int32_t)rows;
+            int32_t* sci = p == 0 ? fpLocal.scissor : fpLocal.shadowScissor;
+            sci[0] = 0; sci[1] = band[shardRank]; sci[2] = (int32_t)(p == 0 ? W : S); sci[3] = band[shardRank + 1] - band[shardRank];
+        }
+    }
 
     // ---- processing order per pass; draws whose bounding sphere misses the pass's scissor rows are left out
     // (sort-first sharding: a rank only touches the draws that reach its band)
