@@ -302,7 +302,7 @@ def run_b200(args):
             "roofline": {"bound": "hbm", "kernel": "geometry_kernel<main>", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": None, "algorithmic_bytes": gk_bytes, "kernel_ms": gk_ms,
                          "peak_source": peak_src},
-            "pass_ms": avg,
+            "pass_ms": avg, "pass_ms_last_pipelined_frame": {k: float(v) for k, v in tm.items()},
             "host_issue_ms_per_step": host_issue_ms, "host_vkr_draw_call_ms": float(np.median(host_call)),
             "cluster_culling": cull,
             "e2e": {"value": args.steps / e2e_s, "unit": "frames/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),

@@ -163,7 +163,9 @@ typedef enum VkrTarget {
 
 /* Pass indices for vkr_get_timings. */
 enum { VKR_T_UPLOAD = 0, VKR_T_SHADOW, VKR_T_GEOMETRY, VKR_T_SHADE, VKR_T_TRANSPARENT, VKR_T_POST, VKR_T_TOTAL,
-       VKR_T_GEOM_KERNEL /* main-pass geometry kernel alone */, VKR_T_LARGE_KERNEL, VKR_T_CLEAR, VKR_T_COUNT };
+       VKR_T_GEOM_KERNEL /* main-pass geometry kernel alone */, VKR_T_LARGE_KERNEL, VKR_T_CLEAR,
+       VKR_T_SHADOW_EXCHANGE /* sharded: shadow band exchange (part of VKR_T_SHADOW) */, VKR_T_FRAME_GATHER /* sharded: image assembly */,
+       VKR_T_COUNT };
 
 /* init_vulkan + init_swapchain + init_shadow_resources + init_default_data
  * (src/vk_engine_init.cpp:42-138,318-402). Seeds bindless slot 0 with the

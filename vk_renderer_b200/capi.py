@@ -21,7 +21,8 @@ FRAG_PBR, FRAG_LAMBERT = 0, 1
 TARGET_RGBA8, TARGET_HDR16F, TARGET_DEPTH, TARGET_SHADOW, TARGET_PRIMID, TARGET_RGBA8_GATHERED = range(6)
 COMM_ID_BYTES = 128
 CONFIG_TIMINGS = 1
-T_NAMES = ["upload", "shadow", "geometry", "shade", "transparent", "post", "total", "geom_kernel", "large_kernel", "clear"]
+T_NAMES = ["upload", "shadow", "geometry", "shade", "transparent", "post", "total", "geom_kernel", "large_kernel", "clear",
+           "shadow_exchange", "frame_gather"]
 
 # struct Vertex (src/vk_types.h:85-91), 48 bytes
 VERTEX_DTYPE = np.dtype(

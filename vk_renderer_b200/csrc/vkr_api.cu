@@ -55,6 +55,23 @@ __global__ void extract_vis_kernel(const uint64_t* __restrict__ vis, uint32_t* _
     out[i] = objects[ch.x].primBase + ch.y + (seq & 255u);                        // dense submission-order id
 }
 
+// ---- sort-first exchange: ranks own row bands of different heights (NCCL has no all-gather-v), so the exchange
+// is one grouped send/recv: every rank sends its band to every peer and receives theirs in place.
+static ncclResult_t exchange_bands(const uint32_t* src, uint32_t* dst, const std::vector<int32_t>& band, int lo, int hi, size_t rowTexels,
+                                   int rank, int nranks, ncclComm_t comm, cudaStream_t stream) {
+    auto clampRow = [&](int32_t y) { return std::min(std::max(y, lo), hi); };
+    ncclResult_t rc = ncclGroupStart();
+    const int32_t m0 = clampRow(band[rank]), m1 = clampRow(band[rank + 1]);
+    for (int peer = 0; peer < nranks && rc == ncclSuccess; ++peer) {
+        const int32_t p0 = clampRow(band[peer]), p1 = clampRow(band[peer + 1]);
+        if (peer == rank && src == dst) continue;      // in place: the own band is already there
+        if (m1 > m0) rc = ncclSend(src + (size_t)m0 * rowTexels, (size_t)(m1 - m0) * rowTexels, ncclUint32, peer, comm, stream);
+        if (rc == ncclSuccess && p1 > p0) rc = ncclRecv(dst + (size_t)p0 * rowTexels, (size_t)(p1 - p0) * rowTexels, ncclUint32, peer, comm, stream);
+    }
+    if (rc == ncclSuccess) rc = ncclGroupEnd();
+    return rc;
+}
+
 // ---- upload_mesh: AoS Vertex (48 B) -> three float4 streams
 __global__ void repack_vertices_kernel(const VkrVertex* __restrict__ v, size_t n, float4* __restrict__ pos,
                                        float4* __restrict__ attrA, float4* __restrict__ attrB) {
@@ -392,7 +409,7 @@ struct VkrDevice {
     const uint2* lastChunkObj = nullptr; const DObject* lastObjects = nullptr;
     FramePlan plan;
 
-    cudaEvent_t tev[10] = {nullptr};   // 0 start, 1 uploaded, 3 cleared, 4 geometry kernel, 5 large kernel, 6 shaded; 7,8 shadow pass (shadow stream)
+    cudaEvent_t tev[13] = {nullptr};  // ... 9 transparent done; 10 shadow raster done (before the exchange); 11, 12 frame gather (gather stream)   // 0 start, 1 uploaded, 3 cleared, 4 geometry kernel, 5 large kernel, 6 shaded; 7,8 shadow pass (shadow stream)
     bool tevValid = false, shadowTimed = false;
     float timings[VKR_T_COUNT] = {0};
 
@@ -819,23 +836,21 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
             }
             CK(cudaMemcpyAsync(dev->countersHost + 4, dev->qShadow.counters, 16, cudaMemcpyDeviceToHost, ss));
         }
-        if (timing) CK(cudaEventRecord(dev->tev[8], ss));
-        if (dev->shardRanks > 1) {      // complete every layer from the other ranks' row bands, in place
-            ncclResult_t rc = ncclGroupStart();
-            for (int layer = 0; layer < plan.shadowLayers && rc == ncclSuccess; ++layer) {
+        if (timing) CK(cudaEventRecord(dev->tev[10], ss));
+        if (dev->shardRanks > 1) {      // complete every layer from the other ranks' row bands (only rows a caster can reach)
+            for (int layer = 0; layer < plan.shadowLayers; ++layer) {
                 uint32_t* base = dev->shadowBits + (size_t)layer * dev->S * dev->S;
-                for (int r = 0; r < dev->shardRanks && rc == ncclSuccess; ++r) {
-                    uint32_t* rows = base + (size_t)plan.bandShadow[r] * dev->S;
-                    rc = ncclBroadcast(rows, rows, (size_t)(plan.bandShadow[r + 1] - plan.bandShadow[r]) * dev->S, ncclUint32, r, dev->commShadow, ss);
-                }
+                // layer 0's casters define the active rows; other cascades see the scene at another scale: exchange them whole
+                const int lo = layer == 0 ? plan.activeShadow[0] : 0, hi = layer == 0 ? plan.activeShadow[1] : (int)dev->S;
+                if (exchange_bands(base, base, plan.bandShadow, lo, hi, dev->S, dev->shardRank, dev->shardRanks, dev->commShadow, ss) != ncclSuccess)
+                    return dev->fail(VKR_ERROR_CUDA, "NCCL shadow band exchange");
             }
-            if (rc == ncclSuccess) rc = ncclGroupEnd();
-            if (rc != ncclSuccess) return dev->fail(VKR_ERROR_CUDA, "NCCL shadow band exchange");
         }
         if (dev->shadowExchange) {
             if (dev->shadowExchange(dev->shadowExchangeUser, dev->shadowBits, (size_t)dev->S * dev->S * 4, plan.shadowLayers, (void*)ss) != 0)
                 return dev->fail(VKR_ERROR_CUDA, "shadow exchange hook failed");
         }
+        if (timing) CK(cudaEventRecord(dev->tev[8], ss));
         CK(cudaEventRecord(dev->evShadow, ss));
     }
 
@@ -905,13 +920,11 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
     CK(cudaEventRecord(slot.rendered, st));
     if (dev->shardRanks > 1) {          // assemble the presented image; overlaps the next frame's rendering
         CK(cudaStreamWaitEvent(dev->gatherStream, slot.rendered, 0));
-        ncclResult_t rc = ncclGroupStart();
-        for (int r = 0; r < dev->shardRanks && rc == ncclSuccess; ++r) {
-            const size_t off = (size_t)plan.bandMain[r] * dev->W, cnt = (size_t)(plan.bandMain[r + 1] - plan.bandMain[r]) * dev->W;
-            rc = ncclBroadcast(dev->rgba8[slotIdx] + off, dev->gathered[slotIdx] + off, cnt, ncclUint32, r, dev->commFrame, dev->gatherStream);
-        }
-        if (rc == ncclSuccess) rc = ncclGroupEnd();
-        if (rc != ncclSuccess) return dev->fail(VKR_ERROR_CUDA, "NCCL frame band gather");
+        if (timing) CK(cudaEventRecord(dev->tev[11], dev->gatherStream));
+        if (exchange_bands(dev->rgba8[slotIdx], dev->gathered[slotIdx], plan.bandMain, 0, (int)dev->H, dev->W, dev->shardRank, dev->shardRanks,
+                           dev->commFrame, dev->gatherStream) != ncclSuccess)
+            return dev->fail(VKR_ERROR_CUDA, "NCCL frame band gather");
+        if (timing) CK(cudaEventRecord(dev->tev[12], dev->gatherStream));
         CK(cudaEventRecord(dev->gatheredEv[slotIdx], dev->gatherStream));
         dev->gatheredValid[slotIdx] = true;
     }
@@ -944,6 +957,8 @@ int vkr_sync(VkrDevice* dev) {
         dev->timings[VKR_T_SHADE] = el(9, 6);
         dev->timings[VKR_T_TRANSPARENT] = el(5, 9); dev->timings[VKR_T_POST] = 0;   // tonemap + present are fused into the shade kernel
         dev->timings[VKR_T_TOTAL] = el(0, 6);
+        dev->timings[VKR_T_SHADOW_EXCHANGE] = dev->shadowTimed ? el(10, 8) : 0.0f;
+        dev->timings[VKR_T_FRAME_GATHER] = dev->shardRanks > 1 ? el(11, 12) : 0.0f;
         dev->stats.frametime = dev->timings[VKR_T_TOTAL];
         dev->stats.mesh_draw_time = dev->timings[VKR_T_SHADOW] + dev->timings[VKR_T_GEOMETRY];
     }

@@ -178,6 +178,7 @@ struct FramePlan {
     std::vector<uint32_t> slotBase;
     std::vector<int32_t> bandMain, bandShadow;   // sort-first: row split points (nranks + 1) of the frame / the shadow layers
     std::vector<double> rowCost;
+    int32_t activeMain[2] = {0, 0}, activeShadow[2] = {0, 0};   // rows reachable by some draw's bounding sphere
     std::vector<uint32_t> passSlots;    // per pass: geometry warp slots in use (= clusters of the draws taking part)
     std::vector<std::pair<float, uint32_t>> sortScratch;
     std::vector<float> sphereScratch;
@@ -281,6 +282,14 @@ inline std::string plan_frame(const VkrGPUSceneData* scene, const VkrRenderObjec
                 const uint32_t a = (uint32_t)std::max(0.0f, std::floor(r0)), b = (uint32_t)std::min((float)rows - 1.0f, std::max(0.0f, std::floor(r1)));
                 const double per = (double)plan.objects[i].triCount / (double)(b - a + 1);
                 cost[a] += per; cost[b + 1] -= per;            // difference array
+            }
+            {   // rows any draw can reach (the rest of a shadow layer stays cleared on every rank and is never exchanged)
+                double run2 = 0.0;
+                int32_t a0 = (int32_t)rows, a1 = 0;
+                for (uint32_t y = 0; y < rows; ++y) { run2 += cost[y]; if (run2 > 1e-9) { a0 = std::min(a0, (int32_t)y); a1 = (int32_t)y + 1; } }
+                if (a0 > a1) a0 = a1 = 0;
+                int32_t* act = p == 0 ? plan.activeMain : plan.activeShadow;
+                act[0] = std::max(0, a0 - 1); act[1] = std::min((int32_t)rows, a1 + 1);
             }
             const double perRow = p == 0 ? (double)W : 0.25 * (double)S;     // a shaded pixel costs about what a triangle costs; clearing a texel less
             std::vector<int32_t>& band = p == 0 ? plan.bandMain : plan.bandShadow;
