@@ -18,13 +18,29 @@
 
 namespace vkr {
 
-// glm mat4*mat4 association: ((A0*b0 + A1*b1) + A2*b2) + A3*b3
+// glm mat4*mat4 association: ((A0*b0 + A1*b1) + A2*b2) + A3*b3, every product and sum rounded (no FMA).
+// Column j of the result is a 4-wide expression of A's columns: written with SSE on x86 (mulps/addps round exactly
+// like the scalar operations), scalar elsewhere.
+#if defined(__SSE__)
+}  // namespace vkr
+#include <xmmintrin.h>
+namespace vkr {
+inline void mat_mul(const float* a, const float* b, float* r) {
+    const __m128 a0 = _mm_loadu_ps(a), a1 = _mm_loadu_ps(a + 4), a2 = _mm_loadu_ps(a + 8), a3 = _mm_loadu_ps(a + 12);
+    for (int j = 0; j < 4; ++j) {
+        const __m128 t = _mm_add_ps(_mm_mul_ps(a0, _mm_set1_ps(b[j * 4 + 0])), _mm_mul_ps(a1, _mm_set1_ps(b[j * 4 + 1])));
+        const __m128 u = _mm_add_ps(t, _mm_mul_ps(a2, _mm_set1_ps(b[j * 4 + 2])));
+        _mm_storeu_ps(r + j * 4, _mm_add_ps(u, _mm_mul_ps(a3, _mm_set1_ps(b[j * 4 + 3]))));
+    }
+}
+#else
 inline void mat_mul(const float* a, const float* b, float* r) {
     for (int j = 0; j < 4; ++j)
         for (int i = 0; i < 4; ++i)
             r[j * 4 + i] = ((a[0 * 4 + i] * b[j * 4 + 0] + a[1 * 4 + i] * b[j * 4 + 1]) + a[2 * 4 + i] * b[j * 4 + 2]) +
                            a[3 * 4 + i] * b[j * 4 + 3];
 }
+#endif
 
 // inverse(view)[3].xyz by cofactors (shaders/mesh_pbr.frag:187 evaluates this per fragment).
 inline void camera_position(const float* m, float out[3]) {
@@ -273,29 +289,34 @@ inline std::string plan_frame(const VkrGPUSceneData* scene, const VkrRenderObjec
                 const float ry = rad * std::sqrt(m[1] * m[1] + m[5] * m[5] + m[9] * m[9]), rw = rad * std::sqrt(m[3] * m[3] + m[7] * m[7] + m[11] * m[11]);
                 float r0 = 0.0f, r1 = (float)rows;
                 if (wc - rw > 1e-6f) {       // wholly in front: interval bound of y/w
-                    const float ylo = yc - ry, yhi = yc + ry, wlo = wc - rw, whi = wc + rw;
-                    const float nlo = std::min(ylo / wlo, ylo / whi), nhi = std::max(yhi / wlo, yhi / whi);
-                    r0 = (nlo + 1.0f) * 0.5f * (float)rows; r1 = (nhi + 1.0f) * 0.5f * (float)rows;
+                    const float ylo = yc - ry, yhi = yc + ry, ilo = 1.0f / (wc - rw), ihi = 1.0f / (wc + rw);
+                    const float nlo = std::min(ylo * ilo, ylo * ihi), nhi = std::max(yhi * ilo, yhi * ihi);
+                    r0 = (nlo + 1.0f) * 0.5f * (float)rows - 1.0f; r1 = (nhi + 1.0f) * 0.5f * (float)rows + 1.0f;   // +-1: the reciprocals' rounding
                 }
                 if (!(r0 == r0) || !(r1 == r1)) { r0 = 0.0f; r1 = (float)rows; }
                 if (r1 < 0.0f || r0 > (float)rows) continue;
-                const uint32_t a = (uint32_t)std::max(0.0f, std::floor(r0)), b = (uint32_t)std::min((float)rows - 1.0f, std::max(0.0f, std::floor(r1)));
+                const uint32_t a = (uint32_t)std::max(0.0f, r0), b = (uint32_t)std::min((float)rows - 1.0f, std::max(0.0f, r1));   // >= 0: the cast floors
                 const double per = (double)plan.objects[i].triCount / (double)(b - a + 1);
                 cost[a] += per; cost[b + 1] -= per;            // difference array
             }
-            {   // rows any draw can reach (the rest of a shadow layer stays cleared on every rank and is never exchanged)
-                double run2 = 0.0;
+            const double perRow = p == 0 ? (double)W : 0.25 * (double)S;     // a shaded pixel costs about what a triangle costs; clearing a texel less
+            double total = 0.0;
+            {   // one sweep: rows any draw can reach (the rest of a shadow layer stays cleared on every rank and is never
+                // exchanged), and cost[y] := cumulative cost through row y
+                double run = 0.0;
                 int32_t a0 = (int32_t)rows, a1 = 0;
-                for (uint32_t y = 0; y < rows; ++y) { run2 += cost[y]; if (run2 > 1e-9) { a0 = std::min(a0, (int32_t)y); a1 = (int32_t)y + 1; } }
+                for (uint32_t y = 0; y < rows; ++y) {
+                    run += cost[y];
+                    if (run > 1e-9) { if (a0 > (int32_t)y) a0 = (int32_t)y; a1 = (int32_t)y + 1; }
+                    total += run + perRow;
+                    cost[y] = total;
+                }
                 if (a0 > a1) a0 = a1 = 0;
                 int32_t* act = p == 0 ? plan.activeMain : plan.activeShadow;
                 act[0] = std::max(0, a0 - 1); act[1] = std::min((int32_t)rows, a1 + 1);
             }
-            const double perRow = p == 0 ? (double)W : 0.25 * (double)S;     // a shaded pixel costs about what a triangle costs; clearing a texel less
             std::vector<int32_t>& band = p == 0 ? plan.bandMain : plan.bandShadow;
             band.assign((size_t)shardRanks + 1, 0);
-            double run = 0.0, total = 0.0;
-            for (uint32_t y = 0; y < rows; ++y) { run += cost[y]; total += run + perRow; cost[y] = total; }   // cost[y] := cumulative cost through row y
             uint32_t y = 0;
             for (int k = 1; k < shardRanks; ++k) {
                 const double target = total * (double)k / (double)shardRanks;
@@ -349,7 +370,8 @@ inline std::string plan_frame(const VkrGPUSceneData* scene, const VkrRenderObjec
             if (!(key == key)) key = 0.0f;
             keys.emplace_back(key, (uint32_t)i);
         }
-        std::stable_sort(keys.begin(), keys.end(), [](const std::pair<float, uint32_t>& a, const std::pair<float, uint32_t>& b) { return a.first < b.first; });
+        // (key, submission index) pairs: the pair order is the stable order; usually already sorted from the draw list's own coherence
+        if (!std::is_sorted(keys.begin(), keys.end())) std::sort(keys.begin(), keys.end());
         uint32_t slot = 0;
         for (const auto& k : keys) {
             plan.slotBase[(size_t)p * n + k.second] = slot;
