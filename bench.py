@@ -263,7 +263,8 @@ def run_b200(args):
     # ---- e2e: host draw list in, RGBA8 frame out to pinned host memory, every step (FRAME_OVERLAP=2 pipelining)
     pinned = [torch.empty((H, W, 4), dtype=torch.uint8).pin_memory() for _ in range(2)]
     n = len(my_objs)
-    h2d = n * 176 + (n + 1) * 4 + ((info["idx_per_mesh"] // 3 + 255) // 256) * n * 8 + n * 64 + 512
+    h2d = r.upload_bytes()                                  # what vkr_draw copied host->device for the last frame (draw records,
+                                                            # cluster/slot prefixes, light MVPs, shading constants)
     d2h = W * H * 4                                         # rank 0 reads the assembled frame back
     barrier()
     t0 = time.perf_counter()
@@ -321,6 +322,113 @@ def run_b200(args):
         dist.destroy_process_group()
 
 
+# ------------------------------------------------------------------------------- frame-parallel views (config 5)
+VW, VH, NVIEWS = 1920, 1080, 256
+
+
+def build_view_scene(r):
+    """BASELINE config 5 = config 2's scene: 16x16 spheres (rings = segments = 29 -> 1682 triangles) on a
+    200x200-quad ground plane, ~511 k triangles, PCF shadow, tonemap; 256 cameras on an orbit."""
+    rng = np.random.default_rng(0xB2000000 + 5)
+    sv, si = mg.uv_sphere(29, 29, 1.0)
+    pv, pi = mg.plane(200, 200, 60.0, -1.0, uv_scale=1)
+    ms, mp_ = r.upload_mesh(si, sv), r.upload_mesh(pi, pv)
+    objs = [mg.render_object(mp_, r.build_material((0.8, 0.8, 0.8, 1.0), 0.0, 0.9), np.eye(4), len(pi))]
+    for ix in range(16):
+        for iz in range(16):
+            mat = r.build_material(tuple(rng.uniform(0.2, 1.0, 3)) + (1.0,), float(rng.random() < 0.3), float(rng.uniform(0.2, 0.9)))
+            objs.append(mg.render_object(ms, mat, mg.translate((ix - 7.5) * 3.0, 0.0, (iz - 7.5) * 3.0), len(si)))
+    L = mg.light_matrix()
+    proj = mg.camera_projection(VW / VH)
+    views = []
+    for k in range(NVIEWS):
+        yaw = 2.0 * np.pi * k / NVIEWS
+        view = mg.camera_view((34.0 * np.sin(yaw), 9.0 + 3.0 * np.sin(3 * yaw), 34.0 * np.cos(yaw)), pitch=-0.28, yaw=-yaw)
+        views.append(capi.make_scene_data(view, proj, [L] * 4, shadow_mode=1, enable_shadows=True))
+    fp = capi.default_frame_params(enableShadows=1, shadowMode=1, enablePostprocess=1, enableSkybox=0, enableBackground=1)
+    tris = (len(pi) + 256 * len(si)) // 3
+    return views, np.array(objs), fp, tris
+
+
+def run_views(args):
+    """--workload views: one step = the batch of 256 views, view i on rank i mod N, no exchange step."""
+    import torch
+    import vk_renderer_b200
+    from vk_renderer_b200.sharding import ViewSharder, view_slice
+
+    rank, world, local = (int(os.environ.get(k, d)) for k, d in (("RANK", "0"), ("WORLD_SIZE", "1"), ("LOCAL_RANK", "0")))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    lib = vk_renderer_b200.load()
+    torch.cuda.set_stream(torch.cuda.Stream())
+    r = capi.Renderer(lib, "vkr", VW, VH, shadow_extent=S, device=local, stream=torch.cuda.current_stream().cuda_stream)
+    views, objs, fp, tris = build_view_scene(r)
+    mine = view_slice(rank, world, NVIEWS)
+    sharder = ViewSharder(r, rank, world, cuda=True)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step():
+        for v in mine:
+            r.draw(views[v], objs, fp)
+
+    def maxed(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    for _ in range(max(3, args.warmup)):
+        step()
+    r.sync()
+    barrier()
+    sampler = ClockSampler(local) if rank == 0 else None
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    launches = 0
+    for _ in range(args.steps):
+        step()
+        launches += r.launch_count() * len(mine)
+    e1.record()
+    barrier()
+    r.sync()
+    ms = maxed(e0.elapsed_time(e1))
+    clocks = sampler.stop() if sampler else None
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        sharder.render(views, objs, fp)            # draw + read every view back to pinned host memory
+    barrier()
+    e2e_s = maxed(time.perf_counter() - t0)
+    if rank == 0:
+        vps = args.steps * NVIEWS / (ms / 1000.0)
+        print(json.dumps({
+            "metric": "views_per_sec_1080p_multiview", "value": vps, "unit": "views/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(3, args.warmup), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "BASELINE config 5: batch of 256 camera views at 1920x1080 of the config-2 scene (16x16 spheres + "
+                                   "ground plane, PBR, 2048^2 PCF shadow, tonemap), frame-parallel",
+                       "triangles": int(tris), "views": NVIEWS, "resolution": [VW, VH], "shadow_extent": S,
+                       "parallelism": f"frame-parallel: view i on rank i mod {world}, scene replicated, no collective"},
+            "mtri_per_s": vps * tris / 1e6, "gpix_per_s": vps * VW * VH / 1e9,
+            "e2e": {"value": args.steps * NVIEWS / e2e_s, "unit": "views/s", "h2d_bytes_per_step": int(r.upload_bytes() * len(mine)),
+                    "d2h_bytes_per_step": int(VW * VH * 4 * len(mine))},
+            "gpu_launches": int(launches), "clocks": clocks}), flush=True)
+    r.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -328,9 +436,13 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="frame", choices=["frame", "views"],
+                    help="frame: BASELINE config 4 (the headline metric, default); views: config 5, frame-parallel multi-view batch")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
+    elif args.workload == "views":
+        run_views(args)
     else:
         run_b200(args)
 

@@ -53,6 +53,22 @@ def basic(r, shadow_mode=1, shadows=True, post=True, skybox=True, frag=capi.FRAG
     return sd, np.array(objs), fp
 
 
+def orbit_views(r, n_views, shadow_mode=1, radius=12.0, height=3.0):
+    """n camera views on an orbit around the `basic` scene (BASELINE config 5 in miniature): one GPUSceneData per view,
+    same light for all."""
+    W, H = r.width, r.height
+    lights = _lights(4 if shadow_mode == 3 else 1)
+    proj = mg.camera_projection(W / H)
+    out = []
+    for k in range(n_views):
+        yaw = 2.0 * np.pi * k / n_views
+        pos = (radius * np.sin(yaw), height, radius * np.cos(yaw))
+        view = mg.camera_view(pos, pitch=-0.2, yaw=-yaw)
+        out.append(capi.make_scene_data(view, proj, lights, shadow_mode=shadow_mode, enable_shadows=True,
+                                        cascade_distances=(6.0, 12.0, 20.0, 100.0)))
+    return out
+
+
 def pixel_space(r):
     """view = I and a projection that maps object (x, y) in pixels straight to window coordinates,
     z in [0,1] straight to depth — hand-placed raster edge cases."""

@@ -127,3 +127,57 @@ def test_cost_balanced_bands_reassemble_the_frame(emu_lib, scene, nranks):
         r.close()
     assert np.array_equal(got, want), f"{(got != want).any(-1).sum()} pixels differ"
     assert np.array_equal(got_shadow[:layers].view(np.uint32), want_shadow[:layers].view(np.uint32))
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# frame-parallel views (BASELINE config 5)
+def _view_worker(rank, world, port, n_views, W, H, S, out_dir):
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, HERE)
+    import ctypes
+    import scenes
+    from vk_renderer_b200 import capi
+    from vk_renderer_b200.sharding import ViewSharder
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    emu = ctypes.CDLL(os.path.join(ROOT, "tests", "_build", "libvkr_emu.so"))
+    r = capi.Renderer(emu, "emu", W, H, shadow_extent=S)
+    sd, objs, fp = scenes.SCENES["basic_pcf"](r)
+    views = scenes.orbit_views(r, n_views)
+    done = []
+
+    def sink(v, img):
+        np.save(os.path.join(out_dir, f"view{v}.npy"), img)
+        done.append(v)
+    n = ViewSharder(r, rank, world, cuda=False).render(views, objs, fp, sink)
+    assert n == len(done)
+    # who rendered what: every view exactly once over the group
+    owners = [None] * world
+    dist.all_gather_object(owners, done)
+    assert sorted(v for o in owners for v in o) == list(range(n_views))
+    r.close()
+    dist.destroy_process_group()
+
+
+def test_frame_parallel_views_equal_single_rank(emu_lib, tmp_path):
+    import scenes
+    from vk_renderer_b200 import capi
+    from vk_renderer_b200.sharding import view_slice
+    W, H, S, n_views, world = 128, 72, 128, 5, 2
+    assert [list(view_slice(k, 3, 7)) for k in range(3)] == [[0, 3, 6], [1, 4], [2, 5]]
+    assert list(view_slice(3, 4, 2)) == []                  # more ranks than views: nothing to do, no error
+    port = 29500 + (os.getpid() % 2000) + 17
+    mp.spawn(_view_worker, args=(world, port, n_views, W, H, S, str(tmp_path)), nprocs=world, join=True)
+    r = capi.Renderer(emu_lib, "emu", W, H, shadow_extent=S)
+    sd, objs, fp = scenes.SCENES["basic_pcf"](r)
+    views = scenes.orbit_views(r, n_views)
+    imgs = []
+    for v in range(n_views):
+        r.draw(views[v], objs, fp)
+        want = r.readback(capi.TARGET_RGBA8)
+        got = np.load(tmp_path / f"view{v}.npy")
+        assert np.array_equal(got, want), f"view {v} differs"
+        imgs.append(want)
+    r.close()
+    assert any(not np.array_equal(imgs[0], im) for im in imgs[1:])     # the views really are different images

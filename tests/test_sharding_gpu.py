@@ -77,3 +77,27 @@ def test_nccl_sharded_frame_equals_single_gpu(vkr_lib, tmp_path, scene, native):
         assert np.array_equal(got, want), f"rank {rank}: {(got != want).any(-1).sum()} pixels differ"
         got_shadow = np.load(tmp_path / f"shadow{rank}.npy")
         assert np.array_equal(got_shadow[:layers].view(np.uint32), want_shadow[:layers].view(np.uint32))
+
+
+def test_frame_parallel_views_on_the_device(vkr_lib):
+    """ViewSharder's CUDA path (draw + asynchronous read-back into two pinned buffers) for world = 1 and for rank 1 of 2:
+    every view it hands to the sink equals that view drawn and read back on its own."""
+    import scenes
+    from vk_renderer_b200 import capi
+    from vk_renderer_b200.sharding import ViewSharder, view_slice
+    W, H, S, n_views = 256, 144, 256, 5
+    r = capi.Renderer(vkr_lib, "vkr", W, H, shadow_extent=S)
+    sd, objs, fp = scenes.SCENES["basic_pcf"](r)
+    views = scenes.orbit_views(r, n_views)
+    want = []
+    for v in range(n_views):
+        r.draw(views[v], objs, fp)
+        want.append(r.readback(capi.TARGET_RGBA8))
+    for rank, world in ((0, 1), (1, 2)):
+        got = {}
+        n = ViewSharder(r, rank, world, cuda=True).render(views, objs, fp, lambda v, img: got.__setitem__(v, img.copy()))
+        assert n == len(got) and sorted(got) == list(view_slice(rank, world, n_views))
+        for v, img in got.items():
+            assert np.array_equal(img, want[v]), f"view {v}"
+        assert ViewSharder(r, rank, world, cuda=True).render(views, objs, fp) == n      # throughput form: no sink
+    r.close()

@@ -226,7 +226,7 @@ struct MakeDepthSink { uint32_t* bits; int32_t width; __device__ DepthSink opera
 struct MakeBlendSink { const ShadeConst* sc; const ShadeBuffers* sb; __device__ BlendSink operator()(uint32_t seq) const { return BlendSink{sc, sb, seq}; } };
 
 template <bool SHADOW>
-__global__ void __launch_bounds__(GEOM_WARPS * 32, 4) geometry_kernel(const DChunk* __restrict__ chunks, const uint32_t* __restrict__ perm,
+__global__ void __launch_bounds__(GEOM_WARPS * 32, VKR_GEOM_MIN_CTAS) geometry_kernel(const DChunk* __restrict__ chunks, const uint32_t* __restrict__ perm,
                                                                      uint32_t nClusters, const float* __restrict__ mvps, uint32_t mvpStride,
                                                                      const __grid_constant__ RasterTarget rt, const __grid_constant__ Queues q) {
     __shared__ uint4 s_vtxAll[GEOM_WARPS][CL_VERTS];
@@ -246,7 +246,7 @@ __global__ void __launch_bounds__(GEOM_WARPS * 32) geometry_transparent_kernel(c
     __shared__ uint4 s_vtxAll[GEOM_WARPS][CL_VERTS];
     __shared__ float s_mvpAll[GEOM_WARPS][16];
     __shared__ float s_lut[256];
-    s_lut[threadIdx.x] = sbIn.srgbLut[threadIdx.x];
+    for (uint32_t i = threadIdx.x; i < 256u; i += GEOM_WARPS * 32) s_lut[i] = sbIn.srgbLut[i];
     __syncthreads();
     __shared__ ShadeBuffers s_sb;
     if (threadIdx.x == 0) { s_sb = sbIn; s_sb.srgbLut = s_lut; }
@@ -322,7 +322,7 @@ __global__ void __launch_bounds__(256) large_transparent_kernel(const __grid_con
 // ---- shade + resolve: one thread per pixel of the scissor rectangle; a CTA is a 16x8 pixel block,
 // each warp an 8x4 footprint (triangle / texel / shadow-map locality).  The sRGB decode table
 // lives in shared memory.
-__global__ void __launch_bounds__(128) shade_kernel(const __grid_constant__ ShadeConst sc, const __grid_constant__ ShadeBuffers sbIn) {
+__global__ void __launch_bounds__(128, VKR_SHADE_MIN_CTAS) shade_kernel(const __grid_constant__ ShadeConst sc, const __grid_constant__ ShadeBuffers sbIn) {
     __shared__ float s_lut[256];
     s_lut[threadIdx.x] = sbIn.srgbLut[threadIdx.x];
     s_lut[threadIdx.x + 128] = sbIn.srgbLut[threadIdx.x + 128];

@@ -34,7 +34,16 @@ static const int SMALL_MAX = 16;           // in-thread raster when bbox is <= S
 static const int CL_TRIS = 128;            // a cluster (one warp's unit of work) holds at most this many triangles ...
 static const int CL_VERTS = 128;           // ... and this many distinct vertices (7-bit local ids, 2 KB of shared memory)
 static const int SEQ_SLOT = 256;           // primitive sequence numbers are handed out to draws in slots of 256
-static const int GEOM_WARPS = 8;           // warps (clusters) per geometry CTA
+#ifndef VKR_GEOM_WARPS
+#define VKR_GEOM_WARPS 4
+#endif
+static const int GEOM_WARPS = VKR_GEOM_WARPS;   // warps (clusters) per geometry CTA
+#ifndef VKR_SHADE_MIN_CTAS
+#define VKR_SHADE_MIN_CTAS 12              // shading CTAs (128 threads) resident per SM the register allocation must allow
+#endif
+#ifndef VKR_GEOM_MIN_CTAS
+#define VKR_GEOM_MIN_CTAS 12               // geometry CTAs resident per SM the register allocation must allow (48 warps, 40 registers)
+#endif
 static const float GUARD_BAND = 64.0f;     // clip x,y only beyond +-GUARD_BAND*w
 
 // One mesh in HBM: SoA, 3 x 16-byte streams + u32 indices.

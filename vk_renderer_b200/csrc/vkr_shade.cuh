@@ -27,7 +27,7 @@ VKR_HD float clamp01(float x) { return fminf(fmaxf(x, 0.0f), 1.0f); }
 #if defined(__CUDA_ARCH__)
 #define VKR_LDG(p) __ldg(p)
 VKR_HD float fdiv(float a, float b) { return __fdividef(a, b); }
-VKR_HD float frcp(float a) { return __frcp_rn(a); }
+VKR_HD float frcp(float a) { float r; asm("rcp.approx.f32 %0, %1;" : "=f"(r) : "f"(a)); return r; }   // 1 ulp; colour only
 VKR_HD float frsqrt(float a) { return rsqrtf(a); }
 VKR_HD float fpow(float x, float e) { return __powf(x, e); }
 VKR_HD float flog2(float x) { return __log2f(x); }
@@ -74,6 +74,17 @@ VKR_HD float h2f_bits(uint16_t h) {
 #endif
 }
 VKR_HD float round_f16(float f) { return h2f_bits(f2h_bits(f)); }
+// Presentation only (colour, +-1 LSB tolerance): saturate + round-to-nearest-even; differs from unorm8() below on exact .5 ties.
+// Texture creation (mip chain; its alpha decides cut-out coverage) must use unorm8().
+VKR_HD uint32_t unorm8_fast(float x) {
+#if defined(__CUDA_ARCH__)
+    return __float2uint_rn(__saturatef(x) * 255.0f);     // NaN -> 0
+#else
+    if (!(x > 0.0f)) return 0u;
+    if (x >= 1.0f) return 255u;
+    return (uint32_t)floorf(x * 255.0f + 0.5f);
+#endif
+}
 VKR_HD uint32_t unorm8(float x) {
     if (!(x > 0.0f)) return 0u;
     if (x >= 1.0f) return 255u;
@@ -88,7 +99,10 @@ VKR_HD float4 fetch_texel(const DTexture& t, const float* __restrict__ lut, int 
     if (t.flags & 1u) return make_float4(lut[p.x], lut[p.y], lut[p.z], p.w * (1.0f / 255.0f));   // lut: shared memory on the device
     return make_float4(p.x * (1.0f / 255.0f), p.y * (1.0f / 255.0f), p.z * (1.0f / 255.0f), p.w * (1.0f / 255.0f));
 }
-VKR_HD int wrap_repeat(int i, int n) { int r = i % n; return r < 0 ? r + n : r; }
+VKR_HD int wrap_repeat(int i, int n) {
+    if ((n & (n - 1)) == 0) return i & (n - 1);       // power-of-two extent (the usual case): two's-complement AND is the floor-mod
+    int r = i % n; return r < 0 ? r + n : r;
+}
 VKR_HD int level_dim(uint32_t d, int level) { int v = (int)(d >> level); return v < 1 ? 1 : v; }
 
 VKR_HD float4 sample_level(const DTexture& t, const float* lut, int level, float u, float v) {
@@ -120,6 +134,9 @@ VKR_HD float4 texture2d(const ShadeBuffers& sb, int id, float u, float v, float 
     if (id < 0 || id >= VKR_MAX_BINDLESS) return make_float4(0, 0, 0, 1);
     const DTexture& t = sb.textures[id];
     if (t.data == nullptr) return make_float4(0, 0, 0, 1);
+    // 1x1 textures — the engine's default white/grey/black/normal images (src/vk_engine_init.cpp:320-333), i.e. every
+    // untextured material: any filter returns that texel
+    if ((t.w | t.h) == 1u) return fetch_texel(t, sb.srgbLut, 0, 0, 0, 1);
     const int levels = (int)t.levels;
     if (levels == 1) return sample_level(t, sb.srgbLut, 0, u, v);
     float w = (float)t.w, h = (float)t.h;
@@ -511,7 +528,7 @@ VKR_HD void shade_pixel(const ShadeConst& sc, const ShadeBuffers& sb, int px, in
 #else
     h[0] = f2h_bits(r); h[1] = f2h_bits(g); h[2] = f2h_bits(b); h[3] = f2h_bits(a);
 #endif
-    sb.rgba8[pix] = unorm8(r) | (unorm8(g) << 8) | (unorm8(b) << 16) | (unorm8(a) << 24);
+    sb.rgba8[pix] = unorm8_fast(r) | (unorm8_fast(g) << 8) | (unorm8_fast(b) << 16) | (unorm8_fast(a) << 24);
 }
 
 }  // namespace vkr

@@ -129,3 +129,51 @@ class _Null:
 
     def __exit__(self, *a):
         return False
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# Frame-parallel multi-view rendering (BASELINE config 5)
+def view_slice(rank: int, world: int, n_views: int) -> range:
+    """Views owned by `rank`: view i -> rank i mod world (the camera paths of a dataset are smooth, so dealing the
+    views round-robin gives every rank the same mix of cheap and expensive ones)."""
+    return range(rank, n_views, world)
+
+
+class ViewSharder:
+    """A batch of camera views of one replicated scene, view i on rank i mod world.  Views are independent: there is
+    no exchange step — every rank renders its views and reads them back to its own host memory.  On the CUDA library
+    the read-back of view k overlaps the rendering of view k+1 (two pinned landing buffers = the renderer's
+    FRAME_OVERLAP), on the host emulation it is a plain copy."""
+
+    def __init__(self, renderer, rank: int, world: int, cuda: bool):
+        self.r, self.rank, self.world, self.cuda = renderer, rank, world, cuda
+        self.W, self.H = renderer.width, renderer.height
+        self._pinned = None
+        if cuda:
+            self._pinned = [torch.empty((self.H, self.W, 4), dtype=torch.uint8).pin_memory() for _ in range(2)]
+
+    def render(self, scenes, objects, fp, sink=None):
+        """`scenes[i]` is view i's GPUSceneData (camera matrices, light, cascades).  Calls `sink(view, image)` for every
+        view of this rank, `image` an (H, W, 4) uint8 array valid during the call; returns how many views it rendered.
+        Without a sink the images are still produced and read back (throughput measurements)."""
+        mine = view_slice(self.rank, self.world, len(scenes))
+        if not self.cuda:
+            for v in mine:
+                self.r.draw(scenes[v], objects, fp)
+                img = self.r.readback(capi.TARGET_RGBA8)
+                if sink is not None:
+                    sink(v, img)
+            return len(mine)
+        nbytes = self.W * self.H * 4
+        prev = None
+        for k, v in enumerate(mine):
+            self.r.draw(scenes[v], objects, fp)
+            self.r.readback_async(capi.TARGET_RGBA8, self._pinned[k % 2].data_ptr(), nbytes)
+            if prev is not None and sink is not None:
+                self.r.sync()          # a consumer on the host serialises the pipeline; throughput runs pass no sink
+                sink(prev[0], self._pinned[prev[1] % 2].numpy())
+            prev = (v, k)
+        self.r.sync()
+        if prev is not None and sink is not None:
+            sink(prev[0], self._pinned[prev[1] % 2].numpy())
+        return len(mine)
