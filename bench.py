@@ -123,6 +123,17 @@ def measured_peak():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def measured_traffic(kernel):
+    """DRAM bytes per launch of `kernel` from the newest committed ncu capture (profiles/*_traffic.json, written by
+    tools/ncu_summary.py), or None."""
+    import glob
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "*_traffic.json")))
+    if not files:
+        return None, None
+    d = json.load(open(files[-1]))
+    return d["dram_bytes_per_launch"].get(kernel), os.path.basename(files[-1])
+
+
 def load_oracle():
     subprocess.run(["make", "-s", "-C", os.path.join(ROOT, "oracle")], check=True)
     return ctypes.CDLL(os.path.join(ROOT, "oracle", "_build", "libork.so"))
@@ -290,6 +301,7 @@ def run_b200(args):
         peak, peak_src = measured_peak()
         frame_bytes, gk_bytes = algorithmic_bytes(info)
         gk_ms = avg["geom_kernel"]
+        traffic, traffic_src = measured_traffic("geometry_kernel<0>")
         achieved = gk_bytes / (gk_ms / 1000.0) / 1e9 if gk_ms > 0 else 0.0
         line = {
             "metric": "frames_per_sec_4k_pbr_shadow", "value": fps, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
@@ -301,7 +313,7 @@ def run_b200(args):
                                "frac": frame_bytes * fps / 1e9 / peak, "algorithmic_bytes": frame_bytes,
                                "frac_of_nominal_8TBs": frame_bytes * fps / 1e9 / 8000.0},
             "roofline": {"bound": "hbm", "kernel": "geometry_kernel<main>", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None, "algorithmic_bytes": gk_bytes, "kernel_ms": gk_ms,
+                         "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "algorithmic_bytes": gk_bytes, "kernel_ms": gk_ms,
                          "peak_source": peak_src},
             "pass_ms": avg, "pass_ms_last_pipelined_frame": {k: float(v) for k, v in tm.items()},
             "host_issue_ms_per_step": host_issue_ms, "host_vkr_draw_call_ms": float(np.median(host_call)),

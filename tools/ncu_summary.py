@@ -23,4 +23,17 @@ with open(f"profiles/{tag}_ncu_summary.md", "w") as f:
         f.write("```\n\n")
     if reading:
         f.write(reading + "\n")
+# per-launch DRAM traffic of each kernel (dram__bytes_read.sum + dram__bytes_write.sum): bench.py reports it as roofline.traffic
+import json, re
+def _bytes(v, u):
+    x = float(v.replace(",", ""))
+    return x * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(u, 1)
+traffic = {}
+ir, iw, ik = H.index('dram__bytes_read.sum'), H.index('dram__bytes_write.sum'), H.index('Kernel Name')
+for r in rows[2:]:
+    name = re.sub(r"\(.*", "", r[ik]).replace("void ", "").strip()
+    traffic.setdefault(name, []).append(_bytes(r[ir], units[ir]) + _bytes(r[iw], units[iw]))
+with open(f"profiles/{tag}_traffic.json", "w") as f:
+    json.dump({"source": f"ncu --set full capture {tag} (bench.py --steps 2 --warmup 3, config 4); bytes per launch, mean over captured launches",
+               "dram_bytes_per_launch": {k: sum(v) / len(v) for k, v in traffic.items()}}, f, indent=1)
 print(open(f"profiles/{tag}_ncu_summary.md").read())
