@@ -277,16 +277,19 @@ def run_b200(args):
     h2d = r.upload_bytes()                                  # what vkr_draw copied host->device for the last frame (draw records,
                                                             # cluster/slot prefixes, light MVPs, shading constants)
     d2h = W * H * 4                                         # rank 0 reads the assembled frame back
+    # two cameras alternate so that consecutive frames differ: a read-back that raced with a later frame's rendering
+    # (or a gather that mixed frames) is caught by the check after the loop
+    view_b = mg.camera_view((0.6, 7.2, 40.0), pitch=-0.17)
+    sd_b = capi.make_scene_data(view_b, mg.camera_projection(W / H), [mg.light_matrix()] * 4, shadow_mode=1, enable_shadows=True)
+    cams = [sd, sd_b]
+    target = capi.TARGET_RGBA8_GATHERED if world > 1 else capi.TARGET_RGBA8
     barrier()
     t0 = time.perf_counter()
     for i in range(args.steps):
         objs_frame = np.array(my_objs, copy=True)            # the host rebuilds its draw list every frame (update_scene)
-        r.draw(sd, objs_frame, fp)
-        if world > 1:
-            if rank == 0:
-                r.readback_async(capi.TARGET_RGBA8_GATHERED, pinned[i % 2].data_ptr(), W * H * 4)
-        else:
-            r.readback_async(capi.TARGET_RGBA8, pinned[i % 2].data_ptr(), W * H * 4)
+        r.draw(cams[i % 2], objs_frame, fp)
+        if world == 1 or rank == 0:
+            r.readback_async(target, pinned[i % 2].data_ptr(), W * H * 4)
     r.sync()
     barrier()
     e2e_s = time.perf_counter() - t0
@@ -295,6 +298,16 @@ def run_b200(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_s = float(t.item())
     checksum = int(pinned[(args.steps - 1) % 2].view(-1)[::4097].to(torch.int64).sum()) if rank == 0 else 0
+    e2e_ok = True
+    for i in (args.steps - 2, args.steps - 1):               # the last two frames, re-rendered and read back synchronously
+        if i < 0:
+            continue
+        r.draw(cams[i % 2], my_objs, fp)
+        want = r.readback(target)
+        if rank == 0 and not np.array_equal(want, pinned[i % 2].numpy()):
+            e2e_ok = False
+    if rank == 0 and not e2e_ok:
+        raise SystemExit("bench.py: an asynchronously read-back frame differs from the same frame rendered synchronously")
 
     if rank == 0:
         fps = args.steps / (ms / 1000.0)
@@ -319,7 +332,7 @@ def run_b200(args):
             "host_issue_ms_per_step": host_issue_ms, "host_vkr_draw_call_ms": float(np.median(host_call)),
             "cluster_culling": cull,
             "e2e": {"value": args.steps / e2e_s, "unit": "frames/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                    "checksum": checksum},
+                    "checksum": checksum, "frames_verified": 2},
             "gpu_launches": int(launches),
             "clocks": clocks,
         }

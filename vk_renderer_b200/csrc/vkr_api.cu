@@ -8,6 +8,7 @@
 #include <nccl.h>
 
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -150,6 +151,7 @@ __global__ void expand_chunks_kernel(const DObject* __restrict__ objects, const 
 // PASS: 0 main (visibility buffer), 1 shadow (depth only), 2 transparent (shade + additive blend, no depth write).
 enum { PASS_MAIN = 0, PASS_SHADOW = 1, PASS_TRANSPARENT = 2 };
 
+
 template <int PASS, class MakeSink>
 __device__ __forceinline__ void geometry_warp(const DChunk* __restrict__ chunk, const float* __restrict__ mvps, uint32_t mvpStride,
                                               const RasterTarget& rt, const Queues& q, uint4* s_vtx, float* mvp, const MakeSink& makeSink) {
@@ -163,6 +165,11 @@ __device__ __forceinline__ void geometry_warp(const DChunk* __restrict__ chunk, 
     const uint32_t* __restrict__ clOrig = reinterpret_cast<const uint32_t*>(((uint64_t)c1.w << 32) | c1.z);
     const uint32_t obj = c2.x, seqBase = c2.y, counts = c2.z, flags = c2.w;
     if (PASS == PASS_MAIN && (flags & 2u)) return;     // alpha-tested draw: geometry_cutout_kernel owns this cluster
+    const uint32_t nVerts = counts & 0xFFFFu, nTris = counts >> 16;
+    // the cluster's vertex indices are needed only if it survives the culls, but their latency hides behind them
+    uint32_t vi[CL_VERTS / 32];
+#pragma unroll
+    for (int k = 0; k < CL_VERTS / 32; ++k) vi[k] = lane + 32u * k < nVerts ? __ldg(clVerts + lane + 32u * k) : 0u;
     if (lane < 16) mvp[lane] = __ldg(mvps + (size_t)obj * mvpStride + lane);
     __syncwarp();
 
@@ -182,17 +189,28 @@ __device__ __forceinline__ void geometry_warp(const DChunk* __restrict__ chunk, 
         const ClusterRect rect = cluster_finalize(a, rt);
         bool culled = rect.verdict == CLUSTER_CULLED;
         if (rect.verdict == CLUSTER_TEST) {
-            // the warp walks the rectangle as 8x4 pixel footprints and stops at the first visible pixel
+            // the warp walks the rectangle as 8x16 pixel footprints (four independent loads per lane in flight) and stops
+            // at the first footprint with a visible pixel
             bool hidden = true;
-            for (int32_t py = rect.y0 + (lane >> 3); __any_sync(0xFFFFFFFFu, py <= rect.y1) && hidden; py += 4) {
-                for (int32_t px = rect.x0 + (lane & 7); px <= rect.x1 && py <= rect.y1; px += 8) {
-                    // .cg: read at L2, where the RED.MIN of the other warps land (stale L1 lines would only lose culls)
-                    uint32_t stored;
-                    if (PASS == PASS_SHADOW) stored = __ldcg(rt.depthBits + (size_t)py * rt.width + px);
-                    else stored = __ldcg(reinterpret_cast<const uint32_t*>(rt.vis + (size_t)py * rt.width + px) + 1);
-                    hidden = hidden && depth_hides(stored, rect.zminBits);
+            const int32_t lx = lane & 7, ly = lane >> 3;
+            for (int32_t by = rect.y0; by <= rect.y1 && hidden; by += 16) {
+                for (int32_t bx = rect.x0; bx <= rect.x1 && hidden; bx += 8) {
+                    const int32_t px = bx + lx;
+                    uint32_t stored[4];
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const int32_t py = by + ly + 4 * k;
+                        stored[k] = 0u;                                     // outside the rectangle: counts as hidden
+                        if (px <= rect.x1 && py <= rect.y1) {
+                            // .cg: read at L2, where the RED.MIN of the other warps land (stale L1 lines would only lose culls)
+                            if (PASS == PASS_SHADOW) stored[k] = __ldcg(rt.depthBits + (size_t)py * rt.width + px);
+                            else stored[k] = __ldcg(reinterpret_cast<const uint32_t*>(rt.vis + (size_t)py * rt.width + px) + 1);
+                        }
+                    }
+                    const bool h = depth_hides(stored[0], rect.zminBits) && depth_hides(stored[1], rect.zminBits) &&
+                                   depth_hides(stored[2], rect.zminBits) && depth_hides(stored[3], rect.zminBits);
+                    hidden = __all_sync(0xFFFFFFFFu, h);
                 }
-                hidden = __all_sync(0xFFFFFFFFu, hidden);
             }
             culled = hidden;
         }
@@ -200,10 +218,16 @@ __device__ __forceinline__ void geometry_warp(const DChunk* __restrict__ chunk, 
     }
 
     // ---- phase 1: distinct vertices
-    const uint32_t nVerts = counts & 0xFFFFu, nTris = counts >> 16;
-    for (uint32_t v = lane; v < nVerts; v += 32) {
-        const CachedVtx cv = cluster_vertex(mvp, __ldg(pos + __ldg(clVerts + v)), rt);
-        s_vtx[v] = make_uint4((uint32_t)cv.X, (uint32_t)cv.Y, cv.zbits, cv.flag);
+    {
+        float4 p[CL_VERTS / 32];
+#pragma unroll
+        for (int k = 0; k < CL_VERTS / 32; ++k) if (lane + 32u * k < nVerts) p[k] = __ldg(pos + vi[k]);
+#pragma unroll
+        for (int k = 0; k < CL_VERTS / 32; ++k)
+            if (lane + 32u * k < nVerts) {
+                const CachedVtx cv = cluster_vertex(mvp, p[k], rt);
+                s_vtx[lane + 32u * k] = make_uint4((uint32_t)cv.X, (uint32_t)cv.Y, cv.zbits, cv.flag);
+            }
     }
     __syncwarp();
 
@@ -358,6 +382,8 @@ struct FrameSlot {
     void* devbuf = nullptr; size_t devCap = 0;
     cudaEvent_t uploaded = nullptr;
     cudaEvent_t rendered = nullptr;
+    cudaEvent_t copied = nullptr;       // last asynchronous read-back of this slot's presented image (copy stream)
+    bool copyPending = false;
 };
 
 struct VkrDevice {
@@ -394,6 +420,8 @@ struct VkrDevice {
     std::vector<std::vector<uint32_t>> meshIndexHost;   // host copy of each mesh's indices (cluster building)
     std::vector<std::vector<float4>> meshPosHost;       // ... and positions (cluster bounds, Morton order)
     size_t uploadBytes = 0;
+    // VKR_HOST_PROF=1: mean host time of vkr_draw's sections, printed at vkr_destroy
+    bool hostProf = false; double hostProfUs[8] = {0}; uint64_t hostProfFrames = 0;
 
     DChunk* chunkBuf = nullptr; size_t chunkCap = 0;   // per-frame cluster table (device-written)
     uint2* chunkObjBuf = nullptr; size_t seqSlotCap = 0;   // seq >> 8 -> (draw, first triangle)
@@ -507,6 +535,7 @@ int vkr_create(const VkrConfig* cfg, VkrDevice** out) {
     dev->S = cfg->shadowExtent ? cfg->shadowExtent : 2048;
     dev->flags = cfg->flags;
     dev->smCount = prop.multiProcessorCount;
+    dev->hostProf = std::getenv("VKR_HOST_PROF") != nullptr;
     *out = dev;
     auto body = [&]() -> int {
         CK(cudaSetDevice(dev->device));
@@ -545,6 +574,7 @@ int vkr_create(const VkrConfig* cfg, VkrDevice** out) {
         for (auto& s : dev->slots) {
             CK(cudaEventCreateWithFlags(&s.uploaded, cudaEventDisableTiming));
             CK(cudaEventCreateWithFlags(&s.rendered, cudaEventDisableTiming));
+            CK(cudaEventCreateWithFlags(&s.copied, cudaEventDisableTiming));
         }
         for (auto& e : dev->tev) CK(cudaEventCreate(&e));
         // shadow image starts cleared to 1.0 so an un-rendered map reads "unshadowed"
@@ -575,12 +605,19 @@ void vkr_destroy(VkrDevice* dev) {
     if (!dev) return;
     cudaSetDevice(dev->device);
     cudaDeviceSynchronize();
+    if (dev->hostProf && dev->hostProfFrames) {
+        const double f = 1.0 / (double)dev->hostProfFrames;
+        std::fprintf(stderr, "[vkr host rank %d] vkr_draw us/frame over %llu frames: plan %.1f | upload+expand %.1f | shadow (+exchange) %.1f | "
+                     "main raster %.1f | transparent+shade %.1f | gather %.1f\n", dev->shardRank, (unsigned long long)dev->hostProfFrames,
+                     dev->hostProfUs[0] * f, dev->hostProfUs[1] * f, dev->hostProfUs[2] * f, dev->hostProfUs[3] * f, dev->hostProfUs[4] * f, dev->hostProfUs[5] * f);
+    }
     for (auto it = dev->allocations.rbegin(); it != dev->allocations.rend(); ++it) cudaFree(*it);
     for (auto& s : dev->slots) {
         if (s.pinned) cudaFreeHost(s.pinned);
         if (s.devbuf) cudaFree(s.devbuf);
         if (s.uploaded) cudaEventDestroy(s.uploaded);
         if (s.rendered) cudaEventDestroy(s.rendered);
+        if (s.copied) cudaEventDestroy(s.copied);
     }
     for (auto& e : dev->tev) if (e) cudaEventDestroy(e);
     if (dev->countersHost) cudaFreeHost(dev->countersHost);
@@ -733,11 +770,19 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
     if (!dev) return VKR_ERROR_INVALID_ARGUMENT;
     if (!scene || !fp || (n && !objs)) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_draw: null argument");
     CK(cudaSetDevice(dev->device));
+    auto hostT = std::chrono::steady_clock::now();
+    auto mark = [&](int k) {
+        if (!dev->hostProf || dev->frameIndex < 16) return;      // skip allocation / NCCL warm-up frames
+        const auto now = std::chrono::steady_clock::now();
+        dev->hostProfUs[k] += std::chrono::duration<double, std::micro>(now - hostT).count();
+        hostT = now;
+    };
     FramePlan& plan = dev->plan;
     DeviceClusterProvider provider(dev);
     std::string why = plan_frame(scene, objs, n, fp, dev->meshes, dev->materials, dev->texHost, provider, dev->W, dev->H, dev->S, plan,
                                  dev->shardRank, dev->shardRanks);     // sharded: also splits the rows into cost-balanced bands
     if (!why.empty()) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, why.c_str());
+    mark(0);
     cudaStream_t st = dev->stream;
     dev->launches = 0;
     const bool timing = dev->flags & VKR_CONFIG_TIMINGS;
@@ -810,6 +855,7 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
         dev->launches += 1;
     }
     if (timing) CK(cudaEventRecord(dev->tev[1], st));
+    mark(1);
 
     const unsigned largeGrid = (unsigned)dev->smCount * 4;
 
@@ -854,6 +900,7 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
         CK(cudaEventRecord(dev->evShadow, ss));
     }
 
+    mark(2);
     // ---- draw_geometry, raster half (src/vk_engine_run.cpp:244-311)
     {
         RasterTarget rt = plan.mainTarget;
@@ -881,6 +928,7 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
         CK(cudaMemcpyAsync(dev->countersHost, dev->q.counters, 16, cudaMemcpyDeviceToHost, st));
     }
     if (timing) CK(cudaEventRecord(dev->tev[5], st));
+    mark(3);
 
     if (plan.shadowLayers) CK(cudaStreamWaitEvent(st, dev->evShadow, 0));   // join: the shaders sample the shadow map
     ShadeBuffers sb{};
@@ -911,6 +959,7 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
 
     // ---- shading half of draw_geometry + draw_skybox + draw_background + draw_postprocess + present blit
     if (dev->shardRanks > 1 && dev->gatheredValid[slotIdx]) CK(cudaStreamWaitEvent(st, dev->gatheredEv[slotIdx], 0));   // rgba8[slot] still being gathered
+    if (slot.copyPending) CK(cudaStreamWaitEvent(st, slot.copied, 0));      // ... or still being read back (FRAME_OVERLAP frames ago)
     {
         dim3 grid((sc.sx1 - sc.sx0 + 15) / 16, (sc.sy1 - sc.sy0 + 7) / 8);
         if (grid.x && grid.y) { shade_kernel<<<grid, 128, 0, st>>>(sc, sb); dev->launches += 1; }
@@ -918,8 +967,10 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
     if (timing) { CK(cudaEventRecord(dev->tev[6], st)); dev->tevValid = true; dev->shadowTimed = plan.shadowLayers > 0; }
     CK(cudaGetLastError());
     CK(cudaEventRecord(slot.rendered, st));
+    mark(4);
     if (dev->shardRanks > 1) {          // assemble the presented image; overlaps the next frame's rendering
         CK(cudaStreamWaitEvent(dev->gatherStream, slot.rendered, 0));
+        if (slot.copyPending) CK(cudaStreamWaitEvent(dev->gatherStream, slot.copied, 0));   // the landing buffer may still be being read back
         if (timing) CK(cudaEventRecord(dev->tev[11], dev->gatherStream));
         if (exchange_bands(dev->rgba8[slotIdx], dev->gathered[slotIdx], plan.bandMain, 0, (int)dev->H, dev->W, dev->shardRank, dev->shardRanks,
                            dev->commFrame, dev->gatherStream) != ncclSuccess)
@@ -928,6 +979,8 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
         CK(cudaEventRecord(dev->gatheredEv[slotIdx], dev->gatherStream));
         dev->gatheredValid[slotIdx] = true;
     }
+    mark(5);
+    if (dev->hostProf && dev->frameIndex >= 16) dev->hostProfFrames++;
     dev->lastSlot = slotIdx;
     dev->lastChunkObj = dev->chunkObjBuf; dev->lastObjects = dObjects;
     dev->frameIndex++;
@@ -999,6 +1052,12 @@ static int do_readback(VkrDevice* dev, VkrTarget what, void* dst, size_t dstByte
     CK(cudaStreamWaitEvent(dev->copyStream, dev->slots[dev->lastSlot].rendered, 0));
     if (what == VKR_TARGET_RGBA8_GATHERED && dev->shardRanks > 1) CK(cudaStreamWaitEvent(dev->copyStream, dev->gatheredEv[dev->lastSlot], 0));
     CK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, dev->copyStream));
+    if (what == VKR_TARGET_RGBA8 || what == VKR_TARGET_RGBA8_GATHERED) {
+        // the frame FRAME_OVERLAP draws from now writes this image again: it must wait for this copy
+        FrameSlot& s = dev->slots[dev->lastSlot];
+        CK(cudaEventRecord(s.copied, dev->copyStream));
+        s.copyPending = true;
+    }
     if (sync) return vkr_sync(dev);
     return VKR_SUCCESS;
 }
