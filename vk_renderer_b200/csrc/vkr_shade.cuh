@@ -26,11 +26,14 @@ VKR_HD float clamp01(float x) { return fminf(fmaxf(x, 0.0f), 1.0f); }
 
 #if defined(__CUDA_ARCH__)
 #define VKR_LDG(p) __ldg(p)
-VKR_HD float fdiv(float a, float b) { return __fdividef(a, b); }
-VKR_HD float frcp(float a) { float r; asm("rcp.approx.f32 %0, %1;" : "=f"(r) : "f"(a)); return r; }   // 1 ulp; colour only
-VKR_HD float frsqrt(float a) { return rsqrtf(a); }
-VKR_HD float fpow(float x, float e) { return __powf(x, e); }
-VKR_HD float flog2(float x) { return __log2f(x); }
+// Colour-only arithmetic (tolerance 1/255 on the 8-bit image): the approximate, flush-to-zero SFU forms, one instruction each —
+// the non-ftz intrinsics wrap every MUFU in a denormal range fix-up.
+VKR_HD float frcp(float a) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a)); return r; }
+VKR_HD float fdiv(float a, float b) { return a * frcp(b); }
+VKR_HD float frsqrt(float a) { float r; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a)); return r; }
+VKR_HD float flog2(float x) { float r; asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+VKR_HD float fexp2(float x) { float r; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+VKR_HD float fpow(float x, float e) { return fexp2(e * flog2(x)); }      // x >= 0; pow(0, e > 0) = ex2(-inf) = 0
 #else
 #define VKR_LDG(p) (*(p))
 VKR_HD float fdiv(float a, float b) { return a / b; }
@@ -125,8 +128,9 @@ VKR_HD float4 sample_level(const DTexture& t, const float* lut, int level, float
                        t00.w * w00 + t10.w * w10 + t01.w * w01 + t11.w * w11);
 }
 
-VKR_HD float lod_from_rho(float rho, int levels) {
-    float lambda = rho > 0.0f ? flog2(rho) : -126.0f;
+// lod from the SQUARE of the footprint's longer axis: log2(sqrt(x)) = log2(x) / 2, no square roots
+VKR_HD float lod_from_rho2(float rho2, int levels) {
+    float lambda = rho2 > 0.0f ? 0.5f * flog2(rho2) : -126.0f;
     return fminf(fmaxf(lambda, 0.0f), (float)(levels - 1));
 }
 
@@ -140,9 +144,9 @@ VKR_HD float4 texture2d(const ShadeBuffers& sb, int id, float u, float v, float 
     const int levels = (int)t.levels;
     if (levels == 1) return sample_level(t, sb.srgbLut, 0, u, v);
     float w = (float)t.w, h = (float)t.h;
-    float rx = sqrtf((dudx * w) * (dudx * w) + (dvdx * h) * (dvdx * h));
-    float ry = sqrtf((dudy * w) * (dudy * w) + (dvdy * h) * (dvdy * h));
-    float lod = lod_from_rho(fmaxf(rx, ry), levels);
+    float rx2 = (dudx * w) * (dudx * w) + (dvdx * h) * (dvdx * h);
+    float ry2 = (dudy * w) * (dudy * w) + (dvdy * h) * (dvdy * h);
+    float lod = lod_from_rho2(fmaxf(rx2, ry2), levels);
     int l0 = (int)floorf(lod);
     int l1 = l0 + 1 < levels ? l0 + 1 : levels - 1;
     float f = lod - (float)l0;
@@ -369,7 +373,7 @@ VKR_HD float4 texture_cube(const ShadeBuffers& sb, f3 r, f3 rdx, f3 rdy) {
     cube_project(rdy, face, sy, ty);
     float w = (float)tex.w, h = (float)tex.h;
     float ax = (sx - s) * w, bx = (tx - t) * h, ay = (sy - s) * w, by = (ty - t) * h;
-    float lod = lod_from_rho(fmaxf(sqrtf(ax * ax + bx * bx), sqrtf(ay * ay + by * by)), levels);
+    float lod = lod_from_rho2(fmaxf(ax * ax + bx * bx, ay * ay + by * by), levels);
     int l0 = (int)floorf(lod);
     int l1 = l0 + 1 < levels ? l0 + 1 : levels - 1;
     float f = lod - (float)l0;
