@@ -14,6 +14,7 @@ NUM_CASCADES = 4
 MAX_BINDLESS = 4096
 
 SUCCESS = 0
+ERROR_INVALID_ARGUMENT, ERROR_OUT_OF_MEMORY, ERROR_CUDA, ERROR_NO_DEVICE, ERROR_CAPACITY = -1, -2, -3, -4, -5
 FORMAT_UNORM, FORMAT_SRGB = 0, 1
 SAMPLER_NEAREST, SAMPLER_LINEAR = 0, 1
 PASS_MAIN_COLOR, PASS_TRANSPARENT, PASS_OTHER = 0, 1, 2
