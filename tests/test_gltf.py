@@ -1,0 +1,168 @@
+"""glTF 2.0 / GLB ingestion of the host engine (csrc/host/vk_gltf.cpp) — VulkanEngine::load_gltf of the reference
+(src/vk_loader.cpp:227-518), SURVEY.md §8f-1.
+
+The files are written by tests/gltf_util.py from a plain-Python scene description, which is also turned — by independent
+numpy code — into what the loader has to produce: draw list (index ranges, world matrices, material constants with the
+reference's id swap, pass types) and, through rendering, vertex data and textures: the scene loaded from the file must
+render bit-identically to the same scene uploaded directly through the C-ABI.
+"""
+import numpy as np
+import pytest
+
+from vk_renderer_b200 import capi, engine as eng_mod
+from vk_renderer_b200.engine import Engine
+import gltf_util as gu
+import parity
+
+W, H, S = 200, 120, 256
+VARIANTS = ["external", "embedded", "glb"]
+
+
+def _engine(lib, prefix, path):
+    e = Engine(W, H, api_lib=lib, api_prefix=prefix, shadow_extent=S)
+    tris = e.load_gltf(path, "test")
+    e.set_camera((-1.0, 1.5, 9.0), pitch=-0.1)
+    e.set_toggles(shadows=1, shadow_mode=1, background=1, postprocess=1)
+    e.update_scene(0.0)
+    return e, tris
+
+
+def test_png_decoder_matches_the_encoder():
+    rng = np.random.default_rng(7)
+    for data, want in gu.make_images(rng):
+        got = eng_mod.decode_png(data)
+        assert got is not None and np.array_equal(got, want)
+    for filt in range(5):                                   # every scan-line filter on its own
+        img = rng.integers(0, 256, (9, 7, 4), dtype=np.uint8)
+        assert np.array_equal(eng_mod.decode_png(gu.png_bytes(img, 6, filt=filt)), img)
+    assert eng_mod.decode_png(b"\xff\xd8\xff\xe0 jpeg") is None
+    good = gu.png_bytes(rng.integers(0, 256, (4, 4, 3), dtype=np.uint8), 2)
+    assert eng_mod.decode_png(good[:len(good) // 2]) is None          # truncated stream
+    assert eng_mod.decode_png(good[:8]) is None
+
+
+@pytest.mark.parametrize("variant", VARIANTS)
+def test_draw_list_matches_the_description(ork_lib, tmp_path, variant):
+    asset = gu.build_asset(np.random.default_rng(11))
+    path = gu.write_gltf(asset, str(tmp_path), variant)
+    e, tris = _engine(ork_lib, "ork", path)
+    want = gu.expected_draws(asset)
+    assert tris == sum(n // 3 for _, _, _, n in want)
+    got = e.render_objects()
+    assert len(got) == len(want), "every object is in view: nothing may be culled or lost"
+    # update_scene sorts opaque-first (src/vk_engine_run.cpp:454-458)
+    passes = [pt for _, _, pt in got]
+    assert passes == sorted(passes)
+    mesh_of_prim = {}
+    unmatched = list(got)
+    for name, world, first, count in want:
+        hit = None
+        for k, (ro, mc, pt) in enumerate(unmatched):
+            if int(ro["firstIndex"]) == first and int(ro["indexCount"]) == count and \
+                    np.allclose(np.asarray(ro["transform"]).reshape(4, 4).T, world, rtol=0, atol=2e-6):
+                hit = k
+                break
+        assert hit is not None, f"no draw for {name}"
+        ro, mc, pt = unmatched.pop(hit)
+        exp = gu.expected_material(asset, asset["prims"][name]["material"])
+        assert list(mc.colorFactors) == [float(np.float32(x)) for x in exp["color"]]
+        assert (mc.metal_rough_factors[0], mc.metal_rough_factors[1]) == (float(np.float32(exp["metallic"])), float(np.float32(exp["roughness"])))
+        assert (mc.albedoID, mc.normalID, mc.metalRoughID) == (exp["albedoID"], exp["normalID"], exp["metalRoughID"]), name
+        assert pt == (1 if exp["transparent"] else 0)
+        mesh_of_prim.setdefault(name, set()).add(int(ro["mesh"]))
+    # one MeshAsset per glTF mesh: the two primitives of "ball" share a buffer, instances reuse it
+    assert mesh_of_prim["sphere"] == mesh_of_prim["cube"] and len(mesh_of_prim["sphere"]) == 1
+    assert mesh_of_prim["plane"].isdisjoint(mesh_of_prim["sphere"]) and mesh_of_prim["quad"].isdisjoint(mesh_of_prim["plane"])
+    e.close()
+
+
+def _render_direct(lib, prefix, asset, objects, sd, fp):
+    """The same scene through the C-ABI, converted from the description by numpy."""
+    r = capi.Renderer(lib, prefix, W, H, shadow_extent=S)
+    for k, (_, rgba) in enumerate(asset["images"]):
+        if rgba is None:          # _errorCheckerboardImage (src/vk_engine_init.cpp:329-341)
+            chk = np.zeros((16, 16, 4), np.uint8)
+            chk[..., 3] = 255
+            yy, xx = np.mgrid[0:16, 0:16]
+            chk[((xx % 2) ^ (yy % 2)) == 1] = (255, 0, 255, 255)
+            img = r.create_image(chk, capi.FORMAT_UNORM, False)
+        else:
+            img = r.create_image(rgba, capi.FORMAT_SRGB, True)
+        r.update_bindless_texture(2 + k, img, capi.SAMPLER_LINEAR)
+    mats = []
+    for i in range(len(asset["materials"])):
+        m = gu.expected_material(asset, i)
+        mats.append(r.build_material(m["color"], m["metallic"], m["roughness"], albedo_id=m["albedoID"], normal_id=m["normalID"],
+                                     metal_rough_id=m["metalRoughID"], pass_type=capi.PASS_TRANSPARENT if m["transparent"] else capi.PASS_MAIN_COLOR))
+    meshes = []
+    for m in asset["meshes"]:
+        vs, idx, base = [], [], 0
+        for name in m["prims"]:
+            p = asset["prims"][name]
+            if p["i"] is None:
+                continue
+            vs.append(p["v"]); idx.append(np.asarray(p["i"], np.uint32) + base); base += len(p["v"])
+        meshes.append(r.upload_mesh(np.concatenate(idx), np.concatenate(vs)))
+    # the engine's own draw list (order, matrices), with its handles mapped onto this renderer's by creation order
+    mesh_ids = sorted({int(o["mesh"]) for o, _, _ in objects})
+    mat_ids = sorted({int(o["material"]) for o, _, _ in objects})
+    assert len(mesh_ids) == len(meshes) and len(mat_ids) == len(mats)
+    objs = []
+    for o, _, _ in objects:
+        o2 = o.copy()
+        o2["mesh"] = meshes[mesh_ids.index(int(o["mesh"]))]
+        o2["material"] = mats[mat_ids.index(int(o["material"]))]
+        objs.append(o2)
+    r.draw(sd, np.array(objs), fp)
+    out = {k: r.readback(v) for k, v in dict(rgba=capi.TARGET_RGBA8, depth=capi.TARGET_DEPTH, prim=capi.TARGET_PRIMID, shadow=capi.TARGET_SHADOW).items()}
+    r.close()
+    return out
+
+
+@pytest.mark.parametrize("variant", VARIANTS)
+def test_loaded_scene_renders_like_direct_upload(ork_lib, tmp_path, variant):
+    asset = gu.build_asset(np.random.default_rng(11))
+    path = gu.write_gltf(asset, str(tmp_path), variant)
+    e, _ = _engine(ork_lib, "ork", path)
+    e.draw()
+    a = {k: e.readback(v) for k, v in dict(rgba=capi.TARGET_RGBA8, depth=capi.TARGET_DEPTH, prim=capi.TARGET_PRIMID, shadow=capi.TARGET_SHADOW).items()}
+    sd = e.scene_data()
+    fp = capi.default_frame_params(enableShadows=1, shadowMode=1, enableBackground=1, enablePostprocess=1, enableSkybox=0)
+    b = _render_direct(ork_lib, "ork", asset, e.render_objects(), sd, fp)
+    e.close()
+    assert (a["prim"] != 0xFFFFFFFF).mean() > 0.02
+    for k in a:
+        assert np.array_equal(a[k].view(np.uint8), b[k].view(np.uint8)), f"{k} differs: vertex data, indices, textures or materials were not loaded as described"
+
+
+def test_malformed_files_are_refused(ork_lib, tmp_path):
+    e = Engine(W, H, api_lib=ork_lib, api_prefix="ork", shadow_extent=S)
+    cases = {"missing.gltf": None, "garbage.gltf": b"{ not json", "empty.glb": b"glTF\x02\x00\x00\x00\x0c\x00\x00\x00",
+             "nobuffer.gltf": b'{"asset":{"version":"2.0"},"buffers":[{"byteLength":4,"uri":"nope.bin"}]}',
+             "badaccessor.gltf": b'{"asset":{"version":"2.0"},"meshes":[{"primitives":[{"indices":3,"attributes":{"POSITION":0}}]}]}'}
+    for name, data in cases.items():
+        p = tmp_path / name
+        if data is not None:
+            p.write_bytes(data)
+        with pytest.raises(RuntimeError):
+            e.load_gltf(str(p))
+    # a file with nothing in it but the asset tag loads as an empty scene (the reference builds a default material and a top node)
+    p = tmp_path / "empty.gltf"
+    p.write_text('{"asset": {"version": "2.0"}}')
+    assert e.load_gltf(str(p)) == 0
+    e.close()
+
+
+@pytest.mark.gpu
+def test_gltf_scene_on_the_device_matches_the_oracle(ork_lib, vkr_lib, tmp_path):
+    asset = gu.build_asset(np.random.default_rng(11))
+    path = gu.write_gltf(asset, str(tmp_path), "glb")
+    out = {}
+    for lib, prefix in ((ork_lib, "ork"), (None, "vkr")):
+        e, tris = _engine(lib, prefix, path)
+        e.draw()
+        out[prefix] = {k: e.readback(v) for k, v in dict(rgba=capi.TARGET_RGBA8, depth=capi.TARGET_DEPTH, prim=capi.TARGET_PRIMID,
+                                                        shadow=capi.TARGET_SHADOW).items()}
+        out[prefix].update(stats=e.stats(), shadows=True, layers=1)
+        e.close()
+    parity.assert_parity(out["ork"], out["vkr"])

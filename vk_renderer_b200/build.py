@@ -61,7 +61,22 @@ def build_engine(force=False):
         return target
     srcs = [s for s in deps if s.endswith(".cpp")]
     cmd = ["g++", "-O2", "-std=c++20", "-ffp-contract=off", "-fPIC", "-shared", "-Wall", "-I", os.path.join(ROOT, "include"),
-           "-o", target, *srcs, "-L", PKG, "-lvkr", "-Wl,-rpath,$ORIGIN", "-lpthread"]
+           "-o", target, *srcs, "-L", PKG, "-lvkr", "-Wl,-rpath,$ORIGIN", "-lpthread", "-lz"]   # zlib: PNG images of glTF files
+    subprocess.run(cmd, check=True)
+    return target
+
+
+def build_cli(force=False):
+    """vkr_render: the headless stand-in for the reference's window + ImGui panel (csrc/cli)."""
+    target = os.path.join(PKG, "vkr_render")
+    src = os.path.join(CSRC, "cli", "vkr_render.cpp")
+    if not os.path.exists(src):
+        return None
+    deps = _sources([os.path.join(CSRC, "host"), os.path.join(CSRC, "cli"), os.path.join(ROOT, "include")], (".cpp", ".h"))
+    if not force and _newer(target, deps):
+        return target
+    cmd = ["g++", "-O2", "-std=c++20", "-ffp-contract=off", "-Wall", "-I", os.path.join(ROOT, "include"), "-o", target, src,
+           "-L", PKG, "-lvkr_engine", "-lvkr", "-Wl,-rpath,$ORIGIN", "-lpthread"]
     subprocess.run(cmd, check=True)
     return target
 
@@ -69,6 +84,7 @@ def build_engine(force=False):
 def build_all(force=False, verbose=False):
     build_libvkr(force, verbose)
     build_engine(force)
+    build_cli(force)
 
 
 if __name__ == "__main__":

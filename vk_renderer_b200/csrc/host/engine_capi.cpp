@@ -4,6 +4,7 @@
 #include <cstring>
 
 #include "vk_engine.h"
+#include "vk_gltf.h"
 #include "vk_loader.h"
 
 const VkrApi& libvkr_api() {
@@ -28,6 +29,40 @@ VkrDevice* vke_device(VulkanEngine* e) { return e->_vkr; }
 
 uint64_t vke_load_procedural(VulkanEngine* e, int config, uint32_t seed) { return load_procedural(e, config, seed); }
 void vke_orbit_camera(VulkanEngine* e, uint32_t seed, int view) { orbit_camera(e, seed, view); }
+
+// init_scene's `_sceneRoot->addChild(load_gltf(name, file))` (src/vk_engine_init.cpp:646-660).  Returns the number of triangles
+// added, or -1 with the reason copied to err (may be null).
+int64_t vke_load_gltf(VulkanEngine* e, const char* name, const char* fileName, char* err, size_t errBytes) {
+    std::string why;
+    std::shared_ptr<Node> top = load_gltf(e, name ? name : "gltf", fileName ? fileName : "", &why);
+    if (!top) {
+        if (err && errBytes) { std::strncpy(err, why.c_str(), errBytes - 1); err[errBytes - 1] = 0; }
+        return -1;
+    }
+    e->_sceneRoot->addChild(top);
+    std::vector<RenderObject> all;
+    top->refreshTransform(vkm::mat4(1.0f), all);
+    int64_t tris = 0;
+    for (const RenderObject& o : all) tris += o.indexCount / 3;
+    return tris;
+}
+// The flattened scene after update_scene: object i's mesh/material handles, world matrix, index range and its material constants.
+int vke_render_object(VulkanEngine* e, size_t i, VkrRenderObject* out, MaterialConstants* params, int* passType) {
+    if (i >= e->_renderObjects.size()) return -1;
+    const RenderObject& o = e->_renderObjects[i];
+    out->mesh = o.mesh->meshBuffer; out->material = o.material ? o.material->materialSet : 0;
+    std::memcpy(out->transform, o.transform.data(), 64);
+    out->indexCount = o.indexCount; out->firstIndex = o.firstIndex;
+    if (params && o.material) *params = o.material->params;
+    if (passType && o.material) *passType = (int)o.material->passType;
+    return 0;
+}
+int vke_decode_png(const unsigned char* data, size_t size, unsigned char* rgbaOut, size_t outBytes, uint32_t* w, uint32_t* h) {
+    std::vector<unsigned char> px;
+    if (!decode_png(data, size, px, *w, *h)) return -1;
+    if (rgbaOut) { if (outBytes < px.size()) return -2; std::memcpy(rgbaOut, px.data(), px.size()); }
+    return 0;
+}
 
 void vke_set_camera(VulkanEngine* e, float x, float y, float z, float pitch, float yaw) {
     e->_mainCamera.position = vkm::vec3{x, y, z};

@@ -60,8 +60,24 @@ def load_engine() -> C.CDLL:
         lib.vke_compute_split.argtypes = [C.c_float, C.c_float, C.c_int]; lib.vke_compute_split.restype = C.c_float
         lib.vke_frustum_planes.argtypes = [p, C.POINTER(C.c_float)]
         lib.vke_is_visible.argtypes = [p, C.POINTER(C.c_float), C.POINTER(C.c_float), C.c_float]; lib.vke_is_visible.restype = C.c_int
+        lib.vke_load_gltf.argtypes = [p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_size_t]; lib.vke_load_gltf.restype = C.c_int64
+        lib.vke_render_object.argtypes = [p, C.c_size_t, p, C.POINTER(capi.MaterialConstants), C.POINTER(C.c_int)]
+        lib.vke_render_object.restype = C.c_int
+        lib.vke_decode_png.argtypes = [C.c_char_p, C.c_size_t, p, C.c_size_t, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
+        lib.vke_decode_png.restype = C.c_int
         _engine_lib = lib
     return _engine_lib
+
+
+def decode_png(data: bytes):
+    """The engine's PNG decoder (csrc/host/vk_gltf.cpp) -> (H, W, 4) uint8, or None when it refuses the stream."""
+    lib = load_engine()
+    w, h = C.c_uint32(), C.c_uint32()
+    if lib.vke_decode_png(data, len(data), None, 0, C.byref(w), C.byref(h)) != 0:
+        return None
+    out = np.empty((h.value, w.value, 4), np.uint8)
+    assert lib.vke_decode_png(data, len(data), out.ctypes.data, out.nbytes, C.byref(w), C.byref(h)) == 0
+    return out
 
 
 class Engine:
@@ -98,6 +114,24 @@ class Engine:
         if n == 0:
             raise RuntimeError("load_procedural failed")
         return n
+
+    def load_gltf(self, path, name="gltf") -> int:
+        """load_gltf + _sceneRoot->addChild (src/vk_engine_init.cpp:646-660).  Returns the triangles added."""
+        err = C.create_string_buffer(256)
+        n = self.lib.vke_load_gltf(self.e, name.encode(), os.fsencode(path), err, len(err))
+        if n < 0:
+            raise RuntimeError(f"load_gltf({path}): {err.value.decode()}")
+        return n
+
+    def render_objects(self):
+        """The draw list update_scene produced: [(VkrRenderObject record, MaterialConstants, pass type)]."""
+        out = []
+        for i in range(self.lib.vke_visible_objects(self.e)):
+            ro = np.zeros((), capi.RENDER_OBJECT_DTYPE)
+            mc, pt = capi.MaterialConstants(), C.c_int(0)
+            assert self.lib.vke_render_object(self.e, i, ro.ctypes.data, C.byref(mc), C.byref(pt)) == 0
+            out.append((ro, mc, pt.value))
+        return out
 
     def set_camera(self, pos, pitch=0.0, yaw=0.0):
         self.lib.vke_set_camera(self.e, *map(float, pos), float(pitch), float(yaw))
