@@ -1,0 +1,43 @@
+#!/usr/bin/env python
+"""Frames/s of BASELINE configs 1-3 (and 4 for reference) through the C++ host engine (update_scene + draw per frame),
+device-side pipelined: K frames issued back to back, one sync at the end.  Writes one JSON line per config.
+    python tools/bench_configs.py [--frames 300]"""
+import argparse
+import json
+import os
+import sys
+import time
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from vk_renderer_b200.engine import Engine  # noqa: E402
+
+SIZES = {1: (1280, 720), 2: (1920, 1080), 3: (3840, 2160), 4: (3840, 2160)}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--frames", type=int, default=300)
+    ap.add_argument("--configs", default="1,2,3,4")
+    args = ap.parse_args()
+    for c in [int(x) for x in args.configs.split(",")]:
+        w, h = SIZES[c]
+        e = Engine(w, h)
+        tris = e.load_procedural(c)
+        for _ in range(10):
+            e.update_scene(0.0); e.draw()
+        e.sync()
+        t0 = time.perf_counter()
+        for _ in range(args.frames):
+            e.update_scene(0.0); e.draw()
+        e.sync()
+        dt = time.perf_counter() - t0
+        st = e.stats()
+        fps = args.frames / dt
+        print(json.dumps({"config": c, "resolution": [w, h], "scene_triangles": int(tris), "visible_objects": e.visible_objects(),
+                          "submitted_triangles": st.triangle_count, "frames_per_s": fps, "mtri_per_s": fps * st.triangle_count / 1e6,
+                          "gpix_per_s": fps * w * h / 1e9, "frames": args.frames}), flush=True)
+        e.close()
+
+
+if __name__ == "__main__":
+    main()

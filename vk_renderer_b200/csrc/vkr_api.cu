@@ -302,6 +302,7 @@ __global__ void __launch_bounds__(CL_TRIS) geometry_cutout_kernel(const DObject*
 template <bool SHADOW>
 __global__ void __launch_bounds__(256) large_raster_kernel(const __grid_constant__ RasterTarget rt, const __grid_constant__ Queues q,
                                                            const __grid_constant__ AlphaCtx ax, int anyCutout) {
+    __shared__ uint32_t s_queue[SHADOW ? 1 : 8][SHADOW ? 1 : RECT_QUEUE];      // cut-out items: compaction queue per warp
     const uint32_t nItems = min(q.counters[1], q.itemCap);
     const uint32_t warpsPerGrid = (gridDim.x * blockDim.x) >> 5;
     const int lane = threadIdx.x & 31;
@@ -320,7 +321,7 @@ __global__ void __launch_bounds__(256) large_raster_kernel(const __grid_constant
                 AlphaTri at;
                 make_alpha_tri(o, o.mvp, o.idx[3 * tri], o.idx[3 * tri + 1], o.idx[3 * tri + 2], ax, rt, at);
                 CutoutSink<VisSink> cs{sink, &at};
-                raster_item(lt, it, cs, lane, 32);
+                raster_item_compact(lt, it, cs, lane, s_queue[SHADOW ? 0 : (threadIdx.x >> 5)]);
             } else raster_item(lt, it, sink, lane, 32);
         }
     }
@@ -328,6 +329,7 @@ __global__ void __launch_bounds__(256) large_raster_kernel(const __grid_constant
 __global__ void __launch_bounds__(256) large_transparent_kernel(const __grid_constant__ RasterTarget rt, const __grid_constant__ Queues q,
                                                                 const __grid_constant__ ShadeConst sc, const __grid_constant__ ShadeBuffers sbIn) {
     __shared__ float s_lut[256];
+    __shared__ uint32_t s_queue[8][RECT_QUEUE];
     s_lut[threadIdx.x] = sbIn.srgbLut[threadIdx.x];
     __syncthreads();
     ShadeBuffers sb = sbIn;
@@ -339,7 +341,7 @@ __global__ void __launch_bounds__(256) large_transparent_kernel(const __grid_con
         const LargeItem it = q.items[i];
         const LargeTri lt = q.tris[it.tri];
         BlendSink sink{&sc, &sb, lt.seq};
-        raster_item(lt, it, sink, lane, 32);
+        raster_item_compact(lt, it, sink, lane, s_queue[threadIdx.x >> 5]);       // shading at raster time: keep the warp converged
     }
 }
 

@@ -127,6 +127,16 @@ VKR_HD float depth_at(float z0, float dzdx, float dzdy, int32_t X0, int32_t Y0, 
 // ---- fragment sinks: the only place the two geometry passes differ ---------------------
 struct VisSink {           // main pass: 64-bit key into the visibility buffer
     uint64_t* vis; int32_t width; uint32_t lo;
+    // Early depth test for fragments that are expensive to produce (alpha-tested): true iff the stored depth is already
+    // nearer than z.  Stored depths only decrease, so such a fragment can never win (LEQUAL: equal depth still can).
+    VKR_HD bool hidden(int32_t px, int32_t py, float z) const {
+        const uint32_t* hi = reinterpret_cast<const uint32_t*>(vis + (size_t)py * width + px) + 1;
+#if defined(__CUDA_ARCH__)
+        return __ldcg(hi) < f2bits(z);
+#else
+        return *hi < f2bits(z);
+#endif
+    }
     VKR_HD void put(int32_t px, int32_t py, float z) const {
         const uint64_t key = ((uint64_t)f2bits(z) << 32) | lo;
         uint64_t* p = vis + (size_t)py * width + px;
@@ -212,12 +222,97 @@ VKR_HD void raster_rect64(const int32_t X[3], const int32_t Y[3], float z0, floa
         int64_t f0 = e.a[0] * Px + e.b[0] * Py + e.c[0];
         int64_t f1 = e.a[1] * Px + e.b[1] * Py + e.c[1];
         int64_t f2 = e.a[2] * Px + e.b[2] * Py + e.c[2];
-        for (int32_t px = pxa; px <= pxb; ++px) {
-            if ((f0 | f1 | f2) >= 0) sink.put(px, py, depth_at(z0, dzdx, dzdy, X[0], Y[0], px, py));
+        // coverage of the strip first (cheap, every lane in step), then one sink call per covered pixel: lanes meet at
+        // their k-th covered pixel, so an expensive sink (alpha test, blending) runs converged even on thin slivers
+        uint32_t mask = 0;
+#pragma unroll
+        for (int32_t k = 0; k < 8; ++k) {
+            if (pxa + k <= pxb && (f0 | f1 | f2) >= 0) mask |= 1u << k;
             f0 += ax0; f1 += ax1; f2 += ax2;
+        }
+        while (mask) {
+#if defined(__CUDA_ARCH__)
+            const int32_t k = __ffs((int)mask) - 1;
+#else
+            const int32_t k = __builtin_ctz(mask);
+#endif
+            mask &= mask - 1;
+            sink.put(pxa + k, py, depth_at(z0, dzdx, dzdy, X[0], Y[0], pxa + k, py));
         }
     }
 }
+
+#if defined(__CUDACC__)
+// The same rectangle for an EXPENSIVE sink (alpha test, shade-and-blend): one warp, covered pixels are first compacted
+// into a per-warp queue in shared memory (`wq`, RECT_QUEUE entries) and the sink then runs on 32 queued pixels at a time,
+// fully converged — thin slivers cover one or two pixels per row, which would otherwise leave a few lanes doing all the
+// sink work while the others wait.
+static const int RECT_QUEUE = 32 + 32 * 8;
+template <class Sink>
+__device__ __forceinline__ void raster_rect64_compact(const int32_t X[3], const int32_t Y[3], float z0, float dzdx, float dzdy,
+                                                      int32_t x0, int32_t y0, int32_t x1, int32_t y1, const Sink& sink, int lane, uint32_t* wq) {
+    EdgeEq e;
+    make_edges(X, Y, e);
+    const int32_t w = x1 - x0 + 1, h = y1 - y0 + 1;
+    const int32_t strips = (w + 7) >> 3;
+    const int32_t n = strips * h;
+    const int64_t ax0 = e.a[0] * 256, ax1 = e.a[1] * 256, ax2 = e.a[2] * 256;
+    uint32_t count = 0;                                   // queued pixels (warp-uniform)
+    for (int32_t base = 0; base < n; base += 32) {
+        const int32_t i = base + lane;
+        uint32_t mask = 0;
+        int32_t py = 0, pxa = 0;
+        if (i < n) {
+            const int32_t row = i / strips, sx = i - row * strips;
+            py = y0 + row; pxa = x0 + sx * 8;
+            const int32_t pxb = imin(pxa + 7, x1);
+            const int64_t Px = (int64_t)pxa * 256 + 128, Py = (int64_t)py * 256 + 128;
+            int64_t f0 = e.a[0] * Px + e.b[0] * Py + e.c[0];
+            int64_t f1 = e.a[1] * Px + e.b[1] * Py + e.c[1];
+            int64_t f2 = e.a[2] * Px + e.b[2] * Py + e.c[2];
+#pragma unroll
+            for (int32_t k = 0; k < 8; ++k) {
+                if (pxa + k <= pxb && (f0 | f1 | f2) >= 0) mask |= 1u << k;
+                f0 += ax0; f1 += ax1; f2 += ax2;
+            }
+        }
+        if (!__any_sync(0xFFFFFFFFu, mask != 0)) continue;
+        const uint32_t c = (uint32_t)__popc(mask);
+        uint32_t incl = c;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= d) incl += t; }
+        const uint32_t total = __shfl_sync(0xFFFFFFFFu, incl, 31);
+        uint32_t off = count + incl - c;
+        while (mask) {
+            const int32_t k = __ffs((int)mask) - 1;
+            mask &= mask - 1;
+            wq[off++] = (uint32_t)(pxa + k) | ((uint32_t)py << 16);
+        }
+        __syncwarp();
+        count += total;
+        uint32_t head = 0;
+        while (count - head >= 32) {
+            const uint32_t q = wq[head + lane];
+            const int32_t px = (int32_t)(q & 0xFFFFu), qy = (int32_t)(q >> 16);
+            sink.put(px, qy, depth_at(z0, dzdx, dzdy, X[0], Y[0], px, qy));
+            head += 32;
+        }
+        const uint32_t rem = count - head;                // < 32: move the tail to the front
+        __syncwarp();
+        const uint32_t v = lane < (int)rem ? wq[head + lane] : 0u;
+        __syncwarp();
+        if (lane < (int)rem) wq[lane] = v;
+        __syncwarp();
+        count = rem;
+    }
+    if (lane < (int)count) {
+        const uint32_t q = wq[lane];
+        const int32_t px = (int32_t)(q & 0xFFFFu), qy = (int32_t)(q >> 16);
+        sink.put(px, qy, depth_at(z0, dzdx, dzdy, X[0], Y[0], px, qy));
+    }
+    __syncwarp();
+}
+#endif
 
 // Conservative tile-vs-triangle test: false if the tile's pixel centres are all outside one edge.
 VKR_HD bool tile_overlaps(const EdgeEq& e, int32_t x0, int32_t y0, int32_t x1, int32_t y1) {
@@ -333,6 +428,15 @@ VKR_HD void raster_item(const LargeTri& lt, const LargeItem& it, const Sink& sin
     const int32_t y0 = imax((int32_t)it.ty * TILE, (int32_t)lt.by0), y1 = imin((int32_t)it.ty * TILE + TILE - 1, (int32_t)lt.by1);
     raster_rect64(lt.X, lt.Y, lt.z0, lt.dzdx, lt.dzdy, x0, y0, x1, y1, sink, lane, nlanes);
 }
+
+#if defined(__CUDACC__)
+template <class Sink>
+__device__ __forceinline__ void raster_item_compact(const LargeTri& lt, const LargeItem& it, const Sink& sink, int lane, uint32_t* wq) {
+    const int32_t x0 = imax((int32_t)it.tx * TILE, (int32_t)lt.bx0), x1 = imin((int32_t)it.tx * TILE + TILE - 1, (int32_t)lt.bx1);
+    const int32_t y0 = imax((int32_t)it.ty * TILE, (int32_t)lt.by0), y1 = imin((int32_t)it.ty * TILE + TILE - 1, (int32_t)lt.by1);
+    raster_rect64_compact(lt.X, lt.Y, lt.z0, lt.dzdx, lt.dzdy, x0, y0, x1, y1, sink, lane, wq);
+}
+#endif
 
 // ---- the two phases of the geometry kernel (one CTA = one cluster of <= 256 triangles) -----
 // Phase 1, one unique vertex: transform, classify, project, snap.  w == 1 flags "outside the clip
@@ -477,10 +581,27 @@ struct AlphaTri {
     float halfW, halfH;
 };
 
+// a / 255.0f, correctly rounded, for a = 0..255: the division the oracle does per texel, from a table (bit-identical)
+struct Unorm8Table {
+    float v[256];
+    constexpr Unorm8Table() : v() { for (int i = 0; i < 256; ++i) v[i] = (float)i / 255.0f; }
+};
+#if defined(__CUDACC__)
+__device__ constexpr Unorm8Table kUnorm8Dev{};
+#endif
+constexpr Unorm8Table kUnorm8Host{};
 VKR_HD float alpha_texel(const DTexture& t, int level, int x, int y, int w) {
-    return xdiv((float)t.data[t.mipOffset[level] + (size_t)y * w + x].w, 255.0f);
+    const uint8_t a = t.data[t.mipOffset[level] + (size_t)y * w + x].w;
+#if defined(__CUDA_ARCH__)
+    return kUnorm8Dev.v[a];
+#else
+    return kUnorm8Host.v[a];
+#endif
 }
-VKR_HD int alpha_wrap(int i, int n) { int r = i % n; return r < 0 ? r + n : r; }
+VKR_HD int alpha_wrap(int i, int n) {
+    if ((n & (n - 1)) == 0) return i & (n - 1);       // power-of-two extent: the AND is the floor-mod
+    int r = i % n; return r < 0 ? r + n : r;
+}
 VKR_HD float alpha_sample_level(const DTexture& t, int level, float u, float v) {
     int w = (int)(t.w >> level), h = (int)(t.h >> level);
     if (w < 1) w = 1;
@@ -566,7 +687,10 @@ template <class Base>
 struct CutoutSink {
     Base base;
     const AlphaTri* a;
-    VKR_HD void put(int32_t px, int32_t py, float z) const { if (alpha_passes(*a, px, py)) base.put(px, py, z); }
+    VKR_HD void put(int32_t px, int32_t py, float z) const {
+        if (base.hidden(px, py, z)) return;              // depth first: the alpha test is ~100x the cost of the probe
+        if (alpha_passes(*a, px, py)) base.put(px, py, z);
+    }
 };
 
 // Phase 2 for a triangle of an alpha-tested draw (always from the original vertices).
