@@ -154,7 +154,8 @@ enum { PASS_MAIN = 0, PASS_SHADOW = 1, PASS_TRANSPARENT = 2 };
 
 template <int PASS, class MakeSink>
 __device__ __forceinline__ void geometry_warp(const DChunk* __restrict__ chunk, const float* __restrict__ mvps, uint32_t mvpStride,
-                                              const RasterTarget& rt, const Queues& q, uint4* s_vtx, float* mvp, const MakeSink& makeSink) {
+                                              const RasterTarget& rt, const Queues& q, uint4* s_vtx, float* mvp, LargeTri* s_pend,
+                                              const MakeSink& makeSink) {
     const int lane = threadIdx.x & 31;
     // the 80-byte cluster record is everything this warp needs: one level of indirection (uniform loads)
     const uint4* chp = reinterpret_cast<const uint4*>(chunk);
@@ -231,17 +232,48 @@ __device__ __forceinline__ void geometry_warp(const DChunk* __restrict__ chunk, 
     }
     __syncwarp();
 
-    // ---- phase 2: triangles
-    for (uint32_t t = lane; t < nTris; t += 32) {
-        const uint32_t packed = __ldg(clTris + t);
-        const uint32_t l0 = packed & 127u, l1 = (packed >> 7) & 127u, l2 = (packed >> 14) & 127u;
-        const uint4 a = s_vtx[l0], b = s_vtx[l1], c = s_vtx[l2];
-        const CachedVtx va{(int32_t)a.x, (int32_t)a.y, a.z, a.w}, vb{(int32_t)b.x, (int32_t)b.y, b.z, b.w}, vc{(int32_t)c.x, (int32_t)c.y, c.z, c.w};
-        uint32_t g0 = 0, g1 = 0, g2 = 0;
-        if (a.w | b.w | c.w) { g0 = __ldg(clVerts + l0); g1 = __ldg(clVerts + l1); g2 = __ldg(clVerts + l2); }
-        // submission-order sequence number, whatever the processing order (the shadow pass has no use for it)
-        const uint32_t seq = PASS == PASS_SHADOW ? 0u : seqBase + __ldg(clOrig + t);
-        cluster_triangle(va, vb, vc, mvp, pos, g0, g1, g2, seq, rt, q, makeSink(seq));
+    // ---- phase 2: triangles.  Small ones are rasterised by the lane that set them up; the others are parked in the warp's
+    // shared-memory slots and then taken by the whole warp one at a time (vkr_raster.cuh, "warp-cooperative handling")
+    for (uint32_t base = 0; base < nTris; base += 32) {
+        const uint32_t t = base + lane;
+        int kind = 0;
+        if (t < nTris) {
+            const uint32_t packed = __ldg(clTris + t);
+            const uint32_t l0 = packed & 127u, l1 = (packed >> 7) & 127u, l2 = (packed >> 14) & 127u;
+            const uint4 a = s_vtx[l0], b = s_vtx[l1], c = s_vtx[l2];
+            const CachedVtx va{(int32_t)a.x, (int32_t)a.y, a.z, a.w}, vb{(int32_t)b.x, (int32_t)b.y, b.z, b.w}, vc{(int32_t)c.x, (int32_t)c.y, c.z, c.w};
+            uint32_t g0 = 0, g1 = 0, g2 = 0;
+            if (a.w | b.w | c.w) { g0 = __ldg(clVerts + l0); g1 = __ldg(clVerts + l1); g2 = __ldg(clVerts + l2); }
+            // submission-order sequence number, whatever the processing order (the shadow pass has no use for it)
+            const uint32_t seq = PASS == PASS_SHADOW ? 0u : seqBase + __ldg(clOrig + t);
+            kind = cluster_triangle_deferred(va, vb, vc, mvp, pos, g0, g1, g2, seq, rt, q, makeSink(seq), s_pend[lane]);
+        }
+        const uint32_t medium = __ballot_sync(0xFFFFFFFFu, kind == 1);
+        uint32_t large = __ballot_sync(0xFFFFFFFFu, kind == 2);
+        if ((medium | large) == 0u) continue;
+        if (medium) {
+            // medium triangles (extent < 64 px): one queue item each, no tile enumeration; the slots of the whole warp are
+            // claimed with one atomic per counter.  large_raster_kernel rasterises them with 32-bit edge functions.
+            uint32_t firstTri = 0, firstItem = 0;
+            if (lane == 0) { firstTri = atomicAdd(&q.counters[0], (uint32_t)__popc(medium)); firstItem = atomicAdd(&q.counters[1], (uint32_t)__popc(medium)); }
+            firstTri = __shfl_sync(0xFFFFFFFFu, firstTri, 0); firstItem = __shfl_sync(0xFFFFFFFFu, firstItem, 0);
+            if (kind == 1) {
+                const uint32_t k = (uint32_t)__popc(medium & ((1u << lane) - 1u));
+                if (firstTri + k >= q.triCap || firstItem + k >= q.itemCap) q.counters[2] = 1;
+                else {
+                    q.tris[firstTri + k] = s_pend[lane];
+                    LargeItem it; it.tri = firstTri + k; it.tx = ITEM_WHOLE; it.ty = ITEM_WHOLE;
+                    q.items[firstItem + k] = it;
+                }
+            }
+        }
+        __syncwarp();
+        while (large) {
+            const int src = __ffs((int)large) - 1;
+            large &= large - 1;
+            enqueue_large_coop(s_pend[src], q, lane);
+        }
+        __syncwarp();
     }
 }
 
@@ -255,11 +287,13 @@ __global__ void __launch_bounds__(GEOM_WARPS * 32, VKR_GEOM_MIN_CTAS) geometry_k
                                                                      const __grid_constant__ RasterTarget rt, const __grid_constant__ Queues q) {
     __shared__ uint4 s_vtxAll[GEOM_WARPS][CL_VERTS];
     __shared__ float s_mvpAll[GEOM_WARPS][16];
+    __shared__ LargeTri s_pendAll[GEOM_WARPS][32];
     const uint32_t slot = blockIdx.x * GEOM_WARPS + (threadIdx.x >> 5);
     if (slot >= nClusters) return;
     const DChunk* chunk = chunks + __ldg(perm + slot);
-    if (SHADOW) geometry_warp<PASS_SHADOW>(chunk, mvps, mvpStride, rt, q, s_vtxAll[threadIdx.x >> 5], s_mvpAll[threadIdx.x >> 5], MakeDepthSink{rt.depthBits, rt.width});
-    else geometry_warp<PASS_MAIN>(chunk, mvps, mvpStride, rt, q, s_vtxAll[threadIdx.x >> 5], s_mvpAll[threadIdx.x >> 5], MakeVisSink{rt.vis, rt.width});
+    const int wi = threadIdx.x >> 5;
+    if (SHADOW) geometry_warp<PASS_SHADOW>(chunk, mvps, mvpStride, rt, q, s_vtxAll[wi], s_mvpAll[wi], s_pendAll[wi], MakeDepthSink{rt.depthBits, rt.width});
+    else geometry_warp<PASS_MAIN>(chunk, mvps, mvpStride, rt, q, s_vtxAll[wi], s_mvpAll[wi], s_pendAll[wi], MakeVisSink{rt.vis, rt.width});
 }
 
 // ---- "Transparent" draws (the tail of the draw list), after every opaque fragment is in the visibility buffer
@@ -269,6 +303,7 @@ __global__ void __launch_bounds__(GEOM_WARPS * 32) geometry_transparent_kernel(c
                                                                               const __grid_constant__ ShadeConst sc, const __grid_constant__ ShadeBuffers sbIn) {
     __shared__ uint4 s_vtxAll[GEOM_WARPS][CL_VERTS];
     __shared__ float s_mvpAll[GEOM_WARPS][16];
+    __shared__ LargeTri s_pendAll[GEOM_WARPS][32];
     __shared__ float s_lut[256];
     for (uint32_t i = threadIdx.x; i < 256u; i += GEOM_WARPS * 32) s_lut[i] = sbIn.srgbLut[i];
     __syncthreads();
@@ -278,7 +313,7 @@ __global__ void __launch_bounds__(GEOM_WARPS * 32) geometry_transparent_kernel(c
     const uint32_t slot = blockIdx.x * GEOM_WARPS + (threadIdx.x >> 5);
     if (slot >= nClusters) return;
     geometry_warp<PASS_TRANSPARENT>(chunks + firstCluster + slot, mvps, mvpStride, rt, q, s_vtxAll[threadIdx.x >> 5], s_mvpAll[threadIdx.x >> 5],
-                                    MakeBlendSink{&sc, &s_sb});
+                                    s_pendAll[threadIdx.x >> 5], MakeBlendSink{&sc, &s_sb});
 }
 
 // ---- main pass, alpha-tested draws only (launched when the frame has any): one thread per triangle,
@@ -309,9 +344,11 @@ __global__ void __launch_bounds__(256) large_raster_kernel(const __grid_constant
     for (uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < nItems; i += warpsPerGrid) {
         const LargeItem it = q.items[i];
         const LargeTri lt = q.tris[it.tri];
+        const bool whole = it.tx == ITEM_WHOLE;          // medium triangle: its whole bounding box, 32-bit edge functions
         if (SHADOW) {
             DepthSink sink{rt.depthBits, rt.width};
-            raster_item(lt, it, sink, lane, 32);
+            if (whole) raster_medium_coop(lt, sink, lane);
+            else raster_item(lt, it, sink, lane, 32);
         } else {
             VisSink sink{rt.vis, rt.width, 0xFFFFFFFEu - lt.seq};
             if (anyCutout && (ax.objects[ax.chunkObj[lt.seq >> 8].x].flags & 2u)) {
@@ -322,7 +359,8 @@ __global__ void __launch_bounds__(256) large_raster_kernel(const __grid_constant
                 make_alpha_tri(o, o.mvp, o.idx[3 * tri], o.idx[3 * tri + 1], o.idx[3 * tri + 2], ax, rt, at);
                 CutoutSink<VisSink> cs{sink, &at};
                 raster_item_compact(lt, it, cs, lane, s_queue[SHADOW ? 0 : (threadIdx.x >> 5)]);
-            } else raster_item(lt, it, sink, lane, 32);
+            } else if (whole) raster_medium_coop(lt, sink, lane);
+            else raster_item(lt, it, sink, lane, 32);
         }
     }
 }

@@ -424,16 +424,18 @@ VKR_HDN void clip_and_emit(float4 c0, float4 c1, float4 c2, uint32_t seq, const 
 // One (large triangle, tile) work item; lanes of a warp split the tile's pixels.
 template <class Sink>
 VKR_HD void raster_item(const LargeTri& lt, const LargeItem& it, const Sink& sink, int lane, int nlanes) {
-    const int32_t x0 = imax((int32_t)it.tx * TILE, (int32_t)lt.bx0), x1 = imin((int32_t)it.tx * TILE + TILE - 1, (int32_t)lt.bx1);
-    const int32_t y0 = imax((int32_t)it.ty * TILE, (int32_t)lt.by0), y1 = imin((int32_t)it.ty * TILE + TILE - 1, (int32_t)lt.by1);
+    const bool whole = it.tx == ITEM_WHOLE;
+    const int32_t x0 = whole ? (int32_t)lt.bx0 : imax((int32_t)it.tx * TILE, (int32_t)lt.bx0), x1 = whole ? (int32_t)lt.bx1 : imin((int32_t)it.tx * TILE + TILE - 1, (int32_t)lt.bx1);
+    const int32_t y0 = whole ? (int32_t)lt.by0 : imax((int32_t)it.ty * TILE, (int32_t)lt.by0), y1 = whole ? (int32_t)lt.by1 : imin((int32_t)it.ty * TILE + TILE - 1, (int32_t)lt.by1);
     raster_rect64(lt.X, lt.Y, lt.z0, lt.dzdx, lt.dzdy, x0, y0, x1, y1, sink, lane, nlanes);
 }
 
 #if defined(__CUDACC__)
 template <class Sink>
 __device__ __forceinline__ void raster_item_compact(const LargeTri& lt, const LargeItem& it, const Sink& sink, int lane, uint32_t* wq) {
-    const int32_t x0 = imax((int32_t)it.tx * TILE, (int32_t)lt.bx0), x1 = imin((int32_t)it.tx * TILE + TILE - 1, (int32_t)lt.bx1);
-    const int32_t y0 = imax((int32_t)it.ty * TILE, (int32_t)lt.by0), y1 = imin((int32_t)it.ty * TILE + TILE - 1, (int32_t)lt.by1);
+    const bool whole = it.tx == ITEM_WHOLE;
+    const int32_t x0 = whole ? (int32_t)lt.bx0 : imax((int32_t)it.tx * TILE, (int32_t)lt.bx0), x1 = whole ? (int32_t)lt.bx1 : imin((int32_t)it.tx * TILE + TILE - 1, (int32_t)lt.bx1);
+    const int32_t y0 = whole ? (int32_t)lt.by0 : imax((int32_t)it.ty * TILE, (int32_t)lt.by0), y1 = whole ? (int32_t)lt.by1 : imin((int32_t)it.ty * TILE + TILE - 1, (int32_t)lt.by1);
     raster_rect64_compact(lt.X, lt.Y, lt.z0, lt.dzdx, lt.dzdy, x0, y0, x1, y1, sink, lane, wq);
 }
 #endif
@@ -471,6 +473,99 @@ VKR_HD void cluster_triangle(const CachedVtx& a, const CachedVtx& b, const Cache
     const SnapVtx v0{a.X, a.Y, bits2f(a.zbits)}, v1{b.X, b.Y, bits2f(b.zbits)}, v2{c.X, c.Y, bits2f(c.zbits)};
     if (setup_snapped(v0, v1, v2, rt, t)) emit_setup(t, seq, q, sink);
 }
+
+#if defined(__CUDACC__)
+// ---- warp-cooperative handling of triangles that are too big for one lane ------------------------------------------
+// cluster_triangle_deferred does what cluster_triangle does for small triangles (in-lane raster) and clipped ones, and
+// returns 1 (medium: extent < 64 px, 32-bit edge functions suffice) or 2 (large) with the set-up triangle in `out` for
+// the others; the warp then takes those one at a time: medium ones are rasterised by all 32 lanes at once, large ones
+// have their 64x64 tiles enumerated by all 32 lanes and queued for large_raster_kernel.
+template <class Sink>
+__device__ __forceinline__ int cluster_triangle_deferred(const CachedVtx& a, const CachedVtx& b, const CachedVtx& c, const float* __restrict__ mvp,
+                                                         const float4* __restrict__ pos, uint32_t g0, uint32_t g1, uint32_t g2, uint32_t seq,
+                                                         const RasterTarget& rt, const Queues& q, const Sink& sink, LargeTri& out) {
+    if ((a.flag | b.flag | c.flag) != 0u) {
+        const float4 p0 = __ldg(pos + g0), p1 = __ldg(pos + g1), p2 = __ldg(pos + g2);
+        clip_and_emit(transform_point(mvp, p0.x, p0.y, p0.z), transform_point(mvp, p1.x, p1.y, p1.z),
+                      transform_point(mvp, p2.x, p2.y, p2.z), seq, rt, q, sink);
+        return 0;
+    }
+    SetupTri t;
+    const SnapVtx v0{a.X, a.Y, bits2f(a.zbits)}, v1{b.X, b.Y, bits2f(b.zbits)}, v2{c.X, c.Y, bits2f(c.zbits)};
+    if (!setup_snapped(v0, v1, v2, rt, t)) return 0;
+    const int32_t w = t.bx1 - t.bx0 + 1, h = t.by1 - t.by0 + 1;
+    if (w <= SMALL_MAX && h <= SMALL_MAX && t.ext < 16384) { raster_small(t, sink); return 0; }
+#pragma unroll
+    for (int i = 0; i < 3; ++i) { out.X[i] = t.X[i]; out.Y[i] = t.Y[i]; }
+    out.z0 = t.z0; out.dzdx = t.dzdx; out.dzdy = t.dzdy;
+    out.bx0 = (int16_t)t.bx0; out.by0 = (int16_t)t.by0; out.bx1 = (int16_t)t.bx1; out.by1 = (int16_t)t.by1;
+    out.seq = seq;
+    return t.ext < 16384 ? 1 : 2;
+}
+
+// All 32 lanes rasterise one medium triangle (warp-uniform `lt`): 8-pixel strips of its bounding box dealt to the lanes,
+// 32-bit edge functions as in raster_small.
+template <class Sink>
+__device__ __forceinline__ void raster_medium_coop(const LargeTri& lt, const Sink& sink, int lane) {
+    int32_t e[3], ax[3], by[3];
+    const int32_t Px = (int32_t)lt.bx0 * 256 + 128, Py = (int32_t)lt.by0 * 256 + 128;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        const int j = (i + 1) % 3, k = (i + 2) % 3;
+        const int32_t dx = lt.X[k] - lt.X[j], dy = lt.Y[k] - lt.Y[j];
+        const bool topleft = (dy < 0) || (dy == 0 && dx > 0);
+        e[i] = dx * (Py - lt.Y[j]) - dy * (Px - lt.X[j]) - (topleft ? 0 : 1);
+        ax[i] = -dy * 256;
+        by[i] = dx * 256;
+    }
+    const int32_t w = lt.bx1 - lt.bx0 + 1, h = lt.by1 - lt.by0 + 1;
+    const int32_t strips = (w + 7) >> 3, n = strips * h;
+    for (int32_t i = lane; i < n; i += 32) {
+        const int32_t row = i / strips, sx = i - row * strips;
+        const int32_t py = lt.by0 + row, pxa = lt.bx0 + sx * 8;
+        int32_t f0 = e[0] + row * by[0] + sx * 8 * ax[0], f1 = e[1] + row * by[1] + sx * 8 * ax[1], f2 = e[2] + row * by[2] + sx * 8 * ax[2];
+#pragma unroll
+        for (int32_t k = 0; k < 8; ++k) {
+            if (pxa + k <= lt.bx1 && (f0 | f1 | f2) >= 0) sink.put(pxa + k, py, depth_at(lt.z0, lt.dzdx, lt.dzdy, lt.X[0], lt.Y[0], pxa + k, py));
+            f0 += ax[0]; f1 += ax[1]; f2 += ax[2];
+        }
+    }
+}
+
+// All 32 lanes enumerate the tiles of one large triangle (warp-uniform `lt`) and queue the overlapping ones.
+__device__ __forceinline__ void enqueue_large_coop(const LargeTri& lt, const Queues& q, int lane) {
+    uint32_t slot = 0;
+    if (lane == 0) slot = atomicAdd(&q.counters[0], 1u);
+    slot = __shfl_sync(0xFFFFFFFFu, slot, 0);
+    if (slot >= q.triCap) { if (lane == 0) q.counters[2] = 1; return; }
+    if (lane == 0) q.tris[slot] = lt;
+    EdgeEq e;
+    make_edges(lt.X, lt.Y, e);
+    const int32_t tx0 = lt.bx0 / TILE, tx1 = lt.bx1 / TILE, ty0 = lt.by0 / TILE, ty1 = lt.by1 / TILE;
+    const int32_t ntx = tx1 - tx0 + 1, n = ntx * (ty1 - ty0 + 1);
+    for (int32_t base = 0; base < n; base += 32) {
+        const int32_t i = base + lane;
+        bool hit = false;
+        int32_t tx = 0, ty = 0;
+        if (i < n) {
+            ty = ty0 + i / ntx; tx = tx0 + i % ntx;
+            const int32_t x0 = imax(tx * TILE, (int32_t)lt.bx0), x1 = imin(tx * TILE + TILE - 1, (int32_t)lt.bx1);
+            const int32_t y0 = imax(ty * TILE, (int32_t)lt.by0), y1 = imin(ty * TILE + TILE - 1, (int32_t)lt.by1);
+            hit = tile_overlaps(e, x0, y0, x1, y1);
+        }
+        const uint32_t m = __ballot_sync(0xFFFFFFFFu, hit);
+        if (!m) continue;
+        uint32_t first = 0;
+        if (lane == 0) first = atomicAdd(&q.counters[1], (uint32_t)__popc(m));
+        first = __shfl_sync(0xFFFFFFFFu, first, 0);
+        if (hit) {
+            const uint32_t is = first + (uint32_t)__popc(m & ((1u << lane) - 1u));
+            if (is >= q.itemCap) q.counters[2] = 1;
+            else { LargeItem it; it.tri = slot; it.tx = (uint16_t)tx; it.ty = (uint16_t)ty; q.items[is] = it; }
+        }
+    }
+}
+#endif
 
 // ---- cluster culling --------------------------------------------------------------------------
 // Before a geometry CTA transforms anything it projects the 8 corners of its cluster's object-space
