@@ -341,7 +341,14 @@ __global__ void __launch_bounds__(256) large_raster_kernel(const __grid_constant
     const uint32_t nItems = min(q.counters[1], q.itemCap);
     const uint32_t warpsPerGrid = (gridDim.x * blockDim.x) >> 5;
     const int lane = threadIdx.x & 31;
-    for (uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < nItems; i += warpsPerGrid) {
+    // items differ in cost by orders of magnitude (an alpha-tested tile vs. an opaque sliver): warps take the next item
+    // from a shared cursor instead of a fixed stride
+    (void)warpsPerGrid;
+    for (;;) {
+        uint32_t i = 0;
+        if (lane == 0) i = atomicAdd(&q.counters[4], 1u);
+        i = __shfl_sync(0xFFFFFFFFu, i, 0);
+        if (i >= nItems) break;
         const LargeItem it = q.items[i];
         const LargeTri lt = q.tris[it.tri];
         const bool whole = it.tx == ITEM_WHOLE;          // medium triangle: its whole bounding box, 32-bit edge functions
@@ -375,7 +382,12 @@ __global__ void __launch_bounds__(256) large_transparent_kernel(const __grid_con
     const uint32_t nItems = min(q.counters[1], q.itemCap);
     const uint32_t warpsPerGrid = (gridDim.x * blockDim.x) >> 5;
     const int lane = threadIdx.x & 31;
-    for (uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < nItems; i += warpsPerGrid) {
+    (void)warpsPerGrid;
+    for (;;) {
+        uint32_t i = 0;
+        if (lane == 0) i = atomicAdd(&q.counters[4], 1u);
+        i = __shfl_sync(0xFFFFFFFFu, i, 0);
+        if (i >= nItems) break;
         const LargeItem it = q.items[i];
         const LargeTri lt = q.tris[it.tri];
         BlendSink sink{&sc, &sb, lt.seq};
@@ -604,11 +616,11 @@ int vkr_create(const VkrConfig* cfg, VkrDevice** out) {
         dev->q.triCap = 1u << 20; dev->q.itemCap = 1u << 22;
         ALLOC(dev->q.tris, sizeof(LargeTri) * dev->q.triCap);
         ALLOC(dev->q.items, sizeof(LargeItem) * dev->q.itemCap);
-        ALLOC(dev->q.counters, 16);
+        ALLOC(dev->q.counters, 32);          // [0..3] see Queues; [4] work cursor of the large-triangle kernels
         dev->qShadow.triCap = 1u << 18; dev->qShadow.itemCap = 1u << 20;
         ALLOC(dev->qShadow.tris, sizeof(LargeTri) * dev->qShadow.triCap);
         ALLOC(dev->qShadow.items, sizeof(LargeItem) * dev->qShadow.itemCap);
-        ALLOC(dev->qShadow.counters, 16);
+        ALLOC(dev->qShadow.counters, 32);
         CK(cudaMallocHost(&dev->countersHost, 48));
         std::memset(dev->countersHost, 0, 48);
         for (auto& s : dev->slots) {
@@ -911,7 +923,7 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
             rt.depthBits = dev->shadowBits + (size_t)layer * dev->S * dev->S;
             const size_t sn = (size_t)dev->S * dev->S;
             fill_u32_kernel<<<grid_for(sn / 4, 256, 2048), 256, 0, ss>>>(rt.depthBits, sn, DEPTH_ONE_BITS);
-            CK(cudaMemsetAsync(dev->qShadow.counters, 0, 16, ss));
+            CK(cudaMemsetAsync(dev->qShadow.counters, 0, 32, ss));
             dev->launches += 1;
             const unsigned shadowSlots = plan.passSlots[1 + layer];
             if (shadowSlots) {
@@ -947,7 +959,7 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
         rt.vis = dev->vis;
         const size_t px = (size_t)dev->W * dev->H;
         fill_u64_kernel<<<grid_for(px / 2, 256, 4096), 256, 0, st>>>(dev->vis, px, VIS_CLEAR);
-        CK(cudaMemsetAsync(dev->q.counters, 0, 16, st));
+        CK(cudaMemsetAsync(dev->q.counters, 0, 32, st));
         dev->launches += 1;
         if (timing) CK(cudaEventRecord(dev->tev[3], st));
         // only the opaque prefix writes depth; transparent draws are blended in a later pass
@@ -986,7 +998,7 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
         if (!dev->accum) ALLOC(dev->accum, px * 16);
         sb.accum = dev->accum;
         CK(cudaMemsetAsync(dev->accum, 0, px * 16, st));
-        CK(cudaMemsetAsync(dev->q.counters, 0, 16, st));
+        CK(cudaMemsetAsync(dev->q.counters, 0, 32, st));
         RasterTarget rt = plan.mainTarget;
         rt.vis = dev->vis;
         geometry_transparent_kernel<<<(transChunks + GEOM_WARPS - 1) / GEOM_WARPS, GEOM_WARPS * 32, 0, st>>>(

@@ -31,6 +31,7 @@ static const uint32_t DEPTH_ONE_BITS = 0x3F800000u;
 
 static const int TILE = 64;                // large-triangle tile edge in pixels
 static const int SMALL_MAX = 16;           // in-thread raster when bbox is <= SMALL_MAX x SMALL_MAX
+static const int CUTOUT_SMALL_MAX = 4;     // ... for alpha-tested triangles (each fragment costs a texture evaluation)
 static const int CL_TRIS = 128;            // a cluster (one warp's unit of work) holds at most this many triangles ...
 static const int CL_VERTS = 128;           // ... and this many distinct vertices (7-bit local ids, 2 KB of shared memory)
 static const int SEQ_SLOT = 256;           // primitive sequence numbers are handed out to draws in slots of 256

@@ -345,6 +345,13 @@ VKR_HDN void enqueue_large(const SetupTri& t, uint32_t seq, const Queues& q) {
     lt.bx0 = (int16_t)t.bx0; lt.by0 = (int16_t)t.by0; lt.bx1 = (int16_t)t.bx1; lt.by1 = (int16_t)t.by1;
     lt.seq = seq;
     q.tris[slot] = lt;
+    if (t.ext < 16384) {          // medium: one item for the whole bounding box (at most 64 x 64 pixels), 32-bit edge functions
+        const uint32_t is = queue_alloc(&q.counters[1], 1);
+        if (is >= q.itemCap) { q.counters[2] = 1; return; }
+        LargeItem it; it.tri = slot; it.tx = ITEM_WHOLE; it.ty = ITEM_WHOLE;
+        q.items[is] = it;
+        return;
+    }
     EdgeEq e;
     make_edges(t.X, t.Y, e);
     const int32_t tx0 = t.bx0 / TILE, tx1 = t.bx1 / TILE, ty0 = t.by0 / TILE, ty1 = t.by1 / TILE;
@@ -360,10 +367,12 @@ VKR_HDN void enqueue_large(const SetupTri& t, uint32_t seq, const Queues& q) {
         }
 }
 
+// smallMax: largest bounding box (pixels per side) the calling lane rasterises itself; expensive sinks pass a small one so
+// that their fragments are produced by the large-triangle kernel, a warp per triangle with converged sink calls
 template <class Sink>
-VKR_HD void emit_setup(const SetupTri& t, uint32_t seq, const Queues& q, const Sink& sink) {
+VKR_HD void emit_setup(const SetupTri& t, uint32_t seq, const Queues& q, const Sink& sink, int32_t smallMax = SMALL_MAX) {
     const int32_t w = t.bx1 - t.bx0 + 1, h = t.by1 - t.by0 + 1;
-    if (w <= SMALL_MAX && h <= SMALL_MAX && t.ext < 16384) raster_small(t, sink);
+    if (w <= smallMax && h <= smallMax && t.ext < 16384) raster_small(t, sink);
     else enqueue_large(t, seq, q);
 }
 
@@ -799,7 +808,7 @@ VKR_HDN void cutout_triangle(const DObject& o, const float* __restrict__ mvp, ui
     const float4 c0 = transform_point(mvp, p0.x, p0.y, p0.z), c1 = transform_point(mvp, p1.x, p1.y, p1.z), c2 = transform_point(mvp, p2.x, p2.y, p2.z);
     if (inside_clip_volume(c0) && inside_clip_volume(c1) && inside_clip_volume(c2)) {
         SetupTri t;
-        if (setup_snapped(project_vertex(c0, rt), project_vertex(c1, rt), project_vertex(c2, rt), rt, t)) emit_setup(t, seq, q, sink);
+        if (setup_snapped(project_vertex(c0, rt), project_vertex(c1, rt), project_vertex(c2, rt), rt, t)) emit_setup(t, seq, q, sink, CUTOUT_SMALL_MAX);
     } else clip_and_emit(c0, c1, c2, seq, rt, q, sink);
 }
 
