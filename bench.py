@@ -210,7 +210,9 @@ def run_b200(args):
     torch.cuda.set_stream(torch.cuda.Stream())
     stream = torch.cuda.current_stream().cuda_stream
     assert stream != 0
-    r = capi.Renderer(lib, "vkr", W, H, shadow_extent=S, device=local, stream=stream, flags=capi.CONFIG_TIMINGS)
+    # timed region: only the two events around the dominant kernel (the full per-pass set costs ~5 % of the frame rate);
+    # the per-pass breakdown is taken from a few extra frames after the timed region
+    r = capi.Renderer(lib, "vkr", W, H, shadow_extent=S, device=local, stream=stream, flags=capi.CONFIG_TIME_GEOM_KERNEL)
     sd, objs, fp, info = build_scene(r)
 
     # ---- sort-first (native, include/vkr.h vkr_shard_init): this rank renders its rows of the frame and of the shadow
@@ -253,7 +255,12 @@ def run_b200(args):
     barrier()
     r.sync()
     ms = e0.elapsed_time(e1)
-    tm = r.timings()   # last frame's per-pass device times
+    gk_timed_region_ms = r.timings()["geom_kernel"]      # mean over the frames of the timed region (event pair per frame)
+    r.set_flags(capi.CONFIG_TIMINGS)
+    for _ in range(3):
+        step()
+    r.sync()
+    tm = r.timings()   # per-pass device times of a frame issued back to back with its neighbours
     if world > 1:
         t = torch.tensor([ms], device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -270,6 +277,7 @@ def run_b200(args):
         gk.append(r.timings())
     avg = {k: float(np.mean([g[k] for g in gk])) for k in gk[0]}
     cull = r.cull_stats()
+    r.set_flags(capi.CONFIG_TIME_GEOM_KERNEL)
 
     # ---- e2e: host draw list in, RGBA8 frame out to pinned host memory, every step (FRAME_OVERLAP=2 pipelining)
     pinned = [torch.empty((H, W, 4), dtype=torch.uint8).pin_memory() for _ in range(2)]
@@ -313,7 +321,7 @@ def run_b200(args):
         fps = args.steps / (ms / 1000.0)
         peak, peak_src = measured_peak()
         frame_bytes, gk_bytes = algorithmic_bytes(info)
-        gk_ms = avg["geom_kernel"]
+        gk_ms = gk_timed_region_ms
         traffic, traffic_src = measured_traffic("geometry_kernel<0>")
         achieved = gk_bytes / (gk_ms / 1000.0) / 1e9 if gk_ms > 0 else 0.0
         line = {

@@ -142,7 +142,10 @@ typedef struct VkrConfig {
     uint32_t flags;            /* VKR_CONFIG_* */
 } VkrConfig;
 
-#define VKR_CONFIG_TIMINGS 1u  /* record CUDA events around every pass */
+#define VKR_CONFIG_TIMINGS 1u  /* record CUDA events around every pass (13 events per frame: costs a few percent) */
+#define VKR_CONFIG_TIME_GEOM_KERNEL 2u /* only the two events around the main pass's geometry kernel, kept for the last 128
+                                          frames: vkr_get_timings' VKR_T_GEOM_KERNEL is then the MEAN over the frames drawn
+                                          since the previous vkr_sync (what bench.py reports the roofline from) */
 
 /* struct EngineStats — src/vk_types.h:78-83. */
 typedef struct VkrEngineStats {
@@ -231,6 +234,7 @@ int vkr_sync(VkrDevice* dev);
 /* stats.triangle_count / drawcall_count — src/vk_engine_run.cpp:70-71,309-310. */
 int vkr_stats(VkrDevice* dev, VkrEngineStats* out);
 int vkr_get_timings(VkrDevice* dev, float* msOut, int count);      /* last synced frame */
+int vkr_set_flags(VkrDevice* dev, uint32_t flags);                 /* VKR_CONFIG_* at run time (takes effect at the next vkr_draw) */
 
 /* Raw device pointer of a target of the last drawn frame (for NCCL gathers). */
 int vkr_device_ptr(VkrDevice* dev, VkrTarget what, void** ptr, size_t* bytes);

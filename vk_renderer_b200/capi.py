@@ -22,6 +22,7 @@ FRAG_PBR, FRAG_LAMBERT = 0, 1
 TARGET_RGBA8, TARGET_HDR16F, TARGET_DEPTH, TARGET_SHADOW, TARGET_PRIMID, TARGET_RGBA8_GATHERED = range(6)
 COMM_ID_BYTES = 128
 CONFIG_TIMINGS = 1
+CONFIG_TIME_GEOM_KERNEL = 2
 T_NAMES = ["upload", "shadow", "geometry", "shade", "transparent", "post", "total", "geom_kernel", "large_kernel", "clear",
            "shadow_exchange", "frame_gather"]
 
@@ -114,7 +115,7 @@ class EngineStats(C.Structure):
 VKR_SYMBOLS = [
     "create", "destroy", "upload_mesh", "create_image", "update_bindless_texture", "set_cubemap",
     "build_material", "draw", "readback", "readback_async", "sync", "stats", "get_timings",
-    "device_ptr", "launch_count", "upload_bytes", "cull_stats", "set_shadow_exchange", "comm_unique_id", "shard_init", "last_error", "version",
+    "set_flags", "device_ptr", "launch_count", "upload_bytes", "cull_stats", "set_shadow_exchange", "comm_unique_id", "shard_init", "last_error", "version",
 ]
 
 
@@ -206,6 +207,7 @@ class Renderer:
                 "get_timings": ([p, C.POINTER(C.c_float), C.c_int], C.c_int),
                 "device_ptr": ([p, C.c_int, C.POINTER(p), C.POINTER(C.c_size_t)], C.c_int),
                 "launch_count": ([p], C.c_int),
+                "set_flags": ([p, C.c_uint32], C.c_int),
                 "upload_bytes": ([p], C.c_size_t),
                 "cull_stats": ([p, C.POINTER(C.c_uint32)], C.c_int),
                 "set_shadow_exchange": ([p, SHADOW_EXCHANGE_FN, p], C.c_int),
@@ -307,6 +309,9 @@ class Renderer:
         arr = (C.c_float * len(T_NAMES))()
         self._check(self._f("get_timings")(self.dev, arr, len(T_NAMES)))
         return dict(zip(T_NAMES, list(arr)))
+
+    def set_flags(self, flags: int):
+        self._check(self._f("set_flags")(self.dev, flags))
 
     def device_ptr(self, what: int):
         p, n = C.c_void_p(), C.c_size_t()

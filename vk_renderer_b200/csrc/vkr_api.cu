@@ -492,6 +492,9 @@ struct VkrDevice {
     cudaEvent_t tev[13] = {nullptr};  // ... 9 transparent done; 10 shadow raster done (before the exchange); 11, 12 frame gather (gather stream)   // 0 start, 1 uploaded, 3 cleared, 4 geometry kernel, 5 large kernel, 6 shaded; 7,8 shadow pass (shadow stream)
     bool tevValid = false, shadowTimed = false;
     float timings[VKR_T_COUNT] = {0};
+    static const int KRING = 128;          // VKR_CONFIG_TIME_GEOM_KERNEL: event pairs of the last KRING frames
+    cudaEvent_t kev[KRING][2] = {};
+    uint64_t kevRecorded = 0, kevRead = 0;
 
     VkrShadowExchangeFn shadowExchange = nullptr; void* shadowExchangeUser = nullptr;
     // native sort-first sharding (vkr_shard_init)
@@ -677,6 +680,7 @@ void vkr_destroy(VkrDevice* dev) {
     if (dev->commFrame) ncclCommDestroy(dev->commFrame);
     if (dev->gatherStream) cudaStreamDestroy(dev->gatherStream);
     for (auto& e : dev->gatheredEv) if (e) cudaEventDestroy(e);
+    for (auto& pr : dev->kev) { if (pr[0]) cudaEventDestroy(pr[0]); if (pr[1]) cudaEventDestroy(pr[1]); }
     if (dev->copyStream) cudaStreamDestroy(dev->copyStream);
     if (dev->shadowStream) cudaStreamDestroy(dev->shadowStream);
     if (dev->upStream) cudaStreamDestroy(dev->upStream);
@@ -838,6 +842,7 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
     cudaStream_t st = dev->stream;
     dev->launches = 0;
     const bool timing = dev->flags & VKR_CONFIG_TIMINGS;
+    const bool timeKernel = !timing && (dev->flags & VKR_CONFIG_TIME_GEOM_KERNEL);
     if (timing) CK(cudaEventRecord(dev->tev[0], st));
 
     // ---- descriptor-ish state
@@ -962,6 +967,12 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
         CK(cudaMemsetAsync(dev->q.counters, 0, 32, st));
         dev->launches += 1;
         if (timing) CK(cudaEventRecord(dev->tev[3], st));
+        cudaEvent_t* kpair = nullptr;
+        if (timeKernel) {
+            kpair = dev->kev[dev->kevRecorded % VkrDevice::KRING];
+            if (!kpair[0]) { CK(cudaEventCreate(&kpair[0])); CK(cudaEventCreate(&kpair[1])); }
+            CK(cudaEventRecord(kpair[0], st));
+        }
         // only the opaque prefix writes depth; transparent draws are blended in a later pass
         const unsigned opaqueChunks = plan.opaqueClusters, mainSlots = plan.passSlots[0];
         if (opaqueChunks) {
@@ -969,6 +980,7 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
                 geometry_kernel<false><<<(mainSlots + GEOM_WARPS - 1) / GEOM_WARPS, GEOM_WARPS * 32, 0, st>>>(dChunks, dPerm, mainSlots, (const float*)dObjects,
                                                                                                             (uint32_t)(sizeof(DObject) / 4), rt, dev->q);
             if (timing) CK(cudaEventRecord(dev->tev[4], st));
+            if (kpair) { CK(cudaEventRecord(kpair[1], st)); dev->kevRecorded++; }
             const AlphaCtx ax{dObjects, dev->chunkObjBuf, dev->matDev, dev->texDev};
             if (plan.anyCutout) {
                 geometry_cutout_kernel<<<opaqueChunks, CL_TRIS, 0, st>>>(dObjects, dChunks, rt, dev->q, ax);
@@ -1051,6 +1063,17 @@ int vkr_sync(VkrDevice* dev) {
     CK(cudaStreamSynchronize(dev->shadowStream));
     if (dev->gatherStream) CK(cudaStreamSynchronize(dev->gatherStream));
     if (dev->countersHost[2] || dev->countersHost[6] || dev->countersHost[10]) return dev->fail(VKR_ERROR_CAPACITY, "large-triangle queue overflow");
+    if (dev->kevRecorded > dev->kevRead) {      // mean main-pass geometry kernel time over the frames since the last sync
+        const uint64_t first = std::max(dev->kevRead, dev->kevRecorded > (uint64_t)VkrDevice::KRING ? dev->kevRecorded - VkrDevice::KRING : 0);
+        double sum = 0.0;
+        for (uint64_t k = first; k < dev->kevRecorded; ++k) {
+            float ms = 0;
+            cudaEventElapsedTime(&ms, dev->kev[k % VkrDevice::KRING][0], dev->kev[k % VkrDevice::KRING][1]);
+            sum += ms;
+        }
+        dev->timings[VKR_T_GEOM_KERNEL] = (float)(sum / (double)(dev->kevRecorded - first));
+        dev->kevRead = dev->kevRecorded;
+    }
     if (dev->tevValid) {
         auto el = [&](int a, int b) { float ms = 0; cudaEventElapsedTime(&ms, dev->tev[a], dev->tev[b]); return ms; };
         dev->timings[VKR_T_UPLOAD] = el(0, 1);
@@ -1120,6 +1143,13 @@ int vkr_readback_async(VkrDevice* dev, VkrTarget what, void* dst, size_t dstByte
 int vkr_stats(VkrDevice* dev, VkrEngineStats* out) {
     if (!dev || !out) return VKR_ERROR_INVALID_ARGUMENT;
     *out = dev->stats;
+    return VKR_SUCCESS;
+}
+
+int vkr_set_flags(VkrDevice* dev, uint32_t flags) {
+    if (!dev) return VKR_ERROR_INVALID_ARGUMENT;
+    if (!(flags & VKR_CONFIG_TIMINGS)) dev->tevValid = false;
+    dev->flags = flags;
     return VKR_SUCCESS;
 }
 
