@@ -436,19 +436,25 @@ struct FrameSlot {
     cudaEvent_t rendered = nullptr;
     cudaEvent_t copied = nullptr;       // last asynchronous read-back of this slot's presented image (copy stream)
     bool copyPending = false;
+    // per-frame tables written on the device by expand_chunks_kernel (one set per frame in flight: the next frame's
+    // tables are built on the upload stream while this frame's kernels still read theirs)
+    DChunk* chunkBuf = nullptr; size_t chunkCap = 0;       // cluster table
+    uint2* chunkObjBuf = nullptr; size_t seqSlotCap = 0;   // seq >> 8 -> (draw, first triangle)
+    uint32_t* permBuf = nullptr; size_t permCap = 0;       // (1 + shadow layers) x clusters: processing order per pass
 };
 
 struct VkrDevice {
     int device = 0;
     cudaStream_t stream = nullptr, copyStream = nullptr;   // frame stream; device->host copies
     cudaStream_t shadowStream = nullptr, upStream = nullptr; // shadow pass runs beside the main pass; host->device uploads
-    cudaEvent_t evFork = nullptr, evShadow = nullptr;
+    cudaEvent_t evShadow = nullptr;
     bool ownStream = false;
     uint32_t W = 0, H = 0, S = 2048, flags = 0;
     int smCount = 148;
 
     uint64_t* vis = nullptr;
-    uint32_t* shadowBits = nullptr;
+    uint32_t* shadowBits = nullptr;        // the shadow map of the frame being (or last) drawn: one of shadowBuf
+    uint32_t* shadowBuf[VKR_FRAME_OVERLAP] = {};   // per frame in flight: frame i+1's shadow pass overlaps frame i's shading
     uint16_t* hdr = nullptr;
     uint32_t* rgba8[VKR_FRAME_OVERLAP] = {nullptr, nullptr};
     uint32_t* scratch = nullptr;        // W*H*4, lazily allocated for depth / primid readback
@@ -475,9 +481,6 @@ struct VkrDevice {
     // VKR_HOST_PROF=1: mean host time of vkr_draw's sections, printed at vkr_destroy
     bool hostProf = false; double hostProfUs[8] = {0}; uint64_t hostProfFrames = 0;
 
-    DChunk* chunkBuf = nullptr; size_t chunkCap = 0;   // per-frame cluster table (device-written)
-    uint2* chunkObjBuf = nullptr; size_t seqSlotCap = 0;   // seq >> 8 -> (draw, first triangle)
-    uint32_t* permBuf = nullptr; size_t permCap = 0;   // (1 + shadow layers) x clusters: processing order per pass
 
     Queues q{};                         // large-triangle queue of the main pass
     Queues qShadow{};                   // ... of the shadow pass (the two passes overlap)
@@ -603,13 +606,13 @@ int vkr_create(const VkrConfig* cfg, VkrDevice** out) {
         CK(cudaDeviceGetStreamPriorityRange(&prLo, &prHi));
         CK(cudaStreamCreateWithPriority(&dev->shadowStream, cudaStreamNonBlocking, prHi));
         CK(cudaStreamCreateWithFlags(&dev->upStream, cudaStreamNonBlocking));
-        CK(cudaEventCreateWithFlags(&dev->evFork, cudaEventDisableTiming));
         CK(cudaEventCreateWithFlags(&dev->evShadow, cudaEventDisableTiming));
         const size_t px = (size_t)dev->W * dev->H;
         ALLOC(dev->vis, px * 8);
         ALLOC(dev->hdr, px * 8);
         for (int i = 0; i < VKR_FRAME_OVERLAP; ++i) ALLOC(dev->rgba8[i], px * 4);
-        ALLOC(dev->shadowBits, (size_t)dev->S * dev->S * 4 * VKR_NUM_CASCADES);
+        for (auto& b : dev->shadowBuf) ALLOC(b, (size_t)dev->S * dev->S * 4 * VKR_NUM_CASCADES);
+        dev->shadowBits = dev->shadowBuf[0];
         ALLOC(dev->lut, 256 * 4);
         init_lut();
         CK(cudaMemcpyAsync(dev->lut, g_srgb_lut, sizeof(g_srgb_lut), cudaMemcpyHostToDevice, dev->stream));
@@ -633,8 +636,9 @@ int vkr_create(const VkrConfig* cfg, VkrDevice** out) {
         }
         for (auto& e : dev->tev) CK(cudaEventCreate(&e));
         // shadow image starts cleared to 1.0 so an un-rendered map reads "unshadowed"
-        fill_u32_kernel<<<grid_for((size_t)dev->S * dev->S * VKR_NUM_CASCADES / 4, 256, 4096), 256, 0, dev->stream>>>(
-            dev->shadowBits, (size_t)dev->S * dev->S * VKR_NUM_CASCADES, DEPTH_ONE_BITS);
+        for (uint32_t* b : dev->shadowBuf)
+            fill_u32_kernel<<<grid_for((size_t)dev->S * dev->S * VKR_NUM_CASCADES / 4, 256, 4096), 256, 0, dev->stream>>>(
+                b, (size_t)dev->S * dev->S * VKR_NUM_CASCADES, DEPTH_ONE_BITS);
         fill_u64_kernel<<<grid_for(px / 2, 256, 4096), 256, 0, dev->stream>>>(dev->vis, px, VIS_CLEAR);
         CK(cudaGetLastError());
         // init_default_data: bindless slot 0 = default normal texture, NEAREST (src/vk_engine_init.cpp:351-355)
@@ -684,7 +688,6 @@ void vkr_destroy(VkrDevice* dev) {
     if (dev->copyStream) cudaStreamDestroy(dev->copyStream);
     if (dev->shadowStream) cudaStreamDestroy(dev->shadowStream);
     if (dev->upStream) cudaStreamDestroy(dev->upStream);
-    if (dev->evFork) cudaEventDestroy(dev->evFork);
     if (dev->evShadow) cudaEventDestroy(dev->evShadow);
     if (dev->ownStream && dev->stream) cudaStreamDestroy(dev->stream);
     delete dev;
@@ -873,17 +876,17 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
     const size_t offObj = 0, offBase = align16(offObj + szObj), offSeq = align16(offBase + szBase), offShadow = align16(offSeq + szBase),
                  offSlot = align16(offShadow + szShadow);
     const size_t total = align16(offSlot + szSlot) + 16;
-    if (dev->chunkCap < nChunks) {
-        dev->chunkCap = std::max<size_t>((size_t)nChunks * 3 / 2, 1024);
-        ALLOC(dev->chunkBuf, dev->chunkCap * sizeof(DChunk));     // the previous tables are freed at destroy
+    if (slot.chunkCap < nChunks) {
+        slot.chunkCap = std::max<size_t>((size_t)nChunks * 3 / 2, 1024);
+        ALLOC(slot.chunkBuf, slot.chunkCap * sizeof(DChunk));     // the previous tables are freed at destroy
     }
-    if (dev->seqSlotCap < nSeqSlots) {
-        dev->seqSlotCap = std::max<size_t>((size_t)nSeqSlots * 3 / 2, 1024);
-        ALLOC(dev->chunkObjBuf, dev->seqSlotCap * sizeof(uint2));
+    if (slot.seqSlotCap < nSeqSlots) {
+        slot.seqSlotCap = std::max<size_t>((size_t)nSeqSlots * 3 / 2, 1024);
+        ALLOC(slot.chunkObjBuf, slot.seqSlotCap * sizeof(uint2));
     }
-    if (dev->permCap < (size_t)passes * nChunks) {
-        dev->permCap = std::max<size_t>((size_t)passes * nChunks * 3 / 2, 1024);
-        ALLOC(dev->permBuf, dev->permCap * 4);
+    if (slot.permCap < (size_t)passes * nChunks) {
+        slot.permCap = std::max<size_t>((size_t)passes * nChunks * 3 / 2, 1024);
+        ALLOC(slot.permBuf, slot.permCap * 4);
     }
     if (dev->frameIndex >= VKR_FRAME_OVERLAP) CK(cudaEventSynchronize(slot.uploaded));   // pinned buffer reuse
     int rc = ensure_slot(dev, slot, total);
@@ -899,18 +902,18 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
     CK(cudaStreamWaitEvent(dev->upStream, slot.rendered, 0));
     CK(cudaMemcpyAsync(slot.devbuf, slot.pinned, total, cudaMemcpyHostToDevice, dev->upStream));
     dev->uploadBytes = total;
-    CK(cudaEventRecord(slot.uploaded, dev->upStream));
-    CK(cudaStreamWaitEvent(st, slot.uploaded, 0));
     char* dp = (char*)slot.devbuf;
     const DObject* dObjects = (const DObject*)(dp + offObj);
-    const DChunk* dChunks = dev->chunkBuf;
+    const DChunk* dChunks = slot.chunkBuf;
     const float* dShadowMvp = (const float*)(dp + offShadow);
-    const uint32_t* dPerm = dev->permBuf;
-    if (n) {
-        expand_chunks_kernel<<<(unsigned)n, 64, 0, st>>>(dObjects, (const uint32_t*)(dp + offBase), (const uint32_t*)(dp + offSeq), (const uint32_t*)(dp + offSlot), (uint32_t)n, passes,
-                                                         nChunks, dev->chunkBuf, dev->chunkObjBuf, dev->permBuf);
+    const uint32_t* dPerm = slot.permBuf;
+    if (n) {   // the frame's tables, on the upload stream too: neither the main nor the shadow stream has to wait for the other
+        expand_chunks_kernel<<<(unsigned)n, 64, 0, dev->upStream>>>(dObjects, (const uint32_t*)(dp + offBase), (const uint32_t*)(dp + offSeq), (const uint32_t*)(dp + offSlot), (uint32_t)n, passes,
+                                                                    nChunks, slot.chunkBuf, slot.chunkObjBuf, slot.permBuf);
         dev->launches += 1;
     }
+    CK(cudaEventRecord(slot.uploaded, dev->upStream));
+    CK(cudaStreamWaitEvent(st, slot.uploaded, 0));
     if (timing) CK(cudaEventRecord(dev->tev[1], st));
     mark(1);
 
@@ -920,8 +923,10 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
     // pass's rasterisation: both are latency-bound, together they fill the SMs' issue slots
     cudaStream_t ss = dev->shadowStream;
     if (plan.shadowLayers) {
-        CK(cudaEventRecord(dev->evFork, st));
-        CK(cudaStreamWaitEvent(ss, dev->evFork, 0));
+        // the shadow pass depends on this frame's upload only (and, through it, on the frame that last used this slot's shadow
+        // map and tables): it may run ahead of the main stream, which is still shading the previous frame
+        CK(cudaStreamWaitEvent(ss, slot.uploaded, 0));
+        dev->shadowBits = dev->shadowBuf[slotIdx];
         if (timing) CK(cudaEventRecord(dev->tev[7], ss));
         for (int layer = 0; layer < plan.shadowLayers; ++layer) {
             RasterTarget rt = plan.shadowTarget;
@@ -981,7 +986,7 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
                                                                                                             (uint32_t)(sizeof(DObject) / 4), rt, dev->q);
             if (timing) CK(cudaEventRecord(dev->tev[4], st));
             if (kpair) { CK(cudaEventRecord(kpair[1], st)); dev->kevRecorded++; }
-            const AlphaCtx ax{dObjects, dev->chunkObjBuf, dev->matDev, dev->texDev};
+            const AlphaCtx ax{dObjects, slot.chunkObjBuf, dev->matDev, dev->texDev};
             if (plan.anyCutout) {
                 geometry_cutout_kernel<<<opaqueChunks, CL_TRIS, 0, st>>>(dObjects, dChunks, rt, dev->q, ax);
                 dev->launches += 1;
@@ -996,7 +1001,7 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
 
     if (plan.shadowLayers) CK(cudaStreamWaitEvent(st, dev->evShadow, 0));   // join: the shaders sample the shadow map
     ShadeBuffers sb{};
-    sb.vis = dev->vis; sb.objects = dObjects; sb.chunkObj = dev->chunkObjBuf; sb.materials = dev->matDev;
+    sb.vis = dev->vis; sb.objects = dObjects; sb.chunkObj = slot.chunkObjBuf; sb.materials = dev->matDev;
     sb.textures = dev->texDev; sb.cube = dev->haveCube ? dev->cubeDev : nullptr;
     sb.shadow = reinterpret_cast<const float*>(dev->shadowBits);
     sb.hdr = dev->hdr; sb.rgba8 = dev->rgba8[slotIdx]; sb.srgbLut = dev->lut;
@@ -1046,7 +1051,7 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
     mark(5);
     if (dev->hostProf && dev->frameIndex >= 16) dev->hostProfFrames++;
     dev->lastSlot = slotIdx;
-    dev->lastChunkObj = dev->chunkObjBuf; dev->lastObjects = dObjects;
+    dev->lastChunkObj = slot.chunkObjBuf; dev->lastObjects = dObjects;
     dev->frameIndex++;
     dev->stats.drawcall_count = (int32_t)n;
     dev->stats.triangle_count = (int32_t)plan.totalTris;
