@@ -143,6 +143,9 @@ typedef struct VkrConfig {
 } VkrConfig;
 
 #define VKR_CONFIG_TIMINGS 1u  /* record CUDA events around every pass (13 events per frame: costs a few percent) */
+#define VKR_CONFIG_SUBMIT_THREAD 4u /* vkr_draw plans the frame (matrices, culling, order, bands) on the caller's thread and hands
+                                       the CUDA / NCCL calls to a submit thread, so planning frame i+1 overlaps issuing frame i.
+                                       A failure while issuing is reported by the next call on the device. */
 #define VKR_CONFIG_TIME_GEOM_KERNEL 2u /* only the two events around the main pass's geometry kernel, kept for the last 128
                                           frames: vkr_get_timings' VKR_T_GEOM_KERNEL is then the MEAN over the frames drawn
                                           since the previous vkr_sync (what bench.py reports the roofline from) */

@@ -85,3 +85,32 @@ def test_gpu_config4_full_size(ork_lib, vkr_lib):
     assert np.array_equal(rev["shadow"][:1].view(np.uint32), got["shadow"][:1].view(np.uint32))
     assert (np.abs(rev["rgba"].astype(np.int32) - got["rgba"].astype(np.int32)).max(-1) <= 1).mean() >= 0.999
     r.close()
+
+
+def test_gpu_submit_thread_matches_synchronous_submission(vkr_lib):
+    """VKR_CONFIG_SUBMIT_THREAD: frames planned on the caller's thread and issued by the submit thread are the same frames;
+    an invalid draw list is still refused by the call that receives it; the device survives switching modes."""
+    from vk_renderer_b200 import capi
+    import scenes as sc
+    frames = {}
+    for flags in (0, capi.CONFIG_SUBMIT_THREAD):
+        r = capi.Renderer(vkr_lib, "vkr", 320, 200, shadow_extent=256, flags=flags)
+        sd, objs, fp = sc.SCENES["lattice"](r)
+        views = sc.orbit_views(r, 6)
+        out = []
+        for k in range(12):                                   # back to back: the submit thread is busy while the next frame is planned
+            r.draw(views[k % 6], objs, fp)
+            if k >= 6:
+                out.append((r.readback(capi.TARGET_RGBA8), r.readback(capi.TARGET_PRIMID)))
+        bad = objs.copy()
+        bad["mesh"][0] = 12345
+        with pytest.raises(capi.VkrError):
+            r.draw(views[0], bad, fp)
+        r.draw(views[0], objs, fp)                            # still usable
+        r.set_flags(0)
+        r.draw(views[1], objs, fp)
+        out.append((r.readback(capi.TARGET_RGBA8), r.readback(capi.TARGET_PRIMID)))
+        frames[flags] = out
+        r.close()
+    for (a_rgba, a_prim), (b_rgba, b_prim) in zip(frames[0], frames[capi.CONFIG_SUBMIT_THREAD]):
+        assert np.array_equal(a_prim, b_prim) and np.array_equal(a_rgba, b_rgba)

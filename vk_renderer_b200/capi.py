@@ -23,6 +23,7 @@ TARGET_RGBA8, TARGET_HDR16F, TARGET_DEPTH, TARGET_SHADOW, TARGET_PRIMID, TARGET_
 COMM_ID_BYTES = 128
 CONFIG_TIMINGS = 1
 CONFIG_TIME_GEOM_KERNEL = 2
+CONFIG_SUBMIT_THREAD = 4
 T_NAMES = ["upload", "shadow", "geometry", "shade", "transparent", "post", "total", "geom_kernel", "large_kernel", "clear",
            "shadow_exchange", "frame_gather"]
 

@@ -8,7 +8,11 @@
 #include <nccl.h>
 
 #include <algorithm>
+#include <atomic>
 #include <chrono>
+#include <condition_variable>
+#include <mutex>
+#include <thread>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -490,7 +494,14 @@ struct VkrDevice {
     uint64_t frameIndex = 0;
     int lastSlot = 0;
     const uint2* lastChunkObj = nullptr; const DObject* lastObjects = nullptr;
-    FramePlan plan;
+    FramePlan plans[2]; int planIdx = 0;      // two: with a submit thread one is being submitted while the next is planned
+    // VKR_CONFIG_SUBMIT_THREAD: vkr_draw plans the frame on the caller's thread and hands the CUDA/NCCL calls to this thread
+    std::thread worker;
+    std::atomic<int> jobState{0};             // 0 idle, 1 posted, 2 running
+    std::atomic<bool> workerStop{false};
+    std::mutex workerMutex; std::condition_variable workerCv;
+    FramePlan* jobPlan = nullptr; size_t jobN = 0;
+    int asyncRc = 0;                          // first failure of an asynchronously submitted frame, reported by the next call
 
     cudaEvent_t tev[13] = {nullptr};  // ... 9 transparent done; 10 shadow raster done (before the exchange); 11, 12 frame gather (gather stream)   // 0 start, 1 uploaded, 3 cleared, 4 geometry kernel, 5 large kernel, 6 shaded; 7,8 shadow pass (shadow stream)
     bool tevValid = false, shadowTimed = false;
@@ -528,6 +539,8 @@ static void init_lut() {
 }
 
 static int dev_alloc(VkrDevice* dev, void** p, size_t bytes);
+static int drain(VkrDevice* dev);
+#define DRAIN(dev) do { if ((dev)->worker.joinable()) { int arc_ = drain(dev); if (arc_ != VKR_SUCCESS) return arc_; } } while (0)
 
 struct DeviceClusterProvider : ClusterProvider {
     VkrDevice* dev;
@@ -536,6 +549,7 @@ struct DeviceClusterProvider : ClusterProvider {
         VkrDevice::RangeKey key{mesh, firstIndex, indexCount};
         auto it = dev->ranges.find(key);
         if (it != dev->ranges.end()) { out = it->second; return true; }
+        { const int arc = drain(dev); if (arc != VKR_SUCCESS) dev->asyncRc = arc; }     // building touches state the submit thread uses
         ClusterData cd;
         build_clusters(dev->meshIndexHost[mesh].data() + firstIndex, indexCount / 3, dev->meshes[mesh].nv, dev->meshPosHost[mesh].data(), cd);
         uint32_t *dv = nullptr, *dt = nullptr, *dorig = nullptr; uint2* di = nullptr; float4* db = nullptr;
@@ -662,6 +676,12 @@ int vkr_create(const VkrConfig* cfg, VkrDevice** out) {
 
 void vkr_destroy(VkrDevice* dev) {
     if (!dev) return;
+    if (dev->worker.joinable()) {
+        (void)drain(dev);
+        dev->workerStop.store(true);
+        dev->workerCv.notify_all();
+        dev->worker.join();
+    }
     cudaSetDevice(dev->device);
     cudaDeviceSynchronize();
     if (dev->hostProf && dev->hostProfFrames) {
@@ -695,6 +715,7 @@ void vkr_destroy(VkrDevice* dev) {
 
 int vkr_upload_mesh(VkrDevice* dev, const uint32_t* indices, size_t ni, const VkrVertex* vertices, size_t nv, VkrMesh* out) {
     if (!dev) return VKR_ERROR_INVALID_ARGUMENT;
+    DRAIN(dev);
     if (!out || (ni && !indices) || (nv && !vertices) || nv >= 0xFFFFFFFFull || ni >= 0xFFFFFFFFull)
         return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_upload_mesh: bad arguments");
     for (size_t i = 0; i < ni; ++i)
@@ -762,6 +783,7 @@ static DTexture make_dtexture(const ImageRec& im, int sampler) {
 
 int vkr_create_image(VkrDevice* dev, const void* rgba8, uint32_t w, uint32_t h, VkrFormat fmt, int mipmapped, VkrImage* out) {
     if (!dev) return VKR_ERROR_INVALID_ARGUMENT;
+    DRAIN(dev);
     if (!rgba8 || !out || w == 0 || h == 0 || (fmt != VKR_FORMAT_R8G8B8A8_UNORM && fmt != VKR_FORMAT_R8G8B8A8_SRGB))
         return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_create_image: bad arguments");
     CK(cudaSetDevice(dev->device));
@@ -775,6 +797,7 @@ int vkr_create_image(VkrDevice* dev, const void* rgba8, uint32_t w, uint32_t h, 
 
 int vkr_update_bindless_texture(VkrDevice* dev, int index, VkrImage image, VkrSampler sampler) {
     if (!dev) return VKR_ERROR_INVALID_ARGUMENT;
+    DRAIN(dev);
     if (index < 0 || index >= VKR_MAX_BINDLESS || image >= dev->images.size())
         return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_update_bindless_texture: bad index or image");
     dev->texHost[index] = make_dtexture(dev->images[image], sampler);
@@ -784,6 +807,7 @@ int vkr_update_bindless_texture(VkrDevice* dev, int index, VkrImage image, VkrSa
 
 int vkr_set_cubemap(VkrDevice* dev, const void* const faces[6], uint32_t w, uint32_t h, VkrFormat fmt, int mipmapped) {
     if (!dev) return VKR_ERROR_INVALID_ARGUMENT;
+    DRAIN(dev);
     if (!faces || w == 0 || h == 0) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_set_cubemap: bad arguments");
     CK(cudaSetDevice(dev->device));
     DTexture t[6];
@@ -802,6 +826,7 @@ int vkr_set_cubemap(VkrDevice* dev, const void* const faces[6], uint32_t w, uint
 
 int vkr_build_material(VkrDevice* dev, const VkrMaterialConstants* p, VkrMaterialPass pass, VkrMaterial* out) {
     if (!dev) return VKR_ERROR_INVALID_ARGUMENT;
+    DRAIN(dev);
     if (!p || !out) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_build_material: bad arguments");
     DMaterial m;
     std::memcpy(m.colorFactors, p->colorFactors, 16);
@@ -825,10 +850,63 @@ static int ensure_slot(VkrDevice* dev, FrameSlot& s, size_t bytes) {
     return VKR_SUCCESS;
 }
 
-int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject* objs, size_t n, const VkrFrameParams* fp) {
+}  // extern "C"
+
+// ---- submit thread (VKR_CONFIG_SUBMIT_THREAD) -------------------------------------------------------------------
+static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n);
+
+static void worker_main(VkrDevice* dev) {
+    cudaSetDevice(dev->device);
+    for (;;) {
+        int spins = 0;
+        while (dev->jobState.load(std::memory_order_acquire) != 1 && !dev->workerStop.load(std::memory_order_acquire)) {
+            if (++spins < 20000) { __builtin_ia32_pause(); continue; }          // ~0.2 ms of spinning covers the gap between frames
+            std::unique_lock<std::mutex> lk(dev->workerMutex);
+            dev->workerCv.wait_for(lk, std::chrono::milliseconds(2), [&] { return dev->jobState.load() == 1 || dev->workerStop.load(); });
+            spins = 0;
+        }
+        if (dev->workerStop.load(std::memory_order_acquire) && dev->jobState.load() != 1) return;
+        dev->jobState.store(2, std::memory_order_release);
+        const int rc = submit_frame(dev, *dev->jobPlan, dev->jobN);
+        if (rc != VKR_SUCCESS && dev->asyncRc == VKR_SUCCESS) dev->asyncRc = rc;
+        dev->jobState.store(0, std::memory_order_release);
+    }
+}
+// Wait until the submit thread has issued everything it was given; returns (and clears) a deferred failure.
+static int drain(VkrDevice* dev) {
+    if (!dev->worker.joinable()) return VKR_SUCCESS;
+    int spins = 0;
+    while (dev->jobState.load(std::memory_order_acquire) != 0) { if (++spins < 4000) __builtin_ia32_pause(); else std::this_thread::yield(); }
+    const int rc = dev->asyncRc;
+    dev->asyncRc = VKR_SUCCESS;
+    return rc;
+}
+
+extern "C" int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject* objs, size_t n, const VkrFrameParams* fp) {
     if (!dev) return VKR_ERROR_INVALID_ARGUMENT;
     if (!scene || !fp || (n && !objs)) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_draw: null argument");
     CK(cudaSetDevice(dev->device));
+    const bool async = (dev->flags & VKR_CONFIG_SUBMIT_THREAD) && !dev->shadowExchange;     // a user hook runs on the caller's thread
+    if (!async) DRAIN(dev);
+    if (async && !dev->worker.joinable()) dev->worker = std::thread(worker_main, dev);
+    const auto hostT = std::chrono::steady_clock::now();
+    FramePlan& plan = dev->plans[dev->planIdx];        // the other one may still be in the submit thread's hands
+    DeviceClusterProvider provider(dev);
+    std::string why = plan_frame(scene, objs, n, fp, dev->meshes, dev->materials, dev->texHost, provider, dev->W, dev->H, dev->S, plan,
+                                 dev->shardRank, dev->shardRanks);     // sharded: also splits the rows into cost-balanced bands
+    if (!why.empty()) { DRAIN(dev); return dev->fail(VKR_ERROR_INVALID_ARGUMENT, why.c_str()); }
+    if (dev->hostProf && dev->frameIndex >= 16)
+        dev->hostProfUs[0] += std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - hostT).count();
+    if (!async) return submit_frame(dev, plan, n);
+    DRAIN(dev);                                        // the previous frame is fully issued (and its failure, if any, reported here)
+    dev->jobPlan = &plan; dev->jobN = n;
+    dev->planIdx ^= 1;
+    dev->jobState.store(1, std::memory_order_release);
+    dev->workerCv.notify_one();
+    return VKR_SUCCESS;
+}
+
+static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
     auto hostT = std::chrono::steady_clock::now();
     auto mark = [&](int k) {
         if (!dev->hostProf || dev->frameIndex < 16) return;      // skip allocation / NCCL warm-up frames
@@ -836,12 +914,6 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
         dev->hostProfUs[k] += std::chrono::duration<double, std::micro>(now - hostT).count();
         hostT = now;
     };
-    FramePlan& plan = dev->plan;
-    DeviceClusterProvider provider(dev);
-    std::string why = plan_frame(scene, objs, n, fp, dev->meshes, dev->materials, dev->texHost, provider, dev->W, dev->H, dev->S, plan,
-                                 dev->shardRank, dev->shardRanks);     // sharded: also splits the rows into cost-balanced bands
-    if (!why.empty()) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, why.c_str());
-    mark(0);
     cudaStream_t st = dev->stream;
     dev->launches = 0;
     const bool timing = dev->flags & VKR_CONFIG_TIMINGS;
@@ -1060,8 +1132,11 @@ int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject
     return VKR_SUCCESS;
 }
 
+extern "C" {
+
 int vkr_sync(VkrDevice* dev) {
     if (!dev) return VKR_ERROR_INVALID_ARGUMENT;
+    DRAIN(dev);
     CK(cudaSetDevice(dev->device));
     CK(cudaStreamSynchronize(dev->stream));
     CK(cudaStreamSynchronize(dev->copyStream));
@@ -1114,6 +1189,7 @@ static int target_info(VkrDevice* dev, VkrTarget what, const void** src, size_t*
 
 static int do_readback(VkrDevice* dev, VkrTarget what, void* dst, size_t dstBytes, bool sync) {
     if (!dev) return VKR_ERROR_INVALID_ARGUMENT;
+    DRAIN(dev);
     const void* src; size_t bytes;
     if (!dst || target_info(dev, what, &src, &bytes)) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_readback: bad target");
     if (dstBytes < bytes) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_readback: destination too small");
@@ -1147,12 +1223,14 @@ int vkr_readback_async(VkrDevice* dev, VkrTarget what, void* dst, size_t dstByte
 
 int vkr_stats(VkrDevice* dev, VkrEngineStats* out) {
     if (!dev || !out) return VKR_ERROR_INVALID_ARGUMENT;
+    DRAIN(dev);
     *out = dev->stats;
     return VKR_SUCCESS;
 }
 
 int vkr_set_flags(VkrDevice* dev, uint32_t flags) {
     if (!dev) return VKR_ERROR_INVALID_ARGUMENT;
+    DRAIN(dev);
     if (!(flags & VKR_CONFIG_TIMINGS)) dev->tevValid = false;
     dev->flags = flags;
     return VKR_SUCCESS;
@@ -1160,12 +1238,14 @@ int vkr_set_flags(VkrDevice* dev, uint32_t flags) {
 
 int vkr_get_timings(VkrDevice* dev, float* msOut, int count) {
     if (!dev || !msOut || count < 0) return VKR_ERROR_INVALID_ARGUMENT;
+    DRAIN(dev);
     for (int i = 0; i < count && i < VKR_T_COUNT; ++i) msOut[i] = dev->timings[i];
     return VKR_SUCCESS;
 }
 
 int vkr_device_ptr(VkrDevice* dev, VkrTarget what, void** ptr, size_t* bytes) {
     if (!dev || !ptr || !bytes) return VKR_ERROR_INVALID_ARGUMENT;
+    DRAIN(dev);
     const void* src; size_t n;
     if (target_info(dev, what, &src, &n) || !src) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_device_ptr: target has no linear buffer");
     *ptr = const_cast<void*>(src); *bytes = n;
@@ -1183,6 +1263,7 @@ int vkr_comm_unique_id(void* out, size_t bytes) {
 
 int vkr_shard_init(VkrDevice* dev, int rank, int nranks, const void* twoIds, size_t bytes) {
     if (!dev) return VKR_ERROR_INVALID_ARGUMENT;
+    DRAIN(dev);
     if (!twoIds || bytes < 2 * VKR_COMM_ID_BYTES || nranks < 1 || rank < 0 || rank >= nranks)
         return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_shard_init: bad arguments");
     if ((int)dev->H < nranks || (int)dev->S < nranks) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_shard_init: more ranks than rows");
@@ -1208,18 +1289,20 @@ int vkr_shard_init(VkrDevice* dev, int rank, int nranks, const void* twoIds, siz
 
 int vkr_set_shadow_exchange(VkrDevice* dev, VkrShadowExchangeFn fn, void* user) {
     if (!dev) return VKR_ERROR_INVALID_ARGUMENT;
+    DRAIN(dev);
     dev->shadowExchange = fn; dev->shadowExchangeUser = user;
     return VKR_SUCCESS;
 }
 
 int vkr_cull_stats(VkrDevice* dev, uint32_t out[4]) {
     if (!dev || !out) return VKR_ERROR_INVALID_ARGUMENT;
+    DRAIN(dev);
     out[0] = dev->lastOpaqueClusters; out[1] = dev->countersHost[3];
     out[2] = dev->lastShadowClusters; out[3] = dev->countersHost[7];
     return VKR_SUCCESS;
 }
 
-int vkr_launch_count(VkrDevice* dev) { return dev ? dev->launches : 0; }
-size_t vkr_upload_bytes(VkrDevice* dev) { return dev ? dev->uploadBytes : 0; }
+int vkr_launch_count(VkrDevice* dev) { if (!dev) return 0; (void)drain(dev); return dev->launches; }
+size_t vkr_upload_bytes(VkrDevice* dev) { if (!dev) return 0; (void)drain(dev); return dev->uploadBytes; }
 
 }  // extern "C"
