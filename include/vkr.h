@@ -164,7 +164,11 @@ typedef enum VkrTarget {
     VKR_TARGET_DEPTH = 2,      /* _depthImage, D32, W*H*4 */
     VKR_TARGET_SHADOW = 3,     /* _shadowImage, D32, S*S*4*NUM_CASCADES */
     VKR_TARGET_PRIMID = 4,     /* uint32 per pixel: submission-order primitive id, 0xFFFFFFFF = none */
-    VKR_TARGET_RGBA8_GATHERED = 5 /* sharded devices: the presented image assembled from every rank's rows (vkr_shard_init) */
+    VKR_TARGET_RGBA8_GATHERED = 5, /* sharded devices: the presented image assembled from every rank's rows (vkr_shard_init) */
+    VKR_TARGET_RGB8 = 6        /* the presented image (assembled, on sharded devices) as packed R,G,B bytes, W*H*3: what an image
+                                  writer or an encoder consumes. The swapchain's alpha is never composited (the builder at
+                                  src/vk_engine.cpp:48-56 leaves vk-bootstrap's composite alpha at its default, OPAQUE), so dropping
+                                  it loses nothing a viewer of the reference could see and saves a quarter of the read-back */
 } VkrTarget;
 
 /* Pass indices for vkr_get_timings. */

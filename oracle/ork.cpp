@@ -1152,6 +1152,13 @@ int ork_readback(OrkDevice* d, VkrTarget what, void* dst, size_t bytes) {
         case VKR_TARGET_DEPTH: src = d->depth.data(); n = d->depth.size() * 4; break;
         case VKR_TARGET_SHADOW: src = d->shadow.data(); n = d->shadow.size() * 4; break;
         case VKR_TARGET_PRIMID: src = d->primid.data(); n = d->primid.size() * 4; break;
+        case VKR_TARGET_RGB8: {
+            const size_t px = d->rgba8.size() / 4;
+            if (bytes < px * 3) return VKR_ERROR_INVALID_ARGUMENT;
+            uint8_t* o = (uint8_t*)dst;
+            for (size_t i = 0; i < px; ++i) { o[3 * i] = d->rgba8[4 * i]; o[3 * i + 1] = d->rgba8[4 * i + 1]; o[3 * i + 2] = d->rgba8[4 * i + 2]; }
+            return VKR_SUCCESS;
+        }
         default: return VKR_ERROR_INVALID_ARGUMENT;
     }
     if (bytes < n) return VKR_ERROR_INVALID_ARGUMENT;

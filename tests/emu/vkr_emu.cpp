@@ -337,6 +337,10 @@ int emu_readback(EmuDevice* d, int what, void* dst, size_t bytes) {
     size_t px = (size_t)d->W * d->H;
     switch (what) {
         case VKR_TARGET_RGBA8: if (bytes < px * 4) return -1; std::memcpy(dst, d->rgba8.data(), px * 4); return 0;
+        case VKR_TARGET_RGB8:
+            if (bytes < px * 3) return -1;
+            for (size_t i = 0; i < px; ++i) std::memcpy((uint8_t*)dst + 3 * i, (const uint8_t*)d->rgba8.data() + 4 * i, 3);
+            return 0;
         case VKR_TARGET_HDR16F: if (bytes < px * 8) return -1; std::memcpy(dst, d->hdr.data(), px * 8); return 0;
         case VKR_TARGET_SHADOW: std::memcpy(dst, d->shadowBits.data(), d->shadowBits.size() * 4); return 0;
         case VKR_TARGET_DEPTH: for (size_t i = 0; i < px; ++i) ((uint32_t*)dst)[i] = (uint32_t)(d->vis[i] >> 32); return 0;

@@ -12,7 +12,8 @@ def render(lib, prefix, scene, width, height, shadow_extent=512, scissor=None):
         fp.scissor[:] = scissor
     r.draw(sd, objs, fp)
     out = {k: r.readback(v) for k, v in dict(rgba=capi.TARGET_RGBA8, depth=capi.TARGET_DEPTH, prim=capi.TARGET_PRIMID,
-                                             shadow=capi.TARGET_SHADOW, hdr=capi.TARGET_HDR16F).items()}
+                                             shadow=capi.TARGET_SHADOW, hdr=capi.TARGET_HDR16F, rgb=capi.TARGET_RGB8).items()}
+    assert np.array_equal(out["rgb"], out["rgba"][..., :3]), "VKR_TARGET_RGB8 is the presented image without its alpha byte"
     out["stats"] = r.stats()
     out["shadows"] = bool(fp.enableShadows)
     out["layers"] = 4 if fp.shadowMode == 3 else 1

@@ -25,6 +25,13 @@ def test_gpu_scissor(ork_lib, vkr_lib):
     assert (got["prim"][mask] == 0xFFFFFFFF).all()
 
 
+def test_gpu_odd_extent(ork_lib, vkr_lib):
+    """An extent that is a multiple of nothing: tile edges, band edges and the tail of the packed RGB8 read-back."""
+    ref = parity.render(ork_lib, "ork", "basic_pcf", 397, 211, shadow_extent=67)
+    got = parity.render(vkr_lib, "vkr", "basic_pcf", 397, 211, shadow_extent=67)
+    parity.assert_parity(ref, got)
+
+
 def test_gpu_1080p_pcf(ork_lib, vkr_lib):
     ref = parity.render(ork_lib, "ork", "basic_pcf", 1920, 1080, shadow_extent=2048)
     got = parity.render(vkr_lib, "vkr", "basic_pcf", 1920, 1080, shadow_extent=2048)

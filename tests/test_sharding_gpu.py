@@ -38,6 +38,8 @@ def _worker(rank, world, port, scene, W, H, S, out_dir, native):
         for _ in range(3):
             r.draw(sd, objs, fp)
         img = r.readback(capi.TARGET_RGBA8_GATHERED)
+        if rank == 0:
+            assert np.array_equal(r.readback(capi.TARGET_RGB8), img[..., :3]), "VKR_TARGET_RGB8 of a sharded device is the assembled frame"
     else:           # the same sharding driven from Python over torch.distributed (vk_renderer_b200/sharding.py)
         sh = TileSharder(r, rank, world, cuda=True, shadow_group=dist.new_group())
         fp = sh.frame_params(fp)

@@ -19,7 +19,7 @@ FORMAT_UNORM, FORMAT_SRGB = 0, 1
 SAMPLER_NEAREST, SAMPLER_LINEAR = 0, 1
 PASS_MAIN_COLOR, PASS_TRANSPARENT, PASS_OTHER = 0, 1, 2
 FRAG_PBR, FRAG_LAMBERT = 0, 1
-TARGET_RGBA8, TARGET_HDR16F, TARGET_DEPTH, TARGET_SHADOW, TARGET_PRIMID, TARGET_RGBA8_GATHERED = range(6)
+TARGET_RGBA8, TARGET_HDR16F, TARGET_DEPTH, TARGET_SHADOW, TARGET_PRIMID, TARGET_RGBA8_GATHERED, TARGET_RGB8 = range(7)
 COMM_ID_BYTES = 128
 CONFIG_TIMINGS = 1
 CONFIG_TIME_GEOM_KERNEL = 2
@@ -281,6 +281,8 @@ class Renderer:
         W, H, S = self.width, self.height, self.shadow_extent
         if what in (TARGET_RGBA8, TARGET_RGBA8_GATHERED):
             out = np.empty((H, W, 4), np.uint8)
+        elif what == TARGET_RGB8:
+            out = np.empty((H, W, 3), np.uint8)
         elif what == TARGET_HDR16F:
             out = np.empty((H, W, 4), np.float16)
         elif what == TARGET_DEPTH:

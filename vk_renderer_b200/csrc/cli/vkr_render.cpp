@@ -96,8 +96,8 @@ int main(int argc, char** argv) {
         engine.update_scene(0.0f);
         if (int rc = engine.draw(); rc != VKR_SUCCESS) { std::fprintf(stderr, "draw failed (%d)\n", rc); return 1; }
     }
-    std::vector<unsigned char> rgba((size_t)W * H * 4);
-    if (engine._api.readback(engine._vkr, VKR_TARGET_RGBA8, rgba.data(), rgba.size()) != VKR_SUCCESS) { std::fprintf(stderr, "readback failed\n"); return 1; }
+    std::vector<unsigned char> rgb((size_t)W * H * 3);
+    if (engine._api.readback(engine._vkr, VKR_TARGET_RGB8, rgb.data(), rgb.size()) != VKR_SUCCESS) { std::fprintf(stderr, "readback failed\n"); return 1; }
     const double wall = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     VkrEngineStats st{};
     vkr_stats(engine._vkr, &st);
@@ -107,11 +107,7 @@ int main(int argc, char** argv) {
         FILE* f = std::fopen(out.c_str(), "wb");
         if (!f) { std::fprintf(stderr, "cannot write %s\n", out.c_str()); return 1; }
         std::fprintf(f, "P6\n%u %u\n255\n", W, H);
-        std::vector<unsigned char> row((size_t)W * 3);
-        for (uint32_t y = 0; y < H; ++y) {
-            for (uint32_t x = 0; x < W; ++x) std::memcpy(&row[(size_t)x * 3], &rgba[((size_t)y * W + x) * 4], 3);
-            std::fwrite(row.data(), 1, row.size(), f);
-        }
+        std::fwrite(rgb.data(), 1, rgb.size(), f);
         std::fclose(f);
     }
     return 0;

@@ -47,6 +47,23 @@ __global__ void fill_u32_kernel(uint32_t* __restrict__ dst, size_t n, uint32_t v
     for (size_t k = i; k < n4; k += stride) d4[k] = make_uint4(v, v, v, v);
     if (i == 0) for (size_t k = n4 << 2; k < n; ++k) dst[k] = v;
 }
+// VKR_TARGET_RGB8: four RGBA8 pixels in (16 B), twelve bytes out; the tail of an image whose pixel count is not a multiple
+// of four is packed bytewise by the first thread
+__global__ void pack_rgb8_kernel(const uint32_t* __restrict__ rgba, uint32_t* __restrict__ out, size_t n) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t n4 = n >> 2;
+    if (i < n4) {
+        const uint4 p = reinterpret_cast<const uint4*>(rgba)[i];
+        const uint32_t a = p.x & 0xFFFFFFu, b = p.y & 0xFFFFFFu, c = p.z & 0xFFFFFFu, d = p.w & 0xFFFFFFu;
+        out[3 * i] = a | (b << 24);
+        out[3 * i + 1] = (b >> 8) | (c << 16);
+        out[3 * i + 2] = (c >> 16) | (d << 8);
+    }
+    if (i == 0) {
+        uint8_t* o = reinterpret_cast<uint8_t*>(out);
+        for (size_t k = n4 << 2; k < n; ++k) { const uint32_t v = rgba[k]; o[3 * k] = (uint8_t)v; o[3 * k + 1] = (uint8_t)(v >> 8); o[3 * k + 2] = (uint8_t)(v >> 16); }
+    }
+}
 __global__ void extract_vis_kernel(const uint64_t* __restrict__ vis, uint32_t* __restrict__ out, size_t n, int what,
                                    const uint2* __restrict__ chunkObj, const DObject* __restrict__ objects) {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -462,6 +479,7 @@ struct VkrDevice {
     uint16_t* hdr = nullptr;
     uint32_t* rgba8[VKR_FRAME_OVERLAP] = {nullptr, nullptr};
     uint32_t* scratch = nullptr;        // W*H*4, lazily allocated for depth / primid readback
+    uint32_t* rgb8[VKR_FRAME_OVERLAP] = {nullptr, nullptr};   // W*H*3 (+pad), lazily allocated for VKR_TARGET_RGB8
     float* accum = nullptr;             // W*H*16, lazily allocated: additive sums of the transparent pass
     float* lut = nullptr;
 
@@ -1177,9 +1195,10 @@ static int target_info(VkrDevice* dev, VkrTarget what, const void** src, size_t*
     const size_t px = (size_t)dev->W * dev->H;
     switch (what) {
         case VKR_TARGET_RGBA8: *src = dev->rgba8[dev->lastSlot]; *bytes = px * 4; return 0;
-        case VKR_TARGET_RGBA8_GATHERED:
-            if (dev->shardRanks <= 1) { *src = dev->rgba8[dev->lastSlot]; *bytes = px * 4; return 0; }
-            *src = dev->gathered[dev->lastSlot]; *bytes = px * 4; return 0;
+        case VKR_TARGET_RGBA8_GATHERED: case VKR_TARGET_RGB8:
+            *src = dev->shardRanks <= 1 ? dev->rgba8[dev->lastSlot] : dev->gathered[dev->lastSlot];
+            *bytes = what == VKR_TARGET_RGB8 ? px * 3 : px * 4;
+            return 0;
         case VKR_TARGET_HDR16F: *src = dev->hdr; *bytes = px * 8; return 0;
         case VKR_TARGET_SHADOW: *src = dev->shadowBits; *bytes = (size_t)dev->S * dev->S * 4 * VKR_NUM_CASCADES; return 0;
         case VKR_TARGET_DEPTH: case VKR_TARGET_PRIMID: *src = nullptr; *bytes = px * 4; return 0;
@@ -1206,9 +1225,19 @@ static int do_readback(VkrDevice* dev, VkrTarget what, void* dst, size_t dstByte
     }
     // copy engine work goes to the copy stream so the next frame's kernels overlap it
     CK(cudaStreamWaitEvent(dev->copyStream, dev->slots[dev->lastSlot].rendered, 0));
-    if (what == VKR_TARGET_RGBA8_GATHERED && dev->shardRanks > 1) CK(cudaStreamWaitEvent(dev->copyStream, dev->gatheredEv[dev->lastSlot], 0));
+    if ((what == VKR_TARGET_RGBA8_GATHERED || what == VKR_TARGET_RGB8) && dev->shardRanks > 1)
+        CK(cudaStreamWaitEvent(dev->copyStream, dev->gatheredEv[dev->lastSlot], 0));
+    if (what == VKR_TARGET_RGB8) {
+        // packed on the copy stream too: ordered after the previous read-back of this slot's buffer, beside the next frame's kernels
+        const size_t px = (size_t)dev->W * dev->H;
+        uint32_t*& packed = dev->rgb8[dev->lastSlot];
+        if (!packed) ALLOC(packed, px * 3 + 16);
+        pack_rgb8_kernel<<<(unsigned)(((px >> 2) + 256) / 256), 256, 0, dev->copyStream>>>((const uint32_t*)src, packed, px);
+        CK(cudaGetLastError());
+        src = packed;
+    }
     CK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, dev->copyStream));
-    if (what == VKR_TARGET_RGBA8 || what == VKR_TARGET_RGBA8_GATHERED) {
+    if (what == VKR_TARGET_RGBA8 || what == VKR_TARGET_RGBA8_GATHERED || what == VKR_TARGET_RGB8) {
         // the frame FRAME_OVERLAP draws from now writes this image again: it must wait for this copy
         FrameSlot& s = dev->slots[dev->lastSlot];
         CK(cudaEventRecord(s.copied, dev->copyStream));
