@@ -150,6 +150,11 @@ typedef struct VkrConfig {
                                           frames: vkr_get_timings' VKR_T_GEOM_KERNEL is then the MEAN over the frames drawn
                                           since the previous vkr_sync (what bench.py reports the roofline from) */
 
+#define VKR_CONFIG_TRANSIENT_DEPTH 8u /* the depth / visibility attachment is not kept after the frame, like the reference's depth
+                                        image, which nothing reads once draw_geometry has ended (src/vk_engine_run.cpp:244-316):
+                                        the shading pass leaves it cleared for the next frame (no separate clear pass) and
+                                        vkr_readback(VKR_TARGET_DEPTH / VKR_TARGET_PRIMID) is refused */
+
 /* struct EngineStats — src/vk_types.h:78-83. */
 typedef struct VkrEngineStats {
     float frametime;           /* ms, device time of the last completed frame (needs VKR_CONFIG_TIMINGS) */
@@ -175,6 +180,7 @@ typedef enum VkrTarget {
 enum { VKR_T_UPLOAD = 0, VKR_T_SHADOW, VKR_T_GEOMETRY, VKR_T_SHADE, VKR_T_TRANSPARENT, VKR_T_POST, VKR_T_TOTAL,
        VKR_T_GEOM_KERNEL /* main-pass geometry kernel alone */, VKR_T_LARGE_KERNEL, VKR_T_CLEAR,
        VKR_T_SHADOW_EXCHANGE /* sharded: shadow band exchange (part of VKR_T_SHADOW) */, VKR_T_FRAME_GATHER /* sharded: image assembly */,
+       VKR_T_READBACK /* the last colour read-back's device-to-host transfer (copy stream) */,
        VKR_T_COUNT };
 
 /* init_vulkan + init_swapchain + init_shadow_resources + init_default_data

@@ -109,6 +109,20 @@ def test_gpu_submit_thread_matches_synchronous_submission(vkr_lib):
             r.draw(views[k % 6], objs, fp)
             if k >= 6:
                 out.append((r.readback(capi.TARGET_RGBA8), r.readback(capi.TARGET_PRIMID)))
+        if flags:
+            # asynchronous read-backs ride the submit thread's queue behind their frame: the caller never waits for a frame to
+            # be issued, and every landing buffer still holds exactly its own frame (both packed formats)
+            import torch
+            land = [torch.zeros((200, 320, 4), dtype=torch.uint8).pin_memory() for _ in range(6)]
+            land3 = [torch.zeros((200, 320, 3), dtype=torch.uint8).pin_memory() for _ in range(6)]
+            for k in range(6):
+                r.draw(views[k], objs, fp)
+                r.readback_async(capi.TARGET_RGBA8, land[k].data_ptr(), 320 * 200 * 4)
+                r.readback_async(capi.TARGET_RGB8, land3[k].data_ptr(), 320 * 200 * 3)
+            r.sync()
+            for k in range(6):
+                assert np.array_equal(land[k].numpy(), out[k][0]), f"asynchronously read-back frame {k} differs"
+                assert np.array_equal(land3[k].numpy(), out[k][0][..., :3]), f"asynchronously read-back RGB8 frame {k} differs"
         bad = objs.copy()
         bad["mesh"][0] = 12345
         with pytest.raises(capi.VkrError):
@@ -121,3 +135,34 @@ def test_gpu_submit_thread_matches_synchronous_submission(vkr_lib):
         r.close()
     for (a_rgba, a_prim), (b_rgba, b_prim) in zip(frames[0], frames[capi.CONFIG_SUBMIT_THREAD]):
         assert np.array_equal(a_prim, b_prim) and np.array_equal(a_rgba, b_rgba)
+
+
+def test_gpu_transient_depth_fuses_the_clear(vkr_lib):
+    """VKR_CONFIG_TRANSIENT_DEPTH: the shading pass leaves the visibility buffer cleared and the next frame skips its clear pass.
+    Frames (changing views, a changing scissor rectangle, flag switched on and off between frames) are identical to the ones
+    drawn with the separate clear; depth read-back is refused while the flag is set and correct again once it is cleared."""
+    from vk_renderer_b200 import capi
+    import scenes as sc
+    r0 = capi.Renderer(vkr_lib, "vkr", 320, 200, shadow_extent=256, flags=0)
+    r1 = capi.Renderer(vkr_lib, "vkr", 320, 200, shadow_extent=256, flags=capi.CONFIG_TRANSIENT_DEPTH)
+    sd0, objs0, fp0 = sc.SCENES["lattice"](r0)
+    sd1, objs1, fp1 = sc.SCENES["lattice"](r1)
+    v0, v1 = sc.orbit_views(r0, 5), sc.orbit_views(r1, 5)
+    rects = [(0, 0, 0, 0), (40, 30, 200, 120), (0, 0, 0, 0), (100, 0, 220, 200), (0, 50, 320, 100)]
+    for k in range(10):
+        for fp in (fp0, fp1):
+            fp.scissor[:] = rects[k % 5]
+        if k == 6:
+            r1.set_flags(0)                       # this frame starts from the cleared buffer the previous one left
+        if k == 8:
+            r1.set_flags(capi.CONFIG_TRANSIENT_DEPTH)
+        r0.draw(v0[k % 5], objs0, fp0)
+        r1.draw(v1[k % 5], objs1, fp1)
+        assert np.array_equal(r0.readback(capi.TARGET_RGBA8), r1.readback(capi.TARGET_RGBA8)), f"frame {k}"
+        if 6 <= k < 8:
+            assert np.array_equal(r0.readback(capi.TARGET_DEPTH).view(np.uint32), r1.readback(capi.TARGET_DEPTH).view(np.uint32))
+            assert np.array_equal(r0.readback(capi.TARGET_PRIMID), r1.readback(capi.TARGET_PRIMID))
+        else:
+            with pytest.raises(capi.VkrError):
+                r1.readback(capi.TARGET_DEPTH)
+    r0.close(); r1.close()

@@ -24,8 +24,9 @@ COMM_ID_BYTES = 128
 CONFIG_TIMINGS = 1
 CONFIG_TIME_GEOM_KERNEL = 2
 CONFIG_SUBMIT_THREAD = 4
+CONFIG_TRANSIENT_DEPTH = 8
 T_NAMES = ["upload", "shadow", "geometry", "shade", "transparent", "post", "total", "geom_kernel", "large_kernel", "clear",
-           "shadow_exchange", "frame_gather"]
+           "shadow_exchange", "frame_gather", "readback"]
 
 # struct Vertex (src/vk_types.h:85-91), 48 bytes
 VERTEX_DTYPE = np.dtype(

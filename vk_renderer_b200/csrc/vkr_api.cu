@@ -195,19 +195,10 @@ __device__ __forceinline__ void geometry_warp(const DChunk* __restrict__ chunk, 
     if (lane < 16) mvp[lane] = __ldg(mvps + (size_t)obj * mvpStride + lane);
     __syncwarp();
 
-    // ---- phase 0: cluster culling (every group of 8 lanes evaluates the 8 corners; all lanes end up with the result)
+    // ---- phase 0: cluster culling (lane = clip component * 8 + box corner; all lanes end up with the result)
     {
         const float4 bmin = __ldg(reinterpret_cast<const float4*>(chp + 3)), bmax = __ldg(reinterpret_cast<const float4*>(chp + 4));
-        CornerAcc a = corner_eval(mvp, bmin, bmax, lane & 7);
-#pragma unroll
-        for (int d = 1; d < 8; d <<= 1) {
-            CornerAcc b;
-            b.xmin = __shfl_xor_sync(0xFFFFFFFFu, a.xmin, d); b.xmax = __shfl_xor_sync(0xFFFFFFFFu, a.xmax, d);
-            b.ymin = __shfl_xor_sync(0xFFFFFFFFu, a.ymin, d); b.ymax = __shfl_xor_sync(0xFFFFFFFFu, a.ymax, d);
-            b.zmin = __shfl_xor_sync(0xFFFFFFFFu, a.zmin, d); b.zmax = __shfl_xor_sync(0xFFFFFFFFu, a.zmax, d);
-            b.outAll = __shfl_xor_sync(0xFFFFFFFFu, a.outAll, d); b.allFront = __shfl_xor_sync(0xFFFFFFFFu, a.allFront, d);
-            a = corner_merge(a, b);
-        }
+        const CornerAcc a = corners_warp(mvp, bmin, bmax, lane);
         const ClusterRect rect = cluster_finalize(a, rt);
         bool culled = rect.verdict == CLUSTER_CULLED;
         if (rect.verdict == CLUSTER_TEST) {
@@ -426,6 +417,11 @@ __global__ void __launch_bounds__(128, VKR_SHADE_MIN_CTAS) shade_kernel(const __
     __syncthreads();
     ShadeBuffers sb = sbIn;
     sb.srgbLut = s_lut;
+    if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x < 12 && sbIn.countersHost != nullptr) {
+        // every raster pass of the frame has ended (stream order / the shadow join): publish their counters to the host
+        const uint32_t* c = sbIn.counters[threadIdx.x >> 2];
+        sbIn.countersHost[threadIdx.x] = c ? c[threadIdx.x & 3] : 0u;
+    }
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int lx = (lane & 7) + ((warp & 1) << 3), ly = (lane >> 3) + ((warp >> 1) << 2);
     const int px = sc.sx0 + blockIdx.x * 16 + lx, py = sc.sy0 + blockIdx.y * 8 + ly;
@@ -468,12 +464,13 @@ struct VkrDevice {
     int device = 0;
     cudaStream_t stream = nullptr, copyStream = nullptr;   // frame stream; device->host copies
     cudaStream_t shadowStream = nullptr, upStream = nullptr; // shadow pass runs beside the main pass; host->device uploads
-    cudaEvent_t evShadow = nullptr;
+    cudaEvent_t evShadow = nullptr, packedEv = nullptr;
     bool ownStream = false;
     uint32_t W = 0, H = 0, S = 2048, flags = 0;
     int smCount = 148;
 
     uint64_t* vis = nullptr;
+    bool visClean = false;                 // VKR_CONFIG_TRANSIENT_DEPTH: the last frame's shading pass left `vis` cleared
     uint32_t* shadowBits = nullptr;        // the shadow map of the frame being (or last) drawn: one of shadowBuf
     uint32_t* shadowBuf[VKR_FRAME_OVERLAP] = {};   // per frame in flight: frame i+1's shadow pass overlaps frame i's shading
     uint16_t* hdr = nullptr;
@@ -506,7 +503,8 @@ struct VkrDevice {
 
     Queues q{};                         // large-triangle queue of the main pass
     Queues qShadow{};                   // ... of the shadow pass (the two passes overlap)
-    uint32_t* countersHost = nullptr;   // pinned mirror of q.counters after the last frame
+    uint32_t* transCounters = nullptr;  // counters of the transparent pass (it reuses the main pass's queues)
+    uint32_t* countersHost = nullptr;   // pinned mirror of the three passes' counters after the last frame (written by shade_kernel)
 
     FrameSlot slots[VKR_FRAME_OVERLAP];
     uint64_t frameIndex = 0;
@@ -514,14 +512,20 @@ struct VkrDevice {
     const uint2* lastChunkObj = nullptr; const DObject* lastObjects = nullptr;
     FramePlan plans[2]; int planIdx = 0;      // two: with a submit thread one is being submitted while the next is planned
     // VKR_CONFIG_SUBMIT_THREAD: vkr_draw plans the frame on the caller's thread and hands the CUDA/NCCL calls to this thread
+    // and asynchronous read-backs (vkr_readback_async) follow their frame through the same queue, so the caller never waits
+    // for a frame to be issued before it can plan the next one
     std::thread worker;
-    std::atomic<int> jobState{0};             // 0 idle, 1 posted, 2 running
+    struct Job { int kind; FramePlan* plan; size_t n; VkrTarget what; void* dst; size_t dstBytes; };   // kind 0: frame, 1: read-back
+    static const uint32_t JOBS = 4;
+    Job jobs[JOBS];
+    std::atomic<uint32_t> jobHead{0}, jobTail{0};   // single producer (the caller's thread), single consumer; head advances when a job is DONE
     std::atomic<bool> workerStop{false};
     std::mutex workerMutex; std::condition_variable workerCv;
-    FramePlan* jobPlan = nullptr; size_t jobN = 0;
     int asyncRc = 0;                          // first failure of an asynchronously submitted frame, reported by the next call
 
-    cudaEvent_t tev[13] = {nullptr};  // ... 9 transparent done; 10 shadow raster done (before the exchange); 11, 12 frame gather (gather stream)   // 0 start, 1 uploaded, 3 cleared, 4 geometry kernel, 5 large kernel, 6 shaded; 7,8 shadow pass (shadow stream)
+    cudaEvent_t tev[15] = {nullptr};  // 13, 14: around the last read-back transfer (copy stream)
+    bool rbTimed = false;
+     // ... 9 transparent done; 10 shadow raster done (before the exchange); 11, 12 frame gather (gather stream)   // 0 start, 1 uploaded, 3 cleared, 4 geometry kernel, 5 large kernel, 6 shaded; 7,8 shadow pass (shadow stream)
     bool tevValid = false, shadowTimed = false;
     float timings[VKR_T_COUNT] = {0};
     static const int KRING = 128;          // VKR_CONFIG_TIME_GEOM_KERNEL: event pairs of the last KRING frames
@@ -631,11 +635,12 @@ int vkr_create(const VkrConfig* cfg, VkrDevice** out) {
         CK(cudaSetDevice(dev->device));
         if (cfg->stream) dev->stream = (cudaStream_t)cfg->stream;
         else { CK(cudaStreamCreateWithFlags(&dev->stream, cudaStreamNonBlocking)); dev->ownStream = true; }
-        CK(cudaStreamCreateWithFlags(&dev->copyStream, cudaStreamNonBlocking));
         // the shadow stream carries the shadow exchange of a sharded frame: highest priority, so that the collective's
-        // CTAs are dispatched ahead of the main pass's thousands of queued geometry CTAs
+        // CTAs are dispatched ahead of the main pass's thousands of queued geometry CTAs; the copy stream's pack kernel likewise
         int prLo = 0, prHi = 0;
         CK(cudaDeviceGetStreamPriorityRange(&prLo, &prHi));
+        CK(cudaStreamCreateWithPriority(&dev->copyStream, cudaStreamNonBlocking, prHi));
+        CK(cudaEventCreateWithFlags(&dev->packedEv, cudaEventDisableTiming));
         CK(cudaStreamCreateWithPriority(&dev->shadowStream, cudaStreamNonBlocking, prHi));
         CK(cudaStreamCreateWithFlags(&dev->upStream, cudaStreamNonBlocking));
         CK(cudaEventCreateWithFlags(&dev->evShadow, cudaEventDisableTiming));
@@ -658,8 +663,9 @@ int vkr_create(const VkrConfig* cfg, VkrDevice** out) {
         dev->qShadow.triCap = 1u << 18; dev->qShadow.itemCap = 1u << 20;
         ALLOC(dev->qShadow.tris, sizeof(LargeTri) * dev->qShadow.triCap);
         ALLOC(dev->qShadow.items, sizeof(LargeItem) * dev->qShadow.itemCap);
-        ALLOC(dev->qShadow.counters, 32);
-        CK(cudaMallocHost(&dev->countersHost, 48));
+        ALLOC(dev->qShadow.counters, 32 * VKR_FRAME_OVERLAP);     // per frame in flight: frame i+1's shadow pass runs beside frame i's shading, which publishes frame i's
+        ALLOC(dev->transCounters, 32);
+        CK(cudaMallocHost(&dev->countersHost, 48));     // (mapped: unified addressing makes every pinned allocation device-visible)
         std::memset(dev->countersHost, 0, 48);
         for (auto& s : dev->slots) {
             CK(cudaEventCreateWithFlags(&s.uploaded, cudaEventDisableTiming));
@@ -705,8 +711,10 @@ void vkr_destroy(VkrDevice* dev) {
     if (dev->hostProf && dev->hostProfFrames) {
         const double f = 1.0 / (double)dev->hostProfFrames;
         std::fprintf(stderr, "[vkr host rank %d] vkr_draw us/frame over %llu frames: plan %.1f | upload+expand %.1f | shadow (+exchange) %.1f | "
-                     "main raster %.1f | transparent+shade %.1f | gather %.1f\n", dev->shardRank, (unsigned long long)dev->hostProfFrames,
-                     dev->hostProfUs[0] * f, dev->hostProfUs[1] * f, dev->hostProfUs[2] * f, dev->hostProfUs[3] * f, dev->hostProfUs[4] * f, dev->hostProfUs[5] * f);
+                     "main raster %.1f | transparent+shade %.1f | gather %.1f | async read-backs %.1f | caller waiting for the submit thread %.1f\n",
+                     dev->shardRank, (unsigned long long)dev->hostProfFrames,
+                     dev->hostProfUs[0] * f, dev->hostProfUs[1] * f, dev->hostProfUs[2] * f, dev->hostProfUs[3] * f, dev->hostProfUs[4] * f, dev->hostProfUs[5] * f,
+                     dev->hostProfUs[6] * f, dev->hostProfUs[7] * f);
     }
     for (auto it = dev->allocations.rbegin(); it != dev->allocations.rend(); ++it) cudaFree(*it);
     for (auto& s : dev->slots) {
@@ -727,6 +735,7 @@ void vkr_destroy(VkrDevice* dev) {
     if (dev->shadowStream) cudaStreamDestroy(dev->shadowStream);
     if (dev->upStream) cudaStreamDestroy(dev->upStream);
     if (dev->evShadow) cudaEventDestroy(dev->evShadow);
+    if (dev->packedEv) cudaEventDestroy(dev->packedEv);
     if (dev->ownStream && dev->stream) cudaStreamDestroy(dev->stream);
     delete dev;
 }
@@ -873,28 +882,43 @@ static int ensure_slot(VkrDevice* dev, FrameSlot& s, size_t bytes) {
 // ---- submit thread (VKR_CONFIG_SUBMIT_THREAD) -------------------------------------------------------------------
 static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n);
 
+extern "C" { static int readback_issue(VkrDevice* dev, VkrTarget what, void* dst, size_t dstBytes); }
+
 static void worker_main(VkrDevice* dev) {
     cudaSetDevice(dev->device);
     for (;;) {
         int spins = 0;
-        while (dev->jobState.load(std::memory_order_acquire) != 1 && !dev->workerStop.load(std::memory_order_acquire)) {
+        uint32_t head = dev->jobHead.load(std::memory_order_relaxed);
+        while (dev->jobTail.load(std::memory_order_acquire) == head && !dev->workerStop.load(std::memory_order_acquire)) {
             if (++spins < 20000) { __builtin_ia32_pause(); continue; }          // ~0.2 ms of spinning covers the gap between frames
             std::unique_lock<std::mutex> lk(dev->workerMutex);
-            dev->workerCv.wait_for(lk, std::chrono::milliseconds(2), [&] { return dev->jobState.load() == 1 || dev->workerStop.load(); });
+            dev->workerCv.wait_for(lk, std::chrono::milliseconds(2), [&] { return dev->jobTail.load() != head || dev->workerStop.load(); });
             spins = 0;
         }
-        if (dev->workerStop.load(std::memory_order_acquire) && dev->jobState.load() != 1) return;
-        dev->jobState.store(2, std::memory_order_release);
-        const int rc = submit_frame(dev, *dev->jobPlan, dev->jobN);
+        if (dev->jobTail.load(std::memory_order_acquire) == head) return;        // stop requested and nothing left to issue
+        const VkrDevice::Job job = dev->jobs[head % VkrDevice::JOBS];
+        const auto jobT = std::chrono::steady_clock::now();
+        const int rc = job.kind == 0 ? submit_frame(dev, *job.plan, job.n) : readback_issue(dev, job.what, job.dst, job.dstBytes);
+        if (job.kind == 1 && dev->hostProf && dev->frameIndex >= 16)
+            dev->hostProfUs[6] += std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - jobT).count();
         if (rc != VKR_SUCCESS && dev->asyncRc == VKR_SUCCESS) dev->asyncRc = rc;
-        dev->jobState.store(0, std::memory_order_release);
+        dev->jobHead.store(head + 1, std::memory_order_release);
     }
+}
+// Hand a job to the submit thread (blocks only while all JOBS slots are taken).
+static void post_job(VkrDevice* dev, const VkrDevice::Job& job) {
+    const uint32_t tail = dev->jobTail.load(std::memory_order_relaxed);
+    while (tail - dev->jobHead.load(std::memory_order_acquire) >= VkrDevice::JOBS) __builtin_ia32_pause();
+    dev->jobs[tail % VkrDevice::JOBS] = job;
+    dev->jobTail.store(tail + 1, std::memory_order_release);
+    dev->workerCv.notify_one();
 }
 // Wait until the submit thread has issued everything it was given; returns (and clears) a deferred failure.
 static int drain(VkrDevice* dev) {
     if (!dev->worker.joinable()) return VKR_SUCCESS;
     int spins = 0;
-    while (dev->jobState.load(std::memory_order_acquire) != 0) { if (++spins < 4000) __builtin_ia32_pause(); else std::this_thread::yield(); }
+    const uint32_t tail = dev->jobTail.load(std::memory_order_relaxed);
+    while (dev->jobHead.load(std::memory_order_acquire) != tail) { if (++spins < 4000) __builtin_ia32_pause(); else std::this_thread::yield(); }
     const int rc = dev->asyncRc;
     dev->asyncRc = VKR_SUCCESS;
     return rc;
@@ -916,11 +940,12 @@ extern "C" int vkr_draw(VkrDevice* dev, const VkrGPUSceneData* scene, const VkrR
     if (dev->hostProf && dev->frameIndex >= 16)
         dev->hostProfUs[0] += std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - hostT).count();
     if (!async) return submit_frame(dev, plan, n);
+    const auto waitT = std::chrono::steady_clock::now();
     DRAIN(dev);                                        // the previous frame is fully issued (and its failure, if any, reported here)
-    dev->jobPlan = &plan; dev->jobN = n;
+    if (dev->hostProf && dev->frameIndex >= 16)
+        dev->hostProfUs[7] += std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - waitT).count();
     dev->planIdx ^= 1;
-    dev->jobState.store(1, std::memory_order_release);
-    dev->workerCv.notify_one();
+    post_job(dev, VkrDevice::Job{0, &plan, n, VKR_TARGET_RGBA8, nullptr, 0});
     return VKR_SUCCESS;
 }
 
@@ -1018,21 +1043,26 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
         CK(cudaStreamWaitEvent(ss, slot.uploaded, 0));
         dev->shadowBits = dev->shadowBuf[slotIdx];
         if (timing) CK(cudaEventRecord(dev->tev[7], ss));
+        Queues qs = dev->qShadow;
+        qs.counters = dev->qShadow.counters + 8 * slotIdx;
         for (int layer = 0; layer < plan.shadowLayers; ++layer) {
             RasterTarget rt = plan.shadowTarget;
             rt.depthBits = dev->shadowBits + (size_t)layer * dev->S * dev->S;
             const size_t sn = (size_t)dev->S * dev->S;
             fill_u32_kernel<<<grid_for(sn / 4, 256, 2048), 256, 0, ss>>>(rt.depthBits, sn, DEPTH_ONE_BITS);
-            CK(cudaMemsetAsync(dev->qShadow.counters, 0, 32, ss));
+            if (layer == 0) CK(cudaMemsetAsync(qs.counters, 0, 32, ss));
+            else {        // the queue and its cursor start over; the overflow flag and the culled count are the frame's
+                CK(cudaMemsetAsync(qs.counters, 0, 8, ss));
+                CK(cudaMemsetAsync(qs.counters + 4, 0, 4, ss));
+            }
             dev->launches += 1;
             const unsigned shadowSlots = plan.passSlots[1 + layer];
             if (shadowSlots) {
                 geometry_kernel<true><<<(shadowSlots + GEOM_WARPS - 1) / GEOM_WARPS, GEOM_WARPS * 32, 0, ss>>>(dChunks, dPerm + (size_t)(1 + layer) * nChunks, shadowSlots,
-                                                                                                      dShadowMvp + (size_t)layer * n * 16, 16u, rt, dev->qShadow);
-                large_raster_kernel<true><<<largeGrid, 256, 0, ss>>>(rt, dev->qShadow, AlphaCtx{}, 0);
+                                                                                                      dShadowMvp + (size_t)layer * n * 16, 16u, rt, qs);
+                large_raster_kernel<true><<<largeGrid, 256, 0, ss>>>(rt, qs, AlphaCtx{}, 0);
                 dev->launches += 2;
             }
-            CK(cudaMemcpyAsync(dev->countersHost + 4, dev->qShadow.counters, 16, cudaMemcpyDeviceToHost, ss));
         }
         if (timing) CK(cudaEventRecord(dev->tev[10], ss));
         if (dev->shardRanks > 1) {      // complete every layer from the other ranks' row bands (only rows a caster can reach)
@@ -1058,9 +1088,13 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
         RasterTarget rt = plan.mainTarget;
         rt.vis = dev->vis;
         const size_t px = (size_t)dev->W * dev->H;
-        fill_u64_kernel<<<grid_for(px / 2, 256, 4096), 256, 0, st>>>(dev->vis, px, VIS_CLEAR);
+        // a transient attachment was left cleared by the previous frame's shading pass (every rasterised pixel lies in the
+        // scissor rectangle that pass walks); otherwise loadOp CLEAR is a pass of its own
+        if (!dev->visClean) {
+            fill_u64_kernel<<<grid_for(px / 2, 256, 4096), 256, 0, st>>>(dev->vis, px, VIS_CLEAR);
+            dev->launches += 1;
+        }
         CK(cudaMemsetAsync(dev->q.counters, 0, 32, st));
-        dev->launches += 1;
         if (timing) CK(cudaEventRecord(dev->tev[3], st));
         cudaEvent_t* kpair = nullptr;
         if (timeKernel) {
@@ -1084,7 +1118,6 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
             large_raster_kernel<false><<<largeGrid, 256, 0, st>>>(rt, dev->q, ax, plan.anyCutout ? 1 : 0);
             dev->launches += 2;
         } else if (timing) CK(cudaEventRecord(dev->tev[4], st));
-        CK(cudaMemcpyAsync(dev->countersHost, dev->q.counters, 16, cudaMemcpyDeviceToHost, st));
     }
     if (timing) CK(cudaEventRecord(dev->tev[5], st));
     mark(3);
@@ -1096,6 +1129,8 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
     sb.shadow = reinterpret_cast<const float*>(dev->shadowBits);
     sb.hdr = dev->hdr; sb.rgba8 = dev->rgba8[slotIdx]; sb.srgbLut = dev->lut;
     sb.accum = nullptr;
+    const bool transientDepth = (dev->flags & VKR_CONFIG_TRANSIENT_DEPTH) != 0;
+    plan.sc.clearVis = transientDepth ? 1 : 0;
     const ShadeConst& sc = plan.sc;
 
     // ---- "Transparent" draws: depth-tested against the finished opaque depth, shaded and summed (BlendSink)
@@ -1105,15 +1140,20 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
         if (!dev->accum) ALLOC(dev->accum, px * 16);
         sb.accum = dev->accum;
         CK(cudaMemsetAsync(dev->accum, 0, px * 16, st));
-        CK(cudaMemsetAsync(dev->q.counters, 0, 32, st));
+        Queues qt = dev->q;                          // the main pass's queues (drained by now), this pass's own counters
+        qt.counters = dev->transCounters;
+        CK(cudaMemsetAsync(qt.counters, 0, 32, st));
         RasterTarget rt = plan.mainTarget;
         rt.vis = dev->vis;
         geometry_transparent_kernel<<<(transChunks + GEOM_WARPS - 1) / GEOM_WARPS, GEOM_WARPS * 32, 0, st>>>(
-            dChunks, plan.opaqueClusters, transChunks, (const float*)dObjects, (uint32_t)(sizeof(DObject) / 4), rt, dev->q, sc, sb);
-        large_transparent_kernel<<<largeGrid, 256, 0, st>>>(rt, dev->q, sc, sb);
+            dChunks, plan.opaqueClusters, transChunks, (const float*)dObjects, (uint32_t)(sizeof(DObject) / 4), rt, qt, sc, sb);
+        large_transparent_kernel<<<largeGrid, 256, 0, st>>>(rt, qt, sc, sb);
         dev->launches += 2;
-        CK(cudaMemcpyAsync(dev->countersHost + 8, dev->q.counters, 16, cudaMemcpyDeviceToHost, st));
-    } else dev->countersHost[10] = 0;
+    }
+    sb.counters[0] = dev->q.counters;
+    sb.counters[1] = plan.shadowLayers ? dev->qShadow.counters + 8 * slotIdx : nullptr;
+    sb.counters[2] = transChunks ? dev->transCounters : nullptr;
+    sb.countersHost = dev->countersHost;
     if (timing) CK(cudaEventRecord(dev->tev[9], st));
 
     // ---- shading half of draw_geometry + draw_skybox + draw_background + draw_postprocess + present blit
@@ -1122,6 +1162,12 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
     {
         dim3 grid((sc.sx1 - sc.sx0 + 15) / 16, (sc.sy1 - sc.sy0 + 7) / 8);
         if (grid.x && grid.y) { shade_kernel<<<grid, 128, 0, st>>>(sc, sb); dev->launches += 1; }
+        else {                                       // nothing to shade (empty rectangle): the counters still reach the host
+            for (int k = 0; k < 3; ++k)
+                if (sb.counters[k]) CK(cudaMemcpyAsync(dev->countersHost + 4 * k, sb.counters[k], 16, cudaMemcpyDeviceToHost, st));
+                else std::memset(dev->countersHost + 4 * k, 0, 16);
+        }
+        dev->visClean = transientDepth;
     }
     if (timing) { CK(cudaEventRecord(dev->tev[6], st)); dev->tevValid = true; dev->shadowTimed = plan.shadowLayers > 0; }
     CK(cudaGetLastError());
@@ -1146,7 +1192,8 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
     dev->stats.drawcall_count = (int32_t)n;
     dev->stats.triangle_count = (int32_t)plan.totalTris;
     dev->lastOpaqueClusters = plan.passSlots[0];
-    dev->lastShadowClusters = plan.shadowLayers ? plan.passSlots[plan.shadowLayers] : 0;
+    dev->lastShadowClusters = 0;                    // over all layers, like the culled count
+    for (int layer = 0; layer < plan.shadowLayers; ++layer) dev->lastShadowClusters += plan.passSlots[1 + layer];
     return VKR_SUCCESS;
 }
 
@@ -1185,6 +1232,7 @@ int vkr_sync(VkrDevice* dev) {
         dev->timings[VKR_T_TOTAL] = el(0, 6);
         dev->timings[VKR_T_SHADOW_EXCHANGE] = dev->shadowTimed ? el(10, 8) : 0.0f;
         dev->timings[VKR_T_FRAME_GATHER] = dev->shardRanks > 1 ? el(11, 12) : 0.0f;
+        dev->timings[VKR_T_READBACK] = dev->rbTimed ? el(13, 14) : 0.0f;
         dev->stats.frametime = dev->timings[VKR_T_TOTAL];
         dev->stats.mesh_draw_time = dev->timings[VKR_T_SHADOW] + dev->timings[VKR_T_GEOMETRY];
     }
@@ -1206,14 +1254,59 @@ static int target_info(VkrDevice* dev, VkrTarget what, const void** src, size_t*
     }
 }
 
+// The copy-stream half of a read-back (colour targets and the shadow map): runs on whichever thread issues CUDA work for the
+// device, after the frame it reads (dev->lastSlot is that frame's slot).
+static int readback_issue(VkrDevice* dev, VkrTarget what, void* dst, size_t dstBytes) {
+    const void* src; size_t bytes;
+    if (target_info(dev, what, &src, &bytes) || dstBytes < bytes) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_readback: bad target");
+    // copy engine work goes to the copy stream so the next frame's kernels overlap it
+    CK(cudaStreamWaitEvent(dev->copyStream, dev->slots[dev->lastSlot].rendered, 0));
+    if ((what == VKR_TARGET_RGBA8_GATHERED || what == VKR_TARGET_RGB8) && dev->shardRanks > 1)
+        CK(cudaStreamWaitEvent(dev->copyStream, dev->gatheredEv[dev->lastSlot], 0));
+    if (what == VKR_TARGET_RGB8) {
+        const size_t px = (size_t)dev->W * dev->H;
+        uint32_t*& packed = dev->rgb8[dev->lastSlot];
+        if (!packed) ALLOC(packed, px * 3 + 16);
+        // Unsharded: packed on the frame stream, straight behind the frame's shading pass (whose wait on this slot's previous
+        // copy also protects `packed`), so the transfer starts as soon as the frame is done.  Sharded: the source is the
+        // gathered image, which the frame stream must not wait for, so the pack stays on the (high-priority) copy stream.
+        cudaStream_t ps = dev->shardRanks > 1 ? dev->copyStream : dev->stream;
+        pack_rgb8_kernel<<<(unsigned)(((px >> 2) + 256) / 256), 256, 0, ps>>>((const uint32_t*)src, packed, px);
+        CK(cudaGetLastError());
+        if (ps != dev->copyStream) {
+            CK(cudaEventRecord(dev->packedEv, ps));
+            CK(cudaStreamWaitEvent(dev->copyStream, dev->packedEv, 0));
+        }
+        src = packed;
+    }
+    const bool timing = (dev->flags & VKR_CONFIG_TIMINGS) != 0;
+    if (timing) CK(cudaEventRecord(dev->tev[13], dev->copyStream));
+    CK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, dev->copyStream));
+    if (timing) { CK(cudaEventRecord(dev->tev[14], dev->copyStream)); dev->rbTimed = true; }
+    if (what == VKR_TARGET_RGBA8 || what == VKR_TARGET_RGBA8_GATHERED || what == VKR_TARGET_RGB8) {
+        // the frame FRAME_OVERLAP draws from now writes this image again: it must wait for this copy
+        FrameSlot& s = dev->slots[dev->lastSlot];
+        CK(cudaEventRecord(s.copied, dev->copyStream));
+        s.copyPending = true;
+    }
+    return VKR_SUCCESS;
+}
+
 static int do_readback(VkrDevice* dev, VkrTarget what, void* dst, size_t dstBytes, bool sync) {
     if (!dev) return VKR_ERROR_INVALID_ARGUMENT;
-    DRAIN(dev);
     const void* src; size_t bytes;
-    if (!dst || target_info(dev, what, &src, &bytes)) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_readback: bad target");
-    if (dstBytes < bytes) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_readback: destination too small");
+    if (!dst || target_info(dev, what, &src, &bytes)) { DRAIN(dev); return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_readback: bad target"); }
+    if (dstBytes < bytes) { DRAIN(dev); return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_readback: destination too small"); }
+    const bool visTarget = what == VKR_TARGET_DEPTH || what == VKR_TARGET_PRIMID;
+    if (visTarget && (dev->flags & VKR_CONFIG_TRANSIENT_DEPTH)) { DRAIN(dev); return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_readback: the depth attachment is transient (VKR_CONFIG_TRANSIENT_DEPTH)"); }
+    if (!sync && !visTarget && dev->worker.joinable() && (dev->flags & VKR_CONFIG_SUBMIT_THREAD)) {
+        // behind the frame it reads, on the submit thread: the caller goes straight on to planning its next frame
+        post_job(dev, VkrDevice::Job{1, nullptr, 0, what, dst, dstBytes});
+        return VKR_SUCCESS;
+    }
+    DRAIN(dev);
     CK(cudaSetDevice(dev->device));
-    if (what == VKR_TARGET_DEPTH || what == VKR_TARGET_PRIMID) {
+    if (visTarget) {
         const size_t px = (size_t)dev->W * dev->H;
         if (!dev->scratch) ALLOC(dev->scratch, px * 4);
         extract_vis_kernel<<<(unsigned)((px + 255) / 256), 256, 0, dev->stream>>>(dev->vis, dev->scratch, px, what == VKR_TARGET_DEPTH ? 0 : 1,
@@ -1223,26 +1316,8 @@ static int do_readback(VkrDevice* dev, VkrTarget what, void* dst, size_t dstByte
         if (sync) return vkr_sync(dev);
         return VKR_SUCCESS;
     }
-    // copy engine work goes to the copy stream so the next frame's kernels overlap it
-    CK(cudaStreamWaitEvent(dev->copyStream, dev->slots[dev->lastSlot].rendered, 0));
-    if ((what == VKR_TARGET_RGBA8_GATHERED || what == VKR_TARGET_RGB8) && dev->shardRanks > 1)
-        CK(cudaStreamWaitEvent(dev->copyStream, dev->gatheredEv[dev->lastSlot], 0));
-    if (what == VKR_TARGET_RGB8) {
-        // packed on the copy stream too: ordered after the previous read-back of this slot's buffer, beside the next frame's kernels
-        const size_t px = (size_t)dev->W * dev->H;
-        uint32_t*& packed = dev->rgb8[dev->lastSlot];
-        if (!packed) ALLOC(packed, px * 3 + 16);
-        pack_rgb8_kernel<<<(unsigned)(((px >> 2) + 256) / 256), 256, 0, dev->copyStream>>>((const uint32_t*)src, packed, px);
-        CK(cudaGetLastError());
-        src = packed;
-    }
-    CK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, dev->copyStream));
-    if (what == VKR_TARGET_RGBA8 || what == VKR_TARGET_RGBA8_GATHERED || what == VKR_TARGET_RGB8) {
-        // the frame FRAME_OVERLAP draws from now writes this image again: it must wait for this copy
-        FrameSlot& s = dev->slots[dev->lastSlot];
-        CK(cudaEventRecord(s.copied, dev->copyStream));
-        s.copyPending = true;
-    }
+    const int rc = readback_issue(dev, what, dst, dstBytes);
+    if (rc != VKR_SUCCESS) return rc;
     if (sync) return vkr_sync(dev);
     return VKR_SUCCESS;
 }
@@ -1261,7 +1336,7 @@ int vkr_set_flags(VkrDevice* dev, uint32_t flags) {
     if (!dev) return VKR_ERROR_INVALID_ARGUMENT;
     DRAIN(dev);
     if (!(flags & VKR_CONFIG_TIMINGS)) dev->tevValid = false;
-    dev->flags = flags;
+    dev->flags = flags;      // (visClean stays as the last frame left it: a frame drawn without the flag resets it)
     return VKR_SUCCESS;
 }
 

@@ -405,6 +405,7 @@ inline std::string plan_frame(const VkrGPUSceneData* scene, const VkrRenderObjec
     sc.shadowMode = (int32_t)scene->sunlightDirection[3];
     sc.enableShadows = scene->sunlightColor[3] > 0.5f ? 1 : 0;
     sc.nobj = (uint32_t)n;
+    sc.clearVis = 0;                   // set by the device library under VKR_CONFIG_TRANSIENT_DEPTH
     sc.halfW = (float)W * 0.5f; sc.halfH = (float)H * 0.5f;
     sc.invHalfW = 1.0f / sc.halfW; sc.invHalfH = 1.0f / sc.halfH;
     {

@@ -169,6 +169,7 @@ struct ShadeConst {
     int32_t sx0, sy0, sx1, sy1;
     int32_t enableBackground, enablePostprocess, enableSkybox, fragShader;
     int32_t shadowMode, enableShadows;
+    int32_t clearVis;                  // VKR_CONFIG_TRANSIENT_DEPTH: every shaded pixel leaves VIS_CLEAR behind
     uint32_t nobj;
     float halfW, halfH;
     float invHalfW, invHalfH;
@@ -178,7 +179,7 @@ struct ShadeConst {
 };
 
 struct ShadeBuffers {
-    const uint64_t* vis;
+    uint64_t* vis;                     // read; written only to clear it (ShadeConst::clearVis)
     const DObject* objects;
     const uint2* chunkObj;             // sequence slots: seq >> 8 -> (draw, first triangle of the slot)
     const DMaterial* materials;
@@ -189,6 +190,11 @@ struct ShadeBuffers {
     uint16_t* hdr;                     // RGBA16F
     uint32_t* rgba8;
     const float* srgbLut;              // 256 floats
+    // the frame's queue counters (main, shadow, transparent pass; 4 words each, nullptr: pass not run) and their pinned host
+    // mirror, which the shading kernel fills through its mapped address: a 16-byte cudaMemcpyAsync on a render stream would
+    // queue behind the previous frame's 25 MB read-back on the device-to-host copy engine and stall the stream for it
+    const uint32_t* counters[3];
+    uint32_t* countersHost;
 };
 
 }  // namespace vkr

@@ -599,30 +599,44 @@ struct CornerAcc {
 };
 static const float CULL_EPS = 9.5367431640625e-07f;   // 2^-20
 
+// One clip-space component (0 = x, 1 = y, 2 = z, 3 = w) of one box corner and its rounding-error bound.
+VKR_HD void corner_component(const float* __restrict__ m, int comp, float px, float py, float pz, float& v, float& e) {
+    v = xfma(m[comp], px, xfma(m[4 + comp], py, xfma(m[8 + comp], pz, m[12 + comp])));
+    e = CULL_EPS * (fabsf(m[comp]) * fabsf(px) + fabsf(m[4 + comp]) * fabsf(py) + fabsf(m[8 + comp]) * fabsf(pz) + fabsf(m[12 + comp]));
+}
+// Outside tests of a component against the planes it takes part in: x, y against +-w; z against 0 and w.
+VKR_HD void corner_outside(int comp, float v, float e, float w, float ew, bool& outLo, bool& outHi) {
+    outLo = comp < 2 ? (v + w < -(e + ew)) : (v < -e);
+    outHi = v - w > (e + ew);
+}
+VKR_HD bool corner_front(float w, float ew) { return w > 2.0f * ew && w > 1e-30f; }
+// Widened NDC interval of a component of a corner with w safely > 0.
+VKR_HD void corner_ndc(float v, float e, float w, float ew, float& lo, float& hi) {
+    const float rw = 1.0f / (w - ew);             // >= 1/w_exact
+    const float n = v / w;
+    const float mg = (e + fabsf(n) * ew) * rw * 2.0f;
+    lo = n - mg; hi = n + mg;
+}
+
 VKR_HD CornerAcc corner_eval(const float* __restrict__ m, float4 bmin, float4 bmax, int corner) {
     const float px = (corner & 1) ? bmax.x : bmin.x, py = (corner & 2) ? bmax.y : bmin.y, pz = (corner & 4) ? bmax.z : bmin.z;
-    const float4 c = transform_point(m, px, py, pz);
-    const float ax = fabsf(px), ay = fabsf(py), az = fabsf(pz);
-    const float ex = CULL_EPS * (fabsf(m[0]) * ax + fabsf(m[4]) * ay + fabsf(m[8]) * az + fabsf(m[12]));
-    const float ey = CULL_EPS * (fabsf(m[1]) * ax + fabsf(m[5]) * ay + fabsf(m[9]) * az + fabsf(m[13]));
-    const float ez = CULL_EPS * (fabsf(m[2]) * ax + fabsf(m[6]) * ay + fabsf(m[10]) * az + fabsf(m[14]));
-    const float ew = CULL_EPS * (fabsf(m[3]) * ax + fabsf(m[7]) * ay + fabsf(m[11]) * az + fabsf(m[15]));
+    float v[4], e[4];
+    for (int c = 0; c < 4; ++c) corner_component(m, c, px, py, pz, v[c], e[c]);
     CornerAcc a;
     uint32_t out = 0;
-    if (c.x + c.w < -(ex + ew)) out |= 1u;
-    if (c.x - c.w > (ex + ew)) out |= 2u;
-    if (c.y + c.w < -(ey + ew)) out |= 4u;
-    if (c.y - c.w > (ey + ew)) out |= 8u;
-    if (c.z < -ez) out |= 16u;
-    if (c.z - c.w > (ez + ew)) out |= 32u;
+    for (int c = 0; c < 3; ++c) {
+        bool lo, hi;
+        corner_outside(c, v[c], e[c], v[3], e[3], lo, hi);
+        if (lo) out |= 1u << (2 * c);
+        if (hi) out |= 2u << (2 * c);
+    }
     a.outAll = out;
-    const bool front = c.w > 2.0f * ew && c.w > 1e-30f;
+    const bool front = corner_front(v[3], e[3]);
     a.allFront = front ? 1u : 0u;
     if (front) {
-        const float rw = 1.0f / (c.w - ew);           // >= 1/w_exact
-        const float xn = c.x / c.w, yn = c.y / c.w, zn = c.z / c.w;
-        const float mx = (ex + fabsf(xn) * ew) * rw * 2.0f, my = (ey + fabsf(yn) * ew) * rw * 2.0f, mz = (ez + fabsf(zn) * ew) * rw * 2.0f;
-        a.xmin = xn - mx; a.xmax = xn + mx; a.ymin = yn - my; a.ymax = yn + my; a.zmin = zn - mz; a.zmax = zn + mz;
+        corner_ndc(v[0], e[0], v[3], e[3], a.xmin, a.xmax);
+        corner_ndc(v[1], e[1], v[3], e[3], a.ymin, a.ymax);
+        corner_ndc(v[2], e[2], v[3], e[3], a.zmin, a.zmax);
     } else {
         a.xmin = a.ymin = a.zmin = 0.0f; a.xmax = a.ymax = a.zmax = 0.0f;
     }
@@ -637,6 +651,41 @@ VKR_HD CornerAcc corner_merge(const CornerAcc& a, const CornerAcc& b) {
     r.allFront = a.allFront & b.allFront;
     return r;
 }
+
+#if defined(__CUDACC__)
+// The same eight corners on the 32 lanes of a warp: lane = component * 8 + corner evaluates ONE clip-space component of ONE
+// corner (a quarter of corner_eval's arithmetic, none of it repeated across the warp); w comes from lane 24 + corner, the
+// plane tests are ballots, the NDC intervals are reduced inside each 8-lane group.  Every lane returns the merged result.
+__device__ __forceinline__ CornerAcc corners_warp(const float* __restrict__ m, float4 bmin, float4 bmax, int lane) {
+    const int comp = lane >> 3, corner = lane & 7;
+    const float px = (corner & 1) ? bmax.x : bmin.x, py = (corner & 2) ? bmax.y : bmin.y, pz = (corner & 4) ? bmax.z : bmin.z;
+    float v, e;
+    corner_component(m, comp, px, py, pz, v, e);
+    const float w = __shfl_sync(0xFFFFFFFFu, v, 24 + corner), ew = __shfl_sync(0xFFFFFFFFu, e, 24 + corner);
+    bool outLo, outHi;
+    corner_outside(comp, v, e, w, ew, outLo, outHi);
+    const uint32_t bl = __ballot_sync(0xFFFFFFFFu, outLo) & 0x00FFFFFFu, bh = __ballot_sync(0xFFFFFFFFu, outHi) & 0x00FFFFFFu;
+    const uint32_t bf = __ballot_sync(0xFFFFFFFFu, corner_front(w, ew));
+    float lo, hi;
+    corner_ndc(v, e, w, ew, lo, hi);
+#pragma unroll
+    for (int d = 1; d < 8; d <<= 1) {
+        lo = fminf(lo, __shfl_xor_sync(0xFFFFFFFFu, lo, d));
+        hi = fmaxf(hi, __shfl_xor_sync(0xFFFFFFFFu, hi, d));
+    }
+    CornerAcc a;
+    a.xmin = __shfl_sync(0xFFFFFFFFu, lo, 0); a.xmax = __shfl_sync(0xFFFFFFFFu, hi, 0);
+    a.ymin = __shfl_sync(0xFFFFFFFFu, lo, 8); a.ymax = __shfl_sync(0xFFFFFFFFu, hi, 8);
+    a.zmin = __shfl_sync(0xFFFFFFFFu, lo, 16); a.zmax = __shfl_sync(0xFFFFFFFFu, hi, 16);
+    // a plane culls the box when all eight corners are outside it: a full byte in one of the ballots
+    uint32_t all = 0;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) all |= (uint32_t)(((bl >> (8 * c)) & 0xFFu) == 0xFFu) | (uint32_t)(((bh >> (8 * c)) & 0xFFu) == 0xFFu);
+    a.outAll = all;
+    a.allFront = (bf >> 24) == 0xFFu ? 1u : 0u;
+    return a;
+}
+#endif
 
 static const int CLUSTER_DRAW = 1, CLUSTER_CULLED = 0, CLUSTER_TEST = 2;
 static const int OCC_MAX_PIXELS = 1024;      // occlusion test only when the rectangle is at most this many pixels

@@ -134,6 +134,11 @@ VKR_HD float lod_from_rho2(float rho2, int levels) {
     return fminf(fmaxf(lambda, 0.0f), (float)(levels - 1));
 }
 
+// texture2d reads its derivative arguments only for a slot with a mip chain (see the early returns below)
+VKR_HD bool texture_has_mips(const ShadeBuffers& sb, int id) {
+    return id >= 0 && id < VKR_MAX_BINDLESS && sb.textures[id].levels > 1u;
+}
+
 VKR_HD float4 texture2d(const ShadeBuffers& sb, int id, float u, float v, float dudx, float dvdx, float dudy, float dvdy) {
     if (id < 0 || id >= VKR_MAX_BINDLESS) return make_float4(0, 0, 0, 1);
     const DTexture& t = sb.textures[id];
@@ -419,12 +424,18 @@ VKR_HD void fetch_fragment(const ShadeConst& sc, const ShadeBuffers& sb, uint32_
     const float4 p0 = VKR_LDG(o.pos + i0), p1 = VKR_LDG(o.pos + i1), p2 = VKR_LDG(o.pos + i2);
     float4 c[3] = {xform(o.mvp, p0), xform(o.mvp, p1), xform(o.mvp, p2)};
     const float cx = (float)px + 0.5f, cy = (float)py + 0.5f;
-    const float ox = (px & 1) ? -1.0f : 1.0f, oy = (py & 1) ? -1.0f : 1.0f;
     const float ihw = sc.invHalfW, ihh = sc.invHalfH;
-    float b[3], bx[3], by[3];
+    float b[3], bx[3] = {0.0f, 0.0f, 0.0f}, by[3] = {0.0f, 0.0f, 0.0f};
     bary_at(c, (cx - sc.halfW) * ihw, (cy - sc.halfH) * ihh, b);
-    bary_at(c, (cx + ox - sc.halfW) * ihw, (cy - sc.halfH) * ihh, bx);
-    bary_at(c, (cx - sc.halfW) * ihw, (cy + oy - sc.halfH) * ihh, by);
+    // the uv derivatives only select a mip level: materials whose textures have a single level (every untextured material
+    // samples the engine's 1x1 defaults) skip the two neighbour evaluations
+    const float ox = (px & 1) ? -1.0f : 1.0f, oy = (py & 1) ? -1.0f : 1.0f;
+    const DMaterial& mat = sb.materials[material];
+    const bool lod = texture_has_mips(sb, mat.albedoID) || texture_has_mips(sb, mat.metalRoughID);
+    if (lod) {
+        bary_at(c, (cx + ox - sc.halfW) * ihw, (cy - sc.halfH) * ihh, bx);
+        bary_at(c, (cx - sc.halfW) * ihw, (cy + oy - sc.halfH) * ihh, by);
+    }
     const float4 a0 = VKR_LDG(o.attrA + i0), a1 = VKR_LDG(o.attrA + i1), a2 = VKR_LDG(o.attrA + i2);
     const float4 c0 = VKR_LDG(o.attrB + i0), c1 = VKR_LDG(o.attrB + i1), c2 = VKR_LDG(o.attrB + i2);
     f3 nobj = {b[0] * a0.x + b[1] * a1.x + b[2] * a2.x, b[0] * a0.y + b[1] * a1.y + b[2] * a2.y, b[0] * a0.z + b[1] * a1.z + b[2] * a2.z};
@@ -436,8 +447,8 @@ VKR_HD void fetch_fragment(const ShadeConst& sc, const ShadeBuffers& sb, uint32_
     fr.v = b[0] * c0.w + b[1] * c1.w + b[2] * c2.w;
     float ux = bx[0] * a0.w + bx[1] * a1.w + bx[2] * a2.w, vx = bx[0] * c0.w + bx[1] * c1.w + bx[2] * c2.w;
     float uy = by[0] * a0.w + by[1] * a1.w + by[2] * a2.w, vy = by[0] * c0.w + by[1] * c1.w + by[2] * c2.w;
-    fr.dudx = (ux - fr.u) * ox; fr.dvdx = (vx - fr.v) * ox;
-    fr.dudy = (uy - fr.u) * oy; fr.dvdy = (vy - fr.v) * oy;
+    fr.dudx = lod ? (ux - fr.u) * ox : 0.0f; fr.dvdx = lod ? (vx - fr.v) * ox : 0.0f;
+    fr.dudy = lod ? (uy - fr.u) * oy : 0.0f; fr.dvdy = lod ? (vy - fr.v) * oy : 0.0f;
     float4 pobj = make_float4(b[0] * p0.x + b[1] * p1.x + b[2] * p2.x, b[0] * p0.y + b[1] * p1.y + b[2] * p2.y,
                               b[0] * p0.z + b[1] * p1.z + b[2] * p2.z, 1.0f);
     float4 pw = xform(wm, pobj);
@@ -533,6 +544,10 @@ VKR_HD void shade_pixel(const ShadeConst& sc, const ShadeBuffers& sb, int px, in
     h[0] = f2h_bits(r); h[1] = f2h_bits(g); h[2] = f2h_bits(b); h[3] = f2h_bits(a);
 #endif
     sb.rgba8[pix] = unorm8_fast(r) | (unorm8_fast(g) << 8) | (unorm8_fast(b) << 16) | (unorm8_fast(a) << 24);
+    // a transient attachment: this is the next frame's clear.  Issued with the other stores, long after the key arrived — a
+    // store right behind the load of the same address waits for that load (a DRAM round trip) with the warp's later loads
+    // queued behind it, which made the kernel 3.6x slower (gpurun_out ab_z2)
+    if (sc.clearVis) sb.vis[pix] = VIS_CLEAR;
 }
 
 }  // namespace vkr
