@@ -106,7 +106,8 @@ typedef struct VkrComputePushConstants {
 
 typedef enum VkrFormat {
     VKR_FORMAT_R8G8B8A8_UNORM = 0,
-    VKR_FORMAT_R8G8B8A8_SRGB = 1
+    VKR_FORMAT_R8G8B8A8_SRGB = 1,
+    VKR_FORMAT_R16G16B16A16_SFLOAT = 2   /* cube maps only (vkr_set_cubemap_levels): the engine's skybox asset is an RGBA16F KTX file */
 } VkrFormat;
 
 typedef enum VkrSampler {
@@ -206,6 +207,13 @@ int vkr_update_bindless_texture(VkrDevice* dev, int index, VkrImage image, VkrSa
  * faces in Vulkan layer order +X,-X,+Y,-Y,+Z,-Z, each width*height*4 bytes. */
 int vkr_set_cubemap(VkrDevice* dev, const void* const faces[6], uint32_t width, uint32_t height,
                     VkrFormat format, int mipmapped);
+
+/* load_cubemap with the file's own mip chain: ktxTexture_VkUploadEx uploads every level stored in the KTX file and the
+ * image view covers vkTexture.levelCount of them (src/vk_loader.cpp:533-553) — no mip generation.
+ * levels[level * 6 + face]: face order as above, level l is max(1, width >> l) x max(1, height >> l) texels of
+ * 4 bytes (UNORM / SRGB) or 8 bytes (R16G16B16A16_SFLOAT); 1 <= levelCount <= 16. */
+int vkr_set_cubemap_levels(VkrDevice* dev, const void* const* levels, uint32_t width, uint32_t height, uint32_t levelCount,
+                           VkrFormat format);
 
 /* MaterialSystem::build_instance — src/vk_materials.cpp:60-85. */
 int vkr_build_material(VkrDevice* dev, const VkrMaterialConstants* params, VkrMaterialPass pass,

@@ -193,6 +193,12 @@ struct Mesh { std::vector<VkrVertex> v; std::vector<uint32_t> idx; };
 struct Material { VkrMaterialConstants c; int pass; };
 
 inline vec4 fetch_texel(const Image& im, int level, int x, int y) {
+    if (im.format == VKR_FORMAT_R16G16B16A16_SFLOAT) {          // cube maps loaded from an RGBA16F KTX file
+        const uint8_t* q = &im.mips[level][((size_t)y * im.w[level] + x) * 8];
+        uint16_t hv[4];
+        std::memcpy(hv, q, 8);
+        return {f16_to_f32(hv[0]), f16_to_f32(hv[1]), f16_to_f32(hv[2]), f16_to_f32(hv[3])};
+    }
     const uint8_t* p = &im.mips[level][((size_t)y * im.w[level] + x) * 4];
     if (im.format == VKR_FORMAT_R8G8B8A8_SRGB)
         return {g_srgb_lut[p[0]], g_srgb_lut[p[1]], g_srgb_lut[p[2]], p[3] / 255.0f};
@@ -1113,6 +1119,25 @@ int ork_set_cubemap(OrkDevice* d, const void* const faces[6], uint32_t w, uint32
         im.w.push_back((int)w); im.h.push_back((int)h);
         im.mips.emplace_back((const uint8_t*)faces[f], (const uint8_t*)faces[f] + (size_t)w * h * 4);
         if (mipmapped) build_mips(im);
+        d->cube[f] = std::move(im);
+    }
+    d->haveCube = true;
+    return VKR_SUCCESS;
+}
+// load_cubemap: every level comes from the KTX file (ktxTexture_VkUploadEx, src/vk_loader.cpp:533-536); no mip generation.
+int ork_set_cubemap_levels(OrkDevice* d, const void* const* levels, uint32_t w, uint32_t h, uint32_t levelCount, VkrFormat fmt) {
+    if (!d || !levels || w == 0 || h == 0 || levelCount == 0 || levelCount > 16) return VKR_ERROR_INVALID_ARGUMENT;
+    const size_t bpt = fmt == VKR_FORMAT_R16G16B16A16_SFLOAT ? 8 : 4;
+    for (int f = 0; f < 6; ++f) {
+        Image im;
+        im.format = fmt;
+        for (uint32_t l = 0; l < levelCount; ++l) {
+            const int lw = (int)std::max(1u, w >> l), lh = (int)std::max(1u, h >> l);
+            const uint8_t* src = (const uint8_t*)levels[(size_t)l * 6 + f];
+            if (!src) return VKR_ERROR_INVALID_ARGUMENT;
+            im.w.push_back(lw); im.h.push_back(lh);
+            im.mips.emplace_back(src, src + (size_t)lw * lh * bpt);
+        }
         d->cube[f] = std::move(im);
     }
     d->haveCube = true;

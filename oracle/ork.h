@@ -37,6 +37,8 @@ int ork_create_image(OrkDevice* dev, const void* rgba8, uint32_t width, uint32_t
 int ork_update_bindless_texture(OrkDevice* dev, int index, VkrImage image, VkrSampler sampler);
 int ork_set_cubemap(OrkDevice* dev, const void* const faces[6], uint32_t width, uint32_t height,
                     VkrFormat format, int mipmapped);
+int ork_set_cubemap_levels(OrkDevice* dev, const void* const* levels, uint32_t width, uint32_t height, uint32_t levelCount,
+                           VkrFormat format);
 int ork_build_material(OrkDevice* dev, const VkrMaterialConstants* params, VkrMaterialPass pass,
                        VkrMaterial* out);
 int ork_draw(OrkDevice* dev, const VkrGPUSceneData* scene, const VkrRenderObject* objects,

@@ -189,6 +189,24 @@ int emu_set_cubemap(EmuDevice* d, const void* const faces[6], uint32_t w, uint32
     d->haveCube = true;
     return 0;
 }
+int emu_set_cubemap_levels(EmuDevice* d, const void* const* levels, uint32_t w, uint32_t h, uint32_t levelCount, int fmt) {
+    const size_t bpt = fmt == 2 ? 8 : 4;          // vkr_set_cubemap_levels: the file's own levels, 4- or 8-byte texels
+    for (int f = 0; f < 6; ++f) {
+        EmuImage* im = new EmuImage();
+        im->w = w; im->h = h; im->levels = levelCount; im->format = fmt; im->cutout = false;
+        size_t total = 0;
+        for (uint32_t l = 0; l < levelCount; ++l) { im->mipOffset[l] = (uint32_t)total; total += (size_t)std::max(1u, w >> l) * std::max(1u, h >> l); }
+        im->data.resize(total * bpt / 4);
+        for (uint32_t l = 0; l < levelCount; ++l)
+            std::memcpy((char*)im->data.data() + (size_t)im->mipOffset[l] * bpt, levels[(size_t)l * 6 + f],
+                        (size_t)std::max(1u, w >> l) * std::max(1u, h >> l) * bpt);
+        d->images.push_back(im);
+        d->cube[f] = make_tex(im, 1);
+        if (fmt == 2) d->cube[f].flags |= 8u;
+    }
+    d->haveCube = true;
+    return 0;
+}
 int emu_build_material(EmuDevice* d, const VkrMaterialConstants* p, int pass, uint32_t* out) {
     DMaterial m;
     std::memcpy(m.colorFactors, p->colorFactors, 16);

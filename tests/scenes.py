@@ -33,7 +33,12 @@ def basic(r, shadow_mode=1, shadows=True, post=True, skybox=True, frag=capi.FRAG
     r.update_bindless_texture(2, tex, capi.SAMPLER_LINEAR)
     tex2 = r.create_image(mg.checker_texture(96, 6, seed=3), capi.FORMAT_UNORM, True)   # npot, UNORM, NEAREST
     r.update_bindless_texture(5, tex2, capi.SAMPLER_NEAREST)
-    if skybox:
+    if skybox == "hdr":     # the engine's real skybox asset is an RGBA16F KTX cube with its own mip chain (load_cubemap)
+        r.set_cubemap_levels(mg.sky_levels_f16(32, 4), capi.FORMAT_RGBA16F)
+    elif skybox == "levels8":
+        r.set_cubemap_levels([[f.astype(np.float32) * 255.0 / max(1.0, float(f.max())) for f in lv] for lv in mg.sky_levels_f16(32, 6)],
+                             capi.FORMAT_SRGB)
+    elif skybox:
         r.set_cubemap(mg.sky_faces(64))
     m_red = r.build_material((1, 0.3, 0.3, 1), 0.0, 0.6)
     m_metal = r.build_material((0.9, 0.8, 0.4, 1), 1.0, 0.5)
@@ -49,7 +54,7 @@ def basic(r, shadow_mode=1, shadows=True, post=True, skybox=True, frag=capi.FRAG
     sd = capi.make_scene_data(view, proj, lights, shadow_mode=shadow_mode, enable_shadows=shadows,
                               cascade_distances=(6.0, 12.0, 20.0, 100.0))
     fp = capi.default_frame_params(enableShadows=int(shadows), shadowMode=shadow_mode, enablePostprocess=int(post),
-                                   enableSkybox=int(skybox), fragShader=frag, enableBackground=int(background))
+                                   enableSkybox=int(bool(skybox)), fragShader=frag, enableBackground=int(background))
     return sd, np.array(objs), fp
 
 
@@ -313,6 +318,8 @@ SCENES = {
     "basic_pcss": lambda r: basic(r, 2),
     "basic_csm": lambda r: basic(r, 3),
     "basic_lambert_noshadow": lambda r: basic(r, 0, shadows=False, post=False, skybox=False, frag=capi.FRAG_LAMBERT),
+    "basic_hdr_sky": lambda r: basic(r, 1, skybox="hdr"),
+    "basic_sky_levels8": lambda r: basic(r, 1, skybox="levels8", post=False),
     "basic_background": lambda r: basic(r, 1, skybox=False, background=True, post=False),
     "edge_cases": edge_cases,
     "clipping": clipping,

@@ -15,7 +15,7 @@ MAX_BINDLESS = 4096
 
 SUCCESS = 0
 ERROR_INVALID_ARGUMENT, ERROR_OUT_OF_MEMORY, ERROR_CUDA, ERROR_NO_DEVICE, ERROR_CAPACITY = -1, -2, -3, -4, -5
-FORMAT_UNORM, FORMAT_SRGB = 0, 1
+FORMAT_UNORM, FORMAT_SRGB, FORMAT_RGBA16F = 0, 1, 2
 SAMPLER_NEAREST, SAMPLER_LINEAR = 0, 1
 PASS_MAIN_COLOR, PASS_TRANSPARENT, PASS_OTHER = 0, 1, 2
 FRAG_PBR, FRAG_LAMBERT = 0, 1
@@ -115,7 +115,7 @@ class EngineStats(C.Structure):
 
 # every symbol include/vkr.h declares (tests check the library exports them all)
 VKR_SYMBOLS = [
-    "create", "destroy", "upload_mesh", "create_image", "update_bindless_texture", "set_cubemap",
+    "create", "destroy", "upload_mesh", "create_image", "update_bindless_texture", "set_cubemap", "set_cubemap_levels",
     "build_material", "draw", "readback", "readback_async", "sync", "stats", "get_timings",
     "set_flags", "device_ptr", "launch_count", "upload_bytes", "cull_stats", "set_shadow_exchange", "comm_unique_id", "shard_init", "last_error", "version",
 ]
@@ -196,6 +196,7 @@ class Renderer:
             "create_image": ([p, p, C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.POINTER(C.c_uint32)], C.c_int),
             "update_bindless_texture": ([p, C.c_int, C.c_uint32, C.c_int], C.c_int),
             "set_cubemap": ([p, C.POINTER(p), C.c_uint32, C.c_uint32, C.c_int, C.c_int], C.c_int),
+            "set_cubemap_levels": ([p, C.POINTER(p), C.c_uint32, C.c_uint32, C.c_uint32, C.c_int], C.c_int),
             "build_material": ([p, C.POINTER(MaterialConstants), C.c_int, C.POINTER(C.c_uint32)], C.c_int),
             "draw": ([p, C.POINTER(GPUSceneData), p, C.c_size_t, C.POINTER(FrameParams)], C.c_int),
             "readback": ([p, C.c_int, p, C.c_size_t], C.c_int),
@@ -262,6 +263,15 @@ class Renderer:
         h, w = fs[0].shape[:2]
         arr = (C.c_void_p * 6)(*[f.ctypes.data for f in fs])
         self._check(self._f("set_cubemap")(self.dev, arr, w, h, fmt, int(mipmapped)))
+
+    def set_cubemap_levels(self, levels, fmt: int):
+        """levels[l][f]: face f (+X,-X,+Y,-Y,+Z,-Z) of mip level l, (h, w, 4) uint8 (UNORM / SRGB) or float16
+        (FORMAT_RGBA16F): the cube map with the file's own mip chain (load_cubemap, src/vk_loader.cpp:521-558)."""
+        dt = np.float16 if fmt == FORMAT_RGBA16F else np.uint8
+        keep = [[np.ascontiguousarray(f, dtype=dt) for f in lv] for lv in levels]
+        h, w = keep[0][0].shape[:2]
+        arr = (C.c_void_p * (6 * len(keep)))(*[f.ctypes.data for lv in keep for f in lv])
+        self._check(self._f("set_cubemap_levels")(self.dev, arr, w, h, len(keep), fmt))
 
     def build_material(self, color=(1, 1, 1, 1), metallic=1.0, roughness=1.0, albedo_id=0, normal_id=1,
                        metal_rough_id=0, pass_type=PASS_MAIN_COLOR) -> int:

@@ -22,6 +22,7 @@ static void usage() {
         "  --shadows 0|1         _enableShadows          --shadow-mode 0..3   hard / PCF / PCSS / CSM\n"
         "  --background 0|1      _enableBackground       --postprocess 0|1    _enablePostprocess\n"
         "  --lambert             mesh.frag instead of mesh_pbr.frag\n"
+        "  --cubemap FILE.ktx    skybox cube map (KTX 1.1 / 2.0; RGBA8, sRGB8_A8 or RGBA16F), as load_cubemap\n"
         "  --camera X,Y,Z[,PITCH,YAW]    --sun X,Y,Z    --ambient R,G,B\n"
         "  --frames N            frames to render (default 1; stats are of the last one)\n"
         "  --device N            CUDA device ordinal\n"
@@ -35,7 +36,7 @@ static std::vector<float> floats(const char* s) {
 }
 
 int main(int argc, char** argv) {
-    std::string gltf, out;
+    std::string gltf, out, cubemap;
     int config = 0, frames = 1, device = 0, shadows = -1, shadowMode = -1, background = -1, post = -1;
     bool lambert = false;
     uint32_t W = 1280, H = 720, S = 2048;
@@ -53,6 +54,7 @@ int main(int argc, char** argv) {
         else if (a == "--background") background = std::atoi(next());
         else if (a == "--postprocess") post = std::atoi(next());
         else if (a == "--lambert") lambert = true;
+        else if (a == "--cubemap") cubemap = next();
         else if (a == "--camera") cam = floats(next());
         else if (a == "--sun") sun = floats(next());
         else if (a == "--ambient") ambient = floats(next());
@@ -80,6 +82,10 @@ int main(int argc, char** argv) {
     } else {
         tris = load_procedural(&engine, config, 0xB2000000u + (uint32_t)config);
         if (!tris) { std::fprintf(stderr, "unknown config %d\n", config); return 1; }
+    }
+    if (!cubemap.empty()) {      // a failed load leaves the scene without a skybox, as in the reference
+        std::string why;
+        if (!engine.load_cubemap(cubemap.c_str(), &why)) std::fprintf(stderr, "load_cubemap: %s\n", why.c_str());
     }
     if (shadows >= 0) engine._enableShadows = shadows != 0;
     if (shadowMode >= 0) engine._shadowMode = shadowMode;

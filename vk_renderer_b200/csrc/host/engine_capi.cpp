@@ -5,11 +5,13 @@
 
 #include "vk_engine.h"
 #include "vk_gltf.h"
+#include "vk_ktx.h"
 #include "vk_loader.h"
 
 const VkrApi& libvkr_api() {
     static const VkrApi api = {vkr_create, vkr_destroy, vkr_upload_mesh, vkr_create_image, vkr_update_bindless_texture,
-                               vkr_set_cubemap, vkr_build_material, vkr_draw, vkr_readback, vkr_readback_async, vkr_sync};
+                               vkr_set_cubemap, vkr_build_material, vkr_draw, vkr_readback, vkr_readback_async, vkr_sync,
+                               vkr_set_cubemap_levels};
     return api;
 }
 
@@ -45,6 +47,31 @@ int64_t vke_load_gltf(VulkanEngine* e, const char* name, const char* fileName, c
     int64_t tris = 0;
     for (const RenderObject& o : all) tris += o.indexCount / 3;
     return tris;
+}
+// load_cubemap("../../assets/pisa_cube.ktx", _skyboxImage) of init_scene (src/vk_engine_init.cpp:677).  0 on success, -1 with the reason.
+int vke_load_cubemap(VulkanEngine* e, const char* fileName, char* err, size_t errBytes) {
+    std::string why;
+    if (e->load_cubemap(fileName, &why)) return 0;
+    if (err && errBytes) { std::strncpy(err, why.c_str(), errBytes - 1); err[errBytes - 1] = 0; }
+    return -1;
+}
+// Test hook: decode a KTX cube held in memory.  info = {width, height, levels, format, generateMips}; when `out` is large enough
+// (all levels, level-major then face) the texels are copied there.  0 on success, -1 with the reason.
+int vke_decode_ktx(const unsigned char* data, size_t size, uint32_t info[5], unsigned char* out, size_t outBytes, char* err, size_t errBytes) {
+    KtxCube cube;
+    std::string why;
+    if (!decode_ktx_cube(data, size, cube, &why)) {
+        if (err && errBytes) { std::strncpy(err, why.c_str(), errBytes - 1); err[errBytes - 1] = 0; }
+        return -1;
+    }
+    info[0] = cube.width; info[1] = cube.height; info[2] = cube.levels; info[3] = (uint32_t)cube.format; info[4] = cube.generateMips ? 1u : 0u;
+    size_t total = 0;
+    for (const auto& img : cube.images) total += img.size();
+    if (out && outBytes >= total) {
+        size_t off = 0;
+        for (const auto& img : cube.images) { std::memcpy(out + off, img.data(), img.size()); off += img.size(); }
+    }
+    return 0;
 }
 // The flattened scene after update_scene: object i's mesh/material handles, world matrix, index range and its material constants.
 int vke_render_object(VulkanEngine* e, size_t i, VkrRenderObject* out, MaterialConstants* params, int* passType) {

@@ -1,6 +1,7 @@
 // vk_engine.cpp — per-frame host path of the engine (scene update, light matrices, draw) on libvkr.
 // Follows src/vk_engine_run.cpp; citations on each function.
 #include "vk_engine.h"
+#include "vk_ktx.h"
 
 #include <algorithm>
 #include <cmath>
@@ -79,6 +80,35 @@ int VulkanEngine::add_texture(const void* rgba8, uint32_t w, uint32_t h) {
 }
 void VulkanEngine::set_cubemap(const void* const faces[6], uint32_t w, uint32_t h) {
     if (_api.set_cubemap(_vkr, faces, w, h, VKR_FORMAT_R8G8B8A8_SRGB, 1) == VKR_SUCCESS) _hasSkybox = true;
+}
+// load_cubemap (src/vk_loader.cpp:521-558): the KTX file's faces and mip levels become the skybox image as they are.  On
+// failure the reference prints a message and carries on without a skybox; so does this (the reason goes to *error).
+bool VulkanEngine::load_cubemap(const char* filename, std::string* error) {
+    KtxCube cube;
+    std::string why;
+    if (!load_ktx_cube(filename ? filename : "", cube, &why)) {
+        std::fprintf(stderr, "failed to load ktx texture image! (%s)\n", why.c_str());
+        if (error) *error = why;
+        return false;
+    }
+    int rc;
+    if (cube.generateMips && cube.format != VKR_FORMAT_R16G16B16A16_SFLOAT) {
+        const void* faces[6];
+        for (int f = 0; f < 6; ++f) faces[f] = cube.images[f].data();
+        rc = _api.set_cubemap(_vkr, faces, cube.width, cube.height, cube.format, 1);
+    } else {
+        if (!_api.set_cubemap_levels) { if (error) *error = "backend has no set_cubemap_levels"; return false; }
+        std::vector<const void*> ptrs;
+        for (const auto& img : cube.images) ptrs.push_back(img.data());
+        rc = _api.set_cubemap_levels(_vkr, ptrs.data(), cube.width, cube.height, cube.levels, cube.format);
+    }
+    if (rc != VKR_SUCCESS) {
+        std::fprintf(stderr, "failed to upload ktx texture!\n");
+        if (error) *error = "upload failed";
+        return false;
+    }
+    _hasSkybox = true;
+    return true;
 }
 std::shared_ptr<MeshAsset> VulkanEngine::add_mesh(const std::string& name, std::span<uint32_t> indices, std::span<Vertex> vertices,
                                                    const std::vector<GeoSurface>& surfaces) {

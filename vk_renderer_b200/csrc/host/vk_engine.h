@@ -28,6 +28,7 @@ struct VkrApi {
     int (*readback)(VkrDevice*, VkrTarget, void*, size_t);
     int (*readback_async)(VkrDevice*, VkrTarget, void*, size_t);   // may be null
     int (*sync)(VkrDevice*);                                        // may be null
+    int (*set_cubemap_levels)(VkrDevice*, const void* const*, uint32_t, uint32_t, uint32_t, VkrFormat);   // may be null
 };
 const VkrApi& libvkr_api();
 
@@ -92,6 +93,7 @@ public:
     void update_bindless_texture(int index, VkrImage image, VkrSampler sampler);
     int add_texture(const void* rgba8, uint32_t w, uint32_t h);     // load_gltf's image loop (:275-329)
     void set_cubemap(const void* const faces[6], uint32_t w, uint32_t h);
+    bool load_cubemap(const char* filename, std::string* error = nullptr);   // src/vk_loader.cpp:521-558 (KTX 1.1 / 2.0)
     std::shared_ptr<MeshAsset> add_mesh(const std::string& name, std::span<uint32_t> indices, std::span<Vertex> vertices,
                                         const std::vector<GeoSurface>& surfaces);   // load_gltf's mesh loop (:382-466)
 

@@ -835,7 +835,8 @@ int vkr_update_bindless_texture(VkrDevice* dev, int index, VkrImage image, VkrSa
 int vkr_set_cubemap(VkrDevice* dev, const void* const faces[6], uint32_t w, uint32_t h, VkrFormat fmt, int mipmapped) {
     if (!dev) return VKR_ERROR_INVALID_ARGUMENT;
     DRAIN(dev);
-    if (!faces || w == 0 || h == 0) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_set_cubemap: bad arguments");
+    if (!faces || w == 0 || h == 0 || (fmt != VKR_FORMAT_R8G8B8A8_UNORM && fmt != VKR_FORMAT_R8G8B8A8_SRGB))
+        return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_set_cubemap: bad arguments");
     CK(cudaSetDevice(dev->device));
     DTexture t[6];
     for (int f = 0; f < 6; ++f) {
@@ -847,6 +848,40 @@ int vkr_set_cubemap(VkrDevice* dev, const void* const faces[6], uint32_t w, uint
     }
     CK(cudaMemcpyAsync(dev->cubeDev, t, sizeof(t), cudaMemcpyHostToDevice, dev->stream));
     CK(cudaStreamSynchronize(dev->stream));
+    dev->haveCube = true;
+    return VKR_SUCCESS;
+}
+
+int vkr_set_cubemap_levels(VkrDevice* dev, const void* const* levels, uint32_t w, uint32_t h, uint32_t levelCount, VkrFormat fmt) {
+    if (!dev) return VKR_ERROR_INVALID_ARGUMENT;
+    DRAIN(dev);
+    if (!levels || w == 0 || h == 0 || w > 16384 || h > 16384 || levelCount == 0 || levelCount > 16 ||
+        (fmt != VKR_FORMAT_R8G8B8A8_UNORM && fmt != VKR_FORMAT_R8G8B8A8_SRGB && fmt != VKR_FORMAT_R16G16B16A16_SFLOAT))
+        return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_set_cubemap_levels: bad arguments");
+    for (uint32_t i = 0; i < levelCount * 6; ++i)
+        if (!levels[i]) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_set_cubemap_levels: null level");
+    CK(cudaSetDevice(dev->device));
+    const size_t bpt = fmt == VKR_FORMAT_R16G16B16A16_SFLOAT ? 8 : 4;
+    DTexture t[6];
+    for (int f = 0; f < 6; ++f) {
+        DTexture& d = t[f];
+        d = DTexture{};
+        size_t total = 0;
+        for (uint32_t l = 0; l < levelCount; ++l) {
+            d.mipOffset[l] = (uint32_t)total;
+            total += (size_t)std::max(1u, w >> l) * std::max(1u, h >> l);
+        }
+        char* data = nullptr;
+        ALLOC(data, total * bpt);
+        for (uint32_t l = 0; l < levelCount; ++l)
+            CK(cudaMemcpyAsync(data + (size_t)d.mipOffset[l] * bpt, levels[(size_t)l * 6 + f],
+                               (size_t)std::max(1u, w >> l) * std::max(1u, h >> l) * bpt, cudaMemcpyHostToDevice, dev->stream));
+        d.data = reinterpret_cast<const uchar4*>(data);
+        d.w = w; d.h = h; d.levels = levelCount;
+        d.flags = (fmt == VKR_FORMAT_R8G8B8A8_SRGB ? 1u : 0u) | 2u | (fmt == VKR_FORMAT_R16G16B16A16_SFLOAT ? 8u : 0u);
+    }
+    CK(cudaMemcpyAsync(dev->cubeDev, t, sizeof(t), cudaMemcpyHostToDevice, dev->stream));
+    CK(cudaStreamSynchronize(dev->stream));      // the caller's arrays and `t` may go away
     dev->haveCube = true;
     return VKR_SUCCESS;
 }

@@ -126,7 +126,8 @@ struct DMaterial {
 struct DTexture {             // one bindless slot (combined image sampler)
     const uchar4* data;       // mip chain, level l at data + mipOffset[l]
     uint32_t w, h, levels;
-    uint32_t flags;           // bit0: sRGB, bit1: LINEAR sampler (else NEAREST), bit2: has alpha < 0.5 somewhere
+    uint32_t flags;           // bit0: sRGB, bit1: LINEAR sampler (else NEAREST), bit2: has alpha < 0.5 somewhere,
+                              // bit3: texels are 4 x f16 (8 bytes; cube maps only), `data` then points at uint2 texels
     uint32_t mipOffset[16];
 };
 

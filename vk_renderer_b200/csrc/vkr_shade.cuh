@@ -351,6 +351,15 @@ VKR_HD int cube_select(f3 r) {
     return r.x >= 0 ? 0 : 1;
 }
 VKR_HD int clampi(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
+// A cube-map texel: RGBA8 (UNORM / sRGB) or RGBA16F (the engine's skybox asset, assets/pisa_cube.ktx, is an HDR image).
+VKR_HD float4 fetch_cube_texel(const DTexture& t, const float* __restrict__ lut, int level, int x, int y, int w) {
+    if (t.flags & 8u) {
+        const uint2 p = VKR_LDG(reinterpret_cast<const uint2*>(t.data) + t.mipOffset[level] + (size_t)y * w + x);
+        return make_float4(h2f_bits((uint16_t)(p.x & 0xFFFFu)), h2f_bits((uint16_t)(p.x >> 16)),
+                           h2f_bits((uint16_t)(p.y & 0xFFFFu)), h2f_bits((uint16_t)(p.y >> 16)));
+    }
+    return fetch_texel(t, lut, level, x, y, w);
+}
 VKR_HD float4 sample_face_level(const DTexture& t, const float* lut, int level, float s, float tt) {
     const int w = level_dim(t.w, level), h = level_dim(t.h, level);
     float fu = s * (float)w - 0.5f, fv = tt * (float)h - 0.5f;
@@ -358,8 +367,8 @@ VKR_HD float4 sample_face_level(const DTexture& t, const float* lut, int level, 
     float a = fu - iu, b = fv - iv;
     int x0 = clampi((int)iu, 0, w - 1), x1 = clampi((int)iu + 1, 0, w - 1);
     int y0 = clampi((int)iv, 0, h - 1), y1 = clampi((int)iv + 1, 0, h - 1);
-    float4 t00 = fetch_texel(t, lut, level, x0, y0, w), t10 = fetch_texel(t, lut, level, x1, y0, w);
-    float4 t01 = fetch_texel(t, lut, level, x0, y1, w), t11 = fetch_texel(t, lut, level, x1, y1, w);
+    float4 t00 = fetch_cube_texel(t, lut, level, x0, y0, w), t10 = fetch_cube_texel(t, lut, level, x1, y0, w);
+    float4 t01 = fetch_cube_texel(t, lut, level, x0, y1, w), t11 = fetch_cube_texel(t, lut, level, x1, y1, w);
     float w00 = (1.0f - a) * (1.0f - b), w10 = a * (1.0f - b), w01 = (1.0f - a) * b, w11 = a * b;
     return make_float4(t00.x * w00 + t10.x * w10 + t01.x * w01 + t11.x * w11,
                        t00.y * w00 + t10.y * w10 + t01.y * w01 + t11.y * w11,

@@ -20,7 +20,7 @@ PKG = os.path.dirname(os.path.abspath(__file__))
 _engine_lib = None
 
 _API_FIELDS = ["create", "destroy", "upload_mesh", "create_image", "update_bindless_texture", "set_cubemap",
-               "build_material", "draw", "readback", "readback_async", "sync"]
+               "build_material", "draw", "readback", "readback_async", "sync", "set_cubemap_levels"]
 
 
 class VkrApi(C.Structure):
@@ -61,6 +61,7 @@ def load_engine() -> C.CDLL:
         lib.vke_frustum_planes.argtypes = [p, C.POINTER(C.c_float)]
         lib.vke_is_visible.argtypes = [p, C.POINTER(C.c_float), C.POINTER(C.c_float), C.c_float]; lib.vke_is_visible.restype = C.c_int
         lib.vke_load_gltf.argtypes = [p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_size_t]; lib.vke_load_gltf.restype = C.c_int64
+        lib.vke_load_cubemap.argtypes = [p, C.c_char_p, C.c_char_p, C.c_size_t]; lib.vke_load_cubemap.restype = C.c_int
         lib.vke_render_object.argtypes = [p, C.c_size_t, p, C.POINTER(capi.MaterialConstants), C.POINTER(C.c_int)]
         lib.vke_render_object.restype = C.c_int
         lib.vke_decode_png.argtypes = [C.c_char_p, C.c_size_t, p, C.c_size_t, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
@@ -114,6 +115,12 @@ class Engine:
         if n == 0:
             raise RuntimeError("load_procedural failed")
         return n
+
+    def load_cubemap(self, path):
+        """load_cubemap (src/vk_loader.cpp:521-558): a KTX 1.1 / 2.0 cube map becomes the skybox, mip chain included."""
+        err = C.create_string_buffer(256)
+        if self.lib.vke_load_cubemap(self.e, os.fsencode(path), err, len(err)) != 0:
+            raise RuntimeError(f"load_cubemap({path}): {err.value.decode()}")
 
     def load_gltf(self, path, name="gltf") -> int:
         """load_gltf + _sceneRoot->addChild (src/vk_engine_init.cpp:646-660).  Returns the triangles added."""

@@ -205,3 +205,20 @@ def sky_faces(size=64, seed=0):
         img = np.clip(img - stripe, 0, 255)
         faces.append(np.concatenate([img, np.full((size, size, 1), 255)], -1).astype(np.uint8))
     return faces
+
+
+def sky_levels_f16(size=32, levels=4, seed=0):
+    """An HDR sky as a KTX file would carry it: levels[l][f], RGBA float16, level l = 2x2 box average of level l-1
+    (the file's own mip chain; values reach ~6 around a "sun" on the +Z face so that tone mapping matters)."""
+    base = [f.astype(np.float32)[..., :3] / 255.0 for f in sky_faces(size, seed)]
+    y, x = np.mgrid[0:size, 0:size]
+    sun = 6.0 * np.exp(-(((x - 0.6 * size) ** 2 + (y - 0.3 * size) ** 2) / (0.02 * size * size)))
+    base[4] = base[4] + sun[..., None].astype(np.float32)
+    out = []
+    cur = [np.concatenate([b ** 2.2, np.ones((size, size, 1), np.float32)], -1) for b in base]
+    for _ in range(levels):
+        out.append([c.astype(np.float16) for c in cur])
+        if cur[0].shape[0] == 1:
+            break
+        cur = [0.25 * (c[0::2, 0::2] + c[1::2, 0::2] + c[0::2, 1::2] + c[1::2, 1::2]) for c in cur]
+    return out
