@@ -266,10 +266,17 @@ def run_b200(args):
         step()
     r.sync()
     tm = r.timings()   # per-pass device times of a frame issued back to back with its neighbours
+    per_rank = None
     if world > 1:
         t = torch.tensor([ms], device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
+        # every rank's own pass times of that frame: how even the cost-balanced bands came out
+        keys = ["shadow", "geometry", "shade", "total", "shadow_exchange", "frame_gather"]
+        mine = torch.tensor([tm[k] for k in keys], device="cuda")
+        allr = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(allr, mine)
+        per_rank = [{k: round(float(v), 4) for k, v in zip(keys, a.tolist())} for a in allr]
     clocks = sampler.stop() if sampler else None
 
     # ---- dominant-kernel duration, averaged over a few extra frames (events around the kernel itself)
@@ -296,6 +303,11 @@ def run_b200(args):
     sd_b = capi.make_scene_data(view_b, mg.camera_projection(W / H), [mg.light_matrix()] * 4, shadow_mode=1, enable_shadows=True)
     cams = [sd, sd_b]
     target = capi.TARGET_RGB8          # the presented frame, packed R,G,B (the assembled frame when sharded)
+    for i in range(max(3, args.warmup)):                     # untimed: the read-back path allocates its packed buffers on first use
+        r.draw(cams[i % 2], my_objs, fp)
+        if world == 1 or rank == 0:
+            r.readback_async(target, pinned[i % 2].data_ptr(), W * H * 3)
+    r.sync()
     barrier()
     t0 = time.perf_counter()
     for i in range(args.steps):
@@ -365,7 +377,7 @@ def run_b200(args):
                          "peak_source": peak_src},
             "pass_ms": avg, "pass_ms_last_pipelined_frame": {k: float(v) for k, v in tm.items()},
             "host_issue_ms_per_step": host_issue_ms, "host_vkr_draw_call_ms": float(np.median(host_call)),
-            "cluster_culling": cull,
+            "cluster_culling": cull, "per_rank_pass_ms_last_pipelined_frame": per_rank,
             "e2e": {"value": args.steps / e2e_s, "unit": "frames/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                     "readback": "VKR_TARGET_RGB8: the presented frame as packed R,G,B bytes", "checksum": checksum, "frames_verified": 2,
                     "d2h_probe_GBps": d2h_gbps, "d2h_bound_frames_per_s": (d2h_gbps * 1e9 / d2h) if d2h_gbps else None},

@@ -417,7 +417,7 @@ __global__ void __launch_bounds__(128, VKR_SHADE_MIN_CTAS) shade_kernel(const __
     __syncthreads();
     ShadeBuffers sb = sbIn;
     sb.srgbLut = s_lut;
-    if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x < 12 && sbIn.countersHost != nullptr) {
+    if ((blockIdx.x | blockIdx.y) == 0 && threadIdx.x < 12 && sbIn.countersHost != nullptr) {
         // every raster pass of the frame has ended (stream order / the shadow join): publish their counters to the host
         const uint32_t* c = sbIn.counters[threadIdx.x >> 2];
         sbIn.countersHost[threadIdx.x] = c ? c[threadIdx.x & 3] : 0u;
@@ -498,7 +498,7 @@ struct VkrDevice {
     std::vector<std::vector<float4>> meshPosHost;       // ... and positions (cluster bounds, Morton order)
     size_t uploadBytes = 0;
     // VKR_HOST_PROF=1: mean host time of vkr_draw's sections, printed at vkr_destroy
-    bool hostProf = false; double hostProfUs[8] = {0}; uint64_t hostProfFrames = 0;
+    bool hostProf = false; double hostProfUs[10] = {0}; uint64_t hostProfFrames = 0;
 
 
     Queues q{};                         // large-triangle queue of the main pass
@@ -711,10 +711,10 @@ void vkr_destroy(VkrDevice* dev) {
     if (dev->hostProf && dev->hostProfFrames) {
         const double f = 1.0 / (double)dev->hostProfFrames;
         std::fprintf(stderr, "[vkr host rank %d] vkr_draw us/frame over %llu frames: plan %.1f | upload+expand %.1f | shadow (+exchange) %.1f | "
-                     "main raster %.1f | transparent+shade %.1f | gather %.1f | async read-backs %.1f | caller waiting for the submit thread %.1f\n",
+                     "main raster %.1f | transparent+shade %.1f | gather %.1f | async read-backs %.1f | caller waiting for the submit thread %.1f | submit thread waiting for the device %.1f\n",
                      dev->shardRank, (unsigned long long)dev->hostProfFrames,
                      dev->hostProfUs[0] * f, dev->hostProfUs[1] * f, dev->hostProfUs[2] * f, dev->hostProfUs[3] * f, dev->hostProfUs[4] * f, dev->hostProfUs[5] * f,
-                     dev->hostProfUs[6] * f, dev->hostProfUs[7] * f);
+                     dev->hostProfUs[6] * f, dev->hostProfUs[7] * f, dev->hostProfUs[8] * f);
     }
     for (auto it = dev->allocations.rbegin(); it != dev->allocations.rend(); ++it) cudaFree(*it);
     for (auto& s : dev->slots) {
@@ -1038,7 +1038,15 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
         slot.permCap = std::max<size_t>((size_t)passes * nChunks * 3 / 2, 1024);
         ALLOC(slot.permBuf, slot.permCap * 4);
     }
-    if (dev->frameIndex >= VKR_FRAME_OVERLAP) CK(cudaEventSynchronize(slot.uploaded));   // pinned buffer reuse
+    if (dev->frameIndex >= VKR_FRAME_OVERLAP) {      // pinned buffer reuse: this is where a submit thread that runs ahead waits for the device
+        const auto w0 = std::chrono::steady_clock::now();
+        CK(cudaEventSynchronize(slot.uploaded));
+        if (dev->hostProf && dev->frameIndex >= 16) {
+            const auto w1 = std::chrono::steady_clock::now();
+            dev->hostProfUs[8] += std::chrono::duration<double, std::micro>(w1 - w0).count();
+            hostT += w1 - w0;                        // not counted as issue time of the section
+        }
+    }
     int rc = ensure_slot(dev, slot, total);
     if (rc) return rc;
     char* hp = (char*)slot.pinned;

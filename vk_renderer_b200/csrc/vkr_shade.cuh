@@ -134,11 +134,6 @@ VKR_HD float lod_from_rho2(float rho2, int levels) {
     return fminf(fmaxf(lambda, 0.0f), (float)(levels - 1));
 }
 
-// texture2d reads its derivative arguments only for a slot with a mip chain (see the early returns below)
-VKR_HD bool texture_has_mips(const ShadeBuffers& sb, int id) {
-    return id >= 0 && id < VKR_MAX_BINDLESS && sb.textures[id].levels > 1u;
-}
-
 VKR_HD float4 texture2d(const ShadeBuffers& sb, int id, float u, float v, float dudx, float dvdx, float dudy, float dvdy) {
     if (id < 0 || id >= VKR_MAX_BINDLESS) return make_float4(0, 0, 0, 1);
     const DTexture& t = sb.textures[id];
@@ -352,14 +347,18 @@ VKR_HD int cube_select(f3 r) {
 }
 VKR_HD int clampi(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
 // A cube-map texel: RGBA8 (UNORM / sRGB) or RGBA16F (the engine's skybox asset, assets/pisa_cube.ktx, is an HDR image).
+// The format is a template parameter chosen once per lookup (texture_cube): as a per-texel test the compiler predicates
+// both fetch paths into every texel, +8 % instructions for the whole shading kernel (profiles/r01z).
+template <bool F16>
 VKR_HD float4 fetch_cube_texel(const DTexture& t, const float* __restrict__ lut, int level, int x, int y, int w) {
-    if (t.flags & 8u) {
+    if (F16) {
         const uint2 p = VKR_LDG(reinterpret_cast<const uint2*>(t.data) + t.mipOffset[level] + (size_t)y * w + x);
         return make_float4(h2f_bits((uint16_t)(p.x & 0xFFFFu)), h2f_bits((uint16_t)(p.x >> 16)),
                            h2f_bits((uint16_t)(p.y & 0xFFFFu)), h2f_bits((uint16_t)(p.y >> 16)));
     }
     return fetch_texel(t, lut, level, x, y, w);
 }
+template <bool F16>
 VKR_HD float4 sample_face_level(const DTexture& t, const float* lut, int level, float s, float tt) {
     const int w = level_dim(t.w, level), h = level_dim(t.h, level);
     float fu = s * (float)w - 0.5f, fv = tt * (float)h - 0.5f;
@@ -367,21 +366,19 @@ VKR_HD float4 sample_face_level(const DTexture& t, const float* lut, int level, 
     float a = fu - iu, b = fv - iv;
     int x0 = clampi((int)iu, 0, w - 1), x1 = clampi((int)iu + 1, 0, w - 1);
     int y0 = clampi((int)iv, 0, h - 1), y1 = clampi((int)iv + 1, 0, h - 1);
-    float4 t00 = fetch_cube_texel(t, lut, level, x0, y0, w), t10 = fetch_cube_texel(t, lut, level, x1, y0, w);
-    float4 t01 = fetch_cube_texel(t, lut, level, x0, y1, w), t11 = fetch_cube_texel(t, lut, level, x1, y1, w);
+    float4 t00 = fetch_cube_texel<F16>(t, lut, level, x0, y0, w), t10 = fetch_cube_texel<F16>(t, lut, level, x1, y0, w);
+    float4 t01 = fetch_cube_texel<F16>(t, lut, level, x0, y1, w), t11 = fetch_cube_texel<F16>(t, lut, level, x1, y1, w);
     float w00 = (1.0f - a) * (1.0f - b), w10 = a * (1.0f - b), w01 = (1.0f - a) * b, w11 = a * b;
     return make_float4(t00.x * w00 + t10.x * w10 + t01.x * w01 + t11.x * w11,
                        t00.y * w00 + t10.y * w10 + t01.y * w01 + t11.y * w11,
                        t00.z * w00 + t10.z * w10 + t01.z * w01 + t11.z * w11,
                        t00.w * w00 + t10.w * w10 + t01.w * w01 + t11.w * w11);
 }
-VKR_HD float4 texture_cube(const ShadeBuffers& sb, f3 r, f3 rdx, f3 rdy) {
-    int face = cube_select(r);
-    float s, t;
-    cube_project(r, face, s, t);
+template <bool F16>
+VKR_HD float4 texture_cube_fmt(const ShadeBuffers& sb, f3 r, f3 rdx, f3 rdy, int face, float s, float t) {
     const DTexture& tex = sb.cube[face];
     const int levels = (int)tex.levels;
-    if (levels == 1) return sample_face_level(tex, sb.srgbLut, 0, s, t);
+    if (levels == 1) return sample_face_level<F16>(tex, sb.srgbLut, 0, s, t);
     float sx, tx, sy, ty;
     cube_project(rdx, face, sx, tx);
     cube_project(rdy, face, sy, ty);
@@ -391,11 +388,18 @@ VKR_HD float4 texture_cube(const ShadeBuffers& sb, f3 r, f3 rdx, f3 rdy) {
     int l0 = (int)floorf(lod);
     int l1 = l0 + 1 < levels ? l0 + 1 : levels - 1;
     float f = lod - (float)l0;
-    float4 c0 = sample_face_level(tex, sb.srgbLut, l0, s, t);
+    float4 c0 = sample_face_level<F16>(tex, sb.srgbLut, l0, s, t);
     if (f == 0.0f) return c0;
-    float4 c1 = sample_face_level(tex, sb.srgbLut, l1, s, t);
+    float4 c1 = sample_face_level<F16>(tex, sb.srgbLut, l1, s, t);
     return make_float4(c0.x * (1.0f - f) + c1.x * f, c0.y * (1.0f - f) + c1.y * f, c0.z * (1.0f - f) + c1.z * f,
                        c0.w * (1.0f - f) + c1.w * f);
+}
+VKR_HD float4 texture_cube(const ShadeBuffers& sb, f3 r, f3 rdx, f3 rdy) {
+    int face = cube_select(r);
+    float s, t;
+    cube_project(r, face, s, t);
+    if (sb.cube[face].flags & 8u) return texture_cube_fmt<true>(sb, r, rdx, rdy, face, s, t);    // all six faces share the format
+    return texture_cube_fmt<false>(sb, r, rdx, rdy, face, s, t);
 }
 VKR_HD f3 sky_dir(const ShadeConst& sc, float sx, float sy) {
     return {sc.skyO[0] + sx * sc.skyX[0] + sy * sc.skyY[0], sc.skyO[1] + sx * sc.skyX[1] + sy * sc.skyY[1],
@@ -434,17 +438,13 @@ VKR_HD void fetch_fragment(const ShadeConst& sc, const ShadeBuffers& sb, uint32_
     float4 c[3] = {xform(o.mvp, p0), xform(o.mvp, p1), xform(o.mvp, p2)};
     const float cx = (float)px + 0.5f, cy = (float)py + 0.5f;
     const float ihw = sc.invHalfW, ihh = sc.invHalfH;
-    float b[3], bx[3] = {0.0f, 0.0f, 0.0f}, by[3] = {0.0f, 0.0f, 0.0f};
-    bary_at(c, (cx - sc.halfW) * ihw, (cy - sc.halfH) * ihh, b);
-    // the uv derivatives only select a mip level: materials whose textures have a single level (every untextured material
-    // samples the engine's 1x1 defaults) skip the two neighbour evaluations
+    float b[3], bx[3], by[3];
     const float ox = (px & 1) ? -1.0f : 1.0f, oy = (py & 1) ? -1.0f : 1.0f;
-    const DMaterial& mat = sb.materials[material];
-    const bool lod = texture_has_mips(sb, mat.albedoID) || texture_has_mips(sb, mat.metalRoughID);
-    if (lod) {
-        bary_at(c, (cx + ox - sc.halfW) * ihw, (cy - sc.halfH) * ihh, bx);
-        bary_at(c, (cx - sc.halfW) * ihw, (cy + oy - sc.halfH) * ihh, by);
-    }
+    bary_at(c, (cx - sc.halfW) * ihw, (cy - sc.halfH) * ihh, b);
+    // (skipping the two neighbour evaluations for materials without a mip chain was tried in r01z: finding that out costs
+    //  two dependent loads and range checks per pixel, more than the ~40 instructions it saves)
+    bary_at(c, (cx + ox - sc.halfW) * ihw, (cy - sc.halfH) * ihh, bx);
+    bary_at(c, (cx - sc.halfW) * ihw, (cy + oy - sc.halfH) * ihh, by);
     const float4 a0 = VKR_LDG(o.attrA + i0), a1 = VKR_LDG(o.attrA + i1), a2 = VKR_LDG(o.attrA + i2);
     const float4 c0 = VKR_LDG(o.attrB + i0), c1 = VKR_LDG(o.attrB + i1), c2 = VKR_LDG(o.attrB + i2);
     f3 nobj = {b[0] * a0.x + b[1] * a1.x + b[2] * a2.x, b[0] * a0.y + b[1] * a1.y + b[2] * a2.y, b[0] * a0.z + b[1] * a1.z + b[2] * a2.z};
@@ -456,8 +456,8 @@ VKR_HD void fetch_fragment(const ShadeConst& sc, const ShadeBuffers& sb, uint32_
     fr.v = b[0] * c0.w + b[1] * c1.w + b[2] * c2.w;
     float ux = bx[0] * a0.w + bx[1] * a1.w + bx[2] * a2.w, vx = bx[0] * c0.w + bx[1] * c1.w + bx[2] * c2.w;
     float uy = by[0] * a0.w + by[1] * a1.w + by[2] * a2.w, vy = by[0] * c0.w + by[1] * c1.w + by[2] * c2.w;
-    fr.dudx = lod ? (ux - fr.u) * ox : 0.0f; fr.dvdx = lod ? (vx - fr.v) * ox : 0.0f;
-    fr.dudy = lod ? (uy - fr.u) * oy : 0.0f; fr.dvdy = lod ? (vy - fr.v) * oy : 0.0f;
+    fr.dudx = (ux - fr.u) * ox; fr.dvdx = (vx - fr.v) * ox;
+    fr.dudy = (uy - fr.u) * oy; fr.dvdy = (vy - fr.v) * oy;
     float4 pobj = make_float4(b[0] * p0.x + b[1] * p1.x + b[2] * p2.x, b[0] * p0.y + b[1] * p1.y + b[2] * p2.y,
                               b[0] * p0.z + b[1] * p1.z + b[2] * p2.z, 1.0f);
     float4 pw = xform(wm, pobj);
