@@ -443,7 +443,7 @@ def run_views(args):
                       flags=capi.CONFIG_SUBMIT_THREAD)
     views, objs, fp, tris = build_view_scene(r)
     mine = view_slice(rank, world, NVIEWS)
-    sharder = ViewSharder(r, rank, world, cuda=True)
+    sharder = ViewSharder(r, rank, world, cuda=True, rgb8=True)
 
     def barrier():
         torch.cuda.synchronize()
@@ -496,7 +496,8 @@ def run_views(args):
                        "parallelism": f"frame-parallel: view i on rank i mod {world}, scene replicated, no collective"},
             "mtri_per_s": vps * tris / 1e6, "gpix_per_s": vps * VW * VH / 1e9,
             "e2e": {"value": args.steps * NVIEWS / e2e_s, "unit": "views/s", "h2d_bytes_per_step": int(r.upload_bytes() * len(mine)),
-                    "d2h_bytes_per_step": int(VW * VH * 4 * len(mine))},
+                    "d2h_bytes_per_step": int(VW * VH * sharder.channels * len(mine)),
+                    "readback": "VKR_TARGET_RGB8: every view as packed R,G,B bytes"},
             "gpu_launches": int(launches), "clocks": clocks}), flush=True)
     r.close()
     if world > 1:

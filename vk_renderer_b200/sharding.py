@@ -145,12 +145,16 @@ class ViewSharder:
     the read-back of view k overlaps the rendering of view k+1 (two pinned landing buffers = the renderer's
     FRAME_OVERLAP), on the host emulation it is a plain copy."""
 
-    def __init__(self, renderer, rank: int, world: int, cuda: bool):
+    def __init__(self, renderer, rank: int, world: int, cuda: bool, rgb8: bool = False):
+        """rgb8: read the views back as packed R,G,B (VKR_TARGET_RGB8, three quarters of the bytes over the bus; CUDA library
+        only) instead of RGBA8."""
         self.r, self.rank, self.world, self.cuda = renderer, rank, world, cuda
         self.W, self.H = renderer.width, renderer.height
+        self.channels = 3 if (rgb8 and cuda) else 4
+        self.target = capi.TARGET_RGB8 if self.channels == 3 else capi.TARGET_RGBA8
         self._pinned = None
         if cuda:
-            self._pinned = [torch.empty((self.H, self.W, 4), dtype=torch.uint8).pin_memory() for _ in range(2)]
+            self._pinned = [torch.empty((self.H, self.W, self.channels), dtype=torch.uint8).pin_memory() for _ in range(2)]
 
     def render(self, scenes, objects, fp, sink=None):
         """`scenes[i]` is view i's GPUSceneData (camera matrices, light, cascades).  Calls `sink(view, image)` for every
@@ -164,11 +168,11 @@ class ViewSharder:
                 if sink is not None:
                     sink(v, img)
             return len(mine)
-        nbytes = self.W * self.H * 4
+        nbytes = self.W * self.H * self.channels
         prev = None
         for k, v in enumerate(mine):
             self.r.draw(scenes[v], objects, fp)
-            self.r.readback_async(capi.TARGET_RGBA8, self._pinned[k % 2].data_ptr(), nbytes)
+            self.r.readback_async(self.target, self._pinned[k % 2].data_ptr(), nbytes)
             if prev is not None and sink is not None:
                 self.r.sync()          # a consumer on the host serialises the pipeline; throughput runs pass no sink
                 sink(prev[0], self._pinned[prev[1] % 2].numpy())
