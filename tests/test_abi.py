@@ -135,6 +135,18 @@ def test_invalid_arguments_are_reported_not_fatal(vkr_lib):
     assert f("update_bindless_texture")(r.dev, capi.MAX_BINDLESS, 0, 0) == capi.ERROR_INVALID_ARGUMENT
     assert f("update_bindless_texture")(r.dev, 3, 12345, 0) == capi.ERROR_INVALID_ARGUMENT
     assert f("shard_init")(r.dev, 2, 2, None, 0) == capi.ERROR_INVALID_ARGUMENT
+    # cube maps: RGBA16F only through set_cubemap_levels; level count within the extent's chain; no null level
+    face = np.zeros((4, 4, 4), np.uint8)
+    six = (C.c_void_p * 6)(*[face.ctypes.data] * 6)
+    assert f("set_cubemap")(r.dev, six, 4, 4, capi.FORMAT_RGBA16F, 1) == capi.ERROR_INVALID_ARGUMENT
+    assert f("set_cubemap_levels")(r.dev, six, 4, 4, 0, capi.FORMAT_SRGB) == capi.ERROR_INVALID_ARGUMENT
+    assert f("set_cubemap_levels")(r.dev, six, 4, 4, 17, capi.FORMAT_SRGB) == capi.ERROR_INVALID_ARGUMENT
+    assert f("set_cubemap_levels")(r.dev, six, 4, 4, 1, 7) == capi.ERROR_INVALID_ARGUMENT
+    holes = (C.c_void_p * 6)(face.ctypes.data, None, face.ctypes.data, face.ctypes.data, face.ctypes.data, face.ctypes.data)
+    assert f("set_cubemap_levels")(r.dev, holes, 4, 4, 1, capi.FORMAT_SRGB) == capi.ERROR_INVALID_ARGUMENT
+    assert f("set_cubemap_levels")(r.dev, None, 4, 4, 1, capi.FORMAT_SRGB) == capi.ERROR_INVALID_ARGUMENT
+    img = C.c_uint32()
+    assert f("create_image")(r.dev, face.ctypes.data, 4, 4, capi.FORMAT_RGBA16F, 0, C.byref(img)) == capi.ERROR_INVALID_ARGUMENT
     # the device is still usable after every refusal
     r.draw(sd, np.array([ok]), fp)
     assert (r.readback(capi.TARGET_PRIMID) != 0xFFFFFFFF).any()
