@@ -49,3 +49,36 @@ def assert_parity(ref, got, region=None, rgb_frac=0.999, min_psnr=50.0):
     assert frac >= rgb_frac, f"only {frac:.5f} of pixels within 1/255"
     assert p >= min_psnr, f"PSNR {p:.1f} dB"
     return frac, p
+
+
+def random_camera_frames(lib, prefix, seed, width=160, height=96):
+    """The lattice scene (27 instanced spheres) from a seeded camera: inside the lattice or around it, aimed at a point of it
+    give or take 0.4 rad (seeds 0-7: clusters cross the near plane, w = 0 and the frustum sides) or anywhere (seeds 8, 9)."""
+    from vk_renderer_b200 import meshgen as mg
+    rng = np.random.default_rng(1000 + seed)
+    pos = rng.uniform(-4.0, 4.0, 3) if seed % 2 else rng.uniform(-1.0, 1.0, 3) * np.array([9.0, 6.0, 9.0])
+    if seed < 8:         # forward = (-sin yaw cos pitch, sin pitch, -cos yaw cos pitch)
+        d = rng.uniform(-2.6, 2.6, 3) - pos
+        d /= np.linalg.norm(d)
+        pitch, yaw = float(np.arcsin(d[1]) + rng.uniform(-0.4, 0.4)), float(np.arctan2(-d[0], -d[2]) + rng.uniform(-0.4, 0.4))
+    else:
+        pitch, yaw = float(rng.uniform(-1.2, 1.2)), float(rng.uniform(-3.1, 3.1))
+    r = capi.Renderer(lib, prefix, width, height, shadow_extent=128)
+    sd, objs, fp = scenes.lattice(r, n=3, rings=12)
+    view = mg.camera_view(tuple(pos), pitch=pitch, yaw=yaw)
+    sd = capi.make_scene_data(view, mg.camera_projection(width / height), scenes._lights(1), shadow_mode=1, enable_shadows=True)
+    r.draw(sd, objs, fp)
+    out = {k: r.readback(v) for k, v in dict(depth=capi.TARGET_DEPTH, prim=capi.TARGET_PRIMID, shadow=capi.TARGET_SHADOW,
+                                             rgba=capi.TARGET_RGBA8).items()}
+    r.close()
+    return out
+
+
+def assert_random_camera_parity(ref_lib, ref_prefix, lib, prefix, seed):
+    a, b = random_camera_frames(ref_lib, ref_prefix, seed), random_camera_frames(lib, prefix, seed)
+    if seed < 8:
+        assert (a["prim"] != 0xFFFFFFFF).mean() > 0.05, "the camera was meant to see the lattice"
+    assert np.array_equal(a["prim"], b["prim"]), f"coverage differs on {(a['prim'] != b['prim']).sum()} pixels"
+    assert np.array_equal(a["depth"].view(np.uint32), b["depth"].view(np.uint32))
+    assert np.array_equal(a["shadow"][:1].view(np.uint32), b["shadow"][:1].view(np.uint32))
+    assert (np.abs(a["rgba"].astype(np.int32) - b["rgba"].astype(np.int32))[..., :3].max(-1) <= 1).mean() >= 0.999

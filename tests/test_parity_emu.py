@@ -39,3 +39,11 @@ def test_emu_cluster_culling_is_exercised(ork_lib, emu_lib):
     assert out[0] > total // 4, f"main pass culled only {out[0]} of {total} clusters"
     assert out[1] > 0, "shadow pass culled nothing"
     r.close()
+
+
+@pytest.mark.parametrize("seed", range(10))
+def test_emu_culling_is_conservative_from_random_cameras(ork_lib, emu_lib, seed):
+    """The cluster culls (frustum, no pixel centre, occlusion against the live depth) argue with margins; here
+    they are tried from cameras a scene author would not pick (parity.random_camera_frames).  The oracle has no culling:
+    every pixel, depth and shadow texel must still be identical."""
+    parity.assert_random_camera_parity(ork_lib, "ork", emu_lib, "emu", seed)

@@ -15,6 +15,13 @@ def test_gpu_matches_oracle(ork_lib, vkr_lib, scene):
     parity.assert_parity(ref, got)
 
 
+@pytest.mark.parametrize("seed", range(10))
+def test_gpu_culling_is_conservative_from_random_cameras(ork_lib, vkr_lib, seed):
+    """Cameras inside and around the lattice, clusters crossing the near plane and the frustum sides: the device's cluster
+    culls must not change a pixel against the oracle, which has none."""
+    parity.assert_random_camera_parity(ork_lib, "ork", vkr_lib, "vkr", seed)
+
+
 def test_gpu_scissor(ork_lib, vkr_lib):
     sc = (64, 40, 160, 100)
     ref = parity.render(ork_lib, "ork", "basic_pcf", 320, 200, shadow_extent=512, scissor=sc)
