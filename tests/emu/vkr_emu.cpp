@@ -384,6 +384,24 @@ int emu_bands(EmuDevice* d, int32_t* out) {
     return (int)d->plan.bandMain.size();
 }
 void* emu_host_ptr(EmuDevice* d, int what) { return what == VKR_TARGET_RGBA8 ? (void*)d->rgba8.data() : nullptr; }
+// Test hook: build_clusters (vkr_frameprep.h) on a bare index / position array.  Returns the number of clusters; when the
+// output arrays are large enough (capacities in elements) the cluster data is copied out: verts (concatenated distinct-vertex
+// lists), tris / orig (clusters * CL_TRIS), info (2 u32 per cluster), bounds (8 floats per cluster).
+int emu_build_clusters(const uint32_t* idx, uint32_t triCount, uint32_t nv, const float* pos4, uint32_t* verts, size_t vertsCap,
+                       uint32_t* tris, uint32_t* orig, size_t trisCap, uint32_t* info, float* bounds, size_t clustersCap, size_t* vertsUsed) {
+    ClusterData cd;
+    build_clusters(idx, triCount, nv, reinterpret_cast<const float4*>(pos4), cd);
+    const size_t nc = cd.info.size();
+    if (vertsUsed) *vertsUsed = cd.verts.size();
+    if (cd.verts.size() <= vertsCap && cd.tris.size() <= trisCap && nc <= clustersCap) {
+        std::memcpy(verts, cd.verts.data(), cd.verts.size() * 4);
+        std::memcpy(tris, cd.tris.data(), cd.tris.size() * 4);
+        std::memcpy(orig, cd.orig.data(), cd.orig.size() * 4);
+        std::memcpy(info, cd.info.data(), nc * 8);
+        std::memcpy(bounds, cd.bounds.data(), nc * 32);
+    }
+    return (int)nc;
+}
 void emu_culled(EmuDevice* d, uint32_t out[2]) { out[0] = d->culled[0]; out[1] = d->culled[1]; }
 const char* emu_last_error(EmuDevice* d) { return d->err.c_str(); }
 

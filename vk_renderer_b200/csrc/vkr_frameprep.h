@@ -83,35 +83,53 @@ inline uint32_t morton_part(uint32_t v) {
     v = (v | (v << 2)) & 0x09249249u;
     return v;
 }
-// `pos` are the mesh's positions (x,y,z,1).  Triangles are ordered along a 30-bit Morton curve of their
-// centroids inside the range's bounding box (ties keep submission order), then cut greedily: a cluster
+// Spatial order of a draw's triangles for the greedy cut below: a k-d partition of the centroids whose split points are
+// multiples of CL_TRIS.  A range that needs k = ceil(n / CL_TRIS) clusters is split along the longest axis of its centroid
+// bounds into the floor(k / 2) * CL_TRIS lowest triangles and the rest, recursively, so every leaf is one full cluster (the
+// last one takes the remainder) and a compact patch of surface.  (A Morton curve, used before, jumps: on BASELINE config 4's
+// sphere half of the clusters were two patches in one box, median box diagonal 0.93 of the radius against 0.5 now, and a
+// box that is too big on screen is never tried against the depth buffer, vkr_raster.cuh OCC_MAX_PIXELS.)
+// Deterministic: ties broken by the triangle number, leaves listed in submission order.
+inline void spatial_order(const uint32_t* idx, uint32_t triCount, const float4* pos, std::vector<uint32_t>& order) {
+    order.resize(triCount);
+    for (uint32_t t = 0; t < triCount; ++t) order[t] = t;
+    if (triCount <= (uint32_t)CL_TRIS) return;
+    std::vector<float> cen((size_t)triCount * 3);
+    for (uint32_t t = 0; t < triCount; ++t) {
+        const float4 a = pos[idx[3 * (size_t)t]], b = pos[idx[3 * (size_t)t + 1]], c = pos[idx[3 * (size_t)t + 2]];
+        const float v[3] = {(a.x + b.x + c.x) * (1.0f / 3.0f), (a.y + b.y + c.y) * (1.0f / 3.0f), (a.z + b.z + c.z) * (1.0f / 3.0f)};
+        for (int k = 0; k < 3; ++k) cen[(size_t)t * 3 + k] = std::isfinite(v[k]) ? v[k] : 0.0f;     // a strict weak order needs no NaN
+    }
+    struct Span { uint32_t begin, end; };
+    std::vector<Span> stack{{0u, triCount}};
+    while (!stack.empty()) {
+        const Span sp = stack.back();
+        stack.pop_back();
+        const uint32_t n = sp.end - sp.begin;
+        if (n <= (uint32_t)CL_TRIS) { std::sort(order.begin() + sp.begin, order.begin() + sp.end); continue; }
+        float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+        for (uint32_t i = sp.begin; i < sp.end; ++i)
+            for (int k = 0; k < 3; ++k) { const float v = cen[(size_t)order[i] * 3 + k]; lo[k] = std::min(lo[k], v); hi[k] = std::max(hi[k], v); }
+        int axis = 0;
+        if (hi[1] - lo[1] > hi[axis] - lo[axis]) axis = 1;
+        if (hi[2] - lo[2] > hi[axis] - lo[axis]) axis = 2;
+        const uint32_t clusters = (n + (uint32_t)CL_TRIS - 1) / (uint32_t)CL_TRIS;
+        const uint32_t mid = sp.begin + (clusters / 2) * (uint32_t)CL_TRIS;
+        std::nth_element(order.begin() + sp.begin, order.begin() + mid, order.begin() + sp.end, [&](uint32_t x, uint32_t y) {
+            const float cx = cen[(size_t)x * 3 + axis], cy = cen[(size_t)y * 3 + axis];
+            return cx != cy ? cx < cy : x < y;
+        });
+        stack.push_back({sp.begin, mid});
+        stack.push_back({mid, sp.end});
+    }
+}
+
+// `pos` are the mesh's positions (x,y,z,1).  Triangles are put in spatial_order, then cut greedily: a cluster
 // closes when it holds CL_TRIS triangles or the next triangle would take it past CL_VERTS vertices.
 inline void build_clusters(const uint32_t* idx, uint32_t triCount, uint32_t nv, const float4* pos, ClusterData& out) {
     out.verts.clear(); out.tris.clear(); out.orig.clear(); out.info.clear(); out.bounds.clear();
-    std::vector<uint32_t> order(triCount);
-    for (uint32_t t = 0; t < triCount; ++t) order[t] = t;
-    if (triCount > (uint32_t)CL_TRIS) {
-        float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
-        for (size_t i = 0; i < (size_t)triCount * 3; ++i) {
-            const float4 p = pos[idx[i]];
-            const float c[3] = {p.x, p.y, p.z};
-            for (int k = 0; k < 3; ++k) { lo[k] = std::min(lo[k], c[k]); hi[k] = std::max(hi[k], c[k]); }
-        }
-        float inv[3];
-        for (int k = 0; k < 3; ++k) inv[k] = hi[k] > lo[k] ? 1023.0f / (hi[k] - lo[k]) : 0.0f;
-        std::vector<uint32_t> code(triCount);
-        for (uint32_t t = 0; t < triCount; ++t) {
-            const float4 a = pos[idx[3 * (size_t)t]], b = pos[idx[3 * (size_t)t + 1]], c = pos[idx[3 * (size_t)t + 2]];
-            const float cen[3] = {(a.x + b.x + c.x) * (1.0f / 3.0f), (a.y + b.y + c.y) * (1.0f / 3.0f), (a.z + b.z + c.z) * (1.0f / 3.0f)};
-            uint32_t q[3];
-            for (int k = 0; k < 3; ++k) {
-                float f = (cen[k] - lo[k]) * inv[k];
-                q[k] = !(f > 0.0f) ? 0u : (f >= 1023.0f ? 1023u : (uint32_t)f);      // NaN-safe
-            }
-            code[t] = morton_part(q[0]) | (morton_part(q[1]) << 1) | (morton_part(q[2]) << 2);
-        }
-        std::stable_sort(order.begin(), order.end(), [&](uint32_t x, uint32_t y) { return code[x] < code[y]; });
-    }
+    std::vector<uint32_t> order;
+    spatial_order(idx, triCount, pos, order);
     std::vector<uint32_t> stamp(nv, 0xFFFFFFFFu), local(nv, 0u);
     uint32_t s = 0, c = 0;
     while (s < triCount) {
