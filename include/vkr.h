@@ -249,7 +249,12 @@ int vkr_shard_init(VkrDevice* dev, int rank, int nranks, const void* twoIds, siz
 
 /* Headless replacement of present (src/vk_engine_run.cpp:159-190). */
 int vkr_readback(VkrDevice* dev, VkrTarget what, void* dst, size_t dstBytes);          /* synchronous */
-int vkr_readback_async(VkrDevice* dev, VkrTarget what, void* pinnedDst, size_t dstBytes); /* last drawn frame */
+/* The frame drawn by the preceding vkr_draw, copied on the copy stream beside the next frame's kernels.  pinnedDst must stay valid
+ * and untouched until vkr_sync (or until FRAME_OVERLAP further frames have been drawn and synchronised).  With
+ * VKR_CONFIG_SUBMIT_THREAD the request is queued behind its frame on the submit thread and the call returns at once; a failure is
+ * reported by the next call on the device.  The presented image is double-buffered: the frame drawn FRAME_OVERLAP draws later
+ * waits, on the device, for this copy before it overwrites the image. */
+int vkr_readback_async(VkrDevice* dev, VkrTarget what, void* pinnedDst, size_t dstBytes);
 int vkr_sync(VkrDevice* dev);
 
 /* stats.triangle_count / drawcall_count — src/vk_engine_run.cpp:70-71,309-310. */
