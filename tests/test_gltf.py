@@ -166,3 +166,38 @@ def test_gltf_scene_on_the_device_matches_the_oracle(ork_lib, vkr_lib, tmp_path)
         out[prefix].update(stats=e.stats(), shadows=True, layers=1)
         e.close()
     parity.assert_parity(out["ork"], out["vkr"])
+
+
+def test_component_conversion_matches_fastgltfs_own_test():
+    """The reference's vendored fastgltf carries one known-answer test for the loader's arithmetic, "Test data type conversion"
+    (external/fastgltf/tests/accessor_tests.cpp:29-51; not built by the reference): a normalised integer i of type T becomes
+    max(i / T_max, -1) to within float epsilon — over every value of int8, uint8, int16 and uint16.  Restated here on the
+    loader's accessor conversion, plus the non-normalised and float pass-through cases of convertComponent
+    (external/fastgltf/include/fastgltf/tools.hpp:126-149)."""
+    import ctypes as C
+    from vk_renderer_b200.engine import load_engine
+    lib = load_engine()
+    lib.vke_gltf_convert.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p]
+    lib.vke_gltf_convert.restype = None
+
+    def convert(values, component_type, normalized):
+        values = np.ascontiguousarray(values)
+        out = np.zeros(len(values), np.float32)
+        lib.vke_gltf_convert(component_type, int(normalized), values.ctypes.data, len(values), out.ctypes.data)
+        return out
+
+    eps = np.finfo(np.float32).eps
+    for dtype, ctype in ((np.int8, 5120), (np.uint8, 5121), (np.int16, 5122), (np.uint16, 5123)):
+        info = np.iinfo(dtype)
+        i = np.arange(info.min, info.max + 1, dtype=np.int64).astype(dtype)
+        got = convert(i, ctype, True)
+        want = np.maximum(i.astype(np.float32) / np.float32(info.max), np.float32(-1.0))
+        assert np.all(np.abs(got - want) <= eps), dtype
+        assert got.min() == (-1.0 if info.min < 0 else 0.0) and got.max() == 1.0
+        back = np.round(got.astype(np.float64) * info.max)              # the test's float -> int leg: exact round trip
+        assert np.array_equal(back[i != info.min], i[i != info.min].astype(np.float64))
+        assert np.array_equal(convert(i, ctype, False), i.astype(np.float32))       # not normalised: a plain cast
+    u32 = np.array([0, 1, 65536, 4000000000], np.uint32)
+    assert np.array_equal(convert(u32, 5125, False), u32.astype(np.float32))
+    f32 = np.array([0.25, -3.5, 1e-20, 7e9], np.float32)
+    assert np.array_equal(convert(f32, 5126, True), f32)                               # floats pass through either way

@@ -55,6 +55,9 @@ int vke_load_cubemap(VulkanEngine* e, const char* fileName, char* err, size_t er
     if (err && errBytes) { std::strncpy(err, why.c_str(), errBytes - 1); err[errBytes - 1] = 0; }
     return -1;
 }
+void vke_gltf_convert(int componentType, int normalized, const unsigned char* data, size_t count, float* out) {
+    gltf_convert_components(componentType, normalized != 0, data, count, out);
+}
 // Test hook: decode a KTX cube held in memory.  info = {width, height, levels, format, generateMips}; when `out` is large enough
 // (all levels, level-major then face) the texels are copied there.  0 on success, -1 with the reason.
 int vke_decode_ktx(const unsigned char* data, size_t size, uint32_t info[5], unsigned char* out, size_t outBytes, char* err, size_t errBytes) {

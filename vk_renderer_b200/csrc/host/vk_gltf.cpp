@@ -422,6 +422,15 @@ long texture_image(const Document& d, const Json* texInfo) {      // textureInfo
 
 }  // namespace
 
+// Test hook: `count` tightly packed scalar components of glTF component type `componentType` through the accessor conversion
+// load_gltf uses for every attribute (fastgltf's convertComponent, external/fastgltf/include/fastgltf/tools.hpp:126-149).
+void gltf_convert_components(int componentType, bool normalized, const unsigned char* data, size_t count, float* out) {
+    AccessorView v;
+    v.base = data; v.count = count; v.componentType = componentType; v.components = 1; v.normalized = normalized;
+    v.stride = (componentType == 5120 || componentType == 5121) ? 1 : ((componentType == 5122 || componentType == 5123) ? 2 : 4);
+    for (size_t i = 0; i < count; ++i) out[i] = v.f(i, 0);
+}
+
 std::shared_ptr<Node> load_gltf(VulkanEngine* engine, const std::string& name, const std::string& fileName, std::string* error) {
     Document d;
     auto bail = [&](const std::string& why) -> std::shared_ptr<Node> { if (error) *error = d.err.empty() ? why : d.err; return nullptr; };

@@ -25,3 +25,6 @@ std::shared_ptr<Node> load_gltf(VulkanEngine* engine, const std::string& name, c
 
 // PNG -> RGBA8 (test hook and used by load_gltf).  Returns false when the stream is not a PNG this decoder handles.
 bool decode_png(const unsigned char* data, size_t size, std::vector<unsigned char>& rgba, uint32_t& width, uint32_t& height);
+
+// Test hook (see vk_gltf.cpp): the accessor component conversion on a packed array of scalars.
+void gltf_convert_components(int componentType, bool normalized, const unsigned char* data, size_t count, float* out);
