@@ -74,15 +74,6 @@ struct ClusterData {
     std::vector<uint2> info;         // per cluster
     std::vector<float4> bounds;      // per cluster: min, max
 };
-// Spread the low 10 bits of v so that there are two zero bits between each.
-inline uint32_t morton_part(uint32_t v) {
-    v &= 1023u;
-    v = (v | (v << 16)) & 0x030000FFu;
-    v = (v | (v << 8)) & 0x0300F00Fu;
-    v = (v | (v << 4)) & 0x030C30C3u;
-    v = (v | (v << 2)) & 0x09249249u;
-    return v;
-}
 // Spatial order of a draw's triangles for the greedy cut below: a k-d partition of the centroids whose split points are
 // multiples of CL_TRIS.  A range that needs k = ceil(n / CL_TRIS) clusters is split along the longest axis of its centroid
 // bounds into the floor(k / 2) * CL_TRIS lowest triangles and the rest, recursively, so every leaf is one full cluster (the
