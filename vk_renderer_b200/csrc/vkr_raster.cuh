@@ -688,7 +688,10 @@ __device__ __forceinline__ CornerAcc corners_warp(const float* __restrict__ m, f
 #endif
 
 static const int CLUSTER_DRAW = 1, CLUSTER_CULLED = 0, CLUSTER_TEST = 2;
-static const int OCC_MAX_PIXELS = 1024;      // occlusion test only when the rectangle is at most this many pixels
+#ifndef VKR_OCC_MAX_PIXELS
+#define VKR_OCC_MAX_PIXELS 1024
+#endif
+static const int OCC_MAX_PIXELS = VKR_OCC_MAX_PIXELS;      // occlusion test only when the rectangle is at most this many pixels
 struct ClusterRect { int32_t x0, y0, x1, y1; uint32_t zminBits; int32_t verdict; };
 
 VKR_HD ClusterRect cluster_finalize(const CornerAcc& a, const RasterTarget& rt) {
