@@ -135,7 +135,7 @@ def measured_traffic(kernel):
     if not files:
         return None, None
     d = json.load(open(files[-1]))
-    return d["dram_bytes_per_launch"].get(kernel), os.path.basename(files[-1])
+    return d["dram_bytes_per_launch"].get(kernel), f"{os.path.basename(files[-1])} (kernels of commit {d.get('kernel_source_commit', 'unrecorded')})"
 
 
 def load_oracle():
@@ -240,7 +240,8 @@ def run_b200(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(max(3, args.warmup)):
+    warmup_run = max(3, args.warmup)                          # the timing rules ask for at least three
+    for _ in range(warmup_run):
         step()
     r.sync()
     barrier()
@@ -350,6 +351,35 @@ def run_b200(args):
     if rank == 0 and not e2e_ok:
         raise SystemExit("bench.py: an asynchronously read-back frame differs from the same frame rendered synchronously")
 
+    # ---- N > 1: the assembled frame and the exchanged shadow map against the SAME frame drawn by one unsharded device
+    # (a second VkrDevice on rank 0's GPU), byte for byte
+    import zlib
+    sharded_equals_single, frame_crc = None, None
+    r.draw(cams[0], my_objs, fp)
+    frame_n = r.readback(target) if rank == 0 or world == 1 else None
+    shadow_n = r.readback(capi.TARGET_SHADOW)[:1] if rank == 0 else None
+    if rank == 0:
+        frame_crc = zlib.crc32(frame_n.tobytes()) & 0xFFFFFFFF
+    if world > 1:
+        ok = torch.ones(1, device="cuda", dtype=torch.int32)
+        if rank == 0:
+            r1 = capi.Renderer(lib, "vkr", W, H, shadow_extent=S, device=local, stream=stream, flags=0)
+            sd1, objs1, fp1, _ = build_scene(r1)
+            r1.draw(cams[0], objs1, fp1)
+            frame_1, shadow_1 = r1.readback(target), r1.readback(capi.TARGET_SHADOW)[:1]
+            r1.close()
+            sharded_equals_single = bool(np.array_equal(frame_1, frame_n) and np.array_equal(shadow_1.view(np.uint32), shadow_n.view(np.uint32)))
+            if not sharded_equals_single:
+                print(f"bench.py: sharded frame differs from the single-GPU frame on {(frame_1 != frame_n).any(-1).sum()} pixels, "
+                      f"shadow map on {(shadow_1.view(np.uint32) != shadow_n.view(np.uint32)).sum()} texels", file=sys.stderr)
+                ok.zero_()
+        dist.broadcast(ok, 0)
+        if int(ok.item()) == 0:
+            r.close()
+            dist.destroy_process_group()
+            raise SystemExit(3)
+
+    line = None
     if rank == 0:
         fps = args.steps / (ms / 1000.0)
         peak, peak_src = measured_peak()
@@ -365,7 +395,7 @@ def run_b200(args):
         achieved = gk_bytes / (gk_ms / 1000.0) / 1e9 if gk_ms > 0 else 0.0
         line = {
             "metric": "frames_per_sec_4k_pbr_shadow", "value": fps, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
-            "warmup": max(3, args.warmup), "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "warmup": warmup_run, "ms_per_step": ms / args.steps, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": workload_config(info, world),
             "mtri_per_s": fps * info["tris"] / 1e6, "gpix_per_s": fps * W * H / 1e9,
@@ -380,17 +410,29 @@ def run_b200(args):
             "cluster_culling": cull, "per_rank_pass_ms_last_pipelined_frame": per_rank,
             "e2e": {"value": args.steps / e2e_s, "unit": "frames/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                     "readback": "VKR_TARGET_RGB8: the presented frame as packed R,G,B bytes", "checksum": checksum, "frames_verified": 2,
+                    "frame_crc32": frame_crc,
                     "d2h_probe_GBps": d2h_gbps, "d2h_bound_frames_per_s": (d2h_gbps * 1e9 / d2h) if d2h_gbps else None},
             "gpu_launches": int(launches),
             "clocks": clocks,
         }
+        if world > 1:
+            line["sharded_equals_single"] = sharded_equals_single
         if world == 1 and not args.no_cpu_baseline:
             times, cores, _ = time_oracle(1, 0, budget_s=60.0)
             cfps = len(times) / sum(times)
             line["cpu_baseline"] = {"value": cfps, "unit": "frames/s", "cores": cores, "kind": "port",
                                     "sample": f"{len(times)} full 4K frame of the same scene, oracle/ork.cpp, {cores} threads"}
-        print(json.dumps(line), flush=True)
     r.close()
+    # ---- BASELINE config 5 (frame-parallel multi-view batch) on the same ranks, reported inside the same line
+    if not args.no_views:
+        barrier()
+        v = measure_views(lib, dist, rank, world, local, steps=2, warmup_req=3)
+        if rank == 0:
+            line["views"] = {"metric": v["metric"], "value": v["value"], "unit": v["unit"], "e2e": v["e2e"], "n_gpus": world,
+                             "steps": v["steps"], "ms_per_step": v["ms_per_step"], "scaling": "strong", "config": v["config"],
+                             "gpu_launches": v["gpu_launches"], "expected": "linear in n_gpus: no exchange step"}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
 
@@ -427,7 +469,6 @@ def run_views(args):
     """--workload views: one step = the batch of 256 views, view i on rank i mod N, no exchange step."""
     import torch
     import vk_renderer_b200
-    from vk_renderer_b200.sharding import ViewSharder, view_slice
 
     rank, world, local = (int(os.environ.get(k, d)) for k, d in (("RANK", "0"), ("WORLD_SIZE", "1"), ("LOCAL_RANK", "0")))
     if not torch.cuda.is_available():
@@ -439,6 +480,22 @@ def run_views(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     lib = vk_renderer_b200.load()
     torch.cuda.set_stream(torch.cuda.Stream())
+    line = measure_views(lib, dist, rank, world, local, args.steps, args.warmup)
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def measure_views(lib, dist, rank, world, local, steps, warmup_req):
+    """Config 5 on the ranks of an initialised process group (or one GPU): returns the JSON line (rank 0; None elsewhere)."""
+    import torch
+    from vk_renderer_b200.sharding import ViewSharder, view_slice
+
+    class _A:
+        pass
+    args = _A()
+    args.steps, args.warmup = steps, warmup_req
     r = capi.Renderer(lib, "vkr", VW, VH, shadow_extent=S, device=local, stream=torch.cuda.current_stream().cuda_stream,
                       flags=capi.CONFIG_SUBMIT_THREAD)
     views, objs, fp, tris = build_view_scene(r)
@@ -484,9 +541,10 @@ def run_views(args):
         sharder.render(views, objs, fp)            # draw + read every view back to pinned host memory
     barrier()
     e2e_s = maxed(time.perf_counter() - t0)
+    line = None
     if rank == 0:
         vps = args.steps * NVIEWS / (ms / 1000.0)
-        print(json.dumps({
+        line = ({
             "metric": "views_per_sec_1080p_multiview", "value": vps, "unit": "views/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(3, args.warmup), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -498,10 +556,9 @@ def run_views(args):
             "e2e": {"value": args.steps * NVIEWS / e2e_s, "unit": "views/s", "h2d_bytes_per_step": int(r.upload_bytes() * len(mine)),
                     "d2h_bytes_per_step": int(VW * VH * sharder.channels * len(mine)),
                     "readback": "VKR_TARGET_RGB8: every view as packed R,G,B bytes"},
-            "gpu_launches": int(launches), "clocks": clocks}), flush=True)
+            "gpu_launches": int(launches), "clocks": clocks})
     r.close()
-    if world > 1:
-        dist.destroy_process_group()
+    return line
 
 
 def main():
@@ -511,6 +568,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-views", action="store_true", help="skip the config-5 pass that follows the frame workload")
     ap.add_argument("--workload", default="frame", choices=["frame", "views"],
                     help="frame: BASELINE config 4 (the headline metric, default); views: config 5, frame-parallel multi-view batch")
     args = ap.parse_args()

@@ -318,6 +318,9 @@ SCENES = {
     "basic_pcss": lambda r: basic(r, 2),
     "basic_csm": lambda r: basic(r, 3),
     "basic_lambert_noshadow": lambda r: basic(r, 0, shadows=False, post=False, skybox=False, frag=capi.FRAG_LAMBERT),
+    # mesh.frag evaluates the same four shadow modes before its Lambert term (shaders/mesh.frag:124-182)
+    "basic_lambert_pcf": lambda r: basic(r, 1, frag=capi.FRAG_LAMBERT),
+    "basic_lambert_csm": lambda r: basic(r, 3, post=False, skybox=False, background=True, frag=capi.FRAG_LAMBERT),
     "basic_hdr_sky": lambda r: basic(r, 1, skybox="hdr"),
     "basic_sky_levels8": lambda r: basic(r, 1, skybox="levels8", post=False),
     "basic_background": lambda r: basic(r, 1, skybox=False, background=True, post=False),

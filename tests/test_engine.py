@@ -119,7 +119,7 @@ def test_engine_emu_matches_oracle(ork_lib, emu_lib, config):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("config,size", [(1, (1280, 720)), (2, (1920, 1080)), (3, (960, 540))])
+@pytest.mark.parametrize("config,size", [(1, (1280, 720)), (2, (1920, 1080)), (3, (960, 540)), (3, (3840, 2160))])
 def test_engine_gpu_matches_oracle(ork_lib, vkr_lib, config, size):
     ref = render_engine(ork_lib, "ork", config, *size, shadow_extent=2048)
     got = render_engine(None, "vkr", config, *size, shadow_extent=2048)

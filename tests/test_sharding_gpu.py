@@ -103,3 +103,40 @@ def test_frame_parallel_views_on_the_device(vkr_lib):
             assert np.array_equal(img, want[v]), f"view {v}"
         assert ViewSharder(r, rank, world, cuda=True).render(views, objs, fp) == n      # throughput form: no sink
     r.close()
+
+
+def test_config5_view_at_1080p_matches_oracle(ork_lib, vkr_lib):
+    """BASELINE config 5 at its own size: views of the 511 k-triangle scene at 1920x1080 (2048^2 PCF shadow, tonemap), rendered
+    and read back by ViewSharder (rank 1 of 4: views 1, 5, 9, ...), against the oracle's frames of the same views."""
+    sys.path.insert(0, ROOT)
+    import bench
+    import parity
+    from vk_renderer_b200 import capi
+    from vk_renderer_b200.sharding import ViewSharder
+    ro = capi.Renderer(ork_lib, "ork", bench.VW, bench.VH, shadow_extent=bench.S)
+    views, objs, fp, tris = bench.build_view_scene(ro)
+    picks = [1, 69]                               # two of rank 1's views, a quarter orbit apart
+    want = {}
+    for v in picks:
+        ro.draw(views[v], objs, fp)
+        want[v] = {k: ro.readback(t) for k, t in dict(rgba=capi.TARGET_RGBA8, depth=capi.TARGET_DEPTH, prim=capi.TARGET_PRIMID,
+                                                       shadow=capi.TARGET_SHADOW).items()}
+        want[v].update(stats=ro.stats(), shadows=True, layers=1)
+    ro.close()
+    r = capi.Renderer(vkr_lib, "vkr", bench.VW, bench.VH, shadow_extent=bench.S)
+    views, objs, fp, tris2 = bench.build_view_scene(r)
+    assert tris == tris2 and 500_000 < tris < 520_000
+    sub = [views[v] for v in range(0, 72)]
+    got = {}
+    ViewSharder(r, 1, 4, cuda=True).render(sub, objs, fp, lambda v, img: got.__setitem__(v, img.copy()) if v in picks else None)
+    assert sorted(got) == picks
+    for v in picks:                               # the frames the sharder delivered, then the full parity bar on the same view
+        d = np.abs(got[v].astype(np.int32) - want[v]["rgba"].astype(np.int32))[..., :3].max(-1)
+        assert (d <= 1).mean() >= 0.999, f"view {v}: only {(d <= 1).mean():.5f} of pixels within 1/255"
+        r.draw(views[v], objs, fp)
+        mine = {k: r.readback(t) for k, t in dict(rgba=capi.TARGET_RGBA8, depth=capi.TARGET_DEPTH, prim=capi.TARGET_PRIMID,
+                                                   shadow=capi.TARGET_SHADOW).items()}
+        mine.update(stats=r.stats(), shadows=True, layers=1)
+        assert np.array_equal(mine["rgba"], got[v])
+        parity.assert_parity(want[v], mine)
+    r.close()

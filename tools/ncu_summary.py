@@ -33,7 +33,10 @@ ir, iw, ik = H.index('dram__bytes_read.sum'), H.index('dram__bytes_write.sum'), 
 for r in rows[2:]:
     name = re.sub(r"\(.*", "", r[ik]).replace("void ", "").strip()
     traffic.setdefault(name, []).append(_bytes(r[ir], units[ir]) + _bytes(r[iw], units[iw]))
+def _git(*a):
+    return subprocess.run(["git", *a], capture_output=True, text=True).stdout.strip()
+commit = _git("rev-parse", "--short", "HEAD") + ("+dirty" if _git("status", "--porcelain", "--", "vk_renderer_b200/csrc", "include") else "")
 with open(f"profiles/{tag}_traffic.json", "w") as f:
-    json.dump({"source": f"ncu --set full capture {tag} (bench.py --steps 2 --warmup 3, config 4); bytes per launch, mean over captured launches",
+    json.dump({"kernel_source_commit": commit, "source": f"ncu --set full capture {tag} (bench.py --steps 2 --warmup 3, config 4); bytes per launch, mean over captured launches",
                "dram_bytes_per_launch": {k: sum(v) / len(v) for k, v in traffic.items()}}, f, indent=1)
 print(open(f"profiles/{tag}_ncu_summary.md").read())
