@@ -35,7 +35,9 @@ W, H, S = 3840, 2160, 2048
 # submit thread: planning frame i+1 on the caller's thread overlaps issuing frame i's CUDA / NCCL calls
 # TRANSIENT_DEPTH: nothing reads the depth attachment after the frame (as in the reference), so its clear is fused into the
 # shading pass instead of being a pass of its own; the work is still done every frame
-BENCH_FLAGS = capi.CONFIG_TIME_GEOM_KERNEL | capi.CONFIG_SUBMIT_THREAD | capi.CONFIG_TRANSIENT_DEPTH
+# TRANSIENT_HDR: nor the RGBA16F draw image once it has been tone-mapped and blitted: its texel stays in registers (the f16
+# roundings are still applied); the presented 8-bit image — what the metric's tolerance is stated on — is written as before
+BENCH_FLAGS = capi.CONFIG_TIME_GEOM_KERNEL | capi.CONFIG_SUBMIT_THREAD | capi.CONFIG_TRANSIENT_DEPTH | capi.CONFIG_TRANSIENT_HDR
 SEED = 0xB2000000 + 4
 
 
@@ -262,7 +264,7 @@ def run_b200(args):
     r.sync()
     ms = e0.elapsed_time(e1)
     gk_timed_region_ms = r.timings()["geom_kernel"]      # mean over the frames of the timed region (event pair per frame)
-    r.set_flags(capi.CONFIG_TIMINGS | capi.CONFIG_SUBMIT_THREAD | capi.CONFIG_TRANSIENT_DEPTH)
+    r.set_flags(capi.CONFIG_TIMINGS | capi.CONFIG_SUBMIT_THREAD | capi.CONFIG_TRANSIENT_DEPTH | capi.CONFIG_TRANSIENT_HDR)
     for _ in range(3):
         step()
     r.sync()

@@ -156,6 +156,11 @@ typedef struct VkrConfig {
                                         the shading pass leaves it cleared for the next frame (no separate clear pass) and
                                         vkr_readback(VKR_TARGET_DEPTH / VKR_TARGET_PRIMID) is refused */
 
+#define VKR_CONFIG_TRANSIENT_HDR 16u /* the RGBA16F draw image is not kept either: once the frame has been tone-mapped and blitted
+                                       to the presented image nothing reads _drawImage (src/vk_engine_run.cpp:384-408,159-161), so
+                                       the shading pass keeps its texel in registers (both f16 roundings still applied, SURVEY A-12)
+                                       and vkr_readback / vkr_device_ptr(VKR_TARGET_HDR16F) is refused */
+
 /* struct EngineStats — src/vk_types.h:78-83. */
 typedef struct VkrEngineStats {
     float frametime;           /* ms, device time of the last completed frame (needs VKR_CONFIG_TIMINGS) */
@@ -253,8 +258,15 @@ int vkr_readback(VkrDevice* dev, VkrTarget what, void* dst, size_t dstBytes);   
  * and untouched until vkr_sync (or until FRAME_OVERLAP further frames have been drawn and synchronised).  With
  * VKR_CONFIG_SUBMIT_THREAD the request is queued behind its frame on the submit thread and the call returns at once; a failure is
  * reported by the next call on the device.  The presented image is double-buffered: the frame drawn FRAME_OVERLAP draws later
- * waits, on the device, for this copy before it overwrites the image. */
+ * waits, on the device, for this copy before it overwrites the image.  Only that image has this protection: VKR_TARGET_HDR16F
+ * and VKR_TARGET_SHADOW are refused here (VKR_ERROR_INVALID_ARGUMENT; use vkr_readback), VKR_TARGET_DEPTH / PRIMID are served
+ * synchronously. */
 int vkr_readback_async(VkrDevice* dev, VkrTarget what, void* pinnedDst, size_t dstBytes);
+/* Waits for everything issued.  Triangles too big for the lane that sets them up go through a queue of fixed capacity; when a
+ * frame overflows it (the device then skips what did not fit, never reads past the queue), vkr_sync — and vkr_readback, which
+ * syncs before it copies — grows the queues to what the frame asked for and draws the frame again before returning, so what
+ * is read back afterwards is complete.  VKR_ERROR_CAPACITY is returned (once) only if an asynchronous read-back had already
+ * been issued for the incomplete frame, or on a sharded device, where a redraw would need every rank (draw the frame again). */
 int vkr_sync(VkrDevice* dev);
 
 /* stats.triangle_count / drawcall_count — src/vk_engine_run.cpp:70-71,309-310. */

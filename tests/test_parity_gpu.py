@@ -173,3 +173,74 @@ def test_gpu_transient_depth_fuses_the_clear(vkr_lib):
             with pytest.raises(capi.VkrError):
                 r1.readback(capi.TARGET_DEPTH)
     r0.close(); r1.close()
+
+
+def test_gpu_transient_hdr_keeps_the_presented_image(vkr_lib):
+    """VKR_CONFIG_TRANSIENT_HDR: the RGBA16F draw image is not stored; the presented image (both f16 roundings applied in
+    registers) is bit-identical, its read-back is refused while the flag is set and works again once it is cleared."""
+    from vk_renderer_b200 import capi
+    import scenes as sc
+    for scene in ("basic_pcf", "transparent", "basic_sky_levels8"):
+        r0 = capi.Renderer(vkr_lib, "vkr", 320, 200, shadow_extent=256, flags=0)
+        r1 = capi.Renderer(vkr_lib, "vkr", 320, 200, shadow_extent=256, flags=capi.CONFIG_TRANSIENT_HDR | capi.CONFIG_TRANSIENT_DEPTH)
+        a, b = sc.SCENES[scene](r0), sc.SCENES[scene](r1)
+        for _ in range(2):
+            r0.draw(*a)
+            r1.draw(*b)
+            assert np.array_equal(r0.readback(capi.TARGET_RGBA8), r1.readback(capi.TARGET_RGBA8)), scene
+        with pytest.raises(capi.VkrError):
+            r1.readback(capi.TARGET_HDR16F)
+        r1.set_flags(0)
+        r1.draw(*b)
+        assert np.array_equal(r0.readback(capi.TARGET_HDR16F).view(np.uint16), r1.readback(capi.TARGET_HDR16F).view(np.uint16))
+        r0.close(); r1.close()
+
+
+def test_gpu_large_triangle_queue_overflow_is_repaired(ork_lib, tmp_path):
+    """Queues of 4 triangles / 8 items (VKR_QUEUE_CAPS, read at vkr_create): the scene's screen-filling triangles overflow both.
+    The device must not fault, and the frame that is read back must be the complete one (queues grown, frame redrawn)."""
+    import subprocess, sys, os, textwrap
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    ref = parity.render(ork_lib, "ork", "big_triangles", 320, 200, shadow_extent=128)
+    np.save(tmp_path / "prim.npy", ref["prim"]); np.save(tmp_path / "depth.npy", ref["depth"]); np.save(tmp_path / "rgba.npy", ref["rgba"])
+    code = textwrap.dedent(f"""
+        import sys, numpy as np
+        sys.path.insert(0, {root!r}); sys.path.insert(0, {os.path.join(root, 'tests')!r})
+        import vk_renderer_b200, parity, scenes
+        from vk_renderer_b200 import capi
+        lib = vk_renderer_b200.load()
+        for scene, shadow in (("big_triangles", 128), ("basic_pcf", 256), ("transparent", 256)):
+            r = capi.Renderer(lib, "vkr", 320, 200, shadow_extent=shadow)
+            r.draw(*scenes.SCENES[scene](r))
+            got = {{k: r.readback(v) for k, v in dict(prim=capi.TARGET_PRIMID, depth=capi.TARGET_DEPTH, rgba=capi.TARGET_RGBA8).items()}}
+            r.close()
+            r = capi.Renderer(lib, "vkr", 320, 200, shadow_extent=shadow)      # and with the submit thread + an asynchronous read-back first
+            import torch
+            land = torch.zeros((200, 320, 4), dtype=torch.uint8).pin_memory()
+            sd, objs, fp = scenes.SCENES[scene](r)
+            r.set_flags(capi.CONFIG_SUBMIT_THREAD)
+            r.draw(sd, objs, fp)
+            r.readback_async(capi.TARGET_RGBA8, land.data_ptr(), 320 * 200 * 4)
+            try:
+                r.sync()
+                reported = False
+            except capi.VkrError as e:
+                reported = e.code == capi.ERROR_CAPACITY
+            assert reported, "an asynchronous read-back of an overflowed frame must be reported"
+            r.draw(sd, objs, fp)
+            r.readback_async(capi.TARGET_RGBA8, land.data_ptr(), 320 * 200 * 4)
+            r.sync()
+            assert np.array_equal(land.numpy(), got["rgba"])
+            r.close()
+            if scene == "big_triangles":
+                for k in ("prim", "depth", "rgba"):
+                    want = np.load({str(tmp_path)!r} + "/" + k + ".npy")
+                    if k == "rgba":
+                        assert (np.abs(want.astype(int) - got[k].astype(int))[..., :3].max(-1) <= 1).mean() >= 0.999
+                    else:
+                        assert np.array_equal(want.view(np.uint32), got[k].view(np.uint32)), k
+        print("ok")
+    """)
+    env = dict(os.environ, VKR_QUEUE_CAPS="4,8")
+    out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0 and "ok" in out.stdout, out.stdout[-2000:] + out.stderr[-4000:]

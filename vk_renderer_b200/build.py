@@ -44,10 +44,12 @@ def build_libvkr(force=False, verbose=False):
         return target
     # -lnccl: the native sort-first sharding (vkr_shard_init).  In a process that has imported torch the loader
     # resolves libnccl.so.2 to the copy torch already mapped; a plain C++ host gets the system library.
-    cmd = ["nvcc", *NVCC_FLAGS, "-o", target, os.path.join(CSRC, "vkr_api.cu"), "-lnccl"]
+    # (written beside the target and moved into place: a snapshot of the tree never sees a half-written library)
+    cmd = ["nvcc", *NVCC_FLAGS, "-o", target + ".tmp", os.path.join(CSRC, "vkr_api.cu"), "-lnccl"]
     if verbose:
         cmd.insert(1, "-Xptxas=-v")
     subprocess.run(cmd, check=True)
+    os.replace(target + ".tmp", target)
     return target
 
 
@@ -61,8 +63,9 @@ def build_engine(force=False):
         return target
     srcs = [s for s in deps if s.endswith(".cpp")]
     cmd = ["g++", "-O2", "-std=c++20", "-ffp-contract=off", "-fPIC", "-shared", "-Wall", "-I", os.path.join(ROOT, "include"),
-           "-o", target, *srcs, "-L", PKG, "-lvkr", "-Wl,-rpath,$ORIGIN", "-lpthread", "-lz"]   # zlib: PNG images of glTF files
+           "-o", target + ".tmp", *srcs, "-L", PKG, "-lvkr", "-Wl,-rpath,$ORIGIN", "-lpthread", "-lz"]   # zlib: PNG images of glTF files
     subprocess.run(cmd, check=True)
+    os.replace(target + ".tmp", target)
     return target
 
 

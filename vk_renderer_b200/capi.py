@@ -25,6 +25,7 @@ CONFIG_TIMINGS = 1
 CONFIG_TIME_GEOM_KERNEL = 2
 CONFIG_SUBMIT_THREAD = 4
 CONFIG_TRANSIENT_DEPTH = 8
+CONFIG_TRANSIENT_HDR = 16
 T_NAMES = ["upload", "shadow", "geometry", "shade", "transparent", "post", "total", "geom_kernel", "large_kernel", "clear",
            "shadow_exchange", "frame_gather", "readback"]
 

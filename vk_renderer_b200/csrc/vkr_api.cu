@@ -175,7 +175,7 @@ enum { PASS_MAIN = 0, PASS_SHADOW = 1, PASS_TRANSPARENT = 2 };
 
 template <int PASS, class MakeSink>
 __device__ __forceinline__ void geometry_warp(const DChunk* __restrict__ chunk, const float* __restrict__ mvps, uint32_t mvpStride,
-                                              const RasterTarget& rt, const Queues& q, uint4* s_vtx, float* mvp, LargeTri* s_pend,
+                                              const RasterTarget& rt, const Queues& q, uint4* s_vtx, float* mvp, ParkedTri* s_park,
                                               const MakeSink& makeSink) {
     const int lane = threadIdx.x & 31;
     // the 80-byte cluster record is everything this warp needs: one level of indirection (uniform loads)
@@ -244,11 +244,14 @@ __device__ __forceinline__ void geometry_warp(const DChunk* __restrict__ chunk, 
     }
     __syncwarp();
 
-    // ---- phase 2: triangles.  Small ones are rasterised by the lane that set them up; the others are parked in the warp's
-    // shared-memory slots and then taken by the whole warp one at a time (vkr_raster.cuh, "warp-cooperative handling")
+    // ---- phase 2: triangles, 32 at a time.  Every lane sets one up and parks it in its shared-memory slot; then the warp
+    // works through what was parked: the candidate samples of all the small ones dealt evenly to the lanes (most triangles
+    // of a dense mesh cover one or two samples, a few cover dozens: a lane never waits for its neighbour's bounding box),
+    // the medium and large ones queued for large_raster_kernel (vkr_raster.cuh, "warp-cooperative handling")
     for (uint32_t base = 0; base < nTris; base += 32) {
         const uint32_t t = base + lane;
         int kind = 0;
+        uint32_t count = 0;
         if (t < nTris) {
             const uint32_t packed = __ldg(clTris + t);
             const uint32_t l0 = packed & 127u, l1 = (packed >> 7) & 127u, l2 = (packed >> 14) & 127u;
@@ -258,11 +261,19 @@ __device__ __forceinline__ void geometry_warp(const DChunk* __restrict__ chunk, 
             if (a.w | b.w | c.w) { g0 = __ldg(clVerts + l0); g1 = __ldg(clVerts + l1); g2 = __ldg(clVerts + l2); }
             // submission-order sequence number, whatever the processing order (the shadow pass has no use for it)
             const uint32_t seq = PASS == PASS_SHADOW ? 0u : seqBase + __ldg(clOrig + t);
-            kind = cluster_triangle_deferred(va, vb, vc, mvp, pos, g0, g1, g2, seq, rt, q, makeSink(seq), s_pend[lane]);
+            kind = cluster_triangle_deferred(va, vb, vc, mvp, pos, g0, g1, g2, seq, rt, q, makeSink(seq), s_park[lane], count);
+            if (kind != 3) count = 0;
         }
+        // inclusive prefix sum of the candidate counts
+        uint32_t incl = count;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= d) incl += v; }
+        const uint32_t total = __shfl_sync(0xFFFFFFFFu, incl, 31);
         const uint32_t medium = __ballot_sync(0xFFFFFFFFu, kind == 1);
         uint32_t large = __ballot_sync(0xFFFFFFFFu, kind == 2);
-        if ((medium | large) == 0u) continue;
+        __syncwarp();
+        if (total) raster_candidates_warp(s_park, incl, count, total, lane, makeSink);
+        if ((medium | large) == 0u) { __syncwarp(); continue; }
         if (medium) {
             // medium triangles (extent < 64 px): one queue item each, no tile enumeration; the slots of the whole warp are
             // claimed with one atomic per counter.  large_raster_kernel rasterises them with 32-bit edge functions.
@@ -271,10 +282,11 @@ __device__ __forceinline__ void geometry_warp(const DChunk* __restrict__ chunk, 
             firstTri = __shfl_sync(0xFFFFFFFFu, firstTri, 0); firstItem = __shfl_sync(0xFFFFFFFFu, firstItem, 0);
             if (kind == 1) {
                 const uint32_t k = (uint32_t)__popc(medium & ((1u << lane) - 1u));
-                if (firstTri + k >= q.triCap || firstItem + k >= q.itemCap) q.counters[2] = 1;
-                else {
-                    q.tris[firstTri + k] = s_pend[lane];
-                    LargeItem it; it.tri = firstTri + k; it.tx = ITEM_WHOLE; it.ty = ITEM_WHOLE;
+                const bool fits = firstTri + k < q.triCap && firstItem + k < q.itemCap;
+                if (fits) q.tris[firstTri + k] = s_park[lane].lt;
+                else q.counters[2] = 1;
+                if (firstItem + k < q.itemCap) {      // every claimed item slot below the capacity is written: a skip marker if the triangle did not fit
+                    LargeItem it; it.tri = fits ? firstTri + k : ITEM_SKIP; it.tx = ITEM_WHOLE; it.ty = ITEM_WHOLE;
                     q.items[firstItem + k] = it;
                 }
             }
@@ -283,7 +295,7 @@ __device__ __forceinline__ void geometry_warp(const DChunk* __restrict__ chunk, 
         while (large) {
             const int src = __ffs((int)large) - 1;
             large &= large - 1;
-            enqueue_large_coop(s_pend[src], q, lane);
+            enqueue_large_coop(s_park[src].lt, q, lane);
         }
         __syncwarp();
     }
@@ -299,13 +311,13 @@ __global__ void __launch_bounds__(GEOM_WARPS * 32, VKR_GEOM_MIN_CTAS) geometry_k
                                                                      const __grid_constant__ RasterTarget rt, const __grid_constant__ Queues q) {
     __shared__ uint4 s_vtxAll[GEOM_WARPS][CL_VERTS];
     __shared__ float s_mvpAll[GEOM_WARPS][16];
-    __shared__ LargeTri s_pendAll[GEOM_WARPS][32];
+    __shared__ ParkedTri s_parkAll[GEOM_WARPS][32];
     const uint32_t slot = blockIdx.x * GEOM_WARPS + (threadIdx.x >> 5);
     if (slot >= nClusters) return;
     const DChunk* chunk = chunks + __ldg(perm + slot);
     const int wi = threadIdx.x >> 5;
-    if (SHADOW) geometry_warp<PASS_SHADOW>(chunk, mvps, mvpStride, rt, q, s_vtxAll[wi], s_mvpAll[wi], s_pendAll[wi], MakeDepthSink{rt.depthBits, rt.width});
-    else geometry_warp<PASS_MAIN>(chunk, mvps, mvpStride, rt, q, s_vtxAll[wi], s_mvpAll[wi], s_pendAll[wi], MakeVisSink{rt.vis, rt.width});
+    if (SHADOW) geometry_warp<PASS_SHADOW>(chunk, mvps, mvpStride, rt, q, s_vtxAll[wi], s_mvpAll[wi], s_parkAll[wi], MakeDepthSink{rt.depthBits, rt.width});
+    else geometry_warp<PASS_MAIN>(chunk, mvps, mvpStride, rt, q, s_vtxAll[wi], s_mvpAll[wi], s_parkAll[wi], MakeVisSink{rt.vis, rt.width});
 }
 
 // ---- "Transparent" draws (the tail of the draw list), after every opaque fragment is in the visibility buffer
@@ -315,7 +327,7 @@ __global__ void __launch_bounds__(GEOM_WARPS * 32) geometry_transparent_kernel(c
                                                                               const __grid_constant__ ShadeConst sc, const __grid_constant__ ShadeBuffers sbIn) {
     __shared__ uint4 s_vtxAll[GEOM_WARPS][CL_VERTS];
     __shared__ float s_mvpAll[GEOM_WARPS][16];
-    __shared__ LargeTri s_pendAll[GEOM_WARPS][32];
+    __shared__ ParkedTri s_parkAll[GEOM_WARPS][32];
     __shared__ float s_lut[256];
     for (uint32_t i = threadIdx.x; i < 256u; i += GEOM_WARPS * 32) s_lut[i] = sbIn.srgbLut[i];
     __syncthreads();
@@ -325,7 +337,7 @@ __global__ void __launch_bounds__(GEOM_WARPS * 32) geometry_transparent_kernel(c
     const uint32_t slot = blockIdx.x * GEOM_WARPS + (threadIdx.x >> 5);
     if (slot >= nClusters) return;
     geometry_warp<PASS_TRANSPARENT>(chunks + firstCluster + slot, mvps, mvpStride, rt, q, s_vtxAll[threadIdx.x >> 5], s_mvpAll[threadIdx.x >> 5],
-                                    s_pendAll[threadIdx.x >> 5], MakeBlendSink{&sc, &s_sb});
+                                    s_parkAll[threadIdx.x >> 5], MakeBlendSink{&sc, &s_sb});
 }
 
 // ---- main pass, alpha-tested draws only (launched when the frame has any): one thread per triangle,
@@ -350,7 +362,7 @@ template <bool SHADOW>
 __global__ void __launch_bounds__(256) large_raster_kernel(const __grid_constant__ RasterTarget rt, const __grid_constant__ Queues q,
                                                            const __grid_constant__ AlphaCtx ax, int anyCutout) {
     __shared__ uint32_t s_queue[SHADOW ? 1 : 8][SHADOW ? 1 : RECT_QUEUE];      // cut-out items: compaction queue per warp
-    const uint32_t nItems = min(q.counters[1], q.itemCap);
+    const uint32_t nItems = min(q.counters[1], q.itemCap), nTris = min(q.counters[0], q.triCap);
     const uint32_t warpsPerGrid = (gridDim.x * blockDim.x) >> 5;
     const int lane = threadIdx.x & 31;
     // items differ in cost by orders of magnitude (an alpha-tested tile vs. an opaque sliver): warps take the next item
@@ -362,6 +374,7 @@ __global__ void __launch_bounds__(256) large_raster_kernel(const __grid_constant
         i = __shfl_sync(0xFFFFFFFFu, i, 0);
         if (i >= nItems) break;
         const LargeItem it = q.items[i];
+        if (it.tri >= nTris) continue;                   // skip marker of an overflowed frame (the host grows the queues and redraws)
         const LargeTri lt = q.tris[it.tri];
         const bool whole = it.tx == ITEM_WHOLE;          // medium triangle: its whole bounding box, 32-bit edge functions
         if (SHADOW) {
@@ -391,7 +404,7 @@ __global__ void __launch_bounds__(256) large_transparent_kernel(const __grid_con
     __syncthreads();
     ShadeBuffers sb = sbIn;
     sb.srgbLut = s_lut;
-    const uint32_t nItems = min(q.counters[1], q.itemCap);
+    const uint32_t nItems = min(q.counters[1], q.itemCap), nTris = min(q.counters[0], q.triCap);
     const uint32_t warpsPerGrid = (gridDim.x * blockDim.x) >> 5;
     const int lane = threadIdx.x & 31;
     (void)warpsPerGrid;
@@ -401,6 +414,7 @@ __global__ void __launch_bounds__(256) large_transparent_kernel(const __grid_con
         i = __shfl_sync(0xFFFFFFFFu, i, 0);
         if (i >= nItems) break;
         const LargeItem it = q.items[i];
+        if (it.tri >= nTris) continue;
         const LargeTri lt = q.tris[it.tri];
         BlendSink sink{&sc, &sb, lt.seq};
         raster_item_compact(lt, it, sink, lane, s_queue[threadIdx.x >> 5]);       // shading at raster time: keep the warp converged
@@ -453,6 +467,7 @@ struct FrameSlot {
     cudaEvent_t rendered = nullptr;
     cudaEvent_t copied = nullptr;       // last asynchronous read-back of this slot's presented image (copy stream)
     bool copyPending = false;
+    uint64_t copiedFrame = ~0ull;       // dev->frameIndex when that read-back was issued (= the frame it reads, plus one)
     // per-frame tables written on the device by expand_chunks_kernel (one set per frame in flight: the next frame's
     // tables are built on the upload stream while this frame's kernels still read theirs)
     DChunk* chunkBuf = nullptr; size_t chunkCap = 0;       // cluster table
@@ -506,6 +521,8 @@ struct VkrDevice {
     uint32_t* transCounters = nullptr;  // counters of the transparent pass (it reuses the main pass's queues)
     uint32_t* countersHost = nullptr;   // pinned mirror of the three passes' counters after the last frame (written by shade_kernel)
 
+    FramePlan* lastPlan = nullptr; size_t lastN = 0;   // the frame drawn last (vkr_sync redraws it after a queue overflow)
+    bool overflowReported = false;
     FrameSlot slots[VKR_FRAME_OVERLAP];
     uint64_t frameIndex = 0;
     int lastSlot = 0;
@@ -599,6 +616,13 @@ static int dev_alloc(VkrDevice* dev, void** p, size_t bytes) {
     dev->allocations.push_back(*p);
     return VKR_SUCCESS;
 }
+// Release one tracked allocation now (the caller has made sure the device no longer uses it).
+static void dev_free(VkrDevice* dev, void* p) {
+    if (!p) return;
+    for (auto it = dev->allocations.begin(); it != dev->allocations.end(); ++it)
+        if (*it == p) { dev->allocations.erase(it); break; }
+    cudaFree(p);
+}
 #define ALLOC(ptr, bytes)                                                    \
     do { int rc_ = dev_alloc(dev, (void**)&(ptr), (bytes)); if (rc_) return rc_; } while (0)
 
@@ -657,10 +681,14 @@ int vkr_create(const VkrConfig* cfg, VkrDevice** out) {
         ALLOC(dev->cubeDev, sizeof(DTexture) * 6);
         dev->texHost.assign(VKR_MAX_BINDLESS, DTexture{});
         dev->q.triCap = 1u << 20; dev->q.itemCap = 1u << 22;
+        dev->qShadow.triCap = 1u << 18; dev->qShadow.itemCap = 1u << 20;
+        if (const char* caps = std::getenv("VKR_QUEUE_CAPS")) {     // "tris,items": starting capacities of both queues (tests of the overflow path)
+            unsigned a = 0, b = 0;
+            if (std::sscanf(caps, "%u,%u", &a, &b) == 2 && a && b) { dev->q.triCap = dev->qShadow.triCap = a; dev->q.itemCap = dev->qShadow.itemCap = b; }
+        }
         ALLOC(dev->q.tris, sizeof(LargeTri) * dev->q.triCap);
         ALLOC(dev->q.items, sizeof(LargeItem) * dev->q.itemCap);
         ALLOC(dev->q.counters, 32);          // [0..3] see Queues; [4] work cursor of the large-triangle kernels
-        dev->qShadow.triCap = 1u << 18; dev->qShadow.itemCap = 1u << 20;
         ALLOC(dev->qShadow.tris, sizeof(LargeTri) * dev->qShadow.triCap);
         ALLOC(dev->qShadow.items, sizeof(LargeItem) * dev->qShadow.itemCap);
         ALLOC(dev->qShadow.counters, 32 * VKR_FRAME_OVERLAP);     // per frame in flight: frame i+1's shadow pass runs beside frame i's shading, which publishes frame i's
@@ -1026,17 +1054,24 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
     const size_t offObj = 0, offBase = align16(offObj + szObj), offSeq = align16(offBase + szBase), offShadow = align16(offSeq + szBase),
                  offSlot = align16(offShadow + szShadow);
     const size_t total = align16(offSlot + szSlot) + 16;
-    if (slot.chunkCap < nChunks) {
-        slot.chunkCap = std::max<size_t>((size_t)nChunks * 3 / 2, 1024);
-        ALLOC(slot.chunkBuf, slot.chunkCap * sizeof(DChunk));     // the previous tables are freed at destroy
-    }
-    if (slot.seqSlotCap < nSeqSlots) {
-        slot.seqSlotCap = std::max<size_t>((size_t)nSeqSlots * 3 / 2, 1024);
-        ALLOC(slot.chunkObjBuf, slot.seqSlotCap * sizeof(uint2));
-    }
-    if (slot.permCap < (size_t)passes * nChunks) {
-        slot.permCap = std::max<size_t>((size_t)passes * nChunks * 3 / 2, 1024);
-        ALLOC(slot.permBuf, slot.permCap * 4);
+    if (slot.chunkCap < nChunks || slot.seqSlotCap < nSeqSlots || slot.permCap < (size_t)passes * nChunks) {
+        // a table has to grow: the frame that last used this slot must have finished with the old one before it is released
+        if (dev->frameIndex >= VKR_FRAME_OVERLAP) CK(cudaEventSynchronize(slot.rendered));
+        if (slot.chunkCap < nChunks) {
+            dev_free(dev, slot.chunkBuf); slot.chunkBuf = nullptr;
+            slot.chunkCap = std::max<size_t>((size_t)nChunks * 3 / 2, 1024);
+            ALLOC(slot.chunkBuf, slot.chunkCap * sizeof(DChunk));
+        }
+        if (slot.seqSlotCap < nSeqSlots) {
+            dev_free(dev, slot.chunkObjBuf); slot.chunkObjBuf = nullptr;
+            slot.seqSlotCap = std::max<size_t>((size_t)nSeqSlots * 3 / 2, 1024);
+            ALLOC(slot.chunkObjBuf, slot.seqSlotCap * sizeof(uint2));
+        }
+        if (slot.permCap < (size_t)passes * nChunks) {
+            dev_free(dev, slot.permBuf); slot.permBuf = nullptr;
+            slot.permCap = std::max<size_t>((size_t)passes * nChunks * 3 / 2, 1024);
+            ALLOC(slot.permBuf, slot.permCap * 4);
+        }
     }
     if (dev->frameIndex >= VKR_FRAME_OVERLAP) {      // pinned buffer reuse: this is where a submit thread that runs ahead waits for the device
         const auto w0 = std::chrono::steady_clock::now();
@@ -1174,6 +1209,7 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
     sb.accum = nullptr;
     const bool transientDepth = (dev->flags & VKR_CONFIG_TRANSIENT_DEPTH) != 0;
     plan.sc.clearVis = transientDepth ? 1 : 0;
+    plan.sc.storeHdr = (dev->flags & VKR_CONFIG_TRANSIENT_HDR) ? 0 : 1;
     const ShadeConst& sc = plan.sc;
 
     // ---- "Transparent" draws: depth-tested against the finished opaque depth, shaded and summed (BlendSink)
@@ -1230,6 +1266,7 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
     mark(5);
     if (dev->hostProf && dev->frameIndex >= 16) dev->hostProfFrames++;
     dev->lastSlot = slotIdx;
+    dev->lastPlan = &plan; dev->lastN = n;
     dev->lastChunkObj = slot.chunkObjBuf; dev->lastObjects = dObjects;
     dev->frameIndex++;
     dev->stats.drawcall_count = (int32_t)n;
@@ -1250,6 +1287,40 @@ int vkr_sync(VkrDevice* dev) {
     CK(cudaStreamSynchronize(dev->copyStream));
     CK(cudaStreamSynchronize(dev->shadowStream));
     if (dev->gatherStream) CK(cudaStreamSynchronize(dev->gatherStream));
+    // A large-triangle queue overflowed in the last frame (its image misses those triangles): the counters kept counting, so
+    // they say how much room the frame needs.  Grow the queues and draw the frame again before returning; a read-back that
+    // follows sees the complete frame.  Only an asynchronous read-back ALREADY issued for the incomplete frame cannot be
+    // repaired: that is reported once as VKR_ERROR_CAPACITY (the queues have grown: drawing again succeeds).
+    for (int attempt = 0; attempt < 4 && (dev->countersHost[2] || dev->countersHost[6] || dev->countersHost[10]); ++attempt) {
+        if (dev->shardRanks > 1 || !dev->lastPlan) return dev->fail(VKR_ERROR_CAPACITY, "large-triangle queue overflow");   // (a sharded redraw would need every rank to take part)
+        const bool stale = dev->slots[dev->lastSlot].copiedFrame == dev->frameIndex;   // (synchronous read-backs sync first: see do_readback)
+        // a pass whose flag is set gets at least twice the room, and what its counters ask for plus a half (the shadow pass's
+        // counters are those of its last layer only, hence the doubling)
+        auto grow = [&](Queues& qq, uint32_t needTris, uint32_t needItems) -> int {
+            dev_free(dev, qq.tris); qq.tris = nullptr;
+            qq.triCap = std::max(needTris + needTris / 2, 2 * qq.triCap);
+            ALLOC(qq.tris, sizeof(LargeTri) * (size_t)qq.triCap);
+            dev_free(dev, qq.items); qq.items = nullptr;
+            qq.itemCap = std::max(needItems + needItems / 2, 2 * qq.itemCap);
+            ALLOC(qq.items, sizeof(LargeItem) * (size_t)qq.itemCap);
+            return VKR_SUCCESS;
+        };
+        int rc = VKR_SUCCESS;
+        if (dev->countersHost[2] || dev->countersHost[10])      // main and transparent passes share dev->q
+            rc = grow(dev->q, std::max(dev->countersHost[0], dev->countersHost[8]), std::max(dev->countersHost[1], dev->countersHost[9]));
+        if (rc == VKR_SUCCESS && dev->countersHost[6]) rc = grow(dev->qShadow, dev->countersHost[4], dev->countersHost[5]);
+        if (rc != VKR_SUCCESS) return rc;
+        std::memset(dev->countersHost, 0, 48);
+        rc = submit_frame(dev, *dev->lastPlan, dev->lastN);
+        if (rc != VKR_SUCCESS) return rc;
+        CK(cudaStreamSynchronize(dev->stream));
+        CK(cudaStreamSynchronize(dev->copyStream));
+        CK(cudaStreamSynchronize(dev->shadowStream));
+        if (stale && !dev->overflowReported) {
+            dev->overflowReported = true;
+            return dev->fail(VKR_ERROR_CAPACITY, "large-triangle queue overflow: an asynchronous read-back saw the incomplete frame (queues grown, frame redrawn)");
+        }
+    }
     if (dev->countersHost[2] || dev->countersHost[6] || dev->countersHost[10]) return dev->fail(VKR_ERROR_CAPACITY, "large-triangle queue overflow");
     if (dev->kevRecorded > dev->kevRead) {      // mean main-pass geometry kernel time over the frames since the last sync
         const uint64_t first = std::max(dev->kevRead, dev->kevRecorded > (uint64_t)VkrDevice::KRING ? dev->kevRecorded - VkrDevice::KRING : 0);
@@ -1331,6 +1402,7 @@ static int readback_issue(VkrDevice* dev, VkrTarget what, void* dst, size_t dstB
         FrameSlot& s = dev->slots[dev->lastSlot];
         CK(cudaEventRecord(s.copied, dev->copyStream));
         s.copyPending = true;
+        s.copiedFrame = dev->frameIndex;
     }
     return VKR_SUCCESS;
 }
@@ -1341,6 +1413,10 @@ static int do_readback(VkrDevice* dev, VkrTarget what, void* dst, size_t dstByte
     if (!dst || target_info(dev, what, &src, &bytes)) { DRAIN(dev); return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_readback: bad target"); }
     if (dstBytes < bytes) { DRAIN(dev); return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_readback: destination too small"); }
     const bool visTarget = what == VKR_TARGET_DEPTH || what == VKR_TARGET_PRIMID;
+    // only the presented image is double-buffered and fenced against the frames that follow: the draw image is one buffer and
+    // the shadow map is rewritten FRAME_OVERLAP frames later without waiting for a copy
+    if (!sync && (what == VKR_TARGET_HDR16F || what == VKR_TARGET_SHADOW)) { DRAIN(dev); return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_readback_async: only the presented image (RGBA8 / RGBA8_GATHERED / RGB8) can be read back asynchronously"); }
+    if (what == VKR_TARGET_HDR16F && (dev->flags & VKR_CONFIG_TRANSIENT_HDR)) { DRAIN(dev); return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_readback: the draw image is transient (VKR_CONFIG_TRANSIENT_HDR)"); }
     if (visTarget && (dev->flags & VKR_CONFIG_TRANSIENT_DEPTH)) { DRAIN(dev); return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_readback: the depth attachment is transient (VKR_CONFIG_TRANSIENT_DEPTH)"); }
     if (!sync && !visTarget && dev->worker.joinable() && (dev->flags & VKR_CONFIG_SUBMIT_THREAD)) {
         // behind the frame it reads, on the submit thread: the caller goes straight on to planning its next frame
@@ -1349,6 +1425,10 @@ static int do_readback(VkrDevice* dev, VkrTarget what, void* dst, size_t dstByte
     }
     DRAIN(dev);
     CK(cudaSetDevice(dev->device));
+    if (sync) {     // the frame is complete (and, had a queue overflowed, redrawn) before it is copied
+        const int rc0 = vkr_sync(dev);
+        if (rc0 != VKR_SUCCESS) return rc0;
+    }
     if (visTarget) {
         const size_t px = (size_t)dev->W * dev->H;
         if (!dev->scratch) ALLOC(dev->scratch, px * 4);
@@ -1394,7 +1474,8 @@ int vkr_device_ptr(VkrDevice* dev, VkrTarget what, void** ptr, size_t* bytes) {
     if (!dev || !ptr || !bytes) return VKR_ERROR_INVALID_ARGUMENT;
     DRAIN(dev);
     const void* src; size_t n;
-    if (target_info(dev, what, &src, &n) || !src) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_device_ptr: target has no linear buffer");
+    if (target_info(dev, what, &src, &n) || !src || (what == VKR_TARGET_HDR16F && (dev->flags & VKR_CONFIG_TRANSIENT_HDR)))
+        return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_device_ptr: target has no linear buffer");
     *ptr = const_cast<void*>(src); *bytes = n;
     return VKR_SUCCESS;
 }

@@ -264,6 +264,11 @@ inline std::string plan_frame(const VkrGPUSceneData* scene, const VkrRenderObjec
         {   // alpha-tested draw: its albedo texture has texels with alpha < 0.5 (DTexture flag bit2)
             const int aid = materials[ro.material].albedoID;
             if (aid >= 0 && aid < (int)textures.size() && textures[aid].data != nullptr && (textures[aid].flags & 4u)) { o.flags |= 2u; plan.anyCutout = true; }
+            // bit2: some texture the fragment shaders sample has a mip chain, i.e. the shading pass needs uv derivatives for
+            // this draw (a 1x1 or single-level image is sampled without them, vkr_shade.cuh texture2d)
+            const int ids[2] = {aid, materials[ro.material].metalRoughID};
+            for (int id : ids)
+                if (id >= 0 && id < (int)textures.size() && textures[id].data != nullptr && textures[id].levels > 1u && (textures[id].w | textures[id].h) != 1u) o.flags |= 4u;
         }
         plan.primBase[i] = (uint32_t)prim;
         plan.clusterBase[i] = (uint32_t)ncl;
@@ -415,6 +420,7 @@ inline std::string plan_frame(const VkrGPUSceneData* scene, const VkrRenderObjec
     sc.enableShadows = scene->sunlightColor[3] > 0.5f ? 1 : 0;
     sc.nobj = (uint32_t)n;
     sc.clearVis = 0;                   // set by the device library under VKR_CONFIG_TRANSIENT_DEPTH
+    sc.storeHdr = 1;                   // cleared by the device library under VKR_CONFIG_TRANSIENT_HDR
     sc.halfW = (float)W * 0.5f; sc.halfH = (float)H * 0.5f;
     sc.invHalfW = 1.0f / sc.halfW; sc.invHalfH = 1.0f / sc.halfH;
     {

@@ -76,7 +76,7 @@ struct DObject {
     uint32_t triCount;
     uint32_t primBase;        // dense submission-order id of this draw's first triangle (readback only)
     uint32_t material;
-    uint32_t flags;           // bit0: transparent pass, bit1: alpha-tested (albedo texture has alpha < 0.5)
+    uint32_t flags;           // bit0: transparent pass, bit1: alpha-tested (albedo texture has alpha < 0.5), bit2: a sampled texture has mips
     uint32_t pad[2];
 };
 static_assert(sizeof(DObject) % 16 == 0, "DObject array is read with 16-byte loads");
@@ -140,6 +140,7 @@ struct LargeTri {
 };
 struct LargeItem { uint32_t tri; uint16_t tx, ty; };   // (triangle, 64x64 tile); tx == ITEM_WHOLE: the triangle's whole bounding box
 static const uint16_t ITEM_WHOLE = 0xFFFFu;
+static const uint32_t ITEM_SKIP = 0xFFFFFFFFu;    // LargeItem::tri of a slot claimed by a triangle that did not fit the queue
 
 struct Queues {
     LargeTri* tris;
@@ -171,6 +172,7 @@ struct ShadeConst {
     int32_t enableBackground, enablePostprocess, enableSkybox, fragShader;
     int32_t shadowMode, enableShadows;
     int32_t clearVis;                  // VKR_CONFIG_TRANSIENT_DEPTH: every shaded pixel leaves VIS_CLEAR behind
+    int32_t storeHdr;                  // 0 under VKR_CONFIG_TRANSIENT_HDR: the RGBA16F draw image is not written (both roundings still applied)
     uint32_t nobj;
     float halfW, halfH;
     float invHalfW, invHalfH;

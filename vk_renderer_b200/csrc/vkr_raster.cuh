@@ -165,11 +165,29 @@ struct DepthSink {         // shadow pass: float bits, LESS_OR_EQUAL + write == 
 // cross(k-j, P-j) > 0.  Top-left rule (y down): an edge owns its boundary samples iff it is a
 // left edge (dy < 0) or a top edge (dy == 0 && dx > 0); otherwise the edge value must be >= 1.
 
-// Small triangles (extent < 2^14 sub-pixels): everything fits 32-bit integers.
-template <class Sink>
-VKR_HD void raster_small(const SetupTri& t, const Sink& sink) {
-    int32_t e[3], ax[3], by[3];
+// Small triangles (extent < 2^14 sub-pixels, bounding box <= SMALL_MAX x SMALL_MAX samples): everything fits 32-bit integers.
+// A set-up small triangle is a 64-byte record; its bounding box holds w*h CANDIDATE samples, numbered row by row, and
+// raster_candidate() decides and emits one of them.  The geometry kernel parks the records of a warp's 32 triangles in
+// shared memory and deals the candidates of all of them to the 32 lanes (geometry_warp: prefix sum of the counts, owner
+// search), so a lane with a 1-sample triangle does not wait for its neighbour's 4x4 box; the host emulation walks them in
+// order.  Both produce the values of the plain per-triangle loop: the edge functions at sample (ix, iy) of the box are
+// e + ix*ax + iy*by exactly (32-bit, no overflow: |e| < 2^30), and the depth is depth_at() of the same integers.
+struct alignas(16) FragRec {
+    int32_t e0, e1, e2;           // edge functions at the box's first sample, top-left bias folded in (covered iff all >= 0)
+    int32_t ax0, ax1, ax2;        // their steps per pixel in x ...
+    int32_t by0, by1, by2;        // ... and in y
+    uint32_t origin;              // first sample of the box: x | y << 16
+    uint32_t wdiv;                // box width w | ceil(2^16 / w) << 8   (k / w == (k * that) >> 16 for k < 256)
+    uint32_t seq;                 // primitive sequence number (sink key)
+    float z0, dzdx, dzdy;         // depth plane about vertex 0
+    uint32_t off;                 // (first sample - vertex 0) in sub-pixels: (x & 0xFFFF) | y << 16, two's complement 16-bit each
+};
+static_assert(sizeof(FragRec) == 64, "FragRec is read as four 16-byte words");
+
+// The record of a small triangle; returns its candidate count (w * h <= SMALL_MAX^2).
+VKR_HD uint32_t make_frag_rec(const SetupTri& t, uint32_t seq, FragRec& r) {
     const int32_t Px = t.bx0 * 256 + 128, Py = t.by0 * 256 + 128;
+    int32_t e[3], ax[3], by[3];
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
         const int j = (i + 1) % 3, k = (i + 2) % 3;
@@ -179,14 +197,41 @@ VKR_HD void raster_small(const SetupTri& t, const Sink& sink) {
         ax[i] = -dy * 256;
         by[i] = dx * 256;
     }
-    for (int32_t py = t.by0; py <= t.by1; ++py) {
-        int32_t f0 = e[0], f1 = e[1], f2 = e[2];
-        for (int32_t px = t.bx0; px <= t.bx1; ++px) {
-            if ((f0 | f1 | f2) >= 0) sink.put(px, py, depth_at(t.z0, t.dzdx, t.dzdy, t.X[0], t.Y[0], px, py));
-            f0 += ax[0]; f1 += ax[1]; f2 += ax[2];
-        }
-        e[0] += by[0]; e[1] += by[1]; e[2] += by[2];
-    }
+    r.e0 = e[0]; r.e1 = e[1]; r.e2 = e[2];
+    r.ax0 = ax[0]; r.ax1 = ax[1]; r.ax2 = ax[2];
+    r.by0 = by[0]; r.by1 = by[1]; r.by2 = by[2];
+    const uint32_t w = (uint32_t)(t.bx1 - t.bx0 + 1), h = (uint32_t)(t.by1 - t.by0 + 1);
+    r.origin = (uint32_t)t.bx0 | ((uint32_t)t.by0 << 16);
+    r.wdiv = w | (((65536u + w - 1u) / w) << 8);
+    r.seq = seq;
+    r.z0 = t.z0; r.dzdx = t.dzdx; r.dzdy = t.dzdy;
+    // |first sample - vertex 0| <= extent + half a pixel < 2^15 sub-pixels
+    r.off = ((uint32_t)(Px - t.X[0]) & 0xFFFFu) | ((uint32_t)(Py - t.Y[0]) << 16);
+    return w * h;
+}
+
+// Candidate k of the record: coverage, then depth and the sink.
+template <class Sink>
+VKR_HD void raster_candidate(const FragRec& r, uint32_t k, const Sink& sink) {
+    const uint32_t w = r.wdiv & 0xFFu;
+    const int32_t iy = (int32_t)((k * (r.wdiv >> 8)) >> 16), ix = (int32_t)k - iy * (int32_t)w;
+    const int32_t f0 = r.e0 + ix * r.ax0 + iy * r.by0, f1 = r.e1 + ix * r.ax1 + iy * r.by1, f2 = r.e2 + ix * r.ax2 + iy * r.by2;
+    if ((f0 | f1 | f2) < 0) return;
+    // depth_at() with (px*256 + 128 - X0) = off.x + ix*256
+    const int32_t ox = (int32_t)(int16_t)(r.off & 0xFFFFu), oy = (int32_t)(int16_t)(r.off >> 16);
+    const float fx = xmul(xi2f(ox + ix * 256), 1.0f / 256.0f), fy = xmul(xi2f(oy + iy * 256), 1.0f / 256.0f);
+    float z = xfma(r.dzdy, fy, xfma(r.dzdx, fx, r.z0));
+    if (!(z > 0.0f)) z = 0.0f;
+    if (z > 1.0f) z = 1.0f;
+    sink.put((int32_t)(r.origin & 0xFFFFu) + ix, (int32_t)(r.origin >> 16) + iy, z);
+}
+
+// One lane (or the host emulation) walking every candidate of its own triangle.
+template <class Sink>
+VKR_HD void raster_small(const SetupTri& t, const Sink& sink) {
+    FragRec r;
+    const uint32_t n = make_frag_rec(t, 0u, r);
+    for (uint32_t k = 0; k < n; ++k) raster_candidate(r, k, sink);
 }
 
 // General case: 64-bit edge functions E_i(P) = a_i*Px + b_i*Py + c_i.
@@ -484,15 +529,17 @@ VKR_HD void cluster_triangle(const CachedVtx& a, const CachedVtx& b, const Cache
 }
 
 #if defined(__CUDACC__)
-// ---- warp-cooperative handling of triangles that are too big for one lane ------------------------------------------
-// cluster_triangle_deferred does what cluster_triangle does for small triangles (in-lane raster) and clipped ones, and
-// returns 1 (medium: extent < 64 px, 32-bit edge functions suffice) or 2 (large) with the set-up triangle in `out` for
-// the others; the warp then takes those one at a time: medium ones are rasterised by all 32 lanes at once, large ones
-// have their 64x64 tiles enumerated by all 32 lanes and queued for large_raster_kernel.
+// ---- warp-cooperative handling: candidates of small triangles dealt to the lanes; triangles too big for that ------------
+// cluster_triangle_deferred sets one triangle up and says who rasterises it: 0 nobody (culled, or clipped and emitted on the
+// spot), 1 medium (extent < 64 px: the warp queues it as one item for large_raster_kernel's 32-bit path), 2 large (the warp
+// enumerates its 64x64 tiles and queues them), 3 small: its record is in `out.rec` and `count` candidates wait for the warp's
+// candidate stage (geometry_warp).  `out` is the lane's slot of the warp's shared memory.
+union ParkedTri { FragRec rec; LargeTri lt; };
+static_assert(sizeof(ParkedTri) == 64, "one 64-byte shared-memory slot per lane");
 template <class Sink>
 __device__ __forceinline__ int cluster_triangle_deferred(const CachedVtx& a, const CachedVtx& b, const CachedVtx& c, const float* __restrict__ mvp,
                                                          const float4* __restrict__ pos, uint32_t g0, uint32_t g1, uint32_t g2, uint32_t seq,
-                                                         const RasterTarget& rt, const Queues& q, const Sink& sink, LargeTri& out) {
+                                                         const RasterTarget& rt, const Queues& q, const Sink& sink, ParkedTri& out, uint32_t& count) {
     if ((a.flag | b.flag | c.flag) != 0u) {
         const float4 p0 = __ldg(pos + g0), p1 = __ldg(pos + g1), p2 = __ldg(pos + g2);
         clip_and_emit(transform_point(mvp, p0.x, p0.y, p0.z), transform_point(mvp, p1.x, p1.y, p1.z),
@@ -503,13 +550,44 @@ __device__ __forceinline__ int cluster_triangle_deferred(const CachedVtx& a, con
     const SnapVtx v0{a.X, a.Y, bits2f(a.zbits)}, v1{b.X, b.Y, bits2f(b.zbits)}, v2{c.X, c.Y, bits2f(c.zbits)};
     if (!setup_snapped(v0, v1, v2, rt, t)) return 0;
     const int32_t w = t.bx1 - t.bx0 + 1, h = t.by1 - t.by0 + 1;
-    if (w <= SMALL_MAX && h <= SMALL_MAX && t.ext < 16384) { raster_small(t, sink); return 0; }
+    if (w <= SMALL_MAX && h <= SMALL_MAX && t.ext < 16384) { count = make_frag_rec(t, seq, out.rec); return 3; }
+    LargeTri& lt = out.lt;
 #pragma unroll
-    for (int i = 0; i < 3; ++i) { out.X[i] = t.X[i]; out.Y[i] = t.Y[i]; }
-    out.z0 = t.z0; out.dzdx = t.dzdx; out.dzdy = t.dzdy;
-    out.bx0 = (int16_t)t.bx0; out.by0 = (int16_t)t.by0; out.bx1 = (int16_t)t.bx1; out.by1 = (int16_t)t.by1;
-    out.seq = seq;
+    for (int i = 0; i < 3; ++i) { lt.X[i] = t.X[i]; lt.Y[i] = t.Y[i]; }
+    lt.z0 = t.z0; lt.dzdx = t.dzdx; lt.dzdy = t.dzdy;
+    lt.bx0 = (int16_t)t.bx0; lt.by0 = (int16_t)t.by0; lt.bx1 = (int16_t)t.bx1; lt.by1 = (int16_t)t.by1;
+    lt.seq = seq;
     return t.ext < 16384 ? 1 : 2;
+}
+
+// The candidate stage: the 32 lanes of a warp hold `count` candidates each (records in `slots`); candidate j of the
+// concatenation goes to lane j mod 32.  `incl` is the inclusive prefix sum of the counts over the lanes, `total` its last
+// value; the owner of candidate j is the first lane whose inclusive sum exceeds j, found by a binary search with shuffles.
+template <class MakeSink>
+__device__ __forceinline__ void raster_candidates_warp(const ParkedTri* slots, uint32_t incl, uint32_t count, uint32_t total, int lane,
+                                                       const MakeSink& makeSink) {
+    const uint32_t excl = incl - count;
+    for (uint32_t jb = 0; jb < total; jb += 32) {
+        const uint32_t j = jb + lane;
+        const uint32_t jc = j < total ? j : total - 1u;
+        uint32_t owner = 0;
+#pragma unroll
+        for (int step = 16; step >= 1; step >>= 1) {
+            const uint32_t v = __shfl_sync(0xFFFFFFFFu, incl, (int)(owner + step - 1));
+            if (v <= jc) owner += step;
+        }
+        const uint32_t first = __shfl_sync(0xFFFFFFFFu, excl, (int)owner);
+        if (j < total) {
+            const uint4* rp = reinterpret_cast<const uint4*>(&slots[owner].rec);
+            const uint4 r0 = rp[0], r1 = rp[1], r2 = rp[2], r3 = rp[3];
+            FragRec r;
+            r.e0 = (int32_t)r0.x; r.e1 = (int32_t)r0.y; r.e2 = (int32_t)r0.z; r.ax0 = (int32_t)r0.w;
+            r.ax1 = (int32_t)r1.x; r.ax2 = (int32_t)r1.y; r.by0 = (int32_t)r1.z; r.by1 = (int32_t)r1.w;
+            r.by2 = (int32_t)r2.x; r.origin = r2.y; r.wdiv = r2.z; r.seq = r2.w;
+            r.z0 = __uint_as_float(r3.x); r.dzdx = __uint_as_float(r3.y); r.dzdy = __uint_as_float(r3.z); r.off = r3.w;
+            raster_candidate(r, j - first, makeSink(r.seq));
+        }
+    }
 }
 
 // All 32 lanes rasterise one medium triangle (warp-uniform `lt`): 8-pixel strips of its bounding box dealt to the lanes,

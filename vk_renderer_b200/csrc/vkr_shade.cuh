@@ -441,10 +441,13 @@ VKR_HD void fetch_fragment(const ShadeConst& sc, const ShadeBuffers& sb, uint32_
     float b[3], bx[3], by[3];
     const float ox = (px & 1) ? -1.0f : 1.0f, oy = (py & 1) ? -1.0f : 1.0f;
     bary_at(c, (cx - sc.halfW) * ihw, (cy - sc.halfH) * ihh, b);
-    // (skipping the two neighbour evaluations for materials without a mip chain was tried in r01z: finding that out costs
-    //  two dependent loads and range checks per pixel, more than the ~40 instructions it saves)
-    bary_at(c, (cx + ox - sc.halfW) * ihw, (cy - sc.halfH) * ihh, bx);
-    bary_at(c, (cx - sc.halfW) * ihw, (cy + oy - sc.halfH) * ihh, by);
+    // uv derivatives (the quad neighbours' barycentrics) only for draws with a mip-mapped texture: plan_frame sets bit 2 of
+    // the draw's flags, which sit in the record this function reads anyway
+    const bool derivs = (o.flags & 4u) != 0u;
+    if (derivs) {
+        bary_at(c, (cx + ox - sc.halfW) * ihw, (cy - sc.halfH) * ihh, bx);
+        bary_at(c, (cx - sc.halfW) * ihw, (cy + oy - sc.halfH) * ihh, by);
+    }
     const float4 a0 = VKR_LDG(o.attrA + i0), a1 = VKR_LDG(o.attrA + i1), a2 = VKR_LDG(o.attrA + i2);
     const float4 c0 = VKR_LDG(o.attrB + i0), c1 = VKR_LDG(o.attrB + i1), c2 = VKR_LDG(o.attrB + i2);
     f3 nobj = {b[0] * a0.x + b[1] * a1.x + b[2] * a2.x, b[0] * a0.y + b[1] * a1.y + b[2] * a2.y, b[0] * a0.z + b[1] * a1.z + b[2] * a2.z};
@@ -454,10 +457,13 @@ VKR_HD void fetch_fragment(const ShadeConst& sc, const ShadeBuffers& sb, uint32_
     fr.color = {b[0] * c0.x + b[1] * c1.x + b[2] * c2.x, b[0] * c0.y + b[1] * c1.y + b[2] * c2.y, b[0] * c0.z + b[1] * c1.z + b[2] * c2.z};
     fr.u = b[0] * a0.w + b[1] * a1.w + b[2] * a2.w;
     fr.v = b[0] * c0.w + b[1] * c1.w + b[2] * c2.w;
-    float ux = bx[0] * a0.w + bx[1] * a1.w + bx[2] * a2.w, vx = bx[0] * c0.w + bx[1] * c1.w + bx[2] * c2.w;
-    float uy = by[0] * a0.w + by[1] * a1.w + by[2] * a2.w, vy = by[0] * c0.w + by[1] * c1.w + by[2] * c2.w;
-    fr.dudx = (ux - fr.u) * ox; fr.dvdx = (vx - fr.v) * ox;
-    fr.dudy = (uy - fr.u) * oy; fr.dvdy = (vy - fr.v) * oy;
+    fr.dudx = fr.dvdx = fr.dudy = fr.dvdy = 0.0f;
+    if (derivs) {
+        float ux = bx[0] * a0.w + bx[1] * a1.w + bx[2] * a2.w, vx = bx[0] * c0.w + bx[1] * c1.w + bx[2] * c2.w;
+        float uy = by[0] * a0.w + by[1] * a1.w + by[2] * a2.w, vy = by[0] * c0.w + by[1] * c1.w + by[2] * c2.w;
+        fr.dudx = (ux - fr.u) * ox; fr.dvdx = (vx - fr.v) * ox;
+        fr.dudy = (uy - fr.u) * oy; fr.dvdy = (vy - fr.v) * oy;
+    }
     float4 pobj = make_float4(b[0] * p0.x + b[1] * p1.x + b[2] * p2.x, b[0] * p0.y + b[1] * p1.y + b[2] * p2.y,
                               b[0] * p0.z + b[1] * p1.z + b[2] * p2.z, 1.0f);
     float4 pw = xform(wm, pobj);
@@ -543,15 +549,17 @@ VKR_HD void shade_pixel(const ShadeConst& sc, const ShadeBuffers& sb, int px, in
         f3 m = tonemap_reinhard({r, g, b});
         r = round_f16(m.x); g = round_f16(m.y); b = round_f16(m.z); a = 1.0f;
     }
-    uint16_t* h = sb.hdr + pix * 4;
+    if (sc.storeHdr) {
+        uint16_t* h = sb.hdr + pix * 4;
 #if defined(__CUDA_ARCH__)
-    uint2 packed;
-    packed.x = (uint32_t)f2h_bits(r) | ((uint32_t)f2h_bits(g) << 16);
-    packed.y = (uint32_t)f2h_bits(b) | ((uint32_t)f2h_bits(a) << 16);
-    *reinterpret_cast<uint2*>(h) = packed;
+        uint2 packed;
+        packed.x = (uint32_t)f2h_bits(r) | ((uint32_t)f2h_bits(g) << 16);
+        packed.y = (uint32_t)f2h_bits(b) | ((uint32_t)f2h_bits(a) << 16);
+        *reinterpret_cast<uint2*>(h) = packed;
 #else
-    h[0] = f2h_bits(r); h[1] = f2h_bits(g); h[2] = f2h_bits(b); h[3] = f2h_bits(a);
+        h[0] = f2h_bits(r); h[1] = f2h_bits(g); h[2] = f2h_bits(b); h[3] = f2h_bits(a);
 #endif
+    }
     sb.rgba8[pix] = unorm8_fast(r) | (unorm8_fast(g) << 8) | (unorm8_fast(b) << 16) | (unorm8_fast(a) << 24);
     // a transient attachment: this is the next frame's clear.  Issued with the other stores, long after the key arrived — a
     // store right behind the load of the same address waits for that load (a DRAM round trip) with the warp's later loads
