@@ -460,7 +460,7 @@ def build_view_scene(r):
     views = []
     for k in range(NVIEWS):
         yaw = 2.0 * np.pi * k / NVIEWS
-        view = mg.camera_view((34.0 * np.sin(yaw), 9.0 + 3.0 * np.sin(3 * yaw), 34.0 * np.cos(yaw)), pitch=-0.28, yaw=-yaw)
+        view = mg.camera_view((34.0 * np.sin(yaw), 9.0 + 3.0 * np.sin(3 * yaw), 34.0 * np.cos(yaw)), pitch=-0.28, yaw=yaw)      # forward = (-sin yaw, ., -cos yaw): towards the orbit's centre
         views.append(capi.make_scene_data(view, proj, [L] * 4, shadow_mode=1, enable_shadows=True))
     fp = capi.default_frame_params(enableShadows=1, shadowMode=1, enablePostprocess=1, enableSkybox=0, enableBackground=1)
     tris = (len(pi) + 256 * len(si)) // 3

@@ -219,18 +219,16 @@ int emu_build_material(EmuDevice* d, const VkrMaterialConstants* p, int pass, ui
 
 }  // extern "C"
 
-// geometry_kernel phase 0 (cluster culling), the 8 corner lanes run as a loop
+// geometry_kernel phase 0 (cluster culling): the box test is expand_chunks_kernel's make_cull_rec, the occlusion test walks the
+// rectangle
 template <bool SHADOW>
-static bool cluster_survives(const DChunk& ch, const float* mvp, const RasterTarget& rt) {
-    CornerAcc a = corner_eval(mvp, ch.bmin, ch.bmax, 0);
-    for (int k = 1; k < 8; ++k) a = corner_merge(a, corner_eval(mvp, ch.bmin, ch.bmax, k));
-    const ClusterRect r = cluster_finalize(a, rt);
-    if (r.verdict == CLUSTER_CULLED) return false;
-    if (r.verdict == CLUSTER_DRAW) return true;
-    for (int32_t py = r.y0; py <= r.y1; ++py)
-        for (int32_t px = r.x0; px <= r.x1; ++px) {
+static bool cluster_survives(const CullRec& c, const RasterTarget& rt) {
+    if (c.verdict == CLUSTER_CULLED) return false;
+    if (c.verdict == CLUSTER_DRAW) return true;
+    for (int32_t py = c.y0; py <= c.y1; ++py)
+        for (int32_t px = c.x0; px <= c.x1; ++px) {
             const uint32_t stored = SHADOW ? rt.depthBits[(size_t)py * rt.width + px] : (uint32_t)(rt.vis[(size_t)py * rt.width + px] >> 32);
-            if (!depth_hides(stored, r.zminBits)) return true;
+            if (!depth_hides(stored, c.zminBits)) return true;
         }
     return false;
 }
@@ -257,10 +255,14 @@ static void run_pass(EmuDevice* d, const FramePlan& plan, RasterTarget rt, const
             }
         }
     for (unsigned slot = 0; slot < nChunks; ++slot) {        // geometry_kernel: one CTA per cluster, in processing order
-        const DChunk ch = d->chunks[perm ? perm[slot] : first + slot];
+        const uint32_t ci = perm ? perm[slot] : first + slot;
+        const DChunk ch = d->chunks[ci];
         if (PASS == 0 && (ch.flags & 2u)) continue;
         const float* mvp = mvps + (size_t)ch.obj * stride;
-        if (!cluster_survives<PASS == 1>(ch, mvp, rt)) { d->culled[SHADOW ? 1 : 0]++; continue; }
+        const DObject& ob = plan.objects[ch.obj];
+        const uint32_t lc = ci - plan.clusterBase[ch.obj];
+        const CullRec cr = make_cull_rec(mvp, ob.clBounds[2 * lc], ob.clBounds[2 * lc + 1], rt);
+        if (!cluster_survives<PASS == 1>(cr, rt)) { d->culled[SHADOW ? 1 : 0]++; continue; }
         const uint32_t nVerts = ch.counts & 0xFFFFu, nTris = ch.counts >> 16;
         const uint32_t* clVerts = ch.clVerts;
         for (uint32_t v = 0; v < nVerts; ++v) svtx[v] = cluster_vertex(mvp, ch.pos[clVerts[v]], rt);     // phase 1

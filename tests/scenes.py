@@ -68,7 +68,7 @@ def orbit_views(r, n_views, shadow_mode=1, radius=12.0, height=3.0):
     for k in range(n_views):
         yaw = 2.0 * np.pi * k / n_views
         pos = (radius * np.sin(yaw), height, radius * np.cos(yaw))
-        view = mg.camera_view(pos, pitch=-0.2, yaw=-yaw)
+        view = mg.camera_view(pos, pitch=-0.2, yaw=yaw)        # forward = (-sin yaw, ., -cos yaw): towards the centre
         out.append(capi.make_scene_data(view, proj, lights, shadow_mode=shadow_mode, enable_shadows=True,
                                         cascade_distances=(6.0, 12.0, 20.0, 100.0)))
     return out

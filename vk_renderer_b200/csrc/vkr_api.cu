@@ -143,21 +143,30 @@ __global__ void mip_blit_kernel(const uchar4* __restrict__ src, int sw, int sh, 
 }
 
 // ---- per-frame tables, written on the device from the per-draw prefixes (one CTA per draw):
-// the 80-byte cluster records, for every pass the processing order (geometry warp slot -> cluster, front to
-// back by draw), and the (draw, first triangle) pairs the shading pass looks up through seq >> 8.
+// the 48-byte cluster records, for every pass the processing order (geometry warp slot -> cluster, front to
+// back by draw) and the outcome of the cluster test (one thread per cluster projects the bounding box's eight corners
+// through the pass's matrix: frustum planes, pixel rectangle, nearest depth — CullRec), and the (draw, first triangle)
+// pairs the shading pass looks up through seq >> 8.
 __global__ void expand_chunks_kernel(const DObject* __restrict__ objects, const uint32_t* __restrict__ clusterBase,
                                      const uint32_t* __restrict__ seqSlotBase, const uint32_t* __restrict__ slotBase,
-                                     uint32_t nobj, uint32_t passes, uint32_t permStride,
-                                     DChunk* __restrict__ chunks, uint2* __restrict__ chunkObj, uint32_t* __restrict__ perm) {
+                                     const float* __restrict__ shadowMvp, uint32_t nobj, uint32_t passes, uint32_t permStride,
+                                     const __grid_constant__ RasterTarget rtMain, const __grid_constant__ RasterTarget rtShadow,
+                                     DChunk* __restrict__ chunks, uint2* __restrict__ chunkObj, uint32_t* __restrict__ perm,
+                                     CullRec* __restrict__ cull) {
     const uint32_t obj = blockIdx.x;
     const uint32_t base = clusterBase[obj], n = clusterBase[obj + 1] - base;
     const uint32_t sbase = seqSlotBase[obj], ns = seqSlotBase[obj + 1] - sbase;
     const DObject& o = objects[obj];
     for (uint32_t c = threadIdx.x; c < n; c += blockDim.x) {
         chunks[base + c] = make_chunk(o, obj, c, sbase);
+        const float4 bmin = o.clBounds[2 * c], bmax = o.clBounds[2 * c + 1];
         for (uint32_t p = 0; p < passes; ++p) {
             const uint32_t sb = slotBase[(size_t)p * nobj + obj];
             if (sb != 0xFFFFFFFFu) perm[(size_t)p * permStride + sb + c] = base + c;
+            // pass 0's record also serves the transparent pass, whose draws have no slot in the opaque order
+            if (sb != 0xFFFFFFFFu || p == 0)
+                cull[(size_t)p * permStride + base + c] = p == 0 ? make_cull_rec(o.mvp, bmin, bmax, rtMain)
+                                                                 : make_cull_rec(shadowMvp + ((size_t)(p - 1) * nobj + obj) * 16, bmin, bmax, rtShadow);
         }
     }
     for (uint32_t k = threadIdx.x; k < ns; k += blockDim.x) chunkObj[sbase + k] = make_uint2(obj, k * SEQ_SLOT);
@@ -174,61 +183,62 @@ enum { PASS_MAIN = 0, PASS_SHADOW = 1, PASS_TRANSPARENT = 2 };
 
 
 template <int PASS, class MakeSink>
-__device__ __forceinline__ void geometry_warp(const DChunk* __restrict__ chunk, const float* __restrict__ mvps, uint32_t mvpStride,
-                                              const RasterTarget& rt, const Queues& q, uint4* s_vtx, float* mvp, ParkedTri* s_park,
+__device__ __forceinline__ void geometry_warp(const DChunk* __restrict__ chunk, const CullRec* __restrict__ cullRec, const float* __restrict__ mvps, uint32_t mvpStride,
+                                              const RasterTarget& rt, const Queues& q, uint4* s_vtx, float* mvp, ParkedTri* s_park, uint2* s_map,
                                               const MakeSink& makeSink) {
     const int lane = threadIdx.x & 31;
-    // the 80-byte cluster record is everything this warp needs: one level of indirection (uniform loads)
+    // the 48-byte cluster record and the 16-byte outcome of its cluster test are everything this warp needs: one level of
+    // indirection (uniform loads)
     const uint4* chp = reinterpret_cast<const uint4*>(chunk);
-    const uint4 c0 = __ldg(chp), c1 = __ldg(chp + 1), c2 = __ldg(chp + 2);
+    const uint4 cr = __ldg(reinterpret_cast<const uint4*>(cullRec));
+    const uint4 c2 = __ldg(chp + 2);
+    const uint32_t obj = c2.x, seqBase = c2.y, counts = c2.z, flags = c2.w;
+    if (PASS == PASS_MAIN && (flags & 2u)) return;     // alpha-tested draw: geometry_cutout_kernel owns this cluster
+    const int32_t verdict = (int32_t)cr.w;
+    if (verdict == CLUSTER_CULLED) { if (lane == 0) atomicAdd(q.counters + 3, 1u); return; }
+    const uint4 c0 = __ldg(chp), c1 = __ldg(chp + 1);
     const float4* __restrict__ pos = reinterpret_cast<const float4*>(((uint64_t)c0.y << 32) | c0.x);
     const uint32_t* __restrict__ clVerts = reinterpret_cast<const uint32_t*>(((uint64_t)c0.w << 32) | c0.z);
     const uint32_t* __restrict__ clTris = reinterpret_cast<const uint32_t*>(((uint64_t)c1.y << 32) | c1.x);
     const uint32_t* __restrict__ clOrig = reinterpret_cast<const uint32_t*>(((uint64_t)c1.w << 32) | c1.z);
-    const uint32_t obj = c2.x, seqBase = c2.y, counts = c2.z, flags = c2.w;
-    if (PASS == PASS_MAIN && (flags & 2u)) return;     // alpha-tested draw: geometry_cutout_kernel owns this cluster
     const uint32_t nVerts = counts & 0xFFFFu, nTris = counts >> 16;
-    // the cluster's vertex indices are needed only if it survives the culls, but their latency hides behind them
+    // the cluster's vertex indices and matrix are needed only if it survives the occlusion test, but their latency hides behind it
     uint32_t vi[CL_VERTS / 32];
 #pragma unroll
     for (int k = 0; k < CL_VERTS / 32; ++k) vi[k] = lane + 32u * k < nVerts ? __ldg(clVerts + lane + 32u * k) : 0u;
     if (lane < 16) mvp[lane] = __ldg(mvps + (size_t)obj * mvpStride + lane);
-    __syncwarp();
 
-    // ---- phase 0: cluster culling (lane = clip component * 8 + box corner; all lanes end up with the result)
-    {
-        const float4 bmin = __ldg(reinterpret_cast<const float4*>(chp + 3)), bmax = __ldg(reinterpret_cast<const float4*>(chp + 4));
-        const CornerAcc a = corners_warp(mvp, bmin, bmax, lane);
-        const ClusterRect rect = cluster_finalize(a, rt);
-        bool culled = rect.verdict == CLUSTER_CULLED;
-        if (rect.verdict == CLUSTER_TEST) {
-            // the warp walks the rectangle as 8x16 pixel footprints (four independent loads per lane in flight) and stops
-            // at the first footprint with a visible pixel
-            bool hidden = true;
-            const int32_t lx = lane & 7, ly = lane >> 3;
-            for (int32_t by = rect.y0; by <= rect.y1 && hidden; by += 16) {
-                for (int32_t bx = rect.x0; bx <= rect.x1 && hidden; bx += 8) {
-                    const int32_t px = bx + lx;
-                    uint32_t stored[4];
+    // ---- phase 0: cluster culling.  The box test (frustum planes, pixel rectangle, nearest depth) was done once per frame by
+    // expand_chunks_kernel; what is left is the occlusion test against the LIVE depth / visibility buffer
+    if (verdict == CLUSTER_TEST) {
+        const int32_t rx0 = (int32_t)(cr.x & 0xFFFFu), ry0 = (int32_t)(cr.x >> 16), rx1 = (int32_t)(cr.y & 0xFFFFu), ry1 = (int32_t)(cr.y >> 16);
+        const uint32_t zminBits = cr.z;
+        // the warp walks the rectangle as 8x16 pixel footprints (four independent loads per lane in flight) and stops
+        // at the first footprint with a visible pixel
+        bool hidden = true;
+        const int32_t lx = lane & 7, ly = lane >> 3;
+        for (int32_t by = ry0; by <= ry1 && hidden; by += 16) {
+            for (int32_t bx = rx0; bx <= rx1 && hidden; bx += 8) {
+                const int32_t px = bx + lx;
+                uint32_t stored[4];
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        const int32_t py = by + ly + 4 * k;
-                        stored[k] = 0u;                                     // outside the rectangle: counts as hidden
-                        if (px <= rect.x1 && py <= rect.y1) {
-                            // .cg: read at L2, where the RED.MIN of the other warps land (stale L1 lines would only lose culls)
-                            if (PASS == PASS_SHADOW) stored[k] = __ldcg(rt.depthBits + (size_t)py * rt.width + px);
-                            else stored[k] = __ldcg(reinterpret_cast<const uint32_t*>(rt.vis + (size_t)py * rt.width + px) + 1);
-                        }
+                for (int k = 0; k < 4; ++k) {
+                    const int32_t py = by + ly + 4 * k;
+                    stored[k] = 0u;                                     // outside the rectangle: counts as hidden
+                    if (px <= rx1 && py <= ry1) {
+                        // .cg: read at L2, where the RED.MIN of the other warps land (stale L1 lines would only lose culls)
+                        if (PASS == PASS_SHADOW) stored[k] = __ldcg(rt.depthBits + (size_t)py * rt.width + px);
+                        else stored[k] = __ldcg(reinterpret_cast<const uint32_t*>(rt.vis + (size_t)py * rt.width + px) + 1);
                     }
-                    const bool h = depth_hides(stored[0], rect.zminBits) && depth_hides(stored[1], rect.zminBits) &&
-                                   depth_hides(stored[2], rect.zminBits) && depth_hides(stored[3], rect.zminBits);
-                    hidden = __all_sync(0xFFFFFFFFu, h);
                 }
+                const bool h = depth_hides(stored[0], zminBits) && depth_hides(stored[1], zminBits) &&
+                               depth_hides(stored[2], zminBits) && depth_hides(stored[3], zminBits);
+                hidden = __all_sync(0xFFFFFFFFu, h);
             }
-            culled = hidden;
         }
-        if (culled) { if (lane == 0) atomicAdd(q.counters + 3, 1u); return; }
+        if (hidden) { if (lane == 0) atomicAdd(q.counters + 3, 1u); return; }
     }
+    __syncwarp();
 
     // ---- phase 1: distinct vertices
     {
@@ -251,7 +261,7 @@ __device__ __forceinline__ void geometry_warp(const DChunk* __restrict__ chunk, 
     for (uint32_t base = 0; base < nTris; base += 32) {
         const uint32_t t = base + lane;
         int kind = 0;
-        uint32_t count = 0;
+        uint32_t count = 0, seqOfLane = 0;
         if (t < nTris) {
             const uint32_t packed = __ldg(clTris + t);
             const uint32_t l0 = packed & 127u, l1 = (packed >> 7) & 127u, l2 = (packed >> 14) & 127u;
@@ -261,6 +271,7 @@ __device__ __forceinline__ void geometry_warp(const DChunk* __restrict__ chunk, 
             if (a.w | b.w | c.w) { g0 = __ldg(clVerts + l0); g1 = __ldg(clVerts + l1); g2 = __ldg(clVerts + l2); }
             // submission-order sequence number, whatever the processing order (the shadow pass has no use for it)
             const uint32_t seq = PASS == PASS_SHADOW ? 0u : seqBase + __ldg(clOrig + t);
+            seqOfLane = seq;
             kind = cluster_triangle_deferred(va, vb, vc, mvp, pos, g0, g1, g2, seq, rt, q, makeSink(seq), s_park[lane], count);
             if (kind != 3) count = 0;
         }
@@ -272,7 +283,7 @@ __device__ __forceinline__ void geometry_warp(const DChunk* __restrict__ chunk, 
         const uint32_t medium = __ballot_sync(0xFFFFFFFFu, kind == 1);
         uint32_t large = __ballot_sync(0xFFFFFFFFu, kind == 2);
         __syncwarp();
-        if (total) raster_candidates_warp(s_park, incl, count, total, lane, makeSink);
+        if (total) raster_candidates_warp(s_park, s_map, incl - count, count, seqOfLane, total, lane, makeSink);
         if ((medium | large) == 0u) { __syncwarp(); continue; }
         if (medium) {
             // medium triangles (extent < 64 px): one queue item each, no tile enumeration; the slots of the whole warp are
@@ -306,28 +317,32 @@ struct MakeDepthSink { uint32_t* bits; int32_t width; __device__ DepthSink opera
 struct MakeBlendSink { const ShadeConst* sc; const ShadeBuffers* sb; __device__ BlendSink operator()(uint32_t seq) const { return BlendSink{sc, sb, seq}; } };
 
 template <bool SHADOW>
-__global__ void __launch_bounds__(GEOM_WARPS * 32, VKR_GEOM_MIN_CTAS) geometry_kernel(const DChunk* __restrict__ chunks, const uint32_t* __restrict__ perm,
+__global__ void __launch_bounds__(GEOM_WARPS * 32, VKR_GEOM_MIN_CTAS) geometry_kernel(const DChunk* __restrict__ chunks, const CullRec* __restrict__ cull, const uint32_t* __restrict__ perm,
                                                                      uint32_t nClusters, const float* __restrict__ mvps, uint32_t mvpStride,
                                                                      const __grid_constant__ RasterTarget rt, const __grid_constant__ Queues q) {
     __shared__ uint4 s_vtxAll[GEOM_WARPS][CL_VERTS];
     __shared__ float s_mvpAll[GEOM_WARPS][16];
     __shared__ ParkedTri s_parkAll[GEOM_WARPS][32];
+    __shared__ uint2 s_mapAll[GEOM_WARPS][32];
     const uint32_t slot = blockIdx.x * GEOM_WARPS + (threadIdx.x >> 5);
     if (slot >= nClusters) return;
-    const DChunk* chunk = chunks + __ldg(perm + slot);
+    const uint32_t ci = __ldg(perm + slot);
+    const DChunk* chunk = chunks + ci;
+    const CullRec* cullRec = cull + ci;
     const int wi = threadIdx.x >> 5;
-    if (SHADOW) geometry_warp<PASS_SHADOW>(chunk, mvps, mvpStride, rt, q, s_vtxAll[wi], s_mvpAll[wi], s_parkAll[wi], MakeDepthSink{rt.depthBits, rt.width});
-    else geometry_warp<PASS_MAIN>(chunk, mvps, mvpStride, rt, q, s_vtxAll[wi], s_mvpAll[wi], s_parkAll[wi], MakeVisSink{rt.vis, rt.width});
+    if (SHADOW) geometry_warp<PASS_SHADOW>(chunk, cullRec, mvps, mvpStride, rt, q, s_vtxAll[wi], s_mvpAll[wi], s_parkAll[wi], s_mapAll[wi], MakeDepthSink{rt.depthBits, rt.width});
+    else geometry_warp<PASS_MAIN>(chunk, cullRec, mvps, mvpStride, rt, q, s_vtxAll[wi], s_mvpAll[wi], s_parkAll[wi], s_mapAll[wi], MakeVisSink{rt.vis, rt.width});
 }
 
 // ---- "Transparent" draws (the tail of the draw list), after every opaque fragment is in the visibility buffer
-__global__ void __launch_bounds__(GEOM_WARPS * 32) geometry_transparent_kernel(const DChunk* __restrict__ chunks, uint32_t firstCluster, uint32_t nClusters,
+__global__ void __launch_bounds__(GEOM_WARPS * 32) geometry_transparent_kernel(const DChunk* __restrict__ chunks, const CullRec* __restrict__ cull, uint32_t firstCluster, uint32_t nClusters,
                                                                               const float* __restrict__ mvps, uint32_t mvpStride,
                                                                               const __grid_constant__ RasterTarget rt, const __grid_constant__ Queues q,
                                                                               const __grid_constant__ ShadeConst sc, const __grid_constant__ ShadeBuffers sbIn) {
     __shared__ uint4 s_vtxAll[GEOM_WARPS][CL_VERTS];
     __shared__ float s_mvpAll[GEOM_WARPS][16];
     __shared__ ParkedTri s_parkAll[GEOM_WARPS][32];
+    __shared__ uint2 s_mapAll[GEOM_WARPS][32];
     __shared__ float s_lut[256];
     for (uint32_t i = threadIdx.x; i < 256u; i += GEOM_WARPS * 32) s_lut[i] = sbIn.srgbLut[i];
     __syncthreads();
@@ -336,8 +351,8 @@ __global__ void __launch_bounds__(GEOM_WARPS * 32) geometry_transparent_kernel(c
     __syncthreads();
     const uint32_t slot = blockIdx.x * GEOM_WARPS + (threadIdx.x >> 5);
     if (slot >= nClusters) return;
-    geometry_warp<PASS_TRANSPARENT>(chunks + firstCluster + slot, mvps, mvpStride, rt, q, s_vtxAll[threadIdx.x >> 5], s_mvpAll[threadIdx.x >> 5],
-                                    s_parkAll[threadIdx.x >> 5], MakeBlendSink{&sc, &s_sb});
+    geometry_warp<PASS_TRANSPARENT>(chunks + firstCluster + slot, cull + firstCluster + slot, mvps, mvpStride, rt, q, s_vtxAll[threadIdx.x >> 5], s_mvpAll[threadIdx.x >> 5],
+                                    s_parkAll[threadIdx.x >> 5], s_mapAll[threadIdx.x >> 5], MakeBlendSink{&sc, &s_sb});
 }
 
 // ---- main pass, alpha-tested draws only (launched when the frame has any): one thread per triangle,
@@ -473,6 +488,7 @@ struct FrameSlot {
     DChunk* chunkBuf = nullptr; size_t chunkCap = 0;       // cluster table
     uint2* chunkObjBuf = nullptr; size_t seqSlotCap = 0;   // seq >> 8 -> (draw, first triangle)
     uint32_t* permBuf = nullptr; size_t permCap = 0;       // (1 + shadow layers) x clusters: processing order per pass
+    CullRec* cullBuf = nullptr;                            // (1 + shadow layers) x clusters: outcome of the cluster test per pass (same capacity)
 };
 
 struct VkrDevice {
@@ -1069,8 +1085,10 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
         }
         if (slot.permCap < (size_t)passes * nChunks) {
             dev_free(dev, slot.permBuf); slot.permBuf = nullptr;
+            dev_free(dev, slot.cullBuf); slot.cullBuf = nullptr;
             slot.permCap = std::max<size_t>((size_t)passes * nChunks * 3 / 2, 1024);
             ALLOC(slot.permBuf, slot.permCap * 4);
+            ALLOC(slot.cullBuf, slot.permCap * sizeof(CullRec));
         }
     }
     if (dev->frameIndex >= VKR_FRAME_OVERLAP) {      // pinned buffer reuse: this is where a submit thread that runs ahead waits for the device
@@ -1101,8 +1119,8 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
     const float* dShadowMvp = (const float*)(dp + offShadow);
     const uint32_t* dPerm = slot.permBuf;
     if (n) {   // the frame's tables, on the upload stream too: neither the main nor the shadow stream has to wait for the other
-        expand_chunks_kernel<<<(unsigned)n, 64, 0, dev->upStream>>>(dObjects, (const uint32_t*)(dp + offBase), (const uint32_t*)(dp + offSeq), (const uint32_t*)(dp + offSlot), (uint32_t)n, passes,
-                                                                    nChunks, slot.chunkBuf, slot.chunkObjBuf, slot.permBuf);
+        expand_chunks_kernel<<<(unsigned)n, 64, 0, dev->upStream>>>(dObjects, (const uint32_t*)(dp + offBase), (const uint32_t*)(dp + offSeq), (const uint32_t*)(dp + offSlot), dShadowMvp,
+                                                                    (uint32_t)n, passes, nChunks, plan.mainTarget, plan.shadowTarget, slot.chunkBuf, slot.chunkObjBuf, slot.permBuf, slot.cullBuf);
         dev->launches += 1;
     }
     CK(cudaEventRecord(slot.uploaded, dev->upStream));
@@ -1136,7 +1154,7 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
             dev->launches += 1;
             const unsigned shadowSlots = plan.passSlots[1 + layer];
             if (shadowSlots) {
-                geometry_kernel<true><<<(shadowSlots + GEOM_WARPS - 1) / GEOM_WARPS, GEOM_WARPS * 32, 0, ss>>>(dChunks, dPerm + (size_t)(1 + layer) * nChunks, shadowSlots,
+                geometry_kernel<true><<<(shadowSlots + GEOM_WARPS - 1) / GEOM_WARPS, GEOM_WARPS * 32, 0, ss>>>(dChunks, slot.cullBuf + (size_t)(1 + layer) * nChunks, dPerm + (size_t)(1 + layer) * nChunks, shadowSlots,
                                                                                                       dShadowMvp + (size_t)layer * n * 16, 16u, rt, qs);
                 large_raster_kernel<true><<<largeGrid, 256, 0, ss>>>(rt, qs, AlphaCtx{}, 0);
                 dev->launches += 2;
@@ -1184,7 +1202,7 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
         const unsigned opaqueChunks = plan.opaqueClusters, mainSlots = plan.passSlots[0];
         if (opaqueChunks) {
             if (mainSlots)
-                geometry_kernel<false><<<(mainSlots + GEOM_WARPS - 1) / GEOM_WARPS, GEOM_WARPS * 32, 0, st>>>(dChunks, dPerm, mainSlots, (const float*)dObjects,
+                geometry_kernel<false><<<(mainSlots + GEOM_WARPS - 1) / GEOM_WARPS, GEOM_WARPS * 32, 0, st>>>(dChunks, slot.cullBuf, dPerm, mainSlots, (const float*)dObjects,
                                                                                                             (uint32_t)(sizeof(DObject) / 4), rt, dev->q);
             if (timing) CK(cudaEventRecord(dev->tev[4], st));
             if (kpair) { CK(cudaEventRecord(kpair[1], st)); dev->kevRecorded++; }
@@ -1225,7 +1243,7 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
         RasterTarget rt = plan.mainTarget;
         rt.vis = dev->vis;
         geometry_transparent_kernel<<<(transChunks + GEOM_WARPS - 1) / GEOM_WARPS, GEOM_WARPS * 32, 0, st>>>(
-            dChunks, plan.opaqueClusters, transChunks, (const float*)dObjects, (uint32_t)(sizeof(DObject) / 4), rt, qt, sc, sb);
+            dChunks, slot.cullBuf, plan.opaqueClusters, transChunks, (const float*)dObjects, (uint32_t)(sizeof(DObject) / 4), rt, qt, sc, sb);
         large_transparent_kernel<<<largeGrid, 256, 0, st>>>(rt, qt, sc, sb);
         dev->launches += 2;
     }

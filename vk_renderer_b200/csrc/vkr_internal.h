@@ -102,9 +102,17 @@ struct DChunk {               // what one geometry warp needs, written on the de
     uint32_t obj, seqBase;    // draw; first sequence number of the draw
     uint32_t counts;          // vertexCount | triCount << 16
     uint32_t flags;           // draw flags (bit0 transparent, bit1 alpha-tested)
-    float4 bmin, bmax;        // object-space bounding box of the cluster
 };
-static_assert(sizeof(DChunk) == 80, "DChunk is read as five 16-byte words");
+static_assert(sizeof(DChunk) == 48, "DChunk is read as three 16-byte words");
+// The outcome of the cluster test of one (pass, cluster), computed once per frame by expand_chunks_kernel from the cluster's
+// bounding box (one THREAD per cluster there; in the geometry kernel it would be one warp per cluster): the warp reads 16 bytes
+// instead of projecting eight corners.
+struct CullRec {
+    int16_t x0, y0, x1, y1;   // pixel rectangle the cluster can touch (valid for verdict CLUSTER_TEST)
+    uint32_t zminBits;        // nearest depth it can write, as float bits
+    int32_t verdict;          // CLUSTER_CULLED / CLUSTER_DRAW / CLUSTER_TEST (vkr_raster.cuh)
+};
+static_assert(sizeof(CullRec) == 16, "CullRec is read as one 16-byte word");
 // Cluster c of draw `obj` whose first sequence slot is `seqSlot`.
 VKR_HD DChunk make_chunk(const DObject& o, uint32_t obj, uint32_t c, uint32_t seqSlot) {
     const uint2 info = o.clInfo[c];
@@ -113,7 +121,6 @@ VKR_HD DChunk make_chunk(const DObject& o, uint32_t obj, uint32_t c, uint32_t se
     ch.clOrig = o.clOrig + (size_t)c * CL_TRIS;
     ch.obj = obj; ch.seqBase = seqSlot * SEQ_SLOT; ch.counts = info.y;
     ch.flags = o.flags;
-    ch.bmin = o.clBounds[2 * c]; ch.bmax = o.clBounds[2 * c + 1];
     return ch;
 }
 

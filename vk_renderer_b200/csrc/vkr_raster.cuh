@@ -176,16 +176,15 @@ struct alignas(16) FragRec {
     int32_t e0, e1, e2;           // edge functions at the box's first sample, top-left bias folded in (covered iff all >= 0)
     int32_t ax0, ax1, ax2;        // their steps per pixel in x ...
     int32_t by0, by1, by2;        // ... and in y
+    float z0, dzdx, dzdy;         // depth plane about vertex 0
+    float fx0, fy0;               // (first sample - vertex 0) in pixels: a multiple of 1/256 below 2^7, exact in f32
     uint32_t origin;              // first sample of the box: x | y << 16
     uint32_t wdiv;                // box width w | ceil(2^16 / w) << 8   (k / w == (k * that) >> 16 for k < 256)
-    uint32_t seq;                 // primitive sequence number (sink key)
-    float z0, dzdx, dzdy;         // depth plane about vertex 0
-    uint32_t off;                 // (first sample - vertex 0) in sub-pixels: (x & 0xFFFF) | y << 16, two's complement 16-bit each
 };
 static_assert(sizeof(FragRec) == 64, "FragRec is read as four 16-byte words");
 
 // The record of a small triangle; returns its candidate count (w * h <= SMALL_MAX^2).
-VKR_HD uint32_t make_frag_rec(const SetupTri& t, uint32_t seq, FragRec& r) {
+VKR_HD uint32_t make_frag_rec(const SetupTri& t, FragRec& r) {
     const int32_t Px = t.bx0 * 256 + 128, Py = t.by0 * 256 + 128;
     int32_t e[3], ax[3], by[3];
 #pragma unroll
@@ -203,10 +202,11 @@ VKR_HD uint32_t make_frag_rec(const SetupTri& t, uint32_t seq, FragRec& r) {
     const uint32_t w = (uint32_t)(t.bx1 - t.bx0 + 1), h = (uint32_t)(t.by1 - t.by0 + 1);
     r.origin = (uint32_t)t.bx0 | ((uint32_t)t.by0 << 16);
     r.wdiv = w | (((65536u + w - 1u) / w) << 8);
-    r.seq = seq;
     r.z0 = t.z0; r.dzdx = t.dzdx; r.dzdy = t.dzdy;
-    // |first sample - vertex 0| <= extent + half a pixel < 2^15 sub-pixels
-    r.off = ((uint32_t)(Px - t.X[0]) & 0xFFFFu) | ((uint32_t)(Py - t.Y[0]) << 16);
+    // depth_at() divides (sample - vertex 0), an integer number of sub-pixels below 2^15, by 256: exact, and so is adding the
+    // sample's integer offset inside the box afterwards (the sum still has at most 15 + 8 significant bits)
+    r.fx0 = xmul(xi2f(Px - t.X[0]), 1.0f / 256.0f);
+    r.fy0 = xmul(xi2f(Py - t.Y[0]), 1.0f / 256.0f);
     return w * h;
 }
 
@@ -217,20 +217,36 @@ VKR_HD void raster_candidate(const FragRec& r, uint32_t k, const Sink& sink) {
     const int32_t iy = (int32_t)((k * (r.wdiv >> 8)) >> 16), ix = (int32_t)k - iy * (int32_t)w;
     const int32_t f0 = r.e0 + ix * r.ax0 + iy * r.by0, f1 = r.e1 + ix * r.ax1 + iy * r.by1, f2 = r.e2 + ix * r.ax2 + iy * r.by2;
     if ((f0 | f1 | f2) < 0) return;
-    // depth_at() with (px*256 + 128 - X0) = off.x + ix*256
-    const int32_t ox = (int32_t)(int16_t)(r.off & 0xFFFFu), oy = (int32_t)(int16_t)(r.off >> 16);
-    const float fx = xmul(xi2f(ox + ix * 256), 1.0f / 256.0f), fy = xmul(xi2f(oy + iy * 256), 1.0f / 256.0f);
+    // depth_at(): fx = (sample - vertex 0) / 256 = fx0 + ix, both exact (see make_frag_rec)
+    const float fx = xadd(r.fx0, xi2f(ix)), fy = xadd(r.fy0, xi2f(iy));
     float z = xfma(r.dzdy, fy, xfma(r.dzdx, fx, r.z0));
     if (!(z > 0.0f)) z = 0.0f;
     if (z > 1.0f) z = 1.0f;
     sink.put((int32_t)(r.origin & 0xFFFFu) + ix, (int32_t)(r.origin >> 16) + iy, z);
 }
 
+// The plain per-triangle double loop (incremental edge functions): what the candidate stage replaces.  Kept for the A/B
+// (-DVKR_RASTER_PER_LANE: every lane rasterises its own triangle and waits for the largest box of the warp).
+template <class Sink>
+VKR_HD void raster_small_loop(const SetupTri& t, const Sink& sink) {
+    FragRec r;
+    make_frag_rec(t, r);
+    int32_t e0 = r.e0, e1 = r.e1, e2 = r.e2;
+    for (int32_t py = t.by0; py <= t.by1; ++py) {
+        int32_t f0 = e0, f1 = e1, f2 = e2;
+        for (int32_t px = t.bx0; px <= t.bx1; ++px) {
+            if ((f0 | f1 | f2) >= 0) sink.put(px, py, depth_at(t.z0, t.dzdx, t.dzdy, t.X[0], t.Y[0], px, py));
+            f0 += r.ax0; f1 += r.ax1; f2 += r.ax2;
+        }
+        e0 += r.by0; e1 += r.by1; e2 += r.by2;
+    }
+}
+
 // One lane (or the host emulation) walking every candidate of its own triangle.
 template <class Sink>
 VKR_HD void raster_small(const SetupTri& t, const Sink& sink) {
     FragRec r;
-    const uint32_t n = make_frag_rec(t, 0u, r);
+    const uint32_t n = make_frag_rec(t, r);
     for (uint32_t k = 0; k < n; ++k) raster_candidate(r, k, sink);
 }
 
@@ -550,7 +566,11 @@ __device__ __forceinline__ int cluster_triangle_deferred(const CachedVtx& a, con
     const SnapVtx v0{a.X, a.Y, bits2f(a.zbits)}, v1{b.X, b.Y, bits2f(b.zbits)}, v2{c.X, c.Y, bits2f(c.zbits)};
     if (!setup_snapped(v0, v1, v2, rt, t)) return 0;
     const int32_t w = t.bx1 - t.bx0 + 1, h = t.by1 - t.by0 + 1;
-    if (w <= SMALL_MAX && h <= SMALL_MAX && t.ext < 16384) { count = make_frag_rec(t, seq, out.rec); return 3; }
+#if defined(VKR_RASTER_PER_LANE)
+    if (w <= SMALL_MAX && h <= SMALL_MAX && t.ext < 16384) { raster_small_loop(t, sink); return 0; }
+#else
+    if (w <= SMALL_MAX && h <= SMALL_MAX && t.ext < 16384) { count = make_frag_rec(t, out.rec); return 3; }
+#endif
     LargeTri& lt = out.lt;
 #pragma unroll
     for (int i = 0; i < 3; ++i) { lt.X[i] = t.X[i]; lt.Y[i] = t.Y[i]; }
@@ -560,32 +580,34 @@ __device__ __forceinline__ int cluster_triangle_deferred(const CachedVtx& a, con
     return t.ext < 16384 ? 1 : 2;
 }
 
-// The candidate stage: the 32 lanes of a warp hold `count` candidates each (records in `slots`); candidate j of the
-// concatenation goes to lane j mod 32.  `incl` is the inclusive prefix sum of the counts over the lanes, `total` its last
-// value; the owner of candidate j is the first lane whose inclusive sum exceeds j, found by a binary search with shuffles.
+// The candidate stage: the 32 lanes of a warp hold `count` candidates each (records in their `slots`); candidate j of the
+// concatenation goes to lane j mod 32, 32 candidates per round.  `excl` is the exclusive prefix sum of the counts over the
+// lanes, `total` the sum.  The non-empty triangles are numbered densely, `map[d]` = (lane | first candidate << 8, seq) of the
+// d-th one.  In the round that starts at candidate jb, the triangles whose first candidate falls inside the round set a bit at
+// that position (one warp-wide OR, REDUX); the owner of the candidate on lane L is then the triangle number
+// (triangles that start before the round) + (bits at positions <= L) - 1: no search.
 template <class MakeSink>
-__device__ __forceinline__ void raster_candidates_warp(const ParkedTri* slots, uint32_t incl, uint32_t count, uint32_t total, int lane,
-                                                       const MakeSink& makeSink) {
-    const uint32_t excl = incl - count;
+__device__ __forceinline__ void raster_candidates_warp(const ParkedTri* slots, uint2* map, uint32_t excl, uint32_t count, uint32_t seq, uint32_t total,
+                                                       int lane, const MakeSink& makeSink) {
+    const uint32_t nonEmpty = __ballot_sync(0xFFFFFFFFu, count != 0u);
+    if (count) map[__popc(nonEmpty & ((1u << lane) - 1u))] = make_uint2((uint32_t)lane | (excl << 8), seq);
+    __syncwarp();
+    const uint32_t below = 0xFFFFFFFFu >> (31 - lane);                  // positions <= lane
     for (uint32_t jb = 0; jb < total; jb += 32) {
+        const uint32_t pos = excl - jb;                                  // (wraps for triangles that started earlier: no bit)
+        const uint32_t heads = __reduce_or_sync(0xFFFFFFFFu, (count != 0u && pos < 32u) ? 1u << pos : 0u);
+        const uint32_t before = (uint32_t)__popc(__ballot_sync(0xFFFFFFFFu, count != 0u && excl < jb));
         const uint32_t j = jb + lane;
-        const uint32_t jc = j < total ? j : total - 1u;
-        uint32_t owner = 0;
-#pragma unroll
-        for (int step = 16; step >= 1; step >>= 1) {
-            const uint32_t v = __shfl_sync(0xFFFFFFFFu, incl, (int)(owner + step - 1));
-            if (v <= jc) owner += step;
-        }
-        const uint32_t first = __shfl_sync(0xFFFFFFFFu, excl, (int)owner);
         if (j < total) {
-            const uint4* rp = reinterpret_cast<const uint4*>(&slots[owner].rec);
+            const uint2 m = map[before + (uint32_t)__popc(heads & below) - 1u];
+            const uint4* rp = reinterpret_cast<const uint4*>(&slots[m.x & 31u].rec);
             const uint4 r0 = rp[0], r1 = rp[1], r2 = rp[2], r3 = rp[3];
             FragRec r;
             r.e0 = (int32_t)r0.x; r.e1 = (int32_t)r0.y; r.e2 = (int32_t)r0.z; r.ax0 = (int32_t)r0.w;
             r.ax1 = (int32_t)r1.x; r.ax2 = (int32_t)r1.y; r.by0 = (int32_t)r1.z; r.by1 = (int32_t)r1.w;
-            r.by2 = (int32_t)r2.x; r.origin = r2.y; r.wdiv = r2.z; r.seq = r2.w;
-            r.z0 = __uint_as_float(r3.x); r.dzdx = __uint_as_float(r3.y); r.dzdy = __uint_as_float(r3.z); r.off = r3.w;
-            raster_candidate(r, j - first, makeSink(r.seq));
+            r.by2 = (int32_t)r2.x; r.z0 = __uint_as_float(r2.y); r.dzdx = __uint_as_float(r2.z); r.dzdy = __uint_as_float(r2.w);
+            r.fx0 = __uint_as_float(r3.x); r.fy0 = __uint_as_float(r3.y); r.origin = r3.z; r.wdiv = r3.w;
+            raster_candidate(r, j - (m.x >> 8), makeSink(m.y));
         }
     }
 }
@@ -730,41 +752,6 @@ VKR_HD CornerAcc corner_merge(const CornerAcc& a, const CornerAcc& b) {
     return r;
 }
 
-#if defined(__CUDACC__)
-// The same eight corners on the 32 lanes of a warp: lane = component * 8 + corner evaluates ONE clip-space component of ONE
-// corner (a quarter of corner_eval's arithmetic, none of it repeated across the warp); w comes from lane 24 + corner, the
-// plane tests are ballots, the NDC intervals are reduced inside each 8-lane group.  Every lane returns the merged result.
-__device__ __forceinline__ CornerAcc corners_warp(const float* __restrict__ m, float4 bmin, float4 bmax, int lane) {
-    const int comp = lane >> 3, corner = lane & 7;
-    const float px = (corner & 1) ? bmax.x : bmin.x, py = (corner & 2) ? bmax.y : bmin.y, pz = (corner & 4) ? bmax.z : bmin.z;
-    float v, e;
-    corner_component(m, comp, px, py, pz, v, e);
-    const float w = __shfl_sync(0xFFFFFFFFu, v, 24 + corner), ew = __shfl_sync(0xFFFFFFFFu, e, 24 + corner);
-    bool outLo, outHi;
-    corner_outside(comp, v, e, w, ew, outLo, outHi);
-    const uint32_t bl = __ballot_sync(0xFFFFFFFFu, outLo) & 0x00FFFFFFu, bh = __ballot_sync(0xFFFFFFFFu, outHi) & 0x00FFFFFFu;
-    const uint32_t bf = __ballot_sync(0xFFFFFFFFu, corner_front(w, ew));
-    float lo, hi;
-    corner_ndc(v, e, w, ew, lo, hi);
-#pragma unroll
-    for (int d = 1; d < 8; d <<= 1) {
-        lo = fminf(lo, __shfl_xor_sync(0xFFFFFFFFu, lo, d));
-        hi = fmaxf(hi, __shfl_xor_sync(0xFFFFFFFFu, hi, d));
-    }
-    CornerAcc a;
-    a.xmin = __shfl_sync(0xFFFFFFFFu, lo, 0); a.xmax = __shfl_sync(0xFFFFFFFFu, hi, 0);
-    a.ymin = __shfl_sync(0xFFFFFFFFu, lo, 8); a.ymax = __shfl_sync(0xFFFFFFFFu, hi, 8);
-    a.zmin = __shfl_sync(0xFFFFFFFFu, lo, 16); a.zmax = __shfl_sync(0xFFFFFFFFu, hi, 16);
-    // a plane culls the box when all eight corners are outside it: a full byte in one of the ballots
-    uint32_t all = 0;
-#pragma unroll
-    for (int c = 0; c < 3; ++c) all |= (uint32_t)(((bl >> (8 * c)) & 0xFFu) == 0xFFu) | (uint32_t)(((bh >> (8 * c)) & 0xFFu) == 0xFFu);
-    a.outAll = all;
-    a.allFront = (bf >> 24) == 0xFFu ? 1u : 0u;
-    return a;
-}
-#endif
-
 static const int CLUSTER_DRAW = 1, CLUSTER_CULLED = 0, CLUSTER_TEST = 2;
 #ifndef VKR_OCC_MAX_PIXELS
 #define VKR_OCC_MAX_PIXELS 1024
@@ -793,6 +780,16 @@ VKR_HD ClusterRect cluster_finalize(const CornerAcc& a, const RasterTarget& rt) 
     r.zminBits = f2bits(z);
     r.verdict = CLUSTER_TEST;
     return r;
+}
+// The whole test of one cluster for one pass, by one thread (expand_chunks_kernel, host emulation).
+VKR_HD CullRec make_cull_rec(const float* __restrict__ mvp, float4 bmin, float4 bmax, const RasterTarget& rt) {
+    CornerAcc a = corner_eval(mvp, bmin, bmax, 0);
+    for (int k = 1; k < 8; ++k) a = corner_merge(a, corner_eval(mvp, bmin, bmax, k));
+    const ClusterRect r = cluster_finalize(a, rt);
+    CullRec c;
+    c.x0 = (int16_t)r.x0; c.y0 = (int16_t)r.y0; c.x1 = (int16_t)r.x1; c.y1 = (int16_t)r.y1;     // extents are <= 16384
+    c.zminBits = r.zminBits; c.verdict = r.verdict;
+    return c;
 }
 // A stored depth hides the cluster at that pixel iff it is strictly nearer than anything the cluster can write.
 VKR_HD bool depth_hides(uint32_t storedBits, uint32_t zminBits) { return storedBits < zminBits; }
