@@ -161,6 +161,9 @@ typedef struct VkrConfig {
                                        the shading pass keeps its texel in registers (both f16 roundings still applied, SURVEY A-12)
                                        and vkr_readback / vkr_device_ptr(VKR_TARGET_HDR16F) is refused */
 
+#define VKR_CONFIG_LOCAL_PRESENT 32u /* sharded devices: every rank keeps (and presents, vkr_readback_band_async) its own rows; the
+                                        frame is not assembled on rank 0 */
+
 /* struct EngineStats — src/vk_types.h:78-83. */
 typedef struct VkrEngineStats {
     float frametime;           /* ms, device time of the last completed frame (needs VKR_CONFIG_TIMINGS) */
@@ -244,10 +247,15 @@ int vkr_set_shadow_exchange(VkrDevice* dev, VkrShadowExchangeFn fn, void* user);
  *   - renders one contiguous band of rows of the frame and one of every shadow layer; the bands are re-split every
  *     frame so that each holds the same estimated cost (triangles of the draws reaching a row + pixels to shade),
  *     identically on every rank from the draw list; draws and clusters outside the band cost (almost) nothing,
- *   - exchanges the shadow bands on the shadow stream (communicator 0, one grouped broadcast per band) before shading,
- *   - assembles the presented RGBA8 image (communicator 1) on its own stream, overlapped with the next frame,
- *     into VKR_TARGET_RGBA8_GATHERED (double-buffered like the presented image).
- * Draw lists, scene data and frame parameters must be identical on every rank. */
+ *   - exchanges the shadow bands before shading and assembles the presented RGBA8 image on rank 0
+ *     (VKR_TARGET_RGBA8_GATHERED / VKR_TARGET_RGB8, double-buffered like the presented image).
+ * The exchange runs over PEER MEMORY when the ranks' buffers can be mapped into each other (CUDA IPC; one process per GPU of an
+ * NVLink / NVSwitch box): a copy kernel stores a rank's shadow rows into every peer's map, the shading kernel stores its pixels
+ * into rank 0's image as it makes them, flags (frame numbers, system-scope release / acquire) order it; only rank 0 can read the
+ * assembled frame back.  Otherwise (or with VKR_EXCHANGE=nccl in the environment) it is two grouped ncclSend / ncclRecv exchanges
+ * per frame and every rank holds the assembled frame.  vkr_shard_init must precede the first vkr_draw; every rank must draw
+ * the same frames (draw lists, scene data, frame parameters, flags) in the same order, and all ranks should be synchronised
+ * (vkr_sync + the host's barrier) before any of them is destroyed. */
 #define VKR_COMM_ID_BYTES 128
 int vkr_comm_unique_id(void* out, size_t bytes);
 int vkr_shard_init(VkrDevice* dev, int rank, int nranks, const void* twoIds, size_t bytes);
@@ -262,6 +270,14 @@ int vkr_readback(VkrDevice* dev, VkrTarget what, void* dst, size_t dstBytes);   
  * and VKR_TARGET_SHADOW are refused here (VKR_ERROR_INVALID_ARGUMENT; use vkr_readback), VKR_TARGET_DEPTH / PRIMID are served
  * synchronously. */
 int vkr_readback_async(VkrDevice* dev, VkrTarget what, void* pinnedDst, size_t dstBytes);
+/* The same for THIS RANK'S ROWS only (VKR_TARGET_RGBA8 or VKR_TARGET_RGB8): they are copied to their place in a whole-frame
+ * buffer at frameBase (pinned; frameBytes >= W*H*4 or W*H*3).  On a sharded device every rank calls it with the same host frame
+ * (e.g. one shared-memory segment registered by every process), so the frame leaves the box over all the ranks' PCIe links at
+ * once and nothing has to be assembled on rank 0 (VKR_CONFIG_LOCAL_PRESENT).  On an unsharded device it is the whole image. */
+int vkr_readback_band_async(VkrDevice* dev, VkrTarget what, void* frameBase, size_t frameBytes);
+/* out[0], out[1]: rows [y0, y1) of the last frame this rank rendered; out[2]: 1 when the ranks exchange over peer memory (CUDA
+ * IPC over NVLink), 0 over NCCL; out[3]: ranks. */
+int vkr_shard_info(VkrDevice* dev, int32_t out[4]);
 /* Waits for everything issued.  Triangles too big for the lane that sets them up go through a queue of fixed capacity; when a
  * frame overflows it (the device then skips what did not fit, never reads past the queue), vkr_sync — and vkr_readback, which
  * syncs before it copies — grows the queues to what the frame asked for and draws the frame again before returning, so what

@@ -68,7 +68,7 @@ bool EmuClusters::get(uint32_t mesh, uint32_t firstIndex, uint32_t indexCount, C
     ClusterData* cd = new ClusterData();
     build_clusters(d->meshes[mesh].idx + firstIndex, indexCount / 3, d->meshes[mesh].nv, d->meshes[mesh].pos, *cd);
     store.push_back(cd);
-    out = ClusterRange{cd->verts.data(), cd->tris.data(), cd->orig.data(), cd->info.data(), cd->bounds.data(), 0u, {0, 0, 0}, 0};
+    out = ClusterRange{cd->verts.data(), cd->tris.data(), cd->orig.data(), cd->info.data(), cd->bounds.data(), cd->blob.data(), 0u, {0, 0, 0}, 0};
     range_sphere(*cd, out);
     cache.push_back({{mesh, firstIndex, indexCount}, out});
     return true;
@@ -125,6 +125,7 @@ static DTexture make_tex(const EmuImage* im, int sampler) {
     t.data = im->data.data(); t.w = im->w; t.h = im->h; t.levels = im->levels;
     t.flags = (im->format == 1 ? 1u : 0u) | (sampler == 1 ? 2u : 0u) | (im->cutout ? 4u : 0u);
     std::memcpy(t.mipOffset, im->mipOffset, sizeof(t.mipOffset));
+    std::memcpy(&t.texel0, im->data.data(), 4);
     return t;
 }
 
@@ -212,6 +213,7 @@ int emu_build_material(EmuDevice* d, const VkrMaterialConstants* p, int pass, ui
     std::memcpy(m.colorFactors, p->colorFactors, 16);
     std::memcpy(m.metalRough, p->metal_rough_factors, 16);
     m.albedoID = p->albedoID; m.normalID = p->normalID; m.metalRoughID = p->metalRoughID; m.pass = pass;
+    m.constFlags = 0u;
     d->materials.push_back(m);
     *out = (uint32_t)d->materials.size() - 1;
     return 0;
@@ -301,6 +303,7 @@ extern "C" {
 
 int emu_draw(EmuDevice* d, const VkrGPUSceneData* scene, const VkrRenderObject* objs, size_t n, const VkrFrameParams* fp) {
     FramePlan& plan = d->plan;
+    for (DMaterial& m : d->materials) material_constants(m, d->tex.data(), d->lut);
     std::string why = plan_frame(scene, objs, n, fp, d->meshes, d->materials, d->tex, d->clusters, d->W, d->H, d->S, plan, d->shardRank, d->shardRanks);
     if (!why.empty()) { d->err = why; return VKR_ERROR_INVALID_ARGUMENT; }
     const unsigned nChunks = plan.clusterBase[n];

@@ -26,6 +26,7 @@ CONFIG_TIME_GEOM_KERNEL = 2
 CONFIG_SUBMIT_THREAD = 4
 CONFIG_TRANSIENT_DEPTH = 8
 CONFIG_TRANSIENT_HDR = 16
+CONFIG_LOCAL_PRESENT = 32
 T_NAMES = ["upload", "shadow", "geometry", "shade", "transparent", "post", "total", "geom_kernel", "large_kernel", "clear",
            "shadow_exchange", "frame_gather", "readback"]
 
@@ -119,6 +120,7 @@ VKR_SYMBOLS = [
     "create", "destroy", "upload_mesh", "create_image", "update_bindless_texture", "set_cubemap", "set_cubemap_levels",
     "build_material", "draw", "readback", "readback_async", "sync", "stats", "get_timings",
     "set_flags", "device_ptr", "launch_count", "upload_bytes", "cull_stats", "set_shadow_exchange", "comm_unique_id", "shard_init", "last_error", "version",
+    "readback_band_async", "shard_info",
 ]
 
 
@@ -207,6 +209,8 @@ class Renderer:
         if self.prefix == "vkr":
             sigs.update({
                 "readback_async": ([p, C.c_int, p, C.c_size_t], C.c_int),
+                "readback_band_async": ([p, C.c_int, p, C.c_size_t], C.c_int),
+                "shard_info": ([p, C.POINTER(C.c_int32)], C.c_int),
                 "sync": ([p], C.c_int),
                 "get_timings": ([p, C.POINTER(C.c_float), C.c_int], C.c_int),
                 "device_ptr": ([p, C.c_int, C.POINTER(p), C.POINTER(C.c_size_t)], C.c_int),
@@ -319,6 +323,15 @@ class Renderer:
 
     def readback_async(self, what: int, pinned_ptr: int, nbytes: int):
         self._check(self._f("readback_async")(self.dev, what, pinned_ptr, nbytes))
+
+    def readback_band_async(self, what: int, frame_ptr: int, nbytes: int):
+        """This rank's rows of the last frame into their place in the whole-frame pinned buffer at frame_ptr."""
+        self._check(self._f("readback_band_async")(self.dev, what, frame_ptr, nbytes))
+
+    def shard_info(self) -> dict:
+        out = (C.c_int32 * 4)()
+        self._check(self._f("shard_info")(self.dev, out))
+        return {"rows": (out[0], out[1]), "peer_memory": bool(out[2]), "ranks": out[3]}
 
     def timings(self) -> dict:
         arr = (C.c_float * len(T_NAMES))()

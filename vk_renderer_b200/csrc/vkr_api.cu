@@ -94,6 +94,56 @@ static ncclResult_t exchange_bands(const uint32_t* src, uint32_t* dst, const std
     return rc;
 }
 
+// ---- sort-first exchange over PEER MEMORY (NVLink / NVSwitch; one process per GPU, buffers shared through CUDA IPC):
+// instead of two NCCL groups per frame, the ranks store their rows straight into their peers' shadow maps (a copy kernel) and
+// into rank 0's presented image (the shading kernel's own stores), and tell each other with flags.  Every flag is a frame
+// number that only grows, lives in the memory of the rank that WAITS on it and is written by a peer with a system-scope
+// release store after a system-scope fence; waiters spin with acquire loads, bounded by a timeout that raises an error word in
+// pinned host memory instead of hanging the device.
+//   shadowCleared[p] = f+1 : rank p has cleared its shadow map for frame f (rows may be stored into it)
+//   shadowReady[p]   = f+1 : rank p's rows of frame f have landed in my shadow map
+//   frameReady[p]    = f+1 : rank p's rows of frame f have landed in my (rank 0's) presented image
+//   gatheredFree     = f+1 : rank 0 has finished with the image that frame f overwrites
+static const int MAX_RANKS = 16;
+struct ShardFlags {
+    uint32_t shadowCleared[MAX_RANKS], shadowReady[MAX_RANKS], frameReady[MAX_RANKS];
+    uint32_t gatheredFree, pad[15];
+};
+struct PeerList { uint32_t* p[MAX_RANKS]; int n; };
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) { asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) { uint32_t v; asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory"); return v; }
+// Everything the stream has done before this kernel is visible to a peer that reads the new flag value.
+__global__ void shard_signal_kernel(const __grid_constant__ PeerList dst, uint32_t value) {
+    if ((int)threadIdx.x < dst.n) { __threadfence_system(); st_release_sys(dst.p[threadIdx.x], value); }
+}
+// Lane i waits until flags[i] >= value, for every i in `mask`.  ~4 s of spinning raises *err (pinned host memory) and goes on.
+__global__ void shard_wait_kernel(const uint32_t* flags, uint32_t mask, uint32_t value, uint32_t* err, uint32_t code) {
+    const uint32_t i = threadIdx.x;
+    if (i < (uint32_t)MAX_RANKS && ((mask >> i) & 1u)) {
+        const long long t0 = clock64();
+        while ((int32_t)(ld_acquire_sys(flags + i) - value) < 0) {
+            if (clock64() - t0 > 8000000000ll) { *err = code | (i << 8); break; }
+            __nanosleep(64);
+        }
+    }
+}
+// My rows of one shadow layer into the same rows of every peer's map (texels [first, first + count) of the layer).
+__global__ void shard_push_rows_kernel(const uint32_t* __restrict__ src, const __grid_constant__ PeerList dst, size_t first, size_t count) {
+    const size_t stride = (size_t)gridDim.x * blockDim.x, tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (((first | count) & 3u) == 0u) {
+        const uint4* s4 = reinterpret_cast<const uint4*>(src + first);
+        for (size_t i = tid; i < (count >> 2); i += stride) {
+            const uint4 v = __ldcg(s4 + i);                    // written by this frame's raster atomics: read at L2
+            for (int k = 0; k < dst.n; ++k) reinterpret_cast<uint4*>(dst.p[k] + first)[i] = v;
+        }
+    } else {
+        for (size_t i = tid; i < count; i += stride) {
+            const uint32_t v = __ldcg(src + first + i);
+            for (int k = 0; k < dst.n; ++k) dst.p[k][first + i] = v;
+        }
+    }
+}
+
 // ---- upload_mesh: AoS Vertex (48 B) -> three float4 streams
 __global__ void repack_vertices_kernel(const VkrVertex* __restrict__ v, size_t n, float4* __restrict__ pos,
                                        float4* __restrict__ attrA, float4* __restrict__ attrB) {
@@ -143,16 +193,16 @@ __global__ void mip_blit_kernel(const uchar4* __restrict__ src, int sw, int sh, 
 }
 
 // ---- per-frame tables, written on the device from the per-draw prefixes (one CTA per draw):
-// the 48-byte cluster records, for every pass the processing order (geometry warp slot -> cluster, front to
-// back by draw) and the outcome of the cluster test (one thread per cluster projects the bounding box's eight corners
-// through the pass's matrix: frustum planes, pixel rectangle, nearest depth — CullRec), and the (draw, first triangle)
-// pairs the shading pass looks up through seq >> 8.
+// for every pass the work items in processing order (geometry warp slot -> cluster, front to back by draw), each with the
+// outcome of its cluster test (one thread per cluster projects the bounding box's eight corners through the pass's matrix:
+// frustum planes, pixel rectangle, nearest depth — CullRec); one more list in submission order with the main pass's matrix
+// (the transparent pass); the 48-byte cluster records the cut-out kernel walks; and the (draw, first triangle) pairs the
+// shading pass looks up through seq >> 8.
 __global__ void expand_chunks_kernel(const DObject* __restrict__ objects, const uint32_t* __restrict__ clusterBase,
                                      const uint32_t* __restrict__ seqSlotBase, const uint32_t* __restrict__ slotBase,
-                                     const float* __restrict__ shadowMvp, uint32_t nobj, uint32_t passes, uint32_t permStride,
+                                     const float* __restrict__ shadowMvp, uint32_t nobj, uint32_t passes, uint32_t listStride,
                                      const __grid_constant__ RasterTarget rtMain, const __grid_constant__ RasterTarget rtShadow,
-                                     DChunk* __restrict__ chunks, uint2* __restrict__ chunkObj, uint32_t* __restrict__ perm,
-                                     CullRec* __restrict__ cull) {
+                                     DChunk* __restrict__ chunks, uint2* __restrict__ chunkObj, WorkItem* __restrict__ work) {
     const uint32_t obj = blockIdx.x;
     const uint32_t base = clusterBase[obj], n = clusterBase[obj + 1] - base;
     const uint32_t sbase = seqSlotBase[obj], ns = seqSlotBase[obj + 1] - sbase;
@@ -160,13 +210,13 @@ __global__ void expand_chunks_kernel(const DObject* __restrict__ objects, const 
     for (uint32_t c = threadIdx.x; c < n; c += blockDim.x) {
         chunks[base + c] = make_chunk(o, obj, c, sbase);
         const float4 bmin = o.clBounds[2 * c], bmax = o.clBounds[2 * c + 1];
+        const CullRec mainRec = make_cull_rec(o.mvp, bmin, bmax, rtMain);
+        work[(size_t)passes * listStride + base + c] = make_work_item(o, obj, c, sbase, mainRec);      // submission order
         for (uint32_t p = 0; p < passes; ++p) {
             const uint32_t sb = slotBase[(size_t)p * nobj + obj];
-            if (sb != 0xFFFFFFFFu) perm[(size_t)p * permStride + sb + c] = base + c;
-            // pass 0's record also serves the transparent pass, whose draws have no slot in the opaque order
-            if (sb != 0xFFFFFFFFu || p == 0)
-                cull[(size_t)p * permStride + base + c] = p == 0 ? make_cull_rec(o.mvp, bmin, bmax, rtMain)
-                                                                 : make_cull_rec(shadowMvp + ((size_t)(p - 1) * nobj + obj) * 16, bmin, bmax, rtShadow);
+            if (sb == 0xFFFFFFFFu) continue;
+            work[(size_t)p * listStride + sb + c] =
+                make_work_item(o, obj, c, sbase, p == 0 ? mainRec : make_cull_rec(shadowMvp + ((size_t)(p - 1) * nobj + obj) * 16, bmin, bmax, rtShadow));
         }
     }
     for (uint32_t k = threadIdx.x; k < ns; k += blockDim.x) chunkObj[sbase + k] = make_uint2(obj, k * SEQ_SLOT);
@@ -174,45 +224,86 @@ __global__ void expand_chunks_kernel(const DObject* __restrict__ objects, const 
 
 // ---- geometry: one WARP per cluster (<= 128 triangles, <= 128 distinct vertices of one draw); the warps of a
 // CTA never synchronise with each other, so every warp of the SM is an independent latency-hiding stream.
-// Phase 0 (8 lanes) projects the cluster's bounding box and drops the cluster when it is outside the
-// frustum, holds no pixel centre, or is hidden by what is already in the depth / visibility buffer.
-// Phase 1 transforms each DISTINCT vertex of the cluster once (128-bit position loads) into the warp's
-// 2 KB of shared memory as snapped window coordinates; phase 2 runs the triangles, 32 at a time, on those.
+// The warp reads its 32-byte work item, and unless expand_chunks_kernel's box test already dropped the cluster, one lane
+// starts ONE bulk copy (cp.async.bulk: the TMA unit, completion on the warp's own mbarrier) of the cluster's block — packed
+// triangles and vertex positions, 1-3 KB — into the warp's shared memory.  While it flies the warp walks the cluster's
+// pixel rectangle in the live depth / visibility buffer (phase 0: hidden -> dropped).  Phase 1 transforms each DISTINCT
+// vertex once, in place, into snapped window coordinates; phase 2 runs the triangles, 32 at a time, on those.
 // PASS: 0 main (visibility buffer), 1 shadow (depth only), 2 transparent (shade + additive blend, no depth write).
 enum { PASS_MAIN = 0, PASS_SHADOW = 1, PASS_TRANSPARENT = 2 };
 
+// VKR_STAGE_TRIS 1: the whole block (packed triangles + positions) is staged; 0 (default): only the positions, the packed
+// triangles are read from L2 one iteration ahead (1 KB less shared memory per warp: 12 instead of 10 CTAs per SM, and it is
+// resident warps, not instructions, that this kernel is short of — profiles/r02d_ab.md)
+#ifndef VKR_STAGE_TRIS
+#define VKR_STAGE_TRIS 0
+#endif
+struct alignas(16) WarpSmem {              // one warp's slice of shared memory: one base register, constant offsets
+#if VKR_STAGE_TRIS
+    uint2 tris[CL_TRIS];                   // bulk-copy destination, part 1 ...
+#endif
+    uint4 vtx[CL_VERTS];                   // ... part 2: positions, overwritten in place by the transformed vertices (CachedVtx)
+    ParkedTri park[32];
+#if defined(VKR_RASTER_CANDIDATES)
+    uint2 map[32];
+#endif
+    float mvp[16];
+    unsigned long long bar;                // the warp's mbarrier
+    unsigned long long pad;
+};
+static_assert(sizeof(WarpSmem) % 16 == 0 && offsetof(WarpSmem, vtx) % 16 == 0, "bulk copies land on 16-byte boundaries");
+
+__device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void bulk_load_start(WarpSmem* ws, const void* src, uint32_t bytes) {      // one lane
+#if VKR_STAGE_TRIS
+    const uint32_t bar = smem_addr(&ws->bar), dst = smem_addr(ws->tris);
+#else
+    const uint32_t bar = smem_addr(&ws->bar), dst = smem_addr(ws->vtx);
+#endif
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar) : "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");          // the async proxy must see the initialised barrier
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src), "r"(bytes), "r"(bar)
+                 : "memory");
+}
+__device__ __forceinline__ bool bulk_load_wait(WarpSmem* ws) {           // every lane; false: gave up (never seen; keeps a fault from hanging the device)
+    const uint32_t bar = smem_addr(&ws->bar);
+    for (int spin = 0; spin < (1 << 24); ++spin) {
+        uint32_t done;
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(done) : "r"(bar) : "memory");
+        if (done) return true;
+    }
+    return false;
+}
 
 template <int PASS, class MakeSink>
-__device__ __forceinline__ void geometry_warp(const DChunk* __restrict__ chunk, const CullRec* __restrict__ cullRec, const float* __restrict__ mvps, uint32_t mvpStride,
-                                              const RasterTarget& rt, const Queues& q, uint4* s_vtx, float* mvp, ParkedTri* s_park, uint2* s_map,
-                                              const MakeSink& makeSink) {
+__device__ __forceinline__ void geometry_warp(const WorkItem* __restrict__ item, const float* __restrict__ mvps, uint32_t mvpStride,
+                                              const RasterTarget& rt, const Queues& q, WarpSmem* ws, const MakeSink& makeSink) {
     const int lane = threadIdx.x & 31;
-    // the 48-byte cluster record and the 16-byte outcome of its cluster test are everything this warp needs: one level of
-    // indirection (uniform loads)
-    const uint4* chp = reinterpret_cast<const uint4*>(chunk);
-    const uint4 cr = __ldg(reinterpret_cast<const uint4*>(cullRec));
-    const uint4 c2 = __ldg(chp + 2);
-    const uint32_t obj = c2.x, seqBase = c2.y, counts = c2.z, flags = c2.w;
+    const uint4 w0 = __ldg(reinterpret_cast<const uint4*>(item)), w1 = __ldg(reinterpret_cast<const uint4*>(item) + 1);
+    const uint32_t info = w1.x, flags = (info >> 16) & 0xFFu;
+    const int32_t verdict = (int32_t)(info >> 24);
     if (PASS == PASS_MAIN && (flags & 2u)) return;     // alpha-tested draw: geometry_cutout_kernel owns this cluster
-    const int32_t verdict = (int32_t)cr.w;
     if (verdict == CLUSTER_CULLED) { if (lane == 0) atomicAdd(q.counters + 3, 1u); return; }
-    const uint4 c0 = __ldg(chp), c1 = __ldg(chp + 1);
-    const float4* __restrict__ pos = reinterpret_cast<const float4*>(((uint64_t)c0.y << 32) | c0.x);
-    const uint32_t* __restrict__ clVerts = reinterpret_cast<const uint32_t*>(((uint64_t)c0.w << 32) | c0.z);
-    const uint32_t* __restrict__ clTris = reinterpret_cast<const uint32_t*>(((uint64_t)c1.y << 32) | c1.x);
-    const uint32_t* __restrict__ clOrig = reinterpret_cast<const uint32_t*>(((uint64_t)c1.w << 32) | c1.z);
-    const uint32_t nVerts = counts & 0xFFFFu, nTris = counts >> 16;
-    // the cluster's vertex indices and matrix are needed only if it survives the occlusion test, but their latency hides behind it
-    uint32_t vi[CL_VERTS / 32];
-#pragma unroll
-    for (int k = 0; k < CL_VERTS / 32; ++k) vi[k] = lane + 32u * k < nVerts ? __ldg(clVerts + lane + 32u * k) : 0u;
-    if (lane < 16) mvp[lane] = __ldg(mvps + (size_t)obj * mvpStride + lane);
+    const uint4* __restrict__ blob = reinterpret_cast<const uint4*>(((uint64_t)w0.y << 32) | w0.x);
+    const uint32_t obj = w0.z, seqBase = w0.w;
+    const uint32_t nVerts = info & 0xFFu, nTris = (info >> 8) & 0xFFu;
+#if VKR_STAGE_TRIS
+    if (lane == 0) bulk_load_start(ws, blob, CL_BLOB_TRI_BYTES + nVerts * 16u);
+#else
+    if (lane == 0) bulk_load_start(ws, blob + CL_BLOB_TRI_BYTES / 16u, nVerts * 16u);
+    const uint2* __restrict__ gtris = reinterpret_cast<const uint2*>(blob);
+    uint2 tpNext = lane < (int)nTris ? __ldg(gtris + lane) : make_uint2(0u, 0u);      // the first iteration's triangles, in flight during the cull
+#endif
+    if (lane < 16) ws->mvp[lane] = __ldg(mvps + (size_t)obj * mvpStride + lane);
+    __syncwarp();
+    const float* mvp = ws->mvp;
 
-    // ---- phase 0: cluster culling.  The box test (frustum planes, pixel rectangle, nearest depth) was done once per frame by
-    // expand_chunks_kernel; what is left is the occlusion test against the LIVE depth / visibility buffer
+    // ---- phase 0: the occlusion test against the LIVE depth / visibility buffer (the box test — frustum planes, pixel
+    // rectangle, nearest depth — was done once per frame by expand_chunks_kernel)
     if (verdict == CLUSTER_TEST) {
-        const int32_t rx0 = (int32_t)(cr.x & 0xFFFFu), ry0 = (int32_t)(cr.x >> 16), rx1 = (int32_t)(cr.y & 0xFFFFu), ry1 = (int32_t)(cr.y >> 16);
-        const uint32_t zminBits = cr.z;
+        const int32_t rx0 = (int32_t)(w1.y & 0xFFFFu), ry0 = (int32_t)(w1.y >> 16), rx1 = (int32_t)(w1.z & 0xFFFFu), ry1 = (int32_t)(w1.z >> 16);
+        const uint32_t zminBits = w1.w;
         // the warp walks the rectangle as 8x16 pixel footprints (four independent loads per lane in flight) and stops
         // at the first footprint with a visible pixel
         bool hidden = true;
@@ -227,8 +318,9 @@ __device__ __forceinline__ void geometry_warp(const DChunk* __restrict__ chunk, 
                     stored[k] = 0u;                                     // outside the rectangle: counts as hidden
                     if (px <= rx1 && py <= ry1) {
                         // .cg: read at L2, where the RED.MIN of the other warps land (stale L1 lines would only lose culls)
-                        if (PASS == PASS_SHADOW) stored[k] = __ldcg(rt.depthBits + (size_t)py * rt.width + px);
-                        else stored[k] = __ldcg(reinterpret_cast<const uint32_t*>(rt.vis + (size_t)py * rt.width + px) + 1);
+                        const uint32_t pix = (uint32_t)(py * rt.width + px);
+                        if (PASS == PASS_SHADOW) stored[k] = __ldcg(rt.depthBits + pix);
+                        else stored[k] = __ldcg(reinterpret_cast<const uint32_t*>(rt.vis + pix) + 1);
                     }
                 }
                 const bool h = depth_hides(stored[0], zminBits) && depth_hides(stored[1], zminBits) &&
@@ -236,22 +328,24 @@ __device__ __forceinline__ void geometry_warp(const DChunk* __restrict__ chunk, 
                 hidden = __all_sync(0xFFFFFFFFu, h);
             }
         }
-        if (hidden) { if (lane == 0) atomicAdd(q.counters + 3, 1u); return; }
+        if (hidden) {
+            bulk_load_wait(ws);                                         // the copy must have landed before this shared memory is given to another CTA
+            if (lane == 0) atomicAdd(q.counters + 3, 1u);
+            return;
+        }
     }
-    __syncwarp();
+    if (!bulk_load_wait(ws)) { if (lane == 0) q.counters[2] = 2u; return; }
+    uint4* s_vtx = ws->vtx;
+    ParkedTri* s_park = ws->park;
 
-    // ---- phase 1: distinct vertices
-    {
-        float4 p[CL_VERTS / 32];
+    // ---- phase 1: distinct vertices, in place (each lane reads and rewrites its own slots)
 #pragma unroll
-        for (int k = 0; k < CL_VERTS / 32; ++k) if (lane + 32u * k < nVerts) p[k] = __ldg(pos + vi[k]);
-#pragma unroll
-        for (int k = 0; k < CL_VERTS / 32; ++k)
-            if (lane + 32u * k < nVerts) {
-                const CachedVtx cv = cluster_vertex(mvp, p[k], rt);
-                s_vtx[lane + 32u * k] = make_uint4((uint32_t)cv.X, (uint32_t)cv.Y, cv.zbits, cv.flag);
-            }
-    }
+    for (int k = 0; k < CL_VERTS / 32; ++k)
+        if (lane + 32u * k < nVerts) {
+            const uint4 pv = s_vtx[lane + 32u * k];
+            const CachedVtx cv = cluster_vertex(mvp, make_float4(__uint_as_float(pv.x), __uint_as_float(pv.y), __uint_as_float(pv.z), 1.0f), rt);
+            s_vtx[lane + 32u * k] = make_uint4((uint32_t)cv.X, (uint32_t)cv.Y, cv.zbits, cv.flag);
+        }
     __syncwarp();
 
     // ---- phase 2: triangles, 32 at a time.  Every lane sets one up and parks it in its shared-memory slot; then the warp
@@ -262,17 +356,25 @@ __device__ __forceinline__ void geometry_warp(const DChunk* __restrict__ chunk, 
         const uint32_t t = base + lane;
         int kind = 0;
         uint32_t count = 0, seqOfLane = 0;
+#if !VKR_STAGE_TRIS
+        const uint2 tpCur = tpNext;
+        if (t + 32u < nTris) tpNext = __ldg(gtris + t + 32u);              // the next iteration's, one iteration ahead
+#endif
         if (t < nTris) {
-            const uint32_t packed = __ldg(clTris + t);
-            const uint32_t l0 = packed & 127u, l1 = (packed >> 7) & 127u, l2 = (packed >> 14) & 127u;
+#if VKR_STAGE_TRIS
+            const uint2 tp = ws->tris[t];
+#else
+            const uint2 tp = tpCur;
+#endif
+            const uint32_t l0 = tp.x & 127u, l1 = (tp.x >> 7) & 127u, l2 = (tp.x >> 14) & 127u;
             const uint4 a = s_vtx[l0], b = s_vtx[l1], c = s_vtx[l2];
             const CachedVtx va{(int32_t)a.x, (int32_t)a.y, a.z, a.w}, vb{(int32_t)b.x, (int32_t)b.y, b.z, b.w}, vc{(int32_t)c.x, (int32_t)c.y, c.z, c.w};
-            uint32_t g0 = 0, g1 = 0, g2 = 0;
-            if (a.w | b.w | c.w) { g0 = __ldg(clVerts + l0); g1 = __ldg(clVerts + l1); g2 = __ldg(clVerts + l2); }
             // submission-order sequence number, whatever the processing order (the shadow pass has no use for it)
-            const uint32_t seq = PASS == PASS_SHADOW ? 0u : seqBase + __ldg(clOrig + t);
+            const uint32_t seq = PASS == PASS_SHADOW ? 0u : seqBase + tp.y;
             seqOfLane = seq;
-            kind = cluster_triangle_deferred(va, vb, vc, mvp, pos, g0, g1, g2, seq, rt, q, makeSink(seq), s_park[lane], count);
+            // (a triangle that needs clipping re-reads its ORIGINAL positions from the cluster's block in global memory)
+            kind = cluster_triangle_deferred(va, vb, vc, mvp, reinterpret_cast<const float4*>(blob + CL_BLOB_TRI_BYTES / 16u), l0, l1, l2, seq, rt, q,
+                                             makeSink(seq), s_park[lane], count);
             if (kind != 3) count = 0;
         }
         // inclusive prefix sum of the candidate counts
@@ -283,7 +385,11 @@ __device__ __forceinline__ void geometry_warp(const DChunk* __restrict__ chunk, 
         const uint32_t medium = __ballot_sync(0xFFFFFFFFu, kind == 1);
         uint32_t large = __ballot_sync(0xFFFFFFFFu, kind == 2);
         __syncwarp();
-        if (total) raster_candidates_warp(s_park, s_map, incl - count, count, seqOfLane, total, lane, makeSink);
+#if defined(VKR_RASTER_CANDIDATES)
+        if (total) raster_candidates_warp(s_park, ws->map, incl - count, count, seqOfLane, total, lane, makeSink);
+#else
+        (void)total; (void)seqOfLane;
+#endif
         if ((medium | large) == 0u) { __syncwarp(); continue; }
         if (medium) {
             // medium triangles (extent < 64 px): one queue item each, no tile enumeration; the slots of the whole warp are
@@ -317,32 +423,23 @@ struct MakeDepthSink { uint32_t* bits; int32_t width; __device__ DepthSink opera
 struct MakeBlendSink { const ShadeConst* sc; const ShadeBuffers* sb; __device__ BlendSink operator()(uint32_t seq) const { return BlendSink{sc, sb, seq}; } };
 
 template <bool SHADOW>
-__global__ void __launch_bounds__(GEOM_WARPS * 32, VKR_GEOM_MIN_CTAS) geometry_kernel(const DChunk* __restrict__ chunks, const CullRec* __restrict__ cull, const uint32_t* __restrict__ perm,
-                                                                     uint32_t nClusters, const float* __restrict__ mvps, uint32_t mvpStride,
+__global__ void __launch_bounds__(GEOM_WARPS * 32, VKR_GEOM_MIN_CTAS) geometry_kernel(const WorkItem* __restrict__ work, uint32_t nClusters,
+                                                                     const float* __restrict__ mvps, uint32_t mvpStride,
                                                                      const __grid_constant__ RasterTarget rt, const __grid_constant__ Queues q) {
-    __shared__ uint4 s_vtxAll[GEOM_WARPS][CL_VERTS];
-    __shared__ float s_mvpAll[GEOM_WARPS][16];
-    __shared__ ParkedTri s_parkAll[GEOM_WARPS][32];
-    __shared__ uint2 s_mapAll[GEOM_WARPS][32];
+    __shared__ WarpSmem s_warp[GEOM_WARPS];
     const uint32_t slot = blockIdx.x * GEOM_WARPS + (threadIdx.x >> 5);
     if (slot >= nClusters) return;
-    const uint32_t ci = __ldg(perm + slot);
-    const DChunk* chunk = chunks + ci;
-    const CullRec* cullRec = cull + ci;
-    const int wi = threadIdx.x >> 5;
-    if (SHADOW) geometry_warp<PASS_SHADOW>(chunk, cullRec, mvps, mvpStride, rt, q, s_vtxAll[wi], s_mvpAll[wi], s_parkAll[wi], s_mapAll[wi], MakeDepthSink{rt.depthBits, rt.width});
-    else geometry_warp<PASS_MAIN>(chunk, cullRec, mvps, mvpStride, rt, q, s_vtxAll[wi], s_mvpAll[wi], s_parkAll[wi], s_mapAll[wi], MakeVisSink{rt.vis, rt.width});
+    WarpSmem* ws = &s_warp[threadIdx.x >> 5];
+    if (SHADOW) geometry_warp<PASS_SHADOW>(work + slot, mvps, mvpStride, rt, q, ws, MakeDepthSink{rt.depthBits, rt.width});
+    else geometry_warp<PASS_MAIN>(work + slot, mvps, mvpStride, rt, q, ws, MakeVisSink{rt.vis, rt.width});
 }
 
 // ---- "Transparent" draws (the tail of the draw list), after every opaque fragment is in the visibility buffer
-__global__ void __launch_bounds__(GEOM_WARPS * 32) geometry_transparent_kernel(const DChunk* __restrict__ chunks, const CullRec* __restrict__ cull, uint32_t firstCluster, uint32_t nClusters,
+__global__ void __launch_bounds__(GEOM_WARPS * 32) geometry_transparent_kernel(const WorkItem* __restrict__ work, uint32_t nClusters,
                                                                               const float* __restrict__ mvps, uint32_t mvpStride,
                                                                               const __grid_constant__ RasterTarget rt, const __grid_constant__ Queues q,
                                                                               const __grid_constant__ ShadeConst sc, const __grid_constant__ ShadeBuffers sbIn) {
-    __shared__ uint4 s_vtxAll[GEOM_WARPS][CL_VERTS];
-    __shared__ float s_mvpAll[GEOM_WARPS][16];
-    __shared__ ParkedTri s_parkAll[GEOM_WARPS][32];
-    __shared__ uint2 s_mapAll[GEOM_WARPS][32];
+    __shared__ WarpSmem s_warp[GEOM_WARPS];
     __shared__ float s_lut[256];
     for (uint32_t i = threadIdx.x; i < 256u; i += GEOM_WARPS * 32) s_lut[i] = sbIn.srgbLut[i];
     __syncthreads();
@@ -351,8 +448,7 @@ __global__ void __launch_bounds__(GEOM_WARPS * 32) geometry_transparent_kernel(c
     __syncthreads();
     const uint32_t slot = blockIdx.x * GEOM_WARPS + (threadIdx.x >> 5);
     if (slot >= nClusters) return;
-    geometry_warp<PASS_TRANSPARENT>(chunks + firstCluster + slot, cull + firstCluster + slot, mvps, mvpStride, rt, q, s_vtxAll[threadIdx.x >> 5], s_mvpAll[threadIdx.x >> 5],
-                                    s_parkAll[threadIdx.x >> 5], s_mapAll[threadIdx.x >> 5], MakeBlendSink{&sc, &s_sb});
+    geometry_warp<PASS_TRANSPARENT>(work + slot, mvps, mvpStride, rt, q, &s_warp[threadIdx.x >> 5], MakeBlendSink{&sc, &s_sb});
 }
 
 // ---- main pass, alpha-tested draws only (launched when the frame has any): one thread per triangle,
@@ -467,6 +563,7 @@ __global__ void __launch_bounds__(128, VKR_SHADE_MIN_CTAS) shade_kernel(const __
     } while (0)
 
 struct ImageRec {
+    uint32_t texel0 = 0;
     uchar4* data = nullptr;
     uint32_t w = 0, h = 0, levels = 1;
     uint32_t mipOffset[16] = {0};
@@ -487,8 +584,7 @@ struct FrameSlot {
     // tables are built on the upload stream while this frame's kernels still read theirs)
     DChunk* chunkBuf = nullptr; size_t chunkCap = 0;       // cluster table
     uint2* chunkObjBuf = nullptr; size_t seqSlotCap = 0;   // seq >> 8 -> (draw, first triangle)
-    uint32_t* permBuf = nullptr; size_t permCap = 0;       // (1 + shadow layers) x clusters: processing order per pass
-    CullRec* cullBuf = nullptr;                            // (1 + shadow layers) x clusters: outcome of the cluster test per pass (same capacity)
+    WorkItem* workBuf = nullptr; size_t workCap = 0;       // (2 + shadow layers) x clusters: every pass's work items in processing order, then one list in submission order
 };
 
 struct VkrDevice {
@@ -548,7 +644,7 @@ struct VkrDevice {
     // and asynchronous read-backs (vkr_readback_async) follow their frame through the same queue, so the caller never waits
     // for a frame to be issued before it can plan the next one
     std::thread worker;
-    struct Job { int kind; FramePlan* plan; size_t n; VkrTarget what; void* dst; size_t dstBytes; };   // kind 0: frame, 1: read-back
+    struct Job { int kind; FramePlan* plan; size_t n; VkrTarget what; void* dst; size_t dstBytes; };   // kind 0: frame, 1: read-back, 2: read-back of this rank's rows
     static const uint32_t JOBS = 4;
     Job jobs[JOBS];
     std::atomic<uint32_t> jobHead{0}, jobTail{0};   // single producer (the caller's thread), single consumer; head advances when a job is DONE
@@ -573,6 +669,16 @@ struct VkrDevice {
     uint32_t* gathered[VKR_FRAME_OVERLAP] = {nullptr, nullptr};
     cudaEvent_t gatheredEv[VKR_FRAME_OVERLAP] = {nullptr, nullptr};
     bool gatheredValid[VKR_FRAME_OVERLAP] = {false, false};
+    // ... over peer memory (CUDA IPC): see "sort-first exchange over PEER MEMORY" above
+    bool p2p = false;
+    uint64_t shardFrame = 0;                       // frames drawn since vkr_shard_init (the same number on every rank)
+    ShardFlags* myFlags = nullptr;                 // in my memory (tail of gathered[0]'s allocation)
+    ShardFlags* peerFlags[MAX_RANKS] = {};         // [p]: rank p's flags, mapped here ([rank] = myFlags)
+    uint32_t* peerShadow[MAX_RANKS][VKR_FRAME_OVERLAP] = {};   // [p][slot]: rank p's shadow maps ([rank] = my own)
+    uint32_t* rootGathered[VKR_FRAME_OVERLAP] = {};            // rank 0's presented (assembled) images
+    std::vector<void*> ipcOpened;
+    int32_t lastBand[2] = {0, 0};                  // rows [y0, y1) of the last frame this rank rendered
+    uint32_t lastGatherF1 = 0;                     // the last frame's flag value if it was assembled on rank 0 over peer memory, else 0
     VkrEngineStats stats{};
     uint32_t lastOpaqueClusters = 0, lastShadowClusters = 0;
     int launches = 0;
@@ -607,19 +713,20 @@ struct DeviceClusterProvider : ClusterProvider {
         { const int arc = drain(dev); if (arc != VKR_SUCCESS) dev->asyncRc = arc; }     // building touches state the submit thread uses
         ClusterData cd;
         build_clusters(dev->meshIndexHost[mesh].data() + firstIndex, indexCount / 3, dev->meshes[mesh].nv, dev->meshPosHost[mesh].data(), cd);
-        uint32_t *dv = nullptr, *dt = nullptr, *dorig = nullptr; uint2* di = nullptr; float4* db = nullptr;
+        uint32_t *dv = nullptr, *dt = nullptr, *dorig = nullptr; uint2* di = nullptr; float4* db = nullptr; uint4* dblob = nullptr;
         if (dev_alloc(dev, (void**)&dv, cd.verts.size() * 4) || dev_alloc(dev, (void**)&dt, cd.tris.size() * 4) ||
             dev_alloc(dev, (void**)&dorig, cd.orig.size() * 4) || dev_alloc(dev, (void**)&di, cd.info.size() * sizeof(uint2)) ||
-            dev_alloc(dev, (void**)&db, cd.bounds.size() * sizeof(float4)))
+            dev_alloc(dev, (void**)&db, cd.bounds.size() * sizeof(float4)) || dev_alloc(dev, (void**)&dblob, cd.blob.size() * sizeof(uint4)))
             return false;
         bool ok = cudaMemcpyAsync(dv, cd.verts.data(), cd.verts.size() * 4, cudaMemcpyHostToDevice, dev->stream) == cudaSuccess &&
                   cudaMemcpyAsync(dt, cd.tris.data(), cd.tris.size() * 4, cudaMemcpyHostToDevice, dev->stream) == cudaSuccess &&
                   cudaMemcpyAsync(dorig, cd.orig.data(), cd.orig.size() * 4, cudaMemcpyHostToDevice, dev->stream) == cudaSuccess &&
                   cudaMemcpyAsync(di, cd.info.data(), cd.info.size() * sizeof(uint2), cudaMemcpyHostToDevice, dev->stream) == cudaSuccess &&
                   cudaMemcpyAsync(db, cd.bounds.data(), cd.bounds.size() * sizeof(float4), cudaMemcpyHostToDevice, dev->stream) == cudaSuccess &&
+                  cudaMemcpyAsync(dblob, cd.blob.data(), cd.blob.size() * sizeof(uint4), cudaMemcpyHostToDevice, dev->stream) == cudaSuccess &&
                   cudaStreamSynchronize(dev->stream) == cudaSuccess;   // cd is a local
         if (!ok) return false;
-        out = ClusterRange{dv, dt, dorig, di, db, 0u, {0, 0, 0}, 0};
+        out = ClusterRange{dv, dt, dorig, di, db, dblob, 0u, {0, 0, 0}, 0};
         range_sphere(cd, out);
         dev->ranges[key] = out;
         return true;
@@ -709,8 +816,8 @@ int vkr_create(const VkrConfig* cfg, VkrDevice** out) {
         ALLOC(dev->qShadow.items, sizeof(LargeItem) * dev->qShadow.itemCap);
         ALLOC(dev->qShadow.counters, 32 * VKR_FRAME_OVERLAP);     // per frame in flight: frame i+1's shadow pass runs beside frame i's shading, which publishes frame i's
         ALLOC(dev->transCounters, 32);
-        CK(cudaMallocHost(&dev->countersHost, 48));     // (mapped: unified addressing makes every pinned allocation device-visible)
-        std::memset(dev->countersHost, 0, 48);
+        CK(cudaMallocHost(&dev->countersHost, 64));     // (mapped: unified addressing makes every pinned allocation device-visible)
+        std::memset(dev->countersHost, 0, 64);          // [0..11] three passes' counters, [12] peer-exchange error word
         for (auto& s : dev->slots) {
             CK(cudaEventCreateWithFlags(&s.uploaded, cudaEventDisableTiming));
             CK(cudaEventCreateWithFlags(&s.rendered, cudaEventDisableTiming));
@@ -770,6 +877,7 @@ void vkr_destroy(VkrDevice* dev) {
     }
     for (auto& e : dev->tev) if (e) cudaEventDestroy(e);
     if (dev->countersHost) cudaFreeHost(dev->countersHost);
+    for (void* p : dev->ipcOpened) cudaIpcCloseMemHandle(p);
     if (dev->commShadow) ncclCommDestroy(dev->commShadow);
     if (dev->commFrame) ncclCommDestroy(dev->commFrame);
     if (dev->gatherStream) cudaStreamDestroy(dev->gatherStream);
@@ -838,6 +946,7 @@ static int build_image(VkrDevice* dev, const void* rgba8, uint32_t w, uint32_t h
     }
     CK(cudaGetLastError());
     const uint8_t* p = (const uint8_t*)rgba8;
+    std::memcpy(&im.texel0, rgba8, 4);
     im.hasCutout = false;
     for (size_t i = 0; i < (size_t)w * h; ++i) if (p[i * 4 + 3] < 128) { im.hasCutout = true; break; }
     CK(cudaStreamSynchronize(dev->stream));
@@ -849,6 +958,7 @@ static DTexture make_dtexture(const ImageRec& im, int sampler) {
     t.data = im.data; t.w = im.w; t.h = im.h; t.levels = im.levels;
     t.flags = (im.format == VKR_FORMAT_R8G8B8A8_SRGB ? 1u : 0u) | (sampler == VKR_SAMPLER_LINEAR ? 2u : 0u) | (im.hasCutout ? 4u : 0u);
     std::memcpy(t.mipOffset, im.mipOffset, sizeof(t.mipOffset));
+    t.texel0 = im.texel0;
     return t;
 }
 
@@ -938,6 +1048,7 @@ int vkr_build_material(VkrDevice* dev, const VkrMaterialConstants* p, VkrMateria
     std::memcpy(m.colorFactors, p->colorFactors, 16);
     std::memcpy(m.metalRough, p->metal_rough_factors, 16);
     m.albedoID = p->albedoID; m.normalID = p->normalID; m.metalRoughID = p->metalRoughID; m.pass = (int32_t)pass;
+    m.constFlags = 0u;               // (filled at the next vkr_draw: material_constants)
     dev->materials.push_back(m);
     dev->matDirty = true;
     *out = (VkrMaterial)(dev->materials.size() - 1);
@@ -961,7 +1072,10 @@ static int ensure_slot(VkrDevice* dev, FrameSlot& s, size_t bytes) {
 // ---- submit thread (VKR_CONFIG_SUBMIT_THREAD) -------------------------------------------------------------------
 static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n);
 
-extern "C" { static int readback_issue(VkrDevice* dev, VkrTarget what, void* dst, size_t dstBytes); }
+extern "C" {
+static int readback_issue(VkrDevice* dev, VkrTarget what, void* dst, size_t dstBytes);
+static int readback_band_issue(VkrDevice* dev, VkrTarget what, void* frameBase, size_t frameBytes);
+}
 
 static void worker_main(VkrDevice* dev) {
     cudaSetDevice(dev->device);
@@ -977,8 +1091,9 @@ static void worker_main(VkrDevice* dev) {
         if (dev->jobTail.load(std::memory_order_acquire) == head) return;        // stop requested and nothing left to issue
         const VkrDevice::Job job = dev->jobs[head % VkrDevice::JOBS];
         const auto jobT = std::chrono::steady_clock::now();
-        const int rc = job.kind == 0 ? submit_frame(dev, *job.plan, job.n) : readback_issue(dev, job.what, job.dst, job.dstBytes);
-        if (job.kind == 1 && dev->hostProf && dev->frameIndex >= 16)
+        const int rc = job.kind == 0 ? submit_frame(dev, *job.plan, job.n)
+                     : job.kind == 1 ? readback_issue(dev, job.what, job.dst, job.dstBytes) : readback_band_issue(dev, job.what, job.dst, job.dstBytes);
+        if (job.kind != 0 && dev->hostProf && dev->frameIndex >= 16)
             dev->hostProfUs[6] += std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - jobT).count();
         if (rc != VKR_SUCCESS && dev->asyncRc == VKR_SUCCESS) dev->asyncRc = rc;
         dev->jobHead.store(head + 1, std::memory_order_release);
@@ -1047,8 +1162,10 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
         CK(cudaMemcpyAsync(dev->texDev, dev->texHost.data(), sizeof(DTexture) * VKR_MAX_BINDLESS, cudaMemcpyHostToDevice, st));
         CK(cudaStreamSynchronize(st));   // texHost may change right after return
         dev->texDirty = false;
+        dev->matDirty = true;            // the materials' uv-independent texels follow the slots
     }
     if (dev->matDirty) {
+        for (DMaterial& m : dev->materials) material_constants(m, dev->texHost.data(), g_srgb_lut);
         if (dev->matCap < dev->materials.size()) {
             dev->matCap = std::max<size_t>(dev->materials.size() * 2, 64);
             ALLOC(dev->matDev, dev->matCap * sizeof(DMaterial));
@@ -1070,7 +1187,7 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
     const size_t offObj = 0, offBase = align16(offObj + szObj), offSeq = align16(offBase + szBase), offShadow = align16(offSeq + szBase),
                  offSlot = align16(offShadow + szShadow);
     const size_t total = align16(offSlot + szSlot) + 16;
-    if (slot.chunkCap < nChunks || slot.seqSlotCap < nSeqSlots || slot.permCap < (size_t)passes * nChunks) {
+    if (slot.chunkCap < nChunks || slot.seqSlotCap < nSeqSlots || slot.workCap < (size_t)(passes + 1) * nChunks) {
         // a table has to grow: the frame that last used this slot must have finished with the old one before it is released
         if (dev->frameIndex >= VKR_FRAME_OVERLAP) CK(cudaEventSynchronize(slot.rendered));
         if (slot.chunkCap < nChunks) {
@@ -1083,12 +1200,10 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
             slot.seqSlotCap = std::max<size_t>((size_t)nSeqSlots * 3 / 2, 1024);
             ALLOC(slot.chunkObjBuf, slot.seqSlotCap * sizeof(uint2));
         }
-        if (slot.permCap < (size_t)passes * nChunks) {
-            dev_free(dev, slot.permBuf); slot.permBuf = nullptr;
-            dev_free(dev, slot.cullBuf); slot.cullBuf = nullptr;
-            slot.permCap = std::max<size_t>((size_t)passes * nChunks * 3 / 2, 1024);
-            ALLOC(slot.permBuf, slot.permCap * 4);
-            ALLOC(slot.cullBuf, slot.permCap * sizeof(CullRec));
+        if (slot.workCap < (size_t)(passes + 1) * nChunks) {
+            dev_free(dev, slot.workBuf); slot.workBuf = nullptr;
+            slot.workCap = std::max<size_t>((size_t)(passes + 1) * nChunks * 3 / 2, 1024);
+            ALLOC(slot.workBuf, slot.workCap * sizeof(WorkItem));
         }
     }
     if (dev->frameIndex >= VKR_FRAME_OVERLAP) {      // pinned buffer reuse: this is where a submit thread that runs ahead waits for the device
@@ -1117,10 +1232,10 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
     const DObject* dObjects = (const DObject*)(dp + offObj);
     const DChunk* dChunks = slot.chunkBuf;
     const float* dShadowMvp = (const float*)(dp + offShadow);
-    const uint32_t* dPerm = slot.permBuf;
+    const WorkItem* dWork = slot.workBuf;
     if (n) {   // the frame's tables, on the upload stream too: neither the main nor the shadow stream has to wait for the other
         expand_chunks_kernel<<<(unsigned)n, 64, 0, dev->upStream>>>(dObjects, (const uint32_t*)(dp + offBase), (const uint32_t*)(dp + offSeq), (const uint32_t*)(dp + offSlot), dShadowMvp,
-                                                                    (uint32_t)n, passes, nChunks, plan.mainTarget, plan.shadowTarget, slot.chunkBuf, slot.chunkObjBuf, slot.permBuf, slot.cullBuf);
+                                                                    (uint32_t)n, passes, nChunks, plan.mainTarget, plan.shadowTarget, slot.chunkBuf, slot.chunkObjBuf, slot.workBuf);
         dev->launches += 1;
     }
     CK(cudaEventRecord(slot.uploaded, dev->upStream));
@@ -1129,6 +1244,20 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
     mark(1);
 
     const unsigned largeGrid = (unsigned)dev->smCount * 4;
+    // sort-first over peer memory (see "sort-first exchange over PEER MEMORY"): this frame's number + 1 is what its flags carry
+    const bool sharded = dev->shardRanks > 1;
+    const bool p2p = sharded && dev->p2p && !dev->shadowExchange;
+    const bool gatherFrame = sharded && !(dev->flags & VKR_CONFIG_LOCAL_PRESENT);
+    const uint32_t F1 = (uint32_t)dev->shardFrame + 1u;
+    const uint32_t allMask = sharded ? (uint32_t)((1ull << dev->shardRanks) - 1ull) : 0u, peersMask = allMask & ~(1u << dev->shardRank);
+    if (p2p && gatherFrame && dev->shardRank == 0) {
+        // rank 0 presents: once the image that this frame overwrites has been read back (if anybody asked), every rank may store
+        // its rows of this frame into it
+        if (slot.copyPending) CK(cudaStreamWaitEvent(dev->gatherStream, slot.copied, 0));
+        PeerList pl{}; pl.n = 0;
+        for (int r = 0; r < dev->shardRanks; ++r) pl.p[pl.n++] = &dev->peerFlags[r]->gatheredFree;
+        shard_signal_kernel<<<1, 32, 0, dev->gatherStream>>>(pl, F1);
+    }
 
     // ---- draw_shadow (src/vk_engine_run.cpp:334-382) on the shadow stream, concurrently with the main
     // pass's rasterisation: both are latency-bound, together they fill the SMs' issue slots
@@ -1141,20 +1270,26 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
         if (timing) CK(cudaEventRecord(dev->tev[7], ss));
         Queues qs = dev->qShadow;
         qs.counters = dev->qShadow.counters + 8 * slotIdx;
+        const size_t sn = (size_t)dev->S * dev->S;
+        // every layer is cleared before anything else: a sharded device then tells its peers that their rows may land
+        fill_u32_kernel<<<grid_for(sn * plan.shadowLayers / 4, 256, 2048), 256, 0, ss>>>(dev->shadowBits, sn * plan.shadowLayers, DEPTH_ONE_BITS);
+        dev->launches += 1;
+        if (p2p) {
+            PeerList pl{}; pl.n = 0;
+            for (int r = 0; r < dev->shardRanks; ++r) if (r != dev->shardRank) pl.p[pl.n++] = &dev->peerFlags[r]->shadowCleared[dev->shardRank];
+            shard_signal_kernel<<<1, 32, 0, ss>>>(pl, F1);
+        }
         for (int layer = 0; layer < plan.shadowLayers; ++layer) {
             RasterTarget rt = plan.shadowTarget;
-            rt.depthBits = dev->shadowBits + (size_t)layer * dev->S * dev->S;
-            const size_t sn = (size_t)dev->S * dev->S;
-            fill_u32_kernel<<<grid_for(sn / 4, 256, 2048), 256, 0, ss>>>(rt.depthBits, sn, DEPTH_ONE_BITS);
+            rt.depthBits = dev->shadowBits + (size_t)layer * sn;
             if (layer == 0) CK(cudaMemsetAsync(qs.counters, 0, 32, ss));
             else {        // the queue and its cursor start over; the overflow flag and the culled count are the frame's
                 CK(cudaMemsetAsync(qs.counters, 0, 8, ss));
                 CK(cudaMemsetAsync(qs.counters + 4, 0, 4, ss));
             }
-            dev->launches += 1;
             const unsigned shadowSlots = plan.passSlots[1 + layer];
             if (shadowSlots) {
-                geometry_kernel<true><<<(shadowSlots + GEOM_WARPS - 1) / GEOM_WARPS, GEOM_WARPS * 32, 0, ss>>>(dChunks, slot.cullBuf + (size_t)(1 + layer) * nChunks, dPerm + (size_t)(1 + layer) * nChunks, shadowSlots,
+                geometry_kernel<true><<<(shadowSlots + GEOM_WARPS - 1) / GEOM_WARPS, GEOM_WARPS * 32, 0, ss>>>(dWork + (size_t)(1 + layer) * nChunks, shadowSlots,
                                                                                                       dShadowMvp + (size_t)layer * n * 16, 16u, rt, qs);
                 large_raster_kernel<true><<<largeGrid, 256, 0, ss>>>(rt, qs, AlphaCtx{}, 0);
                 dev->launches += 2;
@@ -1162,12 +1297,33 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
         }
         if (timing) CK(cudaEventRecord(dev->tev[10], ss));
         if (dev->shardRanks > 1) {      // complete every layer from the other ranks' row bands (only rows a caster can reach)
-            for (int layer = 0; layer < plan.shadowLayers; ++layer) {
-                uint32_t* base = dev->shadowBits + (size_t)layer * dev->S * dev->S;
-                // layer 0's casters define the active rows; other cascades see the scene at another scale: exchange them whole
-                const int lo = layer == 0 ? plan.activeShadow[0] : 0, hi = layer == 0 ? plan.activeShadow[1] : (int)dev->S;
-                if (exchange_bands(base, base, plan.bandShadow, lo, hi, dev->S, dev->shardRank, dev->shardRanks, dev->commShadow, ss) != ncclSuccess)
-                    return dev->fail(VKR_ERROR_CUDA, "NCCL shadow band exchange");
+            auto clampRow = [](int32_t y, int lo, int hi) { return std::min(std::max(y, lo), hi); };
+            if (p2p) {
+                // peer memory: wait until every peer has cleared its map for this frame, store my rows into all of them, tell
+                // them, and wait for theirs
+                shard_wait_kernel<<<1, 32, 0, ss>>>(dev->myFlags->shadowCleared, peersMask, F1, dev->countersHost + 12, 1u);
+                PeerList maps{}; maps.n = 0;
+                for (int r = 0; r < dev->shardRanks; ++r) if (r != dev->shardRank) maps.p[maps.n++] = dev->peerShadow[r][slotIdx];
+                for (int layer = 0; layer < plan.shadowLayers; ++layer) {
+                    const int lo = layer == 0 ? plan.activeShadow[0] : 0, hi = layer == 0 ? plan.activeShadow[1] : (int)dev->S;
+                    const int32_t m0 = clampRow(plan.bandShadow[dev->shardRank], lo, hi), m1 = clampRow(plan.bandShadow[dev->shardRank + 1], lo, hi);
+                    if (m1 <= m0) continue;
+                    const size_t first = (size_t)layer * sn + (size_t)m0 * dev->S, count = (size_t)(m1 - m0) * dev->S;
+                    shard_push_rows_kernel<<<grid_for(count / 4, 256, (unsigned)dev->smCount * 4), 256, 0, ss>>>(dev->shadowBits, maps, first, count);
+                    dev->launches += 1;
+                }
+                PeerList pl{}; pl.n = 0;
+                for (int r = 0; r < dev->shardRanks; ++r) if (r != dev->shardRank) pl.p[pl.n++] = &dev->peerFlags[r]->shadowReady[dev->shardRank];
+                shard_signal_kernel<<<1, 32, 0, ss>>>(pl, F1);
+                shard_wait_kernel<<<1, 32, 0, ss>>>(dev->myFlags->shadowReady, peersMask, F1, dev->countersHost + 12, 2u);
+            } else {
+                for (int layer = 0; layer < plan.shadowLayers; ++layer) {
+                    uint32_t* base = dev->shadowBits + (size_t)layer * sn;
+                    // layer 0's casters define the active rows; other cascades see the scene at another scale: exchange them whole
+                    const int lo = layer == 0 ? plan.activeShadow[0] : 0, hi = layer == 0 ? plan.activeShadow[1] : (int)dev->S;
+                    if (exchange_bands(base, base, plan.bandShadow, lo, hi, dev->S, dev->shardRank, dev->shardRanks, dev->commShadow, ss) != ncclSuccess)
+                        return dev->fail(VKR_ERROR_CUDA, "NCCL shadow band exchange");
+                }
             }
         }
         if (dev->shadowExchange) {
@@ -1202,7 +1358,7 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
         const unsigned opaqueChunks = plan.opaqueClusters, mainSlots = plan.passSlots[0];
         if (opaqueChunks) {
             if (mainSlots)
-                geometry_kernel<false><<<(mainSlots + GEOM_WARPS - 1) / GEOM_WARPS, GEOM_WARPS * 32, 0, st>>>(dChunks, slot.cullBuf, dPerm, mainSlots, (const float*)dObjects,
+                geometry_kernel<false><<<(mainSlots + GEOM_WARPS - 1) / GEOM_WARPS, GEOM_WARPS * 32, 0, st>>>(dWork, mainSlots, (const float*)dObjects,
                                                                                                             (uint32_t)(sizeof(DObject) / 4), rt, dev->q);
             if (timing) CK(cudaEventRecord(dev->tev[4], st));
             if (kpair) { CK(cudaEventRecord(kpair[1], st)); dev->kevRecorded++; }
@@ -1243,7 +1399,7 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
         RasterTarget rt = plan.mainTarget;
         rt.vis = dev->vis;
         geometry_transparent_kernel<<<(transChunks + GEOM_WARPS - 1) / GEOM_WARPS, GEOM_WARPS * 32, 0, st>>>(
-            dChunks, slot.cullBuf, plan.opaqueClusters, transChunks, (const float*)dObjects, (uint32_t)(sizeof(DObject) / 4), rt, qt, sc, sb);
+            dWork + (size_t)passes * nChunks + plan.opaqueClusters, transChunks, (const float*)dObjects, (uint32_t)(sizeof(DObject) / 4), rt, qt, sc, sb);
         large_transparent_kernel<<<largeGrid, 256, 0, st>>>(rt, qt, sc, sb);
         dev->launches += 2;
     }
@@ -1254,8 +1410,13 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
     if (timing) CK(cudaEventRecord(dev->tev[9], st));
 
     // ---- shading half of draw_geometry + draw_skybox + draw_background + draw_postprocess + present blit
-    if (dev->shardRanks > 1 && dev->gatheredValid[slotIdx]) CK(cudaStreamWaitEvent(st, dev->gatheredEv[slotIdx], 0));   // rgba8[slot] still being gathered
+    if (sharded && !p2p && dev->gatheredValid[slotIdx]) CK(cudaStreamWaitEvent(st, dev->gatheredEv[slotIdx], 0));   // rgba8[slot] still being gathered
     if (slot.copyPending) CK(cudaStreamWaitEvent(st, slot.copied, 0));      // ... or still being read back (FRAME_OVERLAP frames ago)
+    if (p2p && gatherFrame) {
+        // the shading kernel stores this rank's rows into rank 0's image as well: wait until rank 0 has released it
+        shard_wait_kernel<<<1, 32, 0, st>>>(&dev->myFlags->gatheredFree, 1u, F1, dev->countersHost + 12, 3u);
+        sb.rgba8Peer = dev->rootGathered[slotIdx];
+    }
     {
         dim3 grid((sc.sx1 - sc.sx0 + 15) / 16, (sc.sy1 - sc.sy0 + 7) / 8);
         if (grid.x && grid.y) { shade_kernel<<<grid, 128, 0, st>>>(sc, sb); dev->launches += 1; }
@@ -1267,10 +1428,15 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
         dev->visClean = transientDepth;
     }
     if (timing) { CK(cudaEventRecord(dev->tev[6], st)); dev->tevValid = true; dev->shadowTimed = plan.shadowLayers > 0; }
+    if (p2p && gatherFrame) {           // my rows of this frame are in rank 0's image
+        PeerList pl{}; pl.n = 1; pl.p[0] = &dev->peerFlags[0]->frameReady[dev->shardRank];
+        shard_signal_kernel<<<1, 32, 0, st>>>(pl, F1);
+        dev->lastGatherF1 = F1;
+    } else if (sharded) dev->lastGatherF1 = 0;
     CK(cudaGetLastError());
     CK(cudaEventRecord(slot.rendered, st));
     mark(4);
-    if (dev->shardRanks > 1) {          // assemble the presented image; overlaps the next frame's rendering
+    if (sharded && !p2p && gatherFrame) {          // assemble the presented image; overlaps the next frame's rendering
         CK(cudaStreamWaitEvent(dev->gatherStream, slot.rendered, 0));
         if (slot.copyPending) CK(cudaStreamWaitEvent(dev->gatherStream, slot.copied, 0));   // the landing buffer may still be being read back
         if (timing) CK(cudaEventRecord(dev->tev[11], dev->gatherStream));
@@ -1284,6 +1450,8 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
     mark(5);
     if (dev->hostProf && dev->frameIndex >= 16) dev->hostProfFrames++;
     dev->lastSlot = slotIdx;
+    if (sharded) { dev->shardFrame++; dev->lastBand[0] = plan.bandMain[dev->shardRank]; dev->lastBand[1] = plan.bandMain[dev->shardRank + 1]; }
+    else { dev->lastBand[0] = 0; dev->lastBand[1] = (int32_t)dev->H; }
     dev->lastPlan = &plan; dev->lastN = n;
     dev->lastChunkObj = slot.chunkObjBuf; dev->lastObjects = dObjects;
     dev->frameIndex++;
@@ -1305,6 +1473,16 @@ int vkr_sync(VkrDevice* dev) {
     CK(cudaStreamSynchronize(dev->copyStream));
     CK(cudaStreamSynchronize(dev->shadowStream));
     if (dev->gatherStream) CK(cudaStreamSynchronize(dev->gatherStream));
+    if (dev->p2p && dev->shardRank == 0 && dev->lastGatherF1) {      // "everything issued" includes the peers' rows of the last frame
+        shard_wait_kernel<<<1, 32, 0, dev->copyStream>>>(dev->myFlags->frameReady, (uint32_t)((1ull << dev->shardRanks) - 1ull), dev->lastGatherF1, dev->countersHost + 12, 4u);
+        CK(cudaStreamSynchronize(dev->copyStream));
+    }
+    if (dev->countersHost[12]) {
+        char msg[128];
+        std::snprintf(msg, sizeof msg, "peer exchange timed out (wait %u on rank %u)", dev->countersHost[12] & 0xFFu, dev->countersHost[12] >> 8);
+        dev->countersHost[12] = 0;
+        return dev->fail(VKR_ERROR_CUDA, msg);
+    }
     // A large-triangle queue overflowed in the last frame (its image misses those triangles): the counters kept counting, so
     // they say how much room the frame needs.  Grow the queues and draw the frame again before returning; a read-back that
     // follows sees the complete frame.  Only an asynchronous read-back ALREADY issued for the incomplete frame cannot be
@@ -1376,6 +1554,8 @@ static int target_info(VkrDevice* dev, VkrTarget what, const void** src, size_t*
     switch (what) {
         case VKR_TARGET_RGBA8: *src = dev->rgba8[dev->lastSlot]; *bytes = px * 4; return 0;
         case VKR_TARGET_RGBA8_GATHERED: case VKR_TARGET_RGB8:
+            // over peer memory only rank 0 holds the assembled frame, and only if the last frame was assembled at all
+            if (dev->shardRanks > 1 && dev->p2p && (dev->shardRank != 0 || dev->lastGatherF1 == 0)) return -1;
             *src = dev->shardRanks <= 1 ? dev->rgba8[dev->lastSlot] : dev->gathered[dev->lastSlot];
             *bytes = what == VKR_TARGET_RGB8 ? px * 3 : px * 4;
             return 0;
@@ -1393,8 +1573,11 @@ static int readback_issue(VkrDevice* dev, VkrTarget what, void* dst, size_t dstB
     if (target_info(dev, what, &src, &bytes) || dstBytes < bytes) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_readback: bad target");
     // copy engine work goes to the copy stream so the next frame's kernels overlap it
     CK(cudaStreamWaitEvent(dev->copyStream, dev->slots[dev->lastSlot].rendered, 0));
-    if ((what == VKR_TARGET_RGBA8_GATHERED || what == VKR_TARGET_RGB8) && dev->shardRanks > 1)
-        CK(cudaStreamWaitEvent(dev->copyStream, dev->gatheredEv[dev->lastSlot], 0));
+    if ((what == VKR_TARGET_RGBA8_GATHERED || what == VKR_TARGET_RGB8) && dev->shardRanks > 1) {
+        if (dev->p2p)      // every rank's rows of that frame have landed in my image
+            shard_wait_kernel<<<1, 32, 0, dev->copyStream>>>(dev->myFlags->frameReady, (uint32_t)((1ull << dev->shardRanks) - 1ull), dev->lastGatherF1, dev->countersHost + 12, 4u);
+        else CK(cudaStreamWaitEvent(dev->copyStream, dev->gatheredEv[dev->lastSlot], 0));
+    }
     if (what == VKR_TARGET_RGB8) {
         const size_t px = (size_t)dev->W * dev->H;
         uint32_t*& packed = dev->rgb8[dev->lastSlot];
@@ -1463,6 +1646,52 @@ static int do_readback(VkrDevice* dev, VkrTarget what, void* dst, size_t dstByte
     return VKR_SUCCESS;
 }
 
+// This rank's rows of the presented image of the last frame, into their place in a whole-frame buffer at frameBase.
+static int readback_band_issue(VkrDevice* dev, VkrTarget what, void* frameBase, size_t frameBytes) {
+    const size_t bpp = what == VKR_TARGET_RGB8 ? 3 : 4, rowBytes = (size_t)dev->W * bpp;
+    if ((what != VKR_TARGET_RGB8 && what != VKR_TARGET_RGBA8) || !frameBase || frameBytes < rowBytes * dev->H)
+        return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_readback_band_async: RGBA8 or RGB8 into a whole-frame buffer");
+    const int32_t y0 = dev->lastBand[0], y1 = dev->lastBand[1];
+    FrameSlot& sl = dev->slots[dev->lastSlot];
+    const uint32_t* src = dev->rgba8[dev->lastSlot] + (size_t)y0 * dev->W;
+    const size_t px = (size_t)(y1 - y0) * dev->W;
+    CK(cudaStreamWaitEvent(dev->copyStream, sl.rendered, 0));
+    const void* from = src;
+    if (what == VKR_TARGET_RGB8 && px) {
+        const size_t all = (size_t)dev->W * dev->H;
+        uint32_t*& packed = dev->rgb8[dev->lastSlot];
+        if (!packed) ALLOC(packed, all * 3 + 16);
+        // (the band starts at a multiple of W pixels: 4-pixel groups stay aligned when W is a multiple of 4, else pack the whole image)
+        if ((dev->W & 3u) == 0u) {
+            uint32_t* out = packed + (size_t)y0 * dev->W * 3 / 4;
+            pack_rgb8_kernel<<<(unsigned)(((px >> 2) + 256) / 256), 256, 0, dev->stream>>>(src, out, px);
+            from = out;
+        } else {
+            pack_rgb8_kernel<<<(unsigned)(((all >> 2) + 256) / 256), 256, 0, dev->stream>>>(dev->rgba8[dev->lastSlot], packed, all);
+            from = reinterpret_cast<const uint8_t*>(packed) + (size_t)y0 * rowBytes;
+        }
+        CK(cudaGetLastError());
+        CK(cudaEventRecord(dev->packedEv, dev->stream));
+        CK(cudaStreamWaitEvent(dev->copyStream, dev->packedEv, 0));
+    }
+    if (px) CK(cudaMemcpyAsync(reinterpret_cast<uint8_t*>(frameBase) + (size_t)y0 * rowBytes, from, px * bpp, cudaMemcpyDeviceToHost, dev->copyStream));
+    CK(cudaEventRecord(sl.copied, dev->copyStream));
+    sl.copyPending = true;
+    sl.copiedFrame = dev->frameIndex;
+    return VKR_SUCCESS;
+}
+
+int vkr_readback_band_async(VkrDevice* dev, VkrTarget what, void* frameBase, size_t frameBytes) {
+    if (!dev) return VKR_ERROR_INVALID_ARGUMENT;
+    if (dev->worker.joinable() && (dev->flags & VKR_CONFIG_SUBMIT_THREAD)) {
+        post_job(dev, VkrDevice::Job{2, nullptr, 0, what, frameBase, frameBytes});
+        return VKR_SUCCESS;
+    }
+    DRAIN(dev);
+    CK(cudaSetDevice(dev->device));
+    return readback_band_issue(dev, what, frameBase, frameBytes);
+}
+
 int vkr_readback(VkrDevice* dev, VkrTarget what, void* dst, size_t dstBytes) { return do_readback(dev, what, dst, dstBytes, true); }
 int vkr_readback_async(VkrDevice* dev, VkrTarget what, void* dst, size_t dstBytes) { return do_readback(dev, what, dst, dstBytes, false); }
 
@@ -1510,10 +1739,11 @@ int vkr_comm_unique_id(void* out, size_t bytes) {
 int vkr_shard_init(VkrDevice* dev, int rank, int nranks, const void* twoIds, size_t bytes) {
     if (!dev) return VKR_ERROR_INVALID_ARGUMENT;
     DRAIN(dev);
-    if (!twoIds || bytes < 2 * VKR_COMM_ID_BYTES || nranks < 1 || rank < 0 || rank >= nranks)
+    if (!twoIds || bytes < 2 * VKR_COMM_ID_BYTES || nranks < 1 || nranks > MAX_RANKS || rank < 0 || rank >= nranks)
         return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_shard_init: bad arguments");
     if ((int)dev->H < nranks || (int)dev->S < nranks) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_shard_init: more ranks than rows");
     if (dev->commShadow || dev->commFrame) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_shard_init: already initialised");
+    if (dev->frameIndex != 0) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_shard_init: must precede the first vkr_draw (the ranks count frames together)");
     CK(cudaSetDevice(dev->device));
     if (nranks == 1) return VKR_SUCCESS;
     ncclUniqueId ids[2];
@@ -1526,10 +1756,83 @@ int vkr_shard_init(VkrDevice* dev, int rank, int nranks, const void* twoIds, siz
     CK(cudaStreamCreateWithPriority(&dev->gatherStream, cudaStreamNonBlocking, prHi));
     const size_t px = (size_t)dev->W * dev->H;
     for (int i = 0; i < VKR_FRAME_OVERLAP; ++i) {
-        ALLOC(dev->gathered[i], px * 4);
+        ALLOC(dev->gathered[i], px * 4 + (i == 0 ? 4096 : 0));      // + the flags (one allocation = one IPC handle)
         CK(cudaEventCreateWithFlags(&dev->gatheredEv[i], cudaEventDisableTiming));
     }
     dev->shardRank = rank; dev->shardRanks = nranks;
+
+    // ---- peer memory: every rank publishes IPC handles of its two shadow maps and its two assembled images (the flags sit
+    // behind the first image), the handles travel through the communicator that was just made, every rank maps its peers'.
+    // VKR_EXCHANGE=nccl keeps the NCCL send/recv exchange (also the fallback when the mapping fails).
+    const char* mode = std::getenv("VKR_EXCHANGE");
+    if (mode && std::strcmp(mode, "nccl") == 0) return VKR_SUCCESS;
+    struct Pack { cudaIpcMemHandle_t shadow[VKR_FRAME_OVERLAP], gathered[VKR_FRAME_OVERLAP]; };
+    std::vector<Pack> packs((size_t)nranks);
+    Pack& mine = packs[(size_t)rank];
+    bool ok = true;
+    for (int i = 0; i < VKR_FRAME_OVERLAP && ok; ++i)
+        ok = cudaIpcGetMemHandle(&mine.shadow[i], dev->shadowBuf[i]) == cudaSuccess && cudaIpcGetMemHandle(&mine.gathered[i], dev->gathered[i]) == cudaSuccess;
+    Pack* dpacks = nullptr;
+    ALLOC(dpacks, sizeof(Pack) * (size_t)nranks);
+    // (every rank takes part in the all-gather even if its own export failed: `ok` travels in the first byte being zeroed)
+    if (!ok) std::memset(&mine, 0, sizeof(Pack));
+    CK(cudaMemcpyAsync(dpacks + rank, &mine, sizeof(Pack), cudaMemcpyHostToDevice, dev->stream));
+    CK(cudaMemsetAsync(reinterpret_cast<char*>(dev->gathered[0]) + px * 4, 0, 4096, dev->stream));
+    if (ncclAllGather(dpacks + rank, dpacks, sizeof(Pack), ncclChar, dev->commShadow, dev->stream) != ncclSuccess)
+        return dev->fail(VKR_ERROR_CUDA, "vkr_shard_init: exchanging the IPC handles");
+    CK(cudaMemcpyAsync(packs.data(), dpacks, sizeof(Pack) * (size_t)nranks, cudaMemcpyDeviceToHost, dev->stream));
+    CK(cudaStreamSynchronize(dev->stream));
+    dev_free(dev, dpacks);
+    const Pack zero{};
+    for (int p = 0; p < nranks; ++p) if (std::memcmp(&packs[(size_t)p], &zero, sizeof(Pack)) == 0) ok = false;
+    dev->myFlags = reinterpret_cast<ShardFlags*>(reinterpret_cast<char*>(dev->gathered[0]) + px * 4);
+    for (int p = 0; p < nranks && ok; ++p) {
+        if (p == rank) {
+            for (int i = 0; i < VKR_FRAME_OVERLAP; ++i) dev->peerShadow[p][i] = dev->shadowBuf[i];
+            dev->peerFlags[p] = dev->myFlags;
+            if (p == 0) for (int i = 0; i < VKR_FRAME_OVERLAP; ++i) dev->rootGathered[i] = dev->gathered[i];
+            continue;
+        }
+        for (int i = 0; i < VKR_FRAME_OVERLAP && ok; ++i) {
+            void* q = nullptr;
+            ok = cudaIpcOpenMemHandle(&q, packs[(size_t)p].shadow[i], cudaIpcMemLazyEnablePeerAccess) == cudaSuccess;
+            if (ok) { dev->ipcOpened.push_back(q); dev->peerShadow[p][i] = (uint32_t*)q; }
+        }
+        // the flags of every peer (behind its first image); the images themselves only of rank 0, which presents
+        void* g0 = nullptr;
+        if (ok) ok = cudaIpcOpenMemHandle(&g0, packs[(size_t)p].gathered[0], cudaIpcMemLazyEnablePeerAccess) == cudaSuccess;
+        if (ok) { dev->ipcOpened.push_back(g0); dev->peerFlags[p] = reinterpret_cast<ShardFlags*>(reinterpret_cast<char*>(g0) + px * 4); }
+        if (ok && p == 0) {
+            void* g1 = nullptr;
+            ok = cudaIpcOpenMemHandle(&g1, packs[0].gathered[1], cudaIpcMemLazyEnablePeerAccess) == cudaSuccess;
+            if (ok) { dev->ipcOpened.push_back(g1); dev->rootGathered[0] = (uint32_t*)g0; dev->rootGathered[1] = (uint32_t*)g1; }
+        }
+    }
+    if (!ok) {
+        cudaGetLastError();
+        for (void* q : dev->ipcOpened) cudaIpcCloseMemHandle(q);
+        dev->ipcOpened.clear();
+    }
+    // all or nothing: the ranks agree on the exchange they use (min over the ranks of `ok`)
+    int* dflag = nullptr;
+    ALLOC(dflag, sizeof(int));
+    const int mineOk = ok ? 1 : 0;
+    CK(cudaMemcpyAsync(dflag, &mineOk, sizeof(int), cudaMemcpyHostToDevice, dev->stream));
+    if (ncclAllReduce(dflag, dflag, 1, ncclInt, ncclMin, dev->commShadow, dev->stream) != ncclSuccess)
+        return dev->fail(VKR_ERROR_CUDA, "vkr_shard_init: agreeing on the exchange");
+    int allOk = 0;
+    CK(cudaMemcpyAsync(&allOk, dflag, sizeof(int), cudaMemcpyDeviceToHost, dev->stream));
+    CK(cudaStreamSynchronize(dev->stream));
+    dev_free(dev, dflag);
+    dev->p2p = allOk == 1;
+    if (!dev->p2p) dev->err = "vkr_shard_init: peer memory unavailable, exchanging over NCCL";
+    return VKR_SUCCESS;
+}
+
+int vkr_shard_info(VkrDevice* dev, int32_t out[4]) {
+    if (!dev || !out) return VKR_ERROR_INVALID_ARGUMENT;
+    DRAIN(dev);
+    out[0] = dev->lastBand[0]; out[1] = dev->lastBand[1]; out[2] = dev->p2p ? 1 : 0; out[3] = dev->shardRanks;
     return VKR_SUCCESS;
 }
 

@@ -73,6 +73,7 @@ struct ClusterData {
     std::vector<uint32_t> orig;      // nClusters * CL_TRIS submission-order triangle numbers
     std::vector<uint2> info;         // per cluster
     std::vector<float4> bounds;      // per cluster: min, max
+    std::vector<uint4> blob;         // per cluster CL_BLOB_BYTES: interleaved (tris, orig), then the gathered positions
 };
 // Spatial order of a draw's triangles for the greedy cut below: a k-d partition of the centroids whose split points are
 // multiples of CL_TRIS.  A range that needs k = ceil(n / CL_TRIS) clusters is split along the longest axis of its centroid
@@ -118,7 +119,7 @@ inline void spatial_order(const uint32_t* idx, uint32_t triCount, const float4* 
 // `pos` are the mesh's positions (x,y,z,1).  Triangles are put in spatial_order, then cut greedily: a cluster
 // closes when it holds CL_TRIS triangles or the next triangle would take it past CL_VERTS vertices.
 inline void build_clusters(const uint32_t* idx, uint32_t triCount, uint32_t nv, const float4* pos, ClusterData& out) {
-    out.verts.clear(); out.tris.clear(); out.orig.clear(); out.info.clear(); out.bounds.clear();
+    out.verts.clear(); out.tris.clear(); out.orig.clear(); out.info.clear(); out.bounds.clear(); out.blob.clear();
     std::vector<uint32_t> order;
     spatial_order(idx, triCount, pos, order);
     std::vector<uint32_t> stamp(nv, 0xFFFFFFFFu), local(nv, 0u);
@@ -158,12 +159,20 @@ inline void build_clusters(const uint32_t* idx, uint32_t triCount, uint32_t nv, 
         // (positions are required to be finite; min/max skip NaNs)
         out.bounds.push_back(make_float4(lo[0], lo[1], lo[2], 0.0f));
         out.bounds.push_back(make_float4(hi[0], hi[1], hi[2], 0.0f));
+        {   // the cluster's self-contained block
+            const size_t b0 = out.blob.size();
+            out.blob.resize(b0 + CL_BLOB_BYTES / 16, uint4{0u, 0u, 0u, 0u});
+            uint32_t* tw = reinterpret_cast<uint32_t*>(out.blob.data() + b0);
+            for (uint32_t k = 0; k < nt; ++k) { tw[2 * k] = out.tris[(size_t)c * CL_TRIS + k]; tw[2 * k + 1] = out.orig[(size_t)c * CL_TRIS + k]; }
+            float4* pw = reinterpret_cast<float4*>(out.blob.data() + b0 + CL_BLOB_TRI_BYTES / 16);
+            for (uint32_t k = 0; k < count; ++k) { const float4 q = pos[out.verts[off + k]]; pw[k] = make_float4(q.x, q.y, q.z, 1.0f); }
+        }
         ++c;
     }
 }
 
 struct ClusterRange {
-    const uint32_t* verts; const uint32_t* tris; const uint32_t* orig; const uint2* info; const float4* bounds;
+    const uint32_t* verts; const uint32_t* tris; const uint32_t* orig; const uint2* info; const float4* bounds; const uint4* blob;
     uint32_t nClusters;
     float center[3], radius;          // bounding sphere of the whole range (object space), for the processing order
 };
@@ -254,8 +263,7 @@ inline std::string plan_frame(const VkrGPUSceneData* scene, const VkrRenderObjec
         o.triCount = ro.indexCount / 3;
         ClusterRange cr{};
         if (o.triCount && !clusters.get(ro.mesh, ro.firstIndex, ro.indexCount, cr)) return "out of memory building clusters";
-        o.clVerts = cr.verts; o.clTris = cr.tris; o.clOrig = cr.orig; o.clInfo = cr.info; o.clBounds = cr.bounds;
-        o.pad[0] = o.pad[1] = 0;
+        o.clVerts = cr.verts; o.clTris = cr.tris; o.clOrig = cr.orig; o.clInfo = cr.info; o.clBounds = cr.bounds; o.clBlob = cr.blob;
         // bounding sphere of the draw's range (object space): sort key of the processing order below
         sphere[4 * i] = cr.center[0]; sphere[4 * i + 1] = cr.center[1]; sphere[4 * i + 2] = cr.center[2]; sphere[4 * i + 3] = cr.radius;
         o.primBase = (uint32_t)prim;

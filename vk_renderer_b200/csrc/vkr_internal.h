@@ -15,6 +15,7 @@ struct alignas(16) float4 { float x, y, z, w; };
 struct alignas(8) float2 { float x, y; };
 struct alignas(4) uchar4 { unsigned char x, y, z, w; };
 struct alignas(8) uint2 { unsigned int x, y; };
+struct alignas(16) uint4 { unsigned int x, y, z, w; };
 static inline float4 make_float4(float x, float y, float z, float w) { return float4{x, y, z, w}; }
 #endif
 
@@ -43,7 +44,7 @@ static const int GEOM_WARPS = VKR_GEOM_WARPS;   // warps (clusters) per geometry
 #define VKR_SHADE_MIN_CTAS 12              // shading CTAs (128 threads) resident per SM the register allocation must allow
 #endif
 #ifndef VKR_GEOM_MIN_CTAS
-#define VKR_GEOM_MIN_CTAS 12               // geometry CTAs resident per SM the register allocation must allow (48 warps, 40 registers)
+#define VKR_GEOM_MIN_CTAS 12               // geometry CTAs resident per SM the register allocation must allow (48 warps, 40 registers; 15 KB of shared memory per CTA)
 #endif
 static const float GUARD_BAND = 64.0f;     // clip x,y only beyond +-GUARD_BAND*w
 
@@ -77,7 +78,7 @@ struct DObject {
     uint32_t primBase;        // dense submission-order id of this draw's first triangle (readback only)
     uint32_t material;
     uint32_t flags;           // bit0: transparent pass, bit1: alpha-tested (albedo texture has alpha < 0.5), bit2: a sampled texture has mips
-    uint32_t pad[2];
+    const uint4* clBlob;      // the same clusters as self-contained CL_BLOB_BYTES blocks (what the geometry kernels stage with one bulk copy)
 };
 static_assert(sizeof(DObject) % 16 == 0, "DObject array is read with 16-byte loads");
 
@@ -94,7 +95,26 @@ static_assert(sizeof(DObject) % 16 == 0, "DObject array is read with 16-byte loa
 // Primitive sequence numbers stay in SUBMISSION order whatever the processing order: a draw owns
 // ceil(triCount / 256) slots of 256 numbers starting at seqBase, triangle t of the draw is seqBase + t,
 // so seq >> 8 indexes the frame's (draw, first triangle) table and later primitives win equal-depth ties.
-struct DChunk {               // what one geometry warp needs, written on the device by expand_chunks_kernel
+// A cluster as ONE contiguous block (CL_BLOB_BYTES apart), what a geometry warp brings into its shared memory with a single
+// bulk copy (cp.async.bulk, the TMA unit) before it knows whether the cluster survives the occlusion test:
+//   [0, 1024)     uint2[CL_TRIS]   (l0 | l1 << 7 | l2 << 14, the triangle's number in the draw)   — clTris and clOrig interleaved
+//   [1024, 3072)  float4[CL_VERTS] the cluster's distinct vertices' positions (x, y, z, 1)         — pos[clVerts[..]] gathered
+// Only the first 1024 + 16 * vertexCount bytes are copied.
+static const uint32_t CL_BLOB_TRI_BYTES = CL_TRIS * 8u, CL_BLOB_BYTES = CL_BLOB_TRI_BYTES + CL_VERTS * 16u;
+
+// One geometry warp's work: cluster `c` of a draw in one pass, with the outcome of its cluster test (CullRec), written per
+// frame by expand_chunks_kernel in the pass's PROCESSING order (front to back by draw) — the warp reads 32 bytes at its slot,
+// no indirection.
+struct WorkItem {
+    const uint4* blob;        // the cluster's block
+    uint32_t obj, seqBase;    // draw; first sequence number of the draw
+    uint32_t info;            // vertexCount | triCount << 8 | draw flags << 16 (bit0 transparent, bit1 alpha-tested) | verdict << 24
+    uint32_t rect0, rect1;    // CullRec: x0 | y0 << 16, x1 | y1 << 16
+    uint32_t zminBits;
+};
+static_assert(sizeof(WorkItem) == 32, "WorkItem is read as two 16-byte words");
+
+struct DChunk {               // a cluster as the cut-out kernel and the read-back paths see it, written on the device by expand_chunks_kernel
     const float4* pos;        // mesh positions
     const uint32_t* clVerts;  // this cluster's distinct-vertex list
     const uint32_t* clTris;   // this cluster's packed triangles
@@ -124,11 +144,31 @@ VKR_HD DChunk make_chunk(const DObject& o, uint32_t obj, uint32_t c, uint32_t se
     return ch;
 }
 
+// The work item of cluster c of draw `obj` (first sequence slot `seqSlot`) with the outcome `cr` of its cluster test.
+VKR_HD WorkItem make_work_item(const DObject& o, uint32_t obj, uint32_t c, uint32_t seqSlot, const CullRec& cr) {
+    const uint2 info = o.clInfo[c];
+    WorkItem w;
+    w.blob = o.clBlob + (size_t)c * (CL_BLOB_BYTES / 16u);
+    w.obj = obj; w.seqBase = seqSlot * SEQ_SLOT;
+    w.info = (info.y & 0xFFu) | ((info.y >> 16) << 8) | ((o.flags & 0xFFu) << 16) | ((uint32_t)cr.verdict << 24);
+    w.rect0 = (uint32_t)(uint16_t)cr.x0 | ((uint32_t)(uint16_t)cr.y0 << 16);
+    w.rect1 = (uint32_t)(uint16_t)cr.x1 | ((uint32_t)(uint16_t)cr.y1 << 16);
+    w.zminBits = cr.zminBits;
+    return w;
+}
+
 struct DMaterial {
     float colorFactors[4];
     float metalRough[4];
     int32_t albedoID, normalID, metalRoughID, pass;
+    // what texture() returns for the albedo / metal-rough slot when that does not depend on uv — a 1x1 image (the engine's default
+    // textures, i.e. every untextured material) or an unbound slot; filled by material_constants() whenever materials or bindless
+    // slots change, so the shading pass does not walk a descriptor to fetch the same texel for every pixel
+    float albedoTexel[4], mrTexel[4];
+    uint32_t constFlags;      // bit0: albedoTexel valid, bit1: mrTexel valid
+    uint32_t pad[3];
 };
+static_assert(sizeof(DMaterial) == 96, "DMaterial");
 
 struct DTexture {             // one bindless slot (combined image sampler)
     const uchar4* data;       // mip chain, level l at data + mipOffset[l]
@@ -136,6 +176,7 @@ struct DTexture {             // one bindless slot (combined image sampler)
     uint32_t flags;           // bit0: sRGB, bit1: LINEAR sampler (else NEAREST), bit2: has alpha < 0.5 somewhere,
                               // bit3: texels are 4 x f16 (8 bytes; cube maps only), `data` then points at uint2 texels
     uint32_t mipOffset[16];
+    uint32_t texel0, pad;     // the first texel of level 0 as uploaded (host-side use: material_constants)
 };
 
 // A projected, snapped, oriented triangle too large for the in-thread path (48 B).
@@ -199,6 +240,7 @@ struct ShadeBuffers {
     float* accum;                      // RGBA32F sums of the transparent pass (nullptr: the frame has none)
     uint16_t* hdr;                     // RGBA16F
     uint32_t* rgba8;
+    uint32_t* rgba8Peer;               // sharded over peer memory: the presenting rank's image (mapped here), stored to as well; else nullptr
     const float* srgbLut;              // 256 floats
     // the frame's queue counters (main, shadow, transparent pass; 4 words each, nullptr: pass not run) and their pinned host
     // mirror, which the shading kernel fills through its mapped address: a 16-byte cudaMemcpyAsync on a render stream would

@@ -89,7 +89,8 @@ struct SetupTri {
 VKR_HD bool setup_snapped(SnapVtx v0, SnapVtx v1, SnapVtx v2, const RasterTarget& rt, SetupTri& t) {
     const int32_t d1x = v1.X - v0.X, d1y = v1.Y - v0.Y, d2x = v2.X - v0.X, d2y = v2.Y - v0.Y;
     int64_t A2;
-    if ((iabs(d1x) | iabs(d1y) | iabs(d2x) | iabs(d2y)) < 32768) A2 = (int64_t)(d1x * d2y - d2x * d1y);   // fits int32
+    const bool narrow = (iabs(d1x) | iabs(d1y) | iabs(d2x) | iabs(d2y)) < 32768;      // the doubled area fits int32 (every small triangle)
+    if (narrow) A2 = (int64_t)(d1x * d2y - d2x * d1y);
     else A2 = (int64_t)d1x * d2y - (int64_t)d2x * d1y;
     if (A2 == 0) return false;
     const bool front = A2 < 0;                 // CCW front in Vulkan's y-down framebuffer (a = -A2/2 > 0)
@@ -108,7 +109,7 @@ VKR_HD bool setup_snapped(SnapVtx v0, SnapVtx v1, SnapVtx v2, const RasterTarget
     // depth plane about vertex 0: z(x,y) = z0 + dzdx*(x-x0) + dzdy*(y-y0), x,y in pixels
     const float e1x = xi2f(v1.X - v0.X), e1y = xi2f(v1.Y - v0.Y), e2x = xi2f(v2.X - v0.X), e2y = xi2f(v2.Y - v0.Y);
     const float d1z = xsub(v1.z, v0.z), d2z = xsub(v2.z, v0.z);
-    const float rA = xrcp(xll2f(A2));
+    const float rA = xrcp(narrow ? xi2f((int32_t)A2) : xll2f(A2));      // (the same value: an int32 converts to the same float either way)
     t.z0 = v0.z;
     t.dzdx = xmul(xmul(xsub(xmul(d1z, e2y), xmul(d2z, e1y)), rA), 256.0f);
     t.dzdy = xmul(xmul(xsub(xmul(d2z, e1x), xmul(d1z, e2x)), rA), 256.0f);
@@ -130,7 +131,7 @@ struct VisSink {           // main pass: 64-bit key into the visibility buffer
     // Early depth test for fragments that are expensive to produce (alpha-tested): true iff the stored depth is already
     // nearer than z.  Stored depths only decrease, so such a fragment can never win (LEQUAL: equal depth still can).
     VKR_HD bool hidden(int32_t px, int32_t py, float z) const {
-        const uint32_t* hi = reinterpret_cast<const uint32_t*>(vis + (size_t)py * width + px) + 1;
+        const uint32_t* hi = reinterpret_cast<const uint32_t*>(vis + (uint32_t)(py * width + px)) + 1;     // (W * H < 2^32)
 #if defined(__CUDA_ARCH__)
         return __ldcg(hi) < f2bits(z);
 #else
@@ -139,7 +140,7 @@ struct VisSink {           // main pass: 64-bit key into the visibility buffer
     }
     VKR_HD void put(int32_t px, int32_t py, float z) const {
         const uint64_t key = ((uint64_t)f2bits(z) << 32) | lo;
-        uint64_t* p = vis + (size_t)py * width + px;
+        uint64_t* p = vis + (uint32_t)(py * width + px);
 #if defined(__CUDA_ARCH__)
         atomicMin((unsigned long long*)p, (unsigned long long)key);   // result unused -> RED.MIN.64: fire and forget, no L2 round trip
 #else
@@ -151,7 +152,7 @@ struct DepthSink {         // shadow pass: float bits, LESS_OR_EQUAL + write == 
     uint32_t* bits; int32_t width;
     VKR_HD void put(int32_t px, int32_t py, float z) const {
         const uint32_t v = f2bits(z);
-        uint32_t* p = bits + (size_t)py * width + px;
+        uint32_t* p = bits + (uint32_t)(py * width + px);
 #if defined(__CUDA_ARCH__)
         atomicMin(p, v);                                                // RED.MIN.32
 #else
@@ -172,6 +173,17 @@ struct DepthSink {         // shadow pass: float bits, LESS_OR_EQUAL + write == 
 // search), so a lane with a 1-sample triangle does not wait for its neighbour's 4x4 box; the host emulation walks them in
 // order.  Both produce the values of the plain per-triangle loop: the edge functions at sample (ix, iy) of the box are
 // e + ix*ax + iy*by exactly (32-bit, no overflow: |e| < 2^30), and the depth is depth_at() of the same integers.
+// w | ceil(2^16 / w) << 8 for the box widths 1..SMALL_MAX: k / w == (k * (that >> 8)) >> 16 for k < 256 (a table: the integer
+// division costs the set-up ~25 instructions)
+struct WdivTable {
+    uint32_t v[SMALL_MAX + 1];
+    constexpr WdivTable() : v() { for (uint32_t w = 1; w <= (uint32_t)SMALL_MAX; ++w) v[w] = w | (((65536u + w - 1u) / w) << 8); }
+};
+#if defined(__CUDACC__)
+__device__ constexpr WdivTable kWdivDev{};
+#endif
+constexpr WdivTable kWdivHost{};
+
 struct alignas(16) FragRec {
     int32_t e0, e1, e2;           // edge functions at the box's first sample, top-left bias folded in (covered iff all >= 0)
     int32_t ax0, ax1, ax2;        // their steps per pixel in x ...
@@ -201,7 +213,11 @@ VKR_HD uint32_t make_frag_rec(const SetupTri& t, FragRec& r) {
     r.by0 = by[0]; r.by1 = by[1]; r.by2 = by[2];
     const uint32_t w = (uint32_t)(t.bx1 - t.bx0 + 1), h = (uint32_t)(t.by1 - t.by0 + 1);
     r.origin = (uint32_t)t.bx0 | ((uint32_t)t.by0 << 16);
-    r.wdiv = w | (((65536u + w - 1u) / w) << 8);
+#if defined(__CUDA_ARCH__)
+    r.wdiv = kWdivDev.v[w];
+#else
+    r.wdiv = kWdivHost.v[w];
+#endif
     r.z0 = t.z0; r.dzdx = t.dzdx; r.dzdy = t.dzdy;
     // depth_at() divides (sample - vertex 0), an integer number of sub-pixels below 2^15, by 256: exact, and so is adding the
     // sample's integer offset inside the box afterwards (the sum still has at most 15 + 8 significant bits)
@@ -225,8 +241,10 @@ VKR_HD void raster_candidate(const FragRec& r, uint32_t k, const Sink& sink) {
     sink.put((int32_t)(r.origin & 0xFFFFu) + ix, (int32_t)(r.origin >> 16) + iy, z);
 }
 
-// The plain per-triangle double loop (incremental edge functions): what the candidate stage replaces.  Kept for the A/B
-// (-DVKR_RASTER_PER_LANE: every lane rasterises its own triangle and waits for the largest box of the warp).
+// The plain per-triangle double loop (incremental edge functions): every lane rasterises its own triangle and waits for the
+// largest box of the warp.  This is what the geometry kernels run.  The candidate stage below (-DVKR_RASTER_CANDIDATES: the
+// samples of all 32 boxes dealt evenly to the lanes through a prefix sum) keeps every lane busy but pays ~90 instructions
+// per round of 32 samples against ~12 per sample here, and measured slower on BASELINE config 4 (profiles/r02d_ab.md).
 template <class Sink>
 VKR_HD void raster_small_loop(const SetupTri& t, const Sink& sink) {
     FragRec r;
@@ -550,8 +568,12 @@ VKR_HD void cluster_triangle(const CachedVtx& a, const CachedVtx& b, const Cache
 // spot), 1 medium (extent < 64 px: the warp queues it as one item for large_raster_kernel's 32-bit path), 2 large (the warp
 // enumerates its 64x64 tiles and queues them), 3 small: its record is in `out.rec` and `count` candidates wait for the warp's
 // candidate stage (geometry_warp).  `out` is the lane's slot of the warp's shared memory.
+#if defined(VKR_RASTER_CANDIDATES)
 union ParkedTri { FragRec rec; LargeTri lt; };
 static_assert(sizeof(ParkedTri) == 64, "one 64-byte shared-memory slot per lane");
+#else
+struct ParkedTri { LargeTri lt; };           // only medium and large triangles are parked
+#endif
 template <class Sink>
 __device__ __forceinline__ int cluster_triangle_deferred(const CachedVtx& a, const CachedVtx& b, const CachedVtx& c, const float* __restrict__ mvp,
                                                          const float4* __restrict__ pos, uint32_t g0, uint32_t g1, uint32_t g2, uint32_t seq,
@@ -566,10 +588,10 @@ __device__ __forceinline__ int cluster_triangle_deferred(const CachedVtx& a, con
     const SnapVtx v0{a.X, a.Y, bits2f(a.zbits)}, v1{b.X, b.Y, bits2f(b.zbits)}, v2{c.X, c.Y, bits2f(c.zbits)};
     if (!setup_snapped(v0, v1, v2, rt, t)) return 0;
     const int32_t w = t.bx1 - t.bx0 + 1, h = t.by1 - t.by0 + 1;
-#if defined(VKR_RASTER_PER_LANE)
-    if (w <= SMALL_MAX && h <= SMALL_MAX && t.ext < 16384) { raster_small_loop(t, sink); return 0; }
-#else
+#if defined(VKR_RASTER_CANDIDATES)
     if (w <= SMALL_MAX && h <= SMALL_MAX && t.ext < 16384) { count = make_frag_rec(t, out.rec); return 3; }
+#else
+    if (w <= SMALL_MAX && h <= SMALL_MAX && t.ext < 16384) { raster_small_loop(t, sink); return 0; }
 #endif
     LargeTri& lt = out.lt;
 #pragma unroll
@@ -586,6 +608,7 @@ __device__ __forceinline__ int cluster_triangle_deferred(const CachedVtx& a, con
 // d-th one.  In the round that starts at candidate jb, the triangles whose first candidate falls inside the round set a bit at
 // that position (one warp-wide OR, REDUX); the owner of the candidate on lane L is then the triangle number
 // (triangles that start before the round) + (bits at positions <= L) - 1: no search.
+#if defined(VKR_RASTER_CANDIDATES)
 template <class MakeSink>
 __device__ __forceinline__ void raster_candidates_warp(const ParkedTri* slots, uint2* map, uint32_t excl, uint32_t count, uint32_t seq, uint32_t total,
                                                        int lane, const MakeSink& makeSink) {
@@ -611,6 +634,8 @@ __device__ __forceinline__ void raster_candidates_warp(const ParkedTri* slots, u
         }
     }
 }
+
+#endif
 
 // All 32 lanes rasterise one medium triangle (warp-uniform `lt`): 8-pixel strips of its bounding box dealt to the lanes,
 // 32-bit edge functions as in raster_small.

@@ -157,6 +157,25 @@ VKR_HD float4 texture2d(const ShadeBuffers& sb, int id, float u, float v, float 
                        c0.w * (1.0f - f) + c1.w * f);
 }
 
+// Host side: the uv-independent texture results of a material (DMaterial::albedoTexel / mrTexel), with fetch_texel's arithmetic.
+// `textures` are the VKR_MAX_BINDLESS slots as the device will see them, `lut` the 256-entry sRGB decode table.
+inline void material_constants(DMaterial& m, const DTexture* textures, const float* lut) {
+    m.constFlags = 0u;
+    const int ids[2] = {m.albedoID, m.metalRoughID};
+    float* dst[2] = {m.albedoTexel, m.mrTexel};
+    for (int k = 0; k < 2; ++k) {
+        const bool unbound = ids[k] < 0 || ids[k] >= VKR_MAX_BINDLESS || textures[ids[k]].data == nullptr;
+        if (unbound) { dst[k][0] = dst[k][1] = dst[k][2] = 0.0f; dst[k][3] = 1.0f; m.constFlags |= 1u << k; continue; }     // texture2d: (0,0,0,1)
+        const DTexture& t = textures[ids[k]];
+        if ((t.w | t.h) != 1u) continue;
+        const uint32_t p = t.texel0;
+        const uint32_t c[4] = {p & 255u, (p >> 8) & 255u, (p >> 16) & 255u, p >> 24};
+        for (int i = 0; i < 3; ++i) dst[k][i] = (t.flags & 1u) ? lut[c[i]] : (float)c[i] * (1.0f / 255.0f);
+        dst[k][3] = (float)c[3] * (1.0f / 255.0f);
+        m.constFlags |= 1u << k;
+    }
+}
+
 // _shadowSampler: LINEAR, CLAMP_TO_BORDER, border 1.0, no compare (src/vk_engine_init.cpp:392-394)
 VKR_HD float shadow_fetch(const float* __restrict__ sm, int S, int x, int y) {
     if ((unsigned)x >= (unsigned)S || (unsigned)y >= (unsigned)S) return 1.0f;
@@ -292,7 +311,8 @@ struct Fragment {
 // The shaders' `discard` (albedo alpha < 0.5) was already applied in the raster stage (vkr_raster.cuh
 // alpha_passes), which owns that decision: a fragment that reached the visibility buffer is shaded.
 VKR_HD bool shade_fragment(const ShadeConst& sc, const ShadeBuffers& sb, const DMaterial& m, const Fragment& fr, f3& out, bool alphaTest = false) {
-    float4 albedoTex = texture2d(sb, m.albedoID, fr.u, fr.v, fr.dudx, fr.dvdx, fr.dudy, fr.dvdy);
+    float4 albedoTex = (m.constFlags & 1u) ? make_float4(m.albedoTexel[0], m.albedoTexel[1], m.albedoTexel[2], m.albedoTexel[3])
+                                           : texture2d(sb, m.albedoID, fr.u, fr.v, fr.dudx, fr.dvdx, fr.dudy, fr.dvdy);
     if (alphaTest && albedoTex.w < 0.5f) return false;      // `discard` of a fragment that writes no depth (transparent pass)
     f3 base = f3{m.colorFactors[0], m.colorFactors[1], m.colorFactors[2]} * f3{albedoTex.x, albedoTex.y, albedoTex.z} * fr.color;
     f3 N = norm3(fr.normal);
@@ -307,7 +327,8 @@ VKR_HD bool shade_fragment(const ShadeConst& sc, const ShadeBuffers& sb, const D
     }
     f3 V = norm3(f3{sc.camPos[0], sc.camPos[1], sc.camPos[2]} - fr.posWorld);
     f3 H = norm3(V + L);
-    float4 mrTex = texture2d(sb, m.metalRoughID, fr.u, fr.v, fr.dudx, fr.dvdx, fr.dudy, fr.dvdy);
+    float4 mrTex = (m.constFlags & 2u) ? make_float4(m.mrTexel[0], m.mrTexel[1], m.mrTexel[2], m.mrTexel[3])
+                                       : texture2d(sb, m.metalRoughID, fr.u, fr.v, fr.dudx, fr.dvdx, fr.dudy, fr.dvdy);
     float metallic = m.metalRough[0] * mrTex.z;
     float roughness = m.metalRough[1] * mrTex.y;
     f3 F0 = f3{0.04f, 0.04f, 0.04f} * (1.0f - metallic) + base * metallic;
@@ -443,7 +464,12 @@ VKR_HD void fetch_fragment(const ShadeConst& sc, const ShadeBuffers& sb, uint32_
     bary_at(c, (cx - sc.halfW) * ihw, (cy - sc.halfH) * ihh, b);
     // uv derivatives (the quad neighbours' barycentrics) only for draws with a mip-mapped texture: plan_frame sets bit 2 of
     // the draw's flags, which sit in the record this function reads anyway
+#if defined(__CUDA_ARCH__)
+    // (warp-uniform, so that the compiler branches around the two evaluations instead of predicating ~80 instructions)
+    const bool derivs = __any_sync(__activemask(), (o.flags & 4u) != 0u);
+#else
     const bool derivs = (o.flags & 4u) != 0u;
+#endif
     if (derivs) {
         bary_at(c, (cx + ox - sc.halfW) * ihw, (cy - sc.halfH) * ihh, bx);
         bary_at(c, (cx - sc.halfW) * ihw, (cy + oy - sc.halfH) * ihh, by);
@@ -560,7 +586,9 @@ VKR_HD void shade_pixel(const ShadeConst& sc, const ShadeBuffers& sb, int px, in
         h[0] = f2h_bits(r); h[1] = f2h_bits(g); h[2] = f2h_bits(b); h[3] = f2h_bits(a);
 #endif
     }
-    sb.rgba8[pix] = unorm8_fast(r) | (unorm8_fast(g) << 8) | (unorm8_fast(b) << 16) | (unorm8_fast(a) << 24);
+    const uint32_t texel = unorm8_fast(r) | (unorm8_fast(g) << 8) | (unorm8_fast(b) << 16) | (unorm8_fast(a) << 24);
+    sb.rgba8[pix] = texel;
+    if (sb.rgba8Peer != nullptr) sb.rgba8Peer[pix] = texel;      // the presenting rank's image, over NVLink
     // a transient attachment: this is the next frame's clear.  Issued with the other stores, long after the key arrived — a
     // store right behind the load of the same address waits for that load (a DRAM round trip) with the warp's later loads
     // queued behind it, which made the kernel 3.6x slower (gpurun_out ab_z2)
