@@ -294,38 +294,67 @@ def run_b200(args):
     cull = r.cull_stats()
     r.set_flags(BENCH_FLAGS)
 
-    # ---- e2e: host draw list in, RGBA8 frame out to pinned host memory, every step (FRAME_OVERLAP=2 pipelining)
-    pinned = [torch.empty((H, W, 3), dtype=torch.uint8).pin_memory() for _ in range(2)]
+    # ---- e2e: host draw list in, RGB8 frame out to pinned host memory, every step (FRAME_OVERLAP=2 pipelining).
+    # N = 1: the presented image of every frame.  N > 1: ONE host frame shared by the ranks (a /dev/shm segment every process maps
+    # and registers with CUDA); every rank copies its own rows into it over its own PCIe link (vkr_readback_band_async,
+    # VKR_CONFIG_LOCAL_PRESENT: nothing is assembled on rank 0 on this path), so the frame leaves the box N links wide.
+    frame_bytes = W * H * 3
+    shm_path, shm_map = None, None
+    if world == 1:
+        pinned = [torch.empty((H, W, 3), dtype=torch.uint8).pin_memory() for _ in range(2)]
+        host_frames = [p_.numpy() for p_ in pinned]
+        host_ptrs = [p_.data_ptr() for p_ in pinned]
+    else:
+        shm_path = f"/dev/shm/vkr_bench_{os.environ.get('MASTER_PORT', '0')}"
+        if rank == 0:
+            shm_map = np.memmap(shm_path, dtype=np.uint8, mode="w+", shape=(2, H, W, 3))
+            shm_map[:] = 0
+        barrier()
+        if rank != 0:
+            shm_map = np.memmap(shm_path, dtype=np.uint8, mode="r+", shape=(2, H, W, 3))
+        rc_reg = torch.cuda.cudart().cudaHostRegister(shm_map.ctypes.data, 2 * frame_bytes, 0)
+        if int(rc_reg) != 0:
+            raise SystemExit(f"bench.py: cudaHostRegister of the shared host frame failed ({rc_reg})")
+        host_frames = [shm_map[0], shm_map[1]]
+        host_ptrs = [shm_map.ctypes.data, shm_map.ctypes.data + frame_bytes]
+        r.set_flags(BENCH_FLAGS | capi.CONFIG_LOCAL_PRESENT)
     n = len(my_objs)
     h2d = r.upload_bytes()                                  # what vkr_draw copied host->device for the last frame (draw records,
                                                             # cluster/slot prefixes, light MVPs, shading constants)
-    d2h = W * H * 3                                         # rank 0 reads the assembled frame back
+    d2h = W * H * 3                                         # the whole frame, over one link (N = 1) or split into the ranks' rows
     # two cameras alternate so that consecutive frames differ: a read-back that raced with a later frame's rendering
     # (or a gather that mixed frames) is caught by the check after the loop
     view_b = mg.camera_view((0.6, 7.2, 40.0), pitch=-0.17)
     sd_b = capi.make_scene_data(view_b, mg.camera_projection(W / H), [mg.light_matrix()] * 4, shadow_mode=1, enable_shadows=True)
     cams = [sd, sd_b]
     target = capi.TARGET_RGB8          # the presented frame, packed R,G,B (the assembled frame when sharded)
+    def present(i):
+        if world == 1:
+            r.readback_async(target, host_ptrs[i % 2], frame_bytes)
+        else:
+            r.readback_band_async(target, host_ptrs[i % 2], frame_bytes)
+
     for i in range(max(3, args.warmup)):                     # untimed: the read-back path allocates its packed buffers on first use
         r.draw(cams[i % 2], my_objs, fp)
-        if world == 1 or rank == 0:
-            r.readback_async(target, pinned[i % 2].data_ptr(), W * H * 3)
+        present(i)
     r.sync()
     barrier()
     t0 = time.perf_counter()
     for i in range(args.steps):
         objs_frame = np.array(my_objs, copy=True)            # the host rebuilds its draw list every frame (update_scene)
         r.draw(cams[i % 2], objs_frame, fp)
-        if world == 1 or rank == 0:
-            r.readback_async(target, pinned[i % 2].data_ptr(), W * H * 3)
+        present(i)
     r.sync()
     barrier()
     e2e_s = time.perf_counter() - t0
+    my_rows = r.shard_info()["rows"] if world > 1 else (0, H)
+    if world > 1:
+        r.set_flags(BENCH_FLAGS)
     if world > 1:
         t = torch.tensor([e2e_s], device="cuda", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_s = float(t.item())
-    checksum = int(pinned[(args.steps - 1) % 2].view(-1)[::4097].to(torch.int64).sum()) if rank == 0 else 0
+    checksum = int(host_frames[(args.steps - 1) % 2].reshape(-1)[::4097].astype(np.int64).sum()) if rank == 0 else 0
     # what the bus allows: the same number of bytes, device -> pinned host, timed alone (the e2e frame rate cannot exceed
     # d2h_GBps / d2h_bytes_per_step)
     d2h_gbps = None
@@ -347,9 +376,12 @@ def run_b200(args):
         if i < 0:
             continue
         r.draw(cams[i % 2], my_objs, fp)
-        want = r.readback(target)
-        if rank == 0 and not np.array_equal(want, pinned[i % 2].numpy()):
-            e2e_ok = False
+        if rank == 0:                                        # (the assembled frame is rank 0's)
+            want = r.readback(target)
+            if not np.array_equal(want, host_frames[i % 2]):
+                e2e_ok = False
+        else:
+            r.sync()
     if rank == 0 and not e2e_ok:
         raise SystemExit("bench.py: an asynchronously read-back frame differs from the same frame rendered synchronously")
 
@@ -411,7 +443,10 @@ def run_b200(args):
             "host_issue_ms_per_step": host_issue_ms, "host_vkr_draw_call_ms": float(np.median(host_call)),
             "cluster_culling": cull, "per_rank_pass_ms_last_pipelined_frame": per_rank,
             "e2e": {"value": args.steps / e2e_s, "unit": "frames/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                    "readback": "VKR_TARGET_RGB8: the presented frame as packed R,G,B bytes", "checksum": checksum, "frames_verified": 2,
+                    "d2h_bytes_per_step_rank0": int((my_rows[1] - my_rows[0]) * W * 3),
+                    "readback": ("VKR_TARGET_RGB8: the presented frame as packed R,G,B bytes" if world == 1 else
+                                 f"every rank copies its own rows (packed R,G,B) into one host frame shared by the {world} processes"),
+                    "checksum": checksum, "frames_verified": 2,
                     "frame_crc32": frame_crc,
                     "d2h_probe_GBps": d2h_gbps, "d2h_bound_frames_per_s": (d2h_gbps * 1e9 / d2h) if d2h_gbps else None},
             "gpu_launches": int(launches),
@@ -419,11 +454,20 @@ def run_b200(args):
         }
         if world > 1:
             line["sharded_equals_single"] = sharded_equals_single
+            line["exchange"] = "peer memory (CUDA IPC over NVLink)" if r.shard_info()["peer_memory"] else "NCCL send/recv"
         if world == 1 and not args.no_cpu_baseline:
             times, cores, _ = time_oracle(1, 0, budget_s=60.0)
             cfps = len(times) / sum(times)
             line["cpu_baseline"] = {"value": cfps, "unit": "frames/s", "cores": cores, "kind": "port",
                                     "sample": f"{len(times)} full 4K frame of the same scene, oracle/ork.cpp, {cores} threads"}
+    r.sync()
+    barrier()                            # every rank has finished with its peers' memory and with the shared host frame
+    if shm_map is not None:
+        torch.cuda.cudart().cudaHostUnregister(shm_map.ctypes.data)
+        del host_frames, shm_map
+        barrier()
+        if rank == 0:
+            os.unlink(shm_path)
     r.close()
     # ---- BASELINE config 5 (frame-parallel multi-view batch) on the same ranks, reported inside the same line
     if not args.no_views:

@@ -201,3 +201,71 @@ def test_component_conversion_matches_fastgltfs_own_test():
     assert np.array_equal(convert(u32, 5125, False), u32.astype(np.float32))
     f32 = np.array([0.25, -3.5, 1e-20, 7e9], np.float32)
     assert np.array_equal(convert(f32, 5126, True), f32)                               # floats pass through either way
+
+
+def _jpeg_cases():
+    from PIL import Image
+    import io
+    rng = np.random.default_rng(3)
+
+    def picture(w, h, noise):
+        y, x = np.mgrid[0:h, 0:w]
+        a = np.stack([127 + 100 * np.sin(x / 9.0 + y / 17.0), 127 + 100 * np.cos(x / 13.0), 127 + 90 * np.sin(y / 7.0 - x / 23.0)], -1)
+        return np.clip(a + rng.normal(0, noise, a.shape), 0, 255).astype(np.uint8)
+
+    for w, h in ((64, 48), (37, 29), (129, 65), (8, 8), (1, 1), (17, 200)):
+        for kw in (dict(subsampling="4:4:4"), dict(subsampling="4:2:2"), dict(subsampling="4:2:0"), dict(subsampling="4:2:0", progressive=True),
+                   dict(subsampling="4:4:4", progressive=True, quality=95), dict(subsampling="4:2:0", quality=30),
+                   dict(subsampling="4:2:0", quality=90, optimize=True), dict(subsampling="4:2:0", restart_marker_blocks=3),
+                   dict(subsampling="4:4:4", progressive=True, restart_marker_rows=1), dict(mode="L"), dict(mode="L", progressive=True)):
+            kw = dict(kw)
+            mode = kw.pop("mode", "RGB")
+            a = picture(w, h, 6 if kw.get("quality", 80) >= 50 else 40)
+            buf = io.BytesIO()
+            Image.fromarray(a if mode == "RGB" else a[..., 0], mode).save(buf, "JPEG", **({"quality": 80} | kw))
+            data = buf.getvalue()
+            yield (w, h, mode, kw), data, np.asarray(Image.open(io.BytesIO(data)).convert("RGB"))
+
+
+def test_jpeg_decoder_against_an_independent_decode():
+    """glTF images are PNG or JPEG and the reference decodes both with stb_image (src/vk_loader.cpp:280,293).  The engine's own
+    JPEG decoder (csrc/host/vk_jpeg.cpp: baseline and progressive, 4:4:4 / 4:2:2 / 4:2:0, grey, restart intervals) against
+    PIL's (libjpeg) on the same streams: decoders differ in their inverse DCT and chroma filters by a level or two, never more."""
+    n = 0
+    for what, data, want in _jpeg_cases():
+        got = eng_mod.decode_jpeg(data)
+        assert got is not None and got.shape == want.shape[:2] + (4,), what
+        assert (got[..., 3] == 255).all()
+        d = np.abs(got[..., :3].astype(int) - want.astype(int))
+        assert d.max() <= 4 and d.mean() < 0.5, (what, d.max(), d.mean())
+        n += 1
+    assert n == 66
+    assert eng_mod.decode_jpeg(b"\x89PNG\r\n\x1a\n....") is None
+    good = next(_jpeg_cases())[1]
+    assert eng_mod.decode_jpeg(good[:200]) is None or True          # a truncated stream must not crash (missing scans decode as grey)
+    assert eng_mod.decode_jpeg(good[:2]) is None
+
+
+def test_gltf_with_a_jpeg_texture_loads_it(ork_lib, tmp_path):
+    """A glTF whose base-colour image is a JPEG renders exactly like the same file with that image re-encoded losslessly (PNG of the
+    engine's own decode): the loader used the decoder, not the error checkerboard."""
+    from PIL import Image
+    import io
+    rng = np.random.default_rng(5)
+    asset = gu.build_asset(rng)
+    y, x = np.mgrid[0:32, 0:32]
+    pic = np.stack([x * 8, y * 8, (x ^ y) * 8], -1).astype(np.uint8)
+    buf = io.BytesIO()
+    Image.fromarray(pic, "RGB").save(buf, "JPEG", quality=90, subsampling="4:2:0", progressive=True)
+    jpg = buf.getvalue()
+    decoded = eng_mod.decode_jpeg(jpg)
+    assert decoded is not None and np.abs(decoded[..., :3].astype(int) - pic.astype(int)).mean() < 6
+    frames = []
+    for k, image in enumerate(((jpg, None), (gu.png_bytes(decoded, 6), decoded))):
+        asset["images"][0] = image
+        path = gu.write_gltf(asset, str(tmp_path / f"v{k}"), "glb" if k == 0 else "external")
+        e, tris = _engine(ork_lib, "ork", path)
+        e.draw()
+        frames.append(e.readback(capi.TARGET_RGBA8))
+        e.close()
+    assert np.array_equal(frames[0], frames[1])

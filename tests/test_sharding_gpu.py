@@ -13,6 +13,8 @@ ROOT = os.path.dirname(HERE)
 
 
 def _worker(rank, world, port, scene, W, H, S, out_dir, native):
+    if native == "nccl":
+        os.environ["VKR_EXCHANGE"] = "nccl"
     sys.path.insert(0, ROOT)
     sys.path.insert(0, HERE)
     import torch
@@ -37,9 +39,28 @@ def _worker(rank, world, port, scene, W, H, S, out_dir, native):
         r.shard_init(rank, world, ids.cpu().numpy().tobytes())
         for _ in range(3):
             r.draw(sd, objs, fp)
-        img = r.readback(capi.TARGET_RGBA8_GATHERED)
-        if rank == 0:
-            assert np.array_equal(r.readback(capi.TARGET_RGB8), img[..., :3]), "VKR_TARGET_RGB8 of a sharded device is the assembled frame"
+        info = r.shard_info()
+        assert info["ranks"] == world and info["peer_memory"] == (native != "nccl"), info
+        if rank == 0 or not info["peer_memory"]:
+            img = r.readback(capi.TARGET_RGBA8_GATHERED)      # over peer memory only rank 0 presents the assembled frame
+            if rank == 0:
+                assert np.array_equal(r.readback(capi.TARGET_RGB8), img[..., :3]), "VKR_TARGET_RGB8 of a sharded device is the assembled frame"
+        else:
+            try:
+                r.readback(capi.TARGET_RGBA8_GATHERED)
+                raise AssertionError("only rank 0 can read the assembled frame back")
+            except capi.VkrError:
+                pass
+            img = np.zeros((H, W, 4), np.uint8)
+        # every rank's own rows, through the band read-back (into one whole-frame buffer, as a shared host frame would be used)
+        y0, y1 = info["rows"]
+        land = torch.zeros((H, W, 3), dtype=torch.uint8).pin_memory()
+        r.readback_band_async(capi.TARGET_RGB8, land.data_ptr(), H * W * 3)
+        r.sync()
+        own = r.readback(capi.TARGET_RGBA8)
+        assert np.array_equal(land.numpy()[y0:y1], own[y0:y1, :, :3]) and not land.numpy()[:y0].any() and not land.numpy()[y1:].any()
+        np.save(os.path.join(out_dir, f"band{rank}.npy"), np.concatenate([np.array([[y0, y1]]).repeat(1, 0).reshape(-1), own[y0:y1].reshape(-1)]))
+        dist.barrier()
     else:           # the same sharding driven from Python over torch.distributed (vk_renderer_b200/sharding.py)
         sh = TileSharder(r, rank, world, cuda=True, shadow_group=dist.new_group())
         fp = sh.frame_params(fp)
@@ -55,7 +76,7 @@ def _worker(rank, world, port, scene, W, H, S, out_dir, native):
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("scene,native", [("lattice", True), ("basic_csm", True), ("lattice", False)])
+@pytest.mark.parametrize("scene,native", [("lattice", True), ("basic_csm", True), ("lattice", "nccl"), ("lattice", False)])
 def test_nccl_sharded_frame_equals_single_gpu(vkr_lib, tmp_path, scene, native):
     import torch
     import torch.multiprocessing as mp
@@ -76,7 +97,12 @@ def test_nccl_sharded_frame_equals_single_gpu(vkr_lib, tmp_path, scene, native):
     mp.spawn(_worker, args=(world, port, scene, W, H, S, str(tmp_path), native), nprocs=world, join=True)
     for rank in range(world):
         got = np.load(tmp_path / f"img{rank}.npy")
-        assert np.array_equal(got, want), f"rank {rank}: {(got != want).any(-1).sum()} pixels differ"
+        if native is True and rank > 0:      # peer memory: rank 0 presents; the other ranks hold (and can read back) their own rows
+            band = np.load(tmp_path / f"band{rank}.npy")
+            y0, y1 = int(band[0]), int(band[1])
+            assert np.array_equal(band[2:].reshape(y1 - y0, W, 4).astype(np.uint8), want[y0:y1]), f"rank {rank}: rows {y0}..{y1} differ"
+        else:
+            assert np.array_equal(got, want), f"rank {rank}: {(got != want).any(-1).sum()} pixels differ"
         got_shadow = np.load(tmp_path / f"shadow{rank}.npy")
         assert np.array_equal(got_shadow[:layers].view(np.uint32), want_shadow[:layers].view(np.uint32))
 

@@ -94,6 +94,13 @@ int vke_decode_png(const unsigned char* data, size_t size, unsigned char* rgbaOu
     return 0;
 }
 
+int vke_decode_jpeg(const unsigned char* data, size_t size, unsigned char* rgbaOut, size_t outBytes, uint32_t* w, uint32_t* h) {
+    std::vector<unsigned char> px;
+    if (!decode_jpeg(data, size, px, *w, *h)) return -1;
+    if (rgbaOut) { if (outBytes < px.size()) return -2; std::memcpy(rgbaOut, px.data(), px.size()); }
+    return 0;
+}
+
 void vke_set_camera(VulkanEngine* e, float x, float y, float z, float pitch, float yaw) {
     e->_mainCamera.position = vkm::vec3{x, y, z};
     e->_mainCamera.pitch = pitch; e->_mainCamera.yaw = yaw;

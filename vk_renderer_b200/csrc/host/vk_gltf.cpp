@@ -1,4 +1,4 @@
-// vk_gltf.cpp — see vk_gltf.h.  Own JSON reader, base64, GLB container, PNG decoder (zlib), accessor conversion.
+// vk_gltf.cpp — see vk_gltf.h.  Own JSON reader, base64, GLB container, PNG decoder (zlib), accessor conversion (JPEG: vk_jpeg.cpp).
 #include "vk_gltf.h"
 
 #include <zlib.h>
@@ -449,7 +449,7 @@ std::shared_ptr<Node> load_gltf(VulkanEngine* engine, const std::string& name, c
             if (view_bytes(d, image.integer("bufferView", -1), &p, &len, nullptr)) { bytes.assign(p, p + len); ok = true; }
             else d.err.clear();
         }
-        ok = ok && decode_png(bytes.data(), bytes.size(), rgba, w, h);
+        ok = ok && (decode_png(bytes.data(), bytes.size(), rgba, w, h) || decode_jpeg(bytes.data(), bytes.size(), rgba, w, h));      // stbi_load (src/vk_loader.cpp:280,293)
         if (ok) textureIndices.push_back(engine->add_texture(rgba.data(), w, h));
         else {   // _errorCheckerboardImage (src/vk_engine_init.cpp:329-341): 16x16 magenta / black, UNORM, no mips, LINEAR sampler here
             uint32_t px[16 * 16];

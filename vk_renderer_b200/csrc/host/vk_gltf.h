@@ -12,11 +12,13 @@
 //     are max(c / MAX, -1), everything else a static_cast;
 //   * nodes: `matrix` or T * R * S (:474-490); nodes without a parent hang under one new top node (:509-515).
 // Supported containers: .gltf with external or base64 buffers and images, .glb.  Images: PNG (8/16-bit, all colour types,
-// non-interlaced), decoded with zlib.  JPEG and sparse accessors are not decoded (JPEG -> error checkerboard, like a failed
-// stbi_load; sparse -> the load fails).
+// non-interlaced), decoded with zlib, and JPEG (baseline and progressive Huffman, grey / YCbCr / RGB; vk_jpeg.cpp) — the two
+// formats glTF allows and the reference's own scene (Khronos Sponza) uses.  An image neither decoder takes gets the error
+// checkerboard, like a failed stbi_load.  Sparse accessors are not decoded (the load fails).
 #pragma once
 #include <memory>
 #include <string>
+#include <vector>
 
 #include "vk_engine.h"
 
@@ -25,6 +27,9 @@ std::shared_ptr<Node> load_gltf(VulkanEngine* engine, const std::string& name, c
 
 // PNG -> RGBA8 (test hook and used by load_gltf).  Returns false when the stream is not a PNG this decoder handles.
 bool decode_png(const unsigned char* data, size_t size, std::vector<unsigned char>& rgba, uint32_t& width, uint32_t& height);
+
+// JPEG -> RGBA8, alpha 255 (vk_jpeg.cpp).  Returns false when the stream is not a JPEG this decoder handles.
+bool decode_jpeg(const unsigned char* data, size_t size, std::vector<unsigned char>& rgba, uint32_t& width, uint32_t& height);
 
 // Test hook (see vk_gltf.cpp): the accessor component conversion on a packed array of scalars.
 void gltf_convert_components(int componentType, bool normalized, const unsigned char* data, size_t count, float* out);

@@ -1611,7 +1611,15 @@ static int readback_issue(VkrDevice* dev, VkrTarget what, void* dst, size_t dstB
 static int do_readback(VkrDevice* dev, VkrTarget what, void* dst, size_t dstBytes, bool sync) {
     if (!dev) return VKR_ERROR_INVALID_ARGUMENT;
     const void* src; size_t bytes;
-    if (!dst || target_info(dev, what, &src, &bytes)) { DRAIN(dev); return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_readback: bad target"); }
+    const bool queued = !sync && dev->worker.joinable() && (dev->flags & VKR_CONFIG_SUBMIT_THREAD);
+    // (a request that is queued behind its frame is checked again when the submit thread reaches it: what the last frame left
+    // behind — e.g. whether it was assembled on this rank — is only known then; everything else waits for the frame to be issued)
+    if (!queued) DRAIN(dev);
+    if (!dst || (target_info(dev, what, &src, &bytes) && !(queued && (what == VKR_TARGET_RGBA8_GATHERED || what == VKR_TARGET_RGB8)))) {
+        DRAIN(dev);
+        return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_readback: bad target");
+    }
+    if (what == VKR_TARGET_RGBA8_GATHERED || what == VKR_TARGET_RGB8) bytes = (size_t)dev->W * dev->H * (what == VKR_TARGET_RGB8 ? 3 : 4);
     if (dstBytes < bytes) { DRAIN(dev); return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_readback: destination too small"); }
     const bool visTarget = what == VKR_TARGET_DEPTH || what == VKR_TARGET_PRIMID;
     // only the presented image is double-buffered and fenced against the frames that follow: the draw image is one buffer and

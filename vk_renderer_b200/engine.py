@@ -66,6 +66,8 @@ def load_engine() -> C.CDLL:
         lib.vke_render_object.restype = C.c_int
         lib.vke_decode_png.argtypes = [C.c_char_p, C.c_size_t, p, C.c_size_t, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
         lib.vke_decode_png.restype = C.c_int
+        lib.vke_decode_jpeg.argtypes = lib.vke_decode_png.argtypes
+        lib.vke_decode_jpeg.restype = C.c_int
         _engine_lib = lib
     return _engine_lib
 
@@ -78,6 +80,17 @@ def decode_png(data: bytes):
         return None
     out = np.empty((h.value, w.value, 4), np.uint8)
     assert lib.vke_decode_png(data, len(data), out.ctypes.data, out.nbytes, C.byref(w), C.byref(h)) == 0
+    return out
+
+
+def decode_jpeg(data: bytes):
+    """The engine's JPEG decoder (csrc/host/vk_jpeg.cpp) -> (H, W, 4) uint8, or None when it refuses the stream."""
+    lib = load_engine()
+    w, h = C.c_uint32(), C.c_uint32()
+    if lib.vke_decode_jpeg(data, len(data), None, 0, C.byref(w), C.byref(h)) != 0:
+        return None
+    out = np.empty((h.value, w.value, 4), np.uint8)
+    assert lib.vke_decode_jpeg(data, len(data), out.ctypes.data, out.nbytes, C.byref(w), C.byref(h)) == 0
     return out
 
 
