@@ -68,7 +68,7 @@ bool EmuClusters::get(uint32_t mesh, uint32_t firstIndex, uint32_t indexCount, C
     ClusterData* cd = new ClusterData();
     build_clusters(d->meshes[mesh].idx + firstIndex, indexCount / 3, d->meshes[mesh].nv, d->meshes[mesh].pos, *cd);
     store.push_back(cd);
-    out = ClusterRange{cd->verts.data(), cd->tris.data(), cd->orig.data(), cd->info.data(), cd->bounds.data(), cd->blob.data(), 0u, {0, 0, 0}, 0};
+    out = ClusterRange{cd->verts.data(), cd->tris.data(), cd->orig.data(), cd->info.data(), cd->bounds.data(), cd->blob.data(), cd->cone.data(), 0u, {0, 0, 0}, 0};
     range_sphere(*cd, out);
     cache.push_back({{mesh, firstIndex, indexCount}, out});
     return true;
@@ -263,7 +263,10 @@ static void run_pass(EmuDevice* d, const FramePlan& plan, RasterTarget rt, const
         const float* mvp = mvps + (size_t)ch.obj * stride;
         const DObject& ob = plan.objects[ch.obj];
         const uint32_t lc = ci - plan.clusterBase[ch.obj];
-        const CullRec cr = make_cull_rec(mvp, ob.clBounds[2 * lc], ob.clBounds[2 * lc + 1], rt);
+        const ClusterCone cone{ob.clCone[3 * lc], ob.clCone[3 * lc + 1], ob.clCone[3 * lc + 2]};
+        float eye[8];
+        eye_point(mvp, eye);
+        const CullRec cr = make_cull_rec(mvp, ob.clBounds[2 * lc], ob.clBounds[2 * lc + 1], rt, &cone, eye);
         if (!cluster_survives<PASS == 1>(cr, rt)) { d->culled[SHADOW ? 1 : 0]++; continue; }
         const uint32_t nVerts = ch.counts & 0xFFFFu, nTris = ch.counts >> 16;
         const uint32_t* clVerts = ch.clVerts;
@@ -411,3 +414,45 @@ void emu_culled(EmuDevice* d, uint32_t out[2]) { out[0] = d->culled[0]; out[1] =
 const char* emu_last_error(EmuDevice* d) { return d->err.c_str(); }
 
 }  // extern "C"
+
+// Test hook for the facing cull of whole clusters (vkr_raster.cuh cone_culls): clusters are built from the index / position
+// arrays, every cluster is run through make_cull_rec with its cone, and for every cluster the cone dropped, each of its
+// triangles goes through the kernels' own vertex and set-up path WITHOUT the cone.  Returns the number of clusters the cone
+// dropped; *violations counts triangles of such clusters that the per-triangle path would have kept (must be 0).
+extern "C" int emu_cone_check(const uint32_t* idx, uint32_t triCount, uint32_t nv, const float* pos4, const float* mvp, int width, int height,
+                              int cullFront, uint32_t* violations, uint32_t* clusters) {
+    ClusterData cd;
+    build_clusters(idx, triCount, nv, reinterpret_cast<const float4*>(pos4), cd);
+    RasterTarget rt{};
+    rt.width = width; rt.height = height; rt.sx0 = 0; rt.sy0 = 0; rt.sx1 = width; rt.sy1 = height;
+    rt.halfW = 0.5f * width; rt.halfH = 0.5f * height; rt.halfW256 = 128.0f * width; rt.halfH256 = 128.0f * height;
+    rt.cullFront = cullFront;
+    float eye[8];
+    eye_point(mvp, eye);
+    int dropped = 0;
+    *violations = 0;
+    *clusters = (uint32_t)cd.info.size();
+    const float4* P = reinterpret_cast<const float4*>(pos4);
+    for (size_t c = 0; c < cd.info.size(); ++c) {
+        const ClusterCone cone{cd.cone[3 * c], cd.cone[3 * c + 1], cd.cone[3 * c + 2]};
+        const CullRec with = make_cull_rec(mvp, cd.bounds[2 * c], cd.bounds[2 * c + 1], rt, &cone, eye);
+        const CullRec without = make_cull_rec(mvp, cd.bounds[2 * c], cd.bounds[2 * c + 1], rt);
+        if (!(with.verdict == CLUSTER_CULLED && without.verdict != CLUSTER_CULLED)) continue;
+        ++dropped;
+        const uint32_t off = cd.info[c].x, nt = cd.info[c].y >> 16;
+        for (uint32_t t = 0; t < nt; ++t) {
+            const uint32_t pk = cd.tris[c * CL_TRIS + t];
+            const uint32_t g[3] = {cd.verts[off + (pk & 127u)], cd.verts[off + ((pk >> 7) & 127u)], cd.verts[off + ((pk >> 14) & 127u)]};
+            CachedVtx v[3];
+            for (int k = 0; k < 3; ++k) v[k] = cluster_vertex(mvp, P[g[k]], rt);
+            if (v[0].flag | v[1].flag | v[2].flag) { ++*violations; continue; }      // (allFront clusters have no clipped vertices near w = 0; count any)
+            // the per-triangle facing decision alone (setup_snapped's first lines), without the scissor / sample tests
+            const int64_t d1x = v[1].X - v[0].X, d1y = v[1].Y - v[0].Y, d2x = v[2].X - v[0].X, d2y = v[2].Y - v[0].Y;
+            const int64_t A2 = d1x * d2y - d2x * d1y;
+            if (A2 == 0) continue;
+            const bool front = A2 < 0;
+            if (!(cullFront ? front : !front)) ++*violations;
+        }
+    }
+    return dropped;
+}

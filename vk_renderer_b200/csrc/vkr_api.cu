@@ -198,7 +198,23 @@ __global__ void mip_blit_kernel(const uchar4* __restrict__ src, int sw, int sh, 
 // frustum planes, pixel rectangle, nearest depth — CullRec); one more list in submission order with the main pass's matrix
 // (the transparent pass); the 48-byte cluster records the cut-out kernel walks; and the (draw, first triangle) pairs the
 // shading pass looks up through seq >> 8.
-__global__ void expand_chunks_kernel(const DObject* __restrict__ objects, const uint32_t* __restrict__ clusterBase,
+__device__ __forceinline__ CullRec cull_rec_8lanes(const float* __restrict__ mvp, float4 bmin, float4 bmax, const RasterTarget& rt, int corner,
+                                                   const ClusterCone& cone, const float* eye) {
+    // make_cull_rec with the eight corners on eight neighbouring lanes: one corner each, merged by three butterfly steps
+    CornerAcc a = corner_eval(mvp, bmin, bmax, corner);
+#pragma unroll
+    for (int d = 1; d < 8; d <<= 1) {
+        CornerAcc o;
+        o.xmin = __shfl_xor_sync(0xFFFFFFFFu, a.xmin, d); o.xmax = __shfl_xor_sync(0xFFFFFFFFu, a.xmax, d);
+        o.ymin = __shfl_xor_sync(0xFFFFFFFFu, a.ymin, d); o.ymax = __shfl_xor_sync(0xFFFFFFFFu, a.ymax, d);
+        o.zmin = __shfl_xor_sync(0xFFFFFFFFu, a.zmin, d); o.zmax = __shfl_xor_sync(0xFFFFFFFFu, a.zmax, d);
+        o.outAll = __shfl_xor_sync(0xFFFFFFFFu, a.outAll, d); o.allFront = __shfl_xor_sync(0xFFFFFFFFu, a.allFront, d);
+        o.wmax = __shfl_xor_sync(0xFFFFFFFFu, a.wmax, d); o.wmin = __shfl_xor_sync(0xFFFFFFFFu, a.wmin, d); o.mgx = __shfl_xor_sync(0xFFFFFFFFu, a.mgx, d); o.mgy = __shfl_xor_sync(0xFFFFFFFFu, a.mgy, d);
+        a = corner_merge(a, o);
+    }
+    return cluster_verdict(a, &cone, eye, rt);
+}
+__global__ void __launch_bounds__(128) expand_chunks_kernel(const DObject* __restrict__ objects, const uint32_t* __restrict__ clusterBase,
                                      const uint32_t* __restrict__ seqSlotBase, const uint32_t* __restrict__ slotBase,
                                      const float* __restrict__ shadowMvp, uint32_t nobj, uint32_t passes, uint32_t listStride,
                                      const __grid_constant__ RasterTarget rtMain, const __grid_constant__ RasterTarget rtShadow,
@@ -207,16 +223,26 @@ __global__ void expand_chunks_kernel(const DObject* __restrict__ objects, const 
     const uint32_t base = clusterBase[obj], n = clusterBase[obj + 1] - base;
     const uint32_t sbase = seqSlotBase[obj], ns = seqSlotBase[obj + 1] - sbase;
     const DObject& o = objects[obj];
-    for (uint32_t c = threadIdx.x; c < n; c += blockDim.x) {
-        chunks[base + c] = make_chunk(o, obj, c, sbase);
+    // the eye points of this draw's matrices (facing cull of whole clusters), once per CTA: [0] main pass, [1..] shadow layers
+    __shared__ float s_eye[1 + VKR_NUM_CASCADES][8];
+    if (threadIdx.x < passes) eye_point(threadIdx.x == 0 ? o.mvp : shadowMvp + ((size_t)(threadIdx.x - 1) * nobj + obj) * 16, s_eye[threadIdx.x]);
+    __syncthreads();
+    const int corner = threadIdx.x & 7;
+    // eight lanes per cluster (one box corner each), 16 clusters per sweep of the CTA
+    for (uint32_t c0 = 0; c0 < n; c0 += blockDim.x >> 3) {
+        const uint32_t cc = c0 + (threadIdx.x >> 3);
+        const bool valid = cc < n, writer = valid && corner == 0;
+        const uint32_t c = valid ? cc : n - 1u;                      // (idle groups shadow the last cluster: the shuffles need every lane)
+        if (writer) chunks[base + c] = make_chunk(o, obj, c, sbase);
         const float4 bmin = o.clBounds[2 * c], bmax = o.clBounds[2 * c + 1];
-        const CullRec mainRec = make_cull_rec(o.mvp, bmin, bmax, rtMain);
-        work[(size_t)passes * listStride + base + c] = make_work_item(o, obj, c, sbase, mainRec);      // submission order
+        const ClusterCone cone{o.clCone[3 * c], o.clCone[3 * c + 1], o.clCone[3 * c + 2]};
+        const CullRec mainRec = cull_rec_8lanes(o.mvp, bmin, bmax, rtMain, corner, cone, s_eye[0]);
+        if (writer) work[(size_t)passes * listStride + base + c] = make_work_item(o, obj, c, sbase, mainRec);      // submission order
         for (uint32_t p = 0; p < passes; ++p) {
             const uint32_t sb = slotBase[(size_t)p * nobj + obj];
-            if (sb == 0xFFFFFFFFu) continue;
-            work[(size_t)p * listStride + sb + c] =
-                make_work_item(o, obj, c, sbase, p == 0 ? mainRec : make_cull_rec(shadowMvp + ((size_t)(p - 1) * nobj + obj) * 16, bmin, bmax, rtShadow));
+            if (sb == 0xFFFFFFFFu) continue;                         // (the same for the whole CTA)
+            const CullRec rec = p == 0 ? mainRec : cull_rec_8lanes(shadowMvp + ((size_t)(p - 1) * nobj + obj) * 16, bmin, bmax, rtShadow, corner, cone, s_eye[p]);
+            if (writer) work[(size_t)p * listStride + sb + c] = make_work_item(o, obj, c, sbase, rec);
         }
     }
     for (uint32_t k = threadIdx.x; k < ns; k += blockDim.x) chunkObj[sbase + k] = make_uint2(obj, k * SEQ_SLOT);
@@ -476,15 +502,14 @@ __global__ void __launch_bounds__(256) large_raster_kernel(const __grid_constant
     const uint32_t nItems = min(q.counters[1], q.itemCap), nTris = min(q.counters[0], q.triCap);
     const uint32_t warpsPerGrid = (gridDim.x * blockDim.x) >> 5;
     const int lane = threadIdx.x & 31;
-    // items differ in cost by orders of magnitude (an alpha-tested tile vs. an opaque sliver): warps take the next item
-    // from a shared cursor instead of a fixed stride
-    (void)warpsPerGrid;
-    for (;;) {
-        uint32_t i = 0;
-        if (lane == 0) i = atomicAdd(&q.counters[4], 1u);
+    // items differ in cost by orders of magnitude (an alpha-tested tile vs. an opaque sliver): a warp's first item is its own
+    // number, the following ones come from a shared cursor (no atomic at all when the queue is shorter than the grid — on a
+    // frame of small triangles it is empty, and 4736 warps hitting one address cost more than the kernel's work)
+    for (uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < nItems;) {
+        const uint32_t cur = i;
+        if (lane == 0) i = warpsPerGrid + atomicAdd(&q.counters[4], 1u);
         i = __shfl_sync(0xFFFFFFFFu, i, 0);
-        if (i >= nItems) break;
-        const LargeItem it = q.items[i];
+        const LargeItem it = q.items[cur];
         if (it.tri >= nTris) continue;                   // skip marker of an overflowed frame (the host grows the queues and redraws)
         const LargeTri lt = q.tris[it.tri];
         const bool whole = it.tx == ITEM_WHOLE;          // medium triangle: its whole bounding box, 32-bit edge functions
@@ -518,13 +543,11 @@ __global__ void __launch_bounds__(256) large_transparent_kernel(const __grid_con
     const uint32_t nItems = min(q.counters[1], q.itemCap), nTris = min(q.counters[0], q.triCap);
     const uint32_t warpsPerGrid = (gridDim.x * blockDim.x) >> 5;
     const int lane = threadIdx.x & 31;
-    (void)warpsPerGrid;
-    for (;;) {
-        uint32_t i = 0;
-        if (lane == 0) i = atomicAdd(&q.counters[4], 1u);
+    for (uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < nItems;) {
+        const uint32_t cur = i;
+        if (lane == 0) i = warpsPerGrid + atomicAdd(&q.counters[4], 1u);
         i = __shfl_sync(0xFFFFFFFFu, i, 0);
-        if (i >= nItems) break;
-        const LargeItem it = q.items[i];
+        const LargeItem it = q.items[cur];
         if (it.tri >= nTris) continue;
         const LargeTri lt = q.tris[it.tri];
         BlendSink sink{&sc, &sb, lt.seq};
@@ -560,6 +583,13 @@ __global__ void __launch_bounds__(128, VKR_SHADE_MIN_CTAS) shade_kernel(const __
     do {                                                                              \
         cudaError_t e_ = (call);                                                      \
         if (e_ != cudaSuccess) { return dev->fail(VKR_ERROR_CUDA, #call, e_); }       \
+    } while (0)
+
+// after a kernel launch: a launch that the driver refused is reported with the kernel's name, on the thread that issued it
+#define LAUNCHED(name)                                                                \
+    do {                                                                              \
+        cudaError_t e_ = cudaGetLastError();                                          \
+        if (e_ != cudaSuccess) { return dev->fail(VKR_ERROR_CUDA, "launch of " name, e_); } \
     } while (0)
 
 struct ImageRec {
@@ -713,10 +743,11 @@ struct DeviceClusterProvider : ClusterProvider {
         { const int arc = drain(dev); if (arc != VKR_SUCCESS) dev->asyncRc = arc; }     // building touches state the submit thread uses
         ClusterData cd;
         build_clusters(dev->meshIndexHost[mesh].data() + firstIndex, indexCount / 3, dev->meshes[mesh].nv, dev->meshPosHost[mesh].data(), cd);
-        uint32_t *dv = nullptr, *dt = nullptr, *dorig = nullptr; uint2* di = nullptr; float4* db = nullptr; uint4* dblob = nullptr;
+        uint32_t *dv = nullptr, *dt = nullptr, *dorig = nullptr; uint2* di = nullptr; float4* db = nullptr; uint4* dblob = nullptr; float4* dcone = nullptr;
         if (dev_alloc(dev, (void**)&dv, cd.verts.size() * 4) || dev_alloc(dev, (void**)&dt, cd.tris.size() * 4) ||
             dev_alloc(dev, (void**)&dorig, cd.orig.size() * 4) || dev_alloc(dev, (void**)&di, cd.info.size() * sizeof(uint2)) ||
-            dev_alloc(dev, (void**)&db, cd.bounds.size() * sizeof(float4)) || dev_alloc(dev, (void**)&dblob, cd.blob.size() * sizeof(uint4)))
+            dev_alloc(dev, (void**)&db, cd.bounds.size() * sizeof(float4)) || dev_alloc(dev, (void**)&dblob, cd.blob.size() * sizeof(uint4)) ||
+            dev_alloc(dev, (void**)&dcone, cd.cone.size() * sizeof(float4)))
             return false;
         bool ok = cudaMemcpyAsync(dv, cd.verts.data(), cd.verts.size() * 4, cudaMemcpyHostToDevice, dev->stream) == cudaSuccess &&
                   cudaMemcpyAsync(dt, cd.tris.data(), cd.tris.size() * 4, cudaMemcpyHostToDevice, dev->stream) == cudaSuccess &&
@@ -724,9 +755,10 @@ struct DeviceClusterProvider : ClusterProvider {
                   cudaMemcpyAsync(di, cd.info.data(), cd.info.size() * sizeof(uint2), cudaMemcpyHostToDevice, dev->stream) == cudaSuccess &&
                   cudaMemcpyAsync(db, cd.bounds.data(), cd.bounds.size() * sizeof(float4), cudaMemcpyHostToDevice, dev->stream) == cudaSuccess &&
                   cudaMemcpyAsync(dblob, cd.blob.data(), cd.blob.size() * sizeof(uint4), cudaMemcpyHostToDevice, dev->stream) == cudaSuccess &&
+                  cudaMemcpyAsync(dcone, cd.cone.data(), cd.cone.size() * sizeof(float4), cudaMemcpyHostToDevice, dev->stream) == cudaSuccess &&
                   cudaStreamSynchronize(dev->stream) == cudaSuccess;   // cd is a local
         if (!ok) return false;
-        out = ClusterRange{dv, dt, dorig, di, db, dblob, 0u, {0, 0, 0}, 0};
+        out = ClusterRange{dv, dt, dorig, di, db, dblob, dcone, 0u, {0, 0, 0}, 0};
         range_sphere(cd, out);
         dev->ranges[key] = out;
         return true;
@@ -1234,7 +1266,7 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
     const float* dShadowMvp = (const float*)(dp + offShadow);
     const WorkItem* dWork = slot.workBuf;
     if (n) {   // the frame's tables, on the upload stream too: neither the main nor the shadow stream has to wait for the other
-        expand_chunks_kernel<<<(unsigned)n, 64, 0, dev->upStream>>>(dObjects, (const uint32_t*)(dp + offBase), (const uint32_t*)(dp + offSeq), (const uint32_t*)(dp + offSlot), dShadowMvp,
+        expand_chunks_kernel<<<(unsigned)n, 128, 0, dev->upStream>>>(dObjects, (const uint32_t*)(dp + offBase), (const uint32_t*)(dp + offSeq), (const uint32_t*)(dp + offSlot), dShadowMvp,
                                                                     (uint32_t)n, passes, nChunks, plan.mainTarget, plan.shadowTarget, slot.chunkBuf, slot.chunkObjBuf, slot.workBuf);
         dev->launches += 1;
     }
@@ -1257,6 +1289,7 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
         PeerList pl{}; pl.n = 0;
         for (int r = 0; r < dev->shardRanks; ++r) pl.p[pl.n++] = &dev->peerFlags[r]->gatheredFree;
         shard_signal_kernel<<<1, 32, 0, dev->gatherStream>>>(pl, F1);
+        LAUNCHED("shard_signal_kernel");
     }
 
     // ---- draw_shadow (src/vk_engine_run.cpp:334-382) on the shadow stream, concurrently with the main
@@ -1278,6 +1311,7 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
             PeerList pl{}; pl.n = 0;
             for (int r = 0; r < dev->shardRanks; ++r) if (r != dev->shardRank) pl.p[pl.n++] = &dev->peerFlags[r]->shadowCleared[dev->shardRank];
             shard_signal_kernel<<<1, 32, 0, ss>>>(pl, F1);
+            LAUNCHED("shard_signal_kernel");
         }
         for (int layer = 0; layer < plan.shadowLayers; ++layer) {
             RasterTarget rt = plan.shadowTarget;
@@ -1302,6 +1336,7 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
                 // peer memory: wait until every peer has cleared its map for this frame, store my rows into all of them, tell
                 // them, and wait for theirs
                 shard_wait_kernel<<<1, 32, 0, ss>>>(dev->myFlags->shadowCleared, peersMask, F1, dev->countersHost + 12, 1u);
+                LAUNCHED("shard_wait_kernel");
                 PeerList maps{}; maps.n = 0;
                 for (int r = 0; r < dev->shardRanks; ++r) if (r != dev->shardRank) maps.p[maps.n++] = dev->peerShadow[r][slotIdx];
                 for (int layer = 0; layer < plan.shadowLayers; ++layer) {
@@ -1310,12 +1345,15 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
                     if (m1 <= m0) continue;
                     const size_t first = (size_t)layer * sn + (size_t)m0 * dev->S, count = (size_t)(m1 - m0) * dev->S;
                     shard_push_rows_kernel<<<grid_for(count / 4, 256, (unsigned)dev->smCount * 4), 256, 0, ss>>>(dev->shadowBits, maps, first, count);
+                    LAUNCHED("shard_push_rows_kernel");
                     dev->launches += 1;
                 }
                 PeerList pl{}; pl.n = 0;
                 for (int r = 0; r < dev->shardRanks; ++r) if (r != dev->shardRank) pl.p[pl.n++] = &dev->peerFlags[r]->shadowReady[dev->shardRank];
                 shard_signal_kernel<<<1, 32, 0, ss>>>(pl, F1);
+                LAUNCHED("shard_signal_kernel");
                 shard_wait_kernel<<<1, 32, 0, ss>>>(dev->myFlags->shadowReady, peersMask, F1, dev->countersHost + 12, 2u);
+                LAUNCHED("shard_wait_kernel");
             } else {
                 for (int layer = 0; layer < plan.shadowLayers; ++layer) {
                     uint32_t* base = dev->shadowBits + (size_t)layer * sn;
@@ -1415,6 +1453,7 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
     if (p2p && gatherFrame) {
         // the shading kernel stores this rank's rows into rank 0's image as well: wait until rank 0 has released it
         shard_wait_kernel<<<1, 32, 0, st>>>(&dev->myFlags->gatheredFree, 1u, F1, dev->countersHost + 12, 3u);
+        LAUNCHED("shard_wait_kernel");
         sb.rgba8Peer = dev->rootGathered[slotIdx];
     }
     {
@@ -1431,6 +1470,7 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
     if (p2p && gatherFrame) {           // my rows of this frame are in rank 0's image
         PeerList pl{}; pl.n = 1; pl.p[0] = &dev->peerFlags[0]->frameReady[dev->shardRank];
         shard_signal_kernel<<<1, 32, 0, st>>>(pl, F1);
+        LAUNCHED("shard_signal_kernel");
         dev->lastGatherF1 = F1;
     } else if (sharded) dev->lastGatherF1 = 0;
     CK(cudaGetLastError());
@@ -1475,6 +1515,7 @@ int vkr_sync(VkrDevice* dev) {
     if (dev->gatherStream) CK(cudaStreamSynchronize(dev->gatherStream));
     if (dev->p2p && dev->shardRank == 0 && dev->lastGatherF1) {      // "everything issued" includes the peers' rows of the last frame
         shard_wait_kernel<<<1, 32, 0, dev->copyStream>>>(dev->myFlags->frameReady, (uint32_t)((1ull << dev->shardRanks) - 1ull), dev->lastGatherF1, dev->countersHost + 12, 4u);
+        LAUNCHED("shard_wait_kernel (vkr_sync)");
         CK(cudaStreamSynchronize(dev->copyStream));
     }
     if (dev->countersHost[12]) {
@@ -1523,14 +1564,15 @@ int vkr_sync(VkrDevice* dev) {
         double sum = 0.0;
         for (uint64_t k = first; k < dev->kevRecorded; ++k) {
             float ms = 0;
-            cudaEventElapsedTime(&ms, dev->kev[k % VkrDevice::KRING][0], dev->kev[k % VkrDevice::KRING][1]);
+            if (cudaEventElapsedTime(&ms, dev->kev[k % VkrDevice::KRING][0], dev->kev[k % VkrDevice::KRING][1]) != cudaSuccess) { cudaGetLastError(); ms = 0; }
             sum += ms;
         }
         dev->timings[VKR_T_GEOM_KERNEL] = (float)(sum / (double)(dev->kevRecorded - first));
         dev->kevRead = dev->kevRecorded;
     }
     if (dev->tevValid) {
-        auto el = [&](int a, int b) { float ms = 0; cudaEventElapsedTime(&ms, dev->tev[a], dev->tev[b]); return ms; };
+        // (an event pair that this frame's configuration never recorded reads as 0 and must not leave an error behind)
+        auto el = [&](int a, int b) { float ms = 0; if (cudaEventElapsedTime(&ms, dev->tev[a], dev->tev[b]) != cudaSuccess) { cudaGetLastError(); ms = 0; } return ms; };
         dev->timings[VKR_T_UPLOAD] = el(0, 1);
         dev->timings[VKR_T_SHADOW] = dev->shadowTimed ? el(7, 8) : 0.0f;   // overlaps the geometry pass
         dev->timings[VKR_T_GEOMETRY] = el(1, 5);
@@ -1541,7 +1583,7 @@ int vkr_sync(VkrDevice* dev) {
         dev->timings[VKR_T_TRANSPARENT] = el(5, 9); dev->timings[VKR_T_POST] = 0;   // tonemap + present are fused into the shade kernel
         dev->timings[VKR_T_TOTAL] = el(0, 6);
         dev->timings[VKR_T_SHADOW_EXCHANGE] = dev->shadowTimed ? el(10, 8) : 0.0f;
-        dev->timings[VKR_T_FRAME_GATHER] = dev->shardRanks > 1 ? el(11, 12) : 0.0f;
+        dev->timings[VKR_T_FRAME_GATHER] = (dev->shardRanks > 1 && !dev->p2p) ? el(11, 12) : 0.0f;     // (over peer memory the shading kernel's stores are the gather)
         dev->timings[VKR_T_READBACK] = dev->rbTimed ? el(13, 14) : 0.0f;
         dev->stats.frametime = dev->timings[VKR_T_TOTAL];
         dev->stats.mesh_draw_time = dev->timings[VKR_T_SHADOW] + dev->timings[VKR_T_GEOMETRY];
@@ -1574,9 +1616,10 @@ static int readback_issue(VkrDevice* dev, VkrTarget what, void* dst, size_t dstB
     // copy engine work goes to the copy stream so the next frame's kernels overlap it
     CK(cudaStreamWaitEvent(dev->copyStream, dev->slots[dev->lastSlot].rendered, 0));
     if ((what == VKR_TARGET_RGBA8_GATHERED || what == VKR_TARGET_RGB8) && dev->shardRanks > 1) {
-        if (dev->p2p)      // every rank's rows of that frame have landed in my image
+        if (dev->p2p) {    // every rank's rows of that frame have landed in my image
             shard_wait_kernel<<<1, 32, 0, dev->copyStream>>>(dev->myFlags->frameReady, (uint32_t)((1ull << dev->shardRanks) - 1ull), dev->lastGatherF1, dev->countersHost + 12, 4u);
-        else CK(cudaStreamWaitEvent(dev->copyStream, dev->gatheredEv[dev->lastSlot], 0));
+            LAUNCHED("shard_wait_kernel (read-back)");
+        } else CK(cudaStreamWaitEvent(dev->copyStream, dev->gatheredEv[dev->lastSlot], 0));
     }
     if (what == VKR_TARGET_RGB8) {
         const size_t px = (size_t)dev->W * dev->H;

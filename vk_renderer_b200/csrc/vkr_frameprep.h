@@ -74,7 +74,9 @@ struct ClusterData {
     std::vector<uint2> info;         // per cluster
     std::vector<float4> bounds;      // per cluster: min, max
     std::vector<uint4> blob;         // per cluster CL_BLOB_BYTES: interleaved (tris, orig), then the gathered positions
+    std::vector<float4> cone;        // per cluster: (axis, cos alpha), (centre, radius), (Nmin, sin alpha, 0, 0) — ClusterCone
 };
+
 // Spatial order of a draw's triangles for the greedy cut below: a k-d partition of the centroids whose split points are
 // multiples of CL_TRIS.  A range that needs k = ceil(n / CL_TRIS) clusters is split along the longest axis of its centroid
 // bounds into the floor(k / 2) * CL_TRIS lowest triangles and the rest, recursively, so every leaf is one full cluster (the
@@ -119,7 +121,7 @@ inline void spatial_order(const uint32_t* idx, uint32_t triCount, const float4* 
 // `pos` are the mesh's positions (x,y,z,1).  Triangles are put in spatial_order, then cut greedily: a cluster
 // closes when it holds CL_TRIS triangles or the next triangle would take it past CL_VERTS vertices.
 inline void build_clusters(const uint32_t* idx, uint32_t triCount, uint32_t nv, const float4* pos, ClusterData& out) {
-    out.verts.clear(); out.tris.clear(); out.orig.clear(); out.info.clear(); out.bounds.clear(); out.blob.clear();
+    out.verts.clear(); out.tris.clear(); out.orig.clear(); out.info.clear(); out.bounds.clear(); out.blob.clear(); out.cone.clear();
     std::vector<uint32_t> order;
     spatial_order(idx, triCount, pos, order);
     std::vector<uint32_t> stamp(nv, 0xFFFFFFFFu), local(nv, 0u);
@@ -159,6 +161,42 @@ inline void build_clusters(const uint32_t* idx, uint32_t triCount, uint32_t nv, 
         // (positions are required to be finite; min/max skip NaNs)
         out.bounds.push_back(make_float4(lo[0], lo[1], lo[2], 0.0f));
         out.bounds.push_back(make_float4(hi[0], hi[1], hi[2], 0.0f));
+        {   // normal cone + bounding sphere (ClusterCone), rounded to the safe side; a degenerate triangle or a cone wider than
+            // ~80 degrees switches the facing cull off for the cluster (Nmin = 0)
+            double ax = 0, ay = 0, az = 0, nmin = INFINITY, lmax = 0;
+            std::vector<double> nn((size_t)nt * 3);
+            for (uint32_t k = 0; k < nt; ++k) {
+                const uint32_t pk = out.tris[(size_t)c * CL_TRIS + k];
+                const float4 q0 = pos[out.verts[off + (pk & 127u)]], q1 = pos[out.verts[off + ((pk >> 7) & 127u)]], q2 = pos[out.verts[off + ((pk >> 14) & 127u)]];
+                const double e1[3] = {(double)q1.x - q0.x, (double)q1.y - q0.y, (double)q1.z - q0.z}, e2[3] = {(double)q2.x - q0.x, (double)q2.y - q0.y, (double)q2.z - q0.z};
+                const double n[3] = {e1[1] * e2[2] - e1[2] * e2[1], e1[2] * e2[0] - e1[0] * e2[2], e1[0] * e2[1] - e1[1] * e2[0]};
+                const double len = std::sqrt(n[0] * n[0] + n[1] * n[1] + n[2] * n[2]);
+                nmin = std::min(nmin, len);
+                const double e3[3] = {(double)q2.x - q1.x, (double)q2.y - q1.y, (double)q2.z - q1.z};
+                lmax = std::max({lmax, std::sqrt(e1[0] * e1[0] + e1[1] * e1[1] + e1[2] * e1[2]), std::sqrt(e2[0] * e2[0] + e2[1] * e2[1] + e2[2] * e2[2]),
+                                 std::sqrt(e3[0] * e3[0] + e3[1] * e3[1] + e3[2] * e3[2])});
+                for (int a = 0; a < 3; ++a) nn[(size_t)k * 3 + a] = len > 0 ? n[a] / len : 0.0;
+                ax += nn[(size_t)k * 3]; ay += nn[(size_t)k * 3 + 1]; az += nn[(size_t)k * 3 + 2];
+            }
+            const double al = std::sqrt(ax * ax + ay * ay + az * az);
+            double cosA = -1.0;
+            if (al > 1e-12 && nmin > 0.0 && std::isfinite(nmin)) {
+                ax /= al; ay /= al; az /= al;
+                cosA = 1.0;
+                for (uint32_t k = 0; k < nt; ++k) cosA = std::min(cosA, nn[(size_t)k * 3] * ax + nn[(size_t)k * 3 + 1] * ay + nn[(size_t)k * 3 + 2] * az);
+            }
+            const double cx = 0.5 * ((double)lo[0] + hi[0]), cy = 0.5 * ((double)lo[1] + hi[1]), cz = 0.5 * ((double)lo[2] + hi[2]);
+            double rad = 0.0;
+            for (uint32_t k = 0; k < count; ++k) {
+                const float4 q = pos[out.verts[off + k]];
+                rad = std::max(rad, std::sqrt((q.x - cx) * (q.x - cx) + (q.y - cy) * (q.y - cy) + (q.z - cz) * (q.z - cz)));
+            }
+            const bool usable = cosA > 0.17 && std::isfinite(rad) && std::isfinite(cx + cy + cz);
+            const double cosSafe = usable ? cosA * (1.0 - 1e-5) - 1e-6 : 0.0, sinSafe = usable ? std::min(1.0, std::sqrt(std::max(0.0, 1.0 - cosSafe * cosSafe)) * (1.0 + 1e-5) + 1e-6) : 1.0;
+            out.cone.push_back(make_float4((float)ax, (float)ay, (float)az, (float)cosSafe));
+            out.cone.push_back(make_float4((float)cx, (float)cy, (float)cz, (float)(rad * (1.0 + 1e-5) + 1e-30)));
+            out.cone.push_back(make_float4(usable && std::isfinite(lmax) ? (float)(nmin * (1.0 - 1e-5)) : 0.0f, (float)sinSafe, (float)(lmax * (1.0 + 1e-5)), 0.0f));
+        }
         {   // the cluster's self-contained block
             const size_t b0 = out.blob.size();
             out.blob.resize(b0 + CL_BLOB_BYTES / 16, uint4{0u, 0u, 0u, 0u});
@@ -172,7 +210,7 @@ inline void build_clusters(const uint32_t* idx, uint32_t triCount, uint32_t nv, 
 }
 
 struct ClusterRange {
-    const uint32_t* verts; const uint32_t* tris; const uint32_t* orig; const uint2* info; const float4* bounds; const uint4* blob;
+    const uint32_t* verts; const uint32_t* tris; const uint32_t* orig; const uint2* info; const float4* bounds; const uint4* blob; const float4* cone;
     uint32_t nClusters;
     float center[3], radius;          // bounding sphere of the whole range (object space), for the processing order
 };
@@ -245,6 +283,9 @@ inline std::string plan_frame(const VkrGPUSceneData* scene, const VkrRenderObjec
     plan.opaqueCount = (uint32_t)n;
     plan.opaqueClusters = 0;
     plan.anyCutout = false;
+    bool haveLast = false;
+    uint32_t lastMesh = 0, lastFirst = 0, lastCount = 0;
+    ClusterRange lastRange{};
     for (size_t i = 0; i < n; ++i) {
         const VkrRenderObject& ro = objs[i];
         if (ro.mesh >= meshes.size()) return "render object references an unknown mesh";
@@ -261,9 +302,13 @@ inline std::string plan_frame(const VkrGPUSceneData* scene, const VkrRenderObjec
         o.pos = m.pos; o.attrA = m.attrA; o.attrB = m.attrB;
         o.idx = m.idx + ro.firstIndex;
         o.triCount = ro.indexCount / 3;
-        ClusterRange cr{};
-        if (o.triCount && !clusters.get(ro.mesh, ro.firstIndex, ro.indexCount, cr)) return "out of memory building clusters";
-        o.clVerts = cr.verts; o.clTris = cr.tris; o.clOrig = cr.orig; o.clInfo = cr.info; o.clBounds = cr.bounds; o.clBlob = cr.blob;
+        // (instances of one range follow each other in most draw lists: the provider is asked once per run)
+        if (o.triCount && !(haveLast && lastMesh == ro.mesh && lastFirst == ro.firstIndex && lastCount == ro.indexCount)) {
+            if (!clusters.get(ro.mesh, ro.firstIndex, ro.indexCount, lastRange)) return "out of memory building clusters";
+            haveLast = true; lastMesh = ro.mesh; lastFirst = ro.firstIndex; lastCount = ro.indexCount;
+        }
+        const ClusterRange cr = o.triCount ? lastRange : ClusterRange{};
+        o.clVerts = cr.verts; o.clTris = cr.tris; o.clOrig = cr.orig; o.clInfo = cr.info; o.clBounds = cr.bounds; o.clBlob = cr.blob; o.clCone = cr.cone; o.pad = 0;
         // bounding sphere of the draw's range (object space): sort key of the processing order below
         sphere[4 * i] = cr.center[0]; sphere[4 * i + 1] = cr.center[1]; sphere[4 * i + 2] = cr.center[2]; sphere[4 * i + 3] = cr.radius;
         o.primBase = (uint32_t)prim;

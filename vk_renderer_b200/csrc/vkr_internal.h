@@ -79,6 +79,8 @@ struct DObject {
     uint32_t material;
     uint32_t flags;           // bit0: transparent pass, bit1: alpha-tested (albedo texture has alpha < 0.5), bit2: a sampled texture has mips
     const uint4* clBlob;      // the same clusters as self-contained CL_BLOB_BYTES blocks (what the geometry kernels stage with one bulk copy)
+    const float4* clCone;     // three float4 per cluster: normal cone and bounding sphere (ClusterCone, vkr_raster.cuh)
+    uint64_t pad;
 };
 static_assert(sizeof(DObject) % 16 == 0, "DObject array is read with 16-byte loads");
 

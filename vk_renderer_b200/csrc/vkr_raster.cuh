@@ -721,6 +721,8 @@ struct CornerAcc {
     float zmin, zmax;               // depth bounds (valid when allFront)
     uint32_t outAll;                // bit p set: every corner is outside frustum plane p by more than the margin
     uint32_t allFront;              // every corner has w safely > 0
+    float wmax, wmin;               // bounds of w over the box (valid when allFront; wmin > 0)
+    float mgx, mgy;                 // largest rounding margin of x/w and y/w over the corners, NDC units (valid when allFront)
 };
 static const float CULL_EPS = 9.5367431640625e-07f;   // 2^-20
 
@@ -736,11 +738,12 @@ VKR_HD void corner_outside(int comp, float v, float e, float w, float ew, bool& 
 }
 VKR_HD bool corner_front(float w, float ew) { return w > 2.0f * ew && w > 1e-30f; }
 // Widened NDC interval of a component of a corner with w safely > 0.
-VKR_HD void corner_ndc(float v, float e, float w, float ew, float& lo, float& hi) {
+VKR_HD float corner_ndc(float v, float e, float w, float ew, float& lo, float& hi) {
     const float rw = 1.0f / (w - ew);             // >= 1/w_exact
     const float n = v / w;
     const float mg = (e + fabsf(n) * ew) * rw * 2.0f;
     lo = n - mg; hi = n + mg;
+    return mg;
 }
 
 VKR_HD CornerAcc corner_eval(const float* __restrict__ m, float4 bmin, float4 bmax, int corner) {
@@ -759,11 +762,13 @@ VKR_HD CornerAcc corner_eval(const float* __restrict__ m, float4 bmin, float4 bm
     const bool front = corner_front(v[3], e[3]);
     a.allFront = front ? 1u : 0u;
     if (front) {
-        corner_ndc(v[0], e[0], v[3], e[3], a.xmin, a.xmax);
-        corner_ndc(v[1], e[1], v[3], e[3], a.ymin, a.ymax);
+        a.mgx = corner_ndc(v[0], e[0], v[3], e[3], a.xmin, a.xmax);
+        a.mgy = corner_ndc(v[1], e[1], v[3], e[3], a.ymin, a.ymax);
         corner_ndc(v[2], e[2], v[3], e[3], a.zmin, a.zmax);
+        a.wmax = v[3] + e[3]; a.wmin = v[3] - e[3];
     } else {
         a.xmin = a.ymin = a.zmin = 0.0f; a.xmax = a.ymax = a.zmax = 0.0f;
+        a.wmax = 0.0f; a.wmin = 0.0f; a.mgx = a.mgy = 0.0f;
     }
     return a;
 }
@@ -774,6 +779,7 @@ VKR_HD CornerAcc corner_merge(const CornerAcc& a, const CornerAcc& b) {
     r.zmin = fminf(a.zmin, b.zmin); r.zmax = fmaxf(a.zmax, b.zmax);
     r.outAll = a.outAll & b.outAll;
     r.allFront = a.allFront & b.allFront;
+    r.wmax = fmaxf(a.wmax, b.wmax); r.wmin = fminf(a.wmin, b.wmin); r.mgx = fmaxf(a.mgx, b.mgx); r.mgy = fmaxf(a.mgy, b.mgy);
     return r;
 }
 
@@ -806,15 +812,87 @@ VKR_HD ClusterRect cluster_finalize(const CornerAcc& a, const RasterTarget& rt) 
     r.verdict = CLUSTER_TEST;
     return r;
 }
-// The whole test of one cluster for one pass, by one thread (expand_chunks_kernel, host emulation).
-VKR_HD CullRec make_cull_rec(const float* __restrict__ mvp, float4 bmin, float4 bmax, const RasterTarget& rt) {
-    CornerAcc a = corner_eval(mvp, bmin, bmax, 0);
-    for (int k = 1; k < 8; ++k) a = corner_merge(a, corner_eval(mvp, bmin, bmax, k));
-    const ClusterRect r = cluster_finalize(a, rt);
+// ---- facing cull of a whole cluster ---------------------------------------------------------------
+// The face cull is decided per triangle on SNAPPED window coordinates (setup_snapped: sign of the doubled area A2).  A cluster
+// can be dropped before any vertex work when every triangle of it would be culled that way, and that can be argued exactly:
+//   * with clip coordinates (x, y, w) = M' (p, 1), the determinant D of a triangle's three (x, y, w) rows equals pi . E, where
+//     pi = (N, -N . p0), N = (p1 - p0) x (p2 - p0), is the triangle's plane and E (4 numbers per matrix, `eye`, computed on the
+//     host in double precision from the very matrix the kernel uses) is the homogeneous point M' maps to (0, 0, 0): the eye.
+//     With every w > 0 the doubled area in sub-pixels is A2 = (128 W)(128 H) D / (w0 w1 w2), so its sign is D's;
+//   * every unit normal of the cluster lies within the angle alpha of the cone axis a (ClusterCone, built with the clusters),
+//     its vertices within r of c.  With v = E.xyz - E.w c and beta the angle between a and +-v:
+//     |D| >= Nmin (|v| cos(alpha + beta) - |E.w| r)  whenever that is positive (Nmin: the smallest |N| of the cluster);
+//   * the kernel's vertices differ from the exact ones by at most delta = 1 sub-pixel (rounding to the grid: 0.5, the divide
+//     and the viewport FMA: < 0.1 at 2^20 sub-pixels) plus the rounding of the matrix product, a quarter of the margin the box
+//     test carries (mgx, mgy: 2^-20 |terms| where three roundings make 3 * 2^-24); moving every vertex by delta changes A2 by at
+//     most 8 delta R + 8 delta^2, R the largest extent of a TRIANGLE in sub-pixels: an object-space edge of length L projects to
+//     at most L (|row x| + max|x/w| |row w|) / wmin in NDC (x1/w1 - x0/w0 = (dx - (x0/w0) dw) / w1), Lmax being stored with the cone.
+// If the lower bound of |A2| exceeds that with a factor to spare, no triangle changes sign (or vanishes) under snapping: all of
+// them are culled by the per-triangle test, and dropping the cluster changes nothing.
+// The point E with M' E = 0 for the 3 x 4 matrix M' of the x, y and w rows of `mvp` (column-major): E_i = +-minor_i.  The sign is
+// fixed so that det[(x, y, w) rows of a triangle] == plane(p0, p1, p2) . E, checked on one triangle in double precision.
+VKR_HD void eye_point(const float* m, float out[8]) {
+    const double r[3][4] = {{m[0], m[4], m[8], m[12]}, {m[1], m[5], m[9], m[13]}, {m[3], m[7], m[11], m[15]}};
+    double E[4];
+    for (int skip = 0; skip < 4; ++skip) {
+        const int c0 = skip == 0 ? 1 : 0, c1 = skip <= 1 ? 2 : 1, c2 = skip <= 2 ? 3 : 2;
+        const double mn = r[0][c0] * (r[1][c1] * r[2][c2] - r[1][c2] * r[2][c1]) - r[0][c1] * (r[1][c0] * r[2][c2] - r[1][c2] * r[2][c0]) +
+                          r[0][c2] * (r[1][c0] * r[2][c1] - r[1][c1] * r[2][c0]);
+        E[skip] = (skip & 1) ? -mn : mn;
+    }
+    // reference triangle (0,0,0) (1,0,0) (0,1,0): plane N = (0,0,1), pi = (0,0,1,0) -> pi . E = E[2]
+    const double P[3][3] = {{r[0][3], r[1][3], r[2][3]}, {r[0][0] + r[0][3], r[1][0] + r[1][3], r[2][0] + r[2][3]}, {r[0][1] + r[0][3], r[1][1] + r[1][3], r[2][1] + r[2][3]}};
+    const double D = P[0][0] * (P[1][1] * P[2][2] - P[1][2] * P[2][1]) - P[0][1] * (P[1][0] * P[2][2] - P[1][2] * P[2][0]) + P[0][2] * (P[1][0] * P[2][1] - P[1][1] * P[2][0]);
+    if ((D < 0.0) != (E[2] < 0.0)) for (int i = 0; i < 4; ++i) E[i] = -E[i];
+    // scale into float range (only ratios and signs matter to the test, but a2min uses the magnitude: keep it)
+    for (int i = 0; i < 4; ++i) out[i] = (float)E[i];
+    // Lipschitz constants of x, y and w in the object-space position (rounded up), for the triangle-extent bound of cone_culls
+    for (int k = 0; k < 3; ++k) out[4 + k] = (float)(sqrt(r[k][0] * r[k][0] + r[k][1] * r[k][1] + r[k][2] * r[k][2]) * (1.0 + 1e-6));
+    out[7] = 0.0f;
+}
+
+struct ClusterCone { float4 axisCos; float4 centerRadius; float4 nminSin; };      // (a, cos alpha) (c, r) (Nmin, sin alpha, Lmax, -)
+
+VKR_HD bool cone_culls(const ClusterCone& k, const float* __restrict__ eye, const CornerAcc& a, const RasterTarget& rt) {
+    if (!a.allFront || !(k.nminSin.x > 0.0f) || !(a.wmin > 0.0f)) return false;
+    const float sgn = rt.cullFront ? -1.0f : 1.0f;            // main pass: culled when D > 0; shadow pass (cull FRONT): when D < 0
+    const float vx = eye[0] - eye[3] * k.centerRadius.x, vy = eye[1] - eye[3] * k.centerRadius.y, vz = eye[2] - eye[3] * k.centerRadius.z;
+    const float lv = sqrtf(vx * vx + vy * vy + vz * vz);
+    if (!(lv > 0.0f)) return false;
+    const float cosb = sgn * (k.axisCos.x * vx + k.axisCos.y * vy + k.axisCos.z * vz) / lv;
+    if (!(cosb > 0.0f)) return false;
+    const float sinb = sqrtf(fmaxf(0.0f, 1.0f - cosb * cosb));
+    const float cab = k.axisCos.w * cosb - k.nminSin.y * sinb;          // cos(alpha + beta)
+    if (!(cab > 0.0f)) return false;
+    const float lower = k.nminSin.x * (lv * cab - fabsf(eye[3]) * k.centerRadius.w);
+    if (!(lower > 0.0f)) return false;
+    const float a2min = (rt.halfW256 * rt.halfH256) * lower / (a.wmax * a.wmax * a.wmax);
+    // eye[4..6]: |row x|, |row y|, |row w| of the matrix (xyz parts); the largest triangle extent, sub-pixels
+    const float ndx = fmaxf(fabsf(a.xmin), fabsf(a.xmax)), ndy = fmaxf(fabsf(a.ymin), fabsf(a.ymax));
+    const float ex = k.nminSin.z * (eye[4] + ndx * eye[6]) / a.wmin * rt.halfW256, ey = k.nminSin.z * (eye[5] + ndy * eye[6]) / a.wmin * rt.halfH256;
+    const float R = fmaxf(ex, ey) * 1.001f + 2.0f;
+    const float delta = 1.0f + 0.25f * fmaxf(a.mgx * rt.halfW256, a.mgy * rt.halfH256);
+    const float moved = 8.0f * delta * R + 8.0f * delta * delta;
+    return a2min * 0.9f > moved;                               // (the bounds are exact; 10 % for the float evaluation of this test.  NaN anywhere: false)
+}
+
+// The whole test of one cluster for one pass, by one thread (host emulation; expand_chunks_kernel spreads the corners over
+// eight lanes and calls cluster_verdict on the merged result).
+VKR_HD CullRec cluster_verdict(const CornerAcc& a, const ClusterCone* cone, const float* __restrict__ eye, const RasterTarget& rt) {
+    ClusterRect r = cluster_finalize(a, rt);
+#if !defined(VKR_NO_CONE)      // (-DVKR_NO_CONE: the A/B of the facing cull)
+    if (r.verdict != CLUSTER_CULLED && cone != nullptr && cone_culls(*cone, eye, a, rt)) r.verdict = CLUSTER_CULLED;
+#endif
     CullRec c;
     c.x0 = (int16_t)r.x0; c.y0 = (int16_t)r.y0; c.x1 = (int16_t)r.x1; c.y1 = (int16_t)r.y1;     // extents are <= 16384
     c.zminBits = r.zminBits; c.verdict = r.verdict;
     return c;
+}
+VKR_HD CullRec make_cull_rec(const float* __restrict__ mvp, float4 bmin, float4 bmax, const RasterTarget& rt,
+                             const ClusterCone* cone = nullptr, const float* eye = nullptr) {
+    CornerAcc a = corner_eval(mvp, bmin, bmax, 0);
+    for (int k = 1; k < 8; ++k) a = corner_merge(a, corner_eval(mvp, bmin, bmax, k));
+    return cluster_verdict(a, cone, eye, rt);
 }
 // A stored depth hides the cluster at that pixel iff it is strictly nearer than anything the cluster can write.
 VKR_HD bool depth_hides(uint32_t storedBits, uint32_t zminBits) { return storedBits < zminBits; }
