@@ -178,6 +178,7 @@ class Renderer:
                  device: int = 0, stream: int | None = None, flags: int = 0):
         self.lib, self.prefix = lib, prefix
         self.width, self.height, self.shadow_extent = width, height, shadow_extent
+        self.stream = stream             # the cudaStream_t frames are submitted on (None: the library's own)
         self._bind()
         cfg = Config(device, width, height, shadow_extent, stream, flags)
         self.dev = C.c_void_p()

@@ -127,8 +127,26 @@ __global__ void shard_wait_kernel(const uint32_t* flags, uint32_t mask, uint32_t
         }
     }
 }
-// My rows of one shadow layer into the same rows of every peer's map (texels [first, first + count) of the layer).
-__global__ void shard_push_rows_kernel(const uint32_t* __restrict__ src, const __grid_constant__ PeerList dst, size_t first, size_t count) {
+__device__ __forceinline__ void spin_until(const uint32_t* flag, uint32_t value, uint32_t* err, uint32_t code) {
+    const long long t0 = clock64();
+    while ((int32_t)(ld_acquire_sys(flag) - value) < 0) {
+        if (clock64() - t0 > 8000000000ll) { *err = code; break; }
+        __nanosleep(64);
+    }
+}
+// Tell the peers (dst), then wait for theirs (flags[i] >= value for i in mask): the two ends of one exchange in one launch.
+__global__ void shard_signal_wait_kernel(const __grid_constant__ PeerList dst, const uint32_t* flags, uint32_t mask, uint32_t value, uint32_t* err, uint32_t code) {
+    if ((int)threadIdx.x < dst.n) { __threadfence_system(); st_release_sys(dst.p[threadIdx.x], value); }
+    const uint32_t i = threadIdx.x;
+    if (i < (uint32_t)MAX_RANKS && ((mask >> i) & 1u)) spin_until(flags + i, value, err, code | (i << 8));
+}
+// My rows of one shadow layer into the same rows of every peer's map (texels [first, first + count) of the layer), once every
+// peer has cleared its map for this frame (waitFlags[i] >= value for i in mask; each CTA checks before its first store — the
+// peers' clears do not wait for anything on this GPU).
+__global__ void shard_push_rows_kernel(const uint32_t* __restrict__ src, const __grid_constant__ PeerList dst, size_t first, size_t count,
+                                       const uint32_t* waitFlags, uint32_t mask, uint32_t value, uint32_t* err) {
+    if (threadIdx.x < (unsigned)MAX_RANKS && ((mask >> threadIdx.x) & 1u)) spin_until(waitFlags + threadIdx.x, value, err, 1u | (threadIdx.x << 8));
+    __syncthreads();
     const size_t stride = (size_t)gridDim.x * blockDim.x, tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (((first | count) & 3u) == 0u) {
         const uint4* s4 = reinterpret_cast<const uint4*>(src + first);
@@ -198,54 +216,40 @@ __global__ void mip_blit_kernel(const uchar4* __restrict__ src, int sw, int sh, 
 // frustum planes, pixel rectangle, nearest depth — CullRec); one more list in submission order with the main pass's matrix
 // (the transparent pass); the 48-byte cluster records the cut-out kernel walks; and the (draw, first triangle) pairs the
 // shading pass looks up through seq >> 8.
-__device__ __forceinline__ CullRec cull_rec_8lanes(const float* __restrict__ mvp, float4 bmin, float4 bmax, const RasterTarget& rt, int corner,
-                                                   const ClusterCone& cone, const float* eye) {
-    // make_cull_rec with the eight corners on eight neighbouring lanes: one corner each, merged by three butterfly steps
-    CornerAcc a = corner_eval(mvp, bmin, bmax, corner);
-#pragma unroll
-    for (int d = 1; d < 8; d <<= 1) {
-        CornerAcc o;
-        o.xmin = __shfl_xor_sync(0xFFFFFFFFu, a.xmin, d); o.xmax = __shfl_xor_sync(0xFFFFFFFFu, a.xmax, d);
-        o.ymin = __shfl_xor_sync(0xFFFFFFFFu, a.ymin, d); o.ymax = __shfl_xor_sync(0xFFFFFFFFu, a.ymax, d);
-        o.zmin = __shfl_xor_sync(0xFFFFFFFFu, a.zmin, d); o.zmax = __shfl_xor_sync(0xFFFFFFFFu, a.zmax, d);
-        o.outAll = __shfl_xor_sync(0xFFFFFFFFu, a.outAll, d); o.allFront = __shfl_xor_sync(0xFFFFFFFFu, a.allFront, d);
-        o.wmax = __shfl_xor_sync(0xFFFFFFFFu, a.wmax, d); o.wmin = __shfl_xor_sync(0xFFFFFFFFu, a.wmin, d); o.mgx = __shfl_xor_sync(0xFFFFFFFFu, a.mgx, d); o.mgy = __shfl_xor_sync(0xFFFFFFFFu, a.mgy, d);
-        a = corner_merge(a, o);
-    }
-    return cluster_verdict(a, &cone, eye, rt);
+// Per draw (one thread each): the eye points of its matrices for the facing cull of whole clusters ([pass][draw][8]: pass 0 the
+// main matrix, 1.. the shadow layers) and its sequence slots.
+__global__ void prepare_draws_kernel(const DObject* __restrict__ objects, const uint32_t* __restrict__ seqSlotBase, const float* __restrict__ shadowMvp,
+                                     uint32_t nobj, uint32_t passes, float* __restrict__ eyes, uint2* __restrict__ chunkObj) {
+    const uint32_t obj = blockIdx.x * blockDim.x + threadIdx.x;
+    if (obj >= nobj) return;
+    for (uint32_t p = 0; p < passes; ++p)
+        eye_point(p == 0 ? objects[obj].mvp : shadowMvp + ((size_t)(p - 1) * nobj + obj) * 16, eyes + ((size_t)p * nobj + obj) * 8);
+    const uint32_t sbase = seqSlotBase[obj], ns = seqSlotBase[obj + 1] - sbase;
+    for (uint32_t k = 0; k < ns; ++k) chunkObj[sbase + k] = make_uint2(obj, k * SEQ_SLOT);
 }
+// Per cluster of the frame (one thread each; the draw is found by bisection of the cluster prefix).
 __global__ void __launch_bounds__(128) expand_chunks_kernel(const DObject* __restrict__ objects, const uint32_t* __restrict__ clusterBase,
                                      const uint32_t* __restrict__ seqSlotBase, const uint32_t* __restrict__ slotBase,
-                                     const float* __restrict__ shadowMvp, uint32_t nobj, uint32_t passes, uint32_t listStride,
+                                     const float* __restrict__ shadowMvp, const float* __restrict__ eyes, uint32_t nobj, uint32_t passes, uint32_t listStride,
                                      const __grid_constant__ RasterTarget rtMain, const __grid_constant__ RasterTarget rtShadow,
-                                     DChunk* __restrict__ chunks, uint2* __restrict__ chunkObj, WorkItem* __restrict__ work) {
-    const uint32_t obj = blockIdx.x;
-    const uint32_t base = clusterBase[obj], n = clusterBase[obj + 1] - base;
-    const uint32_t sbase = seqSlotBase[obj], ns = seqSlotBase[obj + 1] - sbase;
+                                     DChunk* __restrict__ chunks, WorkItem* __restrict__ work) {
+    const uint32_t ci = blockIdx.x * blockDim.x + threadIdx.x;
+    if (ci >= listStride) return;
+    uint32_t lo = 0, hi = nobj;                       // the last draw with clusterBase[draw] <= ci (draws without clusters share a base: skipped)
+    while (hi - lo > 1) { const uint32_t mid = (lo + hi) >> 1; if (__ldg(clusterBase + mid) <= ci) lo = mid; else hi = mid; }
+    const uint32_t obj = lo, c = ci - __ldg(clusterBase + obj), sbase = __ldg(seqSlotBase + obj);
     const DObject& o = objects[obj];
-    // the eye points of this draw's matrices (facing cull of whole clusters), once per CTA: [0] main pass, [1..] shadow layers
-    __shared__ float s_eye[1 + VKR_NUM_CASCADES][8];
-    if (threadIdx.x < passes) eye_point(threadIdx.x == 0 ? o.mvp : shadowMvp + ((size_t)(threadIdx.x - 1) * nobj + obj) * 16, s_eye[threadIdx.x]);
-    __syncthreads();
-    const int corner = threadIdx.x & 7;
-    // eight lanes per cluster (one box corner each), 16 clusters per sweep of the CTA
-    for (uint32_t c0 = 0; c0 < n; c0 += blockDim.x >> 3) {
-        const uint32_t cc = c0 + (threadIdx.x >> 3);
-        const bool valid = cc < n, writer = valid && corner == 0;
-        const uint32_t c = valid ? cc : n - 1u;                      // (idle groups shadow the last cluster: the shuffles need every lane)
-        if (writer) chunks[base + c] = make_chunk(o, obj, c, sbase);
-        const float4 bmin = o.clBounds[2 * c], bmax = o.clBounds[2 * c + 1];
-        const ClusterCone cone{o.clCone[3 * c], o.clCone[3 * c + 1], o.clCone[3 * c + 2]};
-        const CullRec mainRec = cull_rec_8lanes(o.mvp, bmin, bmax, rtMain, corner, cone, s_eye[0]);
-        if (writer) work[(size_t)passes * listStride + base + c] = make_work_item(o, obj, c, sbase, mainRec);      // submission order
-        for (uint32_t p = 0; p < passes; ++p) {
-            const uint32_t sb = slotBase[(size_t)p * nobj + obj];
-            if (sb == 0xFFFFFFFFu) continue;                         // (the same for the whole CTA)
-            const CullRec rec = p == 0 ? mainRec : cull_rec_8lanes(shadowMvp + ((size_t)(p - 1) * nobj + obj) * 16, bmin, bmax, rtShadow, corner, cone, s_eye[p]);
-            if (writer) work[(size_t)p * listStride + sb + c] = make_work_item(o, obj, c, sbase, rec);
-        }
+    chunks[ci] = make_chunk(o, obj, c, sbase);
+    const float4 bmin = o.clBounds[2 * c], bmax = o.clBounds[2 * c + 1];
+    const ClusterCone cone{o.clCone[3 * c], o.clCone[3 * c + 1], o.clCone[3 * c + 2]};
+    const CullRec mainRec = make_cull_rec(o.mvp, bmin, bmax, rtMain, &cone, eyes + (size_t)obj * 8);
+    work[(size_t)passes * listStride + ci] = make_work_item(o, obj, c, sbase, mainRec);      // submission order
+    for (uint32_t p = 0; p < passes; ++p) {
+        const uint32_t sb = slotBase[(size_t)p * nobj + obj];
+        if (sb == 0xFFFFFFFFu) continue;
+        work[(size_t)p * listStride + sb + c] = make_work_item(o, obj, c, sbase, p == 0 ? mainRec :
+            make_cull_rec(shadowMvp + ((size_t)(p - 1) * nobj + obj) * 16, bmin, bmax, rtShadow, &cone, eyes + ((size_t)p * nobj + obj) * 8));
     }
-    for (uint32_t k = threadIdx.x; k < ns; k += blockDim.x) chunkObj[sbase + k] = make_uint2(obj, k * SEQ_SLOT);
 }
 
 // ---- geometry: one WARP per cluster (<= 128 triangles, <= 128 distinct vertices of one draw); the warps of a
@@ -257,6 +261,7 @@ __global__ void __launch_bounds__(128) expand_chunks_kernel(const DObject* __res
 // vertex once, in place, into snapped window coordinates; phase 2 runs the triangles, 32 at a time, on those.
 // PASS: 0 main (visibility buffer), 1 shadow (depth only), 2 transparent (shade + additive blend, no depth write).
 enum { PASS_MAIN = 0, PASS_SHADOW = 1, PASS_TRANSPARENT = 2 };
+static const uint32_t ITEM_CHUNK = 8;          // large-triangle items a warp takes per cursor atomic
 
 // VKR_STAGE_TRIS 1: the whole block (packed triangles + positions) is staged; 0 (default): only the positions, the packed
 // triangles are read from L2 one iteration ahead (1 KB less shared memory per warp: 12 instead of 10 CTAs per SM, and it is
@@ -378,6 +383,8 @@ __device__ __forceinline__ void geometry_warp(const WorkItem* __restrict__ item,
     // works through what was parked: the candidate samples of all the small ones dealt evenly to the lanes (most triangles
     // of a dense mesh cover one or two samples, a few cover dozens: a lane never waits for its neighbour's bounding box),
     // the medium and large ones queued for large_raster_kernel (vkr_raster.cuh, "warp-cooperative handling")
+    unsigned long long mediumBase = 0xFFFFFFFFFFFFFFFFull;      // (first triangle slot | first item slot << 32) of this cluster's room in the queue
+    uint32_t mediumUsed = 0;
     for (uint32_t base = 0; base < nTris; base += 32) {
         const uint32_t t = base + lane;
         int kind = 0;
@@ -418,11 +425,16 @@ __device__ __forceinline__ void geometry_warp(const WorkItem* __restrict__ item,
 #endif
         if ((medium | large) == 0u) { __syncwarp(); continue; }
         if (medium) {
-            // medium triangles (extent < 64 px): one queue item each, no tile enumeration; the slots of the whole warp are
-            // claimed with one atomic per counter.  large_raster_kernel rasterises them with 32-bit edge functions.
-            uint32_t firstTri = 0, firstItem = 0;
-            if (lane == 0) { firstTri = atomicAdd(&q.counters[0], (uint32_t)__popc(medium)); firstItem = atomicAdd(&q.counters[1], (uint32_t)__popc(medium)); }
-            firstTri = __shfl_sync(0xFFFFFFFFu, firstTri, 0); firstItem = __shfl_sync(0xFFFFFFFFu, firstItem, 0);
+            // medium triangles (extent < 64 px): one queue item each, no tile enumeration.  The warp claims room for the whole
+            // cluster (CL_TRIS triangles and items) with ONE 64-bit atomic the first time it needs any — thousands of warps adding
+            // to the same two counters every iteration serialise at the L2 (a fifth of this kernel's stall samples on a scene of
+            // 20-pixel triangles) — and pads what it did not use with skip items when it is done with the cluster.
+            if (mediumBase == 0xFFFFFFFFFFFFFFFFull) {
+                unsigned long long b = 0;
+                if (lane == 0) b = atomicAdd(reinterpret_cast<unsigned long long*>(q.counters), (unsigned long long)CL_TRIS | ((unsigned long long)CL_TRIS << 32));
+                mediumBase = __shfl_sync(0xFFFFFFFFu, b, 0);
+            }
+            const uint32_t firstTri = (uint32_t)mediumBase + mediumUsed, firstItem = (uint32_t)(mediumBase >> 32) + mediumUsed;
             if (kind == 1) {
                 const uint32_t k = (uint32_t)__popc(medium & ((1u << lane) - 1u));
                 const bool fits = firstTri + k < q.triCap && firstItem + k < q.itemCap;
@@ -433,6 +445,7 @@ __device__ __forceinline__ void geometry_warp(const WorkItem* __restrict__ item,
                     q.items[firstItem + k] = it;
                 }
             }
+            mediumUsed += (uint32_t)__popc(medium);
         }
         __syncwarp();
         while (large) {
@@ -441,6 +454,11 @@ __device__ __forceinline__ void geometry_warp(const WorkItem* __restrict__ item,
             enqueue_large_coop(s_park[src].lt, q, lane);
         }
         __syncwarp();
+    }
+    if (mediumBase != 0xFFFFFFFFFFFFFFFFull) {          // the item slots this cluster claimed and did not fill
+        const uint32_t firstItem = (uint32_t)(mediumBase >> 32);
+        for (uint32_t k = mediumUsed + lane; k < (uint32_t)CL_TRIS; k += 32)
+            if (firstItem + k < q.itemCap) { LargeItem it; it.tri = ITEM_SKIP; it.tx = ITEM_WHOLE; it.ty = ITEM_WHOLE; q.items[firstItem + k] = it; }
     }
 }
 
@@ -502,15 +520,18 @@ __global__ void __launch_bounds__(256) large_raster_kernel(const __grid_constant
     const uint32_t nItems = min(q.counters[1], q.itemCap), nTris = min(q.counters[0], q.triCap);
     const uint32_t warpsPerGrid = (gridDim.x * blockDim.x) >> 5;
     const int lane = threadIdx.x & 31;
-    // items differ in cost by orders of magnitude (an alpha-tested tile vs. an opaque sliver): a warp's first item is its own
-    // number, the following ones come from a shared cursor (no atomic at all when the queue is shorter than the grid — on a
-    // frame of small triangles it is empty, and 4736 warps hitting one address cost more than the kernel's work)
-    for (uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < nItems;) {
-        const uint32_t cur = i;
-        if (lane == 0) i = warpsPerGrid + atomicAdd(&q.counters[4], 1u);
-        i = __shfl_sync(0xFFFFFFFFu, i, 0);
-        const LargeItem it = q.items[cur];
-        if (it.tri >= nTris) continue;                   // skip marker of an overflowed frame (the host grows the queues and redraws)
+    uint32_t nextChunk = 0xFFFFFFFFu;
+    // items differ in cost by orders of magnitude (an alpha-tested tile vs. an opaque sliver): warps take them from a shared
+    // cursor — the first ITEM_CHUNK by the warp's own number (no atomic at all on a short queue: on a frame of small triangles
+    // it is empty)
+    // ... and then ITEM_CHUNK at a time, asked for one chunk ahead: the cursor is one address for 4736 warps, and waiting for
+    // it was 60 % of this kernel's stall samples on a frame with a million items)
+    uint32_t chunk = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * ITEM_CHUNK;
+    for (uint32_t i = chunk; chunk < nItems; ++i) {
+        if (i == chunk + ITEM_CHUNK || i >= nItems) { chunk = __shfl_sync(0xFFFFFFFFu, nextChunk, 0); i = chunk; nextChunk = 0xFFFFFFFFu; if (chunk >= nItems) break; }
+        if (i == chunk && lane == 0) nextChunk = (warpsPerGrid + atomicAdd(&q.counters[4], 1u)) * ITEM_CHUNK;
+        const LargeItem it = q.items[i];
+        if (it.tri >= nTris) continue;                   // a skip marker (room a cluster claimed and did not use, or an overflowed frame)
         const LargeTri lt = q.tris[it.tri];
         const bool whole = it.tx == ITEM_WHOLE;          // medium triangle: its whole bounding box, 32-bit edge functions
         if (SHADOW) {
@@ -543,11 +564,11 @@ __global__ void __launch_bounds__(256) large_transparent_kernel(const __grid_con
     const uint32_t nItems = min(q.counters[1], q.itemCap), nTris = min(q.counters[0], q.triCap);
     const uint32_t warpsPerGrid = (gridDim.x * blockDim.x) >> 5;
     const int lane = threadIdx.x & 31;
-    for (uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < nItems;) {
-        const uint32_t cur = i;
-        if (lane == 0) i = warpsPerGrid + atomicAdd(&q.counters[4], 1u);
-        i = __shfl_sync(0xFFFFFFFFu, i, 0);
-        const LargeItem it = q.items[cur];
+    uint32_t chunk = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * ITEM_CHUNK, nextChunk = 0xFFFFFFFFu;
+    for (uint32_t i = chunk; chunk < nItems; ++i) {
+        if (i == chunk + ITEM_CHUNK || i >= nItems) { chunk = __shfl_sync(0xFFFFFFFFu, nextChunk, 0); i = chunk; nextChunk = 0xFFFFFFFFu; if (chunk >= nItems) break; }
+        if (i == chunk && lane == 0) nextChunk = (warpsPerGrid + atomicAdd(&q.counters[4], 1u)) * ITEM_CHUNK;
+        const LargeItem it = q.items[i];
         if (it.tri >= nTris) continue;
         const LargeTri lt = q.tris[it.tri];
         BlendSink sink{&sc, &sb, lt.seq};
@@ -562,6 +583,9 @@ __global__ void __launch_bounds__(128, VKR_SHADE_MIN_CTAS) shade_kernel(const __
     __shared__ float s_lut[256];
     s_lut[threadIdx.x] = sbIn.srgbLut[threadIdx.x];
     s_lut[threadIdx.x + 128] = sbIn.srgbLut[threadIdx.x + 128];
+    // sharded over peer memory: rank 0 must have released the image this frame's pixels are also stored into (nothing on this
+    // GPU stands between rank 0 and that release)
+    if (threadIdx.x == 0 && sbIn.peerFree != nullptr) spin_until(sbIn.peerFree, sbIn.peerFreeValue, sbIn.countersHost + 12, 3u);
     __syncthreads();
     ShadeBuffers sb = sbIn;
     sb.srgbLut = s_lut;
@@ -614,6 +638,7 @@ struct FrameSlot {
     // tables are built on the upload stream while this frame's kernels still read theirs)
     DChunk* chunkBuf = nullptr; size_t chunkCap = 0;       // cluster table
     uint2* chunkObjBuf = nullptr; size_t seqSlotCap = 0;   // seq >> 8 -> (draw, first triangle)
+    float* eyeBuf = nullptr; size_t eyeCap = 0;             // (1 + shadow layers) x draws x 8 floats: eye points (prepare_draws_kernel)
     WorkItem* workBuf = nullptr; size_t workCap = 0;       // (2 + shadow layers) x clusters: every pass's work items in processing order, then one list in submission order
 };
 
@@ -1219,7 +1244,7 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
     const size_t offObj = 0, offBase = align16(offObj + szObj), offSeq = align16(offBase + szBase), offShadow = align16(offSeq + szBase),
                  offSlot = align16(offShadow + szShadow);
     const size_t total = align16(offSlot + szSlot) + 16;
-    if (slot.chunkCap < nChunks || slot.seqSlotCap < nSeqSlots || slot.workCap < (size_t)(passes + 1) * nChunks) {
+    if (slot.chunkCap < nChunks || slot.seqSlotCap < nSeqSlots || slot.workCap < (size_t)(passes + 1) * nChunks || slot.eyeCap < (size_t)passes * n) {
         // a table has to grow: the frame that last used this slot must have finished with the old one before it is released
         if (dev->frameIndex >= VKR_FRAME_OVERLAP) CK(cudaEventSynchronize(slot.rendered));
         if (slot.chunkCap < nChunks) {
@@ -1231,6 +1256,11 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
             dev_free(dev, slot.chunkObjBuf); slot.chunkObjBuf = nullptr;
             slot.seqSlotCap = std::max<size_t>((size_t)nSeqSlots * 3 / 2, 1024);
             ALLOC(slot.chunkObjBuf, slot.seqSlotCap * sizeof(uint2));
+        }
+        if (slot.eyeCap < (size_t)passes * n) {
+            dev_free(dev, slot.eyeBuf); slot.eyeBuf = nullptr;
+            slot.eyeCap = std::max<size_t>((size_t)passes * n * 3 / 2, 256);
+            ALLOC(slot.eyeBuf, slot.eyeCap * 8 * sizeof(float));
         }
         if (slot.workCap < (size_t)(passes + 1) * nChunks) {
             dev_free(dev, slot.workBuf); slot.workBuf = nullptr;
@@ -1266,9 +1296,13 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
     const float* dShadowMvp = (const float*)(dp + offShadow);
     const WorkItem* dWork = slot.workBuf;
     if (n) {   // the frame's tables, on the upload stream too: neither the main nor the shadow stream has to wait for the other
-        expand_chunks_kernel<<<(unsigned)n, 128, 0, dev->upStream>>>(dObjects, (const uint32_t*)(dp + offBase), (const uint32_t*)(dp + offSeq), (const uint32_t*)(dp + offSlot), dShadowMvp,
-                                                                    (uint32_t)n, passes, nChunks, plan.mainTarget, plan.shadowTarget, slot.chunkBuf, slot.chunkObjBuf, slot.workBuf);
-        dev->launches += 1;
+        prepare_draws_kernel<<<(unsigned)((n + 127) / 128), 128, 0, dev->upStream>>>(dObjects, (const uint32_t*)(dp + offSeq), dShadowMvp, (uint32_t)n, passes,
+                                                                                     slot.eyeBuf, slot.chunkObjBuf);
+        if (nChunks)
+            expand_chunks_kernel<<<(nChunks + 127) / 128, 128, 0, dev->upStream>>>(dObjects, (const uint32_t*)(dp + offBase), (const uint32_t*)(dp + offSeq), (const uint32_t*)(dp + offSlot),
+                                                                                   dShadowMvp, slot.eyeBuf, (uint32_t)n, passes, nChunks, plan.mainTarget, plan.shadowTarget,
+                                                                                   slot.chunkBuf, slot.workBuf);
+        dev->launches += 2;
     }
     CK(cudaEventRecord(slot.uploaded, dev->upStream));
     CK(cudaStreamWaitEvent(st, slot.uploaded, 0));
@@ -1335,8 +1369,6 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
             if (p2p) {
                 // peer memory: wait until every peer has cleared its map for this frame, store my rows into all of them, tell
                 // them, and wait for theirs
-                shard_wait_kernel<<<1, 32, 0, ss>>>(dev->myFlags->shadowCleared, peersMask, F1, dev->countersHost + 12, 1u);
-                LAUNCHED("shard_wait_kernel");
                 PeerList maps{}; maps.n = 0;
                 for (int r = 0; r < dev->shardRanks; ++r) if (r != dev->shardRank) maps.p[maps.n++] = dev->peerShadow[r][slotIdx];
                 for (int layer = 0; layer < plan.shadowLayers; ++layer) {
@@ -1344,16 +1376,15 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
                     const int32_t m0 = clampRow(plan.bandShadow[dev->shardRank], lo, hi), m1 = clampRow(plan.bandShadow[dev->shardRank + 1], lo, hi);
                     if (m1 <= m0) continue;
                     const size_t first = (size_t)layer * sn + (size_t)m0 * dev->S, count = (size_t)(m1 - m0) * dev->S;
-                    shard_push_rows_kernel<<<grid_for(count / 4, 256, (unsigned)dev->smCount * 4), 256, 0, ss>>>(dev->shadowBits, maps, first, count);
+                    shard_push_rows_kernel<<<grid_for(count / 4, 256, (unsigned)dev->smCount * 4), 256, 0, ss>>>(dev->shadowBits, maps, first, count,
+                                                                                                                 dev->myFlags->shadowCleared, peersMask, F1, dev->countersHost + 12);
                     LAUNCHED("shard_push_rows_kernel");
                     dev->launches += 1;
                 }
                 PeerList pl{}; pl.n = 0;
                 for (int r = 0; r < dev->shardRanks; ++r) if (r != dev->shardRank) pl.p[pl.n++] = &dev->peerFlags[r]->shadowReady[dev->shardRank];
-                shard_signal_kernel<<<1, 32, 0, ss>>>(pl, F1);
-                LAUNCHED("shard_signal_kernel");
-                shard_wait_kernel<<<1, 32, 0, ss>>>(dev->myFlags->shadowReady, peersMask, F1, dev->countersHost + 12, 2u);
-                LAUNCHED("shard_wait_kernel");
+                shard_signal_wait_kernel<<<1, 32, 0, ss>>>(pl, dev->myFlags->shadowReady, peersMask, F1, dev->countersHost + 12, 2u);
+                LAUNCHED("shard_signal_wait_kernel");
             } else {
                 for (int layer = 0; layer < plan.shadowLayers; ++layer) {
                     uint32_t* base = dev->shadowBits + (size_t)layer * sn;
@@ -1452,9 +1483,8 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
     if (slot.copyPending) CK(cudaStreamWaitEvent(st, slot.copied, 0));      // ... or still being read back (FRAME_OVERLAP frames ago)
     if (p2p && gatherFrame) {
         // the shading kernel stores this rank's rows into rank 0's image as well: wait until rank 0 has released it
-        shard_wait_kernel<<<1, 32, 0, st>>>(&dev->myFlags->gatheredFree, 1u, F1, dev->countersHost + 12, 3u);
-        LAUNCHED("shard_wait_kernel");
         sb.rgba8Peer = dev->rootGathered[slotIdx];
+        sb.peerFree = &dev->myFlags->gatheredFree; sb.peerFreeValue = F1;        // (every CTA of the shading kernel checks it before its first store)
     }
     {
         dim3 grid((sc.sx1 - sc.sx0 + 15) / 16, (sc.sy1 - sc.sy0 + 7) / 8);

@@ -253,6 +253,9 @@ struct FramePlan {
     int32_t activeMain[2] = {0, 0}, activeShadow[2] = {0, 0};   // rows reachable by some draw's bounding sphere
     std::vector<uint32_t> passSlots;    // per pass: geometry warp slots in use (= clusters of the draws taking part)
     std::vector<std::pair<float, uint32_t>> sortScratch;
+    // the last frame planned into this object, per pass: the draws that took part (submission order) and their processing order
+    // (positions into that list) — the next frame's keys are usually in nearly the same order, which an insertion sort finishes in O(n)
+    std::vector<std::vector<uint32_t>> prevCand, prevOrder;
     std::vector<float> sphereScratch;
     int shadowLayers = 0;
     uint32_t totalTris = 0;
@@ -437,12 +440,33 @@ inline std::string plan_frame(const VkrGPUSceneData* scene, const VkrRenderObjec
             if (!(key == key)) key = 0.0f;
             keys.emplace_back(key, (uint32_t)i);
         }
-        // (key, submission index) pairs: the pair order is the stable order; usually already sorted from the draw list's own coherence
-        if (!std::is_sorted(keys.begin(), keys.end())) std::sort(keys.begin(), keys.end());
+        // (key, submission index) pairs: the pair order is the stable order.  The unique sorted order is reached from the previous
+        // frame's order when the same draws take part (an insertion sort, linear for a camera that moves a little), else by std::sort
+        if ((int)plan.prevCand.size() <= p) { plan.prevCand.resize((size_t)p + 1); plan.prevOrder.resize((size_t)p + 1); }
+        std::vector<uint32_t>& pc = plan.prevCand[(size_t)p];
+        std::vector<uint32_t>& po = plan.prevOrder[(size_t)p];
+        bool same = pc.size() == keys.size();
+        for (size_t k = 0; same && k < keys.size(); ++k) same = pc[k] == keys[k].second;
+        if (same) {
+            size_t moves = 0;
+            const size_t budget = 16 * po.size() + 64;          // an order that changed a lot (a cut to another camera) goes to std::sort
+            for (size_t k = 1; k < po.size() && moves <= budget; ++k) {
+                const uint32_t v = po[k];
+                size_t j = k;
+                while (j > 0 && keys[v] < keys[po[j - 1]]) { po[j] = po[j - 1]; --j; ++moves; }
+                po[j] = v;
+            }
+            if (moves > budget) std::sort(po.begin(), po.end(), [&](uint32_t a, uint32_t b) { return keys[a] < keys[b]; });
+        } else {
+            pc.resize(keys.size()); po.resize(keys.size());
+            for (size_t k = 0; k < keys.size(); ++k) { pc[k] = keys[k].second; po[k] = (uint32_t)k; }
+            std::sort(po.begin(), po.end(), [&](uint32_t a, uint32_t b) { return keys[a] < keys[b]; });
+        }
         uint32_t slot = 0;
-        for (const auto& k : keys) {
-            plan.slotBase[(size_t)p * n + k.second] = slot;
-            slot += plan.clusterBase[k.second + 1] - plan.clusterBase[k.second];
+        for (const uint32_t k : po) {
+            const uint32_t obj = keys[k].second;
+            plan.slotBase[(size_t)p * n + obj] = slot;
+            slot += plan.clusterBase[obj + 1] - plan.clusterBase[obj];
         }
         plan.passSlots[p] = slot;
     }

@@ -243,6 +243,7 @@ struct ShadeBuffers {
     uint16_t* hdr;                     // RGBA16F
     uint32_t* rgba8;
     uint32_t* rgba8Peer;               // sharded over peer memory: the presenting rank's image (mapped here), stored to as well; else nullptr
+    const uint32_t* peerFree; uint32_t peerFreeValue;   // ... and the flag (>= value) that says it may be stored to
     const float* srgbLut;              // 256 floats
     // the frame's queue counters (main, shadow, transparent pass; 4 words each, nullptr: pass not run) and their pinned host
     // mirror, which the shading kernel fills through its mapped address: a 16-byte cudaMemcpyAsync on a render stream would

@@ -44,7 +44,17 @@ def host_tensor_from_ptr(ptr: int, nbytes: int) -> torch.Tensor:
 class TileSharder:
     def __init__(self, renderer, rank: int, world: int, cuda: bool, group=None, shard_shadow: bool = True, shadow_group=None):
         """`shadow_group`: a second process group (its own communicator, hence its own NCCL stream) for the shadow
-        exchange, so that frame i+1's shadow bands do not queue behind frame i's image gather."""
+        exchange, so that frame i+1's shadow bands do not queue behind frame i's image gather.
+
+        On CUDA the image gather is issued on torch's CURRENT stream and reads the renderer's presented image through its raw
+        device pointer: it is ordered behind the frame only if the renderer submits on that same stream.  Create the renderer
+        with `stream=torch.cuda.current_stream().cuda_stream` (a non-default stream: handle 0 means "own stream" to vkr_create)
+        and keep that stream current while gathering; anything else is refused here rather than left to race."""
+        if cuda and world > 1:
+            cur = torch.cuda.current_stream().cuda_stream
+            if getattr(renderer, "stream", None) in (None, 0) or renderer.stream != cur:
+                raise ValueError("TileSharder: the renderer must submit on torch's current CUDA stream "
+                                 "(Renderer(..., stream=torch.cuda.current_stream().cuda_stream)); see the class docstring")
         self.r, self.rank, self.world, self.cuda, self.group = renderer, rank, world, cuda, group
         self.shadow_group = shadow_group if shadow_group is not None else group
         self.W, self.H, self.S = renderer.width, renderer.height, renderer.shadow_extent
