@@ -261,7 +261,6 @@ __global__ void __launch_bounds__(128) expand_chunks_kernel(const DObject* __res
 // vertex once, in place, into snapped window coordinates; phase 2 runs the triangles, 32 at a time, on those.
 // PASS: 0 main (visibility buffer), 1 shadow (depth only), 2 transparent (shade + additive blend, no depth write).
 enum { PASS_MAIN = 0, PASS_SHADOW = 1, PASS_TRANSPARENT = 2 };
-static const uint32_t ITEM_CHUNK = 8;          // large-triangle items a warp takes per cursor atomic
 
 // VKR_STAGE_TRIS 1: the whole block (packed triangles + positions) is staged; 0 (default): only the positions, the packed
 // triangles are read from L2 one iteration ahead (1 KB less shared memory per warp: 12 instead of 10 CTAs per SM, and it is
@@ -383,8 +382,6 @@ __device__ __forceinline__ void geometry_warp(const WorkItem* __restrict__ item,
     // works through what was parked: the candidate samples of all the small ones dealt evenly to the lanes (most triangles
     // of a dense mesh cover one or two samples, a few cover dozens: a lane never waits for its neighbour's bounding box),
     // the medium and large ones queued for large_raster_kernel (vkr_raster.cuh, "warp-cooperative handling")
-    unsigned long long mediumBase = 0xFFFFFFFFFFFFFFFFull;      // (first triangle slot | first item slot << 32) of this cluster's room in the queue
-    uint32_t mediumUsed = 0;
     for (uint32_t base = 0; base < nTris; base += 32) {
         const uint32_t t = base + lane;
         int kind = 0;
@@ -425,16 +422,14 @@ __device__ __forceinline__ void geometry_warp(const WorkItem* __restrict__ item,
 #endif
         if ((medium | large) == 0u) { __syncwarp(); continue; }
         if (medium) {
-            // medium triangles (extent < 64 px): one queue item each, no tile enumeration.  The warp claims room for the whole
-            // cluster (CL_TRIS triangles and items) with ONE 64-bit atomic the first time it needs any — thousands of warps adding
-            // to the same two counters every iteration serialise at the L2 (a fifth of this kernel's stall samples on a scene of
-            // 20-pixel triangles) — and pads what it did not use with skip items when it is done with the cluster.
-            if (mediumBase == 0xFFFFFFFFFFFFFFFFull) {
-                unsigned long long b = 0;
-                if (lane == 0) b = atomicAdd(reinterpret_cast<unsigned long long*>(q.counters), (unsigned long long)CL_TRIS | ((unsigned long long)CL_TRIS << 32));
-                mediumBase = __shfl_sync(0xFFFFFFFFu, b, 0);
-            }
-            const uint32_t firstTri = (uint32_t)mediumBase + mediumUsed, firstItem = (uint32_t)(mediumBase >> 32) + mediumUsed;
+            // medium triangles (extent < 64 px): one queue item each, no tile enumeration; the slots of the whole warp are
+            // claimed with ONE 64-bit atomic over the two adjacent counters (triangles | items << 32).  large_raster_kernel
+            // rasterises them with 32-bit edge functions.  (Claiming room for a whole cluster at once and padding the rest with
+            // skip items was measured and lost: profiles/r02_ab.md, "queue room per cluster".)
+            unsigned long long claimed = 0;
+            if (lane == 0) claimed = atomicAdd(reinterpret_cast<unsigned long long*>(q.counters), (unsigned long long)__popc(medium) * 0x100000001ull);
+            claimed = __shfl_sync(0xFFFFFFFFu, claimed, 0);
+            const uint32_t firstTri = (uint32_t)claimed, firstItem = (uint32_t)(claimed >> 32);
             if (kind == 1) {
                 const uint32_t k = (uint32_t)__popc(medium & ((1u << lane) - 1u));
                 const bool fits = firstTri + k < q.triCap && firstItem + k < q.itemCap;
@@ -445,7 +440,6 @@ __device__ __forceinline__ void geometry_warp(const WorkItem* __restrict__ item,
                     q.items[firstItem + k] = it;
                 }
             }
-            mediumUsed += (uint32_t)__popc(medium);
         }
         __syncwarp();
         while (large) {
@@ -454,11 +448,6 @@ __device__ __forceinline__ void geometry_warp(const WorkItem* __restrict__ item,
             enqueue_large_coop(s_park[src].lt, q, lane);
         }
         __syncwarp();
-    }
-    if (mediumBase != 0xFFFFFFFFFFFFFFFFull) {          // the item slots this cluster claimed and did not fill
-        const uint32_t firstItem = (uint32_t)(mediumBase >> 32);
-        for (uint32_t k = mediumUsed + lane; k < (uint32_t)CL_TRIS; k += 32)
-            if (firstItem + k < q.itemCap) { LargeItem it; it.tri = ITEM_SKIP; it.tx = ITEM_WHOLE; it.ty = ITEM_WHOLE; q.items[firstItem + k] = it; }
     }
 }
 
@@ -520,18 +509,17 @@ __global__ void __launch_bounds__(256) large_raster_kernel(const __grid_constant
     const uint32_t nItems = min(q.counters[1], q.itemCap), nTris = min(q.counters[0], q.triCap);
     const uint32_t warpsPerGrid = (gridDim.x * blockDim.x) >> 5;
     const int lane = threadIdx.x & 31;
-    uint32_t nextChunk = 0xFFFFFFFFu;
-    // items differ in cost by orders of magnitude (an alpha-tested tile vs. an opaque sliver): warps take them from a shared
-    // cursor — the first ITEM_CHUNK by the warp's own number (no atomic at all on a short queue: on a frame of small triangles
-    // it is empty)
-    // ... and then ITEM_CHUNK at a time, asked for one chunk ahead: the cursor is one address for 4736 warps, and waiting for
-    // it was 60 % of this kernel's stall samples on a frame with a million items)
-    uint32_t chunk = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * ITEM_CHUNK;
-    for (uint32_t i = chunk; chunk < nItems; ++i) {
-        if (i == chunk + ITEM_CHUNK || i >= nItems) { chunk = __shfl_sync(0xFFFFFFFFu, nextChunk, 0); i = chunk; nextChunk = 0xFFFFFFFFu; if (chunk >= nItems) break; }
-        if (i == chunk && lane == 0) nextChunk = (warpsPerGrid + atomicAdd(&q.counters[4], 1u)) * ITEM_CHUNK;
-        const LargeItem it = q.items[i];
-        if (it.tri >= nTris) continue;                   // a skip marker (room a cluster claimed and did not use, or an overflowed frame)
+    // items differ in cost by orders of magnitude (an alpha-tested tile vs. an opaque sliver): a warp's first item is its own
+    // number, the following ones come from a shared cursor (no atomic at all when the queue is shorter than the grid — on a
+    // frame of small triangles it is empty, and 4736 warps hitting one address cost more than the kernel's work).  Taking the
+    // items in chunks of 8 was measured and lost (profiles/r02_ab.md, "item cursor in chunks": a frame of a few hundred heavy
+    // tile items then runs on an eighth of the warps).
+    for (uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < nItems;) {
+        const uint32_t cur = i;
+        if (lane == 0) i = warpsPerGrid + atomicAdd(&q.counters[4], 1u);
+        i = __shfl_sync(0xFFFFFFFFu, i, 0);
+        const LargeItem it = q.items[cur];
+        if (it.tri >= nTris) continue;                   // skip marker of an overflowed frame (the host grows the queues and redraws)
         const LargeTri lt = q.tris[it.tri];
         const bool whole = it.tx == ITEM_WHOLE;          // medium triangle: its whole bounding box, 32-bit edge functions
         if (SHADOW) {
@@ -564,11 +552,11 @@ __global__ void __launch_bounds__(256) large_transparent_kernel(const __grid_con
     const uint32_t nItems = min(q.counters[1], q.itemCap), nTris = min(q.counters[0], q.triCap);
     const uint32_t warpsPerGrid = (gridDim.x * blockDim.x) >> 5;
     const int lane = threadIdx.x & 31;
-    uint32_t chunk = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * ITEM_CHUNK, nextChunk = 0xFFFFFFFFu;
-    for (uint32_t i = chunk; chunk < nItems; ++i) {
-        if (i == chunk + ITEM_CHUNK || i >= nItems) { chunk = __shfl_sync(0xFFFFFFFFu, nextChunk, 0); i = chunk; nextChunk = 0xFFFFFFFFu; if (chunk >= nItems) break; }
-        if (i == chunk && lane == 0) nextChunk = (warpsPerGrid + atomicAdd(&q.counters[4], 1u)) * ITEM_CHUNK;
-        const LargeItem it = q.items[i];
+    for (uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < nItems;) {
+        const uint32_t cur = i;
+        if (lane == 0) i = warpsPerGrid + atomicAdd(&q.counters[4], 1u);
+        i = __shfl_sync(0xFFFFFFFFu, i, 0);
+        const LargeItem it = q.items[cur];
         if (it.tri >= nTris) continue;
         const LargeTri lt = q.tris[it.tri];
         BlendSink sink{&sc, &sb, lt.seq};
