@@ -304,6 +304,27 @@ size_t vkr_upload_bytes(VkrDevice* dev);
  * test (src/vk_engine_run.cpp:461-480); this one is per 256-triangle cluster and never changes the image. */
 int vkr_cull_stats(VkrDevice* dev, uint32_t out[4]);
 
+/* No counterpart in the reference: added for callers that cannot
+ * call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Packs a width*height RGBA8 image in DEVICE memory (e.g. vkr_device_ptr(VKR_TARGET_RGBA8), 16-byte aligned)
+ * to tightly packed RGB8 and copies it to rgb8Out (host or device memory, >= 3*width*height bytes): the kernel
+ * and the result of vkr_readback(VKR_TARGET_RGB8), but the packed image is staged in a file-scope static
+ * device array of VKR_PACK_STATIC_MAX_BYTES (6 MiB: up to 2 097 152 pixels, 1920x1080 fits) instead of a
+ * cudaMalloc'd buffer.  The call allocates nothing (no cudaMalloc / cudaFree / allocating library routine);
+ * every GPU that loads libvkr.so holds the array until the process exits.
+ *   - a larger image is refused: VKR_ERROR_CAPACITY, vkr_last_error(dev) names the limit;
+ *   - both the kernel and the copy are enqueued on cudaStream (a cudaStream_t of dev's GPU; NULL = the default
+ *     stream), behind whatever the caller ordered there: the caller makes sure the image is complete (vkr_sync,
+ *     or an event wait on that stream).  wait != 0: the call returns after the stream has drained (not under
+ *     capture); wait == 0: the caller synchronises before reading rgb8Out;
+ *   - ALL calls on one GPU share the one array (it keeps the last call's bytes; nothing in it has to start at
+ *     zero, the kernel writes every byte that is copied out): two calls that overlap on the GPU — different
+ *     streams, or two VkrDevice objects on one GPU — race.  Order them on one stream;
+ *   - the first call on a GPU resolves the array's device address (cudaGetSymbolAddress): make it outside capture. */
+#define VKR_PACK_STATIC_MAX_BYTES (6u << 20)
+int vkr_pack_rgb8_static(VkrDevice* dev, const void* rgba8Device, uint32_t width, uint32_t height,
+                         void* rgb8Out, size_t rgb8Bytes, void* cudaStream, int wait);
+
 const char* vkr_last_error(VkrDevice* dev);
 const char* vkr_version(void);
 

@@ -115,12 +115,14 @@ class EngineStats(C.Structure):
     ]
 
 
+PACK_STATIC_MAX_BYTES = 6 << 20     # VKR_PACK_STATIC_MAX_BYTES
+
 # every symbol include/vkr.h declares (tests check the library exports them all)
 VKR_SYMBOLS = [
     "create", "destroy", "upload_mesh", "create_image", "update_bindless_texture", "set_cubemap", "set_cubemap_levels",
     "build_material", "draw", "readback", "readback_async", "sync", "stats", "get_timings",
     "set_flags", "device_ptr", "launch_count", "upload_bytes", "cull_stats", "set_shadow_exchange", "comm_unique_id", "shard_init", "last_error", "version",
-    "readback_band_async", "shard_info",
+    "readback_band_async", "shard_info", "pack_rgb8_static",
 ]
 
 
@@ -223,6 +225,7 @@ class Renderer:
                 "comm_unique_id": ([p, C.c_size_t], C.c_int),
                 "shard_init": ([p, C.c_int, C.c_int, p, C.c_size_t], C.c_int),
                 "version": ([], C.c_char_p),
+                "pack_rgb8_static": ([p, p, C.c_uint32, C.c_uint32, p, C.c_size_t, p, C.c_int], C.c_int),
             })
         if self.prefix == "emu":     # the test-only host emulation (tests/emu) exposes the sharding hooks too
             sigs.update({"set_shadow_exchange": ([p, SHADOW_EXCHANGE_FN, p], C.c_int), "host_ptr": ([p, C.c_int], C.c_void_p)})
@@ -346,6 +349,12 @@ class Renderer:
         p, n = C.c_void_p(), C.c_size_t()
         self._check(self._f("device_ptr")(self.dev, what, C.byref(p), C.byref(n)))
         return p.value, n.value
+
+    def pack_rgb8_static(self, rgba8_ptr: int, width: int, height: int, out: np.ndarray, stream: int = 0, wait: bool = True) -> np.ndarray:
+        """vkr_pack_rgb8_static: the RGBA8 image at DEVICE address rgba8_ptr -> packed RGB8 in `out` (host array), staged in
+        the library's static device array: no allocation (include/vkr.h; PACK_STATIC_MAX_BYTES is the limit)."""
+        self._check(self._f("pack_rgb8_static")(self.dev, rgba8_ptr, width, height, out.ctypes.data, out.nbytes, stream, int(wait)))
+        return out
 
     def launch_count(self) -> int:
         return self._f("launch_count")(self.dev)

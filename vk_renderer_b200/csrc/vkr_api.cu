@@ -1924,3 +1924,51 @@ int vkr_launch_count(VkrDevice* dev) { if (!dev) return 0; (void)drain(dev); ret
 size_t vkr_upload_bytes(VkrDevice* dev) { if (!dev) return 0; (void)drain(dev); return dev->uploadBytes; }
 
 }  // extern "C"
+
+// ======================================================================= allocation-free RGB8 pack (vkr_pack_rgb8_static)
+// No counterpart in the reference: added for callers that cannot call cudaMalloc (CUDA
+// graph capture, tight serving loops, harnesses that forbid it).  It is pack_rgb8_kernel — the kernel behind
+// vkr_readback(VKR_TARGET_RGB8), whose packed image is device scratch memory before it is copied out — with that scratch in a
+// file-scope device array instead of a cudaMalloc'd buffer.  Every GPU that loads the library holds the array until exit.
+//
+// In HOST code `g_packStatic` is only a stand-in for the symbol, not a device address (a kernel handed it would fault, or, where
+// the GPU can reach host memory, quietly use the wrong memory): the address the kernel gets comes from cudaGetSymbolAddress,
+// asked once per device with that device current.
+static __device__ __align__(256) uint32_t g_packStatic[VKR_PACK_STATIC_MAX_BYTES / 4];
+static std::mutex g_packStaticMutex;
+static uint32_t* g_packStaticPtr[64] = {};       // per device ordinal: the device address of g_packStatic on that device
+
+extern "C" int vkr_pack_rgb8_static(VkrDevice* dev, const void* rgba8Device, uint32_t width, uint32_t height, void* rgb8Out, size_t rgb8Bytes,
+                                    void* cudaStream, int wait) {
+    if (!dev) return VKR_ERROR_INVALID_ARGUMENT;
+    if (!rgba8Device || !rgb8Out || width == 0 || height == 0) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_pack_rgb8_static: null or empty argument");
+    if ((reinterpret_cast<uintptr_t>(rgba8Device) & 15u) != 0) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_pack_rgb8_static: the RGBA8 image must be 16-byte aligned");
+    const size_t px = (size_t)width * height, bytes = px * 3;
+    if (bytes > (size_t)VKR_PACK_STATIC_MAX_BYTES) {
+        char msg[192];
+        std::snprintf(msg, sizeof msg, "vkr_pack_rgb8_static: %ux%u needs %zu bytes of scratch, the static array holds %u (VKR_PACK_STATIC_MAX_BYTES); use vkr_readback",
+                      width, height, bytes, (unsigned)VKR_PACK_STATIC_MAX_BYTES);
+        return dev->fail(VKR_ERROR_CAPACITY, msg);
+    }
+    if (rgb8Bytes < bytes) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_pack_rgb8_static: destination too small");
+    if (dev->device < 0 || dev->device >= 64) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_pack_rgb8_static: device ordinal out of range");
+    CK(cudaSetDevice(dev->device));
+    uint32_t* scratch;
+    {
+        std::lock_guard<std::mutex> lock(g_packStaticMutex);
+        if (!g_packStaticPtr[dev->device]) {         // set-up, once per device, that device current
+            void* p = nullptr;
+            const cudaError_t e = cudaGetSymbolAddress(&p, g_packStatic);
+            if (e != cudaSuccess || !p) { cudaGetLastError(); return dev->fail(VKR_ERROR_CUDA, "vkr_pack_rgb8_static: cudaGetSymbolAddress", e); }
+            g_packStaticPtr[dev->device] = static_cast<uint32_t*>(p);
+        }
+        scratch = g_packStaticPtr[dev->device];
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(cudaStream);
+    // (nothing in the array has to start at zero: the kernel writes every one of the 3 * width * height bytes that are copied out)
+    pack_rgb8_kernel<<<(unsigned)(((px >> 2) + 256) / 256), 256, 0, st>>>(static_cast<const uint32_t*>(rgba8Device), scratch, px);
+    LAUNCHED("pack_rgb8_kernel (vkr_pack_rgb8_static)");
+    CK(cudaMemcpyAsync(rgb8Out, scratch, bytes, cudaMemcpyDefault, st));
+    if (wait) CK(cudaStreamSynchronize(st));
+    return VKR_SUCCESS;
+}
