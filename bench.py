@@ -293,6 +293,22 @@ def run_b200(args):
     avg = {k: float(np.mean([g[k] for g in gk])) for k in gk[0]}
     cull = r.cull_stats()
     r.set_flags(BENCH_FLAGS)
+    # ---- where the host's time goes (vkr_host_times): the caller's planning and the submit thread's issue time per frame,
+    # apart from the time either spends waiting (for the other thread, or for the device to free a frame slot).
+    # `host_issue_ms_per_step` above is the wall time of the issuing loop, which a device-bound run holds at the frame time.
+    try:
+        r.host_times(reset=True)
+        for _ in range(max(20, min(args.steps, 100))):
+            step()
+        r.sync()
+        host_us = r.host_times()
+    except AttributeError:                       # an older library variant in an A/B run
+        host_us = dict.fromkeys(("plan", "upload_expand", "shadow", "main_raster", "transparent_shade", "gather", "async_readbacks",
+                                 "caller_waiting_for_submit_thread", "submit_thread_waiting_for_device"), float("nan"))
+    host_busy = {"caller_plan_ms": host_us["plan"] / 1000.0,
+                 "submit_thread_issue_ms": sum(host_us[k] for k in ("upload_expand", "shadow", "main_raster", "transparent_shade", "gather", "async_readbacks")) / 1000.0,
+                 "caller_waiting_ms": host_us["caller_waiting_for_submit_thread"] / 1000.0,
+                 "submit_thread_waiting_for_device_ms": host_us["submit_thread_waiting_for_device"] / 1000.0}
 
     # ---- e2e: host draw list in, RGB8 frame out to pinned host memory, every step (FRAME_OVERLAP=2 pipelining).
     # N = 1: the presented image of every frame.  N > 1: ONE host frame shared by the ranks (a /dev/shm segment every process maps
@@ -440,7 +456,7 @@ def run_b200(args):
                          "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "algorithmic_bytes": gk_bytes, "algorithmic_basis": gk_basis, "kernel_ms": gk_ms,
                          "peak_source": peak_src},
             "pass_ms": avg, "pass_ms_last_pipelined_frame": {k: float(v) for k, v in tm.items()},
-            "host_issue_ms_per_step": host_issue_ms, "host_vkr_draw_call_ms": float(np.median(host_call)),
+            "host_issue_ms_per_step": host_issue_ms, "host_vkr_draw_call_ms": float(np.median(host_call)), "host_busy_ms_per_step": host_busy,
             "cluster_culling": cull, "per_rank_pass_ms_last_pipelined_frame": per_rank,
             "e2e": {"value": args.steps / e2e_s, "unit": "frames/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                     "d2h_bytes_per_step_rank0": int((my_rows[1] - my_rows[0]) * W * 3),

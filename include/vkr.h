@@ -288,6 +288,11 @@ int vkr_sync(VkrDevice* dev);
 /* stats.triangle_count / drawcall_count — src/vk_engine_run.cpp:70-71,309-310. */
 int vkr_stats(VkrDevice* dev, VkrEngineStats* out);
 int vkr_get_timings(VkrDevice* dev, float* msOut, int count);      /* last synced frame */
+/* Mean HOST time per frame (microseconds) of vkr_draw since the last reset: usOut[0] planning on the caller's thread,
+ * [1..6] the submit thread's issue time (upload + expand, shadow, main raster, transparent + shading, gather, queued
+ * read-backs), [7] caller waiting for the submit thread, [8] submit thread waiting for the device.  reset != 0 starts a
+ * new measurement (frames before the 16th of a device are never counted: allocation and NCCL warm-up). */
+int vkr_host_times(VkrDevice* dev, float* usOut, int count, int reset);
 int vkr_set_flags(VkrDevice* dev, uint32_t flags);                 /* VKR_CONFIG_* at run time (takes effect at the next vkr_draw) */
 
 /* Raw device pointer of a target of the last drawn frame (for NCCL gathers). */
@@ -301,7 +306,7 @@ size_t vkr_upload_bytes(VkrDevice* dev);
 /* Cluster culling of the last synced frame: out = {main-pass clusters, of which dropped before any vertex
  * work (outside the frustum, no pixel centre, or hidden by nearer geometry already drawn), shadow-pass
  * clusters (last layer), of which dropped}.  The reference's counterpart is the per-object is_visible
- * test (src/vk_engine_run.cpp:461-480); this one is per 256-triangle cluster and never changes the image. */
+ * test (src/vk_engine_run.cpp:461-480); this one is per 128-triangle cluster and never changes the image. */
 int vkr_cull_stats(VkrDevice* dev, uint32_t out[4]);
 
 /* No counterpart in the reference: added for callers that cannot

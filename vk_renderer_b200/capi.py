@@ -122,7 +122,7 @@ VKR_SYMBOLS = [
     "create", "destroy", "upload_mesh", "create_image", "update_bindless_texture", "set_cubemap", "set_cubemap_levels",
     "build_material", "draw", "readback", "readback_async", "sync", "stats", "get_timings",
     "set_flags", "device_ptr", "launch_count", "upload_bytes", "cull_stats", "set_shadow_exchange", "comm_unique_id", "shard_init", "last_error", "version",
-    "readback_band_async", "shard_info", "pack_rgb8_static",
+    "readback_band_async", "shard_info", "pack_rgb8_static", "host_times",
 ]
 
 
@@ -225,12 +225,18 @@ class Renderer:
                 "comm_unique_id": ([p, C.c_size_t], C.c_int),
                 "shard_init": ([p, C.c_int, C.c_int, p, C.c_size_t], C.c_int),
                 "version": ([], C.c_char_p),
+                "host_times": ([p, C.POINTER(C.c_float), C.c_int, C.c_int], C.c_int),
                 "pack_rgb8_static": ([p, p, C.c_uint32, C.c_uint32, p, C.c_size_t, p, C.c_int], C.c_int),
             })
         if self.prefix == "emu":     # the test-only host emulation (tests/emu) exposes the sharding hooks too
             sigs.update({"set_shadow_exchange": ([p, SHADOW_EXCHANGE_FN, p], C.c_int), "host_ptr": ([p, C.c_int], C.c_void_p)})
         for name, (args, res) in sigs.items():
-            fn = self._f(name)
+            try:
+                fn = self._f(name)
+            except AttributeError:
+                if name in ("host_times", "pack_rgb8_static"):      # an older library variant in an A/B run (tools/run_ab.sh)
+                    continue
+                raise
             fn.argtypes, fn.restype = args, res
 
     def _check(self, rc):
@@ -355,6 +361,14 @@ class Renderer:
         the library's static device array: no allocation (include/vkr.h; PACK_STATIC_MAX_BYTES is the limit)."""
         self._check(self._f("pack_rgb8_static")(self.dev, rgba8_ptr, width, height, out.ctypes.data, out.nbytes, stream, int(wait)))
         return out
+
+    def host_times(self, reset: bool = False) -> dict:
+        """Mean host microseconds per frame of vkr_draw's sections since the last reset (vkr_host_times)."""
+        out = (C.c_float * 9)()
+        self._check(self._f("host_times")(self.dev, out, 9, int(reset)))
+        names = ("plan", "upload_expand", "shadow", "main_raster", "transparent_shade", "gather", "async_readbacks",
+                 "caller_waiting_for_submit_thread", "submit_thread_waiting_for_device")
+        return {k: float(v) for k, v in zip(names, out)}
 
     def launch_count(self) -> int:
         return self._f("launch_count")(self.dev)

@@ -407,20 +407,26 @@ __device__ __forceinline__ void geometry_warp(const WorkItem* __restrict__ item,
                                              makeSink(seq), s_park[lane], count);
             if (kind != 3) count = 0;
         }
-        // inclusive prefix sum of the candidate counts
-        uint32_t incl = count;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) { const uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= d) incl += v; }
-        const uint32_t total = __shfl_sync(0xFFFFFFFFu, incl, 31);
         const uint32_t medium = __ballot_sync(0xFFFFFFFFu, kind == 1);
         uint32_t large = __ballot_sync(0xFFFFFFFFu, kind == 2);
-        __syncwarp();
 #if defined(VKR_RASTER_CANDIDATES)
-        if (total) raster_candidates_warp(s_park, ws->map, incl - count, count, seqOfLane, total, lane, makeSink);
+        __syncwarp();
+        {   // inclusive prefix sum of the candidate counts
+            uint32_t incl = count;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) { const uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= d) incl += v; }
+            const uint32_t total = __shfl_sync(0xFFFFFFFFu, incl, 31);
+            if (total) raster_candidates_warp(s_park, ws->map, incl - count, count, seqOfLane, total, lane, makeSink);
+        }
 #else
-        (void)total; (void)seqOfLane;
+        (void)count; (void)seqOfLane;
 #endif
+#if defined(VKR_RASTER_CANDIDATES)
         if ((medium | large) == 0u) { __syncwarp(); continue; }
+#else
+        if ((medium | large) == 0u) continue;        // (nobody reads a parked slot: nothing to order)
+        __syncwarp();                                // the parked triangles are visible to the whole warp
+#endif
         if (medium) {
             // medium triangles (extent < 64 px): one queue item each, no tile enumeration; the slots of the whole warp are
             // claimed with ONE 64-bit atomic over the two adjacent counters (triangles | items << 32).  large_raster_kernel
@@ -502,43 +508,77 @@ __global__ void __launch_bounds__(CL_TRIS) geometry_cutout_kernel(const DObject*
 }
 
 // ---- large triangles: one warp per (triangle, 64x64 tile) item, grid-stride over the queue
+#ifndef VKR_LARGE_MIN_CTAS
+#define VKR_LARGE_MIN_CTAS 1
+#endif
+#ifndef VKR_ITEM_CHUNK_MAX
+#define VKR_ITEM_CHUNK_MAX 4u      // items a warp of large_raster_kernel takes per trip to the cursor (at most 32)
+#endif
 template <bool SHADOW>
-__global__ void __launch_bounds__(256) large_raster_kernel(const __grid_constant__ RasterTarget rt, const __grid_constant__ Queues q,
+__global__ void __launch_bounds__(256, VKR_LARGE_MIN_CTAS) large_raster_kernel(const __grid_constant__ RasterTarget rt, const __grid_constant__ Queues q,
                                                            const __grid_constant__ AlphaCtx ax, int anyCutout) {
     __shared__ uint32_t s_queue[SHADOW ? 1 : 8][SHADOW ? 1 : RECT_QUEUE];      // cut-out items: compaction queue per warp
     const uint32_t nItems = min(q.counters[1], q.itemCap), nTris = min(q.counters[0], q.triCap);
     const uint32_t warpsPerGrid = (gridDim.x * blockDim.x) >> 5;
     const int lane = threadIdx.x & 31;
-    // items differ in cost by orders of magnitude (an alpha-tested tile vs. an opaque sliver): a warp's first item is its own
-    // number, the following ones come from a shared cursor (no atomic at all when the queue is shorter than the grid — on a
-    // frame of small triangles it is empty, and 4736 warps hitting one address cost more than the kernel's work).  Taking the
-    // items in chunks of 8 was measured and lost (profiles/r02_ab.md, "item cursor in chunks": a frame of a few hundred heavy
-    // tile items then runs on an eighth of the warps).
-    for (uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < nItems;) {
-        const uint32_t cur = i;
-        if (lane == 0) i = warpsPerGrid + atomicAdd(&q.counters[4], 1u);
-        i = __shfl_sync(0xFFFFFFFFu, i, 0);
-        const LargeItem it = q.items[cur];
-        if (it.tri >= nTris) continue;                   // skip marker of an overflowed frame (the host grows the queues and redraws)
-        const LargeTri lt = q.tris[it.tri];
-        const bool whole = it.tx == ITEM_WHOLE;          // medium triangle: its whole bounding box, 32-bit edge functions
-        if (SHADOW) {
-            DepthSink sink{rt.depthBits, rt.width};
-            if (whole) raster_medium_coop(lt, sink, lane);
-            else raster_item(lt, it, sink, lane, 32);
-        } else {
-            VisSink sink{rt.vis, rt.width, 0xFFFFFFFEu - lt.seq};
-            if (anyCutout && (ax.objects[ax.chunkObj[lt.seq >> 8].x].flags & 2u)) {
-                const uint2 co = ax.chunkObj[lt.seq >> 8];
-                const DObject& o = ax.objects[co.x];
-                const uint32_t tri = co.y + (lt.seq & 255u);
-                AlphaTri at;
-                make_alpha_tri(o, o.mvp, o.idx[3 * tri], o.idx[3 * tri + 1], o.idx[3 * tri + 2], ax, rt, at);
-                CutoutSink<VisSink> cs{sink, &at};
-                raster_item_compact(lt, it, cs, lane, s_queue[SHADOW ? 0 : (threadIdx.x >> 5)]);
-            } else if (whole) raster_medium_coop(lt, sink, lane);
-            else raster_item(lt, it, sink, lane, 32);
+    // Items differ in cost by orders of magnitude (an alpha-tested tile vs. an opaque sliver), so warps take them from a shared
+    // cursor — but an item is also two DEPENDENT loads away (item -> triangle record), about a microsecond at this kernel's
+    // occupancy, and a medium triangle's raster work is shorter than that: with one item per trip a frame with a million of
+    // them (config 3) ran at the latency of those loads, 60 % of its stall samples on the cursor atomic in front of them.
+    // A warp therefore takes `cs` consecutive items per trip — cs = 1 when there are fewer than 4 items per warp (a few hundred
+    // heavy tile items must spread over all warps: a fixed chunk of 8 cost config 1 two thirds of its frame rate), up to
+    // VKR_ITEM_CHUNK_MAX = 4 (config 3, frames/s: 1 -> 691, 4 -> 718, 32 -> 661: long chunks of heavy cut-out items make a tail)
+    // — its lanes fetch the chunk's items and triangle records side by side into shared memory, and the cursor is asked for
+    // the next chunk while this one is rasterised.  No atomic at all when the queue is shorter than the grid.
+    // profiles/r02_ab.md, "item cursor".
+    __shared__ LargeItem s_item[8][VKR_ITEM_CHUNK_MAX];
+    __shared__ uint4 s_tri[8][VKR_ITEM_CHUNK_MAX][3];
+    static_assert(sizeof(LargeTri) == 48, "three 16-byte loads per triangle record");
+    const int wslot = threadIdx.x >> 5;
+    const uint32_t cs = min((uint32_t)VKR_ITEM_CHUNK_MAX, max(1u, nItems / (warpsPerGrid * 4u)));
+    uint32_t chunk = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * cs, nextChunk = 0xFFFFFFFFu;
+    while (chunk < nItems) {
+        if (lane == 0) nextChunk = (warpsPerGrid + atomicAdd(&q.counters[4], 1u)) * cs;
+        const uint32_t n = min(cs, nItems - chunk);
+        if ((uint32_t)lane < n) {
+            LargeItem mine = q.items[chunk + lane];
+            if (mine.tri >= nTris) mine.tri = ITEM_SKIP;     // a skip marker of an overflowed frame (the host grows the queues and redraws)
+            else {
+                const uint4* src = reinterpret_cast<const uint4*>(q.tris + mine.tri);
+                s_tri[wslot][lane][0] = src[0]; s_tri[wslot][lane][1] = src[1]; s_tri[wslot][lane][2] = src[2];
+            }
+            s_item[wslot][lane] = mine;
         }
+        __syncwarp();
+        for (uint32_t k = 0; k < n; ++k) {
+            const LargeItem it = s_item[wslot][k];
+            if (it.tri == ITEM_SKIP) continue;
+            LargeTri lt;
+            {
+                uint4* dst = reinterpret_cast<uint4*>(&lt);
+                dst[0] = s_tri[wslot][k][0]; dst[1] = s_tri[wslot][k][1]; dst[2] = s_tri[wslot][k][2];
+            }
+            const bool whole = it.tx == ITEM_WHOLE;          // medium triangle: its whole bounding box, 32-bit edge functions
+            if (SHADOW) {
+                DepthSink sink{rt.depthBits, rt.width};
+                if (whole) raster_medium_coop(lt, sink, lane);
+                else raster_item(lt, it, sink, lane, 32);
+            } else {
+                VisSink sink{rt.vis, rt.width, 0xFFFFFFFEu - lt.seq};
+                if (anyCutout && (ax.objects[ax.chunkObj[lt.seq >> 8].x].flags & 2u)) {
+                    const uint2 co = ax.chunkObj[lt.seq >> 8];
+                    const DObject& o = ax.objects[co.x];
+                    const uint32_t tri = co.y + (lt.seq & 255u);
+                    AlphaTri at;
+                    make_alpha_tri(o, o.mvp, o.idx[3 * tri], o.idx[3 * tri + 1], o.idx[3 * tri + 2], ax, rt, at);
+                    CutoutSink<VisSink> cs2{sink, &at};
+                    raster_item_compact(lt, it, cs2, lane, s_queue[SHADOW ? 0 : wslot]);
+                } else if (whole) raster_medium_coop(lt, sink, lane);
+                else raster_item(lt, it, sink, lane, 32);
+            }
+        }
+        __syncwarp();                                        // the chunk's slots are free again
+        chunk = __shfl_sync(0xFFFFFFFFu, nextChunk, 0);
     }
 }
 __global__ void __launch_bounds__(256) large_transparent_kernel(const __grid_constant__ RasterTarget rt, const __grid_constant__ Queues q,
@@ -565,18 +605,27 @@ __global__ void __launch_bounds__(256) large_transparent_kernel(const __grid_con
 }
 
 // ---- shade + resolve: one thread per pixel of the scissor rectangle; a CTA is a 16x8 pixel block,
-// each warp an 8x4 footprint (triangle / texel / shadow-map locality).  The sRGB decode table
-// lives in shared memory.
+// each warp an 8x4 footprint (triangle / texel / shadow-map locality).  The sRGB decode table is read
+// through L1 (see below).
 __global__ void __launch_bounds__(128, VKR_SHADE_MIN_CTAS) shade_kernel(const __grid_constant__ ShadeConst sc, const __grid_constant__ ShadeBuffers sbIn) {
+#if defined(VKR_SHADE_LUT_SHARED)
     __shared__ float s_lut[256];
     s_lut[threadIdx.x] = sbIn.srgbLut[threadIdx.x];
     s_lut[threadIdx.x + 128] = sbIn.srgbLut[threadIdx.x + 128];
+#endif
     // sharded over peer memory: rank 0 must have released the image this frame's pixels are also stored into (nothing on this
     // GPU stands between rank 0 and that release)
     if (threadIdx.x == 0 && sbIn.peerFree != nullptr) spin_until(sbIn.peerFree, sbIn.peerFreeValue, sbIn.countersHost + 12, 3u);
+#if !defined(VKR_SHADE_LUT_SHARED)
+    // the sRGB decode table (1 KB) is read from global memory and lives in L1: staging it in shared memory cost every 128-pixel
+    // CTA 256 loads, 256 stores and a barrier, +2.8 % frame rate without (profiles/r02_ab.md, "decode table")
+    if (sbIn.peerFree != nullptr) __syncthreads();
+    const ShadeBuffers& sb = sbIn;
+#else
     __syncthreads();
     ShadeBuffers sb = sbIn;
     sb.srgbLut = s_lut;
+#endif
     if ((blockIdx.x | blockIdx.y) == 0 && threadIdx.x < 12 && sbIn.countersHost != nullptr) {
         // every raster pass of the frame has ended (stream order / the shadow join): publish their counters to the host
         const uint32_t* c = sbIn.counters[threadIdx.x >> 2];
@@ -857,6 +906,17 @@ int vkr_create(const VkrConfig* cfg, VkrDevice** out) {
         ALLOC(dev->q.tris, sizeof(LargeTri) * dev->q.triCap);
         ALLOC(dev->q.items, sizeof(LargeItem) * dev->q.itemCap);
         ALLOC(dev->q.counters, 32);          // [0..3] see Queues; [4] work cursor of the large-triangle kernels
+#if defined(VKR_BIN_PROBE)
+        {   // A/B probe only (vkr_raster.cuh): bins for the append half of a tile-binned rasteriser
+            const size_t tiles = (size_t)((dev->W + 63) / 64) * ((dev->H + 63) / 64);
+            uint4* pool = nullptr; uint32_t* cnt = nullptr;
+            ALLOC(pool, tiles * VKR_BIN_CAP * 48);
+            ALLOC(cnt, tiles * 4);
+            CK(cudaMemset(cnt, 0, tiles * 4));
+            CK(cudaMemcpyToSymbol(g_binPool, &pool, sizeof pool));
+            CK(cudaMemcpyToSymbol(g_binCount, &cnt, sizeof cnt));
+        }
+#endif
         ALLOC(dev->qShadow.tris, sizeof(LargeTri) * dev->qShadow.triCap);
         ALLOC(dev->qShadow.items, sizeof(LargeItem) * dev->qShadow.itemCap);
         ALLOC(dev->qShadow.counters, 32 * VKR_FRAME_OVERLAP);     // per frame in flight: frame i+1's shadow pass runs beside frame i's shading, which publishes frame i's
@@ -1783,6 +1843,23 @@ int vkr_get_timings(VkrDevice* dev, float* msOut, int count) {
     if (!dev || !msOut || count < 0) return VKR_ERROR_INVALID_ARGUMENT;
     DRAIN(dev);
     for (int i = 0; i < count && i < VKR_T_COUNT; ++i) msOut[i] = dev->timings[i];
+    return VKR_SUCCESS;
+}
+
+// Mean host time per frame (microseconds) of vkr_draw's sections since the last reset: [0] plan_frame on the caller's
+// thread, [1] upload + expand, [2] shadow pass (+ exchange), [3] main raster, [4] transparent + shading, [5] gather,
+// [6] asynchronous read-backs, [7] caller waiting for the submit thread, [8] submit thread waiting for the device (pinned
+// buffer reuse).  [1..6] are the submit thread's issue time.  reset != 0 starts a new measurement (and switches it on).
+int vkr_host_times(VkrDevice* dev, float* usOut, int count, int reset) {
+    if (!dev || (count > 0 && !usOut) || count < 0) return VKR_ERROR_INVALID_ARGUMENT;
+    DRAIN(dev);
+    const double f = dev->hostProfFrames ? 1.0 / (double)dev->hostProfFrames : 0.0;
+    for (int i = 0; i < count && i < 9; ++i) usOut[i] = (float)(dev->hostProfUs[i] * f);
+    if (reset) {
+        for (double& v : dev->hostProfUs) v = 0.0;
+        dev->hostProfFrames = 0;
+        dev->hostProf = true;
+    }
     return VKR_SUCCESS;
 }
 

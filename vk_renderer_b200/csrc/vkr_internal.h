@@ -31,7 +31,14 @@ static const uint32_t VIS_EMPTY_LO = 0xFFFFFFFFu;
 static const uint32_t DEPTH_ONE_BITS = 0x3F800000u;
 
 static const int TILE = 64;                // large-triangle tile edge in pixels
-static const int SMALL_MAX = 16;           // in-thread raster when bbox is <= SMALL_MAX x SMALL_MAX
+// In-thread raster when the bounding box is <= SMALL_MAX x SMALL_MAX samples; bigger triangles go to large_raster_kernel, where
+// a whole warp works on one.  Measured (profiles/r02_ab.md, "in-lane threshold"; frames/s of configs 1 / 2 / 3 / 4):
+// 16 -> 7447 / 6360 / 714 / 2492, 12 -> 7230 / 6646 / 697, 10 -> 7597 / 6874 / 685 / 2496, 8 -> 8081 / 7244 / 681 / 2489,
+// 6 -> 8580 / 7160 / 555: a lane alone on a 16 x 16 box holds its 31 neighbours for 256 iterations.
+#ifndef VKR_SMALL_MAX
+#define VKR_SMALL_MAX 8
+#endif
+static const int SMALL_MAX = VKR_SMALL_MAX;
 static const int CUTOUT_SMALL_MAX = 4;     // ... for alpha-tested triangles (each fragment costs a texture evaluation)
 static const int CL_TRIS = 128;            // a cluster (one warp's unit of work) holds at most this many triangles ...
 static const int CL_VERTS = 128;           // ... and this many distinct vertices (7-bit local ids, 2 KB of shared memory)

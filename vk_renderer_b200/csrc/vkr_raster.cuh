@@ -563,6 +563,11 @@ VKR_HD void cluster_triangle(const CachedVtx& a, const CachedVtx& b, const Cache
 }
 
 #if defined(__CUDACC__)
+#if defined(VKR_BIN_PROBE)
+static const uint32_t VKR_BIN_CAP = 16384u;          // records per tile bin (the probe wraps around: nothing reads the bins)
+__device__ uint4* g_binPool = nullptr;
+__device__ uint32_t* g_binCount = nullptr;
+#endif
 // ---- warp-cooperative handling: candidates of small triangles dealt to the lanes; triangles too big for that ------------
 // cluster_triangle_deferred sets one triangle up and says who rasterises it: 0 nobody (culled, or clipped and emitted on the
 // spot), 1 medium (extent < 64 px: the warp queues it as one item for large_raster_kernel's 32-bit path), 2 large (the warp
@@ -588,6 +593,19 @@ __device__ __forceinline__ int cluster_triangle_deferred(const CachedVtx& a, con
     const SnapVtx v0{a.X, a.Y, bits2f(a.zbits)}, v1{b.X, b.Y, bits2f(b.zbits)}, v2{c.X, c.Y, bits2f(c.zbits)};
     if (!setup_snapped(v0, v1, v2, rt, t)) return 0;
     const int32_t w = t.bx1 - t.bx0 + 1, h = t.by1 - t.by0 + 1;
+#if defined(VKR_BIN_PROBE)
+    // A/B probe (profiles/r02_ab.md, "tile bins"): what the APPEND half of a tile-binned rasteriser would add to this kernel — the
+    // set-up triangle (48 B) stored into the bin of the 64x64 tile of its first corner, its slot taken from that tile's counter.
+    // Nothing reads the bins: the image is unchanged, only the cost of writing them is measured.
+    if (g_binPool != nullptr) {
+        const uint32_t tile = (uint32_t)(t.by0 >> 6) * (uint32_t)((rt.width + 63) >> 6) + (uint32_t)(t.bx0 >> 6);
+        const uint32_t slot = atomicAdd(g_binCount + tile, 1u) & (VKR_BIN_CAP - 1u);
+        uint4* rec = g_binPool + ((size_t)tile * VKR_BIN_CAP + slot) * 3u;
+        rec[0] = make_uint4((uint32_t)t.X[0], (uint32_t)t.X[1], (uint32_t)t.X[2], (uint32_t)t.Y[0]);
+        rec[1] = make_uint4((uint32_t)t.Y[1], (uint32_t)t.Y[2], f2bits(t.z0), f2bits(t.dzdx));
+        rec[2] = make_uint4(f2bits(t.dzdy), (uint32_t)t.bx0 | ((uint32_t)t.by0 << 16), (uint32_t)t.bx1 | ((uint32_t)t.by1 << 16), seq);
+    }
+#endif
 #if defined(VKR_RASTER_CANDIDATES)
     if (w <= SMALL_MAX && h <= SMALL_MAX && t.ext < 16384) { count = make_frag_rec(t, out.rec); return 3; }
 #else
