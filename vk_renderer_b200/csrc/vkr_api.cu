@@ -268,23 +268,26 @@ enum { PASS_MAIN = 0, PASS_SHADOW = 1, PASS_TRANSPARENT = 2 };
 #ifndef VKR_STAGE_TRIS
 #define VKR_STAGE_TRIS 0
 #endif
-struct alignas(16) WarpSmem {              // one warp's slice of shared memory: one base register, constant offsets
+template <int WARPS>
+struct alignas(16) GeomSmem {              // the shared memory of one cluster's warp (WARPS = 1) or CTA (WARPS = 4): one base register, constant offsets
 #if VKR_STAGE_TRIS
     uint2 tris[CL_TRIS];                   // bulk-copy destination, part 1 ...
 #endif
     uint4 vtx[CL_VERTS];                   // ... part 2: positions, overwritten in place by the transformed vertices (CachedVtx)
-    ParkedTri park[32];
+    ParkedTri park[32 * WARPS];
 #if defined(VKR_RASTER_CANDIDATES)
     uint2 map[32];
 #endif
     float mvp[16];
-    unsigned long long bar;                // the warp's mbarrier
+    unsigned long long bar;                // the mbarrier of the bulk copy
     unsigned long long pad;
 };
+typedef GeomSmem<1> WarpSmem;
 static_assert(sizeof(WarpSmem) % 16 == 0 && offsetof(WarpSmem, vtx) % 16 == 0, "bulk copies land on 16-byte boundaries");
 
 __device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void bulk_load_start(WarpSmem* ws, const void* src, uint32_t bytes) {      // one lane
+template <int WARPS>
+__device__ __forceinline__ void bulk_load_start(GeomSmem<WARPS>* ws, const void* src, uint32_t bytes) {      // one lane
 #if VKR_STAGE_TRIS
     const uint32_t bar = smem_addr(&ws->bar), dst = smem_addr(ws->tris);
 #else
@@ -296,7 +299,8 @@ __device__ __forceinline__ void bulk_load_start(WarpSmem* ws, const void* src, u
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src), "r"(bytes), "r"(bar)
                  : "memory");
 }
-__device__ __forceinline__ bool bulk_load_wait(WarpSmem* ws) {           // every lane; false: gave up (never seen; keeps a fault from hanging the device)
+template <int WARPS>
+__device__ __forceinline__ bool bulk_load_wait(GeomSmem<WARPS>* ws) {           // every lane; false: gave up (never seen; keeps a fault from hanging the device)
     const uint32_t bar = smem_addr(&ws->bar);
     for (int spin = 0; spin < (1 << 24); ++spin) {
         uint32_t done;
@@ -306,27 +310,34 @@ __device__ __forceinline__ bool bulk_load_wait(WarpSmem* ws) {           // ever
     return false;
 }
 
-template <int PASS, class MakeSink>
+// WARPS = 1: the warp owns the cluster (the throughput form: no barrier between clusters).  WARPS = 4: the four warps of a CTA
+// share one cluster — a quarter of the vertices, one 32-triangle iteration and every fourth occlusion footprint each, two
+// CTA barriers — which cuts the LATENCY of a cluster to a third: the form for frames with fewer clusters than the GPU has
+// warp slots (a rank's band of a sharded frame), where the kernel's duration is the duration of its slowest cluster.
+template <int WARPS> __device__ __forceinline__ void geom_sync() { if (WARPS == 1) __syncwarp(); else __syncthreads(); }
+template <int PASS, int WARPS, class MakeSink>
 __device__ __forceinline__ void geometry_warp(const WorkItem* __restrict__ item, const float* __restrict__ mvps, uint32_t mvpStride,
-                                              const RasterTarget& rt, const Queues& q, WarpSmem* ws, const MakeSink& makeSink) {
+                                              const RasterTarget& rt, const Queues& q, GeomSmem<WARPS>* ws, const MakeSink& makeSink) {
     const int lane = threadIdx.x & 31;
+    const int wi = WARPS == 1 ? 0 : (int)(threadIdx.x >> 5);          // this warp's number among the cluster's warps
+    const int tid = WARPS == 1 ? lane : (int)threadIdx.x;             // this thread's number among the cluster's threads
     const uint4 w0 = __ldg(reinterpret_cast<const uint4*>(item)), w1 = __ldg(reinterpret_cast<const uint4*>(item) + 1);
     const uint32_t info = w1.x, flags = (info >> 16) & 0xFFu;
     const int32_t verdict = (int32_t)(info >> 24);
     if (PASS == PASS_MAIN && (flags & 2u)) return;     // alpha-tested draw: geometry_cutout_kernel owns this cluster
-    if (verdict == CLUSTER_CULLED) { if (lane == 0) atomicAdd(q.counters + 3, 1u); return; }
+    if (verdict == CLUSTER_CULLED) { if (tid == 0) atomicAdd(q.counters + 3, 1u); return; }
     const uint4* __restrict__ blob = reinterpret_cast<const uint4*>(((uint64_t)w0.y << 32) | w0.x);
     const uint32_t obj = w0.z, seqBase = w0.w;
     const uint32_t nVerts = info & 0xFFu, nTris = (info >> 8) & 0xFFu;
 #if VKR_STAGE_TRIS
-    if (lane == 0) bulk_load_start(ws, blob, CL_BLOB_TRI_BYTES + nVerts * 16u);
+    if (tid == 0) bulk_load_start(ws, blob, CL_BLOB_TRI_BYTES + nVerts * 16u);
 #else
-    if (lane == 0) bulk_load_start(ws, blob + CL_BLOB_TRI_BYTES / 16u, nVerts * 16u);
+    if (tid == 0) bulk_load_start(ws, blob + CL_BLOB_TRI_BYTES / 16u, nVerts * 16u);
     const uint2* __restrict__ gtris = reinterpret_cast<const uint2*>(blob);
-    uint2 tpNext = lane < (int)nTris ? __ldg(gtris + lane) : make_uint2(0u, 0u);      // the first iteration's triangles, in flight during the cull
+    uint2 tpNext = (uint32_t)(wi * 32 + lane) < nTris ? __ldg(gtris + wi * 32 + lane) : make_uint2(0u, 0u);      // the first iteration's triangles, in flight during the cull
 #endif
-    if (lane < 16) ws->mvp[lane] = __ldg(mvps + (size_t)obj * mvpStride + lane);
-    __syncwarp();
+    if (tid < 16) ws->mvp[tid] = __ldg(mvps + (size_t)obj * mvpStride + tid);
+    geom_sync<WARPS>();
     const float* mvp = ws->mvp;
 
     // ---- phase 0: the occlusion test against the LIVE depth / visibility buffer (the box test — frustum planes, pixel
@@ -338,6 +349,51 @@ __device__ __forceinline__ void geometry_warp(const WorkItem* __restrict__ item,
         // at the first footprint with a visible pixel
         bool hidden = true;
         const int32_t lx = lane & 7, ly = lane >> 3;
+        if (WARPS > 1) {
+            // the footprints dealt to the warps (warp w takes every WARPS-th), a warp stops at its first visible pixel
+            const int32_t fw = (rx1 - rx0 + 8) >> 3, fh = (ry1 - ry0 + 16) >> 4;
+            for (int32_t f = wi; f < fw * fh && hidden; f += WARPS) {
+                const int32_t fy = f / fw, bx = rx0 + (f - fy * fw) * 8, by = ry0 + fy * 16;
+                const int32_t px = bx + lx;
+                uint32_t stored[4];
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const int32_t py = by + ly + 4 * k;
+                    stored[k] = 0u;
+                    if (px <= rx1 && py <= ry1) {
+                        const uint32_t pix = (uint32_t)(py * rt.width + px);
+                        if (PASS == PASS_SHADOW) stored[k] = __ldcg(rt.depthBits + pix);
+                        else stored[k] = __ldcg(reinterpret_cast<const uint32_t*>(rt.vis + pix) + 1);
+                    }
+                }
+                const bool h = depth_hides(stored[0], zminBits) && depth_hides(stored[1], zminBits) &&
+                               depth_hides(stored[2], zminBits) && depth_hides(stored[3], zminBits);
+                hidden = __all_sync(0xFFFFFFFFu, h);
+            }
+            hidden = __syncthreads_and(hidden ? 1 : 0) != 0;
+        } else
+#if defined(VKR_OCC_WIDE)
+        // A/B: 16x16 footprints (eight independent loads per lane in flight): half the dependent round trips of a culled cluster
+        for (int32_t by = ry0; by <= ry1 && hidden; by += 16) {
+            for (int32_t bx = rx0; bx <= rx1 && hidden; bx += 16) {
+                uint32_t stored[8];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    const int32_t px = bx + lx + 8 * (k >> 2), py = by + ly + 4 * (k & 3);
+                    stored[k] = 0u;
+                    if (px <= rx1 && py <= ry1) {
+                        const uint32_t pix = (uint32_t)(py * rt.width + px);
+                        if (PASS == PASS_SHADOW) stored[k] = __ldcg(rt.depthBits + pix);
+                        else stored[k] = __ldcg(reinterpret_cast<const uint32_t*>(rt.vis + pix) + 1);
+                    }
+                }
+                bool h = true;
+#pragma unroll
+                for (int k = 0; k < 8; ++k) h = h && depth_hides(stored[k], zminBits);
+                hidden = __all_sync(0xFFFFFFFFu, h);
+            }
+        }
+#else
         for (int32_t by = ry0; by <= ry1 && hidden; by += 16) {
             for (int32_t bx = rx0; bx <= rx1 && hidden; bx += 8) {
                 const int32_t px = bx + lx;
@@ -358,37 +414,38 @@ __device__ __forceinline__ void geometry_warp(const WorkItem* __restrict__ item,
                 hidden = __all_sync(0xFFFFFFFFu, h);
             }
         }
+#endif
         if (hidden) {
             bulk_load_wait(ws);                                         // the copy must have landed before this shared memory is given to another CTA
-            if (lane == 0) atomicAdd(q.counters + 3, 1u);
+            if (tid == 0) atomicAdd(q.counters + 3, 1u);
             return;
         }
     }
-    if (!bulk_load_wait(ws)) { if (lane == 0) q.counters[2] = 2u; return; }
+    if (!bulk_load_wait(ws)) { if (tid == 0) q.counters[2] = 2u; return; }
     uint4* s_vtx = ws->vtx;
-    ParkedTri* s_park = ws->park;
+    ParkedTri* s_park = ws->park + wi * 32;
 
-    // ---- phase 1: distinct vertices, in place (each lane reads and rewrites its own slots)
+    // ---- phase 1: distinct vertices, in place (each thread reads and rewrites its own slots)
 #pragma unroll
-    for (int k = 0; k < CL_VERTS / 32; ++k)
-        if (lane + 32u * k < nVerts) {
-            const uint4 pv = s_vtx[lane + 32u * k];
+    for (int k = 0; k < CL_VERTS / (32 * WARPS); ++k)
+        if (tid + 32u * WARPS * k < nVerts) {
+            const uint4 pv = s_vtx[tid + 32u * WARPS * k];
             const CachedVtx cv = cluster_vertex(mvp, make_float4(__uint_as_float(pv.x), __uint_as_float(pv.y), __uint_as_float(pv.z), 1.0f), rt);
-            s_vtx[lane + 32u * k] = make_uint4((uint32_t)cv.X, (uint32_t)cv.Y, cv.zbits, cv.flag);
+            s_vtx[tid + 32u * WARPS * k] = make_uint4((uint32_t)cv.X, (uint32_t)cv.Y, cv.zbits, cv.flag);
         }
-    __syncwarp();
+    geom_sync<WARPS>();
 
     // ---- phase 2: triangles, 32 at a time.  Every lane sets one up and parks it in its shared-memory slot; then the warp
     // works through what was parked: the candidate samples of all the small ones dealt evenly to the lanes (most triangles
     // of a dense mesh cover one or two samples, a few cover dozens: a lane never waits for its neighbour's bounding box),
     // the medium and large ones queued for large_raster_kernel (vkr_raster.cuh, "warp-cooperative handling")
-    for (uint32_t base = 0; base < nTris; base += 32) {
+    for (uint32_t base = (uint32_t)wi * 32u; base < nTris; base += 32u * WARPS) {
         const uint32_t t = base + lane;
         int kind = 0;
         uint32_t count = 0, seqOfLane = 0;
 #if !VKR_STAGE_TRIS
         const uint2 tpCur = tpNext;
-        if (t + 32u < nTris) tpNext = __ldg(gtris + t + 32u);              // the next iteration's, one iteration ahead
+        if (t + 32u * WARPS < nTris) tpNext = __ldg(gtris + t + 32u * WARPS);      // the next iteration's, one iteration ahead
 #endif
         if (t < nTris) {
 #if VKR_STAGE_TRIS
@@ -469,9 +526,28 @@ __global__ void __launch_bounds__(GEOM_WARPS * 32, VKR_GEOM_MIN_CTAS) geometry_k
     const uint32_t slot = blockIdx.x * GEOM_WARPS + (threadIdx.x >> 5);
     if (slot >= nClusters) return;
     WarpSmem* ws = &s_warp[threadIdx.x >> 5];
-    if (SHADOW) geometry_warp<PASS_SHADOW>(work + slot, mvps, mvpStride, rt, q, ws, MakeDepthSink{rt.depthBits, rt.width});
-    else geometry_warp<PASS_MAIN>(work + slot, mvps, mvpStride, rt, q, ws, MakeVisSink{rt.vis, rt.width});
+    if (SHADOW) geometry_warp<PASS_SHADOW, 1>(work + slot, mvps, mvpStride, rt, q, ws, MakeDepthSink{rt.depthBits, rt.width});
+    else geometry_warp<PASS_MAIN, 1>(work + slot, mvps, mvpStride, rt, q, ws, MakeVisSink{rt.vis, rt.width});
 }
+#if !VKR_STAGE_TRIS && !defined(VKR_RASTER_CANDIDATES)
+// The latency form: one CTA of four warps per cluster (geometry_warp<.., 4>).  submit_frame picks it when a pass has fewer
+// clusters than VKR_CTA_CLUSTERS (default 32768: on one GPU-eighth bands of config 4 the two forms cross between 26 k and 45 k clusters, profiles/r02_ab.md).
+__global__ void __launch_bounds__(128, VKR_GEOM_MIN_CTAS) geometry_cta_kernel_main(const WorkItem* __restrict__ work, uint32_t nClusters,
+                                                                     const float* __restrict__ mvps, uint32_t mvpStride,
+                                                                     const __grid_constant__ RasterTarget rt, const __grid_constant__ Queues q) {
+    __shared__ GeomSmem<4> s_cta;
+    if (blockIdx.x >= nClusters) return;
+    geometry_warp<PASS_MAIN, 4>(work + blockIdx.x, mvps, mvpStride, rt, q, &s_cta, MakeVisSink{rt.vis, rt.width});
+}
+__global__ void __launch_bounds__(128, VKR_GEOM_MIN_CTAS) geometry_cta_kernel_shadow(const WorkItem* __restrict__ work, uint32_t nClusters,
+                                                                     const float* __restrict__ mvps, uint32_t mvpStride,
+                                                                     const __grid_constant__ RasterTarget rt, const __grid_constant__ Queues q) {
+    __shared__ GeomSmem<4> s_cta;
+    if (blockIdx.x >= nClusters) return;
+    geometry_warp<PASS_SHADOW, 4>(work + blockIdx.x, mvps, mvpStride, rt, q, &s_cta, MakeDepthSink{rt.depthBits, rt.width});
+}
+#define VKR_HAVE_CTA_GEOMETRY 1
+#endif
 
 // ---- "Transparent" draws (the tail of the draw list), after every opaque fragment is in the visibility buffer
 __global__ void __launch_bounds__(GEOM_WARPS * 32) geometry_transparent_kernel(const WorkItem* __restrict__ work, uint32_t nClusters,
@@ -487,7 +563,7 @@ __global__ void __launch_bounds__(GEOM_WARPS * 32) geometry_transparent_kernel(c
     __syncthreads();
     const uint32_t slot = blockIdx.x * GEOM_WARPS + (threadIdx.x >> 5);
     if (slot >= nClusters) return;
-    geometry_warp<PASS_TRANSPARENT>(work + slot, mvps, mvpStride, rt, q, &s_warp[threadIdx.x >> 5], MakeBlendSink{&sc, &s_sb});
+    geometry_warp<PASS_TRANSPARENT, 1>(work + slot, mvps, mvpStride, rt, q, &s_warp[threadIdx.x >> 5], MakeBlendSink{&sc, &s_sb});
 }
 
 // ---- main pass, alpha-tested draws only (launched when the frame has any): one thread per triangle,
@@ -718,6 +794,9 @@ struct VkrDevice {
     size_t uploadBytes = 0;
     // VKR_HOST_PROF=1: mean host time of vkr_draw's sections, printed at vkr_destroy
     bool hostProf = false; double hostProfUs[10] = {0}; uint64_t hostProfFrames = 0;
+    // a pass with fewer clusters than this runs one CTA (four warps) per cluster instead of one warp: the latency form
+    // (geometry_cta_kernel_*); VKR_CTA_CLUSTERS in the environment overrides it (0: never)
+    uint32_t ctaClusters = 32768;
 
 
     Queues q{};                         // large-triangle queue of the main pass
@@ -871,6 +950,7 @@ int vkr_create(const VkrConfig* cfg, VkrDevice** out) {
     dev->flags = cfg->flags;
     dev->smCount = prop.multiProcessorCount;
     dev->hostProf = std::getenv("VKR_HOST_PROF") != nullptr;
+    if (const char* e = std::getenv("VKR_CTA_CLUSTERS")) dev->ctaClusters = (uint32_t)std::strtoul(e, nullptr, 10);
     *out = dev;
     auto body = [&]() -> int {
         CK(cudaSetDevice(dev->device));
@@ -1405,6 +1485,11 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
             }
             const unsigned shadowSlots = plan.passSlots[1 + layer];
             if (shadowSlots) {
+#if defined(VKR_HAVE_CTA_GEOMETRY)
+                if (shadowSlots < dev->ctaClusters)
+                    geometry_cta_kernel_shadow<<<shadowSlots, 128, 0, ss>>>(dWork + (size_t)(1 + layer) * nChunks, shadowSlots, dShadowMvp + (size_t)layer * n * 16, 16u, rt, qs);
+                else
+#endif
                 geometry_kernel<true><<<(shadowSlots + GEOM_WARPS - 1) / GEOM_WARPS, GEOM_WARPS * 32, 0, ss>>>(dWork + (size_t)(1 + layer) * nChunks, shadowSlots,
                                                                                                       dShadowMvp + (size_t)layer * n * 16, 16u, rt, qs);
                 large_raster_kernel<true><<<largeGrid, 256, 0, ss>>>(rt, qs, AlphaCtx{}, 0);
@@ -1474,9 +1559,15 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
         // only the opaque prefix writes depth; transparent draws are blended in a later pass
         const unsigned opaqueChunks = plan.opaqueClusters, mainSlots = plan.passSlots[0];
         if (opaqueChunks) {
-            if (mainSlots)
+            if (mainSlots) {
+#if defined(VKR_HAVE_CTA_GEOMETRY)
+                if (mainSlots < dev->ctaClusters)
+                    geometry_cta_kernel_main<<<mainSlots, 128, 0, st>>>(dWork, mainSlots, (const float*)dObjects, (uint32_t)(sizeof(DObject) / 4), rt, dev->q);
+                else
+#endif
                 geometry_kernel<false><<<(mainSlots + GEOM_WARPS - 1) / GEOM_WARPS, GEOM_WARPS * 32, 0, st>>>(dWork, mainSlots, (const float*)dObjects,
                                                                                                             (uint32_t)(sizeof(DObject) / 4), rt, dev->q);
+            }
             if (timing) CK(cudaEventRecord(dev->tev[4], st));
             if (kpair) { CK(cudaEventRecord(kpair[1], st)); dev->kevRecorded++; }
             const AlphaCtx ax{dObjects, slot.chunkObjBuf, dev->matDev, dev->texDev};
