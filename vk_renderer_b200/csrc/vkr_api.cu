@@ -64,6 +64,15 @@ __global__ void pack_rgb8_kernel(const uint32_t* __restrict__ rgba, uint32_t* __
         for (size_t k = n4 << 2; k < n; ++k) { const uint32_t v = rgba[k]; o[3 * k] = (uint8_t)v; o[3 * k + 1] = (uint8_t)(v >> 8); o[3 * k + 2] = (uint8_t)(v >> 16); }
     }
 }
+// Cube-map texels decoded once, at upload, to the four floats the shading kernel's fetch computes from them (sRGB table
+// lookups / 255ths): one 16-byte load per texel afterwards instead of a 4-byte load, three table lookups and four conversions.
+__global__ void decode_texels_kernel(const uchar4* __restrict__ src, float4* __restrict__ dst, size_t n, const float* __restrict__ lut, int srgb) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uchar4 p = src[i];
+    dst[i] = srgb ? make_float4(lut[p.x], lut[p.y], lut[p.z], p.w * (1.0f / 255.0f))
+                  : make_float4(p.x * (1.0f / 255.0f), p.y * (1.0f / 255.0f), p.z * (1.0f / 255.0f), p.w * (1.0f / 255.0f));
+}
 __global__ void extract_vis_kernel(const uint64_t* __restrict__ vis, uint32_t* __restrict__ out, size_t n, int what,
                                    const uint2* __restrict__ chunkObj, const DObject* __restrict__ objects) {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -100,15 +109,18 @@ static ncclResult_t exchange_bands(const uint32_t* src, uint32_t* dst, const std
 // number that only grows, lives in the memory of the rank that WAITS on it and is written by a peer with a system-scope
 // release store after a system-scope fence; waiters spin with acquire loads, bounded by a timeout that raises an error word in
 // pinned host memory instead of hanging the device.
-//   shadowCleared[p] = f+1 : rank p has cleared its shadow map for frame f (rows may be stored into it)
+//   shadowCleared[s][p] = f+1 : rank p has cleared the shadow map of frame slot s (= f mod 2) for frame f: rows may be stored
+//                              into it.  Normally raised a frame AHEAD (the clear of frame f+1's map is issued in front of frame f's
+//                              main pass), so that nobody ever waits for it
 //   shadowReady[p]   = f+1 : rank p's rows of frame f have landed in my shadow map
 //   frameReady[p]    = f+1 : rank p's rows of frame f have landed in my (rank 0's) presented image
 //   gatheredFree     = f+1 : rank 0 has finished with the image that frame f overwrites
 static const int MAX_RANKS = 16;
 struct ShardFlags {
-    uint32_t shadowCleared[MAX_RANKS], shadowReady[MAX_RANKS], frameReady[MAX_RANKS];
+    uint32_t shadowCleared[2][MAX_RANKS], shadowReady[MAX_RANKS], frameReady[MAX_RANKS];
     uint32_t gatheredFree, pad[15];
 };
+static_assert(VKR_FRAME_OVERLAP == 2, "ShardFlags::shadowCleared has one row per frame slot");
 struct PeerList { uint32_t* p[MAX_RANKS]; int n; };
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) { asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
 __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) { uint32_t v; asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory"); return v; }
@@ -760,6 +772,10 @@ struct VkrDevice {
     cudaStream_t stream = nullptr, copyStream = nullptr;   // frame stream; device->host copies
     cudaStream_t shadowStream = nullptr, upStream = nullptr; // shadow pass runs beside the main pass; host->device uploads
     cudaEvent_t evShadow = nullptr, packedEv = nullptr;
+    // sharded over peer memory: the shadow map of slot s was cleared ahead of time for the frame whose flag value is
+    // preclearedFor[s], preclearedLayers[s] layers of it; the clear is complete at preclearEv[s] (recorded on the frame stream)
+    cudaEvent_t preclearEv[VKR_FRAME_OVERLAP] = {};
+    uint32_t preclearedFor[VKR_FRAME_OVERLAP] = {}, preclearedLayers[VKR_FRAME_OVERLAP] = {};
     bool ownStream = false;
     uint32_t W = 0, H = 0, S = 2048, flags = 0;
     int smCount = 148;
@@ -965,6 +981,7 @@ int vkr_create(const VkrConfig* cfg, VkrDevice** out) {
         CK(cudaStreamCreateWithPriority(&dev->shadowStream, cudaStreamNonBlocking, prHi));
         CK(cudaStreamCreateWithFlags(&dev->upStream, cudaStreamNonBlocking));
         CK(cudaEventCreateWithFlags(&dev->evShadow, cudaEventDisableTiming));
+        for (auto& e : dev->preclearEv) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         const size_t px = (size_t)dev->W * dev->H;
         ALLOC(dev->vis, px * 8);
         ALLOC(dev->hdr, px * 8);
@@ -1072,6 +1089,7 @@ void vkr_destroy(VkrDevice* dev) {
     if (dev->shadowStream) cudaStreamDestroy(dev->shadowStream);
     if (dev->upStream) cudaStreamDestroy(dev->upStream);
     if (dev->evShadow) cudaEventDestroy(dev->evShadow);
+    for (auto& e : dev->preclearEv) if (e) cudaEventDestroy(e);
     if (dev->packedEv) cudaEventDestroy(dev->packedEv);
     if (dev->ownStream && dev->stream) cudaStreamDestroy(dev->stream);
     delete dev;
@@ -1147,6 +1165,20 @@ static DTexture make_dtexture(const ImageRec& im, int sampler) {
     return t;
 }
 
+// The sky is sampled at every background pixel of every frame: its six faces keep decoded RGBA32F texels (DTexture.flags bit 4)
+static int predecode_cube_face(VkrDevice* dev, DTexture& d) {
+    if (d.flags & (8u | 16u)) return VKR_SUCCESS;                     // f16 texels, or decoded already
+    const uint32_t last = d.levels - 1;
+    const size_t total = (size_t)d.mipOffset[last] + (size_t)std::max(1u, d.w >> last) * std::max(1u, d.h >> last);
+    float4* out = nullptr;
+    ALLOC(out, total * sizeof(float4));
+    decode_texels_kernel<<<(unsigned)((total + 255) / 256), 256, 0, dev->stream>>>(d.data, out, total, dev->lut, (int)(d.flags & 1u));
+    LAUNCHED("decode_texels_kernel");
+    d.data = reinterpret_cast<const uchar4*>(out);
+    d.flags |= 16u;
+    return VKR_SUCCESS;
+}
+
 int vkr_create_image(VkrDevice* dev, const void* rgba8, uint32_t w, uint32_t h, VkrFormat fmt, int mipmapped, VkrImage* out) {
     if (!dev) return VKR_ERROR_INVALID_ARGUMENT;
     DRAIN(dev);
@@ -1184,6 +1216,8 @@ int vkr_set_cubemap(VkrDevice* dev, const void* const faces[6], uint32_t w, uint
         int rc = build_image(dev, faces[f], w, h, fmt, mipmapped, im);
         if (rc) return rc;
         t[f] = make_dtexture(im, VKR_SAMPLER_LINEAR);
+        rc = predecode_cube_face(dev, t[f]);
+        if (rc) return rc;
     }
     CK(cudaMemcpyAsync(dev->cubeDev, t, sizeof(t), cudaMemcpyHostToDevice, dev->stream));
     CK(cudaStreamSynchronize(dev->stream));
@@ -1218,6 +1252,8 @@ int vkr_set_cubemap_levels(VkrDevice* dev, const void* const* levels, uint32_t w
         d.data = reinterpret_cast<const uchar4*>(data);
         d.w = w; d.h = h; d.levels = levelCount;
         d.flags = (fmt == VKR_FORMAT_R8G8B8A8_SRGB ? 1u : 0u) | 2u | (fmt == VKR_FORMAT_R16G16B16A16_SFLOAT ? 8u : 0u);
+        const int rc = predecode_cube_face(dev, d);
+        if (rc) return rc;
     }
     CK(cudaMemcpyAsync(dev->cubeDev, t, sizeof(t), cudaMemcpyHostToDevice, dev->stream));
     CK(cudaStreamSynchronize(dev->stream));      // the caller's arrays and `t` may go away
@@ -1466,14 +1502,20 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
         Queues qs = dev->qShadow;
         qs.counters = dev->qShadow.counters + 8 * slotIdx;
         const size_t sn = (size_t)dev->S * dev->S;
-        // every layer is cleared before anything else: a sharded device then tells its peers that their rows may land
-        fill_u32_kernel<<<grid_for(sn * plan.shadowLayers / 4, 256, 2048), 256, 0, ss>>>(dev->shadowBits, sn * plan.shadowLayers, DEPTH_ONE_BITS);
-        dev->launches += 1;
-        if (p2p) {
-            PeerList pl{}; pl.n = 0;
-            for (int r = 0; r < dev->shardRanks; ++r) if (r != dev->shardRank) pl.p[pl.n++] = &dev->peerFlags[r]->shadowCleared[dev->shardRank];
-            shard_signal_kernel<<<1, 32, 0, ss>>>(pl, F1);
-            LAUNCHED("shard_signal_kernel");
+        // every layer is cleared before anything else: a sharded device then tells its peers that their rows may land.  Over peer
+        // memory that was normally done a frame ago (below, in front of the previous frame's main pass): the peers' pushes, which
+        // have to wait for the clear, then never find it missing
+        if (p2p && dev->preclearedFor[slotIdx] == F1 && dev->preclearedLayers[slotIdx] >= (uint32_t)plan.shadowLayers) {
+            CK(cudaStreamWaitEvent(ss, dev->preclearEv[slotIdx], 0));
+        } else {
+            fill_u32_kernel<<<grid_for(sn * plan.shadowLayers / 4, 256, 2048), 256, 0, ss>>>(dev->shadowBits, sn * plan.shadowLayers, DEPTH_ONE_BITS);
+            dev->launches += 1;
+            if (p2p) {
+                PeerList pl{}; pl.n = 0;
+                for (int r = 0; r < dev->shardRanks; ++r) if (r != dev->shardRank) pl.p[pl.n++] = &dev->peerFlags[r]->shadowCleared[slotIdx][dev->shardRank];
+                shard_signal_kernel<<<1, 32, 0, ss>>>(pl, F1);
+                LAUNCHED("shard_signal_kernel");
+            }
         }
         for (int layer = 0; layer < plan.shadowLayers; ++layer) {
             RasterTarget rt = plan.shadowTarget;
@@ -1510,7 +1552,7 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
                     if (m1 <= m0) continue;
                     const size_t first = (size_t)layer * sn + (size_t)m0 * dev->S, count = (size_t)(m1 - m0) * dev->S;
                     shard_push_rows_kernel<<<grid_for(count / 4, 256, (unsigned)dev->smCount * 4), 256, 0, ss>>>(dev->shadowBits, maps, first, count,
-                                                                                                                 dev->myFlags->shadowCleared, peersMask, F1, dev->countersHost + 12);
+                                                                                                                 dev->myFlags->shadowCleared[slotIdx], peersMask, F1, dev->countersHost + 12);
                     LAUNCHED("shard_push_rows_kernel");
                     dev->launches += 1;
                 }
@@ -1534,6 +1576,25 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
         }
         if (timing) CK(cudaEventRecord(dev->tev[8], ss));
         CK(cudaEventRecord(dev->evShadow, ss));
+        if (p2p) {
+            // The NEXT frame's shadow map (the other slot's) is cleared here, a frame ahead, behind this frame's shadow work, and
+            // the peers are told: its last reader, the previous frame's shading pass, has ended (`rendered`), and the peers'
+            // pushes of the next frame, which must not land before the clear, are a frame away — so they never wait for it
+            // (cleared at the start of its own frame, every rank's push waited for the slowest rank's clear: a second
+            // rendezvous per frame).
+            const int other = slotIdx ^ 1;
+            const size_t texels = (size_t)dev->S * dev->S * plan.shadowLayers;
+            if (dev->frameIndex > 0) CK(cudaStreamWaitEvent(ss, dev->slots[other].rendered, 0));
+            fill_u32_kernel<<<grid_for(texels / 4, 256, 2048), 256, 0, ss>>>(dev->shadowBuf[other], texels, DEPTH_ONE_BITS);
+            dev->launches += 1;
+            PeerList pl{}; pl.n = 0;
+            for (int r = 0; r < dev->shardRanks; ++r) if (r != dev->shardRank) pl.p[pl.n++] = &dev->peerFlags[r]->shadowCleared[other][dev->shardRank];
+            shard_signal_kernel<<<1, 32, 0, ss>>>(pl, F1 + 1u);
+            LAUNCHED("shard_signal_kernel (shadow map cleared ahead)");
+            CK(cudaEventRecord(dev->preclearEv[other], ss));
+            dev->preclearedFor[other] = F1 + 1u;
+            dev->preclearedLayers[other] = (uint32_t)plan.shadowLayers;
+        }
     }
 
     mark(2);

@@ -183,7 +183,8 @@ struct DTexture {             // one bindless slot (combined image sampler)
     const uchar4* data;       // mip chain, level l at data + mipOffset[l]
     uint32_t w, h, levels;
     uint32_t flags;           // bit0: sRGB, bit1: LINEAR sampler (else NEAREST), bit2: has alpha < 0.5 somewhere,
-                              // bit3: texels are 4 x f16 (8 bytes; cube maps only), `data` then points at uint2 texels
+                              // bit3: texels are 4 x f16 (8 bytes; cube maps only), `data` then points at uint2 texels,
+                              // bit4: texels are 4 x f32 (8-bit cube-map texels decoded at upload), `data` points at float4 texels
     uint32_t mipOffset[16];
     uint32_t texel0, pad;     // the first texel of level 0 as uploaded (host-side use: material_constants)
 };

@@ -370,16 +370,18 @@ VKR_HD int clampi(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v
 // A cube-map texel: RGBA8 (UNORM / sRGB) or RGBA16F (the engine's skybox asset, assets/pisa_cube.ktx, is an HDR image).
 // The format is a template parameter chosen once per lookup (texture_cube): as a per-texel test the compiler predicates
 // both fetch paths into every texel, +8 % instructions for the whole shading kernel (profiles/r01z).
-template <bool F16>
+// FMT: 0 RGBA8 (UNORM / sRGB), 1 RGBA16F, 2 RGBA32F (8-bit texels decoded at upload: DTexture.flags bit 4, device only)
+template <int FMT>
 VKR_HD float4 fetch_cube_texel(const DTexture& t, const float* __restrict__ lut, int level, int x, int y, int w) {
-    if (F16) {
+    if (FMT == 2) return VKR_LDG(reinterpret_cast<const float4*>(t.data) + t.mipOffset[level] + (size_t)y * w + x);
+    if (FMT == 1) {
         const uint2 p = VKR_LDG(reinterpret_cast<const uint2*>(t.data) + t.mipOffset[level] + (size_t)y * w + x);
         return make_float4(h2f_bits((uint16_t)(p.x & 0xFFFFu)), h2f_bits((uint16_t)(p.x >> 16)),
                            h2f_bits((uint16_t)(p.y & 0xFFFFu)), h2f_bits((uint16_t)(p.y >> 16)));
     }
     return fetch_texel(t, lut, level, x, y, w);
 }
-template <bool F16>
+template <int FMT>
 VKR_HD float4 sample_face_level(const DTexture& t, const float* lut, int level, float s, float tt) {
     const int w = level_dim(t.w, level), h = level_dim(t.h, level);
     float fu = s * (float)w - 0.5f, fv = tt * (float)h - 0.5f;
@@ -387,19 +389,19 @@ VKR_HD float4 sample_face_level(const DTexture& t, const float* lut, int level, 
     float a = fu - iu, b = fv - iv;
     int x0 = clampi((int)iu, 0, w - 1), x1 = clampi((int)iu + 1, 0, w - 1);
     int y0 = clampi((int)iv, 0, h - 1), y1 = clampi((int)iv + 1, 0, h - 1);
-    float4 t00 = fetch_cube_texel<F16>(t, lut, level, x0, y0, w), t10 = fetch_cube_texel<F16>(t, lut, level, x1, y0, w);
-    float4 t01 = fetch_cube_texel<F16>(t, lut, level, x0, y1, w), t11 = fetch_cube_texel<F16>(t, lut, level, x1, y1, w);
+    float4 t00 = fetch_cube_texel<FMT>(t, lut, level, x0, y0, w), t10 = fetch_cube_texel<FMT>(t, lut, level, x1, y0, w);
+    float4 t01 = fetch_cube_texel<FMT>(t, lut, level, x0, y1, w), t11 = fetch_cube_texel<FMT>(t, lut, level, x1, y1, w);
     float w00 = (1.0f - a) * (1.0f - b), w10 = a * (1.0f - b), w01 = (1.0f - a) * b, w11 = a * b;
     return make_float4(t00.x * w00 + t10.x * w10 + t01.x * w01 + t11.x * w11,
                        t00.y * w00 + t10.y * w10 + t01.y * w01 + t11.y * w11,
                        t00.z * w00 + t10.z * w10 + t01.z * w01 + t11.z * w11,
                        t00.w * w00 + t10.w * w10 + t01.w * w01 + t11.w * w11);
 }
-template <bool F16>
+template <int FMT>
 VKR_HD float4 texture_cube_fmt(const ShadeBuffers& sb, f3 r, f3 rdx, f3 rdy, int face, float s, float t) {
     const DTexture& tex = sb.cube[face];
     const int levels = (int)tex.levels;
-    if (levels == 1) return sample_face_level<F16>(tex, sb.srgbLut, 0, s, t);
+    if (levels == 1) return sample_face_level<FMT>(tex, sb.srgbLut, 0, s, t);
     float sx, tx, sy, ty;
     cube_project(rdx, face, sx, tx);
     cube_project(rdy, face, sy, ty);
@@ -409,9 +411,9 @@ VKR_HD float4 texture_cube_fmt(const ShadeBuffers& sb, f3 r, f3 rdx, f3 rdy, int
     int l0 = (int)floorf(lod);
     int l1 = l0 + 1 < levels ? l0 + 1 : levels - 1;
     float f = lod - (float)l0;
-    float4 c0 = sample_face_level<F16>(tex, sb.srgbLut, l0, s, t);
+    float4 c0 = sample_face_level<FMT>(tex, sb.srgbLut, l0, s, t);
     if (f == 0.0f) return c0;
-    float4 c1 = sample_face_level<F16>(tex, sb.srgbLut, l1, s, t);
+    float4 c1 = sample_face_level<FMT>(tex, sb.srgbLut, l1, s, t);
     return make_float4(c0.x * (1.0f - f) + c1.x * f, c0.y * (1.0f - f) + c1.y * f, c0.z * (1.0f - f) + c1.z * f,
                        c0.w * (1.0f - f) + c1.w * f);
 }
@@ -419,8 +421,10 @@ VKR_HD float4 texture_cube(const ShadeBuffers& sb, f3 r, f3 rdx, f3 rdy) {
     int face = cube_select(r);
     float s, t;
     cube_project(r, face, s, t);
-    if (sb.cube[face].flags & 8u) return texture_cube_fmt<true>(sb, r, rdx, rdy, face, s, t);    // all six faces share the format
-    return texture_cube_fmt<false>(sb, r, rdx, rdy, face, s, t);
+    const uint32_t fl = sb.cube[face].flags;                         // all six faces share the format
+    if (fl & 16u) return texture_cube_fmt<2>(sb, r, rdx, rdy, face, s, t);
+    if (fl & 8u) return texture_cube_fmt<1>(sb, r, rdx, rdy, face, s, t);
+    return texture_cube_fmt<0>(sb, r, rdx, rdy, face, s, t);
 }
 VKR_HD f3 sky_dir(const ShadeConst& sc, float sx, float sy) {
     return {sc.skyO[0] + sx * sc.skyX[0] + sy * sc.skyY[0], sc.skyO[1] + sx * sc.skyX[1] + sy * sc.skyY[1],
