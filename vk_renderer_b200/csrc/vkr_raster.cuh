@@ -414,7 +414,15 @@ VKR_HD uint32_t queue_alloc(uint32_t* counter, uint32_t n) {
 #endif
 }
 
-VKR_HDN void enqueue_large(const SetupTri& t, uint32_t seq, const Queues& q) {
+// strips: (alpha-tested triangles, whose every fragment costs a texture evaluation) items of 64 x 16 samples instead of 64 x 64 or
+// the whole box — `ty` then holds ITEM_STRIP | row / 16 — so that no warp of large_raster_kernel is left alone with 4096 alpha
+// tests while the others have run out of items (config 3: 15 % of that kernel's warp slots active, profiles/r02_ab.md)
+#ifndef VKR_CUTOUT_STRIPS
+#define VKR_CUTOUT_STRIPS 0      // measured neutral on config 3 (848 vs 849 frames/s, profiles/r02_ab.md): off
+#endif
+static const uint16_t ITEM_STRIP = 0x8000u;
+static const int STRIP_ROWS = 16;
+VKR_HDN void enqueue_large(const SetupTri& t, uint32_t seq, const Queues& q, bool strips = false) {
     const uint32_t slot = queue_alloc(&q.counters[0], 1);
     if (slot >= q.triCap) { q.counters[2] = 1; return; }
     LargeTri lt;
@@ -424,6 +432,22 @@ VKR_HDN void enqueue_large(const SetupTri& t, uint32_t seq, const Queues& q) {
     lt.bx0 = (int16_t)t.bx0; lt.by0 = (int16_t)t.by0; lt.bx1 = (int16_t)t.bx1; lt.by1 = (int16_t)t.by1;
     lt.seq = seq;
     q.tris[slot] = lt;
+    if (strips) {
+        EdgeEq e;
+        make_edges(t.X, t.Y, e);
+        const int32_t tx0 = t.bx0 / TILE, tx1 = t.bx1 / TILE, sy0 = t.by0 / STRIP_ROWS, sy1 = t.by1 / STRIP_ROWS;
+        for (int32_t sy = sy0; sy <= sy1; ++sy)
+            for (int32_t tx = tx0; tx <= tx1; ++tx) {
+                const int32_t x0 = imax(tx * TILE, t.bx0), x1 = imin(tx * TILE + TILE - 1, t.bx1);
+                const int32_t y0 = imax(sy * STRIP_ROWS, t.by0), y1 = imin(sy * STRIP_ROWS + STRIP_ROWS - 1, t.by1);
+                if (!tile_overlaps(e, x0, y0, x1, y1)) continue;
+                const uint32_t is = queue_alloc(&q.counters[1], 1);
+                if (is >= q.itemCap) { q.counters[2] = 1; return; }
+                LargeItem it; it.tri = slot; it.tx = (uint16_t)tx; it.ty = (uint16_t)(ITEM_STRIP | (uint32_t)sy);
+                q.items[is] = it;
+            }
+        return;
+    }
     if (t.ext < 16384) {          // medium: one item for the whole bounding box (at most 64 x 64 pixels), 32-bit edge functions
         const uint32_t is = queue_alloc(&q.counters[1], 1);
         if (is >= q.itemCap) { q.counters[2] = 1; return; }
@@ -449,10 +473,10 @@ VKR_HDN void enqueue_large(const SetupTri& t, uint32_t seq, const Queues& q) {
 // smallMax: largest bounding box (pixels per side) the calling lane rasterises itself; expensive sinks pass a small one so
 // that their fragments are produced by the large-triangle kernel, a warp per triangle with converged sink calls
 template <class Sink>
-VKR_HD void emit_setup(const SetupTri& t, uint32_t seq, const Queues& q, const Sink& sink, int32_t smallMax = SMALL_MAX) {
+VKR_HD void emit_setup(const SetupTri& t, uint32_t seq, const Queues& q, const Sink& sink, int32_t smallMax = SMALL_MAX, bool strips = false) {
     const int32_t w = t.bx1 - t.bx0 + 1, h = t.by1 - t.by0 + 1;
     if (w <= smallMax && h <= smallMax && t.ext < 16384) raster_small(t, sink);
-    else enqueue_large(t, seq, q);
+    else enqueue_large(t, seq, q, strips);
 }
 
 // ---- clipping (slow path) -------------------------------------------------------------
@@ -510,20 +534,27 @@ VKR_HDN void clip_and_emit(float4 c0, float4 c1, float4 c2, uint32_t seq, const 
 }
 
 // One (large triangle, tile) work item; lanes of a warp split the tile's pixels.
+// The sample rectangle of an item: the triangle's whole box, a 64 x 64 tile of it, or a 64 x 16 strip.
+VKR_HD void item_rect(const LargeTri& lt, const LargeItem& it, int32_t& x0, int32_t& y0, int32_t& x1, int32_t& y1) {
+    if (it.tx == ITEM_WHOLE) { x0 = lt.bx0; y0 = lt.by0; x1 = lt.bx1; y1 = lt.by1; return; }
+    x0 = imax((int32_t)it.tx * TILE, (int32_t)lt.bx0); x1 = imin((int32_t)it.tx * TILE + TILE - 1, (int32_t)lt.bx1);
+    if (it.ty & ITEM_STRIP) {
+        const int32_t sy = (int32_t)(it.ty & (uint16_t)~ITEM_STRIP);
+        y0 = imax(sy * STRIP_ROWS, (int32_t)lt.by0); y1 = imin(sy * STRIP_ROWS + STRIP_ROWS - 1, (int32_t)lt.by1);
+    } else { y0 = imax((int32_t)it.ty * TILE, (int32_t)lt.by0); y1 = imin((int32_t)it.ty * TILE + TILE - 1, (int32_t)lt.by1); }
+}
 template <class Sink>
 VKR_HD void raster_item(const LargeTri& lt, const LargeItem& it, const Sink& sink, int lane, int nlanes) {
-    const bool whole = it.tx == ITEM_WHOLE;
-    const int32_t x0 = whole ? (int32_t)lt.bx0 : imax((int32_t)it.tx * TILE, (int32_t)lt.bx0), x1 = whole ? (int32_t)lt.bx1 : imin((int32_t)it.tx * TILE + TILE - 1, (int32_t)lt.bx1);
-    const int32_t y0 = whole ? (int32_t)lt.by0 : imax((int32_t)it.ty * TILE, (int32_t)lt.by0), y1 = whole ? (int32_t)lt.by1 : imin((int32_t)it.ty * TILE + TILE - 1, (int32_t)lt.by1);
+    int32_t x0, y0, x1, y1;
+    item_rect(lt, it, x0, y0, x1, y1);
     raster_rect64(lt.X, lt.Y, lt.z0, lt.dzdx, lt.dzdy, x0, y0, x1, y1, sink, lane, nlanes);
 }
 
 #if defined(__CUDACC__)
 template <class Sink>
 __device__ __forceinline__ void raster_item_compact(const LargeTri& lt, const LargeItem& it, const Sink& sink, int lane, uint32_t* wq) {
-    const bool whole = it.tx == ITEM_WHOLE;
-    const int32_t x0 = whole ? (int32_t)lt.bx0 : imax((int32_t)it.tx * TILE, (int32_t)lt.bx0), x1 = whole ? (int32_t)lt.bx1 : imin((int32_t)it.tx * TILE + TILE - 1, (int32_t)lt.bx1);
-    const int32_t y0 = whole ? (int32_t)lt.by0 : imax((int32_t)it.ty * TILE, (int32_t)lt.by0), y1 = whole ? (int32_t)lt.by1 : imin((int32_t)it.ty * TILE + TILE - 1, (int32_t)lt.by1);
+    int32_t x0, y0, x1, y1;
+    item_rect(lt, it, x0, y0, x1, y1);
     raster_rect64_compact(lt.X, lt.Y, lt.z0, lt.dzdx, lt.dzdy, x0, y0, x1, y1, sink, lane, wq);
 }
 #endif
@@ -1056,7 +1087,7 @@ VKR_HDN void cutout_triangle(const DObject& o, const float* __restrict__ mvp, ui
     const float4 c0 = transform_point(mvp, p0.x, p0.y, p0.z), c1 = transform_point(mvp, p1.x, p1.y, p1.z), c2 = transform_point(mvp, p2.x, p2.y, p2.z);
     if (inside_clip_volume(c0) && inside_clip_volume(c1) && inside_clip_volume(c2)) {
         SetupTri t;
-        if (setup_snapped(project_vertex(c0, rt), project_vertex(c1, rt), project_vertex(c2, rt), rt, t)) emit_setup(t, seq, q, sink, CUTOUT_SMALL_MAX);
+        if (setup_snapped(project_vertex(c0, rt), project_vertex(c1, rt), project_vertex(c2, rt), rt, t)) emit_setup(t, seq, q, sink, CUTOUT_SMALL_MAX, VKR_CUTOUT_STRIPS != 0);
     } else clip_and_emit(c0, c1, c2, seq, rt, q, sink);
 }
 
