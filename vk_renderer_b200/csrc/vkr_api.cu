@@ -624,12 +624,18 @@ __global__ void __launch_bounds__(256, VKR_LARGE_MIN_CTAS) large_raster_kernel(c
     static_assert(sizeof(LargeTri) == 48, "three 16-byte loads per triangle record");
     const int wslot = threadIdx.x >> 5;
     const uint32_t cs = min((uint32_t)VKR_ITEM_CHUNK_MAX, max(1u, nItems / (warpsPerGrid * 4u)));
+    // The other end of the scale: a queue much SHORTER than the grid (a few hundred tile items of 64 x 64 samples: config 1's
+    // ground plane) leaves most warps idle while each busy one walks 4096 samples alone — the kernel then lasts as long as
+    // one tile (71 us of config 1's 147 us frame).  With at most an eighth / a quarter / half as many items as warps, 8 / 4 / 2
+    // warps share an item, each taking a band of its rows ("virtual items": item * wpi + part).  Config 1: 9550 -> 15350 frames/s.
+    const uint32_t wsh = nItems * 8u <= warpsPerGrid ? 3u : nItems * 4u <= warpsPerGrid ? 2u : nItems * 2u <= warpsPerGrid ? 1u : 0u;
+    const uint32_t nVirtual = nItems << wsh;
     uint32_t chunk = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * cs, nextChunk = 0xFFFFFFFFu;
-    while (chunk < nItems) {
+    while (chunk < nVirtual) {
         if (lane == 0) nextChunk = (warpsPerGrid + atomicAdd(&q.counters[4], 1u)) * cs;
-        const uint32_t n = min(cs, nItems - chunk);
+        const uint32_t n = min(cs, nVirtual - chunk);
         if ((uint32_t)lane < n) {
-            LargeItem mine = q.items[chunk + lane];
+            LargeItem mine = q.items[(chunk + lane) >> wsh];
             if (mine.tri >= nTris) mine.tri = ITEM_SKIP;     // a skip marker of an overflowed frame (the host grows the queues and redraws)
             else {
                 const uint4* src = reinterpret_cast<const uint4*>(q.tris + mine.tri);
@@ -647,22 +653,35 @@ __global__ void __launch_bounds__(256, VKR_LARGE_MIN_CTAS) large_raster_kernel(c
                 dst[0] = s_tri[wslot][k][0]; dst[1] = s_tri[wslot][k][1]; dst[2] = s_tri[wslot][k][2];
             }
             const bool whole = it.tx == ITEM_WHOLE;          // medium triangle: its whole bounding box, 32-bit edge functions
+            const uint32_t part = (chunk + k) & ((1u << wsh) - 1u);
+            const bool cutoutItem = !SHADOW && anyCutout && (ax.objects[ax.chunkObj[lt.seq >> 8].x].flags & 2u);
+            if (whole && !cutoutItem) {
+                if (SHADOW) { DepthSink sink{rt.depthBits, rt.width}; raster_medium_coop(lt, sink, lane, part, wsh); }
+                else { VisSink sink{rt.vis, rt.width, 0xFFFFFFFEu - lt.seq}; raster_medium_coop(lt, sink, lane, part, wsh); }
+                continue;
+            }
+            int32_t x0, y0, x1, y1;
+            item_rect(lt, it, x0, y0, x1, y1);
+            if (wsh) {                                       // this warp's band of the item's rows
+                const int32_t per = ((y1 - y0 + 1) + (int32_t)(1u << wsh) - 1) >> wsh;
+                y0 += (int32_t)part * per;
+                y1 = min(y1, y0 + per - 1);
+                if (y0 > y1) continue;
+            }
             if (SHADOW) {
                 DepthSink sink{rt.depthBits, rt.width};
-                if (whole) raster_medium_coop(lt, sink, lane);
-                else raster_item(lt, it, sink, lane, 32);
+                raster_rect64(lt.X, lt.Y, lt.z0, lt.dzdx, lt.dzdy, x0, y0, x1, y1, sink, lane, 32);
             } else {
                 VisSink sink{rt.vis, rt.width, 0xFFFFFFFEu - lt.seq};
-                if (anyCutout && (ax.objects[ax.chunkObj[lt.seq >> 8].x].flags & 2u)) {
+                if (cutoutItem) {
                     const uint2 co = ax.chunkObj[lt.seq >> 8];
                     const DObject& o = ax.objects[co.x];
                     const uint32_t tri = co.y + (lt.seq & 255u);
                     AlphaTri at;
                     make_alpha_tri(o, o.mvp, o.idx[3 * tri], o.idx[3 * tri + 1], o.idx[3 * tri + 2], ax, rt, at);
                     CutoutSink<VisSink> cs2{sink, &at};
-                    raster_item_compact(lt, it, cs2, lane, s_queue[SHADOW ? 0 : wslot]);
-                } else if (whole) raster_medium_coop(lt, sink, lane);
-                else raster_item(lt, it, sink, lane, 32);
+                    raster_rect64_compact(lt.X, lt.Y, lt.z0, lt.dzdx, lt.dzdy, x0, y0, x1, y1, cs2, lane, s_queue[SHADOW ? 0 : wslot]);
+                } else raster_rect64(lt.X, lt.Y, lt.z0, lt.dzdx, lt.dzdy, x0, y0, x1, y1, sink, lane, 32);
             }
         }
         __syncwarp();                                        // the chunk's slots are free again

@@ -30,7 +30,12 @@ static const uint64_t VIS_CLEAR = 0x3F800000FFFFFFFFull;   // depth 1.0, no prim
 static const uint32_t VIS_EMPTY_LO = 0xFFFFFFFFu;
 static const uint32_t DEPTH_ONE_BITS = 0x3F800000u;
 
-static const int TILE = 64;                // large-triangle tile edge in pixels
+// Large triangles are queued as (triangle, TILE x TILE tile) items, one warp each.  Measured (profiles/r02_ab.md, "tile edge";
+// frames/s of configs 1 / 2 / 3 / 4): 64 -> 14960 / 8180 / 843 / 2586, 32 -> 20200 / 8190 / 887 / 2576, 16 -> 19790 / 8190 / 866.
+#ifndef VKR_TILE
+#define VKR_TILE 32
+#endif
+static const int TILE = VKR_TILE;          // large-triangle tile edge in pixels
 // In-thread raster when the bounding box is <= SMALL_MAX x SMALL_MAX samples; bigger triangles go to large_raster_kernel, where
 // a whole warp works on one.  Measured (profiles/r02_ab.md, "in-lane threshold"; frames/s of configs 1 / 2 / 3 / 4):
 // 16 -> 7447 / 6360 / 714 / 2492, 12 -> 7230 / 6646 / 697, 10 -> 7597 / 6874 / 685 / 2496, 8 -> 8081 / 7244 / 681 / 2489,

@@ -689,7 +689,7 @@ __device__ __forceinline__ void raster_candidates_warp(const ParkedTri* slots, u
 // All 32 lanes rasterise one medium triangle (warp-uniform `lt`): 8-pixel strips of its bounding box dealt to the lanes,
 // 32-bit edge functions as in raster_small.
 template <class Sink>
-__device__ __forceinline__ void raster_medium_coop(const LargeTri& lt, const Sink& sink, int lane) {
+__device__ __forceinline__ void raster_medium_coop(const LargeTri& lt, const Sink& sink, int lane, uint32_t part = 0u, uint32_t partShift = 0u) {
     int32_t e[3], ax[3], by[3];
     const int32_t Px = (int32_t)lt.bx0 * 256 + 128, Py = (int32_t)lt.by0 * 256 + 128;
 #pragma unroll
@@ -702,8 +702,10 @@ __device__ __forceinline__ void raster_medium_coop(const LargeTri& lt, const Sin
         by[i] = dx * 256;
     }
     const int32_t w = lt.bx1 - lt.bx0 + 1, h = lt.by1 - lt.by0 + 1;
-    const int32_t strips = (w + 7) >> 3, n = strips * h;
-    for (int32_t i = lane; i < n; i += 32) {
+    // (part, partShift): this warp's band of the rows when 2^partShift warps share the triangle (large_raster_kernel on a short queue)
+    const int32_t per = (h + (int32_t)(1u << partShift) - 1) >> partShift, rowBegin = (int32_t)part * per, rowEnd = imin(h, rowBegin + per);
+    const int32_t strips = (w + 7) >> 3, n = strips * rowEnd;
+    for (int32_t i = strips * rowBegin + lane; i < n; i += 32) {
         const int32_t row = i / strips, sx = i - row * strips;
         const int32_t py = lt.by0 + row, pxa = lt.bx0 + sx * 8;
         int32_t f0 = e[0] + row * by[0] + sx * 8 * ax[0], f1 = e[1] + row * by[1] + sx * 8 * ax[1], f2 = e[2] + row * by[2] + sx * 8 * ax[2];
