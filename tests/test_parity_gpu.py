@@ -244,3 +244,53 @@ def test_gpu_large_triangle_queue_overflow_is_repaired(ork_lib, tmp_path):
     env = dict(os.environ, VKR_QUEUE_CAPS="4,8")
     out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
     assert out.returncode == 0 and "ok" in out.stdout, out.stdout[-2000:] + out.stderr[-4000:]
+
+
+@pytest.mark.parametrize("cta_clusters", ["0", "1000000"])
+def test_gpu_both_geometry_kernel_forms_give_the_same_frames(vkr_lib, tmp_path, cta_clusters):
+    """A pass with fewer than VKR_CTA_CLUSTERS clusters runs one CTA of four warps per cluster (geometry_cta_kernel_*), a larger
+    one runs one warp per cluster (geometry_kernel<>): the small parity scenes above therefore only see the first form and the
+    4K frame of config 4 only the second.  Here the threshold is forced to 0 (warp form everywhere) and to a million (CTA form
+    everywhere) in a child process, and every buffer of every scene must equal, bit for bit, what the default gives."""
+    import subprocess, sys, os, textwrap
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    names = ["edge_cases", "clipping", "lattice", "big_triangles", "cutout", "basic_csm", "transparent", "soup"]
+    for name in names:
+        got = parity.render(vkr_lib, "vkr", name, 320, 200, shadow_extent=256)
+        np.savez(tmp_path / f"{name}.npz", prim=got["prim"], depth=got["depth"].view(np.uint32), shadow=got["shadow"].view(np.uint32), rgba=got["rgba"])
+    code = textwrap.dedent(f"""
+        import sys, numpy as np
+        sys.path.insert(0, {root!r}); sys.path.insert(0, {os.path.join(root, 'tests')!r})
+        import vk_renderer_b200, parity
+        lib = vk_renderer_b200.load()
+        for name in {names!r}:
+            got = parity.render(lib, "vkr", name, 320, 200, shadow_extent=256)
+            want = np.load({str(tmp_path)!r} + "/" + name + ".npz")
+            assert np.array_equal(want["prim"], got["prim"]), name
+            assert np.array_equal(want["depth"], got["depth"].view(np.uint32)), name
+            assert np.array_equal(want["shadow"], got["shadow"].view(np.uint32)), name
+            assert np.array_equal(want["rgba"], got["rgba"]), name
+        print("ok")
+    """)
+    env = dict(os.environ, VKR_CTA_CLUSTERS=cta_clusters)
+    out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0 and out.stdout.strip().endswith("ok"), out.stderr[-2000:]
+
+
+def test_gpu_host_times_are_reported(vkr_lib):
+    """vkr_host_times: the host's own time per frame, apart from its waiting (bench.py's host_busy_ms_per_step)."""
+    from vk_renderer_b200 import capi
+    import scenes as sc
+    r = capi.Renderer(vkr_lib, "vkr", 320, 200, shadow_extent=256, flags=capi.CONFIG_SUBMIT_THREAD)
+    args = sc.SCENES["basic_pcf"](r)
+    for _ in range(20):                      # frames before a device's 16th are never counted
+        r.draw(*args)
+    r.host_times(reset=True)
+    for _ in range(10):
+        r.draw(*args)
+    r.sync()
+    t = r.host_times()
+    assert set(t) >= {"plan", "upload_expand", "shadow", "main_raster", "transparent_shade", "submit_thread_waiting_for_device"}
+    assert all(v >= 0.0 for v in t.values()) and t["plan"] > 0.0 and t["main_raster"] > 0.0
+    assert sum(t.values()) < 50000.0          # microseconds per frame: a 320x200 frame does not take 50 ms of host time
+    r.close()
