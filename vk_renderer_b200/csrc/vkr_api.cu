@@ -596,8 +596,10 @@ __global__ void __launch_bounds__(CL_TRIS) geometry_cutout_kernel(const DObject*
 }
 
 // ---- large triangles: one warp per (triangle, 64x64 tile) item, grid-stride over the queue
+// CTAs of large_raster_kernel per SM (a register cap: 1 -> 125 registers, 2 resident; 3 -> 85; 4 -> 64 with spills), which is also
+// the size of its persistent grid.  Configs 1 / 2 / 3, frames/s: 2 resident 19930 / 8195 / 891, 3 -> 20090 / 8282 / 899, 4 -> 20590 / 8333 / 885.
 #ifndef VKR_LARGE_MIN_CTAS
-#define VKR_LARGE_MIN_CTAS 1
+#define VKR_LARGE_MIN_CTAS 3
 #endif
 #ifndef VKR_ITEM_CHUNK_MAX
 #define VKR_ITEM_CHUNK_MAX 4u      // items a warp of large_raster_kernel takes per trip to the cursor (at most 32)
@@ -626,9 +628,9 @@ __global__ void __launch_bounds__(256, VKR_LARGE_MIN_CTAS) large_raster_kernel(c
     const uint32_t cs = min((uint32_t)VKR_ITEM_CHUNK_MAX, max(1u, nItems / (warpsPerGrid * 4u)));
     // The other end of the scale: a queue much SHORTER than the grid (a few hundred tile items of 64 x 64 samples: config 1's
     // ground plane) leaves most warps idle while each busy one walks 4096 samples alone — the kernel then lasts as long as
-    // one tile (71 us of config 1's 147 us frame).  With at most an eighth / a quarter / half as many items as warps, 8 / 4 / 2
+    // one tile (71 us of config 1's 147 us frame).  With at most a quarter / half / as many items as warps, 8 / 4 / 2
     // warps share an item, each taking a band of its rows ("virtual items": item * wpi + part).  Config 1: 9550 -> 15350 frames/s.
-    const uint32_t wsh = nItems * 8u <= warpsPerGrid ? 3u : nItems * 4u <= warpsPerGrid ? 2u : nItems * 2u <= warpsPerGrid ? 1u : 0u;
+    const uint32_t wsh = nItems * 4u <= warpsPerGrid ? 3u : nItems * 2u <= warpsPerGrid ? 2u : nItems <= warpsPerGrid ? 1u : 0u;
     const uint32_t nVirtual = nItems << wsh;
     uint32_t chunk = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * cs, nextChunk = 0xFFFFFFFFu;
     while (chunk < nVirtual) {
@@ -1492,7 +1494,7 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
     if (timing) CK(cudaEventRecord(dev->tev[1], st));
     mark(1);
 
-    const unsigned largeGrid = (unsigned)dev->smCount * 4;
+    const unsigned largeGrid = (unsigned)dev->smCount * VKR_LARGE_MIN_CTAS;      // every CTA resident: the cursor logic counts the grid's warps
     // sort-first over peer memory (see "sort-first exchange over PEER MEMORY"): this frame's number + 1 is what its flags carry
     const bool sharded = dev->shardRanks > 1;
     const bool p2p = sharded && dev->p2p && !dev->shadowExchange;
