@@ -595,7 +595,7 @@ __global__ void __launch_bounds__(CL_TRIS) geometry_cutout_kernel(const DObject*
     cutout_triangle(o, o.mvp, g0, g1, g2, seq, rt, q, ax, sink);
 }
 
-// ---- large triangles: one warp per (triangle, 64x64 tile) item, grid-stride over the queue
+// ---- large triangles: one warp (or, on a short queue, up to eight) per (triangle, TILE x TILE tile) or whole-box item, taken from a shared cursor
 // CTAs of large_raster_kernel per SM (a register cap: 1 -> 125 registers, 2 resident; 3 -> 85; 4 -> 64 with spills), which is also
 // the size of its persistent grid.  Configs 1 / 2 / 3, frames/s: 2 resident 19930 / 8195 / 891, 3 -> 20090 / 8282 / 899, 4 -> 20590 / 8333 / 885.
 #ifndef VKR_LARGE_MIN_CTAS
@@ -626,7 +626,7 @@ __global__ void __launch_bounds__(256, VKR_LARGE_MIN_CTAS) large_raster_kernel(c
     static_assert(sizeof(LargeTri) == 48, "three 16-byte loads per triangle record");
     const int wslot = threadIdx.x >> 5;
     const uint32_t cs = min((uint32_t)VKR_ITEM_CHUNK_MAX, max(1u, nItems / (warpsPerGrid * 4u)));
-    // The other end of the scale: a queue much SHORTER than the grid (a few hundred tile items of 64 x 64 samples: config 1's
+    // The other end of the scale: a queue much SHORTER than the grid (a few hundred tile items, 64 x 64 samples each at the time: config 1's
     // ground plane) leaves most warps idle while each busy one walks 4096 samples alone — the kernel then lasts as long as
     // one tile (71 us of config 1's 147 us frame).  With at most a quarter / half / as many items as warps, 8 / 4 / 2
     // warps share an item, each taking a band of its rows ("virtual items": item * wpi + part).  Config 1: 9550 -> 15350 frames/s.

@@ -201,7 +201,7 @@ struct LargeTri {
     int16_t bx0, by0, bx1, by1;
     uint32_t seq;
 };
-struct LargeItem { uint32_t tri; uint16_t tx, ty; };   // (triangle, 64x64 tile); tx == ITEM_WHOLE: the triangle's whole bounding box
+struct LargeItem { uint32_t tri; uint16_t tx, ty; };   // (triangle, TILE x TILE tile); tx == ITEM_WHOLE: the triangle's whole bounding box
 static const uint16_t ITEM_WHOLE = 0xFFFFu;
 static const uint32_t ITEM_SKIP = 0xFFFFFFFFu;    // LargeItem::tri of a slot claimed by a triangle that did not fit the queue
 

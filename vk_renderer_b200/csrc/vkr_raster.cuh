@@ -414,7 +414,7 @@ VKR_HD uint32_t queue_alloc(uint32_t* counter, uint32_t n) {
 #endif
 }
 
-// strips: (alpha-tested triangles, whose every fragment costs a texture evaluation) items of 64 x 16 samples instead of 64 x 64 or
+// strips: (alpha-tested triangles, whose every fragment costs a texture evaluation) items of TILE x 16 samples instead of TILE x TILE or
 // the whole box — `ty` then holds ITEM_STRIP | row / 16 — so that no warp of large_raster_kernel is left alone with 4096 alpha
 // tests while the others have run out of items (config 3: 15 % of that kernel's warp slots active, profiles/r02_ab.md)
 #ifndef VKR_CUTOUT_STRIPS
@@ -534,7 +534,7 @@ VKR_HDN void clip_and_emit(float4 c0, float4 c1, float4 c2, uint32_t seq, const 
 }
 
 // One (large triangle, tile) work item; lanes of a warp split the tile's pixels.
-// The sample rectangle of an item: the triangle's whole box, a 64 x 64 tile of it, or a 64 x 16 strip.
+// The sample rectangle of an item: the triangle's whole box, a TILE x TILE tile of it, or a TILE x 16 strip.
 VKR_HD void item_rect(const LargeTri& lt, const LargeItem& it, int32_t& x0, int32_t& y0, int32_t& x1, int32_t& y1) {
     if (it.tx == ITEM_WHOLE) { x0 = lt.bx0; y0 = lt.by0; x1 = lt.bx1; y1 = lt.by1; return; }
     x0 = imax((int32_t)it.tx * TILE, (int32_t)lt.bx0); x1 = imin((int32_t)it.tx * TILE + TILE - 1, (int32_t)lt.bx1);
@@ -602,7 +602,7 @@ __device__ uint32_t* g_binCount = nullptr;
 // ---- warp-cooperative handling: candidates of small triangles dealt to the lanes; triangles too big for that ------------
 // cluster_triangle_deferred sets one triangle up and says who rasterises it: 0 nobody (culled, or clipped and emitted on the
 // spot), 1 medium (extent < 64 px: the warp queues it as one item for large_raster_kernel's 32-bit path), 2 large (the warp
-// enumerates its 64x64 tiles and queues them), 3 small: its record is in `out.rec` and `count` candidates wait for the warp's
+// enumerates its TILE x TILE tiles and queues them), 3 small: its record is in `out.rec` and `count` candidates wait for the warp's
 // candidate stage (geometry_warp).  `out` is the lane's slot of the warp's shared memory.
 #if defined(VKR_RASTER_CANDIDATES)
 union ParkedTri { FragRec rec; LargeTri lt; };
