@@ -18,10 +18,14 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--frames", type=int, default=300)
     ap.add_argument("--configs", default="1,2,3,4")
+    ap.add_argument("--loop-flags", action="store_true",
+                    help="the flags INTEGRATION.md recommends for a frame loop and bench.py uses: submit thread, transient depth and draw image")
     args = ap.parse_args()
+    from vk_renderer_b200 import capi
+    flags = (capi.CONFIG_SUBMIT_THREAD | capi.CONFIG_TRANSIENT_DEPTH | capi.CONFIG_TRANSIENT_HDR) if args.loop_flags else 0
     for c in [int(x) for x in args.configs.split(",")]:
         w, h = SIZES[c]
-        e = Engine(w, h)
+        e = Engine(w, h, flags=flags)
         tris = e.load_procedural(c)
         for _ in range(10):
             e.update_scene(0.0); e.draw()
@@ -35,7 +39,8 @@ def main():
         fps = args.frames / dt
         print(json.dumps({"config": c, "resolution": [w, h], "scene_triangles": int(tris), "visible_objects": e.visible_objects(),
                           "submitted_triangles": st.triangle_count, "frames_per_s": fps, "mtri_per_s": fps * st.triangle_count / 1e6,
-                          "gpix_per_s": fps * w * h / 1e9, "frames": args.frames}), flush=True)
+                          "gpix_per_s": fps * w * h / 1e9, "frames": args.frames,
+                          "engine_flags": "SUBMIT_THREAD | TRANSIENT_DEPTH | TRANSIENT_HDR" if args.loop_flags else "0"}), flush=True)
         e.close()
 
 

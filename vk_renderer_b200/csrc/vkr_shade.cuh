@@ -319,7 +319,9 @@ VKR_HD bool shade_fragment(const ShadeConst& sc, const ShadeBuffers& sb, const D
     f3 L = norm3(f3{sc.lightVec[0], sc.lightVec[1], sc.lightVec[2]});
     f3 sun = {sc.scene.sunlightColor[0], sc.scene.sunlightColor[1], sc.scene.sunlightColor[2]};
     f3 amb = {sc.scene.ambientColor[0], sc.scene.ambientColor[1], sc.scene.ambientColor[2]};
-    float shadow = calc_shadow(sc, sb, fr.posWorld, fr.viewZ);
+    // a fragment facing away from the light gets no direct light whatever its shadow term (both shaders multiply it by
+    // max(N.L, 0), which is then exactly 0): the shadow-map lookup — 16 texels for PCF — is skipped for it
+    const float shadow = dot3(N, L) > 0.0f ? calc_shadow(sc, sb, fr.posWorld, fr.viewZ) : 0.0f;
     if (sc.fragShader == VKR_FRAG_MESH_LAMBERT) {          // shaders/mesh.frag:171-181
         f3 diffuse = fmaxf(0.0f, dot3(N, L)) * base * sun;
         out = diffuse * (1.0f - shadow) + amb * base;
