@@ -319,9 +319,13 @@ VKR_HD bool shade_fragment(const ShadeConst& sc, const ShadeBuffers& sb, const D
     f3 L = norm3(f3{sc.lightVec[0], sc.lightVec[1], sc.lightVec[2]});
     f3 sun = {sc.scene.sunlightColor[0], sc.scene.sunlightColor[1], sc.scene.sunlightColor[2]};
     f3 amb = {sc.scene.ambientColor[0], sc.scene.ambientColor[1], sc.scene.ambientColor[2]};
-    // a fragment facing away from the light gets no direct light whatever its shadow term (both shaders multiply it by
-    // max(N.L, 0), which is then exactly 0): the shadow-map lookup — 16 texels for PCF — is skipped for it
-    const float shadow = dot3(N, L) > 0.0f ? calc_shadow(sc, sb, fr.posWorld, fr.viewZ) : 0.0f;
+    // A fragment facing away from the light gets no direct light: both shaders multiply the direct term by max(N.L, 0), which
+    // is then exactly 0, and what is left is ambient * base, bit for bit (x + 0 = x).  The shadow-map lookup — 16 texels for
+    // PCF —, the metallic-roughness fetch and the BRDF are skipped for it.  (N.L <= 0 is false for a NaN normal, which takes
+    // the full path like before; the one case this changes is a direct term that is 0 * NaN in the shader — roughness 0 with
+    // the half vector exactly on the normal.)
+    if (dot3(N, L) <= 0.0f) { out = amb * base; return true; }
+    const float shadow = calc_shadow(sc, sb, fr.posWorld, fr.viewZ);
     if (sc.fragShader == VKR_FRAG_MESH_LAMBERT) {          // shaders/mesh.frag:171-181
         f3 diffuse = fmaxf(0.0f, dot3(N, L)) * base * sun;
         out = diffuse * (1.0f - shadow) + amb * base;
