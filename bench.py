@@ -436,6 +436,7 @@ def run_b200(args):
     if rank == 0:
         fps = args.steps / (ms / 1000.0)
         peak, peak_src = measured_peak()
+        my_rows_px = (my_rows[1] - my_rows[0]) * W
         frame_bytes, gk_bytes = algorithmic_bytes(info)
         gk_basis = "SURVEY 8d: every instance's indices + positions once, visibility buffer once"
         if world > 1 and cull.get("main_clusters"):
@@ -458,6 +459,13 @@ def run_b200(args):
             "roofline": {"bound": "hbm", "kernel": "geometry_kernel<main>", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "algorithmic_bytes": gk_bytes, "algorithmic_basis": gk_basis, "kernel_ms": gk_ms,
                          "peak_source": peak_src},
+            # the other long kernel of the frame, for the record (same byte model as DESIGN.md 5: visibility key 8 + presented
+            # texel 4 + material texels 8 per pixel + the shadow map once; its pass is that one kernel)
+            "roofline_shade_kernel": (lambda b, t: {"bound": "hbm", "kernel": "shade_kernel", "algorithmic_bytes": b, "kernel_ms": t,
+                                                    "achieved": b / (t / 1000.0) / 1e9 if t > 0 else 0.0, "peak": peak, "unit": "GB/s",
+                                                    "frac": (b / (t / 1000.0) / 1e9 / peak) if t > 0 else 0.0,
+                                                    "traffic": measured_traffic("shade_kernel")[0]})(
+                (my_rows_px if world > 1 else W * H) * 20 + S * S * 4, avg["shade"]),
             "pass_ms": avg, "pass_ms_last_pipelined_frame": {k: float(v) for k, v in tm.items()},
             "host_issue_ms_per_step": host_issue_ms, "host_vkr_draw_call_ms": float(np.median(host_call)), "host_busy_ms_per_step": host_busy,
             "cluster_culling": cull, "per_rank_pass_ms_last_pipelined_frame": per_rank,
