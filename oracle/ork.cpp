@@ -367,15 +367,65 @@ void cube_face_fixed(vec3 r, int face, float& s, float& t) {  // project onto a 
     s = 0.5f * (sc / ma + 1.0f);
     t = 0.5f * (tc / ma + 1.0f);
 }
-vec4 sample_face_level(const Image& im, int level, float s, float t) {  // LINEAR, clamp to face edge
+// A texel of a cube face addressed possibly ONE texel beyond the face (a bilinear tap at a seam).  Vulkan filters cube maps
+// seamlessly ("Cube Map Edge Handling"): a tap beyond one edge comes from the face that shares the edge.  The faces are
+// unfolded about that edge: the tap's centre, d beyond the edge on this face's plane, is the point d INSIDE the neighbour's
+// plane.  With the face-selection table read backwards, a face is  M + u S + v T  (M the major axis, u = 2s - 1, v = 2t - 1):
+//   +X: M = (1,0,0), S = (0,0,-1), T = (0,-1,0)   -X: M = (-1,0,0), S = (0,0,1), T = (0,-1,0)
+//   +Y: M = (0,1,0), S = (1,0,0),  T = (0,0,1)    -Y: M = (0,-1,0), S = (1,0,0), T = (0,0,-1)
+//   +Z: M = (0,0,1), S = (1,0,0),  T = (0,-1,0)   -Z: M = (0,0,-1), S = (-1,0,0), T = (0,-1,0)
+// Returns false for a tap beyond TWO edges (a cube corner: no such texel exists).
+static const float CUBE_M[6][3] = {{1, 0, 0}, {-1, 0, 0}, {0, 1, 0}, {0, -1, 0}, {0, 0, 1}, {0, 0, -1}};
+static const float CUBE_S[6][3] = {{0, 0, -1}, {0, 0, 1}, {1, 0, 0}, {1, 0, 0}, {1, 0, 0}, {-1, 0, 0}};
+static const float CUBE_T[6][3] = {{0, -1, 0}, {0, -1, 0}, {0, 0, 1}, {0, 0, -1}, {0, -1, 0}, {0, -1, 0}};
+bool cube_tap(const OrkDevice* d, int face, int level, int x, int y, vec4& out) {
+    const Image& im = d->cube[face];
+    const int w = im.w[level], h = im.h[level];
+    const bool xo = x < 0 || x >= w, yo = y < 0 || y >= h;
+    if (!xo && !yo) { out = fetch_texel(im, level, x, y); return true; }
+    if (xo && yo) return false;
+    const float u = (float)(2 * x + 1) / (float)w - 1.0f, v = (float)(2 * y + 1) / (float)h - 1.0f;
+    const float* M = CUBE_M[face]; const float* S = CUBE_S[face]; const float* T = CUBE_T[face];
+    float P[3];
+    if (xo) {
+        const float sg = u > 0 ? 1.0f : -1.0f, dd = std::fabs(u) - 1.0f;
+        for (int k = 0; k < 3; ++k) P[k] = M[k] * (1.0f - dd) + S[k] * sg + T[k] * v;
+    } else {
+        const float sg = v > 0 ? 1.0f : -1.0f, dd = std::fabs(v) - 1.0f;
+        for (int k = 0; k < 3; ++k) P[k] = M[k] * (1.0f - dd) + S[k] * u + T[k] * sg;
+    }
+    int nf; float ns, nt;
+    cube_face(vec3{P[0], P[1], P[2]}, nf, ns, nt);
+    const Image& nim = d->cube[nf];
+    const int nw = nim.w[level], nh = nim.h[level];
+    const int nx = std::clamp((int)std::floor(ns * (float)nw), 0, nw - 1), ny = std::clamp((int)std::floor(nt * (float)nh), 0, nh - 1);
+    out = fetch_texel(nim, level, nx, ny);
+    return true;
+}
+// LINEAR on a cube face, seamless: taps beyond an edge come from the neighbouring face; the one tap a footprint at a cube
+// corner lacks is the average of the other three ("Cube Map Corner Handling": the texels of the three faces averaged).
+vec4 sample_face_level(const OrkDevice* d, int face, int level, float s, float t) {
+    const Image& im = d->cube[face];
     int w = im.w[level], h = im.h[level];
     float fu = s * (float)w - 0.5f, fv = t * (float)h - 0.5f;
     float iu = std::floor(fu), iv = std::floor(fv);
     float a = fu - iu, b = fv - iv;
-    int x0 = std::clamp((int)iu, 0, w - 1), x1 = std::clamp((int)iu + 1, 0, w - 1);
-    int y0 = std::clamp((int)iv, 0, h - 1), y1 = std::clamp((int)iv + 1, 0, h - 1);
-    vec4 t00 = fetch_texel(im, level, x0, y0), t10 = fetch_texel(im, level, x1, y0);
-    vec4 t01 = fetch_texel(im, level, x0, y1), t11 = fetch_texel(im, level, x1, y1);
+    const int x0 = std::clamp((int)iu, -1, w - 1), y0 = std::clamp((int)iv, -1, h - 1);       // s, t in [0, 1]: at most one texel beyond
+    vec4 tap[4];
+    bool have[4];
+    have[0] = cube_tap(d, face, level, x0, y0, tap[0]);
+    have[1] = cube_tap(d, face, level, x0 + 1, y0, tap[1]);
+    have[2] = cube_tap(d, face, level, x0, y0 + 1, tap[2]);
+    have[3] = cube_tap(d, face, level, x0 + 1, y0 + 1, tap[3]);
+    for (int k = 0; k < 4; ++k)
+        if (!have[k]) {
+            vec4 sum{0, 0, 0, 0};
+            int n = 0;
+            for (int j = 0; j < 4; ++j) if (have[j]) { sum.x += tap[j].x; sum.y += tap[j].y; sum.z += tap[j].z; sum.w += tap[j].w; ++n; }
+            const float inv = n ? 1.0f / (float)n : 0.0f;
+            tap[k] = {sum.x * inv, sum.y * inv, sum.z * inv, sum.w * inv};
+        }
+    const vec4 &t00 = tap[0], &t10 = tap[1], &t01 = tap[2], &t11 = tap[3];
     float w00 = (1.0f - a) * (1.0f - b), w10 = a * (1.0f - b), w01 = (1.0f - a) * b, w11 = a * b;
     return {t00.x * w00 + t10.x * w10 + t01.x * w01 + t11.x * w11,
             t00.y * w00 + t10.y * w10 + t01.y * w01 + t11.y * w11,
@@ -388,7 +438,7 @@ vec4 texture_cube(const OrkDevice* d, vec3 r, vec3 rdx, vec3 rdy) {
     cube_face(r, face, s, t);
     const Image& im = d->cube[face];
     int levels = im.levels();
-    if (levels == 1) return sample_face_level(im, 0, s, t);
+    if (levels == 1) return sample_face_level(d, face, 0, s, t);
     float sx, tx, sy, ty;
     cube_face_fixed(rdx, face, sx, tx);
     cube_face_fixed(rdy, face, sy, ty);
@@ -399,9 +449,9 @@ vec4 texture_cube(const OrkDevice* d, vec3 r, vec3 rdx, vec3 rdy) {
     float lod = clampf(lambda, 0.0f, (float)(levels - 1));
     int l0 = (int)std::floor(lod), l1 = std::min(l0 + 1, levels - 1);
     float f = lod - (float)l0;
-    vec4 c0 = sample_face_level(im, l0, s, t);
+    vec4 c0 = sample_face_level(d, face, l0, s, t);
     if (f == 0.0f) return c0;
-    vec4 c1 = sample_face_level(im, l1, s, t);
+    vec4 c1 = sample_face_level(d, face, l1, s, t);
     return {c0.x * (1.0f - f) + c1.x * f, c0.y * (1.0f - f) + c1.y * f, c0.z * (1.0f - f) + c1.z * f,
             c0.w * (1.0f - f) + c1.w * f};
 }

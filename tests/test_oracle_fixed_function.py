@@ -407,3 +407,42 @@ def test_cube_face_selection_and_orientation(ork_lib):
         assert abs(out[2] * 255 - 40 * f) < 1e-3, f"direction {d} must select face {f}"
         assert abs(out[0] * 255 - 8 * (s * n - 0.5)) < 1e-2 and abs(out[1] * 255 - 8 * (t * n - 0.5)) < 1e-2, (f, out[:])
     r.close()
+
+
+def test_cube_filtering_is_seamless_across_all_twelve_edges(ork_lib):
+    """Vulkan filters cube maps seamlessly ("Cube Map Edge Handling"): a bilinear tap beyond a face edge comes from the face that
+    shares the edge.  Stated without any face table: the filtered colour is CONTINUOUS across an edge — two directions a hair
+    apart on either side of it (which select different faces) must give the same colour — whereas clamping the taps to the
+    selected face jumps by about half the difference of the two faces' edge texels.  Random texels, so that a neighbour
+    addressed with a mirrored or transposed coordinate breaks the continuity too.  (Cube corners, where a tap has no texel,
+    are kept a texel and a half away.)"""
+    r = capi.Renderer(ork_lib, "ork", 16, 16, shadow_extent=16)
+    n = 8
+    rng = np.random.default_rng(7)
+    faces = [np.concatenate([rng.integers(0, 256, (n, n, 3), dtype=np.uint8), np.full((n, n, 1), 255, np.uint8)], -1) for _ in range(6)]
+    r.set_cubemap(faces, capi.FORMAT_UNORM, False)
+    ork_lib.ork_cb_cube.argtypes = [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float)]
+    ork_lib.ork_cb_cube.restype = None
+    ctx = TexCtx(r.dev, (C.c_float * 2)(0, 0), (C.c_float * 2)(0, 0))
+
+    def sample(d):
+        out = (C.c_float * 4)()
+        ork_lib.ork_cb_cube(C.byref(ctx), (C.c_float * 3)(*[float(v) for v in d]), out)
+        return np.array(out[:3], np.float64)
+
+    axes = np.eye(3)
+    edges, jumps = 0, []
+    for i in range(3):
+        for j in range(i + 1, 3):
+            k = 3 - i - j
+            for si in (1.0, -1.0):
+                for sj in (1.0, -1.0):                       # the edge shared by the faces (si * axis i) and (sj * axis j)
+                    edges += 1
+                    for along in (-0.55, -0.2, 0.13, 0.4, 0.6):
+                        d = si * axes[i] + sj * axes[j] + along * axes[k]
+                        eps = 1e-4
+                        a, b = sample(d + eps * si * axes[i]), sample(d + eps * sj * axes[j])
+                        jumps.append(np.abs(a - b).max())
+    assert edges == 12
+    assert max(jumps) < 2e-3, f"colour jumps by {max(jumps):.4f} across a cube edge"
+    r.close()

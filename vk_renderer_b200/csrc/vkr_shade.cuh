@@ -387,16 +387,68 @@ VKR_HD float4 fetch_cube_texel(const DTexture& t, const float* __restrict__ lut,
     }
     return fetch_texel(t, lut, level, x, y, w);
 }
+// A bilinear tap ONE texel beyond an edge of `face` (Vulkan filters cube maps seamlessly): the texel of the face across that
+// edge.  The two faces unfolded flat about the edge, the tap lies as far inside the neighbour as it lay outside this face:
+// with the face written as  major + u * sAxis + v * tAxis  (u = 2s - 1, v = 2t - 1; the selection table read backwards),
+// the tap at |u| = 1 + d is the direction  (1 - d) * major + sign(u) * sAxis + v * tAxis, which is then selected and projected
+// like any other.  False: the tap is beyond two edges — a cube corner, where no texel exists.
 template <int FMT>
-VKR_HD float4 sample_face_level(const DTexture& t, const float* lut, int level, float s, float tt) {
+VKR_HD bool cube_edge_tap(const DTexture* cube, const float* lut, int face, int level, int x, int y, int w, int h, float4& out) {
+    const bool xo = (unsigned)x >= (unsigned)w, yo = (unsigned)y >= (unsigned)h;
+    if (xo && yo) return false;
+    const float u = (float)(2 * x + 1) * frcp((float)w) - 1.0f, v = (float)(2 * y + 1) * frcp((float)h) - 1.0f;
+    const float along = xo ? v : u, beyond = xo ? u : v;
+    const float sg = beyond > 0.0f ? 1.0f : -1.0f, depth = 2.0f - fabsf(beyond);          // 1 - d
+    // (major, sAxis, tAxis) per face as signed unit axes: +X (x, -z, -y), -X (-x, z, -y), +Y (y, x, z), -Y (-y, x, -z), +Z (z, x, -y), -Z (-z, -x, -y)
+    const float a0 = depth, a1 = xo ? sg : along, a2 = xo ? along : sg;                      // coefficients of major, sAxis, tAxis
+    f3 r;
+    switch (face) {
+        case 0: r = {a0, -a2, -a1}; break;
+        case 1: r = {-a0, -a2, a1}; break;
+        case 2: r = {a1, a0, a2}; break;
+        case 3: r = {a1, -a0, -a2}; break;
+        case 4: r = {a1, -a2, a0}; break;
+        default: r = {-a1, -a2, -a0}; break;
+    }
+    const int nf = cube_select(r);
+    float ns, nt;
+    cube_project(r, nf, ns, nt);
+    const DTexture& t = cube[nf];
+    const int nw = level_dim(t.w, level), nh = level_dim(t.h, level);
+    out = fetch_cube_texel<FMT>(t, lut, level, clampi((int)floorf(ns * (float)nw), 0, nw - 1), clampi((int)floorf(nt * (float)nh), 0, nh - 1), nw);
+    return true;
+}
+template <int FMT>
+VKR_HD float4 sample_face_level(const DTexture* cube, int face, const float* lut, int level, float s, float tt) {
+    const DTexture& t = cube[face];
     const int w = level_dim(t.w, level), h = level_dim(t.h, level);
     float fu = s * (float)w - 0.5f, fv = tt * (float)h - 0.5f;
     float iu = floorf(fu), iv = floorf(fv);
     float a = fu - iu, b = fv - iv;
-    int x0 = clampi((int)iu, 0, w - 1), x1 = clampi((int)iu + 1, 0, w - 1);
-    int y0 = clampi((int)iv, 0, h - 1), y1 = clampi((int)iv + 1, 0, h - 1);
-    float4 t00 = fetch_cube_texel<FMT>(t, lut, level, x0, y0, w), t10 = fetch_cube_texel<FMT>(t, lut, level, x1, y0, w);
-    float4 t01 = fetch_cube_texel<FMT>(t, lut, level, x0, y1, w), t11 = fetch_cube_texel<FMT>(t, lut, level, x1, y1, w);
+    const int x0 = clampi((int)iu, -1, w - 1), y0 = clampi((int)iv, -1, h - 1);
+    float4 t00, t10, t01, t11;
+    if (x0 >= 0 && y0 >= 0 && x0 + 1 < w && y0 + 1 < h) {          // the whole footprint on this face: every pixel but those on a seam
+        t00 = fetch_cube_texel<FMT>(t, lut, level, x0, y0, w); t10 = fetch_cube_texel<FMT>(t, lut, level, x0 + 1, y0, w);
+        t01 = fetch_cube_texel<FMT>(t, lut, level, x0, y0 + 1, w); t11 = fetch_cube_texel<FMT>(t, lut, level, x0 + 1, y0 + 1, w);
+    } else {
+        float4 tap[4];
+        bool have[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int x = x0 + (k & 1), y = y0 + (k >> 1);
+            if ((unsigned)x < (unsigned)w && (unsigned)y < (unsigned)h) { tap[k] = fetch_cube_texel<FMT>(t, lut, level, x, y, w); have[k] = true; }
+            else have[k] = cube_edge_tap<FMT>(cube, lut, face, level, x, y, w, h, tap[k]);
+        }
+        // a footprint at a cube corner lacks one tap: the average of the other three (Vulkan "Cube Map Corner Handling")
+        float4 sum = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        float n = 0.0f;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) if (have[k]) { sum.x += tap[k].x; sum.y += tap[k].y; sum.z += tap[k].z; sum.w += tap[k].w; n += 1.0f; }
+        const float inv = n > 0.0f ? 1.0f / n : 0.0f;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) if (!have[k]) tap[k] = make_float4(sum.x * inv, sum.y * inv, sum.z * inv, sum.w * inv);
+        t00 = tap[0]; t10 = tap[1]; t01 = tap[2]; t11 = tap[3];
+    }
     float w00 = (1.0f - a) * (1.0f - b), w10 = a * (1.0f - b), w01 = (1.0f - a) * b, w11 = a * b;
     return make_float4(t00.x * w00 + t10.x * w10 + t01.x * w01 + t11.x * w11,
                        t00.y * w00 + t10.y * w10 + t01.y * w01 + t11.y * w11,
@@ -407,7 +459,7 @@ template <int FMT>
 VKR_HD float4 texture_cube_fmt(const ShadeBuffers& sb, f3 r, f3 rdx, f3 rdy, int face, float s, float t) {
     const DTexture& tex = sb.cube[face];
     const int levels = (int)tex.levels;
-    if (levels == 1) return sample_face_level<FMT>(tex, sb.srgbLut, 0, s, t);
+    if (levels == 1) return sample_face_level<FMT>(sb.cube, face, sb.srgbLut, 0, s, t);
     float sx, tx, sy, ty;
     cube_project(rdx, face, sx, tx);
     cube_project(rdy, face, sy, ty);
@@ -417,9 +469,9 @@ VKR_HD float4 texture_cube_fmt(const ShadeBuffers& sb, f3 r, f3 rdx, f3 rdy, int
     int l0 = (int)floorf(lod);
     int l1 = l0 + 1 < levels ? l0 + 1 : levels - 1;
     float f = lod - (float)l0;
-    float4 c0 = sample_face_level<FMT>(tex, sb.srgbLut, l0, s, t);
+    float4 c0 = sample_face_level<FMT>(sb.cube, face, sb.srgbLut, l0, s, t);
     if (f == 0.0f) return c0;
-    float4 c1 = sample_face_level<FMT>(tex, sb.srgbLut, l1, s, t);
+    float4 c1 = sample_face_level<FMT>(sb.cube, face, sb.srgbLut, l1, s, t);
     return make_float4(c0.x * (1.0f - f) + c1.x * f, c0.y * (1.0f - f) + c1.y * f, c0.z * (1.0f - f) + c1.z * f,
                        c0.w * (1.0f - f) + c1.w * f);
 }
