@@ -269,3 +269,94 @@ def test_gltf_with_a_jpeg_texture_loads_it(ork_lib, tmp_path):
         frames.append(e.readback(capi.TARGET_RGBA8))
         e.close()
     assert np.array_equal(frames[0], frames[1])
+
+
+def _make_sparse(path, out_path, rng):
+    """Rewrite an 'external' .gltf so that (a) every POSITION accessor becomes a sparse one over a CORRUPTED copy of its data —
+    a third of the elements zeroed in the base buffer view and restored through sparse.indices / sparse.values — and (b) every
+    index accessor becomes a sparse accessor WITHOUT a buffer view (all zeros) whose sparse part supplies every element.  What
+    the file describes is unchanged."""
+    import json, os, urllib.parse
+    g = json.load(open(path))
+    bin_path = os.path.join(os.path.dirname(path), urllib.parse.unquote(g["buffers"][0]["uri"]))
+    blob = bytearray(open(bin_path, "rb").read())
+
+    def add_view(data):
+        while len(blob) % 4:
+            blob.append(0)
+        g["bufferViews"].append({"buffer": 0, "byteOffset": len(blob), "byteLength": len(data)})
+        blob.extend(data)
+        return len(g["bufferViews"]) - 1
+
+    def dense(acc):
+        v = g["bufferViews"][acc["bufferView"]]
+        comps = {"SCALAR": 1, "VEC3": 3}[acc["type"]]
+        dt = {5121: "<u1", 5123: "<u2", 5125: "<u4", 5126: "<f4"}[acc["componentType"]]
+        elem = np.dtype(dt).itemsize * comps
+        stride = v.get("byteStride", elem)
+        start = v.get("byteOffset", 0) + acc.get("byteOffset", 0)
+        rows = [bytes(blob[start + i * stride: start + i * stride + elem]) for i in range(acc["count"])]
+        return np.frombuffer(b"".join(rows), dt).reshape(acc["count"], comps).copy(), dt
+
+    pos_ids, idx_ids = set(), set()
+    for m in g["meshes"]:
+        for p in m["primitives"]:
+            pos_ids.add(p["attributes"]["POSITION"])
+            if "indices" in p:
+                idx_ids.add(p["indices"])
+    for k in sorted(pos_ids):
+        acc = g["accessors"][k]
+        data, dt = dense(acc)
+        n = len(data)
+        which = np.sort(rng.choice(n, max(1, n // 3), replace=False))
+        broken = data.copy()
+        broken[which] = 0
+        acc["bufferView"], acc.pop("byteOffset", None)
+        acc["bufferView"] = add_view(broken.astype(dt).tobytes())
+        it = 5123 if n < 65536 else 5125
+        acc["sparse"] = {"count": int(len(which)),
+                         "indices": {"bufferView": add_view(which.astype("<u2" if it == 5123 else "<u4").tobytes()), "componentType": it},
+                         "values": {"bufferView": add_view(data[which].astype(dt).tobytes())}}
+    for k in sorted(idx_ids):
+        acc = g["accessors"][k]
+        data, dt = dense(acc)
+        n = len(data)
+        del acc["bufferView"]
+        acc.pop("byteOffset", None)
+        acc["sparse"] = {"count": n, "indices": {"bufferView": add_view(np.arange(n, dtype="<u4").tobytes()), "componentType": 5125},
+                         "values": {"bufferView": add_view(data.astype(dt).tobytes())}}
+    g["buffers"][0]["byteLength"] = len(blob)
+    open(bin_path, "wb").write(bytes(blob))
+    json.dump(g, open(out_path, "w"))
+    return out_path
+
+
+def test_sparse_accessors_are_resolved(ork_lib, tmp_path):
+    """glTF 2.0 sparse accessors (fastgltf's iterateAccessor, which the reference reads every attribute through, resolves them):
+    the same scene written with sparse POSITION and index accessors must load to the same frame, bit for bit."""
+    import os
+    asset = gu.build_asset(np.random.default_rng(11))
+    frames = []
+    for sub, sparse in (("dense", False), ("sparse", True)):
+        d = tmp_path / sub
+        path = gu.write_gltf(asset, str(d), "external")
+        if sparse:
+            path = _make_sparse(path, os.path.join(str(d), "sparse.gltf"), np.random.default_rng(5))
+        e, tris = _engine(ork_lib, "ork", path)
+        e.draw()
+        frames.append((tris, {k: e.readback(v) for k, v in dict(rgba=capi.TARGET_RGBA8, depth=capi.TARGET_DEPTH, prim=capi.TARGET_PRIMID).items()}))
+        e.close()
+    assert frames[0][0] == frames[1][0] and frames[0][0] > 0
+    assert (frames[0][1]["prim"] != 0xFFFFFFFF).mean() > 0.02
+    for k in frames[0][1]:
+        assert np.array_equal(frames[0][1][k].view(np.uint8), frames[1][1][k].view(np.uint8)), k
+    # a sparse index beyond the accessor is refused
+    import json
+    g = json.load(open(os.path.join(str(tmp_path / "sparse"), "sparse.gltf")))
+    acc = next(a for a in g["accessors"] if "sparse" in a and a["type"] == "VEC3")
+    acc["count"] = 1
+    json.dump(g, open(os.path.join(str(tmp_path / "sparse"), "bad.gltf"), "w"))
+    e = Engine(W, H, api_lib=ork_lib, api_prefix="ork", shadow_extent=S)
+    with pytest.raises(RuntimeError):
+        e.load_gltf(os.path.join(str(tmp_path / "sparse"), "bad.gltf"))
+    e.close()

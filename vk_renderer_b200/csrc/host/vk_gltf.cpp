@@ -7,6 +7,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <deque>
 #include <limits>
 #include <utility>
 
@@ -291,6 +292,7 @@ struct Document {
     std::string baseDir;
     std::vector<std::vector<unsigned char>> buffers;
     std::vector<unsigned char> glbBin;
+    std::deque<std::vector<unsigned char>> dense;      // sparse accessors made dense (a deque: AccessorView keeps pointers into them)
     std::string err;
 };
 
@@ -359,7 +361,6 @@ bool accessor_view(Document& d, long index, AccessorView& out) {
     const auto& accs = d.root.array("accessors");
     if (index < 0 || (size_t)index >= accs.size()) return fail(d, "accessor index out of range");
     const Json& a = accs[(size_t)index];
-    if (a.has("sparse")) return fail(d, "sparse accessors are not supported");
     out.componentType = (int)a.integer("componentType", 0);
     out.components = type_components(a.string("type"));
     out.count = (size_t)a.integer("count", 0);
@@ -368,13 +369,45 @@ bool accessor_view(Document& d, long index, AccessorView& out) {
     const int cs = component_size(out.componentType);
     if (!cs || !out.components) return fail(d, "accessor has an unknown component type or element type");
     const size_t elem = (size_t)cs * out.components;
-    if (!a.has("bufferView")) return fail(d, "accessor without a bufferView");
-    const unsigned char* p; size_t len, bs;
-    if (!view_bytes(d, a.integer("bufferView", -1), &p, &len, &bs)) return false;
-    const size_t off = (size_t)a.integer("byteOffset", 0);
-    out.stride = bs ? bs : elem;
-    if (out.count && off + (out.count - 1) * out.stride + elem > len) return fail(d, "accessor exceeds its bufferView");
-    out.base = p + off;
+    const Json* sparse = a.find("sparse");
+    if (!a.has("bufferView") && !sparse) return fail(d, "accessor without a bufferView");
+    const unsigned char* p = nullptr; size_t len = 0, bs = 0, off = 0;
+    if (a.has("bufferView")) {
+        if (!view_bytes(d, a.integer("bufferView", -1), &p, &len, &bs)) return false;
+        off = (size_t)a.integer("byteOffset", 0);
+        out.stride = bs ? bs : elem;
+        if (out.count && off + (out.count - 1) * out.stride + elem > len) return fail(d, "accessor exceeds its bufferView");
+        out.base = p + off;
+    }
+    if (!sparse) return true;
+    // A sparse accessor (glTF 2.0, 3.6.2.3; fastgltf's iterateAccessor resolves it the same way): the elements of the buffer view —
+    // zeros without one — with `count` of them replaced: element indices[k] takes values[k].  Made dense once, tightly packed.
+    if (sparse->type != Json::Object) return fail(d, "accessor.sparse is not an object");
+    d.dense.emplace_back(out.count * elem, (unsigned char)0);
+    std::vector<unsigned char>& dense = d.dense.back();
+    if (out.base)
+        for (size_t i = 0; i < out.count; ++i) std::memcpy(dense.data() + i * elem, out.base + i * out.stride, elem);
+    const size_t n = (size_t)sparse->integer("count", 0);
+    const Json* ji = sparse->find("indices");
+    const Json* jv = sparse->find("values");
+    if (!ji || !jv || ji->type != Json::Object || jv->type != Json::Object) return fail(d, "sparse accessor without indices or values");
+    const int ict = (int)ji->integer("componentType", 0);
+    const size_t ics = ict == 5121 ? 1 : ict == 5123 ? 2 : ict == 5125 ? 4 : 0;
+    if (!ics) return fail(d, "sparse accessor indices must be unsigned bytes, shorts or ints");
+    const unsigned char *ip, *vp; size_t ilen, vlen;
+    if (!view_bytes(d, ji->integer("bufferView", -1), &ip, &ilen, nullptr) || !view_bytes(d, jv->integer("bufferView", -1), &vp, &vlen, nullptr)) return false;
+    const size_t ioff = (size_t)ji->integer("byteOffset", 0), voff = (size_t)jv->integer("byteOffset", 0);
+    if (ioff + n * ics > ilen || voff + n * elem > vlen) return fail(d, "sparse accessor exceeds its bufferViews");
+    for (size_t k = 0; k < n; ++k) {
+        size_t idx = 0;
+        if (ics == 1) idx = ip[ioff + k];
+        else if (ics == 2) { uint16_t v; std::memcpy(&v, ip + ioff + 2 * k, 2); idx = v; }
+        else { uint32_t v; std::memcpy(&v, ip + ioff + 4 * k, 4); idx = v; }
+        if (idx >= out.count) return fail(d, "sparse accessor index out of range");
+        std::memcpy(dense.data() + idx * elem, vp + voff + k * elem, elem);
+    }
+    out.base = dense.data();
+    out.stride = elem;
     return true;
 }
 
