@@ -309,6 +309,52 @@ size_t vkr_upload_bytes(VkrDevice* dev);
  * test (src/vk_engine_run.cpp:461-480); this one is per 128-triangle cluster and never changes the image. */
 int vkr_cull_stats(VkrDevice* dev, uint32_t out[4]);
 
+/* ---- update_scene on the device ---------------------------------------------------------------
+ * The reference walks its scene graph on the CPU every frame: Node::refreshTransform (src/vk_types.h:148-163) multiplies
+ * every node's matrix and emits one RenderObject per mesh surface, update_scene (src/vk_engine_run.cpp:435-459) tests each
+ * with is_visible (:461-480) and sorts the survivors MainColor-first; draw_geometry / draw_shadow then record one draw per
+ * object.  With the calls below the graph is handed over ONCE and all of that per-object work runs in kernels: the host's
+ * share of a frame is a constant number of launches and no upload, whatever the number of objects. */
+typedef uint32_t VkrScene;            /* handle: a flattened scene graph (_sceneRoot and everything under it) */
+
+/* struct Node (src/vk_types.h:139-169), flattened in the order refreshTransform visits the nodes (a parent before its
+ * children).  parent = -1: the node is refreshed with mat4(1), like _sceneRoot (src/vk_engine_run.cpp:441). */
+typedef struct VkrSceneNode {
+    float localTransform[16];  /* column-major */
+    int32_t parent;            /* index into the node array, < this node's index; -1: none */
+} VkrSceneNode;
+
+/* One RenderObject as refreshTransform emits it (src/vk_types.h:152-161): a surface of the node's mesh, with the mesh's
+ * bounds (struct Bounds, src/vk_types.h:112-116) that is_visible tests.  Array order = the order of emission. */
+typedef struct VkrSceneSurface {
+    uint32_t node;             /* the node whose worldTransform the object takes */
+    VkrMesh mesh;
+    VkrMaterial material;
+    uint32_t indexCount;
+    uint32_t firstIndex;
+    float boundsOrigin[3];     /* MeshAsset::bounds.origin */
+    float boundsSphereRadius;  /* MeshAsset::bounds.sphereRadius */
+} VkrSceneSurface;
+
+/* Validates and uploads the graph, builds the clusters of every surface's index range.  The draw order of the scene is the
+ * reference's: order of emission, MainColor materials first (stable) — what update_scene's sort leaves (:454-458). */
+int vkr_scene_create(VkrDevice* dev, const VkrSceneNode* nodes, size_t nodeCount,
+                     const VkrSceneSurface* surfaces, size_t surfaceCount, VkrScene* out);
+/* Node::localTransform of `count` nodes starting at firstNode changed (count * 16 floats); the next vkr_draw_scene
+ * recomputes the world matrices on the device. */
+int vkr_scene_set_transforms(VkrDevice* dev, VkrScene scene, uint32_t firstNode, uint32_t count, const float* localTransforms);
+/* update_scene + draw (src/vk_engine_run.cpp:435-459 + :140-161,234-408) of one frame.  frustumPlanes: the six planes of
+ * extract_frustum_planes(viewproj) (:420-433), 4 floats each — O(1) host work, like the light matrices in sceneData.
+ * An object is_visible rejects takes part in no pass (the reference culls against the CAMERA frustum before the shadow pass
+ * too); the image, depth, primitive ids and shadow map equal those of vkr_draw with the draw list update_scene would have
+ * produced.  Asynchronous like vkr_draw.  Not available on a sharded device (vkr_shard_init). */
+int vkr_draw_scene(VkrDevice* dev, VkrScene scene, const VkrGPUSceneData* sceneData, const float frustumPlanes[24],
+                   const VkrFrameParams* params);
+/* The draw list of the last vkr_draw_scene frame as update_scene would have left it in _renderObjects: the objects
+ * is_visible kept, with their world matrices, in submission order.  Blocks until the frame's scene kernels have run.
+ * out may be NULL (count only); at most `capacity` records are written, *count is the full number. */
+int vkr_scene_draw_list(VkrDevice* dev, VkrScene scene, VkrRenderObject* out, size_t capacity, size_t* count);
+
 /* No counterpart in the reference: added for callers that cannot
  * call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
  * Packs a width*height RGBA8 image in DEVICE memory (e.g. vkr_device_ptr(VKR_TARGET_RGBA8), 16-byte aligned)

@@ -19,6 +19,7 @@
 #include "../../vk_renderer_b200/csrc/vkr_raster.cuh"
 #include "../../vk_renderer_b200/csrc/vkr_shade.cuh"
 #include "../../vk_renderer_b200/csrc/vkr_frameprep.h"
+#include "../../vk_renderer_b200/csrc/vkr_scene.cuh"
 
 using namespace vkr;
 
@@ -36,8 +37,21 @@ struct EmuClusters : ClusterProvider {
     ~EmuClusters() { for (auto* c : store) delete c; }
 };
 
+// vkr_scene_create's record (the device library's SceneRec, host arrays instead of device ones)
+struct EmuScene {
+    std::vector<float> local, world;
+    std::vector<int32_t> parent;
+    std::vector<VkrSceneSurface> surfaces;      // draw order: emission order, MainColor first
+    std::vector<SceneDraw> draws;
+    std::vector<DObject> tmpl;
+    std::vector<uint32_t> clusterBase, seqSlotBase;
+    uint32_t opaqueCount = 0, opaqueClusters = 0, totalTris = 0;
+};
+
 struct EmuDevice {
     uint32_t W, H, S;
+    std::vector<EmuScene*> scenes;
+    EmuScene* lastScene = nullptr;
     EmuClusters clusters;
     std::vector<EmuMesh*> meshStore;
     std::vector<DMesh> meshes;
@@ -155,6 +169,7 @@ void emu_destroy(EmuDevice* d) {
     if (!d) return;
     for (auto* m : d->meshStore) delete m;
     for (auto* i : d->images) delete i;
+    for (auto* sc : d->scenes) delete sc;
     delete d;
 }
 int emu_upload_mesh(EmuDevice* d, const uint32_t* idx, size_t ni, const VkrVertex* v, size_t nv, uint32_t* out) {
@@ -259,6 +274,7 @@ static void run_pass(EmuDevice* d, const FramePlan& plan, RasterTarget rt, const
     for (unsigned slot = 0; slot < nChunks; ++slot) {        // geometry_kernel: one CTA per cluster, in processing order
         const uint32_t ci = perm ? perm[slot] : first + slot;
         const DChunk ch = d->chunks[ci];
+        if (ch.flags & DRAW_HIDDEN) continue;                  // expand_chunks_kernel: a hidden draw's clusters are culled in every list
         if (PASS == 0 && (ch.flags & 2u)) continue;
         const float* mvp = mvps + (size_t)ch.obj * stride;
         const DObject& ob = plan.objects[ch.obj];
@@ -304,11 +320,22 @@ static void run_pass(EmuDevice* d, const FramePlan& plan, RasterTarget rt, const
 
 extern "C" {
 
+static int emu_execute(EmuDevice* d, size_t n);
+
 int emu_draw(EmuDevice* d, const VkrGPUSceneData* scene, const VkrRenderObject* objs, size_t n, const VkrFrameParams* fp) {
     FramePlan& plan = d->plan;
     for (DMaterial& m : d->materials) material_constants(m, d->tex.data(), d->lut);
     std::string why = plan_frame(scene, objs, n, fp, d->meshes, d->materials, d->tex, d->clusters, d->W, d->H, d->S, plan, d->shardRank, d->shardRanks);
     if (!why.empty()) { d->err = why; return VKR_ERROR_INVALID_ARGUMENT; }
+    d->lastScene = nullptr;
+    const int rc = emu_execute(d, n);
+    d->stats.drawcall_count = (int)n; d->stats.triangle_count = (int)plan.totalTris;
+    return rc;
+}
+
+// Everything behind the plan: expand_chunks_kernel, the raster passes, the shading pass.
+static int emu_execute(EmuDevice* d, size_t n) {
+    FramePlan& plan = d->plan;
     const unsigned nChunks = plan.clusterBase[n];
     d->chunks.resize(nChunks);
     d->chunkObj.resize(plan.seqSlotBase[n]);
@@ -356,7 +383,117 @@ int emu_draw(EmuDevice* d, const VkrGPUSceneData* scene, const VkrRenderObject* 
     }
     for (int py = plan.sc.sy0; py < plan.sc.sy1; ++py)
         for (int px = plan.sc.sx0; px < plan.sc.sx1; ++px) shade_pixel(plan.sc, sb, px, py);
-    d->stats.drawcall_count = (int)n; d->stats.triangle_count = (int)plan.totalTris;
+    return 0;
+}
+
+// ---- update_scene on the device (vkr_scene_create / vkr_draw_scene): the same per-thread bodies (vkr_scene.cuh) as loops
+int emu_scene_create(EmuDevice* d, const VkrSceneNode* nodes, size_t nn, const VkrSceneSurface* surfaces, size_t ns, uint32_t* out) {
+    if (!nodes || !nn || !out) return VKR_ERROR_INVALID_ARGUMENT;
+    EmuScene* s = new EmuScene();
+    s->local.resize(nn * 16); s->world.assign(nn * 16, 0.0f); s->parent.resize(nn);
+    for (size_t i = 0; i < nn; ++i) {
+        if (nodes[i].parent < -1 || nodes[i].parent >= (int32_t)i) { delete s; return VKR_ERROR_INVALID_ARGUMENT; }
+        std::memcpy(&s->local[i * 16], nodes[i].localTransform, 64); s->parent[i] = nodes[i].parent;
+    }
+    for (size_t i = 0; i < ns; ++i)
+        if (surfaces[i].node >= nn || surfaces[i].mesh >= d->meshes.size() || surfaces[i].material >= d->materials.size() ||
+            (uint64_t)surfaces[i].firstIndex + surfaces[i].indexCount > d->meshes[surfaces[i].mesh].ni) { delete s; return VKR_ERROR_INVALID_ARGUMENT; }
+    for (int pass = 0; pass < 2; ++pass)
+        for (size_t i = 0; i < ns; ++i)
+            if ((d->materials[surfaces[i].material].pass == VKR_PASS_TRANSPARENT) == (pass == 1)) s->surfaces.push_back(surfaces[i]);
+    while (s->opaqueCount < ns && d->materials[s->surfaces[s->opaqueCount].material].pass != VKR_PASS_TRANSPARENT) s->opaqueCount++;
+    s->draws.resize(ns); s->tmpl.resize(ns); s->clusterBase.resize(ns + 1); s->seqSlotBase.resize(ns + 1);
+    uint32_t ncl = 0, nslot = 0, prim = 0;
+    for (size_t i = 0; i < ns; ++i) {
+        const VkrSceneSurface& sf = s->surfaces[i];
+        const DMesh& m = d->meshes[sf.mesh];
+        DObject& o = s->tmpl[i];
+        std::memset(&o, 0, sizeof(o));
+        o.pos = m.pos; o.attrA = m.attrA; o.attrB = m.attrB; o.idx = m.idx + sf.firstIndex; o.triCount = sf.indexCount / 3;
+        ClusterRange cr{};
+        if (o.triCount) d->clusters.get(sf.mesh, sf.firstIndex, sf.indexCount, cr);
+        o.clVerts = cr.verts; o.clTris = cr.tris; o.clOrig = cr.orig; o.clInfo = cr.info; o.clBounds = cr.bounds; o.clBlob = cr.blob; o.clCone = cr.cone;
+        o.material = sf.material;
+        SceneDraw& sd = s->draws[i];
+        std::memset(&sd, 0, sizeof(sd));
+        sd.node = sf.node; sd.nClusters = o.triCount ? cr.nClusters : 0u;
+        std::memcpy(sd.origin, sf.boundsOrigin, 12); sd.sphereRadius = sf.boundsSphereRadius;
+        std::memcpy(sd.center, cr.center, 12); sd.radius = cr.radius;
+        s->clusterBase[i] = ncl; s->seqSlotBase[i] = nslot;
+        ncl += sd.nClusters; nslot += (o.triCount + SEQ_SLOT - 1) / SEQ_SLOT; prim += o.triCount;
+        if (i + 1 == s->opaqueCount) s->opaqueClusters = ncl;
+    }
+    s->clusterBase[ns] = ncl; s->seqSlotBase[ns] = nslot; s->totalTris = prim;
+    d->scenes.push_back(s);
+    *out = (uint32_t)d->scenes.size() - 1;
+    return 0;
+}
+int emu_scene_set_transforms(EmuDevice* d, uint32_t scene, uint32_t first, uint32_t count, const float* local) {
+    if (scene >= d->scenes.size() || (uint64_t)first + count > d->scenes[scene]->parent.size()) return VKR_ERROR_INVALID_ARGUMENT;
+    if (count) std::memcpy(&d->scenes[scene]->local[(size_t)first * 16], local, (size_t)count * 64);
+    return 0;
+}
+int emu_draw_scene(EmuDevice* d, uint32_t scene, const VkrGPUSceneData* sceneData, const float* planes, const VkrFrameParams* fp) {
+    if (scene >= d->scenes.size()) return VKR_ERROR_INVALID_ARGUMENT;
+    EmuScene& s = *d->scenes[scene];
+    FramePlan& plan = d->plan;
+    for (DMaterial& m : d->materials) material_constants(m, d->tex.data(), d->lut);
+    const size_t n = s.draws.size();
+    plan.shadowLayers = fp->enableShadows ? (fp->shadowMode < 3 ? 1 : VKR_NUM_CASCADES) : 0;
+    const uint32_t passes = 1u + (uint32_t)plan.shadowLayers;
+    SceneFrame f;
+    std::memcpy(f.viewproj, sceneData->viewproj, 64);
+    std::memcpy(f.lightViewproj, sceneData->lightViewproj, sizeof(f.lightViewproj));
+    std::memcpy(f.planes, planes, 96);
+    f.nDraws = (uint32_t)n; f.opaqueCount = s.opaqueCount; f.shadowLayers = (uint32_t)plan.shadowLayers; f.pad = 0;
+    for (size_t i = 0; i < s.parent.size(); ++i) scene_node_world(s.local.data(), s.parent.data(), s.world.data(), (uint32_t)i);   // scene_nodes_kernel (any parents-first order)
+    plan.objects.resize(n); plan.shadowMvp.assign((size_t)plan.shadowLayers * n * 16, 0.0f);
+    std::vector<float> keys((size_t)passes * n);
+    std::vector<uint32_t> visTris(n), order((size_t)passes * n, 0u);
+    for (size_t i = 0; i < n; ++i) {                           // scene_draws_kernel
+        s.tmpl[i].flags = draw_flags(d->materials[s.surfaces[i].material], d->tex);
+        scene_draw_body(f, s.draws[i], s.world.data(), s.tmpl[i], (uint32_t)i, plan.objects[i], plan.shadowMvp.data(), keys.data(), visTris.data());
+    }
+    plan.slotBase.assign((size_t)passes * n, 0xFFFFFFFFu);
+    plan.passSlots.assign(passes, 0u);
+    uint32_t shown = 0, tris = 0;
+    plan.anyCutout = false;
+    for (size_t i = 0; i < n; ++i) {                           // scene_scan_kernel, first part
+        plan.objects[i].primBase = tris; tris += visTris[i];
+        if (!(plan.objects[i].flags & DRAW_HIDDEN)) shown++;
+        if (plan.objects[i].flags & 2u) plan.anyCutout = true;
+    }
+    for (uint32_t p = 0; p < passes; ++p) {                    // scene_rank_kernel, then scene_scan_kernel's per-pass part
+        const uint32_t count = p == 0 ? s.opaqueCount : (uint32_t)n;
+        for (uint32_t i = 0; i < count; ++i) order[(size_t)p * n + scene_rank(keys.data() + (size_t)p * n, count, i)] = i;
+        uint32_t slot = 0;
+        for (uint32_t k = 0; k < count; ++k) { const uint32_t o = order[(size_t)p * n + k]; plan.slotBase[(size_t)p * n + o] = slot; slot += s.draws[o].nClusters; }
+        plan.passSlots[p] = slot;
+    }
+    plan.clusterBase = s.clusterBase; plan.seqSlotBase = s.seqSlotBase;
+    plan.primBase.assign(n + 1, 0u);
+    plan.opaqueCount = s.opaqueCount; plan.opaqueClusters = s.opaqueClusters; plan.totalTris = s.totalTris;
+    plan.bandMain.assign(1, 0); plan.bandShadow.assign(1, 0);
+    plan_constants(sceneData, fp, d->W, d->H, d->S, n, plan);
+    d->lastScene = &s;
+    const int rc = emu_execute(d, n);
+    d->stats.drawcall_count = (int)shown; d->stats.triangle_count = (int)tris;
+    return rc;
+}
+int emu_scene_draw_list(EmuDevice* d, uint32_t scene, VkrRenderObject* out, size_t capacity, size_t* count) {
+    if (scene >= d->scenes.size() || d->lastScene != d->scenes[scene] || !count) return VKR_ERROR_INVALID_ARGUMENT;
+    const EmuScene& s = *d->scenes[scene];
+    size_t k = 0;
+    for (size_t i = 0; i < s.draws.size(); ++i) {
+        if (d->plan.objects[i].flags & DRAW_HIDDEN) continue;
+        if (k < capacity) {
+            out[k].mesh = s.surfaces[i].mesh; out[k].material = s.surfaces[i].material;
+            std::memcpy(out[k].transform, d->plan.objects[i].world, 64);
+            out[k].indexCount = s.surfaces[i].indexCount; out[k].firstIndex = s.surfaces[i].firstIndex;
+        }
+        ++k;
+    }
+    *count = k;
     return 0;
 }
 int emu_readback(EmuDevice* d, int what, void* dst, size_t bytes) {

@@ -117,12 +117,19 @@ class EngineStats(C.Structure):
 
 PACK_STATIC_MAX_BYTES = 6 << 20     # VKR_PACK_STATIC_MAX_BYTES
 
+# struct VkrSceneNode / VkrSceneSurface (include/vkr.h): the flattened scene graph vkr_scene_create takes
+SCENE_NODE_DTYPE = np.dtype([("localTransform", "<f4", 16), ("parent", "<i4")])
+SCENE_SURFACE_DTYPE = np.dtype([("node", "<u4"), ("mesh", "<u4"), ("material", "<u4"), ("indexCount", "<u4"), ("firstIndex", "<u4"),
+                                ("boundsOrigin", "<f4", 3), ("boundsSphereRadius", "<f4")])
+assert SCENE_NODE_DTYPE.itemsize == 68 and SCENE_SURFACE_DTYPE.itemsize == 36
+
 # every symbol include/vkr.h declares (tests check the library exports them all)
 VKR_SYMBOLS = [
     "create", "destroy", "upload_mesh", "create_image", "update_bindless_texture", "set_cubemap", "set_cubemap_levels",
     "build_material", "draw", "readback", "readback_async", "sync", "stats", "get_timings",
     "set_flags", "device_ptr", "launch_count", "upload_bytes", "cull_stats", "set_shadow_exchange", "comm_unique_id", "shard_init", "last_error", "version",
     "readback_band_async", "shard_info", "pack_rgb8_static", "host_times",
+    "scene_create", "scene_set_transforms", "draw_scene", "scene_draw_list",
 ]
 
 
@@ -230,11 +237,18 @@ class Renderer:
             })
         if self.prefix == "emu":     # the test-only host emulation (tests/emu) exposes the sharding hooks too
             sigs.update({"set_shadow_exchange": ([p, SHADOW_EXCHANGE_FN, p], C.c_int), "host_ptr": ([p, C.c_int], C.c_void_p)})
+        if self.prefix in ("vkr", "emu"):     # update_scene on the device
+            sigs.update({
+                "scene_create": ([p, p, C.c_size_t, p, C.c_size_t, C.POINTER(C.c_uint32)], C.c_int),
+                "scene_set_transforms": ([p, C.c_uint32, C.c_uint32, C.c_uint32, p], C.c_int),
+                "draw_scene": ([p, C.c_uint32, C.POINTER(GPUSceneData), C.POINTER(C.c_float), C.POINTER(FrameParams)], C.c_int),
+                "scene_draw_list": ([p, C.c_uint32, p, C.c_size_t, C.POINTER(C.c_size_t)], C.c_int),
+            })
         for name, (args, res) in sigs.items():
             try:
                 fn = self._f(name)
             except AttributeError:
-                if name in ("host_times", "pack_rgb8_static"):      # an older library variant in an A/B run (tools/run_ab.sh)
+                if name in ("host_times", "pack_rgb8_static", "scene_create", "scene_set_transforms", "draw_scene", "scene_draw_list"):      # an older library variant in an A/B run (tools/run_ab.sh)
                     continue
                 raise
             fn.argtypes, fn.restype = args, res
@@ -302,6 +316,30 @@ class Renderer:
     def draw(self, scene: GPUSceneData, objects: np.ndarray, params: FrameParams):
         objs = np.ascontiguousarray(objects, dtype=RENDER_OBJECT_DTYPE)
         self._check(self._f("draw")(self.dev, C.byref(scene), objs.ctypes.data, objs.size, C.byref(params)))
+
+    # ---- update_scene on the device (include/vkr.h: vkr_scene_create ...)
+    def scene_create(self, nodes: np.ndarray, surfaces: np.ndarray) -> int:
+        nd = np.ascontiguousarray(nodes, dtype=SCENE_NODE_DTYPE)
+        sf = np.ascontiguousarray(surfaces, dtype=SCENE_SURFACE_DTYPE)
+        out = C.c_uint32()
+        self._check(self._f("scene_create")(self.dev, nd.ctypes.data, nd.size, sf.ctypes.data, sf.size, C.byref(out)))
+        return out.value
+
+    def scene_set_transforms(self, scene: int, first_node: int, local_colmajor: np.ndarray):
+        m = np.ascontiguousarray(local_colmajor, dtype=np.float32).reshape(-1, 16)
+        self._check(self._f("scene_set_transforms")(self.dev, scene, first_node, m.shape[0], m.ctypes.data))
+
+    def draw_scene(self, scene: int, scene_data: GPUSceneData, planes: np.ndarray, params: FrameParams):
+        pl = np.ascontiguousarray(planes, dtype=np.float32).reshape(24)
+        self._check(self._f("draw_scene")(self.dev, scene, C.byref(scene_data), pl.ctypes.data_as(C.POINTER(C.c_float)), C.byref(params)))
+
+    def scene_draw_list(self, scene: int) -> np.ndarray:
+        """The visible draws of the last draw_scene frame, as update_scene would have left them in _renderObjects."""
+        n = C.c_size_t()
+        self._check(self._f("scene_draw_list")(self.dev, scene, None, 0, C.byref(n)))
+        out = np.zeros(n.value, RENDER_OBJECT_DTYPE)
+        self._check(self._f("scene_draw_list")(self.dev, scene, out.ctypes.data, out.size, C.byref(n)))
+        return out
 
     def readback(self, what: int) -> np.ndarray:
         W, H, S = self.width, self.height, self.shadow_extent

@@ -11,7 +11,8 @@
 const VkrApi& libvkr_api() {
     static const VkrApi api = {vkr_create, vkr_destroy, vkr_upload_mesh, vkr_create_image, vkr_update_bindless_texture,
                                vkr_set_cubemap, vkr_build_material, vkr_draw, vkr_readback, vkr_readback_async, vkr_sync,
-                               vkr_set_cubemap_levels};
+                               vkr_set_cubemap_levels, vkr_scene_create, vkr_scene_set_transforms, vkr_draw_scene, vkr_scene_draw_list,
+                               vkr_stats};
     return api;
 }
 
@@ -29,7 +30,7 @@ VulkanEngine* vke_create(uint32_t width, uint32_t height, int device, void* stre
 void vke_destroy(VulkanEngine* e) { delete e; }
 VkrDevice* vke_device(VulkanEngine* e) { return e->_vkr; }
 
-uint64_t vke_load_procedural(VulkanEngine* e, int config, uint32_t seed) { return load_procedural(e, config, seed); }
+uint64_t vke_load_procedural(VulkanEngine* e, int config, uint32_t seed) { e->scene_changed(); return load_procedural(e, config, seed); }
 void vke_orbit_camera(VulkanEngine* e, uint32_t seed, int view) { orbit_camera(e, seed, view); }
 
 // init_scene's `_sceneRoot->addChild(load_gltf(name, file))` (src/vk_engine_init.cpp:646-660).  Returns the number of triangles
@@ -42,6 +43,7 @@ int64_t vke_load_gltf(VulkanEngine* e, const char* name, const char* fileName, c
         return -1;
     }
     e->_sceneRoot->addChild(top);
+    e->scene_changed();
     std::vector<RenderObject> all;
     top->refreshTransform(vkm::mat4(1.0f), all);
     int64_t tris = 0;
@@ -129,7 +131,45 @@ int vke_present(VulkanEngine* e, void* pinnedDst, size_t bytes) { return e->pres
 int vke_sync(VulkanEngine* e) { return e->_api.sync ? e->_api.sync(e->_vkr) : VKR_SUCCESS; }
 int vke_readback(VulkanEngine* e, int what, void* dst, size_t bytes) { return e->_api.readback(e->_vkr, (VkrTarget)what, dst, bytes); }
 
-void vke_stats(VulkanEngine* e, EngineStats* out) { *out = e->stats; }
+void vke_stats(VulkanEngine* e, EngineStats* out) {
+    if (e->_gpuSceneUpdate && e->_api.stats) {        // the device counted what its is_visible kept (blocks until it has)
+        VkrEngineStats st{};
+        if (e->_api.stats(e->_vkr, &st) == VKR_SUCCESS) { e->stats.drawcall_count = st.drawcall_count; e->stats.triangle_count = st.triangle_count; }
+    }
+    *out = e->stats;
+}
+// update_scene's per-object work on the device (vkr_scene_create / vkr_draw_scene) from the next frame on
+void vke_set_gpu_scene_update(VulkanEngine* e, int on) { e->_gpuSceneUpdate = on != 0; }
+void vke_scene_changed(VulkanEngine* e) { e->scene_changed(); }
+// Node::localTransform of the idx-th node in traversal order (refreshTransform's) := m (column-major); -1 if there is none
+int vke_set_node_transform(VulkanEngine* e, size_t idx, const float m[16]) {
+    std::vector<Node*> order;
+    std::vector<Node*> stack;
+    if (e->_sceneRoot) stack.push_back(e->_sceneRoot.get());
+    while (!stack.empty()) {
+        Node* n = stack.back(); stack.pop_back();
+        order.push_back(n);
+        for (auto c = n->children.rbegin(); c != n->children.rend(); ++c) stack.push_back(c->get());
+    }
+    if (idx >= order.size()) return -1;
+    std::memcpy(order[idx]->localTransform.data(), m, 64);
+    e->transforms_changed();
+    return 0;
+}
+size_t vke_node_count(VulkanEngine* e) {
+    size_t n = 0;
+    std::vector<Node*> stack;
+    if (e->_sceneRoot) stack.push_back(e->_sceneRoot.get());
+    while (!stack.empty()) { Node* nd = stack.back(); stack.pop_back(); ++n; for (auto& c : nd->children) stack.push_back(c.get()); }
+    return n;
+}
+// the draw list of the last frame as the device's update_scene left it (vkr_scene_draw_list); returns the count, -1 on failure
+int64_t vke_gpu_draw_list(VulkanEngine* e, VkrRenderObject* out, size_t capacity) {
+    if (!e->_api.scene_draw_list || !e->_haveScene) return -1;
+    size_t count = 0;
+    if (e->_api.scene_draw_list(e->_vkr, e->_sceneHandle, out, capacity, &count) != VKR_SUCCESS) return -1;
+    return (int64_t)count;
+}
 size_t vke_visible_objects(VulkanEngine* e) { return e->_renderObjects.size(); }
 void vke_scene_data(VulkanEngine* e, GPUSceneData* out) { *out = e->_sceneData; }
 

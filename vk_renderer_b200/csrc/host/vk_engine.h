@@ -29,6 +29,12 @@ struct VkrApi {
     int (*readback_async)(VkrDevice*, VkrTarget, void*, size_t);   // may be null
     int (*sync)(VkrDevice*);                                        // may be null
     int (*set_cubemap_levels)(VkrDevice*, const void* const*, uint32_t, uint32_t, uint32_t, VkrFormat);   // may be null
+    // update_scene on the device (_gpuSceneUpdate); null in a backend without it (the oracle)
+    int (*scene_create)(VkrDevice*, const VkrSceneNode*, size_t, const VkrSceneSurface*, size_t, VkrScene*);
+    int (*scene_set_transforms)(VkrDevice*, VkrScene, uint32_t, uint32_t, const float*);
+    int (*draw_scene)(VkrDevice*, VkrScene, const VkrGPUSceneData*, const float*, const VkrFrameParams*);
+    int (*scene_draw_list)(VkrDevice*, VkrScene, VkrRenderObject*, size_t, size_t*);
+    int (*stats)(VkrDevice*, VkrEngineStats*);
 };
 const VkrApi& libvkr_api();
 
@@ -82,6 +88,19 @@ public:
     bool _cullToScissor = false;                    // also cull draws against the scissor's sub-frustum
 
     GPUSceneData _sceneData{};                      // what draw() last sent
+
+    // update_scene's per-object work (refreshTransform, is_visible, the sort; src/vk_engine_run.cpp:435-480) on the device:
+    // the scene graph is flattened and handed over once (vkr_scene_create), update_scene() then only moves the camera and
+    // draw() sends the frame's constants and the six frustum planes (vkr_draw_scene).  _renderObjects stays empty.
+    bool _gpuSceneUpdate = false;
+    bool _sceneGraphDirty = true;                   // nodes were added or removed: flatten again (scene_changed())
+    bool _sceneTransformsDirty = false;             // some Node::localTransform changed (transforms_changed())
+    bool _haveScene = false;
+    VkrScene _sceneHandle = 0;
+    std::vector<Node*> _flatNodes;                  // the nodes in the order refreshTransform visits them
+    void scene_changed() { _sceneGraphDirty = true; }
+    void transforms_changed() { _sceneTransformsDirty = true; }
+    int flatten_scene();                            // _sceneRoot -> VkrSceneNode[] + VkrSceneSurface[] -> vkr_scene_create
 
     int init(uint32_t width, uint32_t height, int device = 0, void* stream = nullptr, uint32_t flags = 0);
     void cleanup();

@@ -27,6 +27,7 @@ void extract_frustum_planes(const mat4& VP, Frustum& frustum) {
 void VulkanEngine::update_scene(float dt) {
     _mainCamera.update(dt);
     _renderObjects.clear();
+    if (_gpuSceneUpdate) return;        // the traversal, the cull and the sort below run in kernels (draw() -> vkr_draw_scene)
 
     std::vector<RenderObject> allObjects;
     if (_sceneRoot) _sceneRoot->refreshTransform(mat4(1.0f), allObjects);
@@ -144,6 +145,45 @@ CSMData VulkanEngine::compute_csmdata() {
     return csm;
 }
 
+// The scene graph as arrays, in the order Node::refreshTransform (src/vk_types.h:148-163) visits the nodes and emits their
+// surfaces; objects draw() would skip (no material / no pipeline, src/vk_engine_run.cpp:285) are left out.
+int VulkanEngine::flatten_scene() {
+    if (!_api.scene_create) return VKR_ERROR_INVALID_ARGUMENT;
+    std::vector<VkrSceneNode> nodes;
+    std::vector<VkrSceneSurface> surfaces;
+    _flatNodes.clear();
+    struct Item { Node* node; int32_t parent; };
+    std::vector<Item> stack;
+    if (_sceneRoot) stack.push_back({_sceneRoot.get(), -1});
+    while (!stack.empty()) {
+        const Item it = stack.back();
+        stack.pop_back();
+        const int32_t self = (int32_t)nodes.size();
+        VkrSceneNode n;
+        std::memcpy(n.localTransform, it.node->localTransform.data(), 64);
+        n.parent = it.parent;
+        nodes.push_back(n);
+        _flatNodes.push_back(it.node);
+        if (it.node->mesh)
+            for (const GeoSurface& surface : it.node->mesh->surfaces) {
+                if (!surface.material || !surface.material->pipeline) continue;
+                VkrSceneSurface sf;
+                sf.node = (uint32_t)self; sf.mesh = it.node->mesh->meshBuffer; sf.material = surface.material->materialSet;
+                sf.indexCount = surface.count; sf.firstIndex = surface.startIndex;
+                const Bounds& b = it.node->mesh->bounds;
+                sf.boundsOrigin[0] = b.origin.x; sf.boundsOrigin[1] = b.origin.y; sf.boundsOrigin[2] = b.origin.z;
+                sf.boundsSphereRadius = b.sphereRadius;
+                surfaces.push_back(sf);
+            }
+        for (auto c = it.node->children.rbegin(); c != it.node->children.rend(); ++c) stack.push_back({c->get(), self});   // pre-order, children left to right
+    }
+    if (nodes.empty()) return VKR_ERROR_INVALID_ARGUMENT;
+    const int rc = _api.scene_create(_vkr, nodes.data(), nodes.size(), surfaces.data(), surfaces.size(), &_sceneHandle);
+    if (rc != VKR_SUCCESS) return rc;
+    _haveScene = true; _sceneGraphDirty = false; _sceneTransformsDirty = false;
+    return VKR_SUCCESS;
+}
+
 // src/vk_engine_run.cpp:68-193 — fill GPUSceneData (:107-125), then one vkr_draw replaces the five passes
 int VulkanEngine::draw() {
     stats.triangle_count = 0;
@@ -185,6 +225,21 @@ int VulkanEngine::draw() {
     fp.enableSkybox = _hasSkybox; fp.fragShader = _fragShader;
     std::memcpy(fp.scissor, _scissor, sizeof(fp.scissor));
     std::memcpy(&fp.background, &_backgroundData, sizeof(fp.background));
+    if (_gpuSceneUpdate) {
+        // update_scene's camera frustum (:443-445): O(1) on the host; everything per object happens in vkr_draw_scene
+        if (!_api.draw_scene) return VKR_ERROR_INVALID_ARGUMENT;
+        if (_sceneGraphDirty || !_haveScene) { const int rc = flatten_scene(); if (rc != VKR_SUCCESS) return rc; }
+        if (_sceneTransformsDirty) {
+            std::vector<float> local(_flatNodes.size() * 16);
+            for (size_t i = 0; i < _flatNodes.size(); ++i) std::memcpy(&local[i * 16], _flatNodes[i]->localTransform.data(), 64);
+            const int rc = _api.scene_set_transforms(_vkr, _sceneHandle, 0, (uint32_t)_flatNodes.size(), local.data());
+            if (rc != VKR_SUCCESS) return rc;
+            _sceneTransformsDirty = false;
+        }
+        Frustum camFrustum;
+        extract_frustum_planes(sd.viewproj, camFrustum);
+        return _api.draw_scene(_vkr, _sceneHandle, reinterpret_cast<const VkrGPUSceneData*>(&sd), &camFrustum.planes[0].x, &fp);
+    }
     return _api.draw(_vkr, reinterpret_cast<const VkrGPUSceneData*>(&sd), _drawList.data(), _drawList.size(), &fp);
 }
 

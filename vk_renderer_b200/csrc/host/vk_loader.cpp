@@ -147,6 +147,36 @@ void config4(Builder& b, uint32_t seed) {
     e->_enableShadows = true; e->_shadowMode = 1; e->_enablePostprocess = true;
 }
 
+// config 6 (not a BASELINE config: the object-count case of SURVEY 8f-2, "the CPU per-frame O(objects) work that dominates the
+// reference at high object counts"): 16,000 small spheres (168 triangles each, 2.7 M in all) under 40 group nodes of 400 children
+// each, a 40 x 10 x 40 lattice seen from inside, so that is_visible rejects part of it; PBR, PCF shadows, tonemap
+void config6(Builder& b) {
+    VulkanEngine* e = b.e;
+    MeshData sph = make_uv_sphere(8, 12, 0.35f);
+    auto ms = b.mesh("sphere", sph, nullptr);
+    std::vector<std::shared_ptr<MeshAsset>> variants;
+    for (int k = 0; k < 16; ++k) {
+        float metallic = b.rng.uniform() < 0.3f ? 1.0f : 0.0f;
+        variants.push_back(b.variant(ms, b.material(b.randomColor(0.2f), metallic, b.rng.uniform(0.2f, 0.9f))));
+    }
+    int k = 0;
+    for (int ix = 0; ix < 40; ++ix) {
+        auto group = std::make_shared<Node>();
+        group->localTransform = translate(vec3{(ix - 19.5f) * 1.5f, 0.0f, 0.0f});
+        e->_sceneRoot->addChild(group);
+        for (int iy = 0; iy < 10; ++iy)
+            for (int iz = 0; iz < 40; ++iz) {
+                auto n = std::make_shared<Node>();
+                n->mesh = variants[(k++) % 16].get();
+                n->localTransform = translate(vec3{0.0f, (iy - 4.5f) * 1.5f, (iz - 19.5f) * 1.5f});
+                group->addChild(n);
+                for (auto& s : n->mesh->surfaces) b.tris += s.count / 3;
+            }
+    }
+    e->_mainCamera.position = vec3{0, 1.0f, 12.0f}; e->_mainCamera.pitch = -0.05f; e->_mainCamera.yaw = 0.3f;
+    e->_enableShadows = true; e->_shadowMode = 1; e->_enablePostprocess = true;
+}
+
 }  // namespace
 
 uint64_t load_procedural(VulkanEngine* engine, int config, uint32_t seed) {
@@ -157,6 +187,7 @@ uint64_t load_procedural(VulkanEngine* engine, int config, uint32_t seed) {
         case 2: case 5: config2(b); break;
         case 3: config3(b, seed); break;
         case 4: config4(b, seed); break;
+        case 6: config6(b); break;
         default: return 0;
     }
     return b.tris;

@@ -18,6 +18,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <map>
+#include <memory>
 #include <string>
 #include <vector>
 
@@ -27,6 +28,8 @@
 #include "vkr_frameprep.h"
 
 using namespace vkr;
+
+#include "vkr_scene_kernels.cuh"      // update_scene on the device: kernels + SceneRec
 
 // ======================================================================= kernels
 
@@ -254,12 +257,15 @@ __global__ void __launch_bounds__(128) expand_chunks_kernel(const DObject* __res
     chunks[ci] = make_chunk(o, obj, c, sbase);
     const float4 bmin = o.clBounds[2 * c], bmax = o.clBounds[2 * c + 1];
     const ClusterCone cone{o.clCone[3 * c], o.clCone[3 * c + 1], o.clCone[3 * c + 2]};
-    const CullRec mainRec = make_cull_rec(o.mvp, bmin, bmax, rtMain, &cone, eyes + (size_t)obj * 8);
+    // a draw the device's is_visible rejected (vkr_draw_scene, DRAW_HIDDEN) keeps its slots in every list, as culled clusters
+    const bool hidden = (o.flags & DRAW_HIDDEN) != 0u;
+    const CullRec none{0, 0, 0, 0, 0u, CLUSTER_CULLED};
+    const CullRec mainRec = hidden ? none : make_cull_rec(o.mvp, bmin, bmax, rtMain, &cone, eyes + (size_t)obj * 8);
     work[(size_t)passes * listStride + ci] = make_work_item(o, obj, c, sbase, mainRec);      // submission order
     for (uint32_t p = 0; p < passes; ++p) {
         const uint32_t sb = slotBase[(size_t)p * nobj + obj];
         if (sb == 0xFFFFFFFFu) continue;
-        work[(size_t)p * listStride + sb + c] = make_work_item(o, obj, c, sbase, p == 0 ? mainRec :
+        work[(size_t)p * listStride + sb + c] = make_work_item(o, obj, c, sbase, (p == 0 || hidden) ? mainRec :
             make_cull_rec(shadowMvp + ((size_t)(p - 1) * nobj + obj) * 16, bmin, bmax, rtShadow, &cone, eyes + ((size_t)p * nobj + obj) * 8));
     }
 }
@@ -888,6 +894,8 @@ struct VkrDevice {
     int32_t lastBand[2] = {0, 0};                  // rows [y0, y1) of the last frame this rank rendered
     uint32_t lastGatherF1 = 0;                     // the last frame's flag value if it was assembled on rank 0 over peer memory, else 0
     VkrEngineStats stats{};
+    std::vector<SceneRec*> scenes;                 // vkr_scene_create
+    uint64_t bindGen = 0;                          // counts the changes of bindless slots (a scene's draw flags depend on them)
     uint32_t lastOpaqueClusters = 0, lastShadowClusters = 0;
     int launches = 0;
     std::string err;
@@ -1040,7 +1048,7 @@ int vkr_create(const VkrConfig* cfg, VkrDevice** out) {
         ALLOC(dev->qShadow.counters, 32 * VKR_FRAME_OVERLAP);     // per frame in flight: frame i+1's shadow pass runs beside frame i's shading, which publishes frame i's
         ALLOC(dev->transCounters, 32);
         CK(cudaMallocHost(&dev->countersHost, 64));     // (mapped: unified addressing makes every pinned allocation device-visible)
-        std::memset(dev->countersHost, 0, 64);          // [0..11] three passes' counters, [12] peer-exchange error word
+        std::memset(dev->countersHost, 0, 64);          // [0..11] three passes' counters, [12] peer-exchange error word, [13..14] vkr_draw_scene: visible draws, their triangles
         for (auto& s : dev->slots) {
             CK(cudaEventCreateWithFlags(&s.uploaded, cudaEventDisableTiming));
             CK(cudaEventCreateWithFlags(&s.rendered, cudaEventDisableTiming));
@@ -1090,6 +1098,7 @@ void vkr_destroy(VkrDevice* dev) {
                      dev->hostProfUs[0] * f, dev->hostProfUs[1] * f, dev->hostProfUs[2] * f, dev->hostProfUs[3] * f, dev->hostProfUs[4] * f, dev->hostProfUs[5] * f,
                      dev->hostProfUs[6] * f, dev->hostProfUs[7] * f, dev->hostProfUs[8] * f);
     }
+    for (SceneRec* sr : dev->scenes) delete sr;            // (their device arrays are among the tracked allocations)
     for (auto it = dev->allocations.rbegin(); it != dev->allocations.rend(); ++it) cudaFree(*it);
     for (auto& s : dev->slots) {
         if (s.pinned) cudaFreeHost(s.pinned);
@@ -1221,6 +1230,7 @@ int vkr_update_bindless_texture(VkrDevice* dev, int index, VkrImage image, VkrSa
         return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_update_bindless_texture: bad index or image");
     dev->texHost[index] = make_dtexture(dev->images[image], sampler);
     dev->texDirty = true;
+    dev->bindGen++;
     return VKR_SUCCESS;
 }
 
@@ -1421,10 +1431,12 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
     const int slotIdx = (int)(dev->frameIndex % VKR_FRAME_OVERLAP);
     FrameSlot& slot = dev->slots[slotIdx];
     dev->uploadBytes = 0;
+    // vkr_draw_scene: the per-draw arrays are written by the scene kernels (same places in the slot's device buffer), nothing is uploaded
+    SceneRec* scn = static_cast<SceneRec*>(plan.scene);
     const size_t szObj = sizeof(DObject) * n, szBase = 4 * (n + 1);
-    const unsigned nChunks = plan.clusterBase[n], nSeqSlots = plan.seqSlotBase[n];
-    const size_t szShadow = plan.shadowMvp.size() * 4, szSlot = plan.slotBase.size() * 4;
+    const unsigned nChunks = scn ? scn->nClusters : plan.clusterBase[n], nSeqSlots = scn ? scn->nSeqSlots : plan.seqSlotBase[n];
     const uint32_t passes = 1u + (uint32_t)plan.shadowLayers;
+    const size_t szShadow = (size_t)plan.shadowLayers * n * 64, szSlot = (size_t)passes * n * 4;
     auto align16 = [](size_t v) { return (v + 15) & ~(size_t)15; };
     const size_t offObj = 0, offBase = align16(offObj + szObj), offSeq = align16(offBase + szBase), offShadow = align16(offSeq + szBase),
                  offSlot = align16(offShadow + szShadow);
@@ -1465,26 +1477,51 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
     int rc = ensure_slot(dev, slot, total);
     if (rc) return rc;
     char* hp = (char*)slot.pinned;
-    if (n) std::memcpy(hp + offObj, plan.objects.data(), szObj);
-    std::memcpy(hp + offBase, plan.clusterBase.data(), szBase);
-    std::memcpy(hp + offSeq, plan.seqSlotBase.data(), szBase);
-    if (szShadow) std::memcpy(hp + offShadow, plan.shadowMvp.data(), szShadow);
-    if (szSlot) std::memcpy(hp + offSlot, plan.slotBase.data(), szSlot);
+    char* dp = (char*)slot.devbuf;
     // the upload rides its own stream so it overlaps the previous frame's kernels; the slot's device
     // buffer is free once the frame that last used it (FRAME_OVERLAP frames ago) has rendered
     CK(cudaStreamWaitEvent(dev->upStream, slot.rendered, 0));
-    CK(cudaMemcpyAsync(slot.devbuf, slot.pinned, total, cudaMemcpyHostToDevice, dev->upStream));
-    dev->uploadBytes = total;
-    char* dp = (char*)slot.devbuf;
+    const uint32_t* dClusterBase = (const uint32_t*)(dp + offBase);
+    const uint32_t* dSeqSlotBase = (const uint32_t*)(dp + offSeq);
+    if (!scn) {
+        if (n) std::memcpy(hp + offObj, plan.objects.data(), szObj);
+        std::memcpy(hp + offBase, plan.clusterBase.data(), szBase);
+        std::memcpy(hp + offSeq, plan.seqSlotBase.data(), szBase);
+        if (szShadow) std::memcpy(hp + offShadow, plan.shadowMvp.data(), szShadow);
+        if (szSlot) std::memcpy(hp + offSlot, plan.slotBase.data(), szSlot);
+        CK(cudaMemcpyAsync(slot.devbuf, slot.pinned, total, cudaMemcpyHostToDevice, dev->upStream));
+        dev->uploadBytes = total;
+    } else if (n) {
+        // update_scene on the device (vkr_scene_kernels.cuh): world matrices if a transform changed, then per draw is_visible,
+        // MVPs and order keys, the passes' processing order, and the prefix sums — into the places the upload would have filled
+        cudaStream_t up = dev->upStream;
+        if (scn->worldDirty) {
+            for (size_t l = 0; l + 1 < scn->levelFirst.size(); ++l) {
+                const uint32_t first = scn->levelFirst[l], count = scn->levelFirst[l + 1] - first;
+                if (!count) continue;
+                scene_nodes_kernel<<<(count + 127) / 128, 128, 0, up>>>(scn->dLocal, scn->dParent, scn->dWorld, scn->dLevelOrder, first, count);
+                dev->launches += 1;
+            }
+            scn->worldDirty = false;
+        }
+        scene_draws_kernel<<<(unsigned)((n + 127) / 128), 128, 0, up>>>(plan.sceneFrame, scn->dDraws, scn->dWorld, scn->dTmpl, (DObject*)(dp + offObj),
+                                                                        (float*)(dp + offShadow), scn->dKeys, scn->dVisTris);
+        scene_rank_kernel<<<dim3((unsigned)((n + 255) / 256), passes), 256, 0, up>>>(scn->dKeys, (uint32_t)n, scn->opaqueCount, scn->dOrder);
+        scene_scan_kernel<<<1, 1024, 0, up>>>(plan.sceneFrame, scn->dDraws, (DObject*)(dp + offObj), scn->dVisTris, scn->dOrder, (uint32_t*)(dp + offSlot),
+                                              dev->countersHost + 13);
+        LAUNCHED("scene kernels");
+        dev->launches += 3;
+        dClusterBase = scn->dClusterBase; dSeqSlotBase = scn->dSeqSlotBase;
+    }
     const DObject* dObjects = (const DObject*)(dp + offObj);
     const DChunk* dChunks = slot.chunkBuf;
     const float* dShadowMvp = (const float*)(dp + offShadow);
     const WorkItem* dWork = slot.workBuf;
     if (n) {   // the frame's tables, on the upload stream too: neither the main nor the shadow stream has to wait for the other
-        prepare_draws_kernel<<<(unsigned)((n + 127) / 128), 128, 0, dev->upStream>>>(dObjects, (const uint32_t*)(dp + offSeq), dShadowMvp, (uint32_t)n, passes,
+        prepare_draws_kernel<<<(unsigned)((n + 127) / 128), 128, 0, dev->upStream>>>(dObjects, dSeqSlotBase, dShadowMvp, (uint32_t)n, passes,
                                                                                      slot.eyeBuf, slot.chunkObjBuf);
         if (nChunks)
-            expand_chunks_kernel<<<(nChunks + 127) / 128, 128, 0, dev->upStream>>>(dObjects, (const uint32_t*)(dp + offBase), (const uint32_t*)(dp + offSeq), (const uint32_t*)(dp + offSlot),
+            expand_chunks_kernel<<<(nChunks + 127) / 128, 128, 0, dev->upStream>>>(dObjects, dClusterBase, dSeqSlotBase, (const uint32_t*)(dp + offSlot),
                                                                                    dShadowMvp, slot.eyeBuf, (uint32_t)n, passes, nChunks, plan.mainTarget, plan.shadowTarget,
                                                                                    slot.chunkBuf, slot.workBuf);
         dev->launches += 2;
@@ -2010,6 +2047,12 @@ int vkr_readback_async(VkrDevice* dev, VkrTarget what, void* dst, size_t dstByte
 int vkr_stats(VkrDevice* dev, VkrEngineStats* out) {
     if (!dev || !out) return VKR_ERROR_INVALID_ARGUMENT;
     DRAIN(dev);
+    if (dev->lastPlan && dev->lastPlan->scene) {       // vkr_draw_scene: the device counted what is_visible kept
+        CK(cudaSetDevice(dev->device));
+        CK(cudaStreamSynchronize(dev->upStream));
+        dev->stats.drawcall_count = (int32_t)dev->countersHost[13];
+        dev->stats.triangle_count = (int32_t)dev->countersHost[14];
+    }
     *out = dev->stats;
     return VKR_SUCCESS;
 }
@@ -2232,3 +2275,5 @@ extern "C" int vkr_pack_rgb8_static(VkrDevice* dev, const void* rgba8Device, uin
     if (wait) CK(cudaStreamSynchronize(st));
     return VKR_SUCCESS;
 }
+
+#include "vkr_scene_api.cuh"        // vkr_scene_create / vkr_scene_set_transforms / vkr_draw_scene / vkr_scene_draw_list

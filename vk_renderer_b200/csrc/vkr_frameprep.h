@@ -236,6 +236,19 @@ inline void range_sphere(const ClusterData& cd, ClusterRange& r) {
     r.radius = std::sqrt(r2);
 }
 
+// DObject::flags of a draw with this material: bit0 Transparent pass, bit1 alpha-tested (its albedo texture has texels with
+// alpha < 0.5, DTexture flag bit2), bit2 some texture the fragment shaders sample has a mip chain, i.e. the shading pass needs
+// uv derivatives for this draw (a 1x1 or single-level image is sampled without them, vkr_shade.cuh texture2d)
+inline uint32_t draw_flags(const DMaterial& mat, const std::vector<DTexture>& textures) {
+    uint32_t flags = mat.pass == VKR_PASS_TRANSPARENT ? 1u : 0u;
+    const int aid = mat.albedoID;
+    if (aid >= 0 && aid < (int)textures.size() && textures[aid].data != nullptr && (textures[aid].flags & 4u)) flags |= 2u;
+    const int ids[2] = {aid, mat.metalRoughID};
+    for (int id : ids)
+        if (id >= 0 && id < (int)textures.size() && textures[id].data != nullptr && textures[id].levels > 1u && (textures[id].w | textures[id].h) != 1u) flags |= 4u;
+    return flags;
+}
+
 struct FramePlan {
     std::vector<DObject> objects;
     std::vector<uint32_t> primBase;     // nobj + 1 (dense ids, for stats / readback)
@@ -263,7 +276,74 @@ struct FramePlan {
     ShadeConst sc;
     RasterTarget mainTarget;
     RasterTarget shadowTarget;
+    // vkr_draw_scene (update_scene on the device): `scene` is the device library's scene record and the per-draw arrays above
+    // (objects, clusterBase, seqSlotBase, shadowMvp, slotBase) stay empty — the device writes them from the record and
+    // `sceneFrame`; the counts a launch needs (passSlots, opaqueClusters, ...) are the scene's static totals.
+    void* scene = nullptr;
+    SceneFrame sceneFrame;
 };
+
+// The frame's constants: what the shading pass and the two raster passes are told (O(1) in the draw count).
+inline void plan_constants(const VkrGPUSceneData* scene, const VkrFrameParams* fp, uint32_t W, uint32_t H, uint32_t S, size_t n, FramePlan& plan) {
+    ShadeConst& sc = plan.sc;
+    sc.scene = *scene;
+    camera_position(scene->view, sc.camPos);
+    {   // outLightVec = normalize(-sunlightDirection.xyz) (shaders/mesh.vert:21)
+        float x = -scene->sunlightDirection[0], y = -scene->sunlightDirection[1], z = -scene->sunlightDirection[2];
+        float inv = 1.0f / std::sqrt(x * x + y * y + z * z);
+        sc.lightVec[0] = x * inv; sc.lightVec[1] = y * inv; sc.lightVec[2] = z * inv;
+    }
+    const float bias[16] = {0.5f, 0, 0, 0, 0, 0.5f, 0, 0, 0, 0, 1.0f, 0, 0.5f, 0.5f, 0, 1.0f};   // mesh_pbr.frag:31-35
+    for (int l = 0; l < VKR_NUM_CASCADES; ++l) mat_mul(bias, scene->lightViewproj[l], sc.shadowMat[l]);
+    std::memcpy(sc.bgTop, fp->background.data1, 16);
+    std::memcpy(sc.bgBottom, fp->background.data2, 16);
+    sc.width = (int32_t)W; sc.height = (int32_t)H; sc.shadowExtent = (int32_t)S;
+    sc.sx0 = 0; sc.sy0 = 0; sc.sx1 = (int32_t)W; sc.sy1 = (int32_t)H;
+    if (fp->scissor[2] > 0 && fp->scissor[3] > 0) {
+        sc.sx0 = std::max(0, fp->scissor[0]); sc.sy0 = std::max(0, fp->scissor[1]);
+        sc.sx1 = std::min((int32_t)W, fp->scissor[0] + fp->scissor[2]);
+        sc.sy1 = std::min((int32_t)H, fp->scissor[1] + fp->scissor[3]);
+    }
+    sc.enableBackground = fp->enableBackground; sc.enablePostprocess = fp->enablePostprocess;
+    sc.enableSkybox = fp->enableSkybox; sc.fragShader = fp->fragShader;
+    // the shaders read the flags from the UBO .w components (src/vk_engine_run.cpp:124-125)
+    sc.shadowMode = (int32_t)scene->sunlightDirection[3];
+    sc.enableShadows = scene->sunlightColor[3] > 0.5f ? 1 : 0;
+    sc.nobj = (uint32_t)n;
+    sc.clearVis = 0;                   // set by the device library under VKR_CONFIG_TRANSIENT_DEPTH
+    sc.storeHdr = 1;                   // cleared by the device library under VKR_CONFIG_TRANSIENT_HDR
+    sc.halfW = (float)W * 0.5f; sc.halfH = (float)H * 0.5f;
+    sc.invHalfW = 1.0f / sc.halfW; sc.invHalfH = 1.0f / sc.halfH;
+    {
+        const float* P = scene->proj; const float* V = scene->view;
+        for (int j = 0; j < 3; ++j) {
+            double sx = (double)V[4 * j] / ((double)sc.halfW * P[0]), sy = (double)V[4 * j + 1] / ((double)sc.halfH * P[5]);
+            double so = (double)V[4 * j] * ((double)P[8] - 1.0) / P[0] + (double)V[4 * j + 1] * ((double)P[9] - 1.0) / P[5] - (double)V[4 * j + 2];
+            const double sgn = j == 1 ? -1.0 : 1.0;
+            sc.skyX[j] = (float)(sgn * sx); sc.skyY[j] = (float)(sgn * sy); sc.skyO[j] = (float)(sgn * so);
+        }
+    }
+
+    RasterTarget& mt = plan.mainTarget;
+    mt.vis = nullptr; mt.depthBits = nullptr;
+    mt.width = (int32_t)W; mt.height = (int32_t)H;
+    mt.sx0 = sc.sx0; mt.sy0 = sc.sy0; mt.sx1 = sc.sx1; mt.sy1 = sc.sy1;
+    mt.halfW = sc.halfW; mt.halfH = sc.halfH;
+    mt.halfW256 = sc.halfW * 256.0f; mt.halfH256 = sc.halfH * 256.0f;
+    mt.cullFront = 0;                                   // VK_CULL_MODE_BACK_BIT (src/vk_engine_init.cpp:536)
+    RasterTarget& st = plan.shadowTarget;
+    st = mt;
+    st.width = st.height = (int32_t)S;
+    st.sx0 = st.sy0 = 0; st.sx1 = st.sy1 = (int32_t)S;
+    st.halfW = st.halfH = (float)S * 0.5f;
+    st.halfW256 = st.halfH256 = (float)S * 128.0f;
+    if (fp->shadowScissor[2] > 0 && fp->shadowScissor[3] > 0) {
+        st.sx0 = std::max(0, fp->shadowScissor[0]); st.sy0 = std::max(0, fp->shadowScissor[1]);
+        st.sx1 = std::min((int32_t)S, fp->shadowScissor[0] + fp->shadowScissor[2]);
+        st.sy1 = std::min((int32_t)S, fp->shadowScissor[1] + fp->shadowScissor[3]);
+    }
+    st.cullFront = 1;                                   // VK_CULL_MODE_FRONT_BIT (src/vk_engine_init.cpp:441)
+}
 
 // Returns an empty string on success, else the reason the draw list is invalid.
 inline std::string plan_frame(const VkrGPUSceneData* scene, const VkrRenderObject* objs, size_t n, const VkrFrameParams* fp,
@@ -316,16 +396,8 @@ inline std::string plan_frame(const VkrGPUSceneData* scene, const VkrRenderObjec
         sphere[4 * i] = cr.center[0]; sphere[4 * i + 1] = cr.center[1]; sphere[4 * i + 2] = cr.center[2]; sphere[4 * i + 3] = cr.radius;
         o.primBase = (uint32_t)prim;
         o.material = ro.material;
-        o.flags = transparent ? 1u : 0u;
-        {   // alpha-tested draw: its albedo texture has texels with alpha < 0.5 (DTexture flag bit2)
-            const int aid = materials[ro.material].albedoID;
-            if (aid >= 0 && aid < (int)textures.size() && textures[aid].data != nullptr && (textures[aid].flags & 4u)) { o.flags |= 2u; plan.anyCutout = true; }
-            // bit2: some texture the fragment shaders sample has a mip chain, i.e. the shading pass needs uv derivatives for
-            // this draw (a 1x1 or single-level image is sampled without them, vkr_shade.cuh texture2d)
-            const int ids[2] = {aid, materials[ro.material].metalRoughID};
-            for (int id : ids)
-                if (id >= 0 && id < (int)textures.size() && textures[id].data != nullptr && textures[id].levels > 1u && (textures[id].w | textures[id].h) != 1u) o.flags |= 4u;
-        }
+        o.flags = draw_flags(materials[ro.material], textures);
+        if (o.flags & 2u) plan.anyCutout = true;
         plan.primBase[i] = (uint32_t)prim;
         plan.clusterBase[i] = (uint32_t)ncl;
         plan.seqSlotBase[i] = (uint32_t)nslot;
@@ -471,64 +543,8 @@ inline std::string plan_frame(const VkrGPUSceneData* scene, const VkrRenderObjec
         plan.passSlots[p] = slot;
     }
 
-    ShadeConst& sc = plan.sc;
-    sc.scene = *scene;
-    camera_position(scene->view, sc.camPos);
-    {   // outLightVec = normalize(-sunlightDirection.xyz) (shaders/mesh.vert:21)
-        float x = -scene->sunlightDirection[0], y = -scene->sunlightDirection[1], z = -scene->sunlightDirection[2];
-        float inv = 1.0f / std::sqrt(x * x + y * y + z * z);
-        sc.lightVec[0] = x * inv; sc.lightVec[1] = y * inv; sc.lightVec[2] = z * inv;
-    }
-    const float bias[16] = {0.5f, 0, 0, 0, 0, 0.5f, 0, 0, 0, 0, 1.0f, 0, 0.5f, 0.5f, 0, 1.0f};   // mesh_pbr.frag:31-35
-    for (int l = 0; l < VKR_NUM_CASCADES; ++l) mat_mul(bias, scene->lightViewproj[l], sc.shadowMat[l]);
-    std::memcpy(sc.bgTop, fp->background.data1, 16);
-    std::memcpy(sc.bgBottom, fp->background.data2, 16);
-    sc.width = (int32_t)W; sc.height = (int32_t)H; sc.shadowExtent = (int32_t)S;
-    sc.sx0 = 0; sc.sy0 = 0; sc.sx1 = (int32_t)W; sc.sy1 = (int32_t)H;
-    if (fp->scissor[2] > 0 && fp->scissor[3] > 0) {
-        sc.sx0 = std::max(0, fp->scissor[0]); sc.sy0 = std::max(0, fp->scissor[1]);
-        sc.sx1 = std::min((int32_t)W, fp->scissor[0] + fp->scissor[2]);
-        sc.sy1 = std::min((int32_t)H, fp->scissor[1] + fp->scissor[3]);
-    }
-    sc.enableBackground = fp->enableBackground; sc.enablePostprocess = fp->enablePostprocess;
-    sc.enableSkybox = fp->enableSkybox; sc.fragShader = fp->fragShader;
-    // the shaders read the flags from the UBO .w components (src/vk_engine_run.cpp:124-125)
-    sc.shadowMode = (int32_t)scene->sunlightDirection[3];
-    sc.enableShadows = scene->sunlightColor[3] > 0.5f ? 1 : 0;
-    sc.nobj = (uint32_t)n;
-    sc.clearVis = 0;                   // set by the device library under VKR_CONFIG_TRANSIENT_DEPTH
-    sc.storeHdr = 1;                   // cleared by the device library under VKR_CONFIG_TRANSIENT_HDR
-    sc.halfW = (float)W * 0.5f; sc.halfH = (float)H * 0.5f;
-    sc.invHalfW = 1.0f / sc.halfW; sc.invHalfH = 1.0f / sc.halfH;
-    {
-        const float* P = scene->proj; const float* V = scene->view;
-        for (int j = 0; j < 3; ++j) {
-            double sx = (double)V[4 * j] / ((double)sc.halfW * P[0]), sy = (double)V[4 * j + 1] / ((double)sc.halfH * P[5]);
-            double so = (double)V[4 * j] * ((double)P[8] - 1.0) / P[0] + (double)V[4 * j + 1] * ((double)P[9] - 1.0) / P[5] - (double)V[4 * j + 2];
-            const double sgn = j == 1 ? -1.0 : 1.0;
-            sc.skyX[j] = (float)(sgn * sx); sc.skyY[j] = (float)(sgn * sy); sc.skyO[j] = (float)(sgn * so);
-        }
-    }
-
-    RasterTarget& mt = plan.mainTarget;
-    mt.vis = nullptr; mt.depthBits = nullptr;
-    mt.width = (int32_t)W; mt.height = (int32_t)H;
-    mt.sx0 = sc.sx0; mt.sy0 = sc.sy0; mt.sx1 = sc.sx1; mt.sy1 = sc.sy1;
-    mt.halfW = sc.halfW; mt.halfH = sc.halfH;
-    mt.halfW256 = sc.halfW * 256.0f; mt.halfH256 = sc.halfH * 256.0f;
-    mt.cullFront = 0;                                   // VK_CULL_MODE_BACK_BIT (src/vk_engine_init.cpp:536)
-    RasterTarget& st = plan.shadowTarget;
-    st = mt;
-    st.width = st.height = (int32_t)S;
-    st.sx0 = st.sy0 = 0; st.sx1 = st.sy1 = (int32_t)S;
-    st.halfW = st.halfH = (float)S * 0.5f;
-    st.halfW256 = st.halfH256 = (float)S * 128.0f;
-    if (fp->shadowScissor[2] > 0 && fp->shadowScissor[3] > 0) {
-        st.sx0 = std::max(0, fp->shadowScissor[0]); st.sy0 = std::max(0, fp->shadowScissor[1]);
-        st.sx1 = std::min((int32_t)S, fp->shadowScissor[0] + fp->shadowScissor[2]);
-        st.sy1 = std::min((int32_t)S, fp->shadowScissor[1] + fp->shadowScissor[3]);
-    }
-    st.cullFront = 1;                                   // VK_CULL_MODE_FRONT_BIT (src/vk_engine_init.cpp:441)
+    plan.scene = nullptr;
+    plan_constants(scene, fp, W, H, S, n, plan);
     return std::string();
 }
 

@@ -89,12 +89,35 @@ struct DObject {
     uint32_t triCount;
     uint32_t primBase;        // dense submission-order id of this draw's first triangle (readback only)
     uint32_t material;
-    uint32_t flags;           // bit0: transparent pass, bit1: alpha-tested (albedo texture has alpha < 0.5), bit2: a sampled texture has mips
+    uint32_t flags;           // bit0: transparent pass, bit1: alpha-tested (albedo texture has alpha < 0.5), bit2: a sampled texture has mips,
+                              // bit7: DRAW_HIDDEN (set on the device by vkr_draw_scene's is_visible test)
     const uint4* clBlob;      // the same clusters as self-contained CL_BLOB_BYTES blocks (what the geometry kernels stage with one bulk copy)
     const float4* clCone;     // three float4 per cluster: normal cone and bounding sphere (ClusterCone, vkr_raster.cuh)
     uint64_t pad;
 };
 static_assert(sizeof(DObject) % 16 == 0, "DObject array is read with 16-byte loads");
+
+// ---- update_scene on the device (vkr_scene_create / vkr_draw_scene; bodies in vkr_scene.cuh) ----------------------------
+static const uint32_t DRAW_HIDDEN = 0x80u;   // DObject::flags bit7: is_visible said no — the draw takes part in no pass of this frame
+
+// One RenderObject the traversal emits (a surface of a node's mesh), static part.  48 bytes.
+struct SceneDraw {
+    uint32_t node;                     // the node whose worldTransform the draw takes
+    uint32_t nClusters;                // clusters of its index range (0 for a draw without triangles)
+    float origin[3], sphereRadius;     // MeshAsset::bounds (src/vk_types.h:112-116): what is_visible tests
+    float center[3], radius;           // bounding sphere of the range's clusters (ClusterRange): the processing-order key
+    uint32_t pad[2];
+};
+static_assert(sizeof(SceneDraw) == 48, "SceneDraw is read as three 16-byte words");
+
+// Per frame, passed by value.
+struct SceneFrame {
+    float viewproj[16];
+    float lightViewproj[VKR_NUM_CASCADES][16];
+    float planes[24];                  // extract_frustum_planes (src/vk_engine_run.cpp:420-433): 6 x (n.xyz, d), normalised
+    uint32_t nDraws, opaqueCount, shadowLayers, pad;
+};
+
 
 // Cluster data, built once per (mesh, firstIndex, indexCount) at first use (build_clusters):
 // the draw's triangles are sorted along a Morton curve of their centroids and cut into clusters of
@@ -154,7 +177,7 @@ VKR_HD DChunk make_chunk(const DObject& o, uint32_t obj, uint32_t c, uint32_t se
     ch.pos = o.pos; ch.clVerts = o.clVerts + info.x; ch.clTris = o.clTris + (size_t)c * CL_TRIS;
     ch.clOrig = o.clOrig + (size_t)c * CL_TRIS;
     ch.obj = obj; ch.seqBase = seqSlot * SEQ_SLOT; ch.counts = info.y;
-    ch.flags = o.flags;
+    ch.flags = (o.flags & DRAW_HIDDEN) ? DRAW_HIDDEN : o.flags;      // a hidden draw is nobody's work (the cut-out kernel selects on bit1)
     return ch;
 }
 

@@ -20,7 +20,8 @@ PKG = os.path.dirname(os.path.abspath(__file__))
 _engine_lib = None
 
 _API_FIELDS = ["create", "destroy", "upload_mesh", "create_image", "update_bindless_texture", "set_cubemap",
-               "build_material", "draw", "readback", "readback_async", "sync", "set_cubemap_levels"]
+               "build_material", "draw", "readback", "readback_async", "sync", "set_cubemap_levels",
+               "scene_create", "scene_set_transforms", "draw_scene", "scene_draw_list", "stats"]
 
 
 class VkrApi(C.Structure):
@@ -66,6 +67,11 @@ def load_engine() -> C.CDLL:
         lib.vke_render_object.restype = C.c_int
         lib.vke_decode_png.argtypes = [C.c_char_p, C.c_size_t, p, C.c_size_t, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
         lib.vke_decode_png.restype = C.c_int
+        lib.vke_set_gpu_scene_update.argtypes = [p, C.c_int]
+        lib.vke_scene_changed.argtypes = [p]
+        lib.vke_set_node_transform.argtypes = [p, C.c_size_t, C.POINTER(C.c_float)]; lib.vke_set_node_transform.restype = C.c_int
+        lib.vke_node_count.argtypes = [p]; lib.vke_node_count.restype = C.c_size_t
+        lib.vke_gpu_draw_list.argtypes = [p, p, C.c_size_t]; lib.vke_gpu_draw_list.restype = C.c_int64
         lib.vke_decode_jpeg.argtypes = lib.vke_decode_png.argtypes
         lib.vke_decode_jpeg.restype = C.c_int
         _engine_lib = lib
@@ -151,6 +157,29 @@ class Engine:
             mc, pt = capi.MaterialConstants(), C.c_int(0)
             assert self.lib.vke_render_object(self.e, i, ro.ctypes.data, C.byref(mc), C.byref(pt)) == 0
             out.append((ro, mc, pt.value))
+        return out
+
+    def set_gpu_scene_update(self, on=True):
+        """update_scene's per-object work (refreshTransform, is_visible, the sort) on the device from the next frame on
+        (vkr_scene_create / vkr_draw_scene); update_scene() then only moves the camera."""
+        self.lib.vke_set_gpu_scene_update(self.e, int(on))
+
+    def node_count(self) -> int:
+        return self.lib.vke_node_count(self.e)
+
+    def set_node_transform(self, index, local_colmajor):
+        """Node::localTransform of the index-th node in traversal order."""
+        m = (C.c_float * 16)(*[float(x) for x in local_colmajor])
+        if self.lib.vke_set_node_transform(self.e, index, m) != 0:
+            raise IndexError(index)
+
+    def gpu_draw_list(self) -> np.ndarray:
+        """The visible draws of the last frame drawn with set_gpu_scene_update(True), as the device left them."""
+        n = self.lib.vke_gpu_draw_list(self.e, None, 0)
+        if n < 0:
+            raise RuntimeError("vke_gpu_draw_list failed")
+        out = np.zeros(n, capi.RENDER_OBJECT_DTYPE)
+        assert self.lib.vke_gpu_draw_list(self.e, out.ctypes.data, out.size) == n
         return out
 
     def set_camera(self, pos, pitch=0.0, yaw=0.0):
