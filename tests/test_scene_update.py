@@ -96,6 +96,14 @@ def test_emu_device_update_scene_equals_host_update_scene(emu_lib, config):
     host.close(); dev.close()
 
 
+def test_emu_many_objects_under_group_nodes(emu_lib):
+    """Config 6: 16,000 draws under 40 group nodes (two levels of refreshTransform), seen from inside the lattice."""
+    host, dev = _both_engines(emu_lib, "emu", 96, 54, 64, _config(6))
+    seen = _check_cameras(host, dev, [None, ((0, 1, 12), -0.05, 2.0)], "config 6")
+    assert all(1000 < s < 16000 for s in seen) and len(seen) == 2
+    host.close(); dev.close()
+
+
 def test_emu_device_update_scene_against_the_oracle(ork_lib, emu_lib):
     """The oracle never sees the scene graph: it is given the host's list.  Same frame, parity bar."""
     ref = Engine(192, 108, api_lib=ork_lib, api_prefix="ork", shadow_extent=128)
@@ -211,7 +219,7 @@ def test_is_visible_on_the_device_follows_the_reference_bit_for_bit(emu_lib):
         surf[i] = (i, base["mesh"], base["material"], base["indexCount"], base["firstIndex"], tuple(origin), radius)
         want.append(e.is_visible(col, origin, radius))
     sc = r.scene_create(nodes, surf)
-    r.draw_scene(sc, e.scene_data() if False else sd, planes, fp)
+    r.draw_scene(sc, sd, planes, fp)
     got = r.scene_draw_list(sc)
     kept = {tuple(np.asarray(g["transform"]).tolist()) for g in got}
     have = [tuple(nodes[i]["localTransform"].tolist()) in kept for i in range(n)]
