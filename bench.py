@@ -504,10 +504,50 @@ def run_b200(args):
             line["views"] = {"metric": v["metric"], "value": v["value"], "unit": v["unit"], "e2e": v["e2e"], "n_gpus": world,
                              "steps": v["steps"], "ms_per_step": v["ms_per_step"], "scaling": "strong", "config": v["config"],
                              "gpu_launches": v["gpu_launches"], "expected": "linear in n_gpus: no exchange step"}
+    # ---- SURVEY 8f-2 (update_scene on the device), one GPU only: the object-count case through the host engine, both ways
+    if rank == 0 and world == 1 and not args.no_scene_update:
+        try:
+            line["scene_update"] = measure_scene_update()
+        except Exception as e:       # a side measurement: never costs the headline line
+            line["scene_update"] = {"error": repr(e)}
     if rank == 0:
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def measure_scene_update(frames=200):
+    """16,000 draws (procedural config 6: spheres of 192 triangles under 40 group nodes, 1080p, PBR + PCF shadow + tonemap)
+    through the C++ host engine: update_scene + draw per frame with the per-object work on the host (the reference's
+    update_scene: refreshTransform, is_visible, sort — then the draw list is uploaded) and on the device (vkr_draw_scene).
+    Frames issued back to back, one sync at the end, wall clock around the loop."""
+    from vk_renderer_b200.engine import Engine
+    out = {"workload": "procedural config 6: 16,000 draws (3.07 M triangles) under 40 group nodes, 1920x1080, PBR, 2048^2 PCF shadow, tonemap",
+           "frames": frames, "unit": "frames/s", "timing": "wall clock around the loop, one sync at its end"}
+    flags = capi.CONFIG_SUBMIT_THREAD | capi.CONFIG_TRANSIENT_DEPTH | capi.CONFIG_TRANSIENT_HDR
+    for mode in ("host", "device"):
+        e = Engine(1920, 1080, flags=flags)
+        try:
+            e.load_procedural(6)
+            if mode == "device":
+                e.set_gpu_scene_update(True)
+            for _ in range(10):
+                e.update_scene(0.0); e.draw()
+            e.sync()
+            t0 = time.perf_counter()
+            for _ in range(frames):
+                e.update_scene(0.0); e.draw()
+            e.sync()
+            dt = time.perf_counter() - t0
+            st = e.stats()
+            t1 = time.perf_counter()
+            for _ in range(50):
+                e.update_scene(0.0)
+            out[f"update_scene_on_{mode}"] = {"value": frames / dt, "visible_draws": int(st.drawcall_count), "submitted_triangles": int(st.triangle_count),
+                                              "host_update_scene_ms": (time.perf_counter() - t1) / 50 * 1e3}
+        finally:
+            e.close()
+    return out
 
 
 # ------------------------------------------------------------------------------- frame-parallel views (config 5)
@@ -642,6 +682,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-views", action="store_true", help="skip the config-5 pass that follows the frame workload")
+    ap.add_argument("--no-scene-update", action="store_true", help="skip the update_scene (host vs device) side measurement")
     ap.add_argument("--workload", default="frame", choices=["frame", "views"],
                     help="frame: BASELINE config 4 (the headline metric, default); views: config 5, frame-parallel multi-view batch")
     args = ap.parse_args()

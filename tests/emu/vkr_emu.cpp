@@ -465,7 +465,32 @@ int emu_draw_scene(EmuDevice* d, uint32_t scene, const VkrGPUSceneData* sceneDat
     }
     for (uint32_t p = 0; p < passes; ++p) {                    // scene_rank_kernel, then scene_scan_kernel's per-pass part
         const uint32_t count = p == 0 ? s.opaqueCount : (uint32_t)n;
-        for (uint32_t i = 0; i < count; ++i) order[(size_t)p * n + scene_rank(keys.data() + (size_t)p * n, count, i)] = i;
+        const float* kp = keys.data() + (size_t)p * n;
+        if (n <= SCENE_RANK_MAX) {
+            for (uint32_t i = 0; i < count; ++i) order[(size_t)p * n + scene_rank(kp, count, i)] = i;
+        } else {                                               // many draws: scene_draws_kernel's key range, then the three bucket kernels
+            const float inf = bits2f(0x7F800000u);
+            uint32_t rmax = 0, rneg = 0;
+            for (uint32_t i = 0; i < count; ++i)
+                if (kp[i] != inf) { rmax = std::max(rmax, scene_ordered(kp[i])); rneg = std::max(rneg, ~scene_ordered(kp[i])); }
+            std::vector<uint32_t> start(SCENE_BUCKETS + 1, 0u);
+            for (uint32_t i = 0; i < count; ++i) start[scene_bucket(kp[i], rmax, rneg) + 1]++;
+            for (uint32_t b = 0; b < SCENE_BUCKETS; ++b) start[b + 1] += start[b];
+            for (uint32_t i = 0; i < count; ++i) order[(size_t)p * n + start[scene_bucket(kp[i], rmax, rneg)]++] = i;
+            // (front to back up to the width of a bucket: a draw never precedes one whose key is more than a bucket nearer)
+            const float width = (scene_unordered(rmax) - scene_unordered(~rneg)) / (float)(SCENE_BUCKETS - 1u);
+            float nearest = -inf;
+            for (uint32_t k = 0; k < count; ++k) {
+                const float key = kp[order[(size_t)p * n + k]];
+                if (key == inf) continue;
+                if (key < nearest - 1.001f * width - 1e-6f * std::fabs(nearest)) { d->err = "bucket order is not front to back"; return VKR_ERROR_INVALID_ARGUMENT; }
+                nearest = std::max(nearest, key);
+            }
+        }
+        {   // the order must be a permutation of the pass's draws: every draw gets its slots exactly once
+            std::vector<uint8_t> seen(count, 0);
+            for (uint32_t k = 0; k < count; ++k) { const uint32_t o = order[(size_t)p * n + k]; if (o >= count || seen[o]) { d->err = "processing order is not a permutation"; return VKR_ERROR_INVALID_ARGUMENT; } seen[o] = 1; }
+        }
         uint32_t slot = 0;
         for (uint32_t k = 0; k < count; ++k) { const uint32_t o = order[(size_t)p * n + k]; plan.slotBase[(size_t)p * n + o] = slot; slot += s.draws[o].nClusters; }
         plan.passSlots[p] = slot;

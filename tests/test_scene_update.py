@@ -266,6 +266,15 @@ def test_gpu_device_update_scene_equals_host_update_scene(vkr_lib, config, size,
 
 
 @pytest.mark.gpu
+def test_gpu_many_objects_under_group_nodes(vkr_lib):
+    """Config 6: 16,000 draws under 40 group nodes — the bucket order (more than 2048 draws), 16 blocks per pass."""
+    host, dev = _both_engines(None, "vkr", 480, 270, 512, _config(6))
+    seen = _check_cameras(host, dev, [None, ((0, 1, 12), -0.05, 2.0), ((30.0, 3.0, 0.0), -0.1, 1.5708)], "config 6")
+    assert all(100 < s < 16000 for s in seen) and len(seen) == 3
+    host.close(); dev.close()
+
+
+@pytest.mark.gpu
 def test_gpu_device_update_scene_against_the_oracle(ork_lib, vkr_lib):
     ref = Engine(640, 360, api_lib=ork_lib, api_prefix="ork", shadow_extent=512)
     dev = Engine(640, 360, shadow_extent=512)

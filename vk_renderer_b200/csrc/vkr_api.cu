@@ -1504,9 +1504,17 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
             }
             scn->worldDirty = false;
         }
+        const bool buckets = scn->nBlocks != 0;          // many draws: bucket order instead of the counting rank
+        if (buckets) CK(cudaMemsetAsync(scn->dKeyRange, 0, 2 * 4 * (1 + VKR_NUM_CASCADES), up));
         scene_draws_kernel<<<(unsigned)((n + 127) / 128), 128, 0, up>>>(plan.sceneFrame, scn->dDraws, scn->dWorld, scn->dTmpl, (DObject*)(dp + offObj),
-                                                                        (float*)(dp + offShadow), scn->dKeys, scn->dVisTris);
-        scene_rank_kernel<<<dim3((unsigned)((n + 255) / 256), passes), 256, 0, up>>>(scn->dKeys, (uint32_t)n, scn->opaqueCount, scn->dOrder);
+                                                                        (float*)(dp + offShadow), scn->dKeys, scn->dVisTris, buckets ? scn->dKeyRange : nullptr);
+        if (buckets) {
+            scene_bucket_count_kernel<<<dim3(scn->nBlocks, passes), 256, 0, up>>>(scn->dKeys, (uint32_t)n, scn->opaqueCount, scn->nBlocks, scn->dKeyRange, scn->dBucketOf, scn->dHist);
+            scene_bucket_scan_kernel<<<passes, 1024, 0, up>>>(scn->dHist, scn->nBlocks);
+            scene_bucket_place_kernel<<<dim3(scn->nBlocks, passes), 256, 0, up>>>((uint32_t)n, scn->opaqueCount, scn->nBlocks, scn->dBucketOf, scn->dHist, scn->dOrder);
+            dev->launches += 2;
+        } else
+            scene_rank_kernel<<<dim3((unsigned)((n + 255) / 256), passes), 256, 0, up>>>(scn->dKeys, (uint32_t)n, scn->opaqueCount, scn->dOrder);
         scene_scan_kernel<<<1, 1024, 0, up>>>(plan.sceneFrame, scn->dDraws, (DObject*)(dp + offObj), scn->dVisTris, scn->dOrder, (uint32_t*)(dp + offSlot),
                                               dev->countersHost + 13);
         LAUNCHED("scene kernels");

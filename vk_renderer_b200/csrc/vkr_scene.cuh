@@ -81,6 +81,24 @@ VKR_HD float scene_order_key(const float* __restrict__ m, const float* __restric
 // strict total order on (key, draw): no NaN keys (scene_order_key), ties by submission order
 VKR_HD bool scene_key_less(float ka, uint32_t a, float kb, uint32_t b) { return ka < kb || (ka == kb && a < b); }
 
+// ---- processing order of many draws: buckets.  Counting every draw in front of one's own (scene_rank) is n^2 compares per
+// pass — 1 M for 1000 draws, 256 M for 16,000.  Above SCENE_RANK_MAX draws the order is instead: SCENE_BUCKETS equal slices of
+// the pass's key range, front to back, draws of one slice in submission order (a stable counting sort on the slice number).
+static const uint32_t SCENE_RANK_MAX = 2048u, SCENE_BUCKETS = 2048u, SCENE_BLOCK = 1024u;
+// monotone map float -> uint32 (so that atomicMax finds the range of the keys)
+VKR_HD uint32_t scene_ordered(float f) { const uint32_t b = f2bits(f); return (b & 0x80000000u) ? ~b : (b | 0x80000000u); }
+VKR_HD float scene_unordered(uint32_t u) { return bits2f((u & 0x80000000u) ? (u & 0x7FFFFFFFu) : ~u); }
+// range[0] = max of ordered(key), range[1] = max of ~ordered(key) over the pass's visible draws (both start at 0: no draw)
+VKR_HD uint32_t scene_bucket(float key, uint32_t rangeMax, uint32_t rangeNegMin) {
+    if (key == bits2f(0x7F800000u) || rangeMax == 0u) return SCENE_BUCKETS - 1u;          // hidden draws last
+    const float kmin = scene_unordered(~rangeNegMin), kmax = scene_unordered(rangeMax);
+    const float span = kmax - kmin;
+    if (!(span > 0.0f)) return 0u;
+    const float x = (key - kmin) * ((float)(SCENE_BUCKETS - 1u) / span);                   // monotone in key
+    const uint32_t b = x > 0.0f ? (uint32_t)x : 0u;
+    return b < SCENE_BUCKETS - 2u ? b : SCENE_BUCKETS - 2u;
+}
+
 // One thread per draw: the frame's DObject from the static template, the light MVPs, the keys of every pass, and what the
 // scans need (triangles if visible).  keys: [pass][nDraws]; shadowMvp: [layer][nDraws][16].
 VKR_HD void scene_draw_body(const SceneFrame& f, const SceneDraw& sd, const float* __restrict__ nodeWorld, const DObject& tmpl, uint32_t i,

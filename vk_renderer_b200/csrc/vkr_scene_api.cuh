@@ -99,6 +99,11 @@ extern "C" int vkr_scene_create(VkrDevice* dev, const VkrSceneNode* nodes, size_
     ALLOC(s.dDraws, nd * sizeof(SceneDraw)); ALLOC(s.dTmpl, nd * sizeof(DObject));
     ALLOC(s.dClusterBase, (nd + 1) * 4); ALLOC(s.dSeqSlotBase, (nd + 1) * 4);
     ALLOC(s.dKeys, nd * 4 * (1 + VKR_NUM_CASCADES)); ALLOC(s.dOrder, nd * 4 * (1 + VKR_NUM_CASCADES)); ALLOC(s.dVisTris, nd * 4);
+    if (ns > SCENE_RANK_MAX) {
+        s.nBlocks = (ns + SCENE_BLOCK - 1) / SCENE_BLOCK;
+        ALLOC(s.dKeyRange, 2 * 4 * (1 + VKR_NUM_CASCADES)); ALLOC(s.dBucketOf, nd * 2 * (1 + VKR_NUM_CASCADES));
+        ALLOC(s.dHist, (size_t)(1 + VKR_NUM_CASCADES) * SCENE_BUCKETS * s.nBlocks * 4);
+    }
     CK(cudaMemcpy(s.dLocal, local.data(), (size_t)nn * 64, cudaMemcpyHostToDevice));
     CK(cudaMemcpy(s.dParent, parent.data(), (size_t)nn * 4, cudaMemcpyHostToDevice));
     CK(cudaMemcpy(s.dLevelOrder, levelOrder.data(), (size_t)nn * 4, cudaMemcpyHostToDevice));

@@ -18,10 +18,20 @@ __global__ void scene_nodes_kernel(const float* __restrict__ local, const int32_
 
 __global__ void __launch_bounds__(128) scene_draws_kernel(const __grid_constant__ SceneFrame f, const SceneDraw* __restrict__ draws, const float* __restrict__ world,
                                                           const DObject* __restrict__ tmpl, DObject* __restrict__ objects, float* __restrict__ shadowMvp,
-                                                          float* __restrict__ keys, uint32_t* __restrict__ visTris) {
+                                                          float* __restrict__ keys, uint32_t* __restrict__ visTris, uint32_t* keyRange) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= f.nDraws) return;
-    scene_draw_body(f, draws[i], world, tmpl[i], i, objects[i], shadowMvp, keys, visTris);
+    const bool live = i < f.nDraws;
+    if (live) scene_draw_body(f, draws[i], world, tmpl[i], i, objects[i], shadowMvp, keys, visTris);
+    if (keyRange == nullptr) return;
+    // many draws (bucket order): the range of every pass's keys over the visible draws, one pair of atomics per warp and pass
+    const float inf = __uint_as_float(0x7F800000u);
+    for (uint32_t p = 0; p <= f.shadowLayers; ++p) {
+        const bool takes = live && (p > 0 || i < f.opaqueCount);
+        const float k = takes ? keys[(size_t)p * f.nDraws + i] : inf;
+        const uint32_t o = k == inf ? 0u : scene_ordered(k), no = k == inf ? 0u : ~scene_ordered(k);
+        const uint32_t mx = __reduce_max_sync(0xFFFFFFFFu, o), mn = __reduce_max_sync(0xFFFFFFFFu, no);
+        if ((threadIdx.x & 31u) == 0u && mx != 0u) { atomicMax(keyRange + 2 * p, mx); atomicMax(keyRange + 2 * p + 1, mn); }
+    }
 }
 
 // order[pass][rank] = draw.  The main pass (blockIdx.y = 0) orders the opaque prefix only; the shadow layers order every draw.
@@ -43,6 +53,41 @@ __global__ void __launch_bounds__(256) scene_rank_kernel(const float* __restrict
             for (uint32_t j = 0; j < m; ++j) rank += scene_key_less(s_keys[j], base + j, ki, i) ? 1u : 0u;
     }
     if (i < count) order[(size_t)p * nDraws + rank] = i;
+}
+
+// ---- many draws: the bucket order (vkr_scene.cuh).  A CTA owns SCENE_BLOCK consecutive draws of a pass.
+// hist[pass][bucket][block] = draws of the block in the bucket; bucketOf[pass][draw] = its bucket.
+__global__ void __launch_bounds__(256) scene_bucket_count_kernel(const float* __restrict__ keys, uint32_t nDraws, uint32_t opaqueCount, uint32_t nBlocks,
+                                                                  const uint32_t* __restrict__ keyRange, uint16_t* __restrict__ bucketOf, uint32_t* __restrict__ hist) {
+    __shared__ uint32_t s_hist[SCENE_BUCKETS];
+    const uint32_t p = blockIdx.y, count = p == 0 ? opaqueCount : nDraws, block = blockIdx.x;
+    for (uint32_t k = threadIdx.x; k < SCENE_BUCKETS; k += 256u) s_hist[k] = 0u;
+    __syncthreads();
+    const uint32_t rmax = keyRange[2 * p], rneg = keyRange[2 * p + 1];
+    for (uint32_t e = threadIdx.x; e < SCENE_BLOCK; e += 256u) {
+        const uint32_t i = block * SCENE_BLOCK + e;
+        if (i >= count) break;
+        const uint32_t b = scene_bucket(keys[(size_t)p * nDraws + i], rmax, rneg);
+        bucketOf[(size_t)p * nDraws + i] = (uint16_t)b;
+        atomicAdd(&s_hist[b], 1u);
+    }
+    __syncthreads();
+    for (uint32_t k = threadIdx.x; k < SCENE_BUCKETS; k += 256u) hist[((size_t)p * SCENE_BUCKETS + k) * nBlocks + block] = s_hist[k];
+}
+// order[pass][hist-prefix of (bucket, block) + draws of the same bucket earlier in the block] = draw  (stable)
+__global__ void __launch_bounds__(256) scene_bucket_place_kernel(uint32_t nDraws, uint32_t opaqueCount, uint32_t nBlocks, const uint16_t* __restrict__ bucketOf,
+                                                                  const uint32_t* __restrict__ histPrefix, uint32_t* __restrict__ order) {
+    __shared__ uint16_t s_b[SCENE_BLOCK];
+    const uint32_t p = blockIdx.y, count = p == 0 ? opaqueCount : nDraws, block = blockIdx.x;
+    const uint32_t base = block * SCENE_BLOCK, m = base < count ? min(SCENE_BLOCK, count - base) : 0u;
+    for (uint32_t e = threadIdx.x; e < m; e += 256u) s_b[e] = bucketOf[(size_t)p * nDraws + base + e];
+    __syncthreads();
+    for (uint32_t e = threadIdx.x; e < m; e += 256u) {
+        const uint32_t b = s_b[e];
+        uint32_t before = 0;
+        for (uint32_t j = 0; j < e; ++j) before += s_b[j] == b ? 1u : 0u;
+        order[(size_t)p * nDraws + histPrefix[((size_t)p * SCENE_BUCKETS + b) * nBlocks + block] + before] = base + e;
+    }
 }
 
 // Exclusive prefix sums of n values by ONE CTA of 1024 threads; thread t owns a contiguous run of elements.  put(k, prefix).
@@ -69,6 +114,13 @@ __device__ __forceinline__ uint32_t scene_block_scan(uint32_t n, Get get, Put pu
     const uint32_t total = s_warp[32];
     __syncthreads();                 // s_warp is free for the next scan
     return total;
+}
+
+// hist[pass][bucket][block] -> its exclusive prefix over (bucket, block), one CTA per pass
+__global__ void __launch_bounds__(1024) scene_bucket_scan_kernel(uint32_t* hist, uint32_t nBlocks) {
+    __shared__ uint32_t s_warp[33];
+    uint32_t* h = hist + (size_t)blockIdx.x * SCENE_BUCKETS * nBlocks;
+    scene_block_scan(SCENE_BUCKETS * nBlocks, [&](uint32_t k) { return h[k]; }, [&](uint32_t k, uint32_t pre) { h[k] = pre; }, s_warp);
 }
 
 // counts[0] = draws is_visible kept, counts[1] = their triangles (pinned host words: EngineStats::drawcall_count / triangle_count,
@@ -102,6 +154,8 @@ struct SceneRec {
     SceneDraw* dDraws = nullptr; DObject* dTmpl = nullptr;
     uint32_t* dClusterBase = nullptr; uint32_t* dSeqSlotBase = nullptr;      // nDraws + 1 each: static, every draw keeps its slots
     float* dKeys = nullptr; uint32_t* dOrder = nullptr; uint32_t* dVisTris = nullptr;   // per-frame scratch (upload stream only)
+    // more than SCENE_RANK_MAX draws: the bucket order's scratch (key ranges, per-draw bucket, per-block histograms)
+    uint32_t* dKeyRange = nullptr; uint16_t* dBucketOf = nullptr; uint32_t* dHist = nullptr; uint32_t nBlocks = 0;
     std::vector<VkrSceneSurface> surfaces;  // draw order: the traversal's, MainColor first (stable)
     std::vector<DObject> tmplHost;
 };
