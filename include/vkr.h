@@ -340,6 +340,8 @@ typedef struct VkrSceneSurface {
  * reference's: order of emission, MainColor materials first (stable) — what update_scene's sort leaves (:454-458). */
 int vkr_scene_create(VkrDevice* dev, const VkrSceneNode* nodes, size_t nodeCount,
                      const VkrSceneSurface* surfaces, size_t surfaceCount, VkrScene* out);
+/* Releases the scene's device memory (waits for the frames in flight).  The handle is dead afterwards; other handles stay valid. */
+int vkr_scene_destroy(VkrDevice* dev, VkrScene scene);
 /* Node::localTransform of `count` nodes starting at firstNode changed (count * 16 floats); the next vkr_draw_scene
  * recomputes the world matrices on the device. */
 int vkr_scene_set_transforms(VkrDevice* dev, VkrScene scene, uint32_t firstNode, uint32_t count, const float* localTransforms);

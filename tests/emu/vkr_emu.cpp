@@ -428,13 +428,20 @@ int emu_scene_create(EmuDevice* d, const VkrSceneNode* nodes, size_t nn, const V
     *out = (uint32_t)d->scenes.size() - 1;
     return 0;
 }
+int emu_scene_destroy(EmuDevice* d, uint32_t scene) {
+    if (scene >= d->scenes.size() || !d->scenes[scene]) return VKR_ERROR_INVALID_ARGUMENT;
+    if (d->lastScene == d->scenes[scene]) d->lastScene = nullptr;
+    delete d->scenes[scene];
+    d->scenes[scene] = nullptr;
+    return 0;
+}
 int emu_scene_set_transforms(EmuDevice* d, uint32_t scene, uint32_t first, uint32_t count, const float* local) {
-    if (scene >= d->scenes.size() || (uint64_t)first + count > d->scenes[scene]->parent.size()) return VKR_ERROR_INVALID_ARGUMENT;
+    if (scene >= d->scenes.size() || !d->scenes[scene] || (uint64_t)first + count > d->scenes[scene]->parent.size()) return VKR_ERROR_INVALID_ARGUMENT;
     if (count) std::memcpy(&d->scenes[scene]->local[(size_t)first * 16], local, (size_t)count * 64);
     return 0;
 }
 int emu_draw_scene(EmuDevice* d, uint32_t scene, const VkrGPUSceneData* sceneData, const float* planes, const VkrFrameParams* fp) {
-    if (scene >= d->scenes.size()) return VKR_ERROR_INVALID_ARGUMENT;
+    if (scene >= d->scenes.size() || !d->scenes[scene]) return VKR_ERROR_INVALID_ARGUMENT;
     EmuScene& s = *d->scenes[scene];
     FramePlan& plan = d->plan;
     for (DMaterial& m : d->materials) material_constants(m, d->tex.data(), d->lut);
@@ -506,7 +513,7 @@ int emu_draw_scene(EmuDevice* d, uint32_t scene, const VkrGPUSceneData* sceneDat
     return rc;
 }
 int emu_scene_draw_list(EmuDevice* d, uint32_t scene, VkrRenderObject* out, size_t capacity, size_t* count) {
-    if (scene >= d->scenes.size() || d->lastScene != d->scenes[scene] || !count) return VKR_ERROR_INVALID_ARGUMENT;
+    if (scene >= d->scenes.size() || !d->scenes[scene] || d->lastScene != d->scenes[scene] || !count) return VKR_ERROR_INVALID_ARGUMENT;
     const EmuScene& s = *d->scenes[scene];
     size_t k = 0;
     for (size_t i = 0; i < s.draws.size(); ++i) {

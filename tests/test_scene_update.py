@@ -146,6 +146,58 @@ def test_emu_nested_nodes_transparent_and_cutout_draws(emu_lib, tmp_path):
     host.close(); dev.close()
 
 
+def _random_tree_asset(seed, count=60):
+    """The glTF test asset with its six nodes replaced by a seeded random forest: up to seven levels deep, TRS nodes with
+    rotations and non-uniform scales, matrix nodes, empty group nodes, meshes with one or two surfaces, some of them BLEND."""
+    rng = np.random.default_rng(seed)
+    asset = gu.build_asset(np.random.default_rng(11))
+    nodes = []
+    for i in range(count):
+        q = rng.normal(size=4)
+        q = (q / np.linalg.norm(q)).astype(np.float32)
+        t = rng.uniform(-2.5, 2.5, 3).astype(np.float32)
+        sc = rng.uniform(0.6, 1.4, 3).astype(np.float32)
+        kind = rng.integers(0, 4)
+        if kind == 0:
+            m = (np.diag([*sc, 1.0]) + 0.0).astype(np.float32)
+            m[:3, 3] = t
+            node = dict(matrix=[float(x) for x in m.T.reshape(-1)])
+        elif kind == 1:
+            node = dict(trs=dict(t=[float(x) for x in t]))
+        else:
+            node = dict(trs=dict(t=[float(x) for x in t], r=[float(x) for x in q], s=[float(x) for x in sc]))
+        node["mesh"] = [0, 1, 2, None][rng.integers(0, 4)]
+        node["children"] = []
+        nodes.append(node)
+    depth = [0] * count
+    for i in range(1, count):                       # a parent among the earlier nodes (or none), at most six levels above
+        if rng.random() < 0.15:
+            continue
+        cands = [j for j in range(i) if depth[j] < 6]
+        j = int(cands[rng.integers(0, len(cands))])
+        nodes[j]["children"].append(i)
+        depth[i] = depth[j] + 1
+    asset["nodes"] = nodes
+    return asset, max(depth)
+
+
+@pytest.mark.parametrize("seed", [1, 2, 3])
+def test_emu_random_scene_graphs(emu_lib, tmp_path, seed):
+    asset, deepest = _random_tree_asset(seed)
+    assert deepest >= 4
+    path = gu.write_gltf(asset, str(tmp_path), "glb")
+
+    def load(e):
+        e.load_gltf(path, "test")
+        e.set_toggles(shadows=1, shadow_mode=1 if seed != 2 else 3, background=1, postprocess=1)
+    host, dev = _both_engines(emu_lib, "emu", 160, 96, 128, load)
+    rng = np.random.default_rng(100 + seed)
+    cams = [(tuple(rng.uniform(-6, 6, 3) + np.array([0, 0, 6.0])), float(rng.uniform(-0.4, 0.4)), float(rng.uniform(-1.0, 1.0))) for _ in range(3)]
+    seen = _check_cameras(host, dev, cams, f"random tree {seed}")
+    assert max(seen) > 10
+    host.close(); dev.close()
+
+
 def _flat_scene(r, objs, bounds_radius=1.0e6):
     """A draw list as a one-level scene graph: node i carries object i's matrix; bounds so large that is_visible keeps all."""
     nodes = np.zeros(len(objs), capi.SCENE_NODE_DTYPE)
@@ -250,6 +302,15 @@ def test_scene_create_refuses_what_it_cannot_draw(emu_lib):
             s2[0]["indexCount"] = 1 << 30
         with pytest.raises(capi.VkrError):
             r.scene_create(n2, s2)
+    # a destroyed scene is dead, the others live on; the engine replaces its scene when the graph changes
+    a, b = r.scene_create(nodes, surf), r.scene_create(nodes, surf)
+    r.scene_destroy(a)
+    with pytest.raises(capi.VkrError):
+        r.draw_scene(a, sd, _planes_everything(), fp)
+    with pytest.raises(capi.VkrError):
+        r.scene_destroy(a)
+    r.draw_scene(b, sd, _planes_everything(), fp)
+    assert r.scene_draw_list(b).size == 1
     r.close()
 
 
@@ -306,6 +367,21 @@ def test_gpu_nested_nodes_transparent_and_cutout_draws(vkr_lib, tmp_path):
     for e in (host, dev):
         e.set_node_transform(2, m.T.reshape(-1))
     _check_cameras(host, dev, cams[:2], "glTF after moving node 2")
+    host.close(); dev.close()
+
+
+@pytest.mark.gpu
+def test_gpu_random_scene_graph(vkr_lib, tmp_path):
+    asset, deepest = _random_tree_asset(2)
+    path = gu.write_gltf(asset, str(tmp_path), "glb")
+
+    def load(e):
+        e.load_gltf(path, "test")
+        e.set_toggles(shadows=1, shadow_mode=3, background=1, postprocess=1)
+    host, dev = _both_engines(None, "vkr", 480, 270, 512, load)
+    rng = np.random.default_rng(102)
+    cams = [(tuple(rng.uniform(-6, 6, 3) + np.array([0, 0, 6.0])), float(rng.uniform(-0.4, 0.4)), float(rng.uniform(-1.0, 1.0))) for _ in range(3)]
+    _check_cameras(host, dev, cams, "random tree 2")
     host.close(); dev.close()
 
 

@@ -129,7 +129,7 @@ VKR_SYMBOLS = [
     "build_material", "draw", "readback", "readback_async", "sync", "stats", "get_timings",
     "set_flags", "device_ptr", "launch_count", "upload_bytes", "cull_stats", "set_shadow_exchange", "comm_unique_id", "shard_init", "last_error", "version",
     "readback_band_async", "shard_info", "pack_rgb8_static", "host_times",
-    "scene_create", "scene_set_transforms", "draw_scene", "scene_draw_list",
+    "scene_create", "scene_set_transforms", "draw_scene", "scene_draw_list", "scene_destroy",
 ]
 
 
@@ -243,12 +243,13 @@ class Renderer:
                 "scene_set_transforms": ([p, C.c_uint32, C.c_uint32, C.c_uint32, p], C.c_int),
                 "draw_scene": ([p, C.c_uint32, C.POINTER(GPUSceneData), C.POINTER(C.c_float), C.POINTER(FrameParams)], C.c_int),
                 "scene_draw_list": ([p, C.c_uint32, p, C.c_size_t, C.POINTER(C.c_size_t)], C.c_int),
+                "scene_destroy": ([p, C.c_uint32], C.c_int),
             })
         for name, (args, res) in sigs.items():
             try:
                 fn = self._f(name)
             except AttributeError:
-                if name in ("host_times", "pack_rgb8_static", "scene_create", "scene_set_transforms", "draw_scene", "scene_draw_list"):      # an older library variant in an A/B run (tools/run_ab.sh)
+                if name in ("host_times", "pack_rgb8_static", "scene_create", "scene_set_transforms", "draw_scene", "scene_draw_list", "scene_destroy"):      # an older library variant in an A/B run (tools/run_ab.sh)
                     continue
                 raise
             fn.argtypes, fn.restype = args, res
@@ -324,6 +325,9 @@ class Renderer:
         out = C.c_uint32()
         self._check(self._f("scene_create")(self.dev, nd.ctypes.data, nd.size, sf.ctypes.data, sf.size, C.byref(out)))
         return out.value
+
+    def scene_destroy(self, scene: int):
+        self._check(self._f("scene_destroy")(self.dev, scene))
 
     def scene_set_transforms(self, scene: int, first_node: int, local_colmajor: np.ndarray):
         m = np.ascontiguousarray(local_colmajor, dtype=np.float32).reshape(-1, 16)

@@ -12,7 +12,7 @@ const VkrApi& libvkr_api() {
     static const VkrApi api = {vkr_create, vkr_destroy, vkr_upload_mesh, vkr_create_image, vkr_update_bindless_texture,
                                vkr_set_cubemap, vkr_build_material, vkr_draw, vkr_readback, vkr_readback_async, vkr_sync,
                                vkr_set_cubemap_levels, vkr_scene_create, vkr_scene_set_transforms, vkr_draw_scene, vkr_scene_draw_list,
-                               vkr_stats};
+                               vkr_stats, vkr_scene_destroy};
     return api;
 }
 

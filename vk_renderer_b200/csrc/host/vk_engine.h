@@ -35,6 +35,7 @@ struct VkrApi {
     int (*draw_scene)(VkrDevice*, VkrScene, const VkrGPUSceneData*, const float*, const VkrFrameParams*);
     int (*scene_draw_list)(VkrDevice*, VkrScene, VkrRenderObject*, size_t, size_t*);
     int (*stats)(VkrDevice*, VkrEngineStats*);
+    int (*scene_destroy)(VkrDevice*, VkrScene);
 };
 const VkrApi& libvkr_api();
 

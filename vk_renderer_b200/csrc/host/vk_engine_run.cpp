@@ -178,6 +178,7 @@ int VulkanEngine::flatten_scene() {
         for (auto c = it.node->children.rbegin(); c != it.node->children.rend(); ++c) stack.push_back({c->get(), self});   // pre-order, children left to right
     }
     if (nodes.empty()) return VKR_ERROR_INVALID_ARGUMENT;
+    if (_haveScene && _api.scene_destroy) { _api.scene_destroy(_vkr, _sceneHandle); _haveScene = false; }     // the graph it was made from is gone
     const int rc = _api.scene_create(_vkr, nodes.data(), nodes.size(), surfaces.data(), surfaces.size(), &_sceneHandle);
     if (rc != VKR_SUCCESS) return rc;
     _haveScene = true; _sceneGraphDirty = false; _sceneTransformsDirty = false;

@@ -121,10 +121,27 @@ extern "C" int vkr_scene_create(VkrDevice* dev, const VkrSceneNode* nodes, size_
     return VKR_SUCCESS;
 }
 
+extern "C" int vkr_scene_destroy(VkrDevice* dev, VkrScene scene) {
+    if (!dev) return VKR_ERROR_INVALID_ARGUMENT;
+    DRAIN(dev);
+    if (scene >= dev->scenes.size() || !dev->scenes[scene]) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_scene_destroy: unknown scene");
+    CK(cudaSetDevice(dev->device));
+    CK(cudaDeviceSynchronize());                      // frames in flight read the scene's arrays on the upload stream
+    SceneRec* s = dev->scenes[scene];
+    if (dev->lastPlan && dev->lastPlan->scene == s) { dev->lastPlan = nullptr; dev->lastN = 0; }      // (vkr_sync must not redraw from it)
+    for (FramePlan& p : dev->plans) if (p.scene == s) p.scene = nullptr;
+    void* arrays[] = {s->dLocal, s->dParent, s->dWorld, s->dLevelOrder, s->dDraws, s->dTmpl, s->dClusterBase, s->dSeqSlotBase,
+                      s->dKeys, s->dOrder, s->dVisTris, s->dKeyRange, s->dBucketOf, s->dHist};
+    for (void* a : arrays) dev_free(dev, a);
+    delete s;
+    dev->scenes[scene] = nullptr;
+    return VKR_SUCCESS;
+}
+
 extern "C" int vkr_scene_set_transforms(VkrDevice* dev, VkrScene scene, uint32_t firstNode, uint32_t count, const float* localTransforms) {
     if (!dev) return VKR_ERROR_INVALID_ARGUMENT;
     DRAIN(dev);                                       // every frame handed to the submit thread has been issued: it reads the old matrices
-    if (scene >= dev->scenes.size()) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_scene_set_transforms: unknown scene");
+    if (scene >= dev->scenes.size() || !dev->scenes[scene]) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_scene_set_transforms: unknown scene");
     SceneRec& s = *dev->scenes[scene];
     if ((uint64_t)firstNode + count > s.nNodes || (count && !localTransforms)) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_scene_set_transforms: node range");
     if (!count) return VKR_SUCCESS;
@@ -139,7 +156,7 @@ extern "C" int vkr_scene_set_transforms(VkrDevice* dev, VkrScene scene, uint32_t
 extern "C" int vkr_draw_scene(VkrDevice* dev, VkrScene scene, const VkrGPUSceneData* sceneData, const float frustumPlanes[24], const VkrFrameParams* fp) {
     if (!dev) return VKR_ERROR_INVALID_ARGUMENT;
     if (!sceneData || !frustumPlanes || !fp) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_draw_scene: null argument");
-    if (scene >= dev->scenes.size()) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_draw_scene: unknown scene");
+    if (scene >= dev->scenes.size() || !dev->scenes[scene]) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_draw_scene: unknown scene");
     if (dev->shardRanks > 1) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_draw_scene: not available on a sharded device (the band split needs the draw list on the host: use vkr_draw)");
     CK(cudaSetDevice(dev->device));
     const bool async = (dev->flags & VKR_CONFIG_SUBMIT_THREAD) && !dev->shadowExchange;
@@ -182,7 +199,7 @@ extern "C" int vkr_scene_draw_list(VkrDevice* dev, VkrScene scene, VkrRenderObje
     if (!dev) return VKR_ERROR_INVALID_ARGUMENT;
     DRAIN(dev);
     if (!count || (capacity && !out)) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_scene_draw_list: null argument");
-    if (scene >= dev->scenes.size()) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_scene_draw_list: unknown scene");
+    if (scene >= dev->scenes.size() || !dev->scenes[scene]) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_scene_draw_list: unknown scene");
     SceneRec& s = *dev->scenes[scene];
     if (!dev->lastPlan || dev->lastPlan->scene != &s || !dev->lastObjects) return dev->fail(VKR_ERROR_INVALID_ARGUMENT, "vkr_scene_draw_list: the last frame was not drawn from this scene");
     CK(cudaSetDevice(dev->device));

@@ -21,7 +21,7 @@ _engine_lib = None
 
 _API_FIELDS = ["create", "destroy", "upload_mesh", "create_image", "update_bindless_texture", "set_cubemap",
                "build_material", "draw", "readback", "readback_async", "sync", "set_cubemap_levels",
-               "scene_create", "scene_set_transforms", "draw_scene", "scene_draw_list", "stats"]
+               "scene_create", "scene_set_transforms", "draw_scene", "scene_draw_list", "stats", "scene_destroy"]
 
 
 class VkrApi(C.Structure):
