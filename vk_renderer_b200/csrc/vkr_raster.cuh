@@ -283,6 +283,33 @@ VKR_HD void make_edges(const int32_t X[3], const int32_t Y[3], EdgeEq& e) {
     }
 }
 
+// Coverage of the strip pxa..pxb (at most 8 pixels) of row py.  The edge functions are linear along the strip, so their
+// values at its two ends bound them everywhere in between: both ends inside every edge -> the whole strip is covered, both
+// ends outside some edge -> none of it is; only a strip an edge actually crosses is walked pixel by pixel.  Exact (the same
+// integers, the same >= 0 test); interior strips of a big triangle — most of a tile item — cost three multiply-adds instead
+// of eight 64-bit steps.  Measured neutral to slightly slower (configs 1 / 2 / 3 / 4: 20 140 / 8202 / 949 / 2532 frames/s with,
+// 20 345 / 8271 / 956 / 2529 without; profiles/r02_ab.md): the large-triangle kernel does not wait for its coverage
+// arithmetic.  Off; -DVKR_STRIP_BOUNDS switches it on.
+VKR_HD uint32_t strip_coverage(const EdgeEq& e, int64_t ax0, int64_t ax1, int64_t ax2, int32_t pxa, int32_t pxb, int32_t py) {
+    const int64_t Px = (int64_t)pxa * 256 + 128, Py = (int64_t)py * 256 + 128;
+    int64_t f0 = e.a[0] * Px + e.b[0] * Py + e.c[0];
+    int64_t f1 = e.a[1] * Px + e.b[1] * Py + e.c[1];
+    int64_t f2 = e.a[2] * Px + e.b[2] * Py + e.c[2];
+#if defined(VKR_STRIP_BOUNDS)
+    const int32_t last = pxb - pxa;                       // 0..7
+    const int64_t g0 = f0 + ax0 * last, g1 = f1 + ax1 * last, g2 = f2 + ax2 * last;
+    if ((f0 | g0 | f1 | g1 | f2 | g2) >= 0) return (2u << last) - 1u;
+    if (((f0 & g0) | (f1 & g1) | (f2 & g2)) < 0) return 0u;
+#endif
+    uint32_t mask = 0;
+#pragma unroll
+    for (int32_t k = 0; k < 8; ++k) {
+        if (pxa + k <= pxb && (f0 | f1 | f2) >= 0) mask |= 1u << k;
+        f0 += ax0; f1 += ax1; f2 += ax2;
+    }
+    return mask;
+}
+
 // Rectangle [x0,x1]x[y0,y1] of a large triangle, pixels dealt to `nlanes` cooperating lanes in
 // 8-pixel-wide strips (lane -> (row, 8-px column group)), incremental along the strip.
 template <class Sink>
@@ -297,18 +324,9 @@ VKR_HD void raster_rect64(const int32_t X[3], const int32_t Y[3], float z0, floa
     for (int32_t i = lane; i < n; i += nlanes) {
         const int32_t row = i / strips, sx = i - row * strips;
         const int32_t py = y0 + row, pxa = x0 + sx * 8, pxb = imin(pxa + 7, x1);
-        const int64_t Px = (int64_t)pxa * 256 + 128, Py = (int64_t)py * 256 + 128;
-        int64_t f0 = e.a[0] * Px + e.b[0] * Py + e.c[0];
-        int64_t f1 = e.a[1] * Px + e.b[1] * Py + e.c[1];
-        int64_t f2 = e.a[2] * Px + e.b[2] * Py + e.c[2];
         // coverage of the strip first (cheap, every lane in step), then one sink call per covered pixel: lanes meet at
         // their k-th covered pixel, so an expensive sink (alpha test, blending) runs converged even on thin slivers
-        uint32_t mask = 0;
-#pragma unroll
-        for (int32_t k = 0; k < 8; ++k) {
-            if (pxa + k <= pxb && (f0 | f1 | f2) >= 0) mask |= 1u << k;
-            f0 += ax0; f1 += ax1; f2 += ax2;
-        }
+        uint32_t mask = strip_coverage(e, ax0, ax1, ax2, pxa, pxb, py);
         while (mask) {
 #if defined(__CUDA_ARCH__)
             const int32_t k = __ffs((int)mask) - 1;
@@ -344,16 +362,7 @@ __device__ __forceinline__ void raster_rect64_compact(const int32_t X[3], const 
         if (i < n) {
             const int32_t row = i / strips, sx = i - row * strips;
             py = y0 + row; pxa = x0 + sx * 8;
-            const int32_t pxb = imin(pxa + 7, x1);
-            const int64_t Px = (int64_t)pxa * 256 + 128, Py = (int64_t)py * 256 + 128;
-            int64_t f0 = e.a[0] * Px + e.b[0] * Py + e.c[0];
-            int64_t f1 = e.a[1] * Px + e.b[1] * Py + e.c[1];
-            int64_t f2 = e.a[2] * Px + e.b[2] * Py + e.c[2];
-#pragma unroll
-            for (int32_t k = 0; k < 8; ++k) {
-                if (pxa + k <= pxb && (f0 | f1 | f2) >= 0) mask |= 1u << k;
-                f0 += ax0; f1 += ax1; f2 += ax2;
-            }
+            mask = strip_coverage(e, ax0, ax1, ax2, pxa, imin(pxa + 7, x1), py);
         }
         if (!__any_sync(0xFFFFFFFFu, mask != 0)) continue;
         const uint32_t c = (uint32_t)__popc(mask);
@@ -709,6 +718,13 @@ __device__ __forceinline__ void raster_medium_coop(const LargeTri& lt, const Sin
         const int32_t row = i / strips, sx = i - row * strips;
         const int32_t py = lt.by0 + row, pxa = lt.bx0 + sx * 8;
         int32_t f0 = e[0] + row * by[0] + sx * 8 * ax[0], f1 = e[1] + row * by[1] + sx * 8 * ax[1], f2 = e[2] + row * by[2] + sx * 8 * ax[2];
+#if defined(VKR_STRIP_BOUNDS)
+        {   // both ends of the strip outside one edge: none of it is covered (strip_coverage; half of a bounding box is such strips)
+            const int32_t last = imin(7, (int32_t)lt.bx1 - pxa);
+            const int32_t g0 = f0 + last * ax[0], g1 = f1 + last * ax[1], g2 = f2 + last * ax[2];
+            if (((f0 & g0) | (f1 & g1) | (f2 & g2)) < 0) continue;
+        }
+#endif
 #pragma unroll
         for (int32_t k = 0; k < 8; ++k) {
             if (pxa + k <= lt.bx1 && (f0 | f1 | f2) >= 0) sink.put(pxa + k, py, depth_at(lt.z0, lt.dzdx, lt.dzdy, lt.X[0], lt.Y[0], pxa + k, py));
