@@ -51,6 +51,21 @@ def test_cli_renders_what_the_engine_renders(vkr_lib, tmp_path):
 
 
 @pytest.mark.gpu
+def test_cli_gpu_scene_update_renders_the_same_image(vkr_lib, tmp_path):
+    """--gpu-scene: update_scene's per-object work on the device (vkr_draw_scene); same image, same counts."""
+    outs = []
+    for k, extra in enumerate(([], ["--gpu-scene"])):
+        ppm = tmp_path / f"c1_{k}.ppm"
+        out = subprocess.run([CLI, "--config", "1", "--size", "480x270", "--camera", "0,1,4,0,0", "--frames", "2", "--out", str(ppm)] + extra,
+                             capture_output=True, text=True)
+        assert out.returncode == 0, out.stderr
+        stats = {l.split(" ", 1)[0]: l.split(" ", 1)[1] for l in out.stdout.strip().splitlines()}
+        outs.append((read_ppm(ppm), int(stats["triangles"]), int(stats["draws"])))
+    assert np.array_equal(outs[0][0], outs[1][0])
+    assert outs[0][1:] == outs[1][1:] and 0 < outs[0][2] < 64        # inside the grid: is_visible rejects part of it
+
+
+@pytest.mark.gpu
 def test_cli_loads_gltf(vkr_lib, tmp_path):
     import gltf_util as gu
     asset = gu.build_asset(np.random.default_rng(11))

@@ -16,7 +16,7 @@
 
 static void usage() {
     std::puts(
-        "usage: vkr_render (--gltf FILE | --config 1..5) [options]\n"
+        "usage: vkr_render (--gltf FILE | --config 1..6) [options]\n"
         "  --size WxH            draw extent (default 1280x720, the reference's window)\n"
         "  --shadow-extent N     shadow map size (default 2048)\n"
         "  --shadows 0|1         _enableShadows          --shadow-mode 0..3   hard / PCF / PCSS / CSM\n"
@@ -25,6 +25,7 @@ static void usage() {
         "  --cubemap FILE.ktx    skybox cube map (KTX 1.1 / 2.0; RGBA8, sRGB8_A8 or RGBA16F), as load_cubemap\n"
         "  --camera X,Y,Z[,PITCH,YAW]    --sun X,Y,Z    --ambient R,G,B\n"
         "  --frames N            frames to render (default 1; stats are of the last one)\n"
+        "  --gpu-scene           update_scene's per-object work (transforms, is_visible, draw list) on the device\n"
         "  --device N            CUDA device ordinal\n"
         "  --out FILE.ppm        write the presented image (P6)\n");
 }
@@ -38,7 +39,7 @@ static std::vector<float> floats(const char* s) {
 int main(int argc, char** argv) {
     std::string gltf, out, cubemap;
     int config = 0, frames = 1, device = 0, shadows = -1, shadowMode = -1, background = -1, post = -1;
-    bool lambert = false;
+    bool lambert = false, gpuScene = false;
     uint32_t W = 1280, H = 720, S = 2048;
     std::vector<float> cam, sun, ambient;
     for (int i = 1; i < argc; ++i) {
@@ -54,6 +55,7 @@ int main(int argc, char** argv) {
         else if (a == "--background") background = std::atoi(next());
         else if (a == "--postprocess") post = std::atoi(next());
         else if (a == "--lambert") lambert = true;
+        else if (a == "--gpu-scene") gpuScene = true;
         else if (a == "--cubemap") cubemap = next();
         else if (a == "--camera") cam = floats(next());
         else if (a == "--sun") sun = floats(next());
@@ -92,6 +94,7 @@ int main(int argc, char** argv) {
     if (background >= 0) engine._enableBackground = background != 0;
     if (post >= 0) engine._enablePostprocess = post != 0;
     if (lambert) engine._fragShader = VKR_FRAG_MESH_LAMBERT;
+    engine._gpuSceneUpdate = gpuScene;
     if (cam.size() >= 3) engine._mainCamera.position = vkm::vec3{cam[0], cam[1], cam[2]};
     if (cam.size() >= 5) { engine._mainCamera.pitch = cam[3]; engine._mainCamera.yaw = cam[4]; }
     if (sun.size() >= 3) engine._sunlightDirection = vkm::vec4{sun[0], sun[1], sun[2], 0.0f};
@@ -107,8 +110,10 @@ int main(int argc, char** argv) {
     const double wall = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     VkrEngineStats st{};
     vkr_stats(engine._vkr, &st);
+    // (with --gpu-scene the host keeps no draw list: the device counted what its is_visible kept)
+    const int trisDrawn = gpuScene ? st.triangle_count : engine.stats.triangle_count, draws = gpuScene ? st.drawcall_count : engine.stats.drawcall_count;
     std::printf("frametime %.3f ms\ndraw time %.3f ms\ntriangles %d\ndraws %d\nvisible objects %zu\nwall %.3f ms for %d frame(s)\n",
-                st.frametime, st.mesh_draw_time, engine.stats.triangle_count, engine.stats.drawcall_count, engine._renderObjects.size(), wall, frames);
+                st.frametime, st.mesh_draw_time, trisDrawn, draws, gpuScene ? (size_t)draws : engine._renderObjects.size(), wall, frames);
     if (!out.empty()) {
         FILE* f = std::fopen(out.c_str(), "wb");
         if (!f) { std::fprintf(stderr, "cannot write %s\n", out.c_str()); return 1; }
