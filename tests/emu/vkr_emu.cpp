@@ -428,6 +428,15 @@ int emu_scene_create(EmuDevice* d, const VkrSceneNode* nodes, size_t nn, const V
     *out = (uint32_t)d->scenes.size() - 1;
     return 0;
 }
+// Test hooks for the bucket order's helpers (vkr_scene.cuh): the order-preserving float -> uint32 map and the slice of a key
+uint32_t emu_scene_ordered(float f) { return scene_ordered(f); }
+float emu_scene_unordered(uint32_t u) { return scene_unordered(u); }
+void emu_scene_buckets(const float* keys, uint32_t n, uint32_t* out) {
+    const float inf = bits2f(0x7F800000u);
+    uint32_t rmax = 0, rneg = 0;
+    for (uint32_t i = 0; i < n; ++i) if (keys[i] != inf) { rmax = std::max(rmax, scene_ordered(keys[i])); rneg = std::max(rneg, ~scene_ordered(keys[i])); }
+    for (uint32_t i = 0; i < n; ++i) out[i] = scene_bucket(keys[i], rmax, rneg);
+}
 int emu_scene_destroy(EmuDevice* d, uint32_t scene) {
     if (scene >= d->scenes.size() || !d->scenes[scene]) return VKR_ERROR_INVALID_ARGUMENT;
     if (d->lastScene == d->scenes[scene]) d->lastScene = nullptr;

@@ -198,6 +198,35 @@ def test_emu_random_scene_graphs(emu_lib, tmp_path, seed):
     host.close(); dev.close()
 
 
+def test_bucket_order_helpers(emu_lib):
+    """The order-preserving float -> uint32 map (atomicMax finds the key range with it) and the slice number of a key:
+    monotone over negative, zero, denormal and large keys; hidden draws (+inf) in the last slice; every slice in range."""
+    emu_lib.emu_scene_ordered.argtypes = [C.c_float]; emu_lib.emu_scene_ordered.restype = C.c_uint32
+    emu_lib.emu_scene_unordered.argtypes = [C.c_uint32]; emu_lib.emu_scene_unordered.restype = C.c_float
+    emu_lib.emu_scene_buckets.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p]
+    rng = np.random.default_rng(9)
+    keys = np.concatenate([rng.normal(0, 50, 4000), rng.uniform(-1e-38, 1e-38, 50), [0.0, -0.0, 1e30, -1e30, 3.5, 3.5],
+                           np.float32(10.0) + np.arange(64) * np.float32(1e-6)]).astype(np.float32)
+    order = np.argsort(keys, kind="stable")
+    mapped = np.array([emu_lib.emu_scene_ordered(float(k)) for k in keys], np.uint64)
+    ks, ms = keys[order], mapped[order].astype(np.int64)
+    strictly = ks[1:] > ks[:-1]                                        # (-0.0 == 0.0 as keys; their images differ by one)
+    assert np.all(np.diff(ms)[strictly] > 0) and np.all(np.abs(np.diff(ms)[~strictly]) <= 1), "ordered() must not reorder keys"
+    assert all(np.float32(emu_lib.emu_scene_unordered(int(m))).tobytes() == np.float32(k).tobytes() or k == 0.0 for m, k in zip(mapped[:200], keys[:200]))
+    for sample in (keys, keys[:4000], np.float32([5.0, 5.0, 5.0]), np.float32([-3.0, 7.0])):
+        withinf = np.concatenate([sample, np.float32([np.inf, np.inf])])
+        out = np.zeros(withinf.size, np.uint32)
+        emu_lib.emu_scene_buckets(withinf.ctypes.data, withinf.size, out.ctypes.data)
+        assert out[-1] == out[-2] == 2047 and out[:-2].max() <= 2046
+        o = np.argsort(sample, kind="stable")
+        assert np.all(np.diff(out[:-2][o].astype(np.int64)) >= 0), "a nearer key never lands in a later slice"
+        if sample.min() < sample.max():
+            assert out[:-2].min() == 0 and out[:-2].max() == 2046
+    out = np.zeros(2, np.uint32)
+    emu_lib.emu_scene_buckets(np.float32([np.inf, np.inf]).ctypes.data, 2, out.ctypes.data)
+    assert list(out) == [2047, 2047]                                   # no visible draw at all
+
+
 def _flat_scene(r, objs, bounds_radius=1.0e6):
     """A draw list as a one-level scene graph: node i carries object i's matrix; bounds so large that is_visible keeps all."""
     nodes = np.zeros(len(objs), capi.SCENE_NODE_DTYPE)
