@@ -4,7 +4,9 @@
 // Per frame, on the upload stream, in front of prepare_draws_kernel / expand_chunks_kernel (which read what these write):
 //   [scene_nodes_kernel x levels]   only after a transform changed: worldTransform of every node, a level of the tree per launch
 //   scene_draws_kernel              one thread per draw: is_visible, MVP, light MVPs, order keys -> DObject[n], shadowMvp, keys
-//   scene_rank_kernel               one thread per (pass, draw): its place in the pass's front-to-back order (counting rank)
+//   scene_rank_kernel               one thread per (pass, draw): its place in the pass's front-to-back order (counting rank);
+//                                   above SCENE_RANK_MAX draws instead scene_bucket_count / _scan / _place_kernel: a stable
+//                                   counting sort on SCENE_BUCKETS slices of the pass's key range
 //   scene_scan_kernel               one CTA: dense primitive ids of the visible draws, the passes' first work-item slots, the counts
 // The host's share of a frame no longer grows with the number of draws: it uploads nothing and launches a fixed list of kernels.
 #pragma once
