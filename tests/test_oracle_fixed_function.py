@@ -20,6 +20,7 @@ import scenes
 
 W, H = 64, 64
 NONE = 0xFFFFFFFF
+BACKEND_PREFIX = "ork"     # tests/test_rules_on_kernels.py re-runs the raster / depth / blend cases below on the kernels themselves
 
 
 # ------------------------------------------------------------------ the rules, restated independently (exact)
@@ -75,7 +76,7 @@ def rule_raster(tris, front_only=True):
 # ------------------------------------------------------------------ driving the oracle
 class Ork:
     def __init__(self, lib, tris, colors=None):
-        self.r = capi.Renderer(lib, "ork", W, H, shadow_extent=64)
+        self.r = capi.Renderer(lib, BACKEND_PREFIX, W, H, shadow_extent=64)
         pts = np.array([[tuple(v) + ((0.5,) if len(v) == 2 else ()) for v in t] for t in tris], np.float32)
         v, i = mg.triangles(pts, colors)
         self.mesh = self.r.upload_mesh(i, v)
@@ -446,3 +447,96 @@ def test_cube_filtering_is_seamless_across_all_twelve_edges(ork_lib):
     assert edges == 12
     assert max(jumps) < 2e-3, f"colour jumps by {max(jumps):.4f} across a cube edge"
     r.close()
+
+
+# ------------------------------------------------------------------ scissor, attachments, blending, the shadow pass's state
+def test_scissor_keeps_exactly_its_pixels(ork_lib):
+    """VkRect2D scissor: a fragment at pixel (x, y) survives iff offset <= (x, y) < offset + extent."""
+    o = Ork(ork_lib, front(0, 0, 64, 64))
+    o.fp.scissor[:] = (5, 7, 20, 11)
+    prim, depth = o.draw()
+    assert pixels(prim) == {(x, y) for x in range(5, 25) for y in range(7, 18)}
+    assert np.all(depth[prim == NONE] == 1.0)
+    o.close()
+
+
+def _f16(x):
+    return np.float16(np.float32(x))
+
+
+def test_colour_attachment_conversions(ork_lib):
+    """The draw image is R16G16B16A16_SFLOAT (round to nearest even on store), the presented image 8-bit UNORM
+    (round(255 c) on the blit, src/vk_engine_run.cpp:159-161).  Fragment colour = ambient * vertex colour * base texel:
+    ambient 0.25, the default texel of bindless slot 0 is (128, 128, 255) / 255."""
+    cols = np.array([[0.3, 0.7, 0.9, 1.0]] * 6, np.float32)
+    o = Ork(ork_lib, front(8, 8, 24, 24), cols)
+    o.draw()
+    hdr = o.r.readback(capi.TARGET_HDR16F)
+    rgba = o.r.readback(capi.TARGET_RGBA8)
+    base = np.array([128, 128, 255], np.float64) / 255.0
+    want = (np.float32(0.25) * cols[0, :3].astype(np.float64) * base)
+    px = hdr[12, 12]
+    for c in range(3):                      # the f32 product rounded once to f16 (the products' own f32 roundings are below half an f16 ulp apart)
+        assert abs(float(px[c]) - want[c]) <= abs(float(np.spacing(np.float16(want[c])))) * 0.51
+        assert int(rgba[12, 12, c]) == int(np.floor(float(px[c]) * 255.0 + 0.5))
+    assert px[3] == 1.0 and rgba[12, 12, 3] == 255
+    assert np.all(rgba[40, 40] == (0, 0, 0, 255)) and np.all(hdr[40, 40] == (0, 0, 0, 1))     # clear colour (0, 0, 0, 1)
+    o.close()
+
+
+def test_additive_blend_sums_in_the_f16_attachment(ork_lib):
+    """"Transparent" pipeline: colour blend SRC_ALPHA / ONE / ADD, alpha ONE / ZERO (src/vk_pipelines.cpp:108-118): every
+    fragment adds src.rgb * src.a to what the RGBA16F attachment holds; with n layers of one constant colour the stored
+    value stays within n half-ulps of n times that colour (one f16 rounding per fragment at most, one in all at least)."""
+    tri = [(10.5, 10.5), (10.5, 30.5), (30.5, 10.5)]
+    for n in (1, 2, 3, 5):
+        o = Ork(ork_lib, [[p + (0.5,) for p in tri]] * n)
+        o.fragment_counts()                   # draws the n triangles with the additive material
+        hdr = o.r.readback(capi.TARGET_HDR16F).astype(np.float64)
+        assert hdr[40, 40, 0] == 0.0
+        unit = 0.25 * 128.0 / 255.0
+        got = hdr[15, 15, 0]
+        assert abs(got - n * unit) <= n * 0.5 * float(np.spacing(np.float16(n * unit))) + 1e-12
+        assert hdr[15, 15, 3] == 1.0
+        o.close()
+
+
+def test_transparent_pass_tests_depth_but_does_not_write_it(ork_lib):
+    """Transparent: depthTest on (LESS_OR_EQUAL), depthWrite off (src/vk_engine_init.cpp:545-547)."""
+    tri = [(10.5, 10.5), (10.5, 30.5), (30.5, 10.5)]
+    z = lambda zz: [p + (zz,) for p in tri]
+    o = Ork(ork_lib, [z(0.5), z(0.75), z(0.25), z(0.25), z(0.5)])
+    mk = lambda k, mat: mg.render_object(o.mesh, mat, np.eye(4), 3, first_index=3 * k)
+    # opaque at 0.5; transparent ones behind (0.75: fails), in front (0.25, twice: both pass — no depth write between them), equal (0.5: passes)
+    objs = np.array([mk(0, o.opaque), mk(1, o.additive), mk(2, o.additive), mk(3, o.additive), mk(4, o.additive)])
+    o.r.draw(o.sd, objs, o.fp)
+    depth = o.r.readback(capi.TARGET_DEPTH)
+    hdr = o.r.readback(capi.TARGET_HDR16F).astype(np.float64)
+    unit = 0.25 * 128.0 / 255.0
+    assert depth[15, 15] == 0.5                                    # still the opaque surface's depth
+    assert abs(hdr[15, 15, 0] - 4 * unit) < 4 * 0.5 * float(np.spacing(np.float16(4 * unit)))      # opaque + three transparent fragments
+    o.close()
+
+
+def test_shadow_pass_culls_front_faces_and_stores_the_plane_depth(ork_lib):
+    """draw_shadow's pipeline: cull FRONT, front face counter-clockwise, depth-only, D32 cleared to 1.0
+    (src/vk_engine_init.cpp:439-447, src/vk_engine_run.cpp:348-360).  Light matrix = the same pixel-space map onto the 64^2 shadow
+    map: a triangle that is counter-clockwise on the light's screen writes nothing, a clockwise one its plane."""
+    ccw = [(10.5, 10.5, 0.25), (10.5, 30.5, 0.25), (30.5, 10.5, 0.25)]
+    cw = [(40.5, 10.5, 0.25), (60.5, 10.5, 0.5), (40.5, 30.5, 0.75)]
+    o = Ork(ork_lib, [ccw, cw])
+    view, proj = scenes.pixel_space(o.r)
+    o.sd = capi.make_scene_data(view, proj, [proj] * 4, sun_dir=(0.0, 0.0, 1.0, 0.0), sun_color=(0, 0, 0, 1), ambient=(0.25, 0.25, 0.25, 1.0),
+                                shadow_mode=0, enable_shadows=True)
+    o.fp.enableShadows = 1
+    o.fp.shadowMode = 0
+    prim, _ = o.draw()
+    assert len(pixels(prim, 0)) > 100 and len(pixels(prim, 1)) == 0          # the main pass culls the other one
+    sh = o.r.readback(capi.TARGET_SHADOW)[0]
+    assert np.all(sh[8:32, 8:32] == 1.0), "a front face (as the light sees it) must not be in the shadow map"
+    ys, xs = np.nonzero(sh != 1.0)
+    want_px = {p for p, ks in rule_raster([cw], front_only=False).items()}
+    assert set(zip(xs.tolist(), ys.tolist())) == want_px and len(want_px) > 150
+    want = 0.25 + (xs + 0.5 - 40.5) * (0.25 / 20.0) + (ys + 0.5 - 10.5) * (0.5 / 20.0)
+    assert np.max(np.abs(sh[ys, xs].astype(np.float64) - want)) < 4e-7
+    o.close()
