@@ -428,6 +428,40 @@ int emu_scene_create(EmuDevice* d, const VkrSceneNode* nodes, size_t nn, const V
     *out = (uint32_t)d->scenes.size() - 1;
     return 0;
 }
+// Test probes of the kernels' texture unit (vkr_shade.cuh texture2d / texture_cube, the mip chain of create_image), with the
+// signatures of the oracle's ork_image_level / ork_cb_tex2d / ork_cb_cube: tests/test_rules_on_kernels.py asks them the
+// known answers of the Vulkan texture rules.
+struct EmuTexCtx { EmuDevice* dev; float duvdx[2], duvdy[2]; };
+int emu_image_level(EmuDevice* d, uint32_t image, int level, void* dst, size_t bytes, uint32_t* w, uint32_t* h) {
+    if (!d || image >= d->images.size()) return VKR_ERROR_INVALID_ARGUMENT;
+    const EmuImage& im = *d->images[image];
+    if (level < 0) return (int)im.levels;
+    if (level >= (int)im.levels) return VKR_ERROR_INVALID_ARGUMENT;
+    const uint32_t lw = std::max(1u, im.w >> level), lh = std::max(1u, im.h >> level);
+    if (w) *w = lw;
+    if (h) *h = lh;
+    if (dst) {
+        if (bytes < (size_t)lw * lh * 4) return VKR_ERROR_INVALID_ARGUMENT;
+        std::memcpy(dst, im.data.data() + im.mipOffset[level], (size_t)lw * lh * 4);
+    }
+    return 0;
+}
+void emu_cb_tex2d(void* ctx, int id, float u, float v, float out[4]) {
+    const EmuTexCtx* c = (const EmuTexCtx*)ctx;
+    ShadeBuffers sb{};
+    sb.textures = c->dev->tex.data(); sb.srgbLut = c->dev->lut;
+    const float4 t = texture2d(sb, id, u, v, c->duvdx[0], c->duvdx[1], c->duvdy[0], c->duvdy[1]);
+    out[0] = t.x; out[1] = t.y; out[2] = t.z; out[3] = t.w;
+}
+void emu_cb_cube(void* ctx, const float dir[3], float out[4]) {
+    const EmuTexCtx* c = (const EmuTexCtx*)ctx;
+    ShadeBuffers sb{};
+    sb.textures = c->dev->tex.data(); sb.srgbLut = c->dev->lut; sb.cube = c->dev->cube;
+    const f3 r = {dir[0], dir[1], dir[2]};
+    const float4 t = texture_cube(sb, r, r, r);
+    out[0] = t.x; out[1] = t.y; out[2] = t.z; out[3] = t.w;
+}
+
 // Test hooks for the bucket order's helpers (vkr_scene.cuh): the order-preserving float -> uint32 map and the slice of a key
 uint32_t emu_scene_ordered(float f) { return scene_ordered(f); }
 float emu_scene_unordered(uint32_t u) { return scene_unordered(u); }

@@ -300,16 +300,17 @@ def srgb_encode(l):
 
 
 def image_level(lib, r, img, level, w, h):
-    lib.ork_image_level.argtypes = [C.c_void_p, C.c_uint32, C.c_int, C.c_void_p, C.c_size_t, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
+    fn = getattr(lib, f"{BACKEND_PREFIX}_image_level")
+    fn.argtypes = [C.c_void_p, C.c_uint32, C.c_int, C.c_void_p, C.c_size_t, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
     out = np.zeros((h, w, 4), np.uint8)
     ww, hh = C.c_uint32(), C.c_uint32()
-    assert lib.ork_image_level(r.dev, img, level, out.ctypes.data, out.nbytes, C.byref(ww), C.byref(hh)) == 0
+    assert fn(r.dev, img, level, out.ctypes.data, out.nbytes, C.byref(ww), C.byref(hh)) == 0
     assert (ww.value, hh.value) == (w, h)
     return out
 
 
 def test_mip_blit_is_a_linear_light_box_filter(ork_lib):
-    r = capi.Renderer(ork_lib, "ork", 16, 16, shadow_extent=16)
+    r = capi.Renderer(ork_lib, BACKEND_PREFIX, 16, 16, shadow_extent=16)
     tex = np.array([[[255, 0, 10, 255], [0, 0, 200, 0]], [[0, 255, 90, 255], [0, 0, 130, 0]]], np.uint8)
     img = r.create_image(tex, capi.FORMAT_SRGB, True)                 # generate_mipmaps: 2x2 -> 1x1 by one LINEAR blit
     lvl = image_level(ork_lib, r, img, 1, 1, 1)[0, 0]
@@ -331,16 +332,17 @@ class TexCtx(C.Structure):
 
 
 def sample2d(lib, r, slot, u, v, ddx=(0, 0), ddy=(0, 0)):
-    lib.ork_cb_tex2d.argtypes = [C.c_void_p, C.c_int, C.c_float, C.c_float, C.POINTER(C.c_float)]
-    lib.ork_cb_tex2d.restype = None
+    fn = getattr(lib, f"{BACKEND_PREFIX}_cb_tex2d")
+    fn.argtypes = [C.c_void_p, C.c_int, C.c_float, C.c_float, C.POINTER(C.c_float)]
+    fn.restype = None
     ctx = TexCtx(r.dev, (C.c_float * 2)(*ddx), (C.c_float * 2)(*ddy))
     out = (C.c_float * 4)()
-    lib.ork_cb_tex2d(C.byref(ctx), slot, u, v, out)
+    fn(C.byref(ctx), slot, u, v, out)
     return np.array(out[:], np.float64)
 
 
 def test_bilinear_repeat_sample_across_the_wrap(ork_lib):
-    r = capi.Renderer(ork_lib, "ork", 16, 16, shadow_extent=16)
+    r = capi.Renderer(ork_lib, BACKEND_PREFIX, 16, 16, shadow_extent=16)
     tex = np.zeros((4, 4, 4), np.uint8)
     tex[..., 0] = np.array([10, 50, 90, 250])[None, :]                # red varies along x
     tex[..., 1] = np.array([0, 100, 200, 40])[:, None]                # green varies along y
@@ -361,7 +363,7 @@ def test_bilinear_repeat_sample_across_the_wrap(ork_lib):
 
 
 def test_trilinear_level_selection(ork_lib):
-    r = capi.Renderer(ork_lib, "ork", 16, 16, shadow_extent=16)
+    r = capi.Renderer(ork_lib, BACKEND_PREFIX, 16, 16, shadow_extent=16)
     tex = np.zeros((8, 8, 4), np.uint8)
     tex[::2, ::2, 0] = 200                                            # level 1 = 50 everywhere, level 2 = 50, level 3 = 50
     tex[..., 3] = 255
@@ -380,7 +382,7 @@ def test_trilinear_level_selection(ork_lib):
 
 
 def test_cube_face_selection_and_orientation(ork_lib):
-    r = capi.Renderer(ork_lib, "ork", 16, 16, shadow_extent=16)
+    r = capi.Renderer(ork_lib, BACKEND_PREFIX, 16, 16, shadow_extent=16)
     n = 32
     faces = []
     for f in range(6):
@@ -391,8 +393,9 @@ def test_cube_face_selection_and_orientation(ork_lib):
         img[..., 3] = 255
         faces.append(img)
     r.set_cubemap(faces, capi.FORMAT_UNORM, False)
-    ork_lib.ork_cb_cube.argtypes = [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float)]
-    ork_lib.ork_cb_cube.restype = None
+    cb_cube = getattr(ork_lib, f"{BACKEND_PREFIX}_cb_cube")
+    cb_cube.argtypes = [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float)]
+    cb_cube.restype = None
     ctx = TexCtx(r.dev, (C.c_float * 2)(0, 0), (C.c_float * 2)(0, 0))
     # Vulkan's table: face, (s_c, t_c) for the major axis; s = (s_c / |m| + 1) / 2
     table = [((1, 0, 0), lambda x, y, z: (-z, -y)), ((-1, 0, 0), lambda x, y, z: (z, -y)), ((0, 1, 0), lambda x, y, z: (x, z)),
@@ -402,7 +405,7 @@ def test_cube_face_selection_and_orientation(ork_lib):
         d[(np.argmax(np.abs(d)) + 1) % 3] = 0.5
         d[(np.argmax(np.abs(d)) + 2) % 3] = -0.7
         out = (C.c_float * 4)()
-        ork_lib.ork_cb_cube(C.byref(ctx), (C.c_float * 3)(*d), out)
+        cb_cube(C.byref(ctx), (C.c_float * 3)(*d), out)
         sc, tc = st(*d)
         s, t = 0.5 * (sc / 2.0 + 1.0), 0.5 * (tc / 2.0 + 1.0)
         assert abs(out[2] * 255 - 40 * f) < 1e-3, f"direction {d} must select face {f}"
@@ -417,18 +420,19 @@ def test_cube_filtering_is_seamless_across_all_twelve_edges(ork_lib):
     selected face jumps by about half the difference of the two faces' edge texels.  Random texels, so that a neighbour
     addressed with a mirrored or transposed coordinate breaks the continuity too.  (Cube corners, where a tap has no texel,
     are kept a texel and a half away.)"""
-    r = capi.Renderer(ork_lib, "ork", 16, 16, shadow_extent=16)
+    r = capi.Renderer(ork_lib, BACKEND_PREFIX, 16, 16, shadow_extent=16)
     n = 8
     rng = np.random.default_rng(7)
     faces = [np.concatenate([rng.integers(0, 256, (n, n, 3), dtype=np.uint8), np.full((n, n, 1), 255, np.uint8)], -1) for _ in range(6)]
     r.set_cubemap(faces, capi.FORMAT_UNORM, False)
-    ork_lib.ork_cb_cube.argtypes = [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float)]
-    ork_lib.ork_cb_cube.restype = None
+    cb_cube = getattr(ork_lib, f"{BACKEND_PREFIX}_cb_cube")
+    cb_cube.argtypes = [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float)]
+    cb_cube.restype = None
     ctx = TexCtx(r.dev, (C.c_float * 2)(0, 0), (C.c_float * 2)(0, 0))
 
     def sample(d):
         out = (C.c_float * 4)()
-        ork_lib.ork_cb_cube(C.byref(ctx), (C.c_float * 3)(*[float(v) for v in d]), out)
+        cb_cube(C.byref(ctx), (C.c_float * 3)(*[float(v) for v in d]), out)
         return np.array(out[:3], np.float64)
 
     axes = np.eye(3)

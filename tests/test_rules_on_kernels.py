@@ -3,7 +3,8 @@ arithmetic, top-left ties, slivers, winding and culling, LESS_OR_EQUAL in submis
 the scissor, attachment conversions, the additive blend, the Transparent pass's depth state, the shadow pass's cull mode — asked
 of the KERNELS directly: their host emulation on the CPU, libvkr on the B200.  The parity tests hold the kernels to the oracle and
 that file holds the oracle to the rules; this one closes the triangle without going through the oracle at all.
-(The texture-unit cases of that file probe oracle-only entry points and stay there.)"""
+The texture-unit cases (mip blit, REPEAT bilinear, NEAREST, trilinear level selection, cube faces, seamless cube edges) go
+through probe entry points that only the emulation has beside the oracle: they run on the emulated kernels."""
 import pytest
 
 import test_oracle_fixed_function as ff
@@ -29,7 +30,16 @@ CASES = [
 ]
 
 
-@pytest.mark.parametrize("case", CASES, ids=lambda f: f.__name__[5:])
+TEXTURE_CASES = [
+    ff.test_mip_blit_is_a_linear_light_box_filter,
+    ff.test_bilinear_repeat_sample_across_the_wrap,
+    ff.test_trilinear_level_selection,
+    ff.test_cube_face_selection_and_orientation,
+    ff.test_cube_filtering_is_seamless_across_all_twelve_edges,
+]
+
+
+@pytest.mark.parametrize("case", CASES + TEXTURE_CASES, ids=lambda f: f.__name__[5:])
 def test_rule_on_the_emulated_kernels(case, emu_lib, monkeypatch):
     monkeypatch.setattr(ff, "BACKEND_PREFIX", "emu")
     case(emu_lib)
