@@ -331,6 +331,11 @@ def test_scene_create_refuses_what_it_cannot_draw(emu_lib):
             s2[0]["indexCount"] = 1 << 30
         with pytest.raises(capi.VkrError):
             r.scene_create(n2, s2)
+    # a graph without a single surface draws the background and counts nothing
+    empty = r.scene_create(nodes, surf[:0])
+    r.draw_scene(empty, sd, _planes_everything(), fp)
+    assert r.scene_draw_list(empty).size == 0 and r.stats().drawcall_count == 0 and r.stats().triangle_count == 0
+    assert (r.readback(capi.TARGET_PRIMID) == 0xFFFFFFFF).all()
     # a destroyed scene is dead, the others live on; the engine replaces its scene when the graph changes
     a, b = r.scene_create(nodes, surf), r.scene_create(nodes, surf)
     r.scene_destroy(a)
@@ -412,6 +417,34 @@ def test_gpu_random_scene_graph(vkr_lib, tmp_path):
     cams = [(tuple(rng.uniform(-6, 6, 3) + np.array([0, 0, 6.0])), float(rng.uniform(-0.4, 0.4)), float(rng.uniform(-1.0, 1.0))) for _ in range(3)]
     _check_cameras(host, dev, cams, "random tree 2")
     host.close(); dev.close()
+
+
+@pytest.mark.gpu
+def test_gpu_scene_handles_live_and_die_independently(vkr_lib):
+    """vkr_scene_destroy, a scene without surfaces, and a scene created after another was destroyed, on the device."""
+    r = capi.Renderer(vkr_lib, "vkr", 160, 96, shadow_extent=128)
+    sd, objs, fp = scenes.SCENES["basic_pcf"](r)
+    r.draw(sd, objs, fp)
+    want = {k: r.readback(t) for k, t in TARGETS.items()}
+    a = _flat_scene(r, objs)
+    nodes = np.zeros(1, capi.SCENE_NODE_DTYPE)
+    nodes["localTransform"][0] = np.eye(4, dtype=np.float32).reshape(-1)
+    nodes["parent"] = -1
+    empty = r.scene_create(nodes, np.zeros(0, capi.SCENE_SURFACE_DTYPE))
+    r.draw_scene(empty, sd, _planes_everything(), fp)
+    assert r.stats().drawcall_count == 0 and (r.readback(capi.TARGET_PRIMID) == 0xFFFFFFFF).all()
+    r.draw_scene(a, sd, _planes_everything(), fp)
+    r.scene_destroy(empty)
+    b = _flat_scene(r, objs)
+    r.scene_destroy(a)
+    with pytest.raises(capi.VkrError):
+        r.draw_scene(a, sd, _planes_everything(), fp)
+    r.draw_scene(b, sd, _planes_everything(), fp)
+    for k, t in TARGETS.items():
+        got = r.readback(t)
+        assert np.array_equal(got.view(np.uint8), want[k].view(np.uint8)), k
+    assert r.stats().drawcall_count == len(objs)
+    r.close()
 
 
 @pytest.mark.gpu

@@ -1520,6 +1520,9 @@ static int submit_frame(VkrDevice* dev, FramePlan& plan, size_t n) {
         LAUNCHED("scene kernels");
         dev->launches += 3;
         dClusterBase = scn->dClusterBase; dSeqSlotBase = scn->dSeqSlotBase;
+    } else {                                     // a scene without a single surface: nothing runs that would count
+        CK(cudaStreamSynchronize(dev->upStream));
+        dev->countersHost[13] = dev->countersHost[14] = 0u;
     }
     const DObject* dObjects = (const DObject*)(dp + offObj);
     const DChunk* dChunks = slot.chunkBuf;
