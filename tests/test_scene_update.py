@@ -15,7 +15,7 @@ import ctypes as C
 import numpy as np
 import pytest
 
-from vk_renderer_b200 import capi
+from vk_renderer_b200 import capi, meshgen as mg
 from vk_renderer_b200.engine import Engine
 import gltf_util as gu
 import parity
@@ -445,6 +445,49 @@ def test_gpu_scene_handles_live_and_die_independently(vkr_lib):
         assert np.array_equal(got.view(np.uint8), want[k].view(np.uint8)), k
     assert r.stats().drawcall_count == len(objs)
     r.close()
+
+
+def _rebinding_case(lib, prefix):
+    """The cut-out scene with slots 3 and 4 first bound to an opaque checker: the scene is created while no draw is alpha-tested,
+    then the cut-out textures arrive (update_bindless_texture, as a streaming loader would) — the draws' flags, the cut-out
+    kernel's launch and the mip-derivative bit must follow the slots."""
+    a = capi.Renderer(lib, prefix, 200, 120, shadow_extent=128)
+    b = capi.Renderer(lib, prefix, 200, 120, shadow_extent=128)
+    frames = []
+    for r, use_scene in ((a, False), (b, True)):
+        sd, objs, fp = scenes.SCENES["cutout"](r)
+        opaque = r.create_image(mg.checker_texture(64, 8, seed=3), capi.FORMAT_SRGB, True)
+        cut3 = r.create_image(mg.cutout_texture(128, 4, seed=2), capi.FORMAT_SRGB, True)
+        cut4 = r.create_image(mg.cutout_texture(32, 2, seed=5), capi.FORMAT_UNORM, False)
+        r.update_bindless_texture(3, opaque, capi.SAMPLER_LINEAR)
+        r.update_bindless_texture(4, opaque, capi.SAMPLER_LINEAR)
+        sc = _flat_scene(r, objs) if use_scene else None
+        out = []
+        for phase in range(2):
+            if phase == 1:
+                r.update_bindless_texture(3, cut3, capi.SAMPLER_LINEAR)
+                r.update_bindless_texture(4, cut4, capi.SAMPLER_NEAREST)
+            if use_scene:
+                r.draw_scene(sc, sd, _planes_everything(), fp)
+            else:
+                r.draw(sd, objs, fp)
+            out.append({k: r.readback(t) for k, t in TARGETS.items()})
+        frames.append(out)
+        r.close()
+    for phase in range(2):
+        for k in TARGETS:
+            x, y = frames[0][phase][k], frames[1][phase][k]
+            assert np.array_equal(x.view(np.uint8), y.view(np.uint8)), f"phase {phase}: {k} differs on {(x != y).sum()} elements"
+    assert not np.array_equal(frames[0][0]["prim"], frames[0][1]["prim"]), "the cut-outs were meant to open holes"
+
+
+def test_emu_scene_follows_rebound_textures(emu_lib):
+    _rebinding_case(emu_lib, "emu")
+
+
+@pytest.mark.gpu
+def test_gpu_scene_follows_rebound_textures(vkr_lib):
+    _rebinding_case(vkr_lib, "vkr")
 
 
 @pytest.mark.gpu
