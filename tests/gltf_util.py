@@ -18,12 +18,37 @@ FLOAT, UBYTE, USHORT, UINT = 5126, 5121, 5123, 5125
 
 
 # ------------------------------------------------------------------------------------------------------------ PNG
-def png_bytes(img: np.ndarray, color_type: int, filt: int = 0, palette=None, trns=None, depth: int = 8) -> bytes:
-    """img: (H, W, C) uint8 samples already in the PNG's own channel layout (C = 1, 2, 3 or 4; indices for palette)."""
+ADAM7 = [(0, 0, 8, 8), (4, 0, 8, 8), (0, 4, 4, 8), (2, 0, 4, 4), (0, 2, 2, 4), (1, 0, 2, 2), (0, 1, 1, 2)]
+
+
+def png_bytes(img: np.ndarray, color_type: int, filt: int = 0, palette=None, trns=None, depth: int = 8, interlace: bool = False) -> bytes:
+    """img: (H, W, C) uint8 samples already in the PNG's own channel layout (C = 1, 2, 3 or 4; indices for palette).
+    interlace: Adam7 — the seven reduced images one after the other, each with its own scan lines (8-bit samples only here)."""
     h, w = img.shape[:2]
-    rows = img.reshape(h, -1).astype(np.uint8)
     bpp = max(1, img.shape[2] * depth // 8)
     out = bytearray()
+    passes = [img[y0::dy, x0::dx] for x0, y0, dx, dy in ADAM7] if interlace else [img]
+    for sub in passes:
+        if sub.shape[0] == 0 or sub.shape[1] == 0:
+            continue
+        _filter_rows(sub, bpp, filt, out)
+
+    def chunk(tag, body):
+        return struct.pack(">I", len(body)) + tag + body + struct.pack(">I", zlib.crc32(tag + body))
+    data = b"\x89PNG\r\n\x1a\n" + chunk(b"IHDR", struct.pack(">IIBBBBB", w, h, depth, color_type, 0, 0, 1 if interlace else 0))
+    if palette is not None:
+        data += chunk(b"PLTE", np.asarray(palette, np.uint8).tobytes())
+    if trns is not None:
+        data += chunk(b"tRNS", np.asarray(trns, np.uint8).tobytes())
+    comp = zlib.compress(bytes(out), 6)
+    half = len(comp) // 2
+    data += chunk(b"IDAT", comp[:half]) + chunk(b"IDAT", comp[half:]) + chunk(b"IEND", b"")     # two IDAT chunks on purpose
+    return data
+
+
+def _filter_rows(img, bpp, filt, out):
+    h = img.shape[0]
+    rows = np.ascontiguousarray(img).reshape(h, -1).astype(np.uint8)
     prev = np.zeros(rows.shape[1], np.int32)
     for y in range(h):
         cur = rows[y].astype(np.int32)
@@ -45,18 +70,6 @@ def png_bytes(img: np.ndarray, color_type: int, filt: int = 0, palette=None, trn
         out.append(ft)
         out += ((cur - pred) & 255).astype(np.uint8).tobytes()
         prev = cur
-
-    def chunk(tag, body):
-        return struct.pack(">I", len(body)) + tag + body + struct.pack(">I", zlib.crc32(tag + body))
-    data = b"\x89PNG\r\n\x1a\n" + chunk(b"IHDR", struct.pack(">IIBBBBB", w, h, depth, color_type, 0, 0, 0))
-    if palette is not None:
-        data += chunk(b"PLTE", np.asarray(palette, np.uint8).tobytes())
-    if trns is not None:
-        data += chunk(b"tRNS", np.asarray(trns, np.uint8).tobytes())
-    comp = zlib.compress(bytes(out), 6)
-    half = len(comp) // 2
-    data += chunk(b"IDAT", comp[:half]) + chunk(b"IDAT", comp[half:]) + chunk(b"IEND", b"")     # two IDAT chunks on purpose
-    return data
 
 
 def make_images(rng):

@@ -35,6 +35,16 @@ def test_png_decoder_matches_the_encoder():
     for filt in range(5):                                   # every scan-line filter on its own
         img = rng.integers(0, 256, (9, 7, 4), dtype=np.uint8)
         assert np.array_equal(eng_mod.decode_png(gu.png_bytes(img, 6, filt=filt)), img)
+    # Adam7 interlacing (stb_image reads it): sizes around the 8 x 8 pattern, some passes empty; checked against PIL too
+    from PIL import Image
+    import io
+    for (h, w), ctype, ch in (((9, 7), 6, 4), ((1, 1), 2, 3), ((3, 2), 6, 4), ((16, 16), 2, 3), ((5, 33), 0, 1), ((13, 4), 4, 2)):
+        img = rng.integers(0, 256, (h, w, ch), dtype=np.uint8)
+        data = gu.png_bytes(img, ctype, filt=5, interlace=True)
+        got = eng_mod.decode_png(data)
+        ref = np.asarray(Image.open(io.BytesIO(data)).convert("RGBA"))
+        assert got is not None and np.array_equal(got, ref), (h, w, ctype)
+        assert np.array_equal(got, eng_mod.decode_png(gu.png_bytes(img, ctype, filt=5)))      # the same pixels as the plain file
     assert eng_mod.decode_png(b"\xff\xd8\xff\xe0 jpeg") is None
     good = gu.png_bytes(rng.integers(0, 256, (4, 4, 3), dtype=np.uint8), 2)
     assert eng_mod.decode_png(good[:len(good) // 2]) is None          # truncated stream

@@ -219,65 +219,86 @@ bool decode_png(const unsigned char* d, size_t n, std::vector<unsigned char>& rg
         else if (!std::memcmp(tag, "IEND", 4)) break;
         pos += 12 + (size_t)len;
     }
-    if (!haveHdr || W == 0 || H == 0 || W > 16384 || H > 16384 || interlace != 0) return false;
+    if (!haveHdr || W == 0 || H == 0 || W > 16384 || H > 16384 || interlace > 1) return false;
     if (depth != 8 && depth != 16 && !(ctype == 3 || ctype == 0)) return false;
     int channels;
     switch (ctype) { case 0: channels = 1; break; case 2: channels = 3; break; case 3: channels = 1; break; case 4: channels = 2; break; case 6: channels = 4; break; default: return false; }
     if ((ctype == 3 && (depth > 8 || plte.empty())) || (depth != 1 && depth != 2 && depth != 4 && depth != 8 && depth != 16)) return false;
     const size_t bpp = std::max<size_t>(1, (size_t)channels * depth / 8);        // filter unit
-    const size_t stride = ((size_t)W * channels * depth + 7) / 8;
-    std::vector<unsigned char> raw((stride + 1) * H);
+    // The image is one pass, or (interlace method 1, Adam7 — stb_image reads those too) seven reduced images stored one after
+    // the other: pass p holds the pixels (x0 + i * dx, y0 + j * dy), each with its own scan lines and filters.
+    struct Pass { uint32_t x0, y0, dx, dy; };
+    static const Pass adam7[7] = {{0, 0, 8, 8}, {4, 0, 8, 8}, {0, 4, 4, 8}, {2, 0, 4, 4}, {0, 2, 2, 4}, {1, 0, 2, 2}, {0, 1, 1, 2}};
+    static const Pass whole = {0, 0, 1, 1};
+    const int nPasses = interlace ? 7 : 1;
+    auto pass_dim = [](uint32_t full, uint32_t o, uint32_t step) { return full > o ? (full - o + step - 1) / step : 0u; };
+    size_t rawSize = 0;
+    for (int p = 0; p < nPasses; ++p) {
+        const Pass& ps = interlace ? adam7[p] : whole;
+        const uint32_t pw = pass_dim(W, ps.x0, ps.dx), ph = pass_dim(H, ps.y0, ps.dy);
+        if (pw && ph) rawSize += (((size_t)pw * channels * depth + 7) / 8 + 1) * ph;
+    }
+    std::vector<unsigned char> raw(rawSize);
     uLongf rawLen = (uLongf)raw.size();
     if (uncompress(raw.data(), &rawLen, idat.data(), (uLong)idat.size()) != Z_OK || rawLen != raw.size()) return false;
-    // undo the scanline filters in place
-    std::vector<unsigned char> zero(stride, 0);
-    for (uint32_t y = 0; y < H; ++y) {
-        unsigned char* row = raw.data() + (size_t)y * (stride + 1);
-        const int ft = row[0];
-        unsigned char* cur = row + 1;
-        const unsigned char* up = y ? raw.data() + (size_t)(y - 1) * (stride + 1) + 1 : zero.data();
-        for (size_t i = 0; i < stride; ++i) {
-            const int a = i >= bpp ? cur[i - bpp] : 0, b = up[i], c = i >= bpp ? up[i - bpp] : 0;
-            int pred;
-            switch (ft) {
-                case 0: pred = 0; break;
-                case 1: pred = a; break;
-                case 2: pred = b; break;
-                case 3: pred = (a + b) >> 1; break;
-                case 4: { const int p = a + b - c, pa = std::abs(p - a), pb = std::abs(p - b), pc = std::abs(p - c);
-                          pred = (pa <= pb && pa <= pc) ? a : (pb <= pc ? b : c); break; }
-                default: return false;
-            }
-            cur[i] = (unsigned char)(cur[i] + pred);
-        }
-    }
     rgba.resize((size_t)W * H * 4);
-    for (uint32_t y = 0; y < H; ++y) {
-        const unsigned char* row = raw.data() + (size_t)y * (stride + 1) + 1;
-        for (uint32_t x = 0; x < W; ++x) {
-            unsigned char* o = &rgba[((size_t)y * W + x) * 4];
-            auto sample = [&](int ch) -> unsigned {          // channel value reduced to 8 bits the way stb_image does (high byte)
-                if (depth == 16) return row[((size_t)x * channels + ch) * 2];
-                if (depth == 8) return row[(size_t)x * channels + ch];
-                const size_t bit = ((size_t)x * channels + ch) * depth;
-                const unsigned v = (row[bit >> 3] >> (8 - depth - (bit & 7))) & ((1u << depth) - 1);
-                return ctype == 3 ? v : v * 255u / ((1u << depth) - 1);
-            };
-            switch (ctype) {
-                case 0: {
-                    const unsigned g = sample(0);
-                    o[0] = o[1] = o[2] = (unsigned char)g; o[3] = 255;
-                    if (trns.size() >= 2 && depth <= 8 && g == (unsigned)(trns[1] * (depth < 8 ? 255u / ((1u << depth) - 1) : 1u))) o[3] = 0;
-                    break;
+    size_t passBase = 0;
+    for (int p = 0; p < nPasses; ++p) {
+        const Pass& ps = interlace ? adam7[p] : whole;
+        const uint32_t pw = pass_dim(W, ps.x0, ps.dx), ph = pass_dim(H, ps.y0, ps.dy);
+        if (!pw || !ph) continue;
+        const size_t stride = ((size_t)pw * channels * depth + 7) / 8;
+        unsigned char* base = raw.data() + passBase;
+        passBase += (stride + 1) * ph;
+        // undo the scanline filters in place
+        std::vector<unsigned char> zero(stride, 0);
+        for (uint32_t y = 0; y < ph; ++y) {
+            unsigned char* row = base + (size_t)y * (stride + 1);
+            const int ft = row[0];
+            unsigned char* cur = row + 1;
+            const unsigned char* up = y ? base + (size_t)(y - 1) * (stride + 1) + 1 : zero.data();
+            for (size_t i = 0; i < stride; ++i) {
+                const int a = i >= bpp ? cur[i - bpp] : 0, b = up[i], c = i >= bpp ? up[i - bpp] : 0;
+                int pred;
+                switch (ft) {
+                    case 0: pred = 0; break;
+                    case 1: pred = a; break;
+                    case 2: pred = b; break;
+                    case 3: pred = (a + b) >> 1; break;
+                    case 4: { const int pp = a + b - c, pa = std::abs(pp - a), pb = std::abs(pp - b), pc = std::abs(pp - c);
+                              pred = (pa <= pb && pa <= pc) ? a : (pb <= pc ? b : c); break; }
+                    default: return false;
                 }
-                case 2: o[0] = (unsigned char)sample(0); o[1] = (unsigned char)sample(1); o[2] = (unsigned char)sample(2); o[3] = 255;
-                        if (trns.size() >= 6 && depth == 8 && o[0] == trns[1] && o[1] == trns[3] && o[2] == trns[5]) o[3] = 0;
+                cur[i] = (unsigned char)(cur[i] + pred);
+            }
+        }
+        for (uint32_t y = 0; y < ph; ++y) {
+            const unsigned char* row = base + (size_t)y * (stride + 1) + 1;
+            for (uint32_t x = 0; x < pw; ++x) {
+                unsigned char* o = &rgba[((size_t)(ps.y0 + y * ps.dy) * W + (ps.x0 + x * ps.dx)) * 4];
+                auto sample = [&](int ch) -> unsigned {          // channel value reduced to 8 bits the way stb_image does (high byte)
+                    if (depth == 16) return row[((size_t)x * channels + ch) * 2];
+                    if (depth == 8) return row[(size_t)x * channels + ch];
+                    const size_t bit = ((size_t)x * channels + ch) * depth;
+                    const unsigned v = (row[bit >> 3] >> (8 - depth - (bit & 7))) & ((1u << depth) - 1);
+                    return ctype == 3 ? v : v * 255u / ((1u << depth) - 1);
+                };
+                switch (ctype) {
+                    case 0: {
+                        const unsigned g = sample(0);
+                        o[0] = o[1] = o[2] = (unsigned char)g; o[3] = 255;
+                        if (trns.size() >= 2 && depth <= 8 && g == (unsigned)(trns[1] * (depth < 8 ? 255u / ((1u << depth) - 1) : 1u))) o[3] = 0;
                         break;
-                case 3: { unsigned idx = sample(0);
-                          if (idx * 3 + 2 >= plte.size()) { o[0] = o[1] = o[2] = 0; o[3] = 255; break; }
-                          o[0] = plte[idx * 3]; o[1] = plte[idx * 3 + 1]; o[2] = plte[idx * 3 + 2]; o[3] = idx < trns.size() ? trns[idx] : 255; break; }
-                case 4: { unsigned g = sample(0); o[0] = o[1] = o[2] = (unsigned char)g; o[3] = (unsigned char)sample(1); break; }
-                default: o[0] = (unsigned char)sample(0); o[1] = (unsigned char)sample(1); o[2] = (unsigned char)sample(2); o[3] = (unsigned char)sample(3);
+                    }
+                    case 2: o[0] = (unsigned char)sample(0); o[1] = (unsigned char)sample(1); o[2] = (unsigned char)sample(2); o[3] = 255;
+                            if (trns.size() >= 6 && depth == 8 && o[0] == trns[1] && o[1] == trns[3] && o[2] == trns[5]) o[3] = 0;
+                            break;
+                    case 3: { unsigned idx = sample(0);
+                              if (idx * 3 + 2 >= plte.size()) { o[0] = o[1] = o[2] = 0; o[3] = 255; break; }
+                              o[0] = plte[idx * 3]; o[1] = plte[idx * 3 + 1]; o[2] = plte[idx * 3 + 2]; o[3] = idx < trns.size() ? trns[idx] : 255; break; }
+                    case 4: { unsigned g = sample(0); o[0] = o[1] = o[2] = (unsigned char)g; o[3] = (unsigned char)sample(1); break; }
+                    default: o[0] = (unsigned char)sample(0); o[1] = (unsigned char)sample(1); o[2] = (unsigned char)sample(2); o[3] = (unsigned char)sample(3);
+                }
             }
         }
     }
