@@ -33,20 +33,25 @@ def ktx1_cube(levels, kind, big_endian=False, stored_levels=None, key_values=b""
     return out
 
 
-def ktx2_cube(levels, kind):
-    """levels[l][f] -> bytes of a KTX 2.0 file (no supercompression, empty DFD / key-value blocks; mip levels stored
-    smallest first as the specification requires)."""
+def ktx2_cube(levels, kind, scheme=0):
+    """levels[l][f] -> bytes of a KTX 2.0 file (empty DFD / key-value blocks; mip levels stored smallest first as the
+    specification requires).  scheme: supercompressionScheme — 0 none, 3 ZLIB (each level deflated on its own); any other value
+    is written into the header with the level data left as it is (for the refusal test)."""
+    import zlib
     size = levels[0][0].shape[0]
     n = len(levels)
     header = bytes([0xAB, 0x4B, 0x54, 0x58, 0x20, 0x32, 0x30, 0xBB, 0x0D, 0x0A, 0x1A, 0x0A])
-    header += struct.pack("<9I", VK[kind], 2 if kind == "f16" else 1, size, size, 0, 0, 6, n, 0)
+    header += struct.pack("<9I", VK[kind], 2 if kind == "f16" else 1, size, size, 0, 0, 6, n, scheme)
     index_off = len(header) + 4 * 4 + 2 * 8
     data_off = index_off + n * 24
     data_off += -data_off % 16
-    blobs, offsets = [], [0] * n
+    blobs, offsets, stored = [], [0] * n, [0] * n
     cur = data_off
     for l in reversed(range(n)):
         blob = b"".join(_bytes(f, kind) for f in levels[l])
+        if scheme == 3:
+            blob = zlib.compress(blob, 6)
+        stored[l] = len(blob)
         cur += -cur % 16
         offsets[l] = cur
         blobs.append((cur, blob))
@@ -54,7 +59,7 @@ def ktx2_cube(levels, kind):
     out = header + struct.pack("<4I2Q", 0, 0, 0, 0, 0, 0)
     for l in range(n):
         ln = len(_bytes(levels[l][0], kind)) * 6
-        out += struct.pack("<3Q", offsets[l], ln, ln)
+        out += struct.pack("<3Q", offsets[l], stored[l], ln)
     for off, blob in blobs:
         out += b"\0" * (off - len(out)) + blob
     return out

@@ -22,7 +22,7 @@ def decode(data: bytes):
     lib.vke_decode_ktx.restype = C.c_int
     info = (C.c_uint32 * 5)()
     err = C.create_string_buffer(256)
-    out = np.zeros(len(data), np.uint8)
+    out = np.zeros(max(len(data), 1 << 16), np.uint8)      # (a supercompressed file is smaller than its texels)
     rc = lib.vke_decode_ktx(data, len(data), info, out.ctypes.data, out.nbytes, err, len(err))
     if rc != 0:
         raise ValueError(err.value.decode())
@@ -41,13 +41,14 @@ def flat(levels, kind):
 
 
 @pytest.mark.parametrize("kind", ["unorm", "srgb", "f16"])
-@pytest.mark.parametrize("container", ["ktx1", "ktx1_big_endian", "ktx1_key_values", "ktx2"])
+@pytest.mark.parametrize("container", ["ktx1", "ktx1_big_endian", "ktx1_key_values", "ktx2", "ktx2_zlib"])
 def test_decoder_returns_the_files_texels(kind, container):
     lv = levels_of(kind)
     data = {"ktx1": lambda: ktx_util.ktx1_cube(lv, kind),
             "ktx1_big_endian": lambda: ktx_util.ktx1_cube(lv, kind, big_endian=True),
             "ktx1_key_values": lambda: ktx_util.ktx1_cube(lv, kind, key_values=b"KTXorientation\0S=r,T=d\0"),
-            "ktx2": lambda: ktx_util.ktx2_cube(lv, kind)}[container]()
+            "ktx2": lambda: ktx_util.ktx2_cube(lv, kind),
+            "ktx2_zlib": lambda: ktx_util.ktx2_cube(lv, kind, scheme=3)}[container]()
     info, out = decode(data)
     want = flat(lv, kind)
     assert info[:3] == [16, 16, 3] and info[3] == {"unorm": 0, "srgb": 1, "f16": 2}[kind] and info[4] == 0
@@ -61,6 +62,11 @@ def test_decoder_refuses_what_it_cannot_read():
                      (good[:28] + (0x8051).to_bytes(4, "little") + good[32:], "format"),          # GL_RGB8
                      (good[:52] + (1).to_bytes(4, "little") + good[56:], "cube"),                 # one face: a 2-D texture
                      (good[:56] + (9).to_bytes(4, "little") + good[60:], "levels")]:              # 16x16 has five levels
+        with pytest.raises(ValueError):
+            decode(bad)
+    z = ktx_util.ktx2_cube(lv, "f16", scheme=3)
+    for bad in (ktx_util.ktx2_cube(lv, "f16", scheme=2), ktx_util.ktx2_cube(lv, "f16", scheme=1),      # Zstandard, BasisLZ
+                z[:-9] + bytes(9)):                                                                   # a deflate stream cut short
         with pytest.raises(ValueError):
             decode(bad)
     info, _ = decode(ktx_util.ktx1_cube(lv[:1], "srgb" if False else "f16", stored_levels=0))

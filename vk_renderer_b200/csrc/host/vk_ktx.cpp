@@ -1,4 +1,5 @@
 // vk_ktx.cpp — see vk_ktx.h.  Layouts follow the Khronos KTX File Format Specification 1.1 and 2.0.
+#include <zlib.h>
 #include "vk_ktx.h"
 
 #include <algorithm>
@@ -89,7 +90,8 @@ bool decode_ktx2(const uint8_t* bytes, size_t size, KtxCube& out, std::string* e
         !r.u32(36, faces) || !r.u32(40, levels) || !r.u32(44, scheme))
         return fail(error, "KTX2: truncated header");
     if (faces != 6 || layers > 0 || d > 0) return fail(error, "KTX2: not a (non-array) cube map");
-    if (scheme != 0) return fail(error, "KTX2: supercompressed data is not supported");
+    // supercompressionScheme: 0 none, 3 ZLIB (every level deflated on its own); BasisLZ (1) and Zstandard (2) are refused
+    if (scheme != 0 && scheme != 3) return fail(error, "KTX2: BasisLZ / Zstandard supercompression is not supported (none and ZLIB are)");
     if (w == 0 || h == 0 || w != h || w > 16384) return fail(error, "KTX2: bad cube extent");
     size_t bpt;
     if (vkFormat == VK_FORMAT_R8G8B8A8_UNORM) { out.format = VKR_FORMAT_R8G8B8A8_UNORM; bpt = 4; }
@@ -108,10 +110,19 @@ bool decode_ktx2(const uint8_t* bytes, size_t size, KtxCube& out, std::string* e
             !r.u64(indexOff + (size_t)l * 24 + 16, uncompressed))
             return fail(error, "KTX2: truncated level index");
         const size_t want = level_texels(w, h, l) * bpt;
-        if (byteLength != (uint64_t)want * 6) return fail(error, "KTX2: level length does not match its extent");
         if (byteOffset > size || byteLength > size - byteOffset) return fail(error, "KTX2: truncated level");
+        const uint8_t* texels = bytes + byteOffset;
+        std::vector<uint8_t> inflated;
+        if (scheme == 3) {
+            if (uncompressed != (uint64_t)want * 6) return fail(error, "KTX2: level length does not match its extent");
+            inflated.resize(want * 6);
+            uLongf got = (uLongf)inflated.size();
+            if (uncompress(inflated.data(), &got, texels, (uLong)byteLength) != Z_OK || got != inflated.size())
+                return fail(error, "KTX2: a ZLIB-compressed level does not inflate to its extent");
+            texels = inflated.data();
+        } else if (byteLength != (uint64_t)want * 6) return fail(error, "KTX2: level length does not match its extent");
         for (uint32_t f = 0; f < 6; ++f)
-            out.images[(size_t)l * 6 + f].assign(bytes + byteOffset + (size_t)f * want, bytes + byteOffset + (size_t)(f + 1) * want);
+            out.images[(size_t)l * 6 + f].assign(texels + (size_t)f * want, texels + (size_t)(f + 1) * want);
     }
     return true;
 }
