@@ -33,10 +33,34 @@ def ktx1_cube(levels, kind, big_endian=False, stored_levels=None, key_values=b""
     return out
 
 
+def _zstd():
+    """ZSTD_compress of the system's libzstd through ctypes (the image has the library but no Python binding); None without it."""
+    import ctypes
+    try:
+        lib = ctypes.CDLL("libzstd.so.1")
+    except OSError:
+        return None
+    lib.ZSTD_compressBound.restype = ctypes.c_size_t; lib.ZSTD_compressBound.argtypes = [ctypes.c_size_t]
+    lib.ZSTD_compress.restype = ctypes.c_size_t
+    lib.ZSTD_compress.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_char_p, ctypes.c_size_t, ctypes.c_int]
+    lib.ZSTD_isError.restype = ctypes.c_uint; lib.ZSTD_isError.argtypes = [ctypes.c_size_t]
+
+    def compress(data: bytes) -> bytes:
+        cap = lib.ZSTD_compressBound(len(data))
+        buf = ctypes.create_string_buffer(cap)
+        n = lib.ZSTD_compress(buf, cap, data, len(data), 3)
+        assert not lib.ZSTD_isError(n)
+        return buf.raw[:n]
+    return compress
+
+
+zstd_compress = _zstd()
+
+
 def ktx2_cube(levels, kind, scheme=0):
     """levels[l][f] -> bytes of a KTX 2.0 file (empty DFD / key-value blocks; mip levels stored smallest first as the
-    specification requires).  scheme: supercompressionScheme — 0 none, 3 ZLIB (each level deflated on its own); any other value
-    is written into the header with the level data left as it is (for the refusal test)."""
+    specification requires).  scheme: supercompressionScheme — 0 none, 2 Zstandard, 3 ZLIB (each level compressed on its own); any
+    other value is written into the header with the level data left as it is (for the refusal test)."""
     import zlib
     size = levels[0][0].shape[0]
     n = len(levels)
@@ -51,6 +75,8 @@ def ktx2_cube(levels, kind, scheme=0):
         blob = b"".join(_bytes(f, kind) for f in levels[l])
         if scheme == 3:
             blob = zlib.compress(blob, 6)
+        elif scheme == 2 and zstd_compress is not None:
+            blob = zstd_compress(blob)
         stored[l] = len(blob)
         cur += -cur % 16
         offsets[l] = cur

@@ -63,7 +63,7 @@ def build_engine(force=False):
         return target
     srcs = [s for s in deps if s.endswith(".cpp")]
     cmd = ["g++", "-O2", "-std=c++20", "-ffp-contract=off", "-fPIC", "-shared", "-Wall", "-I", os.path.join(ROOT, "include"),
-           "-o", target + ".tmp", *srcs, "-L", PKG, "-lvkr", "-Wl,-rpath,$ORIGIN", "-lpthread", "-lz"]   # zlib: PNG images of glTF files
+           "-o", target + ".tmp", *srcs, "-L", PKG, "-lvkr", "-Wl,-rpath,$ORIGIN", "-lpthread", "-lz", "-ldl"]   # zlib: PNG images of glTF files, KTX2 levels; dl: libzstd looked up when a Zstandard KTX2 file is met
     subprocess.run(cmd, check=True)
     os.replace(target + ".tmp", target)
     return target

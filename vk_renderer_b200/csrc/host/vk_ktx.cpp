@@ -1,4 +1,5 @@
 // vk_ktx.cpp — see vk_ktx.h.  Layouts follow the Khronos KTX File Format Specification 1.1 and 2.0.
+#include <dlfcn.h>
 #include <zlib.h>
 #include "vk_ktx.h"
 
@@ -83,6 +84,18 @@ bool decode_ktx1(const uint8_t* bytes, size_t size, KtxCube& out, std::string* e
     return true;
 }
 
+// Zstandard (KTX2 supercompressionScheme 2, what `toktx --zcmp` writes): the system's libzstd, looked up at the first such file —
+// the engine library does not link it, so a machine without it still loads every other file and refuses these with a reason.
+typedef size_t (*ZstdDecompressFn)(void* dst, size_t dstCapacity, const void* src, size_t compressedSize);
+typedef unsigned (*ZstdIsErrorFn)(size_t code);
+static bool zstd_functions(ZstdDecompressFn& decompress, ZstdIsErrorFn& isError) {
+    static void* lib = dlopen("libzstd.so.1", RTLD_NOW | RTLD_LOCAL);
+    if (!lib) return false;
+    decompress = (ZstdDecompressFn)dlsym(lib, "ZSTD_decompress");
+    isError = (ZstdIsErrorFn)dlsym(lib, "ZSTD_isError");
+    return decompress != nullptr && isError != nullptr;
+}
+
 bool decode_ktx2(const uint8_t* bytes, size_t size, KtxCube& out, std::string* error) {
     Reader r{bytes, size};
     uint32_t vkFormat, typeSize, w, h, d, layers, faces, levels, scheme;
@@ -90,8 +103,10 @@ bool decode_ktx2(const uint8_t* bytes, size_t size, KtxCube& out, std::string* e
         !r.u32(36, faces) || !r.u32(40, levels) || !r.u32(44, scheme))
         return fail(error, "KTX2: truncated header");
     if (faces != 6 || layers > 0 || d > 0) return fail(error, "KTX2: not a (non-array) cube map");
-    // supercompressionScheme: 0 none, 3 ZLIB (every level deflated on its own); BasisLZ (1) and Zstandard (2) are refused
-    if (scheme != 0 && scheme != 3) return fail(error, "KTX2: BasisLZ / Zstandard supercompression is not supported (none and ZLIB are)");
+    // supercompressionScheme: 0 none, 2 Zstandard, 3 ZLIB (every level compressed on its own); BasisLZ (1) is refused
+    if (scheme != 0 && scheme != 2 && scheme != 3) return fail(error, "KTX2: BasisLZ supercompression is not supported (none, Zstandard and ZLIB are)");
+    ZstdDecompressFn zstdDecompress = nullptr; ZstdIsErrorFn zstdIsError = nullptr;
+    if (scheme == 2 && !zstd_functions(zstdDecompress, zstdIsError)) return fail(error, "KTX2: Zstandard supercompression needs libzstd.so.1, which this machine does not have");
     if (w == 0 || h == 0 || w != h || w > 16384) return fail(error, "KTX2: bad cube extent");
     size_t bpt;
     if (vkFormat == VK_FORMAT_R8G8B8A8_UNORM) { out.format = VKR_FORMAT_R8G8B8A8_UNORM; bpt = 4; }
@@ -113,12 +128,17 @@ bool decode_ktx2(const uint8_t* bytes, size_t size, KtxCube& out, std::string* e
         if (byteOffset > size || byteLength > size - byteOffset) return fail(error, "KTX2: truncated level");
         const uint8_t* texels = bytes + byteOffset;
         std::vector<uint8_t> inflated;
-        if (scheme == 3) {
+        if (scheme == 3 || scheme == 2) {
             if (uncompressed != (uint64_t)want * 6) return fail(error, "KTX2: level length does not match its extent");
             inflated.resize(want * 6);
-            uLongf got = (uLongf)inflated.size();
-            if (uncompress(inflated.data(), &got, texels, (uLong)byteLength) != Z_OK || got != inflated.size())
-                return fail(error, "KTX2: a ZLIB-compressed level does not inflate to its extent");
+            if (scheme == 3) {
+                uLongf got = (uLongf)inflated.size();
+                if (uncompress(inflated.data(), &got, texels, (uLong)byteLength) != Z_OK || got != inflated.size())
+                    return fail(error, "KTX2: a ZLIB-compressed level does not inflate to its extent");
+            } else {
+                const size_t got = zstdDecompress(inflated.data(), inflated.size(), texels, (size_t)byteLength);
+                if (zstdIsError(got) || got != inflated.size()) return fail(error, "KTX2: a Zstandard-compressed level does not decompress to its extent");
+            }
             texels = inflated.data();
         } else if (byteLength != (uint64_t)want * 6) return fail(error, "KTX2: level length does not match its extent");
         for (uint32_t f = 0; f < 6; ++f)
